@@ -1,0 +1,136 @@
+/* b2rf — B200-native MLlib-compatible decision-tree / random-forest regression training.
+ *
+ * C-ABI of libb2rf.so.  This is the drop-in boundary for the hot path that the reference reaches through
+ *   pyspark.ml.regression.DecisionTreeRegressor / RandomForestRegressor  .fit()
+ *   (reference call sites: `ML 06 - Decision Trees.py:73-75,118,126`,
+ *    `ML 07 - Random Forests and Hyperparameter Tuning.py:41,107-116,143-149`, `ML 08 - Hyperopt.py:71,97-98`)
+ * i.e. JavaEstimator._fit_java -> py4j -> org.apache.spark.ml.tree.impl.RandomForest.run (Spark MLlib 3.1.2, not
+ * vendored in the reference).  Each entry point names the MLlib function it replaces.
+ *
+ * Conventions
+ *  - Every function returns 0 on success, <0 on error; b2rf_last_error() gives the thread-local message.
+ *    Messages for user errors repeat MLlib's text (e.g. the maxBins requirement `ML 06:81,110-118` expects).
+ *  - Pointers named d_* are DEVICE pointers owned by the caller (e.g. torch tensors); the library never frees them.
+ *    Pointers named h_* are host pointers.  `stream` is a cudaStream_t passed as void*; calls are asynchronous on it
+ *    unless stated otherwise.
+ *  - No CPU fallback exists: without a CUDA device every compute entry point fails with B2RF_ERR_CUDA.
+ *  - Layouts: X is row-major f64 [rows][ldx]; the bin matrix is COLUMN-major uint8 bins[F][ldb] (ldb % 128 == 0);
+ *    bag weights w[T][ldw] uint8; per-tree row->node ids node[T][ldn] int32 (-1 = row inactive for that tree);
+ *    histograms hist[cells][4] f64 = (weight-sum, sum w*y, sum w*y*y, raw count) per (node-slot, feature, bin).
+ */
+#ifndef B2RF_H
+#define B2RF_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2RF_OK 0
+#define B2RF_ERR_ARG (-1)      /* bad argument */
+#define B2RF_ERR_MAXBINS (-2)  /* MLlib: maxBins smaller than a categorical arity */
+#define B2RF_ERR_DATA (-3)     /* MLlib: invalid categorical value */
+#define B2RF_ERR_CUDA (-4)     /* CUDA runtime error / no device */
+#define B2RF_ERR_STATE (-5)    /* call sequence error */
+
+int b2rf_version(void);
+const char* b2rf_last_error(void);
+
+/* Parameters of one fit.  Mirrors the pyspark Params the labs set (`ML 06:118`, `ML 07:41,74-77`, `ML 08:71,97`). */
+typedef struct b2rf_params {
+  int32_t maxDepth;
+  int32_t maxBins;
+  int32_t minInstancesPerNode;
+  int32_t numTrees;
+  int32_t featuresPerNode;  /* resolved featureSubsetStrategy (b2rf_features_per_node) */
+  int32_t maxMemoryInMB;
+  int32_t bootstrap;
+  int32_t reserved;
+  double minInfoGain;
+  double minWeightFractionPerNode;
+  double subsamplingRate;
+  int64_t seed;
+} b2rf_params;
+
+/* DecisionTreeMetadata.buildMetadata featureSubsetStrategy table.  strategy: "auto","all","sqrt","log2","onethird",
+ * "n" (integer > 0) or a fraction in (0,1].  Returns the count or B2RF_ERR_ARG. */
+int b2rf_features_per_node(const char* strategy, int32_t F, int32_t numTrees);
+
+/* DecisionTreeMetadata.buildMetadata checks: fails with B2RF_ERR_MAXBINS and MLlib's message when a
+ * categorical arity exceeds maxPossibleBins = min(maxBins, numExamples) — the error `ML 06:81,91-92` expects.
+ * On success returns metadata.maxBins (= max over features of the initial numBins), the value findSplits squares. */
+int b2rf_check_metadata(const b2rf_params* params, int32_t F, const int32_t* h_arity, int64_t numExamples);
+
+/* ---- K1: RandomForest.findSplits / findSplitsForContinuousFeature ------------------------ */
+/* samplesFractionForFindSplits: max(maxBins_meta^2, 10000) / N if smaller than N, else 1.0 */
+double b2rf_samples_fraction(int64_t numExamples, int32_t metaMaxBins);
+/* Row sample used when fraction < 1 (replaces RDD.sample; per-global-row hash shared with the oracle).  Appends the
+ * kept rows of X[row0_global + i] (i < n_rows) to d_sample_out [cap][F]; *d_count (device int64, caller-zeroed) counts them. */
+int b2rf_sample_rows(const double* d_X, int64_t ldx, int64_t n_rows, int64_t row0_global, int32_t F, int64_t seed,
+                     double fraction, double* d_sample_out, int64_t cap, int64_t* d_count, void* stream);
+size_t b2rf_find_splits_workspace_bytes(int64_t n_sample, int32_t F);
+/* d_sample [n_sample][F]; d_arity[F] (0 = continuous); out: d_thresholds [F][maxPossibleBins-1], d_nsplits[F]. */
+int b2rf_find_splits(const double* d_sample, int64_t n_sample, int32_t F, const int32_t* d_arity, int32_t maxPossibleBins,
+                     double weightedNumSamples, double* d_thresholds, int32_t* d_nsplits, void* d_workspace,
+                     size_t workspace_bytes, void* stream);
+
+/* ---- K2: TreePoint.convertToTreeRDD / findBin (row a3) ------------------------------------------------------ */
+/* Bins rows [0,n_rows) of d_X into d_bins[f][row0 + i].  *d_err (int32, caller-zeroed) becomes feature+1 on an invalid
+ * categorical value. */
+int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const double* d_thresholds, const int32_t* d_nsplits,
+             const int32_t* d_arity, int32_t maxSplits, uint8_t* d_bins, int64_t ldb, int64_t row0, int32_t* d_err,
+             void* stream);
+
+/* ---- K3: BaggedPoint.convertToBaggedRDD (row a4) ------------------------------------------------------------- */
+/* One emulated Spark partition per thread: partition p (global index part0 + p) covers local rows
+ * [h_part_offsets[p], h_part_offsets[p+1]).  Writes d_w[t][row] and the initial d_node[t][row] (0 if w > 0 else -1). */
+int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t part0, int32_t T, double subsamplingRate,
+             int32_t bootstrap, uint8_t* d_w, int64_t ldw, int32_t* d_node, int64_t ldn, void* stream);
+
+/* ---- trainer: RandomForest.run driver loop (rows a1, a5, a9, a11) + K4/K5/K6 launches ------------------------ */
+typedef struct b2rf_trainer b2rf_trainer;
+
+/* h_arity[F], h_nsplits[F], h_thresholds[F][maxPossibleBins-1] (after K1).  numExamples = GLOBAL row count (all ranks).
+ * Fails with B2RF_ERR_MAXBINS and MLlib's message when a categorical arity exceeds min(maxBins, numExamples). */
+int b2rf_trainer_create(const b2rf_params* params, int32_t F, const int32_t* h_arity, const int32_t* h_nsplits,
+                        const double* h_thresholds, int64_t numExamples, b2rf_trainer** out);
+void b2rf_trainer_destroy(b2rf_trainer* t);
+/* Largest histogram (in cells of 4 doubles) any node group can need; the caller allocates d_hist with that many cells. */
+int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t);
+int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const double* d_y, const uint8_t* d_w, int64_t ldw,
+                      int32_t* d_node, int64_t ldn, int64_t n_rows_local, double* d_hist, int64_t hist_cells);
+/* selectNodesToSplit + K4 (findBestSplits.binSeqOp, row a6) with the fused K6 row routing (row a10).
+ * Returns 1 and sets *n_cells (histogram cells written, to be summed across ranks by the caller — row a7) when a group
+ * was launched, 0 when training is finished. */
+int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream);
+/* K5 binsToBestSplit (row a8) on the (reduced) histogram, then the driver tail (row a9).  Synchronises the stream. */
+int b2rf_trainer_end_group(b2rf_trainer* t, void* stream);
+/* timers: init, findSplits(0), findBestSplits(hist), chooseSplits, total — MLlib TimeTracker phase names; counters. */
+int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts4 /* groups, hist launches, rows*trees scanned, nodes */);
+/* finished forest, LearningNode.toNode(prune=true) in pre-order (row a11) */
+int b2rf_trainer_forest_sizes(b2rf_trainer* t, int64_t* n_nodes, int64_t* n_cats);
+int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature, double* h_threshold, int32_t* h_left,
+                        int32_t* h_right, double* h_prediction, double* h_impurity, double* h_gain, double* h_stats4,
+                        int32_t* h_ncat, int32_t* h_cat_off, int32_t* h_cat_len, double* h_cats);
+/* per-node decision trace in processing order: ints [n][5] = group, tree, heap node id, feature, split index;
+ * doubles [n][5] = gain, impurity, count, sum, sumsq */
+int64_t b2rf_trainer_trace_size(const b2rf_trainer* t);
+int b2rf_trainer_trace(const b2rf_trainer* t, int32_t* h_ints, double* h_dbls);
+
+/* ---- stand-alone kernels (same code the trainer launches), for testing and for callers with their own driver -- */
+/* K4: histogram of one node group.  d_slot_of_row [Tg][ldn] gives the group slot of each row per listed tree (-1 = skip);
+ * d_tree_ids[Tg]; d_slot_fo [slots][Fsub] pairs (feature, cell offset inside the slot); d_slot_base[slots] cells. */
+int b2rf_hist_build(const uint8_t* d_bins, int64_t ldb, int32_t F, const double* d_y, const uint8_t* d_w, int64_t ldw,
+                    const int32_t* d_slot_of_row, int64_t ldn, const int32_t* d_tree_ids, int32_t Tg, int64_t n_rows,
+                    const uint32_t* d_slot_fo, const int64_t* d_slot_base, int32_t Fsub, double* d_hist, void* stream);
+/* K7: TreeEnsembleModel.predict on raw features (rows a11): mean over trees, tree-order summation. */
+int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,
+                 const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_prediction,
+                 const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, const double* d_cats,
+                 double* d_out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

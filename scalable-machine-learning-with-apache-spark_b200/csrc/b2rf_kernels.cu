@@ -1,0 +1,777 @@
+// b2rf device code (sm_100a) + kernel launchers.
+//
+// Kernels:  K1 find_splits (RandomForest.findSplitsForContinuousFeature), K2 bin (TreePoint.findBin),
+// K3 bag (BaggedPoint.convertToBaggedRDD), K4 hist (DTStatsAggregator.update via binSeqOp) with the fused K6 row
+// routing (LearningNode.predictImpl), K5 best_split (RandomForest.binsToBestSplit), K7 predict.
+// Compiled with -fmad=false: MLlib's arithmetic is unfused JVM double arithmetic.
+#include "b2rf_internal.h"
+#include "../../include/b2rf.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+namespace b2rf {
+
+static thread_local std::string g_err;
+void set_error(const std::string& m) { g_err = m; }
+const char* last_error_cstr() { return g_err.c_str(); }
+bool cuda_ok(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return true;
+  g_err = std::string(what) + ": " + cudaGetErrorString(e);
+  return false;
+}
+int device_sm_count() {
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  if (dev != cached_dev) {
+    cudaDeviceProp p;
+    if (cudaGetDeviceProperties(&p, dev) != cudaSuccess) return 148;
+    cached = p.multiProcessorCount; cached_dev = dev;
+  }
+  return cached;
+}
+
+// =================================================================================================
+// small PTX helpers: mbarrier + 1-D bulk async copy (TMA engine, SASS UBLKCP)
+// =================================================================================================
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tWAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\tbra WAIT_%=;\n\tDONE_%=:\n\t}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// =================================================================================================
+// K4 (+K6): histogram build over TMA-staged column tiles of the bin matrix
+// =================================================================================================
+constexpr int HIST_THREADS = 512;
+constexpr int HIST_RPT = 2;                       // rows per thread per tile
+constexpr int HIST_R = HIST_THREADS * HIST_RPT;   // rows per tile (1024)
+constexpr int HIST_PAD = 16;                      // smem pitch padding (keeps 16-byte alignment for bulk copies)
+
+struct HistKArgs {
+  HistLaunch a;
+  int32_t R;         // rows per tile actually used (multiple of 128, <= HIST_R)
+  int32_t pitch;     // smem bytes per feature column
+  int32_t nbuf;      // 1 or 2 staging buffers
+  int64_t numTiles;
+};
+
+template <bool TRAVERSE>
+__global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k) {
+  extern __shared__ __align__(128) unsigned char smem[];
+  const HistLaunch& a = k.a;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem);  // 2 barriers
+  unsigned char* tiles = smem + 128;
+  const size_t bufBytes = (size_t)a.F * k.pitch;
+  const int tid = threadIdx.x;
+
+  if (tid == 0) {
+    mbar_init(&bars[0], 1);
+    mbar_init(&bars[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  auto issue = [&](int64_t tile, int buf) {
+    // warp 0: one bulk copy per feature column segment
+    const int64_t r0 = tile * k.R;
+    int64_t rem = a.n_rows - r0;
+    uint32_t nb = (uint32_t)(rem < k.R ? ((rem + 15) & ~(int64_t)15) : k.R);
+    if (tid == 0) mbar_expect_tx(&bars[buf], nb * (uint32_t)a.F);
+    __syncwarp();
+    for (int f = tid; f < a.F; f += 32) bulk_g2s(tiles + buf * bufBytes + (size_t)f * k.pitch, a.bins + (size_t)f * a.ldb + r0, nb, &bars[buf]);
+  };
+
+  int64_t it = 0;
+  const int64_t first = blockIdx.x;
+  if (first < k.numTiles && tid < 32) issue(first, 0);
+  for (int64_t tile = first; tile < k.numTiles; tile += gridDim.x, ++it) {
+    const int buf = (k.nbuf == 2) ? (int)(it & 1) : 0;
+    const int64_t nxt = tile + gridDim.x;
+    if (k.nbuf == 2 && nxt < k.numTiles && tid < 32) issue(nxt, buf ^ 1);
+    const uint32_t parity = (k.nbuf == 2) ? (uint32_t)((it >> 1) & 1) : (uint32_t)(it & 1);
+    mbar_wait(&bars[buf], parity);
+    const unsigned char* tb = tiles + buf * bufBytes;
+    const int64_t r0 = tile * k.R;
+
+    double yv[HIST_RPT];
+#pragma unroll
+    for (int q = 0; q < HIST_RPT; q++) {
+      const int r = tid + q * HIST_THREADS;
+      const int64_t row = r0 + r;
+      yv[q] = (r < k.R && row < a.n_rows) ? a.y[row] : 0.0;
+    }
+    for (int g = 0; g < a.Tg; g++) {
+      const int t = a.tree_ids[g];
+#pragma unroll
+      for (int q = 0; q < HIST_RPT; q++) {
+        const int r = tid + q * HIST_THREADS;
+        const int64_t row = r0 + r;
+        if (r >= k.R || row >= a.n_rows) continue;
+        int slot;
+        if (TRAVERSE) {
+          int32_t* np = a.node + (size_t)t * a.ldn + row;
+          int n = *np;
+          if (n < 0) continue;
+          const DNode* tn = a.dnodes + (size_t)t * a.nodeStride;
+          DNode d = tn[n];
+          bool moved = false;
+          while (d.feature >= 0) {  // K6: LearningNode.predictImpl on binned features, resumed from the cached node
+            const uint32_t bin = tb[(size_t)d.feature * k.pitch + r];
+            bool left;
+            if (d.aux & 0x80000000u) left = (a.catmasks[(size_t)(d.aux & 0x7fffffffu) * 8 + (bin >> 5)] >> (bin & 31)) & 1u;
+            else left = bin <= d.aux;
+            n = d.left + (left ? 0 : 1);
+            d = tn[n];
+            moved = true;
+          }
+          if (d.slot == SLOT_DEAD) { *np = -1; continue; }
+          if (moved) *np = n;
+          slot = d.slot;
+          if (slot < 0) continue;
+        } else {
+          slot = a.node[(size_t)g * a.ldn + row];
+          if (slot < 0) continue;
+        }
+        const uint32_t wv = a.w[(size_t)t * a.ldw + row];
+        if (wv == 0) continue;
+        const double dw = (double)wv;
+        const double wy = dw * yv[q];
+        const double wyy = wy * yv[q];
+        const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
+        double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
+        for (int j = 0; j < a.Fsub; j++) {
+          const uint2 e = fo[j];
+          const uint32_t bin = tb[(size_t)e.x * k.pitch + r];
+          double* c = hb + ((size_t)e.y + bin) * 4;
+          atomicAdd(c, dw);
+          atomicAdd(c + 1, wy);
+          atomicAdd(c + 2, wyy);
+        }
+      }
+    }
+    __syncthreads();  // tile fully consumed before its buffer is refilled
+    if (k.nbuf == 1 && nxt < k.numTiles && tid < 32) issue(nxt, 0);
+  }
+}
+
+cudaError_t launch_hist(const HistLaunch& a, bool traverse, cudaStream_t s, std::string* err) {
+  if (a.n_rows <= 0 || a.Tg <= 0) return cudaSuccess;
+  HistKArgs k;
+  k.a = a;
+  // tile geometry: largest R (multiple of 128, <= 1024) whose staging fits; double-buffer when possible
+  const size_t budget = 200 * 1024;
+  int R = HIST_R, nbuf = 2;
+  while (R > 128 && (size_t)2 * a.F * (R + HIST_PAD) > budget) R -= 128;
+  if ((size_t)2 * a.F * (R + HIST_PAD) > budget) { nbuf = 1; R = HIST_R; while (R > 128 && (size_t)a.F * (R + HIST_PAD) > budget) R -= 128; }
+  if ((size_t)nbuf * a.F * (R + HIST_PAD) > budget) {
+    if (err) *err = "hist: too many features for one shared-memory tile (F > 1400 unsupported)";
+    return cudaErrorInvalidValue;
+  }
+  k.R = R; k.pitch = R + HIST_PAD; k.nbuf = nbuf;
+  k.numTiles = (a.n_rows + R - 1) / R;
+  const size_t smem = 128 + (size_t)nbuf * a.F * k.pitch;
+  auto kern = traverse ? hist_kernel<true> : hist_kernel<false>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  int64_t grid = device_sm_count();
+  if (grid > k.numTiles) grid = k.numTiles;
+  kern<<<(unsigned)grid, HIST_THREADS, smem, s>>>(k);
+  return cudaGetLastError();
+}
+
+__global__ void scatter_dnodes_kernel(DNode* dn, const DNodeUpdate* u, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) dn[u[i].pos] = u[i].node;
+}
+cudaError_t launch_scatter_dnodes(DNode* dnodes, const DNodeUpdate* upd, int64_t n, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  scatter_dnodes_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(dnodes, upd, n);
+  return cudaGetLastError();
+}
+
+// =================================================================================================
+// K5: binsToBestSplit — one warp per node slot
+// =================================================================================================
+constexpr int SPLIT_WARPS = 4;
+constexpr int SPLIT_MAXB = 256;
+struct SplitSmem {
+  double raw[SPLIT_MAXB][3];
+  double cum[SPLIT_MAXB][3];
+  double key[SPLIT_MAXB];
+  uint16_t order[SPLIT_MAXB];
+};
+
+__device__ __forceinline__ double variance_calc(double cnt, double sum, double sq) {  // Variance.calculate
+  if (cnt == 0) return 0.0;
+  const double sl = sq - (sum * sum) / cnt;
+  return sl / cnt;
+}
+
+__global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const SplitLaunch a) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slot = blockIdx.x * SPLIT_WARPS + warp;
+  if (slot >= a.nSlots) return;
+  SplitSmem& sm = reinterpret_cast<SplitSmem*>(smraw)[warp];
+  const unsigned FULL = 0xffffffffu;
+
+  double P[3] = {0, 0, 0};
+  double Pimp = 0;
+  bool haveP = a.hasParent[slot] != 0;
+  if (haveP) {
+    P[0] = a.parent4[(size_t)slot * 4]; P[1] = a.parent4[(size_t)slot * 4 + 1]; P[2] = a.parent4[(size_t)slot * 4 + 2];
+    Pimp = variance_calc(P[0], P[1], P[2]);
+  }
+  bool any = false;
+  double bestGain = 0; int bestF = -1, bestS = -1, bestJ = -1;
+  double bL[3] = {0, 0, 0}, bR[3] = {0, 0, 0};
+  uint32_t bmask[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  int firstF = -1;
+  const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
+  const double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
+
+  for (int j = 0; j < a.Fsub; j++) {
+    const uint2 e = fo[j];
+    const int f = (int)e.x;
+    if (firstF < 0) firstF = f;
+    const int nb = a.numBins[f];
+    const int ns = nb - 1;
+    if (ns <= 0) continue;
+    const double* cells = hb + (size_t)e.y * 4;
+    __syncwarp();
+    for (int b = lane; b < nb; b += 32) {
+      sm.raw[b][0] = cells[(size_t)b * 4]; sm.raw[b][1] = cells[(size_t)b * 4 + 1]; sm.raw[b][2] = cells[(size_t)b * 4 + 2];
+    }
+    __syncwarp();
+    const bool cat = a.isCat[f] != 0;
+    if (cat) {
+      for (int b = lane; b < nb; b += 32) sm.key[b] = sm.raw[b][0] != 0 ? sm.raw[b][1] / sm.raw[b][0] : DBL_MAX;
+      __syncwarp();
+      for (int b = lane; b < nb; b += 32) {  // stable rank by counting == List.sortBy(_._2)
+        const double kb = sm.key[b];
+        int rank = 0;
+        for (int c = 0; c < nb; c++) { const double kc = sm.key[c]; rank += (kc < kb) || (kc == kb && c < b); }
+        sm.order[rank] = (uint16_t)b;
+      }
+    } else {
+      for (int b = lane; b < nb; b += 32) sm.order[b] = (uint16_t)b;
+    }
+    __syncwarp();
+    if (lane == 0) {  // sequential prefix in MLlib's association order: h[next] += h[cur]
+      int o = sm.order[0];
+      double c0 = sm.raw[o][0], c1 = sm.raw[o][1], c2 = sm.raw[o][2];
+      sm.cum[0][0] = c0; sm.cum[0][1] = c1; sm.cum[0][2] = c2;
+      for (int q = 1; q < nb; q++) {
+        o = sm.order[q];
+        c0 = sm.raw[o][0] + c0; c1 = sm.raw[o][1] + c1; c2 = sm.raw[o][2] + c2;
+        sm.cum[q][0] = c0; sm.cum[q][1] = c1; sm.cum[q][2] = c2;
+      }
+    }
+    __syncwarp();
+    const double T0 = sm.cum[nb - 1][0], T1 = sm.cum[nb - 1][1], T2 = sm.cum[nb - 1][2];
+    if (!haveP) {  // root: parent = left + right of the first evaluated candidate (calculateImpurityStats, stats == null)
+      const double l0 = sm.cum[0][0], l1 = sm.cum[0][1], l2 = sm.cum[0][2];
+      P[0] = l0 + (T0 - l0); P[1] = l1 + (T1 - l1); P[2] = l2 + (T2 - l2);
+      Pimp = variance_calc(P[0], P[1], P[2]);
+      haveP = true;
+    }
+    double lg = 0; int ls = -1;
+    for (int s = lane; s < ns; s += 32) {
+      const double L0 = sm.cum[s][0], L1 = sm.cum[s][1], L2 = sm.cum[s][2];
+      const double R0 = T0 - L0, R1 = T1 - L1, R2 = T2 - L2;
+      double gain;
+      if (L0 < a.minInstances || R0 < a.minInstances || L0 < a.minWeight || R0 < a.minWeight) gain = -DBL_MAX;
+      else {
+        const double total = L0 + R0;
+        const double li = variance_calc(L0, L1, L2), ri = variance_calc(R0, R1, R2);
+        const double lw = L0 / total, rw = R0 / total;
+        gain = Pimp - lw * li - rw * ri;
+        if (gain < a.minInfoGain) gain = -DBL_MAX;
+      }
+      if (ls < 0 || gain > lg) { lg = gain; ls = s; }
+    }
+    // warp argmax: larger gain wins, ties -> lower split index (maxBy keeps the first maximum)
+    for (int o = 16; o > 0; o >>= 1) {
+      const double og = __shfl_xor_sync(FULL, lg, o);
+      const int os = __shfl_xor_sync(FULL, ls, o);
+      if (os >= 0 && (ls < 0 || og > lg || (og == lg && os < ls))) { lg = og; ls = os; }
+    }
+    if (!any || lg > bestGain) {  // strict >: the earliest feature in subset order wins ties
+      any = true; bestGain = lg; bestF = f; bestS = ls; bestJ = j;
+      bL[0] = sm.cum[ls][0]; bL[1] = sm.cum[ls][1]; bL[2] = sm.cum[ls][2];
+      bR[0] = T0 - bL[0]; bR[1] = T1 - bL[1]; bR[2] = T2 - bL[2];
+      for (int q = 0; q < 8; q++) bmask[q] = 0;
+      if (cat) for (int q = 0; q <= ls; q++) { const int c = sm.order[q]; bmask[c >> 5] |= 1u << (c & 31); }
+    }
+  }
+  (void)bestJ;
+  if (lane == 0) {
+    SplitRec r;
+    memset(&r, 0, sizeof r);
+    if (!any) {  // no feature with candidate splits: dummy split, invalid stats on the node totals
+      if (!haveP && firstF >= 0) {
+        const double* cells = hb + (size_t)fo[0].y * 4;
+        const int nb = a.numBins[firstF];
+        for (int b = 0; b < nb; b++) { P[0] += cells[(size_t)b * 4]; P[1] += cells[(size_t)b * 4 + 1]; P[2] += cells[(size_t)b * 4 + 2]; }
+        Pimp = variance_calc(P[0], P[1], P[2]);
+      }
+      r.gain = -DBL_MAX; r.valid = 0; r.feature = firstF < 0 ? 0 : firstF; r.splitIdx = 0;
+    } else {
+      r.gain = bestGain; r.valid = bestGain != -DBL_MAX; r.feature = bestF; r.splitIdx = bestS;
+      for (int q = 0; q < 3; q++) { r.left[q] = bL[q]; r.right[q] = bR[q]; }
+      r.left[3] = bL[0]; r.right[3] = bR[0];
+      r.leftImp = variance_calc(bL[0], bL[1], bL[2]);
+      r.rightImp = variance_calc(bR[0], bR[1], bR[2]);
+      for (int q = 0; q < 8; q++) r.catmask[q] = bmask[q];
+    }
+    r.impurity = Pimp;
+    r.parent[0] = P[0]; r.parent[1] = P[1]; r.parent[2] = P[2]; r.parent[3] = P[0];
+    a.out[slot] = r;
+  }
+}
+
+cudaError_t launch_best_split(const SplitLaunch& a, cudaStream_t s) {
+  if (a.nSlots <= 0) return cudaSuccess;
+  const size_t smem = sizeof(SplitSmem) * SPLIT_WARPS;
+  cudaError_t e = cudaFuncSetAttribute(best_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  best_split_kernel<<<(a.nSlots + SPLIT_WARPS - 1) / SPLIT_WARPS, SPLIT_WARPS * 32, smem, s>>>(a);
+  return cudaGetLastError();
+}
+
+// =================================================================================================
+// K1: findSplits
+// =================================================================================================
+__host__ __device__ inline uint64_t mix64(uint64_t z) {
+  z = (z ^ (z >> 30)) * 0xbf58476d1ce4e5b9ULL;
+  z = (z ^ (z >> 27)) * 0x94d049bb133111ebULL;
+  return z ^ (z >> 31);
+}
+
+__global__ void sample_rows_kernel(const double* X, int64_t ldx, int64_t n_rows, int64_t row0, int F, uint64_t seedWord, double fraction,
+                                   double* out, int64_t cap, unsigned long long* count) {
+  // one warp per row: lane 0 decides, the warp copies the row
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= n_rows) return;
+  const uint64_t h = mix64(seedWord + (uint64_t)(row0 + row) * 0x9E3779B97F4A7C15ULL);
+  const bool keep = ((double)(h >> 11) * 0x1.0p-53) < fraction;
+  if (!keep) return;
+  unsigned long long pos = 0;
+  if (lane == 0) pos = atomicAdd(count, 1ULL);
+  pos = __shfl_sync(0xffffffffu, pos, 0);
+  if ((int64_t)pos >= cap) return;
+  for (int f = lane; f < F; f += 32) out[(size_t)pos * F + f] = X[(size_t)row * ldx + f];
+}
+
+// One CTA per feature.  Workspace: F * n_pad doubles (sorted non-zero sample values, +inf padded).
+__global__ void __launch_bounds__(1024) find_splits_kernel(const double* sample, int64_t n_s, int F, const int32_t* arity, int maxSplits,
+                                                            double wns, double* thresholds, int32_t* nsplits, double* ws, int64_t n_pad) {
+  const int f = blockIdx.x;
+  if (arity[f] != 0) { if (threadIdx.x == 0) nsplits[f] = 0; return; }
+  double* v = ws + (size_t)f * n_pad;
+  __shared__ unsigned long long s_cnt;
+  __shared__ unsigned long long s_distinct;
+  if (threadIdx.x == 0) { s_cnt = 0; s_distinct = 0; }
+  __syncthreads();
+  unsigned long long mycnt = 0;
+  for (int64_t i = threadIdx.x; i < n_pad; i += blockDim.x) {
+    double x = INFINITY;
+    if (i < n_s) { const double xv = sample[(size_t)i * F + f]; if (xv != 0.0) { x = xv; mycnt++; } }
+    v[i] = x;
+  }
+  atomicAdd(&s_cnt, mycnt);
+  __syncthreads();
+  // bitonic sort ascending (n_pad is a power of two)
+  for (int64_t kk = 2; kk <= n_pad; kk <<= 1) {
+    for (int64_t jj = kk >> 1; jj > 0; jj >>= 1) {
+      for (int64_t i = threadIdx.x; i < n_pad; i += blockDim.x) {
+        const int64_t ixj = i ^ jj;
+        if (ixj > i) {
+          const double x = v[i], y = v[ixj];
+          const bool up = (i & kk) == 0;
+          if ((x > y) == up) { v[i] = y; v[ixj] = x; }
+        }
+      }
+      __syncthreads();
+    }
+  }
+  const int64_t c = (int64_t)s_cnt;  // number of non-zero sample values
+  unsigned long long myd = 0;
+  for (int64_t i = threadIdx.x; i < c; i += blockDim.x) if (i == 0 || v[i] != v[i - 1]) myd++;
+  atomicAdd(&s_distinct, myd);
+  __syncthreads();
+  if (threadIdx.x != 0) return;
+  double* out = thresholds + (size_t)f * maxSplits;
+  if (c == 0) { nsplits[f] = 0; return; }
+  const double partNum = (double)c;
+  const double tol = 0x1.0p-52 * (double)c * 100;
+  const bool hasZero = (wns - partNum) > tol;
+  const double zeroCnt = wns - partNum;
+  const int64_t distinct = (int64_t)s_distinct + (hasZero ? 1 : 0);
+  const int64_t possible = distinct - 1;
+  if (possible == 0) { nsplits[f] = 0; return; }
+  const bool all = possible <= maxSplits;
+  const double stride = wns / (double)(maxSplits + 1);
+  // run iterator over the merged ascending sequence (negatives, [virtual zero], positives)
+  int64_t i = 0;
+  bool zeroDone = !hasZero;
+  int nout = 0;
+  bool firstRun = true;
+  double prevVal = 0, cur = 0, target = stride;
+  while (i < c || !zeroDone) {
+    double val, cnt;
+    if (!zeroDone && (i >= c || v[i] > 0.0)) { val = 0.0; cnt = zeroCnt; zeroDone = true; }
+    else {
+      val = v[i];
+      int64_t e = i + 1;
+      while (e < c && v[e] == val) e++;
+      cnt = (double)(e - i);
+      i = e;
+    }
+    if (firstRun) { cur = cnt; firstRun = false; }
+    else {
+      const double prev = cur;
+      cur += cnt;
+      if (all) { if (nout < maxSplits) out[nout++] = (prevVal + val) / 2.0; }
+      else if (fabs(prev - target) < fabs(cur - target)) {
+        if (nout < maxSplits) out[nout++] = (prevVal + val) / 2.0;
+        target += stride;
+      }
+    }
+    prevVal = val;
+  }
+  nsplits[f] = nout;
+}
+
+// =================================================================================================
+// K2: binning (row-major f64 -> column-major u8)
+// =================================================================================================
+constexpr int BIN_FT = 32;    // features per block
+constexpr int BIN_RT = 128;   // rows per block
+__global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, int64_t n_rows, int F, const double* thresholds,
+                                                   const int32_t* nsplits, const int32_t* arity, int maxSplits, uint8_t* bins, int64_t ldb,
+                                                   int64_t row0, int32_t* err) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  double* thr = reinterpret_cast<double*>(smraw);                                   // [BIN_FT][maxSplits]
+  uint8_t* tile = smraw + (size_t)BIN_FT * (maxSplits > 0 ? maxSplits : 1) * 8;     // [BIN_FT][BIN_RT]
+  const int f0 = blockIdx.y * BIN_FT;
+  const int64_t r0 = (int64_t)blockIdx.x * BIN_RT;
+  const int nf = min(BIN_FT, F - f0);
+  for (int i = threadIdx.x; i < nf * maxSplits; i += blockDim.x) {
+    const int ff = i / maxSplits, q = i % maxSplits;
+    thr[ff * maxSplits + q] = (q < nsplits[f0 + ff]) ? thresholds[(size_t)(f0 + ff) * maxSplits + q] : INFINITY;
+  }
+  __syncthreads();
+  const int fl = threadIdx.x & 31;  // feature lane
+  const int rl = threadIdx.x >> 5;  // 8 rows per pass
+  for (int rr = rl; rr < BIN_RT; rr += 8) {
+    const int64_t row = r0 + rr;
+    uint8_t b = 0;
+    if (row < n_rows && fl < nf) {
+      const int f = f0 + fl;
+      const double x = X[(size_t)row * ldx + f];
+      const int ar = arity[f];
+      if (ar == 0) {
+        // TreePoint.findBin: Arrays.binarySearch -> number of thresholds strictly below x
+        const double* t = thr + fl * maxSplits;
+        int lo = 0, hi = nsplits[f];
+        while (lo < hi) { const int mid = (lo + hi) >> 1; if (t[mid] < x) lo = mid + 1; else hi = mid; }
+        b = (uint8_t)lo;
+      } else {
+        if (x < 0 || x >= (double)ar) atomicMax(err, f + 1);
+        b = (uint8_t)(int)x;
+      }
+    }
+    tile[fl * BIN_RT + rr] = b;
+  }
+  __syncthreads();
+  // coalesced column-major stores: 32-bit words
+  const int words = nf * (BIN_RT / 4);
+  for (int i = threadIdx.x; i < words; i += blockDim.x) {
+    const int ff = i / (BIN_RT / 4), wq = i % (BIN_RT / 4);
+    const int64_t row = r0 + wq * 4;
+    if (row + 3 < n_rows && ((row0 + row) & 3) == 0) {
+      *reinterpret_cast<uint32_t*>(bins + (size_t)(f0 + ff) * ldb + row0 + row) = *reinterpret_cast<const uint32_t*>(tile + ff * BIN_RT + wq * 4);
+    } else {
+      for (int q = 0; q < 4; q++) if (row + q < n_rows) bins[(size_t)(f0 + ff) * ldb + row0 + row + q] = tile[ff * BIN_RT + wq * 4 + q];
+    }
+  }
+}
+
+// =================================================================================================
+// K3: bagging.  One thread per emulated Spark partition; generator state in local memory.
+// =================================================================================================
+struct Well19937cDev {
+  uint32_t v[624];
+  int index;
+  __device__ void seed(int64_t sd) {
+    v[0] = (uint32_t)((uint64_t)sd >> 32);
+    v[1] = (uint32_t)((uint64_t)sd & 0xffffffffULL);
+    for (int i = 2; i < 624; i++) {
+      const int64_t l = (int64_t)(int32_t)v[i - 2];
+      v[i] = (uint32_t)((1812433253LL * (l ^ (l >> 30)) + i) & 0xffffffffLL);
+    }
+    index = 0;
+  }
+  __device__ __forceinline__ uint32_t next(int bits) {
+    const int i0 = index;
+    const int iRm1 = i0 == 0 ? 623 : i0 - 1;
+    const int iRm2 = iRm1 == 0 ? 623 : iRm1 - 1;
+    int i1 = i0 + 70; if (i1 >= 624) i1 -= 624;
+    int i2 = i0 + 179; if (i2 >= 624) i2 -= 624;
+    int i3 = i0 + 449; if (i3 >= 624) i3 -= 624;
+    const uint32_t v0 = v[i0], vM1 = v[i1], vM2 = v[i2], vM3 = v[i3];
+    const uint32_t z0 = (0x80000000u & v[iRm1]) ^ (0x7FFFFFFFu & v[iRm2]);
+    const uint32_t z1 = (v0 ^ (v0 << 25)) ^ (vM1 ^ (vM1 >> 27));
+    const uint32_t z2 = (vM2 >> 9) ^ (vM3 ^ (vM3 >> 1));
+    const uint32_t z3 = z1 ^ z2;
+    uint32_t z4 = z0 ^ (z1 ^ (z1 << 9)) ^ (z2 ^ (z2 << 21)) ^ (z3 ^ (z3 >> 21));
+    v[i0] = z3;
+    v[iRm1] = z4;
+    v[iRm2] &= 0x80000000u;
+    index = iRm1;
+    z4 ^= (z4 << 7) & 0xe46e1700u;
+    z4 ^= (z4 << 15) & 0x9b868000u;
+    return z4 >> (32 - bits);
+  }
+  __device__ __forceinline__ double nextDouble() {
+    const int64_t high = (int64_t)next(26) << 26;
+    const int64_t low = (int64_t)next(26);
+    return (double)(high | low) * 0x1.0p-52;
+  }
+};
+
+__device__ inline uint32_t rotl32d(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+__device__ uint32_t murmur3_8bytes(const uint8_t* data, uint32_t seed) {
+  uint32_t h = seed;
+  for (int i = 0; i < 8; i += 4) {
+    uint32_t k = (uint32_t)data[i] | ((uint32_t)data[i + 1] << 8) | ((uint32_t)data[i + 2] << 16) | ((uint32_t)data[i + 3] << 24);
+    k *= 0xcc9e2d51u; k = rotl32d(k, 15); k *= 0x1b873593u;
+    h ^= k; h = rotl32d(h, 13); h = h * 5 + 0xe6546b64u;
+  }
+  h ^= 8u;
+  h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+struct XorShiftDev {
+  uint64_t s;
+  __device__ void seed(int64_t init) {
+    uint8_t b[8];
+    for (int i = 0; i < 8; i++) b[i] = (uint8_t)((uint64_t)init >> (56 - 8 * i));
+    const uint32_t lo = murmur3_8bytes(b, 0x3c074a61u);
+    const uint32_t hi = murmur3_8bytes(b, lo);
+    s = ((uint64_t)hi << 32) | (uint64_t)lo;
+  }
+  __device__ __forceinline__ int32_t next(int bits) {
+    uint64_t n = s ^ (s << 21);
+    n ^= n >> 35;
+    n ^= n << 4;
+    s = n;
+    return (int32_t)(n & ((1ULL << bits) - 1));
+  }
+  __device__ __forceinline__ double nextDouble() { return (double)(((int64_t)next(26) << 27) + next(27)) * 0x1.0p-53; }
+};
+
+// mode 0: Poisson (with replacement); 1: Bernoulli (without replacement); 2: all ones
+__global__ void __launch_bounds__(64) bag_kernel(int64_t seed, const int64_t* part_offsets, int P, int part0, int T, double rate, double expNegRate,
+                                                 int mode, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  const int64_t r0 = part_offsets[p], r1 = part_offsets[p + 1];
+  if (mode == 0) {
+    Well19937cDev rng;
+    rng.seed(seed + (int64_t)(part0 + p) + 1);
+    const double lim = 1000 * rate;
+    for (int64_t i = r0; i < r1; i++)
+      for (int t = 0; t < T; t++) {
+        long n = 0; double r = 1.0;
+        while ((double)n < lim) { r *= rng.nextDouble(); if (r >= expNegRate) n++; else break; }
+        const int c = n > 255 ? 255 : (int)n;
+        w[(size_t)t * ldw + i] = (uint8_t)c;
+        node[(size_t)t * ldn + i] = c > 0 ? 0 : -1;
+      }
+  } else if (mode == 1) {
+    XorShiftDev rng;
+    rng.seed(seed + (int64_t)(part0 + p) + 1);
+    for (int64_t i = r0; i < r1; i++)
+      for (int t = 0; t < T; t++) {
+        const int c = rng.nextDouble() < rate ? 1 : 0;
+        w[(size_t)t * ldw + i] = (uint8_t)c;
+        node[(size_t)t * ldn + i] = c > 0 ? 0 : -1;
+      }
+  }
+}
+__global__ void bag_ones_kernel(int64_t n, int T, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  for (int t = 0; t < T; t++) { w[(size_t)t * ldw + i] = 1; node[(size_t)t * ldn + i] = 0; }
+}
+
+// =================================================================================================
+// K7: predict
+// =================================================================================================
+__global__ void predict_kernel(const double* X, int64_t ldx, int64_t n_rows, int T, const int64_t* tree_off, const int32_t* feature,
+                               const double* threshold, const int32_t* left, const int32_t* right, const double* prediction,
+                               const int32_t* ncat, const int32_t* cat_off, const int32_t* cat_len, const double* cats, double* out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows) return;
+  const double* x = X + (size_t)i * ldx;
+  double acc = 0.0;
+  for (int t = 0; t < T; t++) {
+    const int64_t base = tree_off[t];
+    int n = 0;
+    int f;
+    while ((f = feature[base + n]) >= 0) {
+      const double xv = x[f];
+      bool l;
+      if (ncat[base + n] == 0) l = xv <= threshold[base + n];
+      else {
+        l = false;
+        const int co = cat_off[base + n], cl = cat_len[base + n];
+        for (int c = 0; c < cl; c++) if (cats[co + c] == xv) { l = true; break; }
+      }
+      n = l ? left[base + n] : right[base + n];
+    }
+    acc += prediction[base + n];
+  }
+  out[i] = acc / (double)T;
+}
+
+}  // namespace b2rf
+
+// =================================================================================================
+// C-ABI wrappers for the stand-alone kernels
+// =================================================================================================
+using namespace b2rf;
+
+extern "C" {
+
+int b2rf_version(void) { return 100; }
+const char* b2rf_last_error(void) { return b2rf::last_error_cstr(); }
+
+double b2rf_samples_fraction(int64_t numExamples, int32_t metaMaxBins) {
+  const int64_t required = (int64_t)metaMaxBins * metaMaxBins > 10000 ? (int64_t)metaMaxBins * metaMaxBins : 10000;
+  return required < numExamples ? (double)required / (double)numExamples : 1.0;
+}
+
+// XORShiftRandom(seed).nextInt() — host copy of the hashSeed chain, used to derive the row-sample seed word
+static uint32_t h_rotl(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+static uint32_t h_murmur8(const uint8_t* d, uint32_t seed) {
+  uint32_t h = seed;
+  for (int i = 0; i < 8; i += 4) {
+    uint32_t k = (uint32_t)d[i] | ((uint32_t)d[i + 1] << 8) | ((uint32_t)d[i + 2] << 16) | ((uint32_t)d[i + 3] << 24);
+    k *= 0xcc9e2d51u; k = h_rotl(k, 15); k *= 0x1b873593u; h ^= k; h = h_rotl(h, 13); h = h * 5 + 0xe6546b64u;
+  }
+  h ^= 8u; h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+static int32_t xorshift_first_int(int64_t seed) {
+  uint8_t b[8];
+  for (int i = 0; i < 8; i++) b[i] = (uint8_t)((uint64_t)seed >> (56 - 8 * i));
+  const uint32_t lo = h_murmur8(b, 0x3c074a61u), hi = h_murmur8(b, lo);
+  uint64_t s = ((uint64_t)hi << 32) | lo;
+  uint64_t n = s ^ (s << 21); n ^= n >> 35; n ^= n << 4;
+  return (int32_t)(n & 0xffffffffULL);
+}
+
+int b2rf_sample_rows(const double* d_X, int64_t ldx, int64_t n_rows, int64_t row0_global, int32_t F, int64_t seed, double fraction,
+                     double* d_sample_out, int64_t cap, int64_t* d_count, void* stream) {
+  if (!d_X || !d_sample_out || !d_count || F <= 0) { set_error("b2rf_sample_rows: bad argument"); return B2RF_ERR_ARG; }
+  if (n_rows <= 0) return B2RF_OK;
+  const uint64_t seedWord = ((uint64_t)(uint32_t)xorshift_first_int(seed) << 32) | 0x9E3779B9u;
+  const int64_t threads = n_rows * 32;
+  sample_rows_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, row0_global, F, seedWord, fraction,
+                                                                                        d_sample_out, cap, (unsigned long long*)d_count);
+  return cuda_ok(cudaGetLastError(), "b2rf_sample_rows") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+static int64_t next_pow2(int64_t n) { int64_t p = 1; while (p < n) p <<= 1; return p; }
+
+size_t b2rf_find_splits_workspace_bytes(int64_t n_sample, int32_t F) { return (size_t)next_pow2(n_sample < 2 ? 2 : n_sample) * (size_t)F * 8; }
+
+int b2rf_find_splits(const double* d_sample, int64_t n_sample, int32_t F, const int32_t* d_arity, int32_t maxPossibleBins,
+                     double weightedNumSamples, double* d_thresholds, int32_t* d_nsplits, void* d_workspace, size_t workspace_bytes,
+                     void* stream) {
+  if (F <= 0 || n_sample <= 0 || maxPossibleBins < 1) { set_error("b2rf_find_splits: bad argument"); return B2RF_ERR_ARG; }
+  if (workspace_bytes < b2rf_find_splits_workspace_bytes(n_sample, F)) { set_error("b2rf_find_splits: workspace too small"); return B2RF_ERR_ARG; }
+  const int64_t n_pad = next_pow2(n_sample < 2 ? 2 : n_sample);
+  find_splits_kernel<<<F, 1024, 0, (cudaStream_t)stream>>>(d_sample, n_sample, F, d_arity, maxPossibleBins - 1, weightedNumSamples, d_thresholds,
+                                                            d_nsplits, (double*)d_workspace, n_pad);
+  return cuda_ok(cudaGetLastError(), "b2rf_find_splits") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const double* d_thresholds, const int32_t* d_nsplits,
+             const int32_t* d_arity, int32_t maxSplits, uint8_t* d_bins, int64_t ldb, int64_t row0, int32_t* d_err, void* stream) {
+  if (F <= 0 || maxSplits < 0 || maxSplits > 255) { set_error("b2rf_bin: maxBins must be <= 256 for uint8 bin codes"); return B2RF_ERR_ARG; }
+  if (n_rows <= 0) return B2RF_OK;
+  const int ms = maxSplits > 0 ? maxSplits : 1;
+  const size_t smem = (size_t)BIN_FT * ms * 8 + (size_t)BIN_FT * BIN_RT;
+  if (!cuda_ok(cudaFuncSetAttribute(bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bin attr")) return B2RF_ERR_CUDA;
+  dim3 grid((unsigned)((n_rows + BIN_RT - 1) / BIN_RT), (unsigned)((F + BIN_FT - 1) / BIN_FT));
+  bin_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(d_X, ldx, n_rows, F, d_thresholds, d_nsplits, d_arity, ms, d_bins, ldb, row0, d_err);
+  return cuda_ok(cudaGetLastError(), "b2rf_bin") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t part0, int32_t T, double subsamplingRate, int32_t bootstrap,
+             uint8_t* d_w, int64_t ldw, int32_t* d_node, int64_t ldn, void* stream) {
+  if (P <= 0 || T <= 0 || !h_part_offsets) { set_error("b2rf_bag: bad argument"); return B2RF_ERR_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t n = h_part_offsets[P];
+  if (!bootstrap && T == 1 && subsamplingRate == 1.0) {
+    if (n > 0) bag_ones_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(n, T, d_w, ldw, d_node, ldn);
+    return cuda_ok(cudaGetLastError(), "b2rf_bag") ? B2RF_OK : B2RF_ERR_CUDA;
+  }
+  int64_t* d_po = nullptr;
+  if (!cuda_ok(cudaMallocAsync((void**)&d_po, (size_t)(P + 1) * 8, s), "b2rf_bag alloc")) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaMemcpyAsync(d_po, h_part_offsets, (size_t)(P + 1) * 8, cudaMemcpyHostToDevice, s), "b2rf_bag copy")) return B2RF_ERR_CUDA;
+  // exp(-rate) is evaluated once on the host so that every consumer of the stream compares against the same constant
+  bag_kernel<<<(P + 63) / 64, 64, 0, s>>>(seed, d_po, P, part0, T, subsamplingRate, std::exp(-subsamplingRate), bootstrap ? 0 : 1, d_w, ldw, d_node, ldn);
+  const bool ok = cuda_ok(cudaGetLastError(), "b2rf_bag");
+  cudaStreamSynchronize(s);  // h_part_offsets may be pageable: finish the copy before returning
+  cudaFreeAsync(d_po, s);
+  return ok ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+int b2rf_hist_build(const uint8_t* d_bins, int64_t ldb, int32_t F, const double* d_y, const uint8_t* d_w, int64_t ldw,
+                    const int32_t* d_slot_of_row, int64_t ldn, const int32_t* d_tree_ids, int32_t Tg, int64_t n_rows,
+                    const uint32_t* d_slot_fo, const int64_t* d_slot_base, int32_t Fsub, double* d_hist, void* stream) {
+  if ((ldb & 15) != 0 || ldb < n_rows) { set_error("b2rf_hist_build: ldb must be a multiple of 16 and >= n_rows (128 recommended)"); return B2RF_ERR_ARG; }
+  HistLaunch a;
+  a.bins = d_bins; a.ldb = ldb; a.F = F; a.y = d_y; a.w = d_w; a.ldw = ldw;
+  a.node = const_cast<int32_t*>(d_slot_of_row); a.ldn = ldn; a.tree_ids = d_tree_ids; a.Tg = Tg; a.n_rows = n_rows;
+  a.dnodes = nullptr; a.nodeStride = 0; a.catmasks = nullptr;
+  a.slot_fo = reinterpret_cast<const uint2*>(d_slot_fo); a.slot_base = d_slot_base; a.Fsub = Fsub; a.hist = d_hist;
+  std::string err;
+  cudaError_t e = launch_hist(a, false, (cudaStream_t)stream, &err);
+  if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "b2rf_hist_build"); return e == cudaErrorInvalidValue && !err.empty() ? B2RF_ERR_ARG : B2RF_ERR_CUDA; }
+  return B2RF_OK;
+}
+
+int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,
+                 const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_prediction, const int32_t* d_ncat,
+                 const int32_t* d_cat_off, const int32_t* d_cat_len, const double* d_cats, double* d_out, void* stream) {
+  if (n_rows <= 0) return B2RF_OK;
+  predict_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, d_feature, d_threshold, d_left, d_right,
+                                                                                     d_prediction, d_ncat, d_cat_off, d_cat_len, d_cats, d_out);
+  return cuda_ok(cudaGetLastError(), "b2rf_predict") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+}  // extern "C"

@@ -1,0 +1,677 @@
+// b2rf host driver: the RandomForest.run loop of Spark MLlib 3.1.2 (selectNodesToSplit -> findBestSplits -> driver tail),
+// re-designed around device-resident data: the host keeps only the tiny LearningNode trees, the LIFO node stack and the
+// RNGs that define MLlib's order-dependent semantics; every pass over rows is a kernel.
+#include "b2rf_internal.h"
+#include "../../include/b2rf.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+using namespace b2rf;
+
+namespace {
+
+// ---- java.util.Random (feature-subset master stream; RandomForest.run `rng`) ----
+struct JRandom {
+  uint64_t s;
+  explicit JRandom(int64_t seed) : s(((uint64_t)seed ^ 0x5DEECE66DULL) & ((1ULL << 48) - 1)) {}
+  int32_t bits32() { s = (s * 0x5DEECE66DULL + 0xBULL) & ((1ULL << 48) - 1); return (int32_t)((int64_t)s >> 16); }
+  int64_t nextLong() { const int64_t hi = bits32(); const int64_t lo = bits32(); return (int64_t)((uint64_t)hi << 32) + lo; }
+};
+
+// ---- org.apache.spark.util.random.XORShiftRandom (reservoir sampler stream) ----
+inline uint32_t rotl(uint32_t x, int r) { return (x << r) | (x >> (32 - r)); }
+uint32_t murmur_long(uint64_t be_value, uint32_t seed) {
+  // MurmurHash3_x86_32 over the 8 big-endian bytes of a long
+  uint8_t d[8];
+  for (int i = 0; i < 8; i++) d[i] = (uint8_t)(be_value >> (56 - 8 * i));
+  uint32_t h = seed;
+  for (int i = 0; i < 8; i += 4) {
+    uint32_t k = (uint32_t)d[i] | ((uint32_t)d[i + 1] << 8) | ((uint32_t)d[i + 2] << 16) | ((uint32_t)d[i + 3] << 24);
+    k *= 0xcc9e2d51u; k = rotl(k, 15); k *= 0x1b873593u;
+    h ^= k; h = rotl(h, 13); h = h * 5 + 0xe6546b64u;
+  }
+  h ^= 8u; h ^= h >> 16; h *= 0x85ebca6bu; h ^= h >> 13; h *= 0xc2b2ae35u; h ^= h >> 16;
+  return h;
+}
+struct XorShift {
+  uint64_t s;
+  explicit XorShift(int64_t init) {
+    const uint32_t lo = murmur_long((uint64_t)init, 0x3c074a61u);
+    const uint32_t hi = murmur_long((uint64_t)init, lo);
+    s = ((uint64_t)hi << 32) | lo;
+  }
+  int32_t next(int bits) { uint64_t n = s ^ (s << 21); n ^= n >> 35; n ^= n << 4; s = n; return (int32_t)(n & ((1ULL << bits) - 1)); }
+  double nextDouble() { return (double)(((int64_t)next(26) << 27) + next(27)) * 0x1.0p-53; }
+};
+
+// SamplingUtils.reservoirSampleAndCount(0 until F, k, seed)
+void reservoir_features(int F, int k, int64_t seed, uint32_t* out) {
+  for (int i = 0; i < k; i++) out[i] = (uint32_t)i;
+  if (k >= F) return;
+  XorShift r(seed);
+  long l = k;
+  for (int item = k; item < F; item++) {
+    l++;
+    const long rep = (long)(r.nextDouble() * (double)l);
+    if (rep < k) out[rep] = (uint32_t)item;
+  }
+}
+
+// Iteration order of `nodesForGroup` (immutable.Map built by .toMap from a mutable.HashMap) — Appendix A.6.
+uint32_t bswap_hash(uint32_t v) {
+  uint32_t hc = v * 0x9e3775cdu;
+  hc = __builtin_bswap32(hc);
+  return hc * 0x9e3775cdu;
+}
+uint32_t trie_improve(uint32_t hcode) {
+  uint32_t h = hcode + ~(hcode << 9);
+  h ^= h >> 14;
+  h += h << 4;
+  return h ^ (h >> 10);
+}
+void group_tree_order(const std::vector<int>& inserted, std::vector<int>& out) {
+  int tbl = 16;
+  while ((int)inserted.size() > tbl * 3 / 4) tbl *= 2;
+  const uint32_t ones = (uint32_t)tbl - 1;
+  const int rot = __builtin_popcount(ones) % 32;
+  const int shift = __builtin_clz(ones);
+  std::vector<std::vector<int>> bucket(tbl);
+  for (int key : inserted) {
+    const uint32_t i = bswap_hash((uint32_t)key);
+    const uint32_t imp = rot ? ((i >> rot) | (i << (32 - rot))) : i;
+    auto& b = bucket[(imp >> shift) & ones];
+    b.insert(b.begin(), key);
+  }
+  std::vector<int> mut;
+  for (int b = tbl - 1; b >= 0; b--) for (int key : bucket[b]) mut.push_back(key);
+  if (mut.size() <= 4) { out = mut; return; }
+  std::vector<std::pair<uint64_t, int>> ks;
+  for (int key : mut) {
+    const uint32_t h = trie_improve((uint32_t)key);
+    uint64_t k = 0;
+    for (int lvl = 0; lvl < 7; lvl++) k = (k << 5) | ((h >> (5 * lvl)) & 31u);
+    ks.push_back({k, key});
+  }
+  std::sort(ks.begin(), ks.end());
+  out.clear();
+  for (auto& p : ks) out.push_back(p.second);
+}
+
+struct NodeStats {  // ImpurityStats (regression)
+  double gain = 0, impurity = 0;
+  double calc[4] = {0, 0, 0, 0};
+  bool valid = true;
+};
+struct HNode {  // LearningNode
+  int32_t id = 1;
+  int32_t left = -1;  // tree-local index; right = left + 1
+  bool isLeaf = false, hasSplit = false;
+  int32_t feature = -1;
+  int32_t splitBin = -1;
+  double threshold = 0;
+  int32_t catMaskIdx = -1;
+  NodeStats stats;
+};
+struct GNode { int32_t tree, nidx; };
+
+inline int level_of(int id) { return 31 - __builtin_clz((unsigned)id); }
+inline double vimp(const double* c) { if (c[0] == 0) return 0; const double sl = c[2] - (c[1] * c[1]) / c[0]; return sl / c[0]; }
+inline double vpred(const double* c) { return c[0] == 0 ? 0.0 : c[1] / c[0]; }
+
+template <class T> struct DevBuf {
+  T* p = nullptr; size_t cap = 0;
+  bool ensure(size_t n) {
+    if (n <= cap) return true;
+    size_t nc = std::max(n, cap * 2);
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    if (!cuda_ok(cudaMalloc((void**)&p, nc * sizeof(T)), "trainer device alloc")) return false;
+    cap = nc; return true;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+};
+template <class T> struct PinBuf {
+  T* p = nullptr; size_t cap = 0;
+  bool ensure(size_t n) {
+    if (n <= cap) return true;
+    size_t nc = std::max(n, cap * 2);
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    if (!cuda_ok(cudaMallocHost((void**)&p, nc * sizeof(T)), "trainer pinned alloc")) return false;
+    cap = nc; return true;
+  }
+  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+};
+
+double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
+}  // namespace
+
+struct b2rf_trainer {
+  b2rf_params p;
+  int32_t F = 0, T = 0;
+  int64_t numExamples = 0;
+  int32_t maxPossibleBins = 0, maxSplits = 0, Fsub = 0;
+  bool subsampling = false;
+  double minWeightPerNode = 0;
+  std::vector<int32_t> arity, numBins;
+  std::vector<double> thresholds;  // [F][maxSplits]
+  int64_t allBins = 0;
+
+  // bound device data (caller-owned)
+  const uint8_t* d_bins = nullptr; int64_t ldb = 0;
+  const double* d_y = nullptr;
+  const uint8_t* d_w = nullptr; int64_t ldw = 0;
+  int32_t* d_node = nullptr; int64_t ldn = 0;
+  int64_t nLocal = 0;
+  double* d_hist = nullptr; int64_t histCells = 0;
+
+  // host trees + scheduler
+  std::vector<std::vector<HNode>> trees;
+  std::vector<std::pair<int32_t, int32_t>> stack;  // back() == head of MLlib's nodeStack
+  JRandom rng{0};
+  std::vector<uint32_t> catPool;  // 8 words per categorical split
+  size_t catUploaded = 0;
+
+  // device-side descriptors (library-owned, small)
+  int64_t nodeStride = 0;
+  DevBuf<DNode> dn;
+  DevBuf<DNodeUpdate> dnUpd;
+  DevBuf<uint32_t> dCat;
+  DevBuf<uint2> dSlotFo;
+  DevBuf<int64_t> dSlotBase;
+  DevBuf<double> dParent;
+  DevBuf<int32_t> dHasParent, dNumBins, dIsCat, dTreeIds;
+  DevBuf<SplitRec> dRec;
+  PinBuf<DNodeUpdate> hUpd;
+  PinBuf<uint2> hSlotFo;
+  PinBuf<int64_t> hSlotBase;
+  PinBuf<double> hParent;
+  PinBuf<int32_t> hHasParent, hTreeIds;
+  PinBuf<SplitRec> hRec;
+  std::vector<DNodeUpdate> pending;  // node-table changes produced by the last driver tail
+
+  // current group
+  std::vector<GNode> group;
+  std::vector<int> groupTreeInsertOrder;
+  int64_t groupCells = 0;
+  bool inGroup = false;
+  int groupNo = 0;
+
+  // trace + stats
+  struct Trace { int32_t g, t, id, f, s; double gain, imp, cnt, sum, sq; };
+  std::vector<Trace> trace;
+  double tHist = 0, tChoose = 0, tStart = 0, tTotal = 0;
+  int64_t nHistLaunches = 0, nScanned = 0;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  bool evPending = false;
+  int64_t l2CellBudget = 1500000;  // cells per K4 launch kept L2-resident (32 B each => 48 MB)
+
+  // flat export cache
+  bool exported = false;
+  std::vector<int64_t> x_tree_off;
+  std::vector<int32_t> x_feature, x_left, x_right, x_ncat, x_cat_off, x_cat_len;
+  std::vector<double> x_threshold, x_prediction, x_impurity, x_gain, x_stats, x_cats;
+
+  ~b2rf_trainer() {
+    dn.release(); dnUpd.release(); dCat.release(); dSlotFo.release(); dSlotBase.release(); dParent.release();
+    dHasParent.release(); dNumBins.release(); dIsCat.release(); dTreeIds.release(); dRec.release();
+    hUpd.release(); hSlotFo.release(); hSlotBase.release(); hParent.release(); hHasParent.release(); hTreeIds.release(); hRec.release();
+    if (ev0) cudaEventDestroy(ev0);
+    if (ev1) cudaEventDestroy(ev1);
+  }
+
+  DNode mirror(int t, int ni, int slot) const {
+    const HNode& n = trees[t][ni];
+    DNode d;
+    d.feature = n.hasSplit ? n.feature : -1;
+    d.left = n.left;
+    d.slot = slot;
+    d.aux = n.hasSplit ? (n.catMaskIdx >= 0 ? (0x80000000u | (uint32_t)n.catMaskIdx) : (uint32_t)n.splitBin) : 0u;
+    return d;
+  }
+  int state_slot(const HNode& n) const { return (n.isLeaf && !n.hasSplit) ? SLOT_DEAD : SLOT_PENDING; }
+};
+
+extern "C" {
+
+int b2rf_features_per_node(const char* strategy, int32_t F, int32_t numTrees) {
+  std::string s = strategy ? strategy : "auto";
+  if (s == "auto") s = numTrees == 1 ? "all" : "onethird";  // regression
+  if (s == "all") return F;
+  if (s == "sqrt") return (int)std::ceil(std::sqrt((double)F));
+  if (s == "log2") return std::max(1, (int)std::ceil(std::log((double)F) / std::log(2.0)));
+  if (s == "onethird") return (int)std::ceil((double)F / 3.0);
+  char* end = nullptr;
+  const long n = std::strtol(s.c_str(), &end, 10);
+  if (end && *end == 0 && !s.empty()) { if (n > 0) return (int)std::min<long>(n, F); }
+  else {
+    const double x = std::strtod(s.c_str(), &end);
+    if (end && *end == 0 && !s.empty() && x > 0.0 && x <= 1.0) return (int)std::ceil(x * F);
+  }
+  set_error("Supported values: auto, all, onethird, sqrt, log2, (0.0-1.0], [1-n]. Got \"" + s + "\"");
+  return B2RF_ERR_ARG;
+}
+
+static int check_arity(int32_t maxBins, int32_t F, const int32_t* h_arity, int64_t numExamples, int* maxPossibleBinsOut) {
+  const int mpb = (int)std::min<int64_t>(maxBins, numExamples);
+  int maxCat = 0, maxCatF = -1;
+  for (int f = 0; f < F; f++) if (h_arity[f] > maxCat) { maxCat = h_arity[f]; maxCatF = f; }
+  if (maxCatF >= 0 && maxCat > mpb) {
+    char buf[512];
+    snprintf(buf, sizeof buf,
+             "requirement failed: DecisionTree requires maxBins (= %d) to be at least as large as the number of values in each "
+             "categorical feature, but categorical feature %d has %d values. Consider removing this and other categorical "
+             "features with a large number of values, or add more training examples.",
+             mpb, maxCatF, maxCat);
+    set_error(buf);
+    return B2RF_ERR_MAXBINS;
+  }
+  *maxPossibleBinsOut = mpb;
+  return B2RF_OK;
+}
+
+int b2rf_check_metadata(const b2rf_params* params, int32_t F, const int32_t* h_arity, int64_t numExamples) {
+  if (!params || F <= 0 || !h_arity || numExamples <= 0) { set_error("b2rf_check_metadata: bad argument"); return B2RF_ERR_ARG; }
+  int mpb = 0;
+  const int rc = check_arity(params->maxBins, F, h_arity, numExamples, &mpb);
+  if (rc) return rc;
+  int mx = 0;
+  for (int f = 0; f < F; f++) mx = std::max(mx, h_arity[f] > 1 ? h_arity[f] : mpb);
+  return mx;
+}
+
+int b2rf_trainer_create(const b2rf_params* params, int32_t F, const int32_t* h_arity, const int32_t* h_nsplits, const double* h_thresholds,
+                        int64_t numExamples, b2rf_trainer** out) {
+  if (!params || !out || F <= 0 || numExamples <= 0 || params->numTrees <= 0 || params->maxDepth < 0 || params->maxDepth > 30) {
+    set_error("b2rf_trainer_create: bad argument"); return B2RF_ERR_ARG;
+  }
+  b2rf_trainer* t = new b2rf_trainer();
+  t->p = *params; t->F = F; t->T = params->numTrees; t->numExamples = numExamples;
+  { int mpb = 0; const int rc = check_arity(params->maxBins, F, h_arity, numExamples, &mpb); if (rc) { delete t; return rc; } t->maxPossibleBins = mpb; }
+  t->maxSplits = std::max(t->maxPossibleBins - 1, 1);
+  t->arity.assign(h_arity, h_arity + F);
+  if (t->maxPossibleBins > 256) { set_error("b2rf: maxBins > 256 needs uint16 bin codes, not built yet"); delete t; return B2RF_ERR_ARG; }
+  t->numBins.assign(F, t->maxPossibleBins);
+  for (int f = 0; f < F; f++) {
+    if (h_arity[f] > 1) t->numBins[f] = h_arity[f];
+    else if (h_arity[f] == 0) t->numBins[f] = h_nsplits[f] + 1;
+  }
+  t->thresholds.assign(h_thresholds, h_thresholds + (size_t)F * t->maxSplits);
+  t->allBins = 0;
+  for (int f = 0; f < F; f++) t->allBins += t->numBins[f];
+  t->Fsub = params->featuresPerNode > 0 ? std::min(params->featuresPerNode, F) : F;
+  t->subsampling = t->Fsub != F;
+  t->minWeightPerNode = params->minWeightFractionPerNode * (double)numExamples;
+  t->trees.assign(t->T, {});
+  for (int i = 0; i < t->T; i++) { t->trees[i].reserve(64); t->trees[i].push_back(HNode()); t->stack.push_back({i, 0}); }
+  t->rng = JRandom(params->seed);
+  *out = t;
+  return B2RF_OK;
+}
+
+void b2rf_trainer_destroy(b2rf_trainer* t) { delete t; }
+
+int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t) {
+  // selectNodesToSplit admits nodes while 3*totalBins*8 bytes fit maxMemoryInMB; always at least one node
+  const int64_t maxMem = (int64_t)t->p.maxMemoryInMB * 1024 * 1024;
+  std::vector<int32_t> nb(t->numBins);
+  std::sort(nb.begin(), nb.end(), std::greater<int32_t>());
+  int64_t worstNode = 0;
+  for (int j = 0; j < t->Fsub; j++) worstNode += nb[j];
+  const int64_t byMem = maxMem / 24 + worstNode;
+  const int64_t maxNodesTotal = (int64_t)t->T << std::min(t->p.maxDepth, 24);
+  return std::max<int64_t>(worstNode, std::min<int64_t>(byMem, maxNodesTotal * worstNode));
+}
+
+int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const double* d_y, const uint8_t* d_w, int64_t ldw, int32_t* d_node,
+                      int64_t ldn, int64_t n_rows_local, double* d_hist, int64_t hist_cells) {
+  if (!t || !d_bins || !d_y || !d_w || !d_node || !d_hist || n_rows_local < 0 || (ldb & 15) || ldb < n_rows_local || ldw < n_rows_local || ldn < n_rows_local) {
+    set_error("b2rf_trainer_bind: bad argument (ldb must be a multiple of 16 and every leading dimension >= n_rows)"); return B2RF_ERR_ARG;
+  }
+  t->d_bins = d_bins; t->ldb = ldb; t->d_y = d_y; t->d_w = d_w; t->ldw = ldw; t->d_node = d_node; t->ldn = ldn; t->nLocal = n_rows_local;
+  t->d_hist = d_hist; t->histCells = hist_cells;
+  // device node table: one stride per tree
+  const int64_t full = (int64_t)1 << std::min(t->p.maxDepth + 1, 17);
+  t->nodeStride = full;
+  if (!t->dn.ensure((size_t)t->nodeStride * t->T)) return B2RF_ERR_CUDA;
+  if (!t->dNumBins.ensure(t->F) || !t->dIsCat.ensure(t->F)) return B2RF_ERR_CUDA;
+  std::vector<int32_t> isCat(t->F);
+  for (int f = 0; f < t->F; f++) isCat[f] = t->arity[f] != 0;
+  if (!cuda_ok(cudaMemcpy(t->dNumBins.p, t->numBins.data(), t->F * 4, cudaMemcpyHostToDevice), "bind copy")) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaMemcpy(t->dIsCat.p, isCat.data(), t->F * 4, cudaMemcpyHostToDevice), "bind copy")) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaEventCreate(&t->ev0), "event") || !cuda_ok(cudaEventCreate(&t->ev1), "event")) return B2RF_ERR_CUDA;
+  t->pending.clear();
+  for (int i = 0; i < t->T; i++) t->pending.push_back({(int64_t)i * t->nodeStride, t->mirror(i, 0, SLOT_PENDING)});
+  t->tStart = now_s();
+  return B2RF_OK;
+}
+
+static int grow_node_table(b2rf_trainer* t, int64_t need, cudaStream_t s) {
+  int64_t ns = t->nodeStride;
+  while (ns < need) ns *= 2;
+  cudaStreamSynchronize(s);
+  t->nodeStride = ns;
+  if (!t->dn.ensure((size_t)ns * t->T)) return B2RF_ERR_CUDA;
+  // rebuild every entry from the host trees
+  t->pending.clear();
+  for (int i = 0; i < t->T; i++)
+    for (size_t k = 0; k < t->trees[i].size(); k++)
+      t->pending.push_back({(int64_t)i * ns + (int64_t)k, t->mirror(i, (int)k, t->state_slot(t->trees[i][k]))});
+  return B2RF_OK;
+}
+
+int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
+  if (!t || !t->d_bins) { set_error("b2rf_trainer_begin_group: trainer not bound"); return B2RF_ERR_STATE; }
+  if (t->inGroup) { set_error("b2rf_trainer_begin_group: previous group not finished"); return B2RF_ERR_STATE; }
+  cudaStream_t s = (cudaStream_t)stream;
+  if (t->stack.empty()) { if (n_cells) *n_cells = 0; if (t->tTotal == 0) t->tTotal = now_s() - t->tStart; return 0; }
+  const double tc0 = now_s();
+
+  // ---- RandomForest.selectNodesToSplit ----
+  const int64_t maxMem = (int64_t)t->p.maxMemoryInMB * 1024 * 1024;
+  t->group.clear(); t->groupTreeInsertOrder.clear();
+  std::vector<uint32_t> feats;  // [slots][Fsub]
+  std::vector<uint32_t> tmp(t->Fsub);
+  std::vector<char> treeSeen(t->T, 0);
+  int64_t mem = 0, cells = 0;
+  std::vector<int64_t> slotBase;
+  while (!t->stack.empty()) {
+    const auto [tr, ni] = t->stack.back();
+    int64_t totalBins;
+    if (t->subsampling) {
+      reservoir_features(t->F, t->Fsub, t->rng.nextLong(), tmp.data());  // drawn before the memory check
+      totalBins = 0;
+      for (int j = 0; j < t->Fsub; j++) totalBins += t->numBins[tmp[j]];
+    } else {
+      for (int j = 0; j < t->Fsub; j++) tmp[j] = (uint32_t)j;
+      totalBins = t->allBins;
+    }
+    const int64_t nodeMem = 3 * totalBins * 8;
+    if (!(mem + nodeMem <= maxMem || mem == 0)) break;
+    t->stack.pop_back();
+    if (!treeSeen[tr]) { treeSeen[tr] = 1; t->groupTreeInsertOrder.push_back(tr); }
+    t->group.push_back({tr, ni});
+    feats.insert(feats.end(), tmp.begin(), tmp.end());
+    slotBase.push_back(cells);
+    cells += totalBins;
+    mem += nodeMem;
+  }
+  const size_t nSlots = t->group.size();
+  if (cells > t->histCells) { set_error("b2rf_trainer_begin_group: histogram buffer too small for this node group"); return B2RF_ERR_ARG; }
+  t->groupCells = cells;
+
+  // ---- descriptors ----
+  if (!t->hSlotFo.ensure(nSlots * t->Fsub) || !t->hSlotBase.ensure(nSlots) || !t->hParent.ensure(nSlots * 4) || !t->hHasParent.ensure(nSlots) ||
+      !t->dSlotFo.ensure(nSlots * t->Fsub) || !t->dSlotBase.ensure(nSlots) || !t->dParent.ensure(nSlots * 4) || !t->dHasParent.ensure(nSlots) ||
+      !t->dRec.ensure(nSlots) || !t->hRec.ensure(nSlots) || !t->hTreeIds.ensure(t->T) || !t->dTreeIds.ensure(t->T))
+    return B2RF_ERR_CUDA;
+  int64_t maxNodes = 0;
+  for (size_t sl = 0; sl < nSlots; sl++) {
+    const GNode& g = t->group[sl];
+    const HNode& n = t->trees[g.tree][g.nidx];
+    uint32_t off = 0;
+    for (int j = 0; j < t->Fsub; j++) {
+      const uint32_t f = feats[sl * t->Fsub + j];
+      t->hSlotFo.p[sl * t->Fsub + j] = make_uint2(f, off);
+      off += (uint32_t)t->numBins[f];
+    }
+    t->hSlotBase.p[sl] = slotBase[sl];
+    const bool hasParent = level_of(n.id) > 0;
+    t->hHasParent.p[sl] = hasParent;
+    for (int q = 0; q < 4; q++) t->hParent.p[sl * 4 + q] = hasParent ? n.stats.calc[q] : 0.0;
+    t->pending.push_back({(int64_t)g.tree * t->nodeStride + g.nidx, t->mirror(g.tree, g.nidx, (int)sl)});
+    maxNodes = std::max<int64_t>(maxNodes, (int64_t)t->trees[g.tree].size());
+  }
+  (void)maxNodes;
+  // trees of this group, ascending, cut into launches whose histogram cells stay L2-resident
+  std::vector<int64_t> cellsPerTree(t->T, 0);
+  for (size_t sl = 0; sl < nSlots; sl++) {
+    int64_t c = 0;
+    for (int j = 0; j < t->Fsub; j++) c += t->numBins[feats[sl * t->Fsub + j]];
+    cellsPerTree[t->group[sl].tree] += c;
+  }
+  int nTg = 0;
+  for (int i = 0; i < t->T; i++) if (treeSeen[i]) t->hTreeIds.p[nTg++] = i;
+
+  // ---- uploads ----
+  // one scatter launch must not carry two records for the same node: keep the latest
+  {
+    std::unordered_map<int64_t, size_t> last;
+    last.reserve(t->pending.size() * 2);
+    size_t w = 0;
+    for (size_t i = 0; i < t->pending.size(); i++) {
+      auto it = last.find(t->pending[i].pos);
+      if (it == last.end()) { last.emplace(t->pending[i].pos, w); t->pending[w++] = t->pending[i]; }
+      else t->pending[it->second] = t->pending[i];
+    }
+    t->pending.resize(w);
+  }
+  const size_t nUpd = t->pending.size();
+  if (!t->hUpd.ensure(nUpd) || !t->dnUpd.ensure(nUpd)) return B2RF_ERR_CUDA;
+  memcpy(t->hUpd.p, t->pending.data(), nUpd * sizeof(DNodeUpdate));
+  t->pending.clear();
+  bool ok = true;
+  ok &= cuda_ok(cudaMemcpyAsync(t->dnUpd.p, t->hUpd.p, nUpd * sizeof(DNodeUpdate), cudaMemcpyHostToDevice, s), "upload node updates");
+  ok &= cuda_ok(launch_scatter_dnodes(t->dn.p, t->dnUpd.p, (int64_t)nUpd, s), "scatter node updates");
+  if (t->catPool.size() > t->catUploaded) {
+    if (t->catPool.size() > t->dCat.cap) {  // grow, keeping old contents
+      DevBuf<uint32_t> nb;
+      if (!nb.ensure(std::max<size_t>(t->catPool.size() * 2, 1024))) return B2RF_ERR_CUDA;
+      cudaStreamSynchronize(s);
+      t->dCat.release(); t->dCat = nb; t->catUploaded = 0;
+    }
+    ok &= cuda_ok(cudaMemcpyAsync(t->dCat.p + t->catUploaded, t->catPool.data() + t->catUploaded, (t->catPool.size() - t->catUploaded) * 4,
+                                  cudaMemcpyHostToDevice, s), "upload cat masks");
+    cudaStreamSynchronize(s);  // catPool is pageable host memory
+    t->catUploaded = t->catPool.size();
+  }
+  ok &= cuda_ok(cudaMemcpyAsync(t->dSlotFo.p, t->hSlotFo.p, nSlots * t->Fsub * sizeof(uint2), cudaMemcpyHostToDevice, s), "upload slot_fo");
+  ok &= cuda_ok(cudaMemcpyAsync(t->dSlotBase.p, t->hSlotBase.p, nSlots * 8, cudaMemcpyHostToDevice, s), "upload slot_base");
+  ok &= cuda_ok(cudaMemcpyAsync(t->dParent.p, t->hParent.p, nSlots * 32, cudaMemcpyHostToDevice, s), "upload parent stats");
+  ok &= cuda_ok(cudaMemcpyAsync(t->dHasParent.p, t->hHasParent.p, nSlots * 4, cudaMemcpyHostToDevice, s), "upload hasParent");
+  ok &= cuda_ok(cudaMemcpyAsync(t->dTreeIds.p, t->hTreeIds.p, (size_t)nTg * 4, cudaMemcpyHostToDevice, s), "upload tree ids");
+  ok &= cuda_ok(cudaMemsetAsync(t->d_hist, 0, (size_t)cells * 32, s), "zero histogram");
+  if (!ok) return B2RF_ERR_CUDA;
+  t->tChoose += now_s() - tc0;
+
+  // ---- K4 launches (findBestSplits.binSeqOp over all local rows) ----
+  cudaEventRecord(t->ev0, s);
+  HistLaunch a;
+  a.bins = t->d_bins; a.ldb = t->ldb; a.F = t->F; a.y = t->d_y; a.w = t->d_w; a.ldw = t->ldw; a.node = t->d_node; a.ldn = t->ldn;
+  a.n_rows = t->nLocal; a.dnodes = t->dn.p; a.nodeStride = t->nodeStride; a.catmasks = t->dCat.p;
+  a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.hist = t->d_hist;
+  int start = 0;
+  while (start < nTg) {
+    int end = start; int64_t c = 0;
+    while (end < nTg && (end == start || c + cellsPerTree[t->hTreeIds.p[end]] <= t->l2CellBudget)) { c += cellsPerTree[t->hTreeIds.p[end]]; end++; }
+    a.tree_ids = t->dTreeIds.p + start; a.Tg = end - start;
+    std::string err;
+    cudaError_t e = launch_hist(a, true, s, &err);
+    if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "hist launch"); return B2RF_ERR_CUDA; }
+    t->nHistLaunches++;
+    t->nScanned += (int64_t)(end - start) * t->nLocal;
+    start = end;
+  }
+  cudaEventRecord(t->ev1, s);
+  t->evPending = true;
+  t->inGroup = true;
+  if (n_cells) *n_cells = cells;
+  return 1;
+}
+
+int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
+  if (!t || !t->inGroup) { set_error("b2rf_trainer_end_group: no group in flight"); return B2RF_ERR_STATE; }
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t nSlots = t->group.size();
+  // ---- K5 ----
+  SplitLaunch a;
+  a.hist = t->d_hist; a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.nSlots = (int32_t)nSlots;
+  a.parent4 = t->dParent.p; a.hasParent = t->dHasParent.p; a.numBins = t->dNumBins.p; a.isCat = t->dIsCat.p;
+  a.minInstances = (double)t->p.minInstancesPerNode; a.minWeight = t->minWeightPerNode; a.minInfoGain = t->p.minInfoGain;
+  a.out = t->dRec.p;
+  if (!cuda_ok(launch_best_split(a, s), "best_split launch")) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaMemcpyAsync(t->hRec.p, t->dRec.p, nSlots * sizeof(SplitRec), cudaMemcpyDeviceToHost, s), "download split records")) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
+  const double tc0 = now_s();
+  if (t->evPending) { float ms = 0; if (cudaEventElapsedTime(&ms, t->ev0, t->ev1) == cudaSuccess) t->tHist += ms * 1e-3; t->evPending = false; }
+
+  // ---- driver tail of findBestSplits: trees in Scala map order, nodes in pop order ----
+  std::vector<int> order;
+  group_tree_order(t->groupTreeInsertOrder, order);
+  std::vector<std::vector<int>> slotsOfTree(t->T);
+  for (size_t sl = 0; sl < nSlots; sl++) slotsOfTree[t->group[sl].tree].push_back((int)sl);
+  int64_t needStride = t->nodeStride;
+  for (int tr : order) {
+    std::vector<HNode>& nodes = t->trees[tr];
+    for (int sl : slotsOfTree[tr]) {
+      const SplitRec& r = t->hRec.p[sl];
+      const int ni = t->group[sl].nidx;
+      const int id = nodes[ni].id;
+      const int lvl = level_of(id);
+      const bool isLeaf = (r.gain <= 0) || (lvl == t->p.maxDepth);
+      HNode& n = nodes[ni];
+      n.isLeaf = isLeaf;
+      n.stats.gain = r.gain; n.stats.impurity = r.impurity; n.stats.valid = r.valid != 0;
+      for (int q = 0; q < 4; q++) n.stats.calc[q] = r.parent[q];
+      t->trace.push_back({t->groupNo, tr, id, r.feature, r.splitIdx, r.gain, r.impurity, r.parent[0], r.parent[1], r.parent[2]});
+      if (!isLeaf) {
+        n.hasSplit = true; n.feature = r.feature;
+        if (t->arity[r.feature] == 0) { n.splitBin = r.splitIdx; n.threshold = t->thresholds[(size_t)r.feature * t->maxSplits + r.splitIdx]; }
+        else { n.catMaskIdx = (int32_t)(t->catPool.size() / 8); t->catPool.insert(t->catPool.end(), r.catmask, r.catmask + 8); n.splitBin = r.splitIdx; }
+        const bool childLeaf = (lvl + 1) == t->p.maxDepth;
+        const bool lLeaf = childLeaf || std::fabs(r.leftImp) < 0x1.0p-52;
+        const bool rLeaf = childLeaf || std::fabs(r.rightImp) < 0x1.0p-52;
+        HNode L, R;
+        L.id = 2 * id; L.isLeaf = lLeaf; L.stats.gain = NAN; L.stats.impurity = r.leftImp; for (int q = 0; q < 4; q++) L.stats.calc[q] = r.left[q];
+        R.id = 2 * id + 1; R.isLeaf = rLeaf; R.stats.gain = NAN; R.stats.impurity = r.rightImp; for (int q = 0; q < 4; q++) R.stats.calc[q] = r.right[q];
+        const int li = (int)nodes.size();
+        nodes.push_back(L); nodes.push_back(R);
+        nodes[ni].left = li;
+        needStride = std::max<int64_t>(needStride, (int64_t)nodes.size());
+        t->pending.push_back({(int64_t)tr * t->nodeStride + ni, t->mirror(tr, ni, SLOT_PENDING)});
+        t->pending.push_back({(int64_t)tr * t->nodeStride + li, t->mirror(tr, li, lLeaf ? SLOT_DEAD : SLOT_PENDING)});
+        t->pending.push_back({(int64_t)tr * t->nodeStride + li + 1, t->mirror(tr, li + 1, rLeaf ? SLOT_DEAD : SLOT_PENDING)});
+        if (!lLeaf) t->stack.push_back({tr, li});
+        if (!rLeaf) t->stack.push_back({tr, li + 1});
+      } else {
+        t->pending.push_back({(int64_t)tr * t->nodeStride + ni, t->mirror(tr, ni, SLOT_DEAD)});
+      }
+    }
+  }
+  if (needStride > t->nodeStride) { const int rc = grow_node_table(t, needStride, s); if (rc) return rc; }
+  t->inGroup = false;
+  t->groupNo++;
+  t->exported = false;
+  t->tChoose += now_s() - tc0;
+  return B2RF_OK;
+}
+
+int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts4) {
+  if (!t) return B2RF_ERR_ARG;
+  if (h_seconds5) { h_seconds5[0] = 0; h_seconds5[1] = 0; h_seconds5[2] = t->tHist; h_seconds5[3] = t->tChoose; h_seconds5[4] = t->tTotal > 0 ? t->tTotal : now_s() - t->tStart; }
+  if (h_counts4) {
+    int64_t nodes = 0; for (auto& tr : t->trees) nodes += (int64_t)tr.size();
+    h_counts4[0] = t->groupNo; h_counts4[1] = t->nHistLaunches; h_counts4[2] = t->nScanned; h_counts4[3] = nodes;
+  }
+  return B2RF_OK;
+}
+
+// LearningNode.toNode(prune = true): pre-order flattening; an internal node whose children are leaves with equal
+// predictions collapses into a leaf.
+static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
+  const HNode& n = t->trees[tr][ni];
+  const int me = (int)(t->x_feature.size() - base);
+  t->x_feature.push_back(-1); t->x_left.push_back(-1); t->x_right.push_back(-1); t->x_ncat.push_back(0);
+  t->x_cat_off.push_back((int32_t)t->x_cats.size()); t->x_cat_len.push_back(0);
+  t->x_threshold.push_back(0); t->x_prediction.push_back(0); t->x_impurity.push_back(0); t->x_gain.push_back(0);
+  for (int q = 0; q < 4; q++) t->x_stats.push_back(n.stats.calc[q]);
+  const size_t at = base + me;
+  if (n.left >= 0) {
+    const size_t catMark = t->x_cats.size();
+    const int l = flatten_node(t, tr, n.left, base);
+    const int r = flatten_node(t, tr, n.left + 1, base);
+    const bool bothLeaves = t->x_feature[base + l] < 0 && t->x_feature[base + r] < 0;
+    if (bothLeaves && t->x_prediction[base + l] == t->x_prediction[base + r]) {
+      const double pred = t->x_prediction[base + l];
+      const size_t keep = at + 1;
+      t->x_feature.resize(keep); t->x_left.resize(keep); t->x_right.resize(keep); t->x_ncat.resize(keep); t->x_cat_off.resize(keep);
+      t->x_cat_len.resize(keep); t->x_threshold.resize(keep); t->x_prediction.resize(keep); t->x_impurity.resize(keep); t->x_gain.resize(keep);
+      t->x_stats.resize(keep * 4); t->x_cats.resize(catMark);
+      t->x_prediction[at] = pred; t->x_impurity[at] = n.stats.impurity;
+      return me;
+    }
+    t->x_feature[at] = n.feature; t->x_left[at] = l; t->x_right[at] = r; t->x_threshold[at] = n.threshold;
+    t->x_prediction[at] = vpred(n.stats.calc); t->x_impurity[at] = n.stats.impurity; t->x_gain[at] = n.stats.gain;
+    if (n.catMaskIdx >= 0) {
+      t->x_ncat[at] = t->numBins[n.feature];
+      t->x_cat_off[at] = (int32_t)t->x_cats.size();
+      const uint32_t* m = &t->catPool[(size_t)n.catMaskIdx * 8];
+      int cnt = 0;
+      for (int c = 0; c < 256; c++) if ((m[c >> 5] >> (c & 31)) & 1u) { t->x_cats.push_back((double)c); cnt++; }
+      t->x_cat_len[at] = cnt;
+    }
+    return me;
+  }
+  t->x_prediction[at] = vpred(n.stats.calc);
+  t->x_impurity[at] = n.stats.valid ? n.stats.impurity : -1.0;
+  return me;
+}
+
+static void do_export(b2rf_trainer* t) {
+  if (t->exported) return;
+  t->x_tree_off.clear(); t->x_feature.clear(); t->x_left.clear(); t->x_right.clear(); t->x_ncat.clear(); t->x_cat_off.clear(); t->x_cat_len.clear();
+  t->x_threshold.clear(); t->x_prediction.clear(); t->x_impurity.clear(); t->x_gain.clear(); t->x_stats.clear(); t->x_cats.clear();
+  t->x_tree_off.push_back(0);
+  for (int tr = 0; tr < t->T; tr++) {
+    // categorical lists are appended after the subtree, so a node's cat_off is only final for kept nodes
+    flatten_node(t, tr, 0, (int64_t)t->x_feature.size());
+    t->x_tree_off.push_back((int64_t)t->x_feature.size());
+  }
+  t->exported = true;
+}
+
+int b2rf_trainer_forest_sizes(b2rf_trainer* t, int64_t* n_nodes, int64_t* n_cats) {
+  if (!t) return B2RF_ERR_ARG;
+  do_export(t);
+  if (n_nodes) *n_nodes = (int64_t)t->x_feature.size();
+  if (n_cats) *n_cats = (int64_t)t->x_cats.size();
+  return B2RF_OK;
+}
+
+int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature, double* h_threshold, int32_t* h_left, int32_t* h_right,
+                        double* h_prediction, double* h_impurity, double* h_gain, double* h_stats4, int32_t* h_ncat, int32_t* h_cat_off,
+                        int32_t* h_cat_len, double* h_cats) {
+  if (!t) return B2RF_ERR_ARG;
+  do_export(t);
+  const size_t n = t->x_feature.size();
+  memcpy(h_tree_off, t->x_tree_off.data(), t->x_tree_off.size() * 8);
+  memcpy(h_feature, t->x_feature.data(), n * 4); memcpy(h_threshold, t->x_threshold.data(), n * 8);
+  memcpy(h_left, t->x_left.data(), n * 4); memcpy(h_right, t->x_right.data(), n * 4);
+  memcpy(h_prediction, t->x_prediction.data(), n * 8); memcpy(h_impurity, t->x_impurity.data(), n * 8); memcpy(h_gain, t->x_gain.data(), n * 8);
+  memcpy(h_stats4, t->x_stats.data(), n * 32);
+  memcpy(h_ncat, t->x_ncat.data(), n * 4); memcpy(h_cat_off, t->x_cat_off.data(), n * 4); memcpy(h_cat_len, t->x_cat_len.data(), n * 4);
+  if (!t->x_cats.empty()) memcpy(h_cats, t->x_cats.data(), t->x_cats.size() * 8);
+  return B2RF_OK;
+}
+
+int64_t b2rf_trainer_trace_size(const b2rf_trainer* t) { return t ? (int64_t)t->trace.size() : 0; }
+int b2rf_trainer_trace(const b2rf_trainer* t, int32_t* h_ints, double* h_dbls) {
+  if (!t) return B2RF_ERR_ARG;
+  for (size_t i = 0; i < t->trace.size(); i++) {
+    const auto& r = t->trace[i];
+    h_ints[i * 5] = r.g; h_ints[i * 5 + 1] = r.t; h_ints[i * 5 + 2] = r.id; h_ints[i * 5 + 3] = r.f; h_ints[i * 5 + 4] = r.s;
+    h_dbls[i * 5] = r.gain; h_dbls[i * 5 + 1] = r.imp; h_dbls[i * 5 + 2] = r.cnt; h_dbls[i * 5 + 3] = r.sum; h_dbls[i * 5 + 4] = r.sq;
+  }
+  return B2RF_OK;
+}
+
+}  // extern "C"

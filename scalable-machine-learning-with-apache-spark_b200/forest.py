@@ -1,0 +1,168 @@
+"""Fitted model arrays (LearningNode.toNode(prune=true) output, pre-order per tree) and the model-side API of
+pyspark's DecisionTreeRegressionModel / RandomForestRegressionModel (`ML 06 - Decision Trees.py:137,141,153,188`,
+`ML 07 ...:162`): predict, featureImportances, toDebugString, depth, numNodes."""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+
+import numpy as np
+
+
+def java_double_str(x: float) -> str:
+    """java.lang.Double.toString formatting (used by MLlib's toDebugString)."""
+    x = float(x)
+    if x != x:
+        return "NaN"
+    if x in (float("inf"), float("-inf")):
+        return "Infinity" if x > 0 else "-Infinity"
+    if x == 0:
+        return "-0.0" if str(x).startswith("-") else "0.0"
+    ax = abs(x)
+    r = repr(ax)
+    if "e" in r or "E" in r:
+        mant, exp = r.lower().split("e")
+        digits = mant.replace(".", "")
+        e10 = int(exp) + (mant.index(".") if "." in mant else len(mant)) - 1
+    else:
+        ip, _, fp = r.partition(".")
+        digits = (ip + fp).lstrip("0")
+        e10 = len(ip) - 1 if ip.strip("0") else -(len(fp) - len(fp.lstrip("0")) + 1)
+    digits = digits.rstrip("0") or "0"
+    sign = "-" if x < 0 else ""
+    if 1e-3 <= ax < 1e7:
+        if e10 >= 0:
+            ip = digits[: e10 + 1].ljust(e10 + 1, "0")
+            fp = digits[e10 + 1:] or "0"
+        else:
+            ip = "0"
+            fp = "0" * (-e10 - 1) + digits
+        return f"{sign}{ip}.{fp}"
+    return f"{sign}{digits[0]}.{digits[1:] or '0'}E{e10}"
+
+
+@dataclass
+class Forest:
+    num_features: int
+    tree_off: np.ndarray      # int64 [T+1]
+    feature: np.ndarray       # int32 [n]; -1 = leaf
+    threshold: np.ndarray     # f64 [n]
+    left: np.ndarray          # int32 [n] tree-local pre-order index
+    right: np.ndarray
+    prediction: np.ndarray    # f64 [n]
+    impurity: np.ndarray
+    gain: np.ndarray
+    stats: np.ndarray         # f64 [n,4] weight, sum, sumsq, rawCount
+    ncat: np.ndarray          # int32 [n] numCategories (0 = continuous split)
+    cat_off: np.ndarray
+    cat_len: np.ndarray
+    cats: np.ndarray          # f64 left-category lists
+    thresholds: np.ndarray = None   # [F, maxSplits] split candidates (findSplits output)
+    nsplits: np.ndarray = None
+    timers: dict = field(default_factory=dict)
+    counters: dict = field(default_factory=dict)
+    trace_i: np.ndarray = None
+    trace_d: np.ndarray = None
+    uid: str = ""
+    _dev: dict = field(default_factory=dict, repr=False)
+
+    # ---- structure ----
+    @property
+    def num_trees(self) -> int:
+        return len(self.tree_off) - 1
+
+    def tree_slice(self, t: int) -> slice:
+        return slice(int(self.tree_off[t]), int(self.tree_off[t + 1]))
+
+    def num_nodes(self, t: int | None = None) -> int:
+        if t is None:
+            return int(self.tree_off[-1])
+        return int(self.tree_off[t + 1] - self.tree_off[t])
+
+    def depth(self, t: int = 0) -> int:
+        base = int(self.tree_off[t])
+
+        def d(i):
+            if self.feature[base + i] < 0:
+                return 0
+            return 1 + max(d(int(self.left[base + i])), d(int(self.right[base + i])))
+        return d(0)
+
+    # ---- TreeEnsembleModel.featureImportances (perTreeNormalization = true) ----
+    def feature_importances(self) -> np.ndarray:
+        total = np.zeros(self.num_features)
+        for t in range(self.num_trees):
+            s = self.tree_slice(t)
+            f = self.feature[s]
+            m = f >= 0
+            imp = np.zeros(self.num_features)
+            np.add.at(imp, f[m], self.gain[s][m] * self.stats[s][m, 0])
+            norm = imp.sum()
+            if norm != 0:
+                total += imp / norm
+        tot = total.sum()
+        return total / tot if tot != 0 else total
+
+    # ---- toDebugString ----
+    def _subtree(self, base: int, i: int, indent: int, out: list):
+        p = " " * indent
+        if self.feature[base + i] < 0:
+            out.append(f"{p}Predict: {java_double_str(self.prediction[base + i])}\n")
+            return
+        f = int(self.feature[base + i])
+        if self.ncat[base + i] == 0:
+            l = f"feature {f} <= {java_double_str(self.threshold[base + i])}"
+            r = f"feature {f} > {java_double_str(self.threshold[base + i])}"
+        else:
+            o, n = int(self.cat_off[base + i]), int(self.cat_len[base + i])
+            cs = "{" + ",".join(java_double_str(c) for c in sorted(self.cats[o:o + n])) + "}"
+            l, r = f"feature {f} in {cs}", f"feature {f} not in {cs}"
+        out.append(f"{p}If ({l})\n")
+        self._subtree(base, int(self.left[base + i]), indent + 1, out)
+        out.append(f"{p}Else ({r})\n")
+        self._subtree(base, int(self.right[base + i]), indent + 1, out)
+
+    def to_debug_string(self, ensemble: bool | None = None) -> str:
+        ensemble = self.num_trees > 1 if ensemble is None else ensemble
+        out = []
+        if not ensemble:
+            out.append(f"DecisionTreeRegressionModel: uid={self.uid}, depth={self.depth(0)}, numNodes={self.num_nodes(0)}, "
+                       f"numFeatures={self.num_features}\n")
+            self._subtree(0, 0, 2, out)
+        else:
+            out.append(f"RandomForestRegressionModel: uid={self.uid}, numTrees={self.num_trees}, numFeatures={self.num_features}\n")
+            for t in range(self.num_trees):
+                out.append(f"  Tree {t} (weight 1.0):\n")
+                self._subtree(int(self.tree_off[t]), 0, 4, out)
+        return "".join(out)
+
+    # ---- K7 predict on the device ----
+    def _device_arrays(self, device):
+        import torch
+        key = str(device)
+        if key not in self._dev:
+            def T(a, dt):
+                return torch.as_tensor(np.ascontiguousarray(a), dtype=dt).to(device)
+            cats = self.cats if len(self.cats) else np.zeros(1)
+            self._dev[key] = dict(tree_off=T(self.tree_off, torch.int64), feature=T(self.feature, torch.int32),
+                                  threshold=T(self.threshold, torch.float64), left=T(self.left, torch.int32), right=T(self.right, torch.int32),
+                                  prediction=T(self.prediction, torch.float64), ncat=T(self.ncat, torch.int32),
+                                  cat_off=T(self.cat_off, torch.int32), cat_len=T(self.cat_len, torch.int32), cats=T(cats, torch.float64))
+        return self._dev[key]
+
+    def predict(self, X):
+        """X: torch.float64 CUDA tensor [n, F] (row-major).  Returns torch.float64 [n] on the same device."""
+        import torch
+        from ._lib import check, lib
+        if not (isinstance(X, torch.Tensor) and X.is_cuda):
+            raise TypeError("Forest.predict needs a CUDA tensor: this package has no CPU path")
+        X = X.to(torch.float64).contiguous()
+        d = self._device_arrays(X.device)
+        out = torch.empty(X.shape[0], dtype=torch.float64, device=X.device)
+        with torch.cuda.device(X.device):
+            st = torch.cuda.current_stream().cuda_stream
+            check(lib().b2rf_predict(X.data_ptr(), X.stride(0), X.shape[0], self.num_trees, d["tree_off"].data_ptr(), d["feature"].data_ptr(),
+                                     d["threshold"].data_ptr(), d["left"].data_ptr(), d["right"].data_ptr(), d["prediction"].data_ptr(),
+                                     d["ncat"].data_ptr(), d["cat_off"].data_ptr(), d["cat_len"].data_ptr(), d["cats"].data_ptr(),
+                                     out.data_ptr(), C.c_void_p(st)))
+        return out

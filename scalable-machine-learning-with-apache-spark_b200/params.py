@@ -1,0 +1,51 @@
+"""Tree-training parameters with pyspark.ml's names and defaults (reference call sites
+`ML 06 - Decision Trees.py:75,118`, `ML 07 - Random Forests and Hyperparameter Tuning.py:41,74-77`, `ML 08 - Hyperopt.py:71,97`)."""
+from __future__ import annotations
+
+from dataclasses import dataclass, replace
+
+from ._lib import B2rfParams, check, lib
+
+
+@dataclass
+class TreeParams:
+    maxDepth: int = 5
+    maxBins: int = 32
+    minInstancesPerNode: int = 1
+    minWeightFractionPerNode: float = 0.0
+    minInfoGain: float = 0.0
+    maxMemoryInMB: int = 256
+    cacheNodeIds: bool = False        # accepted, ignored (row->node ids are always cached on the device)
+    checkpointInterval: int = 10      # accepted, ignored
+    impurity: str = "variance"
+    subsamplingRate: float = 1.0
+    numTrees: int = 1
+    featureSubsetStrategy: str = "auto"
+    bootstrap: bool = False           # DecisionTreeRegressor: False; RandomForestRegressor default: True
+    seed: int = 0
+
+    def copy(self, **kw) -> "TreeParams":
+        return replace(self, **kw)
+
+    def validate(self):
+        if self.impurity != "variance":
+            raise ValueError(f"impurity must be 'variance' for regression, got {self.impurity!r}")
+        if self.maxDepth < 0 or self.maxDepth > 30:
+            raise ValueError(f"DecisionTree currently only supports maxDepth <= 30, but was given maxDepth = {self.maxDepth}.")
+        if self.maxBins < 2:
+            raise ValueError(f"maxBins must be >= 2, got {self.maxBins}")
+        if not (0.0 < self.subsamplingRate <= 1.0):
+            raise ValueError(f"subsamplingRate must be in (0, 1], got {self.subsamplingRate}")
+        if self.minInstancesPerNode < 1:
+            raise ValueError("minInstancesPerNode must be >= 1")
+        if not (0.0 <= self.minWeightFractionPerNode < 0.5):
+            raise ValueError("minWeightFractionPerNode must be in [0, 0.5)")
+
+    def features_per_node(self, F: int) -> int:
+        return check(lib().b2rf_features_per_node(self.featureSubsetStrategy.encode(), F, self.numTrees))
+
+    def to_c(self, F: int) -> B2rfParams:
+        self.validate()
+        return B2rfParams(int(self.maxDepth), int(self.maxBins), int(self.minInstancesPerNode), int(self.numTrees),
+                          self.features_per_node(F), int(self.maxMemoryInMB), int(bool(self.bootstrap)), 0, float(self.minInfoGain),
+                          float(self.minWeightFractionPerNode), float(self.subsamplingRate), int(self.seed))

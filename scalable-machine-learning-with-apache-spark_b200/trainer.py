@@ -1,0 +1,283 @@
+"""Tensor-level entry point of the hot path: ``fit_tensors`` = RandomForest.run of Spark MLlib 3.1.2 on device tensors.
+
+It is what `DecisionTreeRegressor.fit` / `RandomForestRegressor.fit` (`ML 06 - Decision Trees.py:126`,
+`ML 07 - Random Forests and Hyperparameter Tuning.py:116,149`) reach after the Spark adapter (spark.py) has turned the
+`features` column into a tensor.  PyTorch here is plumbing only (device memory, streams, torch.distributed); every
+pass over rows is a hand-written kernel behind the C-ABI in include/b2rf.h.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import time
+
+import numpy as np
+import torch
+
+from ._lib import check, lib
+from .forest import Forest
+from .params import TreeParams
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _pad(n: int, m: int = 128) -> int:
+    return max(m, (n + m - 1) // m * m)
+
+
+def _require_cuda(t: torch.Tensor, name: str):
+    if not (isinstance(t, torch.Tensor) and t.is_cuda):
+        raise TypeError(f"{name} must be a CUDA tensor: b2rf has no CPU fallback")
+
+
+def _dist_info(group):
+    import torch.distributed as dist
+    if group is None and not (dist.is_available() and dist.is_initialized()):
+        return None, 0, 1
+    return dist, dist.get_rank(group), dist.get_world_size(group)
+
+
+# ------------------------------------------------------------------------------------------------
+# stage wrappers (K1, K2, K3, K4) — thin; used by fit_tensors and by the parity tests
+# ------------------------------------------------------------------------------------------------
+def find_splits(sample: torch.Tensor, arity: torch.Tensor, max_possible_bins: int, weighted_num_samples: float):
+    """K1.  sample: f64 [n_s, F] CUDA; arity: int32 [F] CUDA.  Returns (thresholds f64 [F, maxSplits], nsplits int32 [F])."""
+    _require_cuda(sample, "sample")
+    sample = sample.contiguous()
+    n_s, F = sample.shape
+    ms = max(max_possible_bins - 1, 1)
+    thr = torch.zeros((F, ms), dtype=torch.float64, device=sample.device)
+    ns = torch.zeros(F, dtype=torch.int32, device=sample.device)
+    if n_s == 0:
+        return thr, ns
+    wsb = lib().b2rf_find_splits_workspace_bytes(n_s, F)
+    ws = torch.empty(wsb, dtype=torch.uint8, device=sample.device)
+    check(lib().b2rf_find_splits(sample.data_ptr(), n_s, F, arity.data_ptr(), max_possible_bins, float(weighted_num_samples),
+                                 thr.data_ptr(), ns.data_ptr(), ws.data_ptr(), wsb, _stream()))
+    return thr, ns
+
+
+def sample_rows(X: torch.Tensor, row0_global: int, seed: int, fraction: float) -> torch.Tensor:
+    """Row sample for findSplits when fraction < 1 (hash of the global row index)."""
+    _require_cuda(X, "X")
+    n, F = X.shape
+    cap = int(n * fraction + 6.0 * (n * fraction * (1 - fraction)) ** 0.5 + 64)
+    out = torch.empty((cap, F), dtype=torch.float64, device=X.device)
+    cnt = torch.zeros(1, dtype=torch.int64, device=X.device)
+    check(lib().b2rf_sample_rows(X.data_ptr(), X.stride(0), n, row0_global, F, seed, float(fraction), out.data_ptr(), cap, cnt.data_ptr(),
+                                 _stream()))
+    k = int(cnt.item())
+    if k > cap:
+        raise RuntimeError("b2rf sample_rows: capacity exceeded")
+    return out[:k]
+
+
+def bin_features(X: torch.Tensor, thresholds: torch.Tensor, nsplits: torch.Tensor, arity: torch.Tensor, bins: torch.Tensor = None,
+                 row0: int = 0) -> torch.Tensor:
+    """K2.  X f64 [n, F] row-major CUDA -> column-major uint8 bins [F, ldb] (rows row0..row0+n)."""
+    _require_cuda(X, "X")
+    n, F = X.shape
+    if X.stride(1) != 1:
+        X = X.contiguous()
+    if bins is None:
+        bins = torch.zeros((F, _pad(row0 + n)), dtype=torch.uint8, device=X.device)
+    err = torch.zeros(1, dtype=torch.int32, device=X.device)
+    check(lib().b2rf_bin(X.data_ptr(), X.stride(0), n, F, thresholds.data_ptr(), nsplits.data_ptr(), arity.data_ptr(), thresholds.shape[1],
+                         bins.data_ptr(), bins.stride(0), row0, err.data_ptr(), _stream()))
+    e = int(err.item())
+    if e:
+        from ._lib import ERR_DATA, IllegalArgumentException
+        f = e - 1
+        raise IllegalArgumentException(ERR_DATA, f"DecisionTree given invalid data: Feature {f} is categorical with values in "
+                                       f"{{0,...,{int(arity[f].item()) - 1}}}, but a data point gives it an out-of-range value.")
+    return bins
+
+
+def bag(seed: int, part_offsets, part0: int, T: int, rate: float, bootstrap: bool, device, ld: int = None):
+    """K3.  Returns (w uint8 [T, ld], node int32 [T, ld])."""
+    po = np.ascontiguousarray(part_offsets, np.int64)
+    n = int(po[-1])
+    ld = ld or _pad(n)
+    w = torch.zeros((T, ld), dtype=torch.uint8, device=device)
+    node = torch.full((T, ld), -1, dtype=torch.int32, device=device)
+    with torch.cuda.device(device):
+        check(lib().b2rf_bag(int(seed), po.ctypes.data_as(C.c_void_p), len(po) - 1, int(part0), T, float(rate), int(bool(bootstrap)),
+                             w.data_ptr(), w.stride(0), node.data_ptr(), node.stride(0), _stream()))
+    return w, node
+
+
+def hist_build(bins, y, w, slot_of_row, tree_ids, slot_fo, slot_base, n_rows, total_cells):
+    """K4 stand-alone.  Returns hist f64 [total_cells, 4]."""
+    hist = torch.zeros((total_cells, 4), dtype=torch.float64, device=bins.device)
+    check(lib().b2rf_hist_build(bins.data_ptr(), bins.stride(0), bins.shape[0], y.data_ptr(), w.data_ptr(), w.stride(0), slot_of_row.data_ptr(),
+                                slot_of_row.stride(0), tree_ids.data_ptr(), tree_ids.numel(), n_rows, slot_fo.data_ptr(), slot_base.data_ptr(),
+                                slot_fo.shape[1], hist.data_ptr(), _stream()))
+    return hist
+
+
+# ------------------------------------------------------------------------------------------------
+# multi-rank plumbing (device-agnostic: exercised on CPU with gloo in tests/test_cpu_distributed.py)
+# ------------------------------------------------------------------------------------------------
+def global_numbering(n_local: int, n_parts_local: int, dist, group, device, part0=None):
+    """Rows and emulated partitions are numbered rank-major.  Returns (N_global, row0_global, part0_global)."""
+    if dist is None or dist.get_world_size(group) == 1:
+        return n_local, 0, (part0 or 0)
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    info = torch.tensor([n_local, n_parts_local], dtype=torch.int64, device=device)
+    allinfo = [torch.zeros_like(info) for _ in range(world)]
+    dist.all_gather(allinfo, info, group=group)
+    counts = [int(a[0].item()) for a in allinfo]
+    pcounts = [int(a[1].item()) for a in allinfo]
+    return sum(counts), sum(counts[:rank]), (sum(pcounts[:rank]) if part0 is None else part0)
+
+
+def gather_samples(samp: torch.Tensor, dist, group) -> torch.Tensor:
+    """findSplits needs the whole (small) row sample on every rank: all-gather of ragged [n_r, F] blocks, rank order."""
+    if dist is None or dist.get_world_size(group) == 1:
+        return samp
+    world = dist.get_world_size(group)
+    cnt = torch.tensor([samp.shape[0]], dtype=torch.int64, device=samp.device)
+    cnts = [torch.zeros_like(cnt) for _ in range(world)]
+    dist.all_gather(cnts, cnt, group=group)
+    cnts = [int(c.item()) for c in cnts]
+    buf = torch.zeros((max(max(cnts), 1), samp.shape[1]), dtype=samp.dtype, device=samp.device)
+    buf[: samp.shape[0]] = samp
+    bufs = [torch.empty_like(buf) for _ in range(world)]
+    dist.all_gather(bufs, buf, group=group)
+    return torch.cat([b[:c] for b, c in zip(bufs, cnts)], 0)
+
+
+# ------------------------------------------------------------------------------------------------
+# the fit
+# ------------------------------------------------------------------------------------------------
+def default_partitions(n_rows: int, rows_per_partition: int = 4096):
+    """Emulated Spark partition layout used when the caller gives none: contiguous chunks of rows_per_partition rows."""
+    P = max(1, (n_rows + rows_per_partition - 1) // rows_per_partition)
+    return np.minimum(np.arange(P + 1, dtype=np.int64) * rows_per_partition, n_rows)
+
+
+def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, part_offsets=None, part0: int = None, group=None,
+                keep_trace: bool = False, prebinned=None) -> Forest:
+    """Train a forest on this rank's rows.
+
+    X: f64 [n_local, F] CUDA, row-major (the VectorAssembler `features` column); y: f64 [n_local];
+    arity[F]: 0 = continuous, k > 0 = categorical with k values (from the column's ml_attr metadata);
+    part_offsets: local row offsets of the emulated Spark partitions (bagging streams are seeded per partition, A.4);
+    part0: global index of this rank's first partition (default: partitions are numbered rank-major).
+    With torch.distributed initialised, rows are sharded over ranks and only per-group histograms are all-reduced.
+    """
+    _require_cuda(X, "X")
+    _require_cuda(y, "y")
+    dev = X.device
+    L = lib()
+    t_start = time.perf_counter()
+    with torch.cuda.device(dev):
+        y = y.to(torch.float64).contiguous()
+        n_local, F = X.shape
+        arity_np = np.ascontiguousarray(arity, np.int32)
+        if arity_np.shape != (F,):
+            raise ValueError("arity must have one entry per feature")
+        dist, rank, world = _dist_info(group)
+        if part_offsets is None:
+            part_offsets = default_partitions(n_local)
+        po = np.ascontiguousarray(part_offsets, np.int64)
+        if po[0] != 0 or po[-1] != n_local:
+            raise ValueError("part_offsets must start at 0 and end at the local row count")
+        N, row0, part0 = global_numbering(n_local, len(po) - 1, dist, group, dev, part0)
+        cp = params.to_c(F)
+        meta_max_bins = check(L.b2rf_check_metadata(C.byref(cp), F, arity_np.ctypes.data_as(C.c_void_p), N))
+        mpb = min(params.maxBins, N)
+        T = params.numTrees
+        arity_d = torch.as_tensor(arity_np, device=dev)
+        torch.cuda.synchronize(dev)
+        t0 = time.perf_counter()
+
+        # ---- findSplits (K1) ----
+        fraction = L.b2rf_samples_fraction(N, meta_max_bins)
+        if fraction < 1.0:
+            samp = sample_rows(X, row0, params.seed, fraction)
+        else:
+            samp = X
+        samp = gather_samples(samp, dist, group)
+        thr, ns = find_splits(samp, arity_d, mpb, fraction * float(N))
+        thr_h = thr.cpu().numpy()
+        ns_h = ns.cpu().numpy()
+        torch.cuda.synchronize(dev)
+        t1 = time.perf_counter()
+
+        # ---- TreePoint (K2) + BaggedPoint (K3) ----
+        ld = _pad(n_local)
+        if prebinned is not None:
+            bins = prebinned
+        else:
+            bins = torch.empty((F, ld), dtype=torch.uint8, device=dev)
+            bin_features(X, thr, ns, arity_d, bins=bins, row0=0)
+        w, node = bag(params.seed, po, part0, T, params.subsamplingRate, params.bootstrap, dev, ld=ld)
+        torch.cuda.synchronize(dev)
+        t2 = time.perf_counter()
+
+        # ---- RandomForest.run loop ----
+        h = C.c_void_p()
+        check(L.b2rf_trainer_create(C.byref(cp), F, arity_np.ctypes.data_as(C.c_void_p), ns_h.ctypes.data_as(C.c_void_p),
+                                    thr_h.ctypes.data_as(C.c_void_p), N, C.byref(h)))
+        try:
+            cells = int(L.b2rf_trainer_max_group_cells(h))
+            hist = torch.empty(cells * 4, dtype=torch.float64, device=dev)
+            check(L.b2rf_trainer_bind(h, bins.data_ptr(), bins.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0), node.data_ptr(),
+                                      node.stride(0), n_local, hist.data_ptr(), cells))
+            ncell = C.c_int64()
+            st = _stream()
+            t_comm = 0.0
+            while check(L.b2rf_trainer_begin_group(h, C.byref(ncell), st)) == 1:
+                if world > 1:
+                    dist.all_reduce(hist[: ncell.value * 4], group=group)   # DTStatsAggregator.merge (reduceByKey), row a7
+                check(L.b2rf_trainer_end_group(h, st))
+            torch.cuda.synchronize(dev)
+            t3 = time.perf_counter()
+            forest = _export(h, F, keep_trace)
+        finally:
+            L.b2rf_trainer_destroy(h)
+        forest.thresholds, forest.nsplits = thr_h, ns_h
+        tm = forest.timers
+        tm.update(init=(t0 - t_start) + (t2 - t1), findSplits=t1 - t0, total=t3 - t_start, loop=t3 - t2, comm=t_comm)
+        forest.counters.update(rows=N, rows_local=n_local, partitions=len(po) - 1, world=world, fraction=fraction)
+        return forest
+
+
+def _export(h, F: int, keep_trace: bool) -> Forest:
+    L = lib()
+    nn, nc = C.c_int64(), C.c_int64()
+    check(L.b2rf_trainer_forest_sizes(h, C.byref(nn), C.byref(nc)))
+    n, ncat = nn.value, nc.value
+    sec = np.zeros(5)
+    cnt = np.zeros(4, np.int64)
+    L.b2rf_trainer_stats(h, sec.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p))
+    T = None
+    # number of trees = len(tree_off) - 1; query through a first export of tree_off sized generously
+    def Z(shape, dt):
+        return np.zeros(shape, dt)
+    # the trainer knows T; tree_off has T+1 entries <= n+1
+    tree_off = Z(n + 2, np.int64)
+    feature, left, right = Z(n, np.int32), Z(n, np.int32), Z(n, np.int32)
+    threshold, prediction, impurity, gain = Z(n, np.float64), Z(n, np.float64), Z(n, np.float64), Z(n, np.float64)
+    stats = Z((n, 4), np.float64)
+    ncat_a, cat_off, cat_len = Z(n, np.int32), Z(n, np.int32), Z(n, np.int32)
+    cats = Z(max(ncat, 1), np.float64)
+    P = lambda a: a.ctypes.data_as(C.c_void_p)
+    tree_off[:] = -1
+    check(L.b2rf_trainer_export(h, P(tree_off), P(feature), P(threshold), P(left), P(right), P(prediction), P(impurity), P(gain), P(stats),
+                                P(ncat_a), P(cat_off), P(cat_len), P(cats)))
+    T = int(np.argmax(tree_off == n)) if n > 0 else 0
+    # tree_off is strictly increasing (every tree has >= 1 node) and ends at n
+    T = int(np.nonzero(tree_off == n)[0][0])
+    tree_off = tree_off[: T + 1].copy()
+    fo = Forest(F, tree_off, feature, threshold, left, right, prediction, impurity, gain, stats, ncat_a, cat_off, cat_len, cats[:ncat])
+    fo.timers = dict(findBestSplits=float(sec[2]), chooseSplits=float(sec[3]))
+    fo.counters = dict(groups=int(cnt[0]), hist_launches=int(cnt[1]), rows_trees_scanned=int(cnt[2]), learning_nodes=int(cnt[3]))
+    if keep_trace:
+        nt = int(L.b2rf_trainer_trace_size(h))
+        ti, td = Z((nt, 5), np.int32), Z((nt, 5), np.float64)
+        check(L.b2rf_trainer_trace(h, P(ti), P(td)))
+        fo.trace_i, fo.trace_d = ti, td
+    return fo

@@ -1,0 +1,285 @@
+"""GPU parity tests: every kernel and the whole fit against the CPU oracle on the same seeded inputs, through the C-ABI.
+Contract (BASELINE.json north_star): (1) bin codes and histogram counts bit-exact, (2) fp64 label sums to 1e-9 relative,
+(3) tree structure / thresholds / predictions identical, test RMSE within 1e-6."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import REL, assert_forest_parity, assert_trace_parity, rmse
+
+pytestmark = pytest.mark.gpu
+
+
+def _airbnb(b2rf, n=7146, seed=42):
+    X, y, arity = b2rf.synth.airbnb(n, seed=seed)
+    ntr = int(n * 0.8)
+    return X[:ntr].numpy(), y[:ntr].numpy(), X[ntr:].numpy(), y[ntr:].numpy(), arity
+
+
+def _fit_both(b2rf, oracle, cuda, X, y, arity, part_offsets=None, **kw):
+    from b2rf import trainer
+    p = b2rf.TreeParams(**kw)
+    if part_offsets is None:
+        part_offsets = trainer.default_partitions(len(y), 1024)
+    Xd = torch.as_tensor(X, device=cuda)
+    yd = torch.as_tensor(y, device=cuda)
+    g = trainer.fit_tensors(Xd, yd, arity, p, part_offsets=part_offsets, keep_trace=True)
+    N = len(y)
+    mpb = min(p.maxBins, N)
+    meta_max = max([a if a > 1 else mpb for a in arity])
+    req = max(meta_max * meta_max, 10000)
+    fraction = req / N if req < N else 1.0
+    sample_idx = None
+    if fraction < 1.0:
+        sample_idx = np.nonzero(oracle.sample_keep(p.seed, np.arange(N), fraction))[0]
+    o = oracle.fit(X, y, arity, maxDepth=p.maxDepth, maxBins=p.maxBins, minInstancesPerNode=p.minInstancesPerNode, numTrees=p.numTrees,
+                   featureSubsetStrategy=p.featureSubsetStrategy, maxMemoryInMB=p.maxMemoryInMB, bootstrap=p.bootstrap,
+                   minInfoGain=p.minInfoGain, minWeightFractionPerNode=p.minWeightFractionPerNode, subsamplingRate=p.subsamplingRate,
+                   seed=p.seed, part_offsets=part_offsets, sample_idx=sample_idx, fraction=fraction)
+    return g, o
+
+
+# ---------------------------------------------------------------- K1
+def test_find_splits_kats(b2rf, cuda):
+    from b2rf import trainer
+    cases = [([1, 1, 2, 2, 3, 3, 3, 3], 5, [1.5, 2.5]), ([2] * 10 + [3, 4, 5], 3, [2.5, 3.5]), ([0, 1] + [2] * 10, 2, [1.5]),
+             ([0, 0, 0], 3, []), ([0, 1, 0, 0, 1, 0, 1, 1], 3, [0.5]), ([0, 0, 1, 1, 2, 2, 3, 3], 3, [0.5, 2.5])]
+    for vals, nbins, want in cases:   # upstream RandomForestSuite "find splits for a continuous feature" 
+        s = torch.tensor(vals, dtype=torch.float64, device=cuda).reshape(-1, 1)
+        thr, ns = trainer.find_splits(s, torch.zeros(1, dtype=torch.int32, device=cuda), nbins, float(len(vals)))
+        assert thr[0, : int(ns[0])].tolist() == want, (vals, nbins)
+
+
+@pytest.mark.parametrize("shape", ["airbnb", "c3", "c4"])
+def test_find_splits_and_bins_bit_exact(b2rf, oracle, cuda, shape):
+    from b2rf import trainer
+    if shape == "airbnb":
+        X, y, arity = b2rf.synth.airbnb(5716)
+        maxBins = 40
+    elif shape == "c3":
+        X, y, arity = b2rf.synth.c3(60000, device="cpu")
+        maxBins = 64
+    else:
+        X, y, arity = b2rf.synth.c4(90000, device="cpu")
+        maxBins = 256
+    N, F = X.shape
+    mpb = min(maxBins, N)
+    meta_max = max([a if a > 1 else mpb for a in arity])
+    req = max(meta_max * meta_max, 10000)
+    fraction = req / N if req < N else 1.0
+    Xd = X.to(cuda)
+    ar_d = torch.as_tensor(arity, device=cuda)
+    seed = 42
+    if fraction < 1.0:
+        samp = trainer.sample_rows(Xd, 0, seed, fraction)
+        keep = oracle.sample_keep(seed, np.arange(N), fraction)
+        assert samp.shape[0] == int(keep.sum())
+        so = X.numpy()[keep]
+        # same multiset of rows (GPU order is arbitrary)
+        assert np.array_equal(np.sort(samp.cpu().numpy()[:, 0]), np.sort(so[:, 0]))
+    else:
+        samp, so = Xd, X.numpy()
+    thr, ns = trainer.find_splits(samp, ar_d, mpb, fraction * N)
+    thr_o, ns_o = oracle.find_splits(so, arity, mpb, fraction * N)
+    assert np.array_equal(ns.cpu().numpy(), ns_o)
+    for f in range(F):
+        assert np.array_equal(thr[f, : ns_o[f]].cpu().numpy(), thr_o[f, : ns_o[f]]), f"feature {f}"   # bit-exact
+    bins = trainer.bin_features(Xd, thr, ns, ar_d)
+    bins_o = oracle.bin_features(X.numpy(), thr_o, ns_o, arity)
+    assert np.array_equal(bins[:, :N].cpu().numpy().T.astype(np.int32), bins_o)                       # contract (1)
+    # streaming form: binning in two row chunks into one matrix gives the same codes
+    bins2 = torch.zeros_like(bins)
+    h = N // 2 + 3
+    trainer.bin_features(Xd[:h], thr, ns, ar_d, bins=bins2, row0=0)
+    trainer.bin_features(Xd[h:], thr, ns, ar_d, bins=bins2, row0=h)
+    assert torch.equal(bins2[:, :N], bins[:, :N])
+
+
+def test_bin_invalid_categorical(b2rf, cuda):
+    from b2rf import trainer
+    X = torch.tensor([[0.0, 1.0], [1.0, 5.0]], dtype=torch.float64, device=cuda)
+    ar = torch.tensor([0, 3], dtype=torch.int32, device=cuda)
+    thr = torch.tensor([[0.5], [0.0]], dtype=torch.float64, device=cuda)
+    ns = torch.tensor([1, 0], dtype=torch.int32, device=cuda)
+    with pytest.raises(b2rf.IllegalArgumentException, match="Feature 1 is categorical"):
+        trainer.bin_features(X, thr, ns, ar)
+
+
+# ---------------------------------------------------------------- K3
+@pytest.mark.parametrize("bootstrap,rate,T", [(True, 1.0, 7), (True, 0.6, 3), (False, 0.5, 4), (False, 1.0, 1)])
+def test_bag_bit_exact(b2rf, oracle, cuda, bootstrap, rate, T):
+    from b2rf import trainer
+    po = np.array([0, 5, 5, 300, 1000, 1001, 2500], np.int64)   # ragged, with an empty partition
+    w, node = trainer.bag(42, po, 0, T, rate, bootstrap, cuda)
+    wo = oracle.bag(42, po, T, rate, bootstrap)
+    assert np.array_equal(w[:, : po[-1]].cpu().numpy().T, wo)
+    assert np.array_equal((node[:, : po[-1]].cpu().numpy() == 0), (wo.T > 0))
+    # partition numbering offset: partitions 3.. of the same stream family
+    w2, _ = trainer.bag(42, po[3:] - po[3], 3, T, rate, bootstrap, cuda)
+    if bootstrap or not (T == 1 and rate == 1.0):
+        assert np.array_equal(w2[:, : po[-1] - po[3]].cpu().numpy().T, wo[po[3]:])
+
+
+# ---------------------------------------------------------------- K4
+def test_hist_parity(b2rf, oracle, cuda):
+    from b2rf import trainer
+    rng = np.random.default_rng(1)
+    N, F, T, Fsub, S = 20011, 40, 5, 13, 37
+    nbins = rng.integers(2, 64, F)
+    bins = np.stack([rng.integers(0, nbins[f], N) for f in range(F)], 1).astype(np.int32)
+    y = rng.normal(size=N) * 100 + 7
+    counts = rng.poisson(1.0, (N, T)).astype(np.uint8)
+    tree_ids = np.array([0, 2, 3], np.int32)
+    slot = rng.integers(-1, S, (len(tree_ids), N)).astype(np.int32)
+    feats = np.stack([rng.permutation(F)[:Fsub] for _ in range(S)]).astype(np.int32)
+    off = np.zeros((S, Fsub), np.int64)
+    base = np.zeros(S, np.int64)
+    total = 0
+    for s in range(S):
+        base[s] = total
+        o = 0
+        for j in range(Fsub):
+            off[s, j] = total + o
+            o += nbins[feats[s, j]]
+        total += o
+    ho = oracle.hist(bins, y, counts, tree_ids, slot, feats, off, total)
+    ld = (N + 127) // 128 * 128
+    bd = torch.zeros((F, ld), dtype=torch.uint8, device=cuda)
+    bd[:, :N] = torch.as_tensor(bins.T.astype(np.uint8))
+    wd = torch.zeros((T, ld), dtype=torch.uint8, device=cuda)
+    wd[:, :N] = torch.as_tensor(counts.T.copy())
+    sd = torch.full((len(tree_ids), ld), -1, dtype=torch.int32, device=cuda)
+    sd[:, :N] = torch.as_tensor(slot)
+    fo = np.zeros((S, Fsub, 2), np.uint32)
+    fo[:, :, 0] = feats
+    fo[:, :, 1] = off - base[:, None]
+    hg = trainer.hist_build(bd, torch.as_tensor(y, device=cuda), wd, sd, torch.as_tensor(tree_ids, device=cuda),
+                            torch.as_tensor(fo.view(np.int32)).to(cuda), torch.as_tensor(base, device=cuda), N, total).cpu().numpy()
+    assert np.array_equal(hg[:, 0], ho[:, 0])                              # counts bit-exact
+    np.testing.assert_allclose(hg[:, 1:3], ho[:, 1:3], rtol=REL, atol=1e-9)
+    # size-independent property: linearity — histogram of all rows == sum of histograms of two row halves
+    h = N // 2
+    def part(a, b):
+        bb = torch.zeros((F, ld), dtype=torch.uint8, device=cuda); bb[:, : b - a] = bd[:, a:b]
+        ww = torch.zeros((T, ld), dtype=torch.uint8, device=cuda); ww[:, : b - a] = wd[:, a:b]
+        ss = torch.full((len(tree_ids), ld), -1, dtype=torch.int32, device=cuda); ss[:, : b - a] = sd[:, a:b]
+        return trainer.hist_build(bb, torch.as_tensor(y[a:b], device=cuda), ww, ss, torch.as_tensor(tree_ids, device=cuda),
+                                  torch.as_tensor(fo.view(np.int32)).to(cuda), torch.as_tensor(base, device=cuda), b - a, total).cpu().numpy()
+    hs = part(0, h) + part(h, N)
+    assert np.array_equal(hs[:, 0], hg[:, 0])
+    np.testing.assert_allclose(hs[:, 1:3], hg[:, 1:3], rtol=REL, atol=1e-9)
+
+
+# ---------------------------------------------------------------- whole fits
+def test_doctest_kats(b2rf, oracle, cuda):
+    """pyspark doctests of DecisionTreeRegressor / RandomForestRegressor, on the GPU path."""
+    from b2rf import trainer
+    X = torch.tensor([[1.0], [0.0]], dtype=torch.float64, device=cuda)
+    y = torch.tensor([1.0, 0.0], dtype=torch.float64, device=cuda)
+    dt = trainer.fit_tensors(X, y, [0], b2rf.TreeParams(maxDepth=2), part_offsets=[0, 2])
+    assert dt.depth(0) == 1 and dt.num_nodes(0) == 3
+    assert dt.feature_importances().tolist() == [1.0]
+    t = torch.tensor([[-1.0], [1.0]], dtype=torch.float64, device=cuda)
+    assert dt.predict(t).tolist() == [0.0, 1.0]
+    rf = trainer.fit_tensors(X, y, [0], b2rf.TreeParams(maxDepth=2, numTrees=2, bootstrap=True, seed=42), part_offsets=[0, 1, 2])
+    assert rf.predict(t).tolist() == [0.0, 0.5]
+    assert rf.feature_importances().tolist() == [1.0]
+    # categorical stump (upstream RandomForestSuite): 1000 rows, arity 3, left = {1}, prediction 0.6, impurity/gain 0.24
+    Xs = np.zeros((1000, 2)); ys = np.zeros(1000)
+    Xs[:600, 1] = 1; ys[:600] = 1; Xs[600:, 0] = 1
+    st = trainer.fit_tensors(torch.as_tensor(Xs, device=cuda), torch.as_tensor(ys, device=cuda), [3, 3], b2rf.TreeParams(maxDepth=2, maxBins=100))
+    assert st.feature[0] == 0 and st.cats[: st.cat_len[0]].tolist() == [1.0]
+    assert st.prediction[0] == pytest.approx(0.6, abs=1e-15) and st.impurity[0] == pytest.approx(0.24, abs=1e-15) and st.gain[0] == pytest.approx(0.24, abs=1e-15)
+
+
+def test_maxbins_error_ml06(b2rf, cuda):
+    """`ML 06 - Decision Trees.py:81,91-92,110-118`: default maxBins=32 must fail on the 36-value categorical, 40 works."""
+    from b2rf import trainer
+    X, y, arity = b2rf.synth.airbnb(2000)
+    with pytest.raises(b2rf.IllegalArgumentException, match=r"DecisionTree requires maxBins \(= 32\) to be at least as large as the number of values"):
+        trainer.fit_tensors(X.to(cuda), y.to(cuda), arity, b2rf.TreeParams(maxBins=32))
+    f = trainer.fit_tensors(X.to(cuda), y.to(cuda), arity, b2rf.TreeParams(maxBins=40))
+    assert f.num_nodes(0) > 1
+
+
+def test_c1_decision_tree(b2rf, oracle, cuda):
+    """C1: ML 06 DecisionTreeRegressor maxDepth=5 maxBins=40 on the Airbnb-shaped table."""
+    Xtr, ytr, Xte, yte, arity = _airbnb(b2rf)
+    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, maxDepth=5, maxBins=40)
+    assert_forest_parity(g, o)
+    assert_trace_parity(g, o)
+    pg = g.predict(torch.as_tensor(Xte, device=cuda)).cpu().numpy()
+    po = o.predict(Xte)
+    np.testing.assert_allclose(pg, po, rtol=REL)
+    assert abs(rmse(pg, yte) - rmse(po, yte)) < 1e-6
+    np.testing.assert_allclose(g.feature_importances().sum(), 1.0, rtol=1e-12)
+
+
+@pytest.mark.parametrize("T,depth,mem", [(100, 8, 256), (20, 8, 1), (3, 5, 256), (7, 10, 1)])
+def test_c2_random_forest(b2rf, oracle, cuda, T, depth, mem):
+    """C2: ML 07 RandomForestRegressor on the same pipeline; small maxMemoryInMB forces MLlib's multi-group schedule."""
+    Xtr, ytr, Xte, yte, arity = _airbnb(b2rf)
+    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, maxDepth=depth, maxBins=40, numTrees=T, bootstrap=True, seed=42, maxMemoryInMB=mem)
+    assert_trace_parity(g, o)
+    assert_forest_parity(g, o)
+    pg = g.predict(torch.as_tensor(Xte, device=cuda)).cpu().numpy()
+    po = o.predict(Xte)
+    np.testing.assert_allclose(pg, po, rtol=REL)
+    assert abs(rmse(pg, yte) - rmse(po, yte)) < 1e-6
+
+
+@pytest.mark.parametrize("kw", [dict(minInstancesPerNode=20), dict(minInfoGain=50.0), dict(subsamplingRate=0.5), dict(bootstrap=False, subsamplingRate=0.7),
+                                dict(featureSubsetStrategy="sqrt"), dict(featureSubsetStrategy="all"), dict(minWeightFractionPerNode=0.05)])
+def test_param_variants(b2rf, oracle, cuda, kw):
+    Xtr, ytr, Xte, yte, arity = _airbnb(b2rf, n=3000)
+    base = dict(maxDepth=6, maxBins=40, numTrees=6, bootstrap=True, seed=7)
+    base.update(kw)
+    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, **base)
+    assert_trace_parity(g, o)
+    assert_forest_parity(g, o)
+
+
+def test_c3_slice(b2rf, oracle, cuda):
+    """C3 shape (64 continuous features, maxBins 64) on a slice the oracle finishes in seconds; findSplits samples rows."""
+    X, y, arity = b2rf.synth.c3(150000, device="cpu")
+    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=7, maxBins=64, numTrees=8, bootstrap=True, seed=42)
+    assert g.counters["fraction"] < 1.0
+    assert_trace_parity(g, o)
+    assert_forest_parity(g, o)
+    Xt, yt, _ = b2rf.synth.c3(20000, row0=10_000_000, device="cpu")
+    pg = g.predict(Xt.to(cuda)).cpu().numpy()
+    assert abs(rmse(pg, yt.numpy()) - rmse(o.predict(Xt.numpy()), yt.numpy())) < 1e-6
+
+
+def test_c4_slice(b2rf, oracle, cuda):
+    """C4 shape (96 continuous + 32 categorical up to arity 256, maxBins 256)."""
+    X, y, arity = b2rf.synth.c4(120000, device="cpu")
+    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=8, maxBins=256, numTrees=4, bootstrap=True, seed=42, maxMemoryInMB=8)
+    assert_trace_parity(g, o)
+    assert_forest_parity(g, o)
+
+
+def test_edge_cases(b2rf, oracle, cuda):
+    from b2rf import trainer
+    # one row; constant label; constant features; ragged partitions with empties
+    X = np.array([[3.0, 1.0]]); y = np.array([5.0])
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 1], maxDepth=3)
+    assert_forest_parity(g, o)
+    rng = np.random.default_rng(0)
+    X = rng.integers(0, 4, (500, 3)).astype(float); y = np.full(500, 2.5)
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 4, 0], part_offsets=[0, 0, 100, 100, 500], maxDepth=4, numTrees=3, bootstrap=True, seed=1)
+    assert_forest_parity(g, o)
+    X = np.zeros((300, 2)); y = rng.normal(size=300)
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 300], maxDepth=4)
+    assert_forest_parity(g, o)
+    assert g.num_nodes(0) == 1
+    # deep tree on few rows: every leaf pure
+    X = rng.normal(size=(64, 2)); y = np.arange(64.0)
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 64], maxDepth=12, maxBins=64)
+    assert_forest_parity(g, o)
+
+
+def test_no_cpu_path(b2rf):
+    from b2rf import trainer
+    with pytest.raises(TypeError, match="CUDA tensor"):
+        trainer.fit_tensors(torch.zeros((4, 2), dtype=torch.float64), torch.zeros(4, dtype=torch.float64), [0, 0], b2rf.TreeParams())
