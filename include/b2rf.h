@@ -106,8 +106,10 @@ int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const
 int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream);
 /* K5 binsToBestSplit (row a8) on the (reduced) histogram, then the driver tail (row a9).  Synchronises the stream. */
 int b2rf_trainer_end_group(b2rf_trainer* t, void* stream);
-/* timers: init, findSplits(0), findBestSplits(hist), chooseSplits, total — MLlib TimeTracker phase names; counters. */
-int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts4 /* groups, hist launches, rows*trees scanned, nodes */);
+/* h_seconds5: init(0), findSplits(0), findBestSplits (K4 device time from CUDA events), chooseSplits (K5 + driver tail),
+ * total — MLlib TimeTracker phase names.  h_counts6: node groups, K4 launches, rows*trees scanned, learning nodes,
+ * kernels launched by the trainer, algorithmic bytes summed over K4 launches (SURVEY.md §8d formula). */
+int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts6);
 /* finished forest, LearningNode.toNode(prune=true) in pre-order (row a11) */
 int b2rf_trainer_forest_sizes(b2rf_trainer* t, int64_t* n_nodes, int64_t* n_cats);
 int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature, double* h_threshold, int32_t* h_left,

@@ -210,7 +210,8 @@ struct b2rf_trainer {
   struct Trace { int32_t g, t, id, f, s; double gain, imp, cnt, sum, sq; };
   std::vector<Trace> trace;
   double tHist = 0, tChoose = 0, tStart = 0, tTotal = 0;
-  int64_t nHistLaunches = 0, nScanned = 0;
+  int64_t nHistLaunches = 0, nScanned = 0, nKernels = 0;
+  double histAlgBytes = 0;  // SURVEY §8(d) algorithmic bytes summed over K4 launches
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   bool evPending = false;
   int64_t l2CellBudget = 1500000;  // cells per K4 launch kept L2-resident (32 B each => 48 MB)
@@ -462,6 +463,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   bool ok = true;
   ok &= cuda_ok(cudaMemcpyAsync(t->dnUpd.p, t->hUpd.p, nUpd * sizeof(DNodeUpdate), cudaMemcpyHostToDevice, s), "upload node updates");
   ok &= cuda_ok(launch_scatter_dnodes(t->dn.p, t->dnUpd.p, (int64_t)nUpd, s), "scatter node updates");
+  t->nKernels += nUpd > 0;
   if (t->catPool.size() > t->catUploaded) {
     if (t->catPool.size() > t->dCat.cap) {  // grow, keeping old contents
       DevBuf<uint32_t> nb;
@@ -497,8 +499,10 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     std::string err;
     cudaError_t e = launch_hist(a, true, s, &err);
     if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "hist launch"); return B2RF_ERR_CUDA; }
-    t->nHistLaunches++;
+    t->nHistLaunches++; t->nKernels++;
     t->nScanned += (int64_t)(end - start) * t->nLocal;
+    // algorithmic bytes of this launch: bin matrix + labels + (bag weight u8 + node slot u16) per active tree + histogram cells*20
+    t->histAlgBytes += (double)t->nLocal * ((double)t->F + 8.0 + 3.0 * (end - start)) + 20.0 * (double)c;
     start = end;
   }
   cudaEventRecord(t->ev1, s);
@@ -519,6 +523,7 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   a.minInstances = (double)t->p.minInstancesPerNode; a.minWeight = t->minWeightPerNode; a.minInfoGain = t->p.minInfoGain;
   a.out = t->dRec.p;
   if (!cuda_ok(launch_best_split(a, s), "best_split launch")) return B2RF_ERR_CUDA;
+  t->nKernels++;
   if (!cuda_ok(cudaMemcpyAsync(t->hRec.p, t->dRec.p, nSlots * sizeof(SplitRec), cudaMemcpyDeviceToHost, s), "download split records")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
   const double tc0 = now_s();
@@ -576,11 +581,13 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
 }
 
 int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts4) {
+  // h_counts4 has room for 6 entries: groups, hist launches, rows*trees scanned, learning nodes, kernel launches, hist algorithmic bytes
   if (!t) return B2RF_ERR_ARG;
   if (h_seconds5) { h_seconds5[0] = 0; h_seconds5[1] = 0; h_seconds5[2] = t->tHist; h_seconds5[3] = t->tChoose; h_seconds5[4] = t->tTotal > 0 ? t->tTotal : now_s() - t->tStart; }
   if (h_counts4) {
     int64_t nodes = 0; for (auto& tr : t->trees) nodes += (int64_t)tr.size();
     h_counts4[0] = t->groupNo; h_counts4[1] = t->nHistLaunches; h_counts4[2] = t->nScanned; h_counts4[3] = nodes;
+    h_counts4[4] = t->nKernels; h_counts4[5] = (int64_t)t->histAlgBytes;
   }
   return B2RF_OK;
 }

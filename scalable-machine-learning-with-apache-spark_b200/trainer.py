@@ -242,7 +242,23 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         tm = forest.timers
         tm.update(init=(t0 - t_start) + (t2 - t1), findSplits=t1 - t0, total=t3 - t_start, loop=t3 - t2, comm=t_comm)
         forest.counters.update(rows=N, rows_local=n_local, partitions=len(po) - 1, world=world, fraction=fraction)
+        # stage kernels outside the trainer: sample_rows (if sampling), find_splits, bin, bag
+        forest.counters["kernel_launches"] += (1 if fraction < 1.0 else 0) + 3 - (1 if prebinned is not None else 0)
         return forest
+
+
+def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", **kw) -> Forest:
+    """Public host-buffer entry point (what the Spark adapter calls): X_host f64 [n, F] / y_host f64 [n] are HOST arrays
+    (numpy or CPU torch tensors, ideally pinned).  Copies them to the device, trains, returns the Forest (host arrays)."""
+    dev = torch.device(device)
+    Xh = torch.as_tensor(X_host, dtype=torch.float64)
+    yh = torch.as_tensor(y_host, dtype=torch.float64)
+    with torch.cuda.device(dev):
+        Xd = torch.empty(Xh.shape, dtype=torch.float64, device=dev)
+        Xd.copy_(Xh, non_blocking=True)
+        yd = torch.empty(yh.shape, dtype=torch.float64, device=dev)
+        yd.copy_(yh, non_blocking=True)
+        return fit_tensors(Xd, yd, arity, params, **kw)
 
 
 def _export(h, F: int, keep_trace: bool) -> Forest:
@@ -251,7 +267,7 @@ def _export(h, F: int, keep_trace: bool) -> Forest:
     check(L.b2rf_trainer_forest_sizes(h, C.byref(nn), C.byref(nc)))
     n, ncat = nn.value, nc.value
     sec = np.zeros(5)
-    cnt = np.zeros(4, np.int64)
+    cnt = np.zeros(6, np.int64)
     L.b2rf_trainer_stats(h, sec.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p))
     T = None
     # number of trees = len(tree_off) - 1; query through a first export of tree_off sized generously
@@ -274,7 +290,8 @@ def _export(h, F: int, keep_trace: bool) -> Forest:
     tree_off = tree_off[: T + 1].copy()
     fo = Forest(F, tree_off, feature, threshold, left, right, prediction, impurity, gain, stats, ncat_a, cat_off, cat_len, cats[:ncat])
     fo.timers = dict(findBestSplits=float(sec[2]), chooseSplits=float(sec[3]))
-    fo.counters = dict(groups=int(cnt[0]), hist_launches=int(cnt[1]), rows_trees_scanned=int(cnt[2]), learning_nodes=int(cnt[3]))
+    fo.counters = dict(groups=int(cnt[0]), hist_launches=int(cnt[1]), rows_trees_scanned=int(cnt[2]), learning_nodes=int(cnt[3]),
+                       kernel_launches=int(cnt[4]), hist_alg_bytes=int(cnt[5]))
     if keep_trace:
         nt = int(L.b2rf_trainer_trace_size(h))
         ti, td = Z((nt, 5), np.int32), Z((nt, 5), np.float64)

@@ -42,3 +42,72 @@ def assert_trace_parity(g, o):
 
 def rmse(pred, y):
     return float(np.sqrt(np.mean((np.asarray(pred) - np.asarray(y)) ** 2)))
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Tie-aware comparison.  fp64 sums are order-dependent (MLlib itself is not bit-reproducible across cluster shapes), so
+# two candidate splits whose gains agree to ~1 ulp can be ranked differently: the contract allows "documented gain
+# ties".  A tie is accepted only when both sides evaluated the SAME node and their best gains agree to 1e-12 relative;
+# everything outside the subtrees under tie nodes must still be identical.
+# ---------------------------------------------------------------------------------------------------------------
+def find_ties(g, o, rel=1e-12):
+    gi = {(int(r[1]), int(r[2])): k for k, r in enumerate(g.trace_i)}
+    oi = {(int(r[1]), int(r[2])): k for k, r in enumerate(o.trace_i)}
+    ties = []
+
+    def under_tie(key):
+        t, nid = key
+        return any(t == tt and _is_descendant(nid, tn) for tt, tn in ties)
+
+    for key in sorted(set(gi) | set(oi), key=lambda k: (k[0], k[1])):   # ancestors (smaller heap ids) first within a tree
+        if under_tie(key):
+            continue
+        assert key in gi and key in oi, f"node {key} evaluated by only one side"
+        a, b = g.trace_i[gi[key]], o.trace_i[oi[key]]
+        da, db = g.trace_d[gi[key]], o.trace_d[oi[key]]
+        assert da[2] == db[2], f"node {key}: counts differ {da[2]} vs {db[2]}"
+        np.testing.assert_allclose(da[3:5], db[3:5], rtol=REL, atol=0)
+        if a[3] != b[3] or a[4] != b[4]:
+            assert abs(da[0] - db[0]) <= rel * max(1.0, abs(db[0])), f"node {key}: different split and gains differ: {da[0]!r} vs {db[0]!r}"
+            ties.append(key)
+    return ties
+
+
+def _is_descendant(nid, root):
+    while nid > root:
+        nid >>= 1
+    return nid == root and True
+
+
+def assert_forest_parity_with_ties(g, o, ties):
+    assert g.num_trees == o.num_trees
+    for t in range(g.num_trees):
+        gb, ob = int(g.tree_off[t]), int(o.tree_off[t])
+        stack = [(0, 0, 1)]
+        while stack:
+            ig, io, hid = stack.pop()
+            if (t, hid) in ties:
+                continue
+            a, b = gb + ig, ob + io
+            assert g.feature[a] == o.feature[b], f"tree {t} node {hid}: feature {g.feature[a]} vs {o.feature[b]}"
+            assert g.threshold[a] == o.threshold[b]
+            assert g.stats[a, 0] == o.stats[b, 0]
+            np.testing.assert_allclose(g.stats[a, 1:3], o.stats[b, 1:3], rtol=REL, atol=0)
+            np.testing.assert_allclose(g.prediction[a], o.prediction[b], rtol=REL, atol=1e-300)
+            if g.ncat[a] > 0:
+                assert sorted(g.cats[g.cat_off[a]:g.cat_off[a] + g.cat_len[a]]) == sorted(o.cats[o.cat_off[b]:o.cat_off[b] + o.cat_len[b]])
+            if g.feature[a] >= 0:
+                stack.append((int(g.left[a]), int(o.left[b]), 2 * hid))
+                stack.append((int(g.right[a]), int(o.right[b]), 2 * hid + 1))
+
+
+def assert_parity_allowing_ties(g, o, max_ties):
+    ties = find_ties(g, o)
+    assert len(ties) <= max_ties, f"too many gain ties: {ties}"
+    if not ties:
+        assert_trace_parity(g, o)
+        assert_forest_parity(g, o)
+    else:
+        print(f"documented gain ties (tree, heap node id): {ties}")
+        assert_forest_parity_with_ties(g, o, set(ties))
+    return ties
