@@ -7,6 +7,25 @@ from dataclasses import dataclass, replace
 from ._lib import B2rfParams, check, lib
 
 
+def _to_int(v, name):
+    """pyspark TypeConverters.toInt: accepts integral floats (`ML 08 - Hyperopt.py:97,120-121` passes hp.quniform floats)."""
+    if isinstance(v, bool):
+        raise TypeError(f"Could not convert {v!r} to int for Param {name}")
+    if isinstance(v, int):
+        return v
+    if isinstance(v, float) and v.is_integer():
+        return int(v)
+    try:
+        import numpy as np
+        if isinstance(v, np.integer):
+            return int(v)
+        if isinstance(v, np.floating) and float(v).is_integer():
+            return int(v)
+    except ImportError:
+        pass
+    raise TypeError(f"Could not convert {v!r} to int for Param {name}")
+
+
 @dataclass
 class TreeParams:
     maxDepth: int = 5
@@ -42,10 +61,11 @@ class TreeParams:
             raise ValueError("minWeightFractionPerNode must be in [0, 0.5)")
 
     def features_per_node(self, F: int) -> int:
-        return check(lib().b2rf_features_per_node(self.featureSubsetStrategy.encode(), F, self.numTrees))
+        return check(lib().b2rf_features_per_node(str(self.featureSubsetStrategy).encode(), int(F), _to_int(self.numTrees, 'numTrees')))
 
     def to_c(self, F: int) -> B2rfParams:
         self.validate()
-        return B2rfParams(int(self.maxDepth), int(self.maxBins), int(self.minInstancesPerNode), int(self.numTrees),
+        return B2rfParams(_to_int(self.maxDepth, "maxDepth"), _to_int(self.maxBins, "maxBins"),
+                          _to_int(self.minInstancesPerNode, "minInstancesPerNode"), _to_int(self.numTrees, "numTrees"),
                           self.features_per_node(F), int(self.maxMemoryInMB), int(bool(self.bootstrap)), 0, float(self.minInfoGain),
                           float(self.minWeightFractionPerNode), float(self.subsamplingRate), int(self.seed))

@@ -282,3 +282,24 @@ def test_no_cpu_path(b2rf):
     from b2rf import trainer
     with pytest.raises(TypeError, match="CUDA tensor"):
         trainer.fit_tensors(torch.zeros((4, 2), dtype=torch.float64), torch.zeros(4, dtype=torch.float64), [0, 0], b2rf.TreeParams())
+
+
+def test_golden_fixtures_gpu(b2rf, cuda):
+    """The CUDA path against the committed golden vectors (tests/golden/*.json; no oracle call at run time)."""
+    import json
+    import os
+    from b2rf import trainer
+    gold_dir = os.path.join(os.path.dirname(__file__), "golden")
+    files = sorted(f for f in os.listdir(gold_dir) if f.endswith(".json"))
+    assert files
+    for fn in files:
+        gold = json.load(open(os.path.join(gold_dir, fn)))
+        c = gold["config"]
+        X, y, arity = b2rf.synth.airbnb(c["rows"], seed=c["data_seed"])
+        f = trainer.fit_tensors(X.to(cuda), y.to(cuda), arity, b2rf.TreeParams(**c["params"]), part_offsets=c["part_offsets"])
+        assert f.tree_off.tolist() == gold["tree_off"], fn
+        assert f.feature.tolist() == gold["feature"], fn
+        assert [float(v).hex() for v in f.threshold] == gold["threshold_hex"], fn
+        assert [float(v).hex() for v in f.prediction] == gold["prediction_hex"], fn     # integer labels: sums are exact
+        assert f.stats[:, 0].tolist() == gold["count"], fn
+        assert [sorted(f.cats[o:o + n].tolist()) for o, n in zip(f.cat_off, f.cat_len)] == gold["cats"], fn
