@@ -80,7 +80,7 @@ int b2rf_find_splits(const double* d_sample, int64_t n_sample, int32_t F, const 
  * categorical value. */
 int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const double* d_thresholds, const int32_t* d_nsplits,
              const int32_t* d_arity, int32_t maxSplits, uint8_t* d_bins, int64_t ldb, int64_t row0, int32_t* d_err,
-             void* stream);
+             uint8_t* d_bins_rm /* optional row-major twin [row][ldr], may be NULL */, int64_t ldr, void* stream);
 
 /* ---- K3: BaggedPoint.convertToBaggedRDD (row a4) ------------------------------------------------------------- */
 /* One emulated Spark partition per thread: partition p (global index part0 + p) covers local rows
@@ -98,8 +98,12 @@ int b2rf_trainer_create(const b2rf_params* params, int32_t F, const int32_t* h_a
 void b2rf_trainer_destroy(b2rf_trainer* t);
 /* Largest histogram (in cells of 4 doubles) any node group can need; the caller allocates d_hist with that many cells. */
 int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t);
-int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const double* d_y, const uint8_t* d_w, int64_t ldw,
-                      int32_t* d_node, int64_t ldn, int64_t n_rows_local, double* d_hist, int64_t hist_cells);
+/* d_bins_rm (optional, may be NULL): row-major twin of the bin matrix written by b2rf_bin.  With it the trainer buckets each
+ * group's rows by node (counting sort) and builds the histograms in shared memory; without it, it scans the column-major
+ * matrix and accumulates with global reductions (also selectable with B2RF_HIST_MODE=scan). */
+int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const uint8_t* d_bins_rm, int64_t ldr, const double* d_y,
+                      const uint8_t* d_w, int64_t ldw, int32_t* d_node, int64_t ldn, int64_t n_rows_local, double* d_hist,
+                      int64_t hist_cells);
 /* selectNodesToSplit + K4 (findBestSplits.binSeqOp, row a6) with the fused K6 row routing (row a10).
  * Returns 1 and sets *n_cells (histogram cells written, to be summed across ranks by the caller — row a7) when a group
  * was launched, 0 when training is finished. */

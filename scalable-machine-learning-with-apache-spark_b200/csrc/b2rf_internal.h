@@ -43,9 +43,25 @@ struct HistLaunch {
   const DNode* dnodes; int64_t nodeStride; const uint32_t* catmasks;
   const uint2* slot_fo; const int64_t* slot_base; int32_t Fsub;
   double* hist;
+  uint32_t* slot_count;             // MODE 2 only: rows per slot
 };
 
-cudaError_t launch_hist(const HistLaunch& a, bool traverse, cudaStream_t s, std::string* err);
+struct BucketLaunch {
+  const uint8_t* bins_rm; int64_t ldr;   // row-major bin codes [row][ldr]
+  const double* y;
+  const uint32_t* rowlist;               // packed row | weight << 27, grouped by slot
+  const uint64_t* slot_start;            // [nSlots + 1]
+  const uint32_t* slot_count;            // [nSlots]
+  const uint32_t* chunk_prefix;          // [nSlots + 1] exclusive prefix of ceil(count / CH)
+  int32_t nSlots, CH;
+  const uint2* slot_fo; const int64_t* slot_base; const int32_t* slot_cells; int32_t Fsub;
+  int32_t maxCells;                      // shared-memory histogram capacity in cells
+  double* hist;
+};
+
+cudaError_t launch_hist(const HistLaunch& a, int mode, cudaStream_t s, std::string* err);
+cudaError_t launch_bucket_pipeline(const HistLaunch& h, const BucketLaunch& b, uint32_t* cursor, cudaStream_t s, std::string* err);
+cudaError_t launch_count_active(const int32_t* node, int64_t ldn, int T, int64_t n_rows, unsigned long long* out, cudaStream_t s);
 cudaError_t launch_scatter_dnodes(DNode* dnodes, const DNodeUpdate* upd, int64_t n, cudaStream_t s);
 
 struct SplitLaunch {

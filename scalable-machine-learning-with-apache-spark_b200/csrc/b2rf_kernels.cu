@@ -72,8 +72,12 @@ struct HistKArgs {
   int64_t numTiles;
 };
 
-template <bool TRAVERSE>
+// MODE 0: slot ids given per (listed tree, row), histogram by global RED   (stand-alone b2rf_hist_build)
+// MODE 1: K6 routing from the cached node + histogram by global RED        (trainer, scan mode)
+// MODE 2: K6 routing from the cached node + per-slot row COUNT only        (trainer, bucket mode, pass 1)
+template <int MODE>
 __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k) {
+  constexpr bool TRAVERSE = MODE != 0;
   extern __shared__ __align__(128) unsigned char smem[];
   const HistLaunch& a = k.a;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem);  // 2 barriers
@@ -149,6 +153,7 @@ __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k
           slot = a.node[(size_t)g * a.ldn + row];
           if (slot < 0) continue;
         }
+        if (MODE == 2) { atomicAdd(&a.slot_count[slot], 1u); continue; }
         const uint32_t wv = a.w[(size_t)t * a.ldw + row];
         if (wv == 0) continue;
         const double dw = (double)wv;
@@ -171,7 +176,7 @@ __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k
   }
 }
 
-cudaError_t launch_hist(const HistLaunch& a, bool traverse, cudaStream_t s, std::string* err) {
+cudaError_t launch_hist(const HistLaunch& a, int mode, cudaStream_t s, std::string* err) {
   if (a.n_rows <= 0 || a.Tg <= 0) return cudaSuccess;
   HistKArgs k;
   k.a = a;
@@ -187,12 +192,179 @@ cudaError_t launch_hist(const HistLaunch& a, bool traverse, cudaStream_t s, std:
   k.R = R; k.pitch = R + HIST_PAD; k.nbuf = nbuf;
   k.numTiles = (a.n_rows + R - 1) / R;
   const size_t smem = 128 + (size_t)nbuf * a.F * k.pitch;
-  auto kern = traverse ? hist_kernel<true> : hist_kernel<false>;
+  auto kern = mode == 0 ? hist_kernel<0> : (mode == 1 ? hist_kernel<1> : hist_kernel<2>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int64_t grid = device_sm_count();
   if (grid > k.numTiles) grid = k.numTiles;
   kern<<<(unsigned)grid, HIST_THREADS, smem, s>>>(k);
+  return cudaGetLastError();
+}
+
+
+// =================================================================================================
+// Bucket mode (K4'): rows of each node slot are gathered into a per-group row list by a counting sort
+// (count in hist_kernel<2>, exclusive scan, scatter), then one CTA per (slot, row chunk) accumulates that
+// slot's histogram in SHARED memory (u32 count by native ATOMS, f64 sums by CAS) with lane == feature, so the
+// lanes of a warp never hit the same cell; the CTA flushes its non-empty cells with global RED.
+// =================================================================================================
+__global__ void __launch_bounds__(1024) scan_slots_kernel(const uint32_t* cnt, int nSlots, int CH, uint64_t* start, uint32_t* chunkPrefix,
+                                                           uint32_t* cursor) {
+  __shared__ unsigned long long s_rows[1024];
+  __shared__ uint32_t s_chunks[1024];
+  const int tid = threadIdx.x;
+  const int per = (nSlots + 1023) / 1024;
+  const int b = tid * per, e = min(nSlots, b + per);
+  unsigned long long r = 0; uint32_t c = 0;
+  for (int i = b; i < e; i++) { r += cnt[i]; c += (cnt[i] + CH - 1) / CH; }
+  s_rows[tid] = r; s_chunks[tid] = c;
+  __syncthreads();
+  if (tid == 0) {
+    unsigned long long ar = 0; uint32_t ac = 0;
+    for (int i = 0; i < 1024; i++) { const unsigned long long tr = s_rows[i]; const uint32_t tc = s_chunks[i]; s_rows[i] = ar; s_chunks[i] = ac; ar += tr; ac += tc; }
+    start[nSlots] = ar; chunkPrefix[nSlots] = ac;
+  }
+  __syncthreads();
+  r = s_rows[tid]; c = s_chunks[tid];
+  for (int i = b; i < e; i++) { start[i] = r; chunkPrefix[i] = c; cursor[i] = 0; r += cnt[i]; c += (cnt[i] + CH - 1) / CH; }
+}
+
+__global__ void __launch_bounds__(256) scatter_rows_kernel(const int32_t* node, int64_t ldn, const uint8_t* w, int64_t ldw, const int32_t* tree_ids,
+                                                            int Tg, int64_t n_rows, const DNode* dnodes, int64_t nodeStride, const uint64_t* start,
+                                                            uint32_t* cursor, uint32_t* rowlist) {
+  const int g = blockIdx.y;
+  const int t = tree_ids[g];
+  const DNode* tn = dnodes + (size_t)t * nodeStride;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n_rows; row += (int64_t)gridDim.x * blockDim.x) {
+    const int n = node[(size_t)t * ldn + row];
+    if (n < 0) continue;
+    const int slot = tn[n].slot;
+    if (slot < 0) continue;
+    uint32_t wv = w[(size_t)t * ldw + row];
+    if (wv > 31u) wv = 31u;   // packed in 5 bits; a Poisson(<=1) draw above 31 has probability < 1e-34
+    const uint32_t pos = atomicAdd(&cursor[slot], 1u);
+    rowlist[start[slot] + pos] = (uint32_t)row | (wv << 27);
+  }
+}
+
+constexpr int BUCKET_THREADS = 256;
+template <bool DIRECT>
+__device__ __forceinline__ void bucket_update(double* hb, double* ssum, double* ssq, unsigned* scnt, uint32_t cell, uint32_t w, double yv) {
+  const double dw = (double)w;
+  const double wy = dw * yv;
+  const double wyy = wy * yv;
+  if (DIRECT) {
+    double* c = hb + (size_t)cell * 4;
+    atomicAdd(c, dw); atomicAdd(c + 1, wy); atomicAdd(c + 2, wyy);
+  } else {
+    atomicAdd(&scnt[cell], w); atomicAdd(&ssum[cell], wy); atomicAdd(&ssq[cell], wyy);
+  }
+}
+
+__global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const BucketLaunch a) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  double* ssum = reinterpret_cast<double*>(smraw);
+  double* ssq = ssum + a.maxCells;
+  unsigned* scnt = reinterpret_cast<unsigned*>(ssq + a.maxCells);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  constexpr int W = BUCKET_THREADS / 32;
+  const unsigned FULL = 0xffffffffu;
+  const uint32_t total = a.chunk_prefix[a.nSlots];
+  for (uint32_t task = blockIdx.x; task < total; task += gridDim.x) {
+    int lo = 0, hi = a.nSlots;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.chunk_prefix[mid] <= task) lo = mid; else hi = mid; }
+    const int slot = lo;
+    const uint32_t chunk = task - a.chunk_prefix[slot];
+    const uint32_t cnt = a.slot_count[slot];
+    const uint32_t begin = chunk * (uint32_t)a.CH;
+    const int n = (int)min((uint32_t)a.CH, cnt - begin);
+    const uint32_t* rl = a.rowlist + a.slot_start[slot] + begin;
+    const int ncell = a.slot_cells[slot];
+    const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
+    double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
+    const bool direct = (int64_t)n * a.Fsub < (int64_t)ncell || ncell > a.maxCells;   // few rows: skip the shared-memory round trip
+    if (!direct) {
+      for (int c = tid; c < ncell; c += BUCKET_THREADS) { ssum[c] = 0.0; ssq[c] = 0.0; scnt[c] = 0u; }
+      __syncthreads();
+    }
+    for (int j0 = 0; j0 < a.Fsub; j0 += 32) {
+      const int j = j0 + lane;
+      const bool active = j < a.Fsub;
+      const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
+      for (int base = warp * 32; base < n; base += W * 32) {
+        const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;
+        const int nb = min(32, n - base);
+        for (int q = 0; q < nb; q += 4) {
+          uint32_t bin[4], wv[4]; double yv[4];
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            const uint32_t p = __shfl_sync(FULL, mine, (q + u) & 31);
+            const bool valid = (q + u) < nb;
+            const uint32_t row = p & 0x7ffffffu;
+            wv[u] = valid ? (p >> 27) : 0u;
+            bin[u] = (valid && active) ? a.bins_rm[(size_t)row * a.ldr + e.x] : 0u;
+            yv[u] = valid ? a.y[row] : 0.0;
+          }
+#pragma unroll
+          for (int u = 0; u < 4; u++) {
+            if (wv[u] != 0u && active) {
+              if (direct) bucket_update<true>(hb, ssum, ssq, scnt, e.y + bin[u], wv[u], yv[u]);
+              else bucket_update<false>(hb, ssum, ssq, scnt, e.y + bin[u], wv[u], yv[u]);
+            }
+          }
+        }
+      }
+    }
+    if (!direct) {
+      __syncthreads();
+      for (int c = tid; c < ncell; c += BUCKET_THREADS) {
+        const unsigned k = scnt[c];
+        if (k) { double* g = hb + (size_t)c * 4; atomicAdd(g, (double)k); atomicAdd(g + 1, ssum[c]); atomicAdd(g + 2, ssq[c]); }
+      }
+      __syncthreads();
+    }
+  }
+}
+
+cudaError_t launch_bucket_pipeline(const HistLaunch& h, const BucketLaunch& b, uint32_t* cursor, cudaStream_t s, std::string* err) {
+  // pass 1: route rows (K6) and count rows per slot
+  cudaError_t e = launch_hist(h, 2, s, err);
+  if (e != cudaSuccess) return e;
+  scan_slots_kernel<<<1, 1024, 0, s>>>(b.slot_count, b.nSlots, b.CH, const_cast<uint64_t*>(b.slot_start), const_cast<uint32_t*>(b.chunk_prefix), cursor);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  // pass 2: scatter packed (row, weight) entries into per-slot segments
+  {
+    int64_t bx = (h.n_rows + 255) / 256;
+    const int64_t cap = (int64_t)device_sm_count() * 16;
+    if (bx > cap) bx = cap;
+    dim3 grid((unsigned)bx, (unsigned)h.Tg);
+    scatter_rows_kernel<<<grid, 256, 0, s>>>(h.node, h.ldn, h.w, h.ldw, h.tree_ids, h.Tg, h.n_rows, h.dnodes, h.nodeStride, b.slot_start, cursor,
+                                             const_cast<uint32_t*>(b.rowlist));
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  }
+  // pass 3: per-(slot, chunk) shared-memory histograms
+  const size_t smem = (size_t)b.maxCells * 20 + 16;
+  e = cudaFuncSetAttribute(bucket_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  int perSM = (int)((size_t)200 * 1024 / (smem + 1024));
+  if (perSM < 1) perSM = 1;
+  if (perSM > 8) perSM = 8;
+  bucket_hist_kernel<<<device_sm_count() * perSM, BUCKET_THREADS, smem, s>>>(b);
+  return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(256) count_active_kernel(const int32_t* node, int64_t ldn, int64_t n_rows, unsigned long long* out) {
+  const int t = blockIdx.y;
+  unsigned long long c = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_rows; i += (int64_t)gridDim.x * blockDim.x) c += node[(size_t)t * ldn + i] >= 0;
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) atomicAdd(&out[t], c);
+}
+cudaError_t launch_count_active(const int32_t* node, int64_t ldn, int T, int64_t n_rows, unsigned long long* out, cudaStream_t s) {
+  if (n_rows <= 0 || T <= 0) return cudaSuccess;
+  int64_t bx = (n_rows + 255) / 256;
+  if (bx > 1024) bx = 1024;
+  count_active_kernel<<<dim3((unsigned)bx, (unsigned)T), 256, 0, s>>>(node, ldn, n_rows, out);
   return cudaGetLastError();
 }
 
@@ -468,7 +640,7 @@ constexpr int BIN_FT = 32;    // features per block
 constexpr int BIN_RT = 128;   // rows per block
 __global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, int64_t n_rows, int F, const double* thresholds,
                                                    const int32_t* nsplits, const int32_t* arity, int maxSplits, uint8_t* bins, int64_t ldb,
-                                                   int64_t row0, int32_t* err) {
+                                                   int64_t row0, int32_t* err, uint8_t* bins_rm, int64_t ldr) {
   extern __shared__ __align__(16) unsigned char smraw[];
   double* thr = reinterpret_cast<double*>(smraw);                                   // [BIN_FT][maxSplits]
   uint8_t* tile = smraw + (size_t)BIN_FT * (maxSplits > 0 ? maxSplits : 1) * 8;     // [BIN_FT][BIN_RT]
@@ -501,6 +673,7 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, 
       }
     }
     tile[fl * BIN_RT + rr] = b;
+    if (bins_rm != nullptr && row < n_rows && fl < nf) bins_rm[(size_t)(row0 + row) * ldr + f0 + fl] = b;   // row-major twin for gathers
   }
   __syncthreads();
   // coalesced column-major stores: 32-bit words
@@ -719,14 +892,15 @@ int b2rf_find_splits(const double* d_sample, int64_t n_sample, int32_t F, const 
 }
 
 int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const double* d_thresholds, const int32_t* d_nsplits,
-             const int32_t* d_arity, int32_t maxSplits, uint8_t* d_bins, int64_t ldb, int64_t row0, int32_t* d_err, void* stream) {
+             const int32_t* d_arity, int32_t maxSplits, uint8_t* d_bins, int64_t ldb, int64_t row0, int32_t* d_err, uint8_t* d_bins_rm,
+             int64_t ldr, void* stream) {
   if (F <= 0 || maxSplits < 0 || maxSplits > 255) { set_error("b2rf_bin: maxBins must be <= 256 for uint8 bin codes"); return B2RF_ERR_ARG; }
   if (n_rows <= 0) return B2RF_OK;
   const int ms = maxSplits > 0 ? maxSplits : 1;
   const size_t smem = (size_t)BIN_FT * ms * 8 + (size_t)BIN_FT * BIN_RT;
   if (!cuda_ok(cudaFuncSetAttribute(bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bin attr")) return B2RF_ERR_CUDA;
   dim3 grid((unsigned)((n_rows + BIN_RT - 1) / BIN_RT), (unsigned)((F + BIN_FT - 1) / BIN_FT));
-  bin_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(d_X, ldx, n_rows, F, d_thresholds, d_nsplits, d_arity, ms, d_bins, ldb, row0, d_err);
+  bin_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(d_X, ldx, n_rows, F, d_thresholds, d_nsplits, d_arity, ms, d_bins, ldb, row0, d_err, d_bins_rm, ldr);
   return cuda_ok(cudaGetLastError(), "b2rf_bin") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
@@ -758,9 +932,9 @@ int b2rf_hist_build(const uint8_t* d_bins, int64_t ldb, int32_t F, const double*
   a.bins = d_bins; a.ldb = ldb; a.F = F; a.y = d_y; a.w = d_w; a.ldw = ldw;
   a.node = const_cast<int32_t*>(d_slot_of_row); a.ldn = ldn; a.tree_ids = d_tree_ids; a.Tg = Tg; a.n_rows = n_rows;
   a.dnodes = nullptr; a.nodeStride = 0; a.catmasks = nullptr;
-  a.slot_fo = reinterpret_cast<const uint2*>(d_slot_fo); a.slot_base = d_slot_base; a.Fsub = Fsub; a.hist = d_hist;
+  a.slot_fo = reinterpret_cast<const uint2*>(d_slot_fo); a.slot_base = d_slot_base; a.Fsub = Fsub; a.hist = d_hist; a.slot_count = nullptr;
   std::string err;
-  cudaError_t e = launch_hist(a, false, (cudaStream_t)stream, &err);
+  cudaError_t e = launch_hist(a, 0, (cudaStream_t)stream, &err);
   if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "b2rf_hist_build"); return e == cudaErrorInvalidValue && !err.empty() ? B2RF_ERR_ARG : B2RF_ERR_CUDA; }
   return B2RF_OK;
 }

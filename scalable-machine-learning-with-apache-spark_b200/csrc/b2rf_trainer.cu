@@ -173,6 +173,9 @@ struct b2rf_trainer {
   int32_t* d_node = nullptr; int64_t ldn = 0;
   int64_t nLocal = 0;
   double* d_hist = nullptr; int64_t histCells = 0;
+  const uint8_t* d_bins_rm = nullptr; int64_t ldr = 0;   // optional row-major twin of the bin matrix => bucket mode
+  bool bucketMode = false;
+  int32_t chunkRows = 4096;
 
   // host trees + scheduler
   std::vector<std::vector<HNode>> trees;
@@ -191,6 +194,11 @@ struct b2rf_trainer {
   DevBuf<double> dParent;
   DevBuf<int32_t> dHasParent, dNumBins, dIsCat, dTreeIds;
   DevBuf<SplitRec> dRec;
+  DevBuf<uint32_t> dSlotCount, dCursor, dChunkPrefix, dRowList;
+  DevBuf<uint64_t> dSlotStart;
+  DevBuf<int32_t> dSlotCells;
+  PinBuf<int32_t> hSlotCells;
+  std::vector<int64_t> inBag;   // rows with weight > 0 per tree (bound of the per-group row list)
   PinBuf<DNodeUpdate> hUpd;
   PinBuf<uint2> hSlotFo;
   PinBuf<int64_t> hSlotBase;
@@ -225,6 +233,7 @@ struct b2rf_trainer {
   ~b2rf_trainer() {
     dn.release(); dnUpd.release(); dCat.release(); dSlotFo.release(); dSlotBase.release(); dParent.release();
     dHasParent.release(); dNumBins.release(); dIsCat.release(); dTreeIds.release(); dRec.release();
+    dSlotCount.release(); dCursor.release(); dChunkPrefix.release(); dRowList.release(); dSlotStart.release(); dSlotCells.release(); hSlotCells.release();
     hUpd.release(); hSlotFo.release(); hSlotBase.release(); hParent.release(); hHasParent.release(); hTreeIds.release(); hRec.release();
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
@@ -333,13 +342,28 @@ int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t) {
   return std::max<int64_t>(worstNode, std::min<int64_t>(byMem, maxNodesTotal * worstNode));
 }
 
-int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const double* d_y, const uint8_t* d_w, int64_t ldw, int32_t* d_node,
-                      int64_t ldn, int64_t n_rows_local, double* d_hist, int64_t hist_cells) {
+int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const uint8_t* d_bins_rm, int64_t ldr, const double* d_y,
+                      const uint8_t* d_w, int64_t ldw, int32_t* d_node, int64_t ldn, int64_t n_rows_local, double* d_hist, int64_t hist_cells) {
   if (!t || !d_bins || !d_y || !d_w || !d_node || !d_hist || n_rows_local < 0 || (ldb & 15) || ldb < n_rows_local || ldw < n_rows_local || ldn < n_rows_local) {
     set_error("b2rf_trainer_bind: bad argument (ldb must be a multiple of 16 and every leading dimension >= n_rows)"); return B2RF_ERR_ARG;
   }
   t->d_bins = d_bins; t->ldb = ldb; t->d_y = d_y; t->d_w = d_w; t->ldw = ldw; t->d_node = d_node; t->ldn = ldn; t->nLocal = n_rows_local;
   t->d_hist = d_hist; t->histCells = hist_cells;
+  t->d_bins_rm = d_bins_rm; t->ldr = ldr;
+  t->bucketMode = d_bins_rm != nullptr && ldr >= t->F && n_rows_local < ((int64_t)1 << 27);
+  if (const char* m = std::getenv("B2RF_HIST_MODE")) { if (std::string(m) == "scan") t->bucketMode = false; }
+  if (t->bucketMode) {
+    // rows in bag per tree bound the per-group row list
+    unsigned long long* d_cnt = nullptr;
+    std::vector<unsigned long long> h_cnt(t->T, 0);
+    if (!cuda_ok(cudaMalloc((void**)&d_cnt, (size_t)t->T * 8), "bind alloc")) return B2RF_ERR_CUDA;
+    bool ok = cuda_ok(cudaMemset(d_cnt, 0, (size_t)t->T * 8), "bind memset");
+    ok = ok && cuda_ok(launch_count_active(d_node, ldn, t->T, n_rows_local, d_cnt, 0), "count in-bag rows");
+    ok = ok && cuda_ok(cudaMemcpy(h_cnt.data(), d_cnt, (size_t)t->T * 8, cudaMemcpyDeviceToHost), "bind copy");
+    cudaFree(d_cnt);
+    if (!ok) return B2RF_ERR_CUDA;
+    t->inBag.assign(h_cnt.begin(), h_cnt.end());
+  }
   // device node table: one stride per tree
   const int64_t full = (int64_t)1 << std::min(t->p.maxDepth + 1, 17);
   t->nodeStride = full;
@@ -490,20 +514,51 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   HistLaunch a;
   a.bins = t->d_bins; a.ldb = t->ldb; a.F = t->F; a.y = t->d_y; a.w = t->d_w; a.ldw = t->ldw; a.node = t->d_node; a.ldn = t->ldn;
   a.n_rows = t->nLocal; a.dnodes = t->dn.p; a.nodeStride = t->nodeStride; a.catmasks = t->dCat.p;
-  a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.hist = t->d_hist;
-  int start = 0;
-  while (start < nTg) {
-    int end = start; int64_t c = 0;
-    while (end < nTg && (end == start || c + cellsPerTree[t->hTreeIds.p[end]] <= t->l2CellBudget)) { c += cellsPerTree[t->hTreeIds.p[end]]; end++; }
-    a.tree_ids = t->dTreeIds.p + start; a.Tg = end - start;
+  a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.hist = t->d_hist; a.slot_count = nullptr;
+  if (t->bucketMode) {
+    // counting sort of the group's rows by slot, then shared-memory histograms per (slot, chunk)
+    int64_t listCap = 0;
+    for (int i = 0; i < nTg; i++) listCap += t->inBag[t->hTreeIds.p[i]];
+    int32_t maxCells = 0;
+    if (!t->hSlotCells.ensure(nSlots) || !t->dSlotCells.ensure(nSlots) || !t->dSlotCount.ensure(nSlots) || !t->dCursor.ensure(nSlots) ||
+        !t->dChunkPrefix.ensure(nSlots + 1) || !t->dSlotStart.ensure(nSlots + 1) || !t->dRowList.ensure((size_t)std::max<int64_t>(listCap, 1)))
+      return B2RF_ERR_CUDA;
+    for (size_t sl = 0; sl < nSlots; sl++) {
+      int32_t c = 0;
+      for (int j = 0; j < t->Fsub; j++) c += t->numBins[feats[sl * t->Fsub + j]];
+      t->hSlotCells.p[sl] = c;
+      maxCells = std::max(maxCells, c);
+    }
+    if ((size_t)maxCells * 20 + 16 > (size_t)220 * 1024) maxCells = (int32_t)(((size_t)220 * 1024 - 16) / 20);   // larger slots take the direct path
+    ok &= cuda_ok(cudaMemcpyAsync(t->dSlotCells.p, t->hSlotCells.p, nSlots * 4, cudaMemcpyHostToDevice, s), "upload slot cells");
+    ok &= cuda_ok(cudaMemsetAsync(t->dSlotCount.p, 0, nSlots * 4, s), "zero slot counts");
+    if (!ok) return B2RF_ERR_CUDA;
+    a.tree_ids = t->dTreeIds.p; a.Tg = nTg; a.slot_count = t->dSlotCount.p;
+    BucketLaunch b;
+    b.bins_rm = t->d_bins_rm; b.ldr = t->ldr; b.y = t->d_y; b.rowlist = t->dRowList.p; b.slot_start = t->dSlotStart.p; b.slot_count = t->dSlotCount.p;
+    b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->chunkRows; b.slot_fo = t->dSlotFo.p; b.slot_base = t->dSlotBase.p;
+    b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.hist = t->d_hist;
     std::string err;
-    cudaError_t e = launch_hist(a, true, s, &err);
-    if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "hist launch"); return B2RF_ERR_CUDA; }
-    t->nHistLaunches++; t->nKernels++;
-    t->nScanned += (int64_t)(end - start) * t->nLocal;
-    // algorithmic bytes of this launch: bin matrix + labels + (bag weight u8 + node slot u16) per active tree + histogram cells*20
-    t->histAlgBytes += (double)t->nLocal * ((double)t->F + 8.0 + 3.0 * (end - start)) + 20.0 * (double)c;
-    start = end;
+    cudaError_t e = launch_bucket_pipeline(a, b, t->dCursor.p, s, &err);
+    if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "bucket pipeline launch"); return B2RF_ERR_CUDA; }
+    t->nHistLaunches++; t->nKernels += 4;
+    t->nScanned += (int64_t)nTg * t->nLocal;
+    t->histAlgBytes += (double)t->nLocal * ((double)t->F + 8.0 + 3.0 * nTg) + 20.0 * (double)cells;
+  } else {
+    int start = 0;
+    while (start < nTg) {
+      int end = start; int64_t c = 0;
+      while (end < nTg && (end == start || c + cellsPerTree[t->hTreeIds.p[end]] <= t->l2CellBudget)) { c += cellsPerTree[t->hTreeIds.p[end]]; end++; }
+      a.tree_ids = t->dTreeIds.p + start; a.Tg = end - start;
+      std::string err;
+      cudaError_t e = launch_hist(a, 1, s, &err);
+      if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "hist launch"); return B2RF_ERR_CUDA; }
+      t->nHistLaunches++; t->nKernels++;
+      t->nScanned += (int64_t)(end - start) * t->nLocal;
+      // algorithmic bytes of this launch: bin matrix + labels + (bag weight u8 + node slot u16) per active tree + histogram cells*20
+      t->histAlgBytes += (double)t->nLocal * ((double)t->F + 8.0 + 3.0 * (end - start)) + 20.0 * (double)c;
+      start = end;
+    }
   }
   cudaEventRecord(t->ev1, s);
   t->evPending = true;

@@ -74,8 +74,9 @@ def sample_rows(X: torch.Tensor, row0_global: int, seed: int, fraction: float) -
 
 
 def bin_features(X: torch.Tensor, thresholds: torch.Tensor, nsplits: torch.Tensor, arity: torch.Tensor, bins: torch.Tensor = None,
-                 row0: int = 0) -> torch.Tensor:
-    """K2.  X f64 [n, F] row-major CUDA -> column-major uint8 bins [F, ldb] (rows row0..row0+n)."""
+                 row0: int = 0, bins_rm: torch.Tensor = None) -> torch.Tensor:
+    """K2.  X f64 [n, F] row-major CUDA -> column-major uint8 bins [F, ldb] (rows row0..row0+n); optionally also the
+    row-major twin bins_rm [rows, ldr] that the bucket-mode histogram kernel gathers from."""
     _require_cuda(X, "X")
     n, F = X.shape
     if X.stride(1) != 1:
@@ -84,7 +85,8 @@ def bin_features(X: torch.Tensor, thresholds: torch.Tensor, nsplits: torch.Tenso
         bins = torch.zeros((F, _pad(row0 + n)), dtype=torch.uint8, device=X.device)
     err = torch.zeros(1, dtype=torch.int32, device=X.device)
     check(lib().b2rf_bin(X.data_ptr(), X.stride(0), n, F, thresholds.data_ptr(), nsplits.data_ptr(), arity.data_ptr(), thresholds.shape[1],
-                         bins.data_ptr(), bins.stride(0), row0, err.data_ptr(), _stream()))
+                         bins.data_ptr(), bins.stride(0), row0, err.data_ptr(), 0 if bins_rm is None else bins_rm.data_ptr(),
+                         0 if bins_rm is None else bins_rm.stride(0), _stream()))
     e = int(err.item())
     if e:
         from ._lib import ERR_DATA, IllegalArgumentException
@@ -158,7 +160,7 @@ def default_partitions(n_rows: int, rows_per_partition: int = 4096):
 
 
 def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, part_offsets=None, part0: int = None, group=None,
-                keep_trace: bool = False, prebinned=None) -> Forest:
+                keep_trace: bool = False, prebinned=None, hist_mode: str = "bucket") -> Forest:
     """Train a forest on this rank's rows.
 
     X: f64 [n_local, F] CUDA, row-major (the VectorAssembler `features` column); y: f64 [n_local];
@@ -166,6 +168,7 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
     part_offsets: local row offsets of the emulated Spark partitions (bagging streams are seeded per partition, A.4);
     part0: global index of this rank's first partition (default: partitions are numbered rank-major).
     With torch.distributed initialised, rows are sharded over ranks and only per-group histograms are all-reduced.
+    hist_mode: "bucket" (default: rows bucketed by node, shared-memory histograms) or "scan" (column-major scan + global RED).
     """
     _require_cuda(X, "X")
     _require_cuda(y, "y")
@@ -209,10 +212,11 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         # ---- TreePoint (K2) + BaggedPoint (K3) ----
         ld = _pad(n_local)
         if prebinned is not None:
-            bins = prebinned
+            bins, bins_rm = prebinned
         else:
             bins = torch.empty((F, ld), dtype=torch.uint8, device=dev)
-            bin_features(X, thr, ns, arity_d, bins=bins, row0=0)
+            bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=torch.uint8, device=dev) if hist_mode != "scan" else None
+            bin_features(X, thr, ns, arity_d, bins=bins, row0=0, bins_rm=bins_rm)
         w, node = bag(params.seed, po, part0, T, params.subsamplingRate, params.bootstrap, dev, ld=ld)
         torch.cuda.synchronize(dev)
         t2 = time.perf_counter()
@@ -224,7 +228,8 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         try:
             cells = int(L.b2rf_trainer_max_group_cells(h))
             hist = torch.empty(cells * 4, dtype=torch.float64, device=dev)
-            check(L.b2rf_trainer_bind(h, bins.data_ptr(), bins.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0), node.data_ptr(),
+            check(L.b2rf_trainer_bind(h, bins.data_ptr(), bins.stride(0), 0 if bins_rm is None else bins_rm.data_ptr(),
+                                      0 if bins_rm is None else bins_rm.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0), node.data_ptr(),
                                       node.stride(0), n_local, hist.data_ptr(), cells))
             ncell = C.c_int64()
             st = _stream()

@@ -16,14 +16,20 @@ def _airbnb(b2rf, n=7146, seed=42):
     return X[:ntr].numpy(), y[:ntr].numpy(), X[ntr:].numpy(), y[ntr:].numpy(), arity
 
 
-def _fit_both(b2rf, oracle, cuda, X, y, arity, part_offsets=None, **kw):
+@pytest.fixture(params=["bucket", "scan"])
+def mode(request):
+    """Both K4 implementations: rows bucketed by node + shared-memory histograms, and column-major scan + global RED."""
+    return request.param
+
+
+def _fit_both(b2rf, oracle, cuda, X, y, arity, part_offsets=None, hist_mode="bucket", **kw):
     from b2rf import trainer
     p = b2rf.TreeParams(**kw)
     if part_offsets is None:
         part_offsets = trainer.default_partitions(len(y), 1024)
     Xd = torch.as_tensor(X, device=cuda)
     yd = torch.as_tensor(y, device=cuda)
-    g = trainer.fit_tensors(Xd, yd, arity, p, part_offsets=part_offsets, keep_trace=True)
+    g = trainer.fit_tensors(Xd, yd, arity, p, part_offsets=part_offsets, keep_trace=True, hist_mode=hist_mode)
     N = len(y)
     mpb = min(p.maxBins, N)
     meta_max = max([a if a > 1 else mpb for a in arity])
@@ -202,10 +208,10 @@ def test_maxbins_error_ml06(b2rf, cuda):
     assert f.num_nodes(0) > 1
 
 
-def test_c1_decision_tree(b2rf, oracle, cuda):
+def test_c1_decision_tree(b2rf, oracle, cuda, mode):
     """C1: ML 06 DecisionTreeRegressor maxDepth=5 maxBins=40 on the Airbnb-shaped table."""
     Xtr, ytr, Xte, yte, arity = _airbnb(b2rf)
-    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, maxDepth=5, maxBins=40)
+    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, maxDepth=5, maxBins=40, hist_mode=mode)
     assert_forest_parity(g, o)
     assert_trace_parity(g, o)
     pg = g.predict(torch.as_tensor(Xte, device=cuda)).cpu().numpy()
@@ -216,10 +222,10 @@ def test_c1_decision_tree(b2rf, oracle, cuda):
 
 
 @pytest.mark.parametrize("T,depth,mem", [(100, 8, 256), (20, 8, 1), (3, 5, 256), (7, 10, 1)])
-def test_c2_random_forest(b2rf, oracle, cuda, T, depth, mem):
+def test_c2_random_forest(b2rf, oracle, cuda, mode, T, depth, mem):
     """C2: ML 07 RandomForestRegressor on the same pipeline; small maxMemoryInMB forces MLlib's multi-group schedule."""
     Xtr, ytr, Xte, yte, arity = _airbnb(b2rf)
-    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, maxDepth=depth, maxBins=40, numTrees=T, bootstrap=True, seed=42, maxMemoryInMB=mem)
+    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, maxDepth=depth, maxBins=40, numTrees=T, bootstrap=True, seed=42, maxMemoryInMB=mem, hist_mode=mode)
     assert_trace_parity(g, o)
     assert_forest_parity(g, o)
     pg = g.predict(torch.as_tensor(Xte, device=cuda)).cpu().numpy()
@@ -230,19 +236,19 @@ def test_c2_random_forest(b2rf, oracle, cuda, T, depth, mem):
 
 @pytest.mark.parametrize("kw", [dict(minInstancesPerNode=20), dict(minInfoGain=50.0), dict(subsamplingRate=0.5), dict(bootstrap=False, subsamplingRate=0.7),
                                 dict(featureSubsetStrategy="sqrt"), dict(featureSubsetStrategy="all"), dict(minWeightFractionPerNode=0.05)])
-def test_param_variants(b2rf, oracle, cuda, kw):
+def test_param_variants(b2rf, oracle, cuda, mode, kw):
     Xtr, ytr, Xte, yte, arity = _airbnb(b2rf, n=3000)
     base = dict(maxDepth=6, maxBins=40, numTrees=6, bootstrap=True, seed=7)
     base.update(kw)
-    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, **base)
+    g, o = _fit_both(b2rf, oracle, cuda, Xtr, ytr, arity, **base, hist_mode=mode)
     assert_trace_parity(g, o)
     assert_forest_parity(g, o)
 
 
-def test_c3_slice(b2rf, oracle, cuda):
+def test_c3_slice(b2rf, oracle, cuda, mode):
     """C3 shape (64 continuous features, maxBins 64) on a slice the oracle finishes in seconds; findSplits samples rows."""
     X, y, arity = b2rf.synth.c3(150000, device="cpu")
-    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=7, maxBins=64, numTrees=8, bootstrap=True, seed=42)
+    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=7, maxBins=64, numTrees=8, bootstrap=True, seed=42, hist_mode=mode)
     assert g.counters["fraction"] < 1.0
     ties = assert_parity_allowing_ties(g, o, max_ties=3)   # labels carry N(0,1) noise: sums are inexact, near-ties can flip
     Xt, yt, _ = b2rf.synth.c3(20000, row0=10_000_000, device="cpu")
@@ -251,30 +257,30 @@ def test_c3_slice(b2rf, oracle, cuda):
         assert abs(rmse(pg, yt.numpy()) - rmse(o.predict(Xt.numpy()), yt.numpy())) < 1e-6
 
 
-def test_c4_slice(b2rf, oracle, cuda):
+def test_c4_slice(b2rf, oracle, cuda, mode):
     """C4 shape (96 continuous + 32 categorical up to arity 256, maxBins 256)."""
     X, y, arity = b2rf.synth.c4(120000, device="cpu")
-    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=8, maxBins=256, numTrees=4, bootstrap=True, seed=42, maxMemoryInMB=8)
+    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=8, maxBins=256, numTrees=4, bootstrap=True, seed=42, maxMemoryInMB=8, hist_mode=mode)
     assert_parity_allowing_ties(g, o, max_ties=3)
 
 
-def test_edge_cases(b2rf, oracle, cuda):
+def test_edge_cases(b2rf, oracle, cuda, mode):
     from b2rf import trainer
     # one row; constant label; constant features; ragged partitions with empties
     X = np.array([[3.0, 1.0]]); y = np.array([5.0])
-    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 1], maxDepth=3)
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 1], maxDepth=3, hist_mode=mode)
     assert_forest_parity(g, o)
     rng = np.random.default_rng(0)
     X = rng.integers(0, 4, (500, 3)).astype(float); y = np.full(500, 2.5)
-    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 4, 0], part_offsets=[0, 0, 100, 100, 500], maxDepth=4, numTrees=3, bootstrap=True, seed=1)
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 4, 0], part_offsets=[0, 0, 100, 100, 500], maxDepth=4, numTrees=3, bootstrap=True, seed=1, hist_mode=mode)
     assert_forest_parity(g, o)
     X = np.zeros((300, 2)); y = rng.normal(size=300)
-    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 300], maxDepth=4)
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 300], maxDepth=4, hist_mode=mode)
     assert_forest_parity(g, o)
     assert g.num_nodes(0) == 1
     # deep tree on few rows: every leaf pure
     X = rng.normal(size=(64, 2)); y = np.arange(64.0)
-    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 64], maxDepth=12, maxBins=64)
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, [0, 0], part_offsets=[0, 64], maxDepth=12, maxBins=64, hist_mode=mode)
     assert_forest_parity(g, o)
 
 
