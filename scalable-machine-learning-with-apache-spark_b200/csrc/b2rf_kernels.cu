@@ -127,8 +127,34 @@ __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k
       for (int q = 0; q < HIST_RPT; q++) {
         const int r = tid + q * HIST_THREADS;
         const int64_t row = r0 + r;
+        int slot = -1;
+        if (MODE == 2) {
+          // convergent form (no early exits): the lanes of a warp aggregate their per-slot counts before touching memory
+          if (r < k.R && row < a.n_rows) {
+            int32_t* np = a.node + (size_t)t * a.ldn + row;
+            int n = *np;
+            if (n >= 0) {
+              const DNode* tn = a.dnodes + (size_t)t * a.nodeStride;
+              DNode d = tn[n];
+              bool moved = false;
+              while (d.feature >= 0) {
+                const uint32_t bin = tb[(size_t)d.feature * k.pitch + r];
+                bool left;
+                if (d.aux & 0x80000000u) left = (a.catmasks[(size_t)(d.aux & 0x7fffffffu) * 8 + (bin >> 5)] >> (bin & 31)) & 1u;
+                else left = bin <= d.aux;
+                n = d.left + (left ? 0 : 1);
+                d = tn[n];
+                moved = true;
+              }
+              if (d.slot == SLOT_DEAD) *np = -1;
+              else { if (moved) *np = n; slot = d.slot; }
+            }
+          }
+          const unsigned peers = __match_any_sync(0xffffffffu, slot);
+          if (slot >= 0 && (int)(__ffs(peers) - 1) == (tid & 31)) atomicAdd(&a.slot_count[slot], (uint32_t)__popc(peers));
+          continue;
+        }
         if (r >= k.R || row >= a.n_rows) continue;
-        int slot;
         if (TRAVERSE) {
           int32_t* np = a.node + (size_t)t * a.ldn + row;
           int n = *np;
@@ -153,7 +179,6 @@ __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k
           slot = a.node[(size_t)g * a.ldn + row];
           if (slot < 0) continue;
         }
-        if (MODE == 2) { atomicAdd(&a.slot_count[slot], 1u); continue; }
         const uint32_t wv = a.w[(size_t)t * a.ldw + row];
         if (wv == 0) continue;
         const double dw = (double)wv;
@@ -235,15 +260,27 @@ __global__ void __launch_bounds__(256) scatter_rows_kernel(const int32_t* node, 
   const int g = blockIdx.y;
   const int t = tree_ids[g];
   const DNode* tn = dnodes + (size_t)t * nodeStride;
-  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n_rows; row += (int64_t)gridDim.x * blockDim.x) {
-    const int n = node[(size_t)t * ldn + row];
-    if (n < 0) continue;
-    const int slot = tn[n].slot;
-    if (slot < 0) continue;
-    uint32_t wv = w[(size_t)t * ldw + row];
-    if (wv > 31u) wv = 31u;   // packed in 5 bits; a Poisson(<=1) draw above 31 has probability < 1e-34
-    const uint32_t pos = atomicAdd(&cursor[slot], 1u);
-    rowlist[start[slot] + pos] = (uint32_t)row | (wv << 27);
+  const int lane = threadIdx.x & 31;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  const int64_t n_pad = (n_rows + 31) & ~(int64_t)31;   // whole warps stay in the loop together
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < n_pad; row += stride) {
+    int slot = -1;
+    if (row < n_rows) {
+      const int n = node[(size_t)t * ldn + row];
+      if (n >= 0) slot = tn[n].slot;
+    }
+    // one cursor bump per (warp, slot): lanes that share a slot take consecutive places
+    const unsigned peers = __match_any_sync(0xffffffffu, slot);
+    const int leader = __ffs(peers) - 1;
+    uint32_t base = 0;
+    if (slot >= 0 && lane == leader) base = atomicAdd(&cursor[slot], (uint32_t)__popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (slot >= 0) {
+      uint32_t wv = w[(size_t)t * ldw + row];
+      if (wv > 31u) wv = 31u;   // packed in 5 bits; a Poisson(<=1) draw above 31 has probability < 1e-34
+      const uint32_t pos = base + (uint32_t)__popc(peers & ((1u << lane) - 1u));
+      rowlist[start[slot] + pos] = (uint32_t)row | (wv << 27);
+    }
   }
 }
 
@@ -692,15 +729,21 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, 
 // =================================================================================================
 // K3: bagging.  One thread per emulated Spark partition; generator state in local memory.
 // =================================================================================================
-struct Well19937cDev {
-  uint32_t v[624];
+constexpr int BAG_THREADS = 64;
+// Well19937c with its 624-word state in shared memory, laid out [word][thread] so that a thread's word w lives in bank
+// (thread % 32) whatever w is: the per-thread indices diverge (variable draws per sample) without bank conflicts.
+struct Well19937cSm {
+  uint32_t* v;   // &state[0][threadIdx.x]; word w is v[w * BAG_THREADS]
   int index;
+  __device__ __forceinline__ uint32_t& at(int w) { return v[w * BAG_THREADS]; }
   __device__ void seed(int64_t sd) {
-    v[0] = (uint32_t)((uint64_t)sd >> 32);
-    v[1] = (uint32_t)((uint64_t)sd & 0xffffffffULL);
+    uint32_t a = (uint32_t)((uint64_t)sd >> 32), b = (uint32_t)((uint64_t)sd & 0xffffffffULL);
+    at(0) = a; at(1) = b;
     for (int i = 2; i < 624; i++) {
-      const int64_t l = (int64_t)(int32_t)v[i - 2];
-      v[i] = (uint32_t)((1812433253LL * (l ^ (l >> 30)) + i) & 0xffffffffLL);
+      const int64_t l = (int64_t)(int32_t)a;
+      const uint32_t c = (uint32_t)((1812433253LL * (l ^ (l >> 30)) + i) & 0xffffffffLL);
+      at(i) = c;
+      a = b; b = c;
     }
     index = 0;
   }
@@ -711,15 +754,16 @@ struct Well19937cDev {
     int i1 = i0 + 70; if (i1 >= 624) i1 -= 624;
     int i2 = i0 + 179; if (i2 >= 624) i2 -= 624;
     int i3 = i0 + 449; if (i3 >= 624) i3 -= 624;
-    const uint32_t v0 = v[i0], vM1 = v[i1], vM2 = v[i2], vM3 = v[i3];
-    const uint32_t z0 = (0x80000000u & v[iRm1]) ^ (0x7FFFFFFFu & v[iRm2]);
+    const uint32_t v0 = at(i0), vM1 = at(i1), vM2 = at(i2), vM3 = at(i3);
+    const uint32_t vR1 = at(iRm1), vR2 = at(iRm2);
+    const uint32_t z0 = (0x80000000u & vR1) ^ (0x7FFFFFFFu & vR2);
     const uint32_t z1 = (v0 ^ (v0 << 25)) ^ (vM1 ^ (vM1 >> 27));
     const uint32_t z2 = (vM2 >> 9) ^ (vM3 ^ (vM3 >> 1));
     const uint32_t z3 = z1 ^ z2;
     uint32_t z4 = z0 ^ (z1 ^ (z1 << 9)) ^ (z2 ^ (z2 << 21)) ^ (z3 ^ (z3 >> 21));
-    v[i0] = z3;
-    v[iRm1] = z4;
-    v[iRm2] &= 0x80000000u;
+    at(i0) = z3;
+    at(iRm1) = z4;
+    at(iRm2) = vR2 & 0x80000000u;
     index = iRm1;
     z4 ^= (z4 << 7) & 0xe46e1700u;
     z4 ^= (z4 << 15) & 0x9b868000u;
@@ -763,14 +807,16 @@ struct XorShiftDev {
   __device__ __forceinline__ double nextDouble() { return (double)(((int64_t)next(26) << 27) + next(27)) * 0x1.0p-53; }
 };
 
-// mode 0: Poisson (with replacement); 1: Bernoulli (without replacement); 2: all ones
-__global__ void __launch_bounds__(64) bag_kernel(int64_t seed, const int64_t* part_offsets, int P, int part0, int T, double rate, double expNegRate,
-                                                 int mode, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
+// mode 0: Poisson (with replacement); 1: Bernoulli (without replacement)
+__global__ void __launch_bounds__(BAG_THREADS) bag_kernel(int64_t seed, const int64_t* part_offsets, int P, int part0, int T, double rate, double expNegRate,
+                                                          int mode, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
+  extern __shared__ uint32_t bag_state[];   // [624][BAG_THREADS]
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
   if (p >= P) return;
   const int64_t r0 = part_offsets[p], r1 = part_offsets[p + 1];
   if (mode == 0) {
-    Well19937cDev rng;
+    Well19937cSm rng;
+    rng.v = bag_state + threadIdx.x;
     rng.seed(seed + (int64_t)(part0 + p) + 1);
     const double lim = 1000 * rate;
     for (int64_t i = r0; i < r1; i++)
@@ -917,8 +963,13 @@ int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t par
   if (!cuda_ok(cudaMallocAsync((void**)&d_po, (size_t)(P + 1) * 8, s), "b2rf_bag alloc")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpyAsync(d_po, h_part_offsets, (size_t)(P + 1) * 8, cudaMemcpyHostToDevice, s), "b2rf_bag copy")) return B2RF_ERR_CUDA;
   // exp(-rate) is evaluated once on the host so that every consumer of the stream compares against the same constant
-  bag_kernel<<<(P + 63) / 64, 64, 0, s>>>(seed, d_po, P, part0, T, subsamplingRate, std::exp(-subsamplingRate), bootstrap ? 0 : 1, d_w, ldw, d_node, ldn);
-  const bool ok = cuda_ok(cudaGetLastError(), "b2rf_bag");
+  const size_t smem = (size_t)624 * BAG_THREADS * 4;
+  bool ok = cuda_ok(cudaFuncSetAttribute(bag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bag attr");
+  if (ok) {
+    bag_kernel<<<(P + BAG_THREADS - 1) / BAG_THREADS, BAG_THREADS, smem, s>>>(seed, d_po, P, part0, T, subsamplingRate, std::exp(-subsamplingRate),
+                                                                             bootstrap ? 0 : 1, d_w, ldw, d_node, ldn);
+    ok = cuda_ok(cudaGetLastError(), "b2rf_bag");
+  }
   cudaStreamSynchronize(s);  // h_part_offsets may be pageable: finish the copy before returning
   cudaFreeAsync(d_po, s);
   return ok ? B2RF_OK : B2RF_ERR_CUDA;
