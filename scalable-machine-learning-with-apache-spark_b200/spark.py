@@ -1,0 +1,353 @@
+"""Drop-in pyspark.ml Estimator / Model classes for the tree stage of the labs' Pipelines.
+
+    from b2rf.spark import B200DecisionTreeRegressor as DecisionTreeRegressor      # `ML 06 - Decision Trees.py:73-75`
+    from b2rf.spark import B200RandomForestRegressor as RandomForestRegressor      # `ML 07 ...:25,41`, `ML 08 - Hyperopt.py:59,71`
+
+They accept the same Params with the same defaults and converters as pyspark 3.1.2 (kwargs constructor, setX/getX,
+setParams, copy(extra) keeping the uid, explainParams), read categorical arities from the `ml_attr` metadata that
+StringIndexer -> VectorAssembler attach to the features column (`ML 06:47,60-63`), override fitMultiple so a
+CrossValidator placed around the tree stage trains every candidate on ONE binned copy of the fold
+(`ML 07:143-149`), and append a double `prediction` column in _transform.
+
+pyspark cannot be installed in this image (no JVM, no wheel): when it is missing the same classes are built on
+_pyspark_stub.py, which is what tests/test_cpu_spark_adapter.py and the GPU adapter test exercise.
+"""
+from __future__ import annotations
+
+import threading
+
+import numpy as np
+
+try:  # real Spark
+    from pyspark.ml import Estimator, Model
+    from pyspark.ml.linalg import SparseVector
+    from pyspark.ml.param import Param, Params, TypeConverters
+    HAVE_PYSPARK = True
+except ImportError:  # this image
+    from ._pyspark_stub import Estimator, Model, Param, Params, SparseVector, TypeConverters
+    HAVE_PYSPARK = False
+
+from .forest import Forest
+from .params import TreeParams
+
+
+def _java_string_hash(s: str) -> int:
+    """pyspark's HasSeed default is hash(type(self).__name__) — process-dependent; Scala's is className.hashCode.
+    A stable value is used here so an unseeded fit (`ML 07:41`) is at least reproducible across processes."""
+    h = 0
+    for ch in s:
+        h = (31 * h + ord(ch)) & 0xFFFFFFFF
+    return h - (1 << 32) if h >= (1 << 31) else h
+
+
+class _TreeRegressorParams(Params):
+    """Param declarations with pyspark.ml.tree._DecisionTreeParams/_TreeEnsembleParams/_RandomForestParams names and docs."""
+    featuresCol = Param(Params, "featuresCol", "features column name.", TypeConverters.toString)
+    labelCol = Param(Params, "labelCol", "label column name.", TypeConverters.toString)
+    predictionCol = Param(Params, "predictionCol", "prediction column name.", TypeConverters.toString)
+    maxDepth = Param(Params, "maxDepth", "Maximum depth of the tree. (>= 0) E.g., depth 0 means 1 leaf node; depth 1 means 1 internal "
+                     "node + 2 leaf nodes. Must be in range [0, 30].", TypeConverters.toInt)
+    maxBins = Param(Params, "maxBins", "Max number of bins for discretizing continuous features.  Must be >=2 and >= number of categories "
+                    "for any categorical feature.", TypeConverters.toInt)
+    minInstancesPerNode = Param(Params, "minInstancesPerNode", "Minimum number of instances each child must have after split. If a split "
+                                "causes the left or right child to have fewer than minInstancesPerNode, the split will be discarded as "
+                                "invalid. Should be >= 1.", TypeConverters.toInt)
+    minWeightFractionPerNode = Param(Params, "minWeightFractionPerNode", "Minimum fraction of the weighted sample count that each child must "
+                                     "have after split. Should be in interval [0.0, 0.5).", TypeConverters.toFloat)
+    minInfoGain = Param(Params, "minInfoGain", "Minimum information gain for a split to be considered at a tree node.", TypeConverters.toFloat)
+    maxMemoryInMB = Param(Params, "maxMemoryInMB", "Maximum memory in MB allocated to histogram aggregation. If too small, then 1 node will "
+                          "be split per iteration, and its aggregates may exceed this size.", TypeConverters.toInt)
+    cacheNodeIds = Param(Params, "cacheNodeIds", "If false, the algorithm will pass trees to executors to match instances with nodes. If "
+                         "true, the algorithm will cache node IDs for each instance.", TypeConverters.toBoolean)
+    checkpointInterval = Param(Params, "checkpointInterval", "set checkpoint interval (>= 1) or disable checkpoint (-1).", TypeConverters.toInt)
+    impurity = Param(Params, "impurity", "Criterion used for information gain calculation (case-insensitive). Supported options: variance",
+                     TypeConverters.toString)
+    seed = Param(Params, "seed", "random seed.", TypeConverters.toInt)
+    leafCol = Param(Params, "leafCol", "Leaf indices column name. Predicted leaf index of each instance in each tree by preorder.",
+                    TypeConverters.toString)
+
+    def _base_defaults(self):
+        self._setDefault(featuresCol="features", labelCol="label", predictionCol="prediction", maxDepth=5, maxBins=32, minInstancesPerNode=1,
+                         minWeightFractionPerNode=0.0, minInfoGain=0.0, maxMemoryInMB=256, cacheNodeIds=False, checkpointInterval=10,
+                         impurity="variance", leafCol="", seed=_java_string_hash(type(self).__name__))
+
+
+def _accessors(cls, names):
+    for n in names:
+        cap = n[0].upper() + n[1:]
+
+        def getter(self, _n=n):
+            return self.getOrDefault(_n)
+
+        def setter(self, value, _n=n):
+            return self._set(**{_n: value})
+        if not hasattr(cls, "get" + cap):
+            setattr(cls, "get" + cap, getter)
+        if not hasattr(cls, "set" + cap):
+            setattr(cls, "set" + cap, setter)
+    return cls
+
+
+_COMMON = ["featuresCol", "labelCol", "predictionCol", "maxDepth", "maxBins", "minInstancesPerNode", "minWeightFractionPerNode", "minInfoGain",
+           "maxMemoryInMB", "cacheNodeIds", "checkpointInterval", "impurity", "seed", "leafCol"]
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# dataset plumbing
+# ------------------------------------------------------------------------------------------------------------------
+def categorical_arities(dataset, featuresCol: str, num_features: int) -> np.ndarray:
+    """MetadataUtils.getCategoricalFeatures: nominal attrs -> len(vals) (or num_vals); binary -> 2; no metadata -> continuous."""
+    arity = np.zeros(num_features, np.int32)
+    try:
+        meta = dataset.schema[featuresCol].metadata
+    except Exception:  # noqa: BLE001
+        meta = {}
+    attrs = (meta or {}).get("ml_attr", {}).get("attrs", {})
+    for a in attrs.get("nominal", []):
+        k = len(a["vals"]) if "vals" in a else int(a.get("num_vals", 0))
+        if 0 <= a["idx"] < num_features:
+            arity[a["idx"]] = k
+    for a in attrs.get("binary", []):
+        if 0 <= a["idx"] < num_features:
+            arity[a["idx"]] = 2
+    return arity
+
+
+def _extract(dataset, featuresCol, labelCol=None):
+    """(X f64 [n, F] host, y f64 [n] host or None, partition sizes).  Real Spark: Arrow via toPandas(); stub: LocalFrame."""
+    if HAVE_PYSPARK and hasattr(dataset, "sparkSession"):
+        from pyspark.ml.functions import vector_to_array
+        from pyspark.sql import functions as F
+        cols = [vector_to_array(F.col(featuresCol)).alias("f")]
+        if labelCol:
+            cols.append(F.col(labelCol).cast("double").alias("y"))
+        sel = dataset.select(*cols)
+        sizes = sel.rdd.mapPartitions(lambda it: [sum(1 for _ in it)]).collect()      # row order == partition order (A.4)
+        pdf = sel.toPandas()
+        X = np.ascontiguousarray(np.stack(pdf["f"].to_numpy()), dtype=np.float64) if len(pdf) else np.zeros((0, 0))
+        y = pdf["y"].to_numpy(np.float64) if labelCol else None
+        return X, y, sizes
+    X = np.ascontiguousarray(dataset.col(featuresCol), dtype=np.float64)
+    y = np.ascontiguousarray(dataset.col(labelCol), dtype=np.float64) if labelCol else None
+    n = X.shape[0]
+    P = max(1, int(getattr(dataset, "num_partitions", 1)))
+    sizes = [n // P + (1 if i < n % P else 0) for i in range(P)]
+    return X, y, sizes
+
+
+def _append_prediction(dataset, predictionCol, pred):
+    if HAVE_PYSPARK and hasattr(dataset, "sparkSession"):
+        import pandas as pd
+        from pyspark.sql import functions as F
+        from pyspark.sql.window import Window
+        spark = dataset.sparkSession
+        idx = dataset.withColumn("__b2rf_i", F.monotonically_increasing_id())
+        w = Window.orderBy("__b2rf_i")
+        idx = idx.withColumn("__b2rf_r", F.row_number().over(w) - 1)
+        p = spark.createDataFrame(pd.DataFrame({"__b2rf_r": np.arange(len(pred)), predictionCol: pred}))
+        return idx.join(p, "__b2rf_r").drop("__b2rf_r", "__b2rf_i")
+    return dataset.withColumn(predictionCol, np.asarray(pred, np.float64))
+
+
+class _ForestModelBase(Model, _TreeRegressorParams):
+    def __init__(self, forest: Forest = None):
+        super().__init__()
+        self._base_defaults()
+        self._forest = forest
+
+    # Model.copy(extra) must carry the fitted forest: CrossValidator evaluates with model.transform(validation, epm[i])
+    def copy(self, extra=None):
+        that = super().copy(extra)
+        that._forest = self._forest
+        return that
+
+    @property
+    def numFeatures(self):
+        return self._forest.num_features
+
+    @property
+    def featureImportances(self):
+        imp = self._forest.feature_importances()
+        nz = np.nonzero(imp)[0]
+        return SparseVector(len(imp), nz, imp[nz])
+
+    @property
+    def toDebugString(self):
+        self._forest.uid = self.uid
+        return self._forest.to_debug_string(ensemble=self._ensemble)
+
+    def predict(self, value):
+        import torch
+        v = np.asarray(value.toArray() if hasattr(value, "toArray") else value, np.float64).reshape(1, -1)
+        return float(self._forest.predict(torch.as_tensor(v, device=self._device())).item())
+
+    @staticmethod
+    def _device():
+        import torch
+        if not torch.cuda.is_available():
+            raise RuntimeError("b2rf models predict on the GPU: no CUDA device is visible and there is no CPU fallback")
+        return torch.device("cuda", torch.cuda.current_device())
+
+    def _transform(self, dataset):
+        import torch
+        X, _, _ = _extract(dataset, self.getOrDefault("featuresCol"))
+        if X.shape[0] == 0:
+            return _append_prediction(dataset, self.getOrDefault("predictionCol"), np.zeros(0))
+        pred = self._forest.predict(torch.as_tensor(X, device=self._device())).cpu().numpy()
+        return _append_prediction(dataset, self.getOrDefault("predictionCol"), pred)
+
+
+class B200DecisionTreeRegressionModel(_ForestModelBase):
+    _ensemble = False
+
+    @property
+    def depth(self):
+        return self._forest.depth(0)
+
+    @property
+    def numNodes(self):
+        return self._forest.num_nodes(0)
+
+
+class B200RandomForestRegressionModel(_ForestModelBase):
+    _ensemble = True
+    numTrees = Param(Params, "numTrees", "Number of trees to train (>= 1).", TypeConverters.toInt)
+    featureSubsetStrategy = Param(Params, "featureSubsetStrategy", "The number of features to consider for splits at each tree node.",
+                                  TypeConverters.toString)
+    subsamplingRate = Param(Params, "subsamplingRate", "Fraction of the training data used for learning each decision tree, in range (0, 1].",
+                            TypeConverters.toFloat)
+    bootstrap = Param(Params, "bootstrap", "Whether bootstrap samples are used when building trees.", TypeConverters.toBoolean)
+
+    def __init__(self, forest=None):
+        super().__init__(forest)
+        self._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True)
+
+    @property
+    def getNumTrees(self):
+        return self._forest.num_trees
+
+    @property
+    def treeWeights(self):
+        return [1.0] * self._forest.num_trees
+
+    @property
+    def totalNumNodes(self):
+        return self._forest.num_nodes()
+
+    @property
+    def trees(self):
+        out = []
+        fo = self._forest
+        for t in range(fo.num_trees):
+            s = fo.tree_slice(t)
+            sub = Forest(fo.num_features, np.array([0, s.stop - s.start], np.int64), fo.feature[s], fo.threshold[s], fo.left[s], fo.right[s],
+                         fo.prediction[s], fo.impurity[s], fo.gain[s], fo.stats[s], fo.ncat[s], fo.cat_off[s], fo.cat_len[s], fo.cats)
+            out.append(B200DecisionTreeRegressionModel(sub))
+        return out
+
+
+class _TreeEstimatorBase(Estimator, _TreeRegressorParams):
+    _model_cls = None
+
+    def _tree_params(self) -> TreeParams:
+        g = self.getOrDefault
+        return TreeParams(maxDepth=g("maxDepth"), maxBins=g("maxBins"), minInstancesPerNode=g("minInstancesPerNode"),
+                          minWeightFractionPerNode=g("minWeightFractionPerNode"), minInfoGain=g("minInfoGain"), maxMemoryInMB=g("maxMemoryInMB"),
+                          impurity=g("impurity").lower(), seed=g("seed"), **self._ensemble_params())
+
+    def _make_model(self, forest):
+        m = self._model_cls(forest)
+        m.uid = self.uid                       # pyspark models carry their estimator's uid, so shared Params route to them
+        for p in list(m.params):
+            setattr(m, p.name, p._copy_new_parent(m)) if hasattr(p, "_copy_new_parent") else None
+        m._paramMap = {}
+        m._defaultParamMap = {}
+        m._base_defaults()
+        if isinstance(m, B200RandomForestRegressionModel):
+            m._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True)
+        self._copyValues(m)
+        return m
+
+    def _fit_many(self, dataset, estimators):
+        """Train several parameterisations on one extraction of the dataset (one host->device copy, shared by all)."""
+        import torch
+        from . import trainer
+        est0 = estimators[0]
+        X, y, sizes = _extract(dataset, est0.getOrDefault("featuresCol"), est0.getOrDefault("labelCol"))
+        if X.shape[0] == 0:
+            raise ValueError("DecisionTree requires size of input RDD > 0, but was given by empty one.")
+        arity = categorical_arities(dataset, est0.getOrDefault("featuresCol"), X.shape[1])
+        po = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+        dev = _ForestModelBase._device()
+        Xd = torch.as_tensor(X, device=dev)
+        yd = torch.as_tensor(y, device=dev)
+        for est in estimators:
+            forest = trainer.fit_tensors(Xd, yd, arity, est._tree_params(), part_offsets=po)
+            yield est._make_model(forest)
+
+    def _fit(self, dataset):
+        return next(self._fit_many(dataset, [self]))
+
+    def fitMultiple(self, dataset, paramMaps):
+        """Thread-safe iterator of (index, model) (CrossValidator's ThreadPool calls next() concurrently, `ML 07:130,143-144`).
+        All candidates share one extraction / device copy of the fold."""
+        ests = [self.copy(pm) for pm in paramMaps]
+        gen = self._fit_many(dataset, ests)
+        lock = threading.Lock()
+        counter = iter(range(len(ests)))
+
+        class _It:
+            def __iter__(s):
+                return s
+
+            def __next__(s):
+                with lock:
+                    i = next(counter)
+                    return i, next(gen)
+            next = __next__
+        return _It()
+
+
+class B200DecisionTreeRegressor(_TreeEstimatorBase):
+    """pyspark.ml.regression.DecisionTreeRegressor, trained on the GPU (`ML 06 - Decision Trees.py:73-75,118,126`)."""
+    _model_cls = B200DecisionTreeRegressionModel
+
+    def __init__(self, **kwargs):
+        super().__init__()
+        self._base_defaults()
+        self.setParams(**kwargs)
+
+    def setParams(self, **kwargs):
+        return self._set(**kwargs)
+
+    def _ensemble_params(self):
+        return dict(numTrees=1, featureSubsetStrategy="all", subsamplingRate=1.0, bootstrap=False)
+
+
+class B200RandomForestRegressor(_TreeEstimatorBase):
+    """pyspark.ml.regression.RandomForestRegressor, trained on the GPU (`ML 07 ...:41,74-77`, `ML 08 - Hyperopt.py:71,97`)."""
+    _model_cls = B200RandomForestRegressionModel
+    numTrees = B200RandomForestRegressionModel.numTrees
+    featureSubsetStrategy = B200RandomForestRegressionModel.featureSubsetStrategy
+    subsamplingRate = B200RandomForestRegressionModel.subsamplingRate
+    bootstrap = B200RandomForestRegressionModel.bootstrap
+
+    def __init__(self, **kwargs):
+        super().__init__()
+        self._base_defaults()
+        self._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True)
+        self.setParams(**kwargs)
+
+    def setParams(self, **kwargs):
+        return self._set(**kwargs)
+
+    def _ensemble_params(self):
+        g = self.getOrDefault
+        return dict(numTrees=g("numTrees"), featureSubsetStrategy=g("featureSubsetStrategy"), subsamplingRate=g("subsamplingRate"),
+                    bootstrap=g("bootstrap"))
+
+
+for _c in (B200DecisionTreeRegressor, B200DecisionTreeRegressionModel):
+    _accessors(_c, _COMMON)
+for _c in (B200RandomForestRegressor, B200RandomForestRegressionModel):
+    _accessors(_c, _COMMON + ["numTrees", "featureSubsetStrategy", "subsamplingRate", "bootstrap"])

@@ -1,0 +1,83 @@
+"""Host-side contract of the pyspark.ml drop-in classes, exercised without a GPU.  pyspark is not
+installable in this image, so the classes run on the in-repo stub of the pyspark.ml.param surface."""
+import numpy as np
+import pytest
+
+
+@pytest.fixture(scope="module")
+def sp(b2rf):
+    from b2rf import spark
+    return spark
+
+
+def test_defaults_match_pyspark_3_1(sp):
+    dt = sp.B200DecisionTreeRegressor()
+    want = dict(maxDepth=5, maxBins=32, minInstancesPerNode=1, minWeightFractionPerNode=0.0, minInfoGain=0.0, maxMemoryInMB=256,
+                cacheNodeIds=False, checkpointInterval=10, impurity="variance", featuresCol="features", labelCol="label",
+                predictionCol="prediction", leafCol="")
+    for k, v in want.items():
+        assert dt.getOrDefault(k) == v, k
+    rf = sp.B200RandomForestRegressor()
+    for k, v in dict(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True, **want).items():
+        assert rf.getOrDefault(k) == v, k
+    assert isinstance(rf.getSeed(), int)
+
+
+def test_ml06_setter_and_kwargs(sp):
+    dt = sp.B200DecisionTreeRegressor(labelCol="price")          # `ML 06 - Decision Trees.py:75`
+    assert dt.getLabelCol() == "price" and dt.getMaxBins() == 32
+    assert dt.setMaxBins(40) is dt and dt.getMaxBins() == 40     # `ML 06:118`
+    rf = sp.B200RandomForestRegressor(labelCol="price", maxBins=40, seed=42)   # `ML 08 - Hyperopt.py:71`
+    assert (rf.getMaxBins(), rf.getSeed()) == (40, 42)
+    assert "maxDepth: Maximum depth of the tree." in rf.explainParams()        # `ML 07:56`
+    assert "current: 40" in rf.explainParam("maxBins")
+
+
+def test_copy_keeps_uid_and_converts_integral_floats(sp):
+    rf = sp.B200RandomForestRegressor(labelCol="price", maxBins=40, seed=42)
+    c = rf.copy({rf.maxDepth: 4.0, rf.numTrees: 37.0})           # `ML 08:97,120-121`: hp.quniform yields floats
+    assert c.uid == rf.uid and c is not rf
+    assert c.getMaxDepth() == 4 and isinstance(c.getMaxDepth(), int) and c.getNumTrees() == 37
+    assert rf.getMaxDepth() == 5 and rf.getNumTrees() == 20      # original untouched
+    with pytest.raises(TypeError):
+        rf.copy({rf.maxDepth: 4.5})
+    tp = c._tree_params()
+    assert (tp.maxDepth, tp.numTrees, tp.bootstrap, tp.featureSubsetStrategy) == (4, 37, True, "auto")
+    dt = sp.B200DecisionTreeRegressor(maxDepth=3)
+    tp = dt._tree_params()
+    assert (tp.numTrees, tp.bootstrap, tp.featureSubsetStrategy, tp.subsamplingRate) == (1, False, "all", 1.0)
+
+
+def test_param_grid_style_maps(sp):
+    rf = sp.B200RandomForestRegressor()
+    grid = [{rf.maxDepth: d, rf.numTrees: t} for d in (2, 5) for t in (5, 10)]      # `ML 07:74-77`
+    got = [(rf.copy(pm).getMaxDepth(), rf.copy(pm).getNumTrees()) for pm in grid]
+    assert got == [(2, 5), (2, 10), (5, 5), (5, 10)]
+    other = sp.B200RandomForestRegressor()
+    assert other.copy({rf.maxDepth: 9}).getMaxDepth() == 5       # a Param owned by another uid is not applied
+
+
+def test_categorical_arities_from_ml_attr(sp, b2rf):
+    from b2rf._pyspark_stub import LocalFrame, ml_attr_metadata
+    arity = [2, 0, 36, 0]
+    lf = LocalFrame({"features": np.zeros((3, 4)), "price": np.zeros(3)}, {"features": ml_attr_metadata(arity)})
+    assert sp.categorical_arities(lf, "features", 4).tolist() == arity
+    meta = {"ml_attr": {"attrs": {"binary": [{"idx": 1, "name": "b"}], "nominal": [{"idx": 0, "name": "n", "num_vals": 7}]}, "num_attrs": 3}}
+    lf = LocalFrame({"features": np.zeros((3, 3))}, {"features": meta})
+    assert sp.categorical_arities(lf, "features", 3).tolist() == [7, 2, 0]
+    assert sp.categorical_arities(LocalFrame({"features": np.zeros((3, 3))}), "features", 3).tolist() == [0, 0, 0]
+
+
+def test_model_copy_carries_forest_and_api(sp, b2rf, oracle):
+    X = np.array([[1.0], [0.0]]); y = np.array([1.0, 0.0])
+    o = oracle.fit(X, y, [0], maxDepth=2)
+    fo = b2rf.Forest(1, o.tree_off, o.feature, o.threshold, o.left, o.right, o.prediction, o.impurity, o.gain, o.stats, o.ncat, o.cat_off,
+                     o.cat_len, o.cats)
+    est = sp.B200DecisionTreeRegressor(maxDepth=2)
+    m = est._make_model(fo)
+    assert m.uid == est.uid and m.getMaxDepth() == 2
+    assert (m.depth, m.numNodes, m.numFeatures) == (1, 3, 1)
+    assert list(m.featureImportances) == [1.0] and "SparseVector(1, {0: 1.0})" == repr(m.featureImportances)
+    assert m.toDebugString.startswith(f"DecisionTreeRegressionModel: uid={est.uid}, depth=1, numNodes=3, numFeatures=1\n  If (feature 0 <= 0.5)")
+    m2 = m.copy({m.predictionCol: "p2"})
+    assert m2._forest is m._forest and m2.getPredictionCol() == "p2" and m.getPredictionCol() == "prediction"

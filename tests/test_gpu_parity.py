@@ -309,3 +309,43 @@ def test_golden_fixtures_gpu(b2rf, cuda):
         assert [float(v).hex() for v in f.prediction] == gold["prediction_hex"], fn     # integer labels: sums are exact
         assert f.stats[:, 0].tolist() == gold["count"], fn
         assert [sorted(f.cats[o:o + n].tolist()) for o, n in zip(f.cat_off, f.cat_len)] == gold["cats"], fn
+
+
+def test_spark_adapter_pipeline_flow(b2rf, oracle, cuda):
+    """The labs' flow on the drop-in classes (stub frame instead of a Spark DataFrame): ML 06 maxBins error then fit,
+    featureImportances zipped with columns, transform + RMSE; ML 07 fitMultiple over a ParamGrid; ML 08 copy({...: float})."""
+    from b2rf import spark as sp
+    from b2rf._pyspark_stub import LocalFrame, ml_attr_metadata
+    X, y, arity = b2rf.synth.airbnb(7146)
+    ntr = 5716
+    meta = {"features": ml_attr_metadata(arity)}
+    train = LocalFrame({"features": X[:ntr].numpy(), "price": y[:ntr].numpy()}, meta, num_partitions=4)
+    test = LocalFrame({"features": X[ntr:].numpy(), "price": y[ntr:].numpy()}, meta)
+    dt = sp.B200DecisionTreeRegressor(labelCol="price")
+    with pytest.raises(b2rf.IllegalArgumentException, match="DecisionTree requires maxBins"):
+        dt.fit(train)                                          # `ML 06:81,91-92`
+    dt.setMaxBins(40)
+    model = dt.fit(train)                                      # `ML 06:126`
+    po = np.array([0, 1429, 2858, 4287, 5716])
+    o = oracle.fit(X[:ntr].numpy(), y[:ntr].numpy(), arity, maxDepth=5, maxBins=40, part_offsets=po)
+    assert model.numNodes == len(o.feature) and model.depth == 5
+    imp = list(model.featureImportances)                       # `ML 06:141,153`
+    assert len(imp) == 33 and abs(sum(imp) - 1.0) < 1e-12
+    pred = model.transform(test).col("prediction")             # `ML 06:188`
+    np.testing.assert_allclose(pred, o.predict(X[ntr:].numpy()), rtol=REL)
+    assert "If (feature" in model.toDebugString
+    # ML 07: candidates of a ParamGrid through fitMultiple, evaluated with model.transform(validation, epm[i])
+    rf = sp.B200RandomForestRegressor(labelCol="price", maxBins=40, seed=42)
+    grid = [{rf.maxDepth: d, rf.numTrees: t} for d in (2, 5) for t in (5, 10)]
+    got = dict(rf.fitMultiple(train, grid))
+    assert sorted(got) == [0, 1, 2, 3]
+    for i, pm in enumerate(grid):
+        m = got[i]
+        oo = oracle.fit(X[:ntr].numpy(), y[:ntr].numpy(), arity, maxDepth=pm[rf.maxDepth], maxBins=40, numTrees=pm[rf.numTrees], bootstrap=True,
+                        seed=42, part_offsets=po)
+        assert m.getNumTrees == pm[rf.numTrees] and m.totalNumNodes == len(oo.feature)
+        p = m.transform(test, {m.predictionCol: "p"}).col("p")
+        np.testing.assert_allclose(p, oo.predict(X[ntr:].numpy()), rtol=REL)
+    # ML 08: float-valued params through copy
+    m = rf.copy({rf.maxDepth: 3.0, rf.numTrees: 4.0}).fit(train)
+    assert m.getNumTrees == 4 and len(m.trees) == 4 and m.trees[0].depth <= 3
