@@ -75,6 +75,19 @@ int b2rf_find_splits(const double* d_sample, int64_t n_sample, int32_t F, const 
                      double weightedNumSamples, double* d_thresholds, int32_t* d_nsplits, void* d_workspace,
                      size_t workspace_bytes, void* stream);
 
+/* Split finding for callers that must not allocate.  (No counterpart in the reference: MLlib allocates freely on the JVM
+ * heap; this exists for hosts of this library whose GPU memory is entirely owned by their own pool — e.g. a Spark
+ * executor plugin — or that cannot tolerate the device synchronisation of cudaMalloc/cudaFree.)
+ * Same inputs, outputs and results as b2rf_find_splits, but the sort workspace is a fixed 8 MiB array built into the
+ * library (resident on every GPU that loads it), so neither the caller nor the library allocates anything.
+ * Limit: next_pow2(n_sample) * F * 8 <= B2RF_NOALLOC_WORKSPACE_BYTES, otherwise B2RF_ERR_ARG with an explanatory message.
+ * The first call on a device resolves the array's address (do it before any stream capture); calls on one device share
+ * the array, so calls that could overlap on the GPU must be serialised by the caller.  The array needs no clearing. */
+#define B2RF_NOALLOC_WORKSPACE_BYTES (8u << 20)
+size_t b2rf_find_splits_noalloc_max_bytes(void);
+int b2rf_find_splits_noalloc(const double* d_sample, int64_t n_sample, int32_t F, const int32_t* d_arity, int32_t maxPossibleBins,
+                             double weightedNumSamples, double* d_thresholds, int32_t* d_nsplits, void* stream);
+
 /* ---- K2: TreePoint.convertToTreeRDD / findBin (row a3) ------------------------------------------------------ */
 /* Bins rows [0,n_rows) of d_X into d_bins[f][row0 + i].  *d_err (int32, caller-zeroed) becomes feature+1 on an invalid
  * categorical value. */

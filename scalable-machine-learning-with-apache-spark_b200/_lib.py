@@ -40,6 +40,8 @@ _SIGS = {
     "b2rf_sample_rows": (C.c_int, [vp, i64, i64, i64, i32, i64, f64, vp, i64, vp, vp]),
     "b2rf_find_splits_workspace_bytes": (sz, [i64, i32]),
     "b2rf_find_splits": (C.c_int, [vp, i64, i32, vp, i32, f64, vp, vp, vp, sz, vp]),
+    "b2rf_find_splits_noalloc_max_bytes": (sz, []),
+    "b2rf_find_splits_noalloc": (C.c_int, [vp, i64, i32, vp, i32, f64, vp, vp, vp]),
     "b2rf_bin": (C.c_int, [vp, i64, i64, i32, vp, vp, vp, i32, vp, i64, i64, vp, vp, i64, vp]),
     "b2rf_bag": (C.c_int, [i64, vp, i32, i32, i32, f64, i32, vp, i64, vp, i64, vp]),
     "b2rf_trainer_create": (C.c_int, [vp, i32, vp, vp, vp, i64, vp]),

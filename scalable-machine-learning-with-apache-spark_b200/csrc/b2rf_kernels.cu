@@ -11,6 +11,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 
 namespace b2rf {
 
@@ -935,6 +936,70 @@ int b2rf_find_splits(const double* d_sample, int64_t n_sample, int32_t F, const 
   find_splits_kernel<<<F, 1024, 0, (cudaStream_t)stream>>>(d_sample, n_sample, F, d_arity, maxPossibleBins - 1, weightedNumSamples, d_thresholds,
                                                             d_nsplits, (double*)d_workspace, n_pad);
   return cuda_ok(cudaGetLastError(), "b2rf_find_splits") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+// ---- split finding without any allocation ----------------------------------------------------------------------
+// Some hosts of this library cannot call the CUDA allocator at all: a Spark executor plugin (or any serving process) whose
+// own memory pool has already reserved the whole GPU leaves nothing for cudaMalloc to hand out, and a latency-critical
+// caller cannot accept the device-wide synchronisation that cudaMalloc / cudaFree imply.  Such a caller can still lend
+// input and output buffers from its pool, but b2rf_find_splits also needs a sort workspace.  This variant keeps that
+// workspace in a fixed array that is part of the loaded module itself.
+//
+//  * The array is B2RF_NOALLOC_WORKSPACE_BYTES (8 MiB) on EVERY GPU that loads libb2rf.so, from load until exit.
+//  * Requests needing more (next_pow2(n_sample) * F * 8 bytes) are refused with B2RF_ERR_ARG; use b2rf_find_splits then.
+//  * The first call on each device looks the array's device address up (one cudaGetSymbolAddress, no allocation) with
+//    that device current.  Make that first call outside of any stream capture.
+//  * All calls on a device share the one array and it keeps whatever the previous call left in it.  Nothing in it has
+//    to start at zero: the kernel overwrites every element it later reads.  Two calls whose kernels overlap on the GPU
+//    (different streams, or different host threads) would sort in the same memory and corrupt each other — serialise them.
+static __device__ __align__(256) unsigned char g_noalloc_workspace[B2RF_NOALLOC_WORKSPACE_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;
+void* g_noalloc_addr[kMaxDevices] = {};   // device address of g_noalloc_workspace, per device ordinal
+
+// In host code `g_noalloc_workspace` is only a handle for the symbol, not a device address; the address a kernel can use
+// comes from cudaGetSymbolAddress, queried once per device while that device is current.
+int noalloc_workspace(void** out) {
+  int dev = -1;
+  if (!cuda_ok(cudaGetDevice(&dev), "b2rf_find_splits_noalloc: cudaGetDevice")) return B2RF_ERR_CUDA;
+  if (dev < 0 || dev >= kMaxDevices) { set_error("b2rf_find_splits_noalloc: device ordinal out of range"); return B2RF_ERR_ARG; }
+  std::lock_guard<std::mutex> lock(g_noalloc_mu);
+  if (g_noalloc_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    if (!cuda_ok(cudaGetSymbolAddress(&ptr, g_noalloc_workspace), "b2rf_find_splits_noalloc: cudaGetSymbolAddress")) return B2RF_ERR_CUDA;
+    if (ptr == nullptr) { set_error("b2rf_find_splits_noalloc: symbol address is null"); return B2RF_ERR_CUDA; }
+    g_noalloc_addr[dev] = ptr;
+  }
+  *out = g_noalloc_addr[dev];
+  return B2RF_OK;
+}
+}  // namespace
+
+size_t b2rf_find_splits_noalloc_max_bytes(void) { return (size_t)B2RF_NOALLOC_WORKSPACE_BYTES; }
+
+int b2rf_find_splits_noalloc(const double* d_sample, int64_t n_sample, int32_t F, const int32_t* d_arity, int32_t maxPossibleBins,
+                             double weightedNumSamples, double* d_thresholds, int32_t* d_nsplits, void* stream) {
+  if (F <= 0 || n_sample <= 0 || maxPossibleBins < 1 || !d_sample || !d_arity || !d_thresholds || !d_nsplits) {
+    set_error("b2rf_find_splits_noalloc: bad argument"); return B2RF_ERR_ARG;
+  }
+  const size_t need = b2rf_find_splits_workspace_bytes(n_sample, F);
+  if (need > (size_t)B2RF_NOALLOC_WORKSPACE_BYTES) {
+    char buf[256];
+    snprintf(buf, sizeof buf, "b2rf_find_splits_noalloc: this sample needs a %zu-byte workspace but the built-in one holds %zu bytes "
+             "(next_pow2(n_sample) * F * 8 must not exceed it); call b2rf_find_splits with a caller-provided workspace instead",
+             need, (size_t)B2RF_NOALLOC_WORKSPACE_BYTES);
+    set_error(buf);
+    return B2RF_ERR_ARG;
+  }
+  void* ws = nullptr;
+  const int rc = noalloc_workspace(&ws);
+  if (rc != B2RF_OK) return rc;
+  const int64_t n_pad = next_pow2(n_sample < 2 ? 2 : n_sample);
+  find_splits_kernel<<<F, 1024, 0, (cudaStream_t)stream>>>(d_sample, n_sample, F, d_arity, maxPossibleBins - 1, weightedNumSamples, d_thresholds,
+                                                            d_nsplits, static_cast<double*>(ws), n_pad);
+  return cuda_ok(cudaGetLastError(), "b2rf_find_splits_noalloc") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
 int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const double* d_thresholds, const int32_t* d_nsplits,
