@@ -1,0 +1,66 @@
+"""Multi-GPU parity check, run under torchrun on N GPUs (not collected by pytest):
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/mgpu_check.py
+Rows are sharded contiguously over the ranks; the sharded fit must equal the CPU oracle's fit of the whole dataset."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+
+def main():
+    rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dev = torch.device("cuda", lr)
+    dist.init_process_group("nccl", device_id=dev)
+    import b2rf
+    from b2rf import trainer
+    from helpers import assert_forest_parity, assert_parity_allowing_ties, assert_trace_parity
+    from oracle import oracle as O
+    ok = True
+    for name, gen, n, kw in [("airbnb-rf", b2rf.synth.airbnb, 6001, dict(maxDepth=7, maxBins=40, numTrees=12, bootstrap=True, seed=42)),
+                             ("airbnb-dt", b2rf.synth.airbnb, 5716, dict(maxDepth=5, maxBins=40)),
+                             ("c3-slice", lambda m, row0=0: b2rf.synth.c3(m, row0=row0, device="cpu"), 90000,
+                              dict(maxDepth=6, maxBins=64, numTrees=6, bootstrap=True, seed=42))]:
+        cuts = [n * r // world for r in range(world + 1)]
+        cuts[1] += 7 if world > 1 else 0                         # ragged shards
+        lo, hi = cuts[rank], cuts[rank + 1]
+        X, y, arity = gen(hi - lo, row0=lo)
+        # partitions: 512 rows each inside a shard (a partition never spans ranks); global partition list = concatenation
+        po_local = np.minimum(np.arange(0, hi - lo + 512, 512), hi - lo).astype(np.int64)
+        p = b2rf.TreeParams(**kw)
+        g = trainer.fit_tensors(X.to(dev), y.to(dev), arity, p, part_offsets=po_local, keep_trace=True)
+        if rank == 0:
+            Xa, ya, _ = gen(n, row0=0)
+            po = [0]
+            for r in range(world):
+                m = cuts[r + 1] - cuts[r]
+                loc = np.minimum(np.arange(0, m + 512, 512), m)[1:]
+                po += [cuts[r] + int(v) for v in loc]
+            mpb = min(p.maxBins, n)
+            meta_max = max([a if a > 1 else mpb for a in arity])
+            req = max(meta_max * meta_max, 10000)
+            fraction = req / n if req < n else 1.0
+            sidx = np.nonzero(O.sample_keep(p.seed, np.arange(n), fraction))[0] if fraction < 1 else None
+            o = O.fit(Xa.numpy(), ya.numpy(), arity, part_offsets=po, sample_idx=sidx, fraction=fraction,
+                      **{k: v for k, v in kw.items()})
+            try:
+                assert_parity_allowing_ties(g, o, max_ties=2)
+                print(f"[mgpu] {name}: world={world} OK ({g.num_nodes()} nodes, groups={g.counters['groups']})", flush=True)
+            except AssertionError as e:
+                ok = False
+                print(f"[mgpu] {name}: FAILED {e}", flush=True)
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.broadcast(flag, 0)
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(0 if int(flag.item()) else 1)
+
+
+if __name__ == "__main__":
+    main()
