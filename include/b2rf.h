@@ -46,7 +46,7 @@ typedef struct b2rf_params {
   int32_t featuresPerNode;  /* resolved featureSubsetStrategy (b2rf_features_per_node) */
   int32_t maxMemoryInMB;
   int32_t bootstrap;
-  int32_t reserved;
+  int32_t histMode;  /* K4 implementation: 0 = segments (default), 1 = per-group counting sort, 2 = column scan + global RED */
   double minInfoGain;
   double minWeightFractionPerNode;
   double subsamplingRate;

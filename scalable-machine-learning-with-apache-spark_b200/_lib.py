@@ -13,7 +13,7 @@ B2RF_OK, ERR_ARG, ERR_MAXBINS, ERR_DATA, ERR_CUDA, ERR_STATE = 0, -1, -2, -3, -4
 
 class B2rfParams(C.Structure):
     _fields_ = [("maxDepth", C.c_int32), ("maxBins", C.c_int32), ("minInstancesPerNode", C.c_int32), ("numTrees", C.c_int32),
-                ("featuresPerNode", C.c_int32), ("maxMemoryInMB", C.c_int32), ("bootstrap", C.c_int32), ("reserved", C.c_int32),
+                ("featuresPerNode", C.c_int32), ("maxMemoryInMB", C.c_int32), ("bootstrap", C.c_int32), ("histMode", C.c_int32),
                 ("minInfoGain", C.c_double), ("minWeightFractionPerNode", C.c_double), ("subsamplingRate", C.c_double),
                 ("seed", C.c_int64)]
 

@@ -46,6 +46,13 @@ struct HistLaunch {
   uint32_t* slot_count;             // MODE 2 only: rows per slot
 };
 
+// Row segment of one node in a tree's row list (segment mode): rows [start, start+count) of list `buf` (0/1 ping-pong).
+struct __align__(16) DSeg {
+  uint64_t start;
+  uint32_t count;
+  uint32_t buf;
+};
+
 struct BucketLaunch {
   const uint8_t* bins_rm; int64_t ldr;   // row-major bin codes [row][ldr]
   const double* y;
@@ -57,7 +64,28 @@ struct BucketLaunch {
   const uint2* slot_fo; const int64_t* slot_base; const int32_t* slot_cells; int32_t Fsub;
   int32_t maxCells;                      // shared-memory histogram capacity in cells
   double* hist;
+  // segment mode (dseg != nullptr): slot s owns rows idx[seg.buf][seg.start ...] with seg = dseg[slot_pos[s]]
+  const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;
 };
+
+constexpr int SEG_CH = 4096;            // rows per (node, chunk) task
+constexpr int COMPACT_ROWS = 2048;      // rows per compaction block
+
+struct PartLaunch {                      // stable partition of the row segments of the nodes split in one group
+  const int64_t* split_pos; int32_t nSplits;          // flat node-table positions (tree * stride + node) of the split nodes
+  const DNode* dnodes; DSeg* dseg; const uint32_t* catmasks;
+  const uint8_t* bins; int64_t ldb;                    // column-major bin matrix
+  uint32_t* idx0; uint32_t* idx1;
+  uint32_t* chunk_prefix;                              // [nSplits + 1]
+  uint32_t* left_cnt; uint32_t* left_off;              // [tasks]
+  uint32_t* predbits;                                  // [tasks][SEG_CH / 32]
+};
+cudaError_t launch_partition(const PartLaunch& p, cudaStream_t s);
+cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s);
+cudaError_t launch_compact_count(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, uint32_t* blockCnt, unsigned long long* totals, cudaStream_t s);
+cudaError_t launch_compact_write(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, const uint32_t* blockOff, const uint64_t* treeBase, uint32_t* idx,
+                                 cudaStream_t s);
+cudaError_t launch_regrow_segs(const DSeg* src, int64_t oldStride, DSeg* dst, int64_t newStride, int T, cudaStream_t s);
 
 cudaError_t launch_hist(const HistLaunch& a, int mode, cudaStream_t s, std::string* err);
 cudaError_t launch_bucket_pipeline(const HistLaunch& h, const BucketLaunch& b, uint32_t* cursor, cudaStream_t s, std::string* err);

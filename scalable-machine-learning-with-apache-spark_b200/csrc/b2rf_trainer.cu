@@ -175,6 +175,7 @@ struct b2rf_trainer {
   double* d_hist = nullptr; int64_t histCells = 0;
   const uint8_t* d_bins_rm = nullptr; int64_t ldr = 0;   // optional row-major twin of the bin matrix => bucket mode
   bool bucketMode = false;
+  bool segMode = false;   // bucket mode with per-tree row lists kept partitioned by node (default); else per-group counting sort
   int32_t chunkRows = 4096;
 
   // host trees + scheduler
@@ -199,6 +200,12 @@ struct b2rf_trainer {
   DevBuf<int32_t> dSlotCells;
   PinBuf<int32_t> hSlotCells;
   std::vector<int64_t> inBag;   // rows with weight > 0 per tree (bound of the per-group row list)
+  // segment mode
+  DevBuf<DSeg> dSeg;
+  DevBuf<uint32_t> dIdx0, dIdx1, dPartPrefix, dLeftCnt, dLeftOff, dPredBits;
+  DevBuf<int64_t> dSlotPos, dSplitPos;
+  PinBuf<int64_t> hSlotPos, hSplitPos;
+  std::vector<uint64_t> treeBase;
   PinBuf<DNodeUpdate> hUpd;
   PinBuf<uint2> hSlotFo;
   PinBuf<int64_t> hSlotBase;
@@ -233,6 +240,8 @@ struct b2rf_trainer {
   ~b2rf_trainer() {
     dn.release(); dnUpd.release(); dCat.release(); dSlotFo.release(); dSlotBase.release(); dParent.release();
     dHasParent.release(); dNumBins.release(); dIsCat.release(); dTreeIds.release(); dRec.release();
+    dSeg.release(); dIdx0.release(); dIdx1.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
+    dSlotPos.release(); dSplitPos.release(); hSlotPos.release(); hSplitPos.release();
     dSlotCount.release(); dCursor.release(); dChunkPrefix.release(); dRowList.release(); dSlotStart.release(); dSlotCells.release(); hSlotCells.release();
     hUpd.release(); hSlotFo.release(); hSlotBase.release(); hParent.release(); hHasParent.release(); hTreeIds.release(); hRec.release();
     if (ev0) cudaEventDestroy(ev0);
@@ -351,22 +360,49 @@ int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const
   t->d_hist = d_hist; t->histCells = hist_cells;
   t->d_bins_rm = d_bins_rm; t->ldr = ldr;
   t->bucketMode = d_bins_rm != nullptr && ldr >= t->F && n_rows_local < ((int64_t)1 << 27);
-  if (const char* m = std::getenv("B2RF_HIST_MODE")) { if (std::string(m) == "scan") t->bucketMode = false; }
-  if (t->bucketMode) {
-    // rows in bag per tree bound the per-group row list
-    unsigned long long* d_cnt = nullptr;
-    std::vector<unsigned long long> h_cnt(t->T, 0);
-    if (!cuda_ok(cudaMalloc((void**)&d_cnt, (size_t)t->T * 8), "bind alloc")) return B2RF_ERR_CUDA;
-    bool ok = cuda_ok(cudaMemset(d_cnt, 0, (size_t)t->T * 8), "bind memset");
-    ok = ok && cuda_ok(launch_count_active(d_node, ldn, t->T, n_rows_local, d_cnt, 0), "count in-bag rows");
-    ok = ok && cuda_ok(cudaMemcpy(h_cnt.data(), d_cnt, (size_t)t->T * 8, cudaMemcpyDeviceToHost), "bind copy");
-    cudaFree(d_cnt);
-    if (!ok) return B2RF_ERR_CUDA;
-    t->inBag.assign(h_cnt.begin(), h_cnt.end());
+  t->segMode = t->bucketMode;
+  if (t->p.histMode == 2) { t->bucketMode = false; t->segMode = false; }
+  else if (t->p.histMode == 1) t->segMode = false;
+  if (const char* m = std::getenv("B2RF_HIST_MODE")) {
+    const std::string mode(m);
+    if (mode == "scan") { t->bucketMode = false; t->segMode = false; }
+    else if (mode == "sort") t->segMode = false;
   }
   // device node table: one stride per tree
   const int64_t full = (int64_t)1 << std::min(t->p.maxDepth + 1, 17);
   t->nodeStride = full;
+  if (t->bucketMode) {
+    // in-bag rows per tree; in segment mode also the initial row lists (ascending rows, packed row | weight << 27)
+    const int nb = (int)((n_rows_local + COMPACT_ROWS - 1) / COMPACT_ROWS);
+    DevBuf<uint32_t> blockCnt;
+    unsigned long long* d_tot = nullptr;
+    std::vector<unsigned long long> h_tot(t->T, 0);
+    if (!blockCnt.ensure((size_t)std::max(nb, 1) * t->T)) return B2RF_ERR_CUDA;
+    if (!cuda_ok(cudaMalloc((void**)&d_tot, (size_t)t->T * 8), "bind alloc")) { blockCnt.release(); return B2RF_ERR_CUDA; }
+    bool ok = cuda_ok(cudaMemset(d_tot, 0, (size_t)t->T * 8), "bind memset");
+    ok = ok && cuda_ok(launch_compact_count(d_w, ldw, t->T, n_rows_local, blockCnt.p, d_tot, 0), "count in-bag rows");
+    ok = ok && cuda_ok(cudaMemcpy(h_tot.data(), d_tot, (size_t)t->T * 8, cudaMemcpyDeviceToHost), "bind copy");
+    t->inBag.assign(h_tot.begin(), h_tot.end());
+    if (ok && t->segMode) {
+      t->treeBase.assign(t->T + 1, 0);
+      for (int i = 0; i < t->T; i++) t->treeBase[i + 1] = t->treeBase[i] + h_tot[i];
+      const size_t total = std::max<uint64_t>(t->treeBase[t->T], 1);
+      uint64_t* d_base = nullptr;
+      ok = ok && t->dIdx0.ensure(total) && t->dIdx1.ensure(total) && t->dSeg.ensure((size_t)t->nodeStride * t->T);
+      ok = ok && cuda_ok(cudaMalloc((void**)&d_base, (size_t)(t->T + 1) * 8), "bind alloc");
+      ok = ok && cuda_ok(cudaMemcpy(d_base, t->treeBase.data(), (size_t)(t->T + 1) * 8, cudaMemcpyHostToDevice), "bind copy");
+      ok = ok && cuda_ok(launch_compact_write(d_w, ldw, t->T, n_rows_local, blockCnt.p, d_base, t->dIdx0.p, 0), "build row lists");
+      std::vector<DSeg> roots(t->T);
+      for (int i = 0; i < t->T; i++) { roots[i].start = t->treeBase[i]; roots[i].count = (uint32_t)h_tot[i]; roots[i].buf = 0; }
+      ok = ok && cuda_ok(cudaMemcpy2D(t->dSeg.p, (size_t)t->nodeStride * sizeof(DSeg), roots.data(), sizeof(DSeg), sizeof(DSeg), t->T,
+                                      cudaMemcpyHostToDevice), "bind copy root segments");
+      ok = ok && cuda_ok(cudaDeviceSynchronize(), "bind sync");
+      if (d_base) cudaFree(d_base);
+    }
+    cudaFree(d_tot);
+    blockCnt.release();
+    if (!ok) return B2RF_ERR_CUDA;
+  }
   if (!t->dn.ensure((size_t)t->nodeStride * t->T)) return B2RF_ERR_CUDA;
   if (!t->dNumBins.ensure(t->F) || !t->dIsCat.ensure(t->F)) return B2RF_ERR_CUDA;
   std::vector<int32_t> isCat(t->F);
@@ -380,12 +416,59 @@ int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const
   return B2RF_OK;
 }
 
+// Uploads the queued node-table changes (and new categorical masks) and applies them with one scatter launch.
+static int flush_node_updates(b2rf_trainer* t, cudaStream_t s) {
+  {  // one scatter launch must not carry two records for the same node: keep the latest
+    std::unordered_map<int64_t, size_t> last;
+    last.reserve(t->pending.size() * 2);
+    size_t w = 0;
+    for (size_t i = 0; i < t->pending.size(); i++) {
+      auto it = last.find(t->pending[i].pos);
+      if (it == last.end()) { last.emplace(t->pending[i].pos, w); t->pending[w++] = t->pending[i]; }
+      else t->pending[it->second] = t->pending[i];
+    }
+    t->pending.resize(w);
+  }
+  const size_t nUpd = t->pending.size();
+  bool ok = true;
+  if (nUpd) {
+    if (!t->hUpd.ensure(nUpd) || !t->dnUpd.ensure(nUpd)) return B2RF_ERR_CUDA;
+    memcpy(t->hUpd.p, t->pending.data(), nUpd * sizeof(DNodeUpdate));
+    t->pending.clear();
+    ok &= cuda_ok(cudaMemcpyAsync(t->dnUpd.p, t->hUpd.p, nUpd * sizeof(DNodeUpdate), cudaMemcpyHostToDevice, s), "upload node updates");
+    ok &= cuda_ok(launch_scatter_dnodes(t->dn.p, t->dnUpd.p, (int64_t)nUpd, s), "scatter node updates");
+    t->nKernels++;
+  }
+  if (t->catPool.size() > t->catUploaded) {
+    if (t->catPool.size() > t->dCat.cap) {  // grow, keeping old contents
+      DevBuf<uint32_t> nb;
+      if (!nb.ensure(std::max<size_t>(t->catPool.size() * 2, 1024))) return B2RF_ERR_CUDA;
+      cudaStreamSynchronize(s);
+      t->dCat.release(); t->dCat = nb; t->catUploaded = 0;
+    }
+    ok &= cuda_ok(cudaMemcpyAsync(t->dCat.p + t->catUploaded, t->catPool.data() + t->catUploaded, (t->catPool.size() - t->catUploaded) * 4,
+                                  cudaMemcpyHostToDevice, s), "upload cat masks");
+    cudaStreamSynchronize(s);  // catPool is pageable host memory
+    t->catUploaded = t->catPool.size();
+  }
+  return ok ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
 static int grow_node_table(b2rf_trainer* t, int64_t need, cudaStream_t s) {
   int64_t ns = t->nodeStride;
   while (ns < need) ns *= 2;
   cudaStreamSynchronize(s);
+  const int64_t oldStride = t->nodeStride;
   t->nodeStride = ns;
   if (!t->dn.ensure((size_t)ns * t->T)) return B2RF_ERR_CUDA;
+  if (t->segMode) {   // the row segments exist only on the device: copy them into the wider table
+    DevBuf<DSeg> wide;
+    if (!wide.ensure((size_t)ns * t->T)) return B2RF_ERR_CUDA;
+    if (!cuda_ok(launch_regrow_segs(t->dSeg.p, oldStride, wide.p, ns, t->T, s), "regrow segments")) return B2RF_ERR_CUDA;
+    cudaStreamSynchronize(s);
+    t->dSeg.release();
+    t->dSeg = wide;
+  }
   // rebuild every entry from the host trees
   t->pending.clear();
   for (int i = 0; i < t->T; i++)
@@ -468,38 +551,8 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   for (int i = 0; i < t->T; i++) if (treeSeen[i]) t->hTreeIds.p[nTg++] = i;
 
   // ---- uploads ----
-  // one scatter launch must not carry two records for the same node: keep the latest
-  {
-    std::unordered_map<int64_t, size_t> last;
-    last.reserve(t->pending.size() * 2);
-    size_t w = 0;
-    for (size_t i = 0; i < t->pending.size(); i++) {
-      auto it = last.find(t->pending[i].pos);
-      if (it == last.end()) { last.emplace(t->pending[i].pos, w); t->pending[w++] = t->pending[i]; }
-      else t->pending[it->second] = t->pending[i];
-    }
-    t->pending.resize(w);
-  }
-  const size_t nUpd = t->pending.size();
-  if (!t->hUpd.ensure(nUpd) || !t->dnUpd.ensure(nUpd)) return B2RF_ERR_CUDA;
-  memcpy(t->hUpd.p, t->pending.data(), nUpd * sizeof(DNodeUpdate));
-  t->pending.clear();
   bool ok = true;
-  ok &= cuda_ok(cudaMemcpyAsync(t->dnUpd.p, t->hUpd.p, nUpd * sizeof(DNodeUpdate), cudaMemcpyHostToDevice, s), "upload node updates");
-  ok &= cuda_ok(launch_scatter_dnodes(t->dn.p, t->dnUpd.p, (int64_t)nUpd, s), "scatter node updates");
-  t->nKernels += nUpd > 0;
-  if (t->catPool.size() > t->catUploaded) {
-    if (t->catPool.size() > t->dCat.cap) {  // grow, keeping old contents
-      DevBuf<uint32_t> nb;
-      if (!nb.ensure(std::max<size_t>(t->catPool.size() * 2, 1024))) return B2RF_ERR_CUDA;
-      cudaStreamSynchronize(s);
-      t->dCat.release(); t->dCat = nb; t->catUploaded = 0;
-    }
-    ok &= cuda_ok(cudaMemcpyAsync(t->dCat.p + t->catUploaded, t->catPool.data() + t->catUploaded, (t->catPool.size() - t->catUploaded) * 4,
-                                  cudaMemcpyHostToDevice, s), "upload cat masks");
-    cudaStreamSynchronize(s);  // catPool is pageable host memory
-    t->catUploaded = t->catPool.size();
-  }
+  { const int rc = flush_node_updates(t, s); if (rc) return rc; }
   ok &= cuda_ok(cudaMemcpyAsync(t->dSlotFo.p, t->hSlotFo.p, nSlots * t->Fsub * sizeof(uint2), cudaMemcpyHostToDevice, s), "upload slot_fo");
   ok &= cuda_ok(cudaMemcpyAsync(t->dSlotBase.p, t->hSlotBase.p, nSlots * 8, cudaMemcpyHostToDevice, s), "upload slot_base");
   ok &= cuda_ok(cudaMemcpyAsync(t->dParent.p, t->hParent.p, nSlots * 32, cudaMemcpyHostToDevice, s), "upload parent stats");
@@ -516,12 +569,18 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   a.n_rows = t->nLocal; a.dnodes = t->dn.p; a.nodeStride = t->nodeStride; a.catmasks = t->dCat.p;
   a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.hist = t->d_hist; a.slot_count = nullptr;
   if (t->bucketMode) {
-    // counting sort of the group's rows by slot, then shared-memory histograms per (slot, chunk)
+    // shared-memory histograms per (slot, chunk).  Segment mode: every pending node already owns a contiguous row segment
+    // (kept by the stable partitions launched from end_group).  Sort mode: counting sort of the group's rows by slot.
     int64_t listCap = 0;
     for (int i = 0; i < nTg; i++) listCap += t->inBag[t->hTreeIds.p[i]];
     int32_t maxCells = 0;
-    if (!t->hSlotCells.ensure(nSlots) || !t->dSlotCells.ensure(nSlots) || !t->dSlotCount.ensure(nSlots) || !t->dCursor.ensure(nSlots) ||
-        !t->dChunkPrefix.ensure(nSlots + 1) || !t->dSlotStart.ensure(nSlots + 1) || !t->dRowList.ensure((size_t)std::max<int64_t>(listCap, 1)))
+    if (!t->hSlotCells.ensure(nSlots) || !t->dSlotCells.ensure(nSlots) || !t->dChunkPrefix.ensure(nSlots + 1)) return B2RF_ERR_CUDA;
+    if (t->segMode) {
+      if (!t->hSlotPos.ensure(nSlots) || !t->dSlotPos.ensure(nSlots)) return B2RF_ERR_CUDA;
+      for (size_t sl = 0; sl < nSlots; sl++) t->hSlotPos.p[sl] = (int64_t)t->group[sl].tree * t->nodeStride + t->group[sl].nidx;
+      ok &= cuda_ok(cudaMemcpyAsync(t->dSlotPos.p, t->hSlotPos.p, nSlots * 8, cudaMemcpyHostToDevice, s), "upload slot positions");
+    } else if (!t->dSlotCount.ensure(nSlots) || !t->dCursor.ensure(nSlots) || !t->dSlotStart.ensure(nSlots + 1) ||
+               !t->dRowList.ensure((size_t)std::max<int64_t>(listCap, 1)))
       return B2RF_ERR_CUDA;
     for (size_t sl = 0; sl < nSlots; sl++) {
       int32_t c = 0;
@@ -531,17 +590,26 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     }
     if ((size_t)maxCells * 20 + 16 > (size_t)220 * 1024) maxCells = (int32_t)(((size_t)220 * 1024 - 16) / 20);   // larger slots take the direct path
     ok &= cuda_ok(cudaMemcpyAsync(t->dSlotCells.p, t->hSlotCells.p, nSlots * 4, cudaMemcpyHostToDevice, s), "upload slot cells");
-    ok &= cuda_ok(cudaMemsetAsync(t->dSlotCount.p, 0, nSlots * 4, s), "zero slot counts");
+    if (!t->segMode) ok &= cuda_ok(cudaMemsetAsync(t->dSlotCount.p, 0, nSlots * 4, s), "zero slot counts");
     if (!ok) return B2RF_ERR_CUDA;
     a.tree_ids = t->dTreeIds.p; a.Tg = nTg; a.slot_count = t->dSlotCount.p;
     BucketLaunch b;
     b.bins_rm = t->d_bins_rm; b.ldr = t->ldr; b.y = t->d_y; b.rowlist = t->dRowList.p; b.slot_start = t->dSlotStart.p; b.slot_count = t->dSlotCount.p;
-    b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->chunkRows; b.slot_fo = t->dSlotFo.p; b.slot_base = t->dSlotBase.p;
-    b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.hist = t->d_hist;
+    b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->segMode ? SEG_CH : t->chunkRows; b.slot_fo = t->dSlotFo.p;
+    b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.hist = t->d_hist;
+    b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr;
     std::string err;
-    cudaError_t e = launch_bucket_pipeline(a, b, t->dCursor.p, s, &err);
-    if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "bucket pipeline launch"); return B2RF_ERR_CUDA; }
-    t->nHistLaunches++; t->nKernels += 4;
+    cudaError_t e;
+    if (t->segMode) {
+      b.dseg = t->dSeg.p; b.slot_pos = t->dSlotPos.p; b.idx0 = t->dIdx0.p; b.idx1 = t->dIdx1.p;
+      e = launch_segment_hist(b, s);
+      t->nKernels += 2;
+    } else {
+      e = launch_bucket_pipeline(a, b, t->dCursor.p, s, &err);
+      t->nKernels += 4;
+    }
+    if (e != cudaSuccess) { if (!err.empty()) set_error(err); else cuda_ok(e, "histogram launch"); return B2RF_ERR_CUDA; }
+    t->nHistLaunches++;
     t->nScanned += (int64_t)nTg * t->nLocal;
     t->histAlgBytes += (double)t->nLocal * ((double)t->F + 8.0 + 3.0 * nTg) + 20.0 * (double)cells;
   } else {
@@ -590,6 +658,8 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   std::vector<std::vector<int>> slotsOfTree(t->T);
   for (size_t sl = 0; sl < nSlots; sl++) slotsOfTree[t->group[sl].tree].push_back((int)sl);
   int64_t needStride = t->nodeStride;
+  std::vector<std::pair<int32_t, std::pair<int32_t, int32_t>>> splits;   // (tree, (node, left child)) of the nodes split in this group
+  int64_t splitRowsBound = 0;
   for (int tr : order) {
     std::vector<HNode>& nodes = t->trees[tr];
     for (int sl : slotsOfTree[tr]) {
@@ -622,12 +692,35 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
         t->pending.push_back({(int64_t)tr * t->nodeStride + li + 1, t->mirror(tr, li + 1, rLeaf ? SLOT_DEAD : SLOT_PENDING)});
         if (!lLeaf) t->stack.push_back({tr, li});
         if (!rLeaf) t->stack.push_back({tr, li + 1});
+        if (!lLeaf || !rLeaf) splits.push_back({tr, {ni, li}});   // children that are both leaves never need their rows again
       } else {
         t->pending.push_back({(int64_t)tr * t->nodeStride + ni, t->mirror(tr, ni, SLOT_DEAD)});
       }
     }
   }
   if (needStride > t->nodeStride) { const int rc = grow_node_table(t, needStride, s); if (rc) return rc; }
+  if (t->segMode && !splits.empty()) {
+    // K6 in segment mode: stable partition of every split node's row segment into its children's segments
+    { const int rc = flush_node_updates(t, s); if (rc) return rc; }   // the partition kernels read the parents' split descriptors
+    const size_t k = splits.size();
+    std::vector<char> seen(t->T, 0);
+    for (auto& sp : splits) if (!seen[sp.first]) { seen[sp.first] = 1; splitRowsBound += t->inBag[sp.first]; }
+    const size_t maxTasks = (size_t)(splitRowsBound / SEG_CH) + k + 1;
+    if (!t->hSplitPos.ensure(2 * k) || !t->dSplitPos.ensure(2 * k) || !t->dPartPrefix.ensure(k + 1) || !t->dLeftCnt.ensure(maxTasks) ||
+        !t->dLeftOff.ensure(maxTasks) || !t->dPredBits.ensure(maxTasks * (SEG_CH / 32)))
+      return B2RF_ERR_CUDA;
+    for (size_t i = 0; i < k; i++) {
+      t->hSplitPos.p[i] = (int64_t)splits[i].first * t->nodeStride + splits[i].second.first;
+      t->hSplitPos.p[k + i] = (int64_t)splits[i].first * t->nodeStride + splits[i].second.second;
+    }
+    if (!cuda_ok(cudaMemcpyAsync(t->dSplitPos.p, t->hSplitPos.p, 2 * k * 8, cudaMemcpyHostToDevice, s), "upload split list")) return B2RF_ERR_CUDA;
+    PartLaunch pl;
+    pl.split_pos = t->dSplitPos.p; pl.nSplits = (int32_t)k; pl.dnodes = t->dn.p; pl.dseg = t->dSeg.p; pl.catmasks = t->dCat.p;
+    pl.bins = t->d_bins; pl.ldb = t->ldb; pl.idx0 = t->dIdx0.p; pl.idx1 = t->dIdx1.p; pl.chunk_prefix = t->dPartPrefix.p;
+    pl.left_cnt = t->dLeftCnt.p; pl.left_off = t->dLeftOff.p; pl.predbits = t->dPredBits.p;
+    if (!cuda_ok(launch_partition(pl, s), "partition launch")) return B2RF_ERR_CUDA;
+    t->nKernels += 4;
+  }
   t->inGroup = false;
   t->groupNo++;
   t->exported = false;

@@ -160,7 +160,7 @@ def default_partitions(n_rows: int, rows_per_partition: int = 4096):
 
 
 def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, part_offsets=None, part0: int = None, group=None,
-                keep_trace: bool = False, prebinned=None, hist_mode: str = "bucket") -> Forest:
+                keep_trace: bool = False, prebinned=None, hist_mode: str = "segment") -> Forest:
     """Train a forest on this rank's rows.
 
     X: f64 [n_local, F] CUDA, row-major (the VectorAssembler `features` column); y: f64 [n_local];
@@ -168,7 +168,8 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
     part_offsets: local row offsets of the emulated Spark partitions (bagging streams are seeded per partition, A.4);
     part0: global index of this rank's first partition (default: partitions are numbered rank-major).
     With torch.distributed initialised, rows are sharded over ranks and only per-group histograms are all-reduced.
-    hist_mode: "bucket" (default: rows bucketed by node, shared-memory histograms) or "scan" (column-major scan + global RED).
+    hist_mode: "segment" (default: per-tree row lists kept partitioned by node, shared-memory histograms), "sort" (rows
+    bucketed by a per-group counting sort, same histogram kernel) or "scan" (column-major scan + global RED).
     """
     _require_cuda(X, "X")
     _require_cuda(y, "y")
@@ -189,6 +190,7 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
             raise ValueError("part_offsets must start at 0 and end at the local row count")
         N, row0, part0 = global_numbering(n_local, len(po) - 1, dist, group, dev, part0)
         cp = params.to_c(F)
+        cp.histMode = {"segment": 0, "bucket": 0, "sort": 1, "scan": 2}[hist_mode]
         meta_max_bins = check(L.b2rf_check_metadata(C.byref(cp), F, arity_np.ctypes.data_as(C.c_void_p), N))
         mpb = min(params.maxBins, N)
         T = params.numTrees

@@ -16,13 +16,14 @@ def _airbnb(b2rf, n=7146, seed=42):
     return X[:ntr].numpy(), y[:ntr].numpy(), X[ntr:].numpy(), y[ntr:].numpy(), arity
 
 
-@pytest.fixture(params=["bucket", "scan"])
+@pytest.fixture(params=["segment", "sort", "scan"])
 def mode(request):
-    """Both K4 implementations: rows bucketed by node + shared-memory histograms, and column-major scan + global RED."""
+    """All K4 implementations: node-partitioned row lists / per-group counting sort (both + shared-memory histograms), and
+    column-major scan + global RED."""
     return request.param
 
 
-def _fit_both(b2rf, oracle, cuda, X, y, arity, part_offsets=None, hist_mode="bucket", **kw):
+def _fit_both(b2rf, oracle, cuda, X, y, arity, part_offsets=None, hist_mode="segment", **kw):
     from b2rf import trainer
     p = b2rf.TreeParams(**kw)
     if part_offsets is None:
