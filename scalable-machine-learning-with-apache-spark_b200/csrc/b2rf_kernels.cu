@@ -327,15 +327,21 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
     const int ncell = a.slot_cells[slot];
     const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
     double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
-    const bool direct = (int64_t)n * a.Fsub < (int64_t)ncell || ncell > a.maxCells;   // few rows: skip the shared-memory round trip
+    // Shared layout.  padded (padB > 0): cell (feature j, bin b) sits at ((j/32)*padB + b)*32 + j%32, i.e. bank == lane: the
+    // lanes of a warp (lane == feature) can never conflict, whatever their bins.  compact: cell = feature offset + bin.
+    const int padB = a.padB;
+    const int scells = padB > 0 ? ((a.Fsub + 31) / 32) * padB * 32 : ncell;
+    const bool direct = (int64_t)n * a.Fsub < (int64_t)ncell || scells > a.maxCells;   // few rows: skip the shared-memory round trip
     if (!direct) {
-      for (int c = tid; c < ncell; c += BUCKET_THREADS) { ssum[c] = 0.0; ssq[c] = 0.0; scnt[c] = 0u; }
+      for (int c = tid; c < scells; c += BUCKET_THREADS) { ssum[c] = 0.0; ssq[c] = 0.0; scnt[c] = 0u; }
       __syncthreads();
     }
     for (int j0 = 0; j0 < a.Fsub; j0 += 32) {
       const int j = j0 + lane;
       const bool active = j < a.Fsub;
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
+      const uint32_t sbase = padB > 0 ? (uint32_t)((j0 >> 5) * padB * 32 + lane) : e.y;   // shared-memory cell of bin 0
+      const uint32_t sstep = padB > 0 ? 32u : 1u;
       for (int base = warp * 32; base < n; base += W * 32) {
         const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;
         const int nb = min(32, n - base);
@@ -354,7 +360,7 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
           for (int u = 0; u < 4; u++) {
             if (wv[u] != 0u && active) {
               if (direct) bucket_update<true>(hb, ssum, ssq, scnt, e.y + bin[u], wv[u], yv[u]);
-              else bucket_update<false>(hb, ssum, ssq, scnt, e.y + bin[u], wv[u], yv[u]);
+              else bucket_update<false>(hb, ssum, ssq, scnt, sbase + bin[u] * sstep, wv[u], yv[u]);
             }
           }
         }
@@ -362,9 +368,13 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
     }
     if (!direct) {
       __syncthreads();
-      for (int c = tid; c < ncell; c += BUCKET_THREADS) {
+      for (int c = tid; c < scells; c += BUCKET_THREADS) {
         const unsigned k = scnt[c];
-        if (k) { double* g = hb + (size_t)c * 4; atomicAdd(g, (double)k); atomicAdd(g + 1, ssum[c]); atomicAdd(g + 2, ssq[c]); }
+        if (!k) continue;
+        size_t gc = (size_t)c;
+        if (padB > 0) { const int jj = (c / (padB * 32)) * 32 + (c & 31); gc = (size_t)fo[jj].y + (size_t)((c >> 5) % padB); }   // untouched cells of idle lanes stay 0
+        double* g = hb + gc * 4;
+        atomicAdd(g, (double)k); atomicAdd(g + 1, ssum[c]); atomicAdd(g + 2, ssq[c]);
       }
       __syncthreads();
     }
