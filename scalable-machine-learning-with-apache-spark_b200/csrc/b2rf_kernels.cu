@@ -958,7 +958,18 @@ constexpr int BAG_THREADS = 64;
 struct Well19937cSm {
   uint32_t* v;   // &state[0][threadIdx.x]; word w is v[w * BAG_THREADS]
   int index;
+  // The recurrence's loop-carried values stay in registers: c0 = v[index] (the z4 of the previous step) and cTop = the word
+  // whose top bit feeds z0.  Of the three words a step writes, two are overwritten before anything reads them, so only z3
+  // is stored; the four old words a step needs are fetched one step ahead (p*), off the dependent chain.
+  uint32_t c0, cTop, pM1, pM2, pM3, pR2;
   __device__ __forceinline__ uint32_t& at(int w) { return v[w * BAG_THREADS]; }
+  __device__ __forceinline__ void prefetch() {
+    int i1 = index + 70; if (i1 >= 624) i1 -= 624;
+    int i2 = index + 179; if (i2 >= 624) i2 -= 624;
+    int i3 = index + 449; if (i3 >= 624) i3 -= 624;
+    int r2 = index - 2; if (r2 < 0) r2 += 624;
+    pM1 = at(i1); pM2 = at(i2); pM3 = at(i3); pR2 = at(r2);
+  }
   __device__ void seed(int64_t sd) {
     uint32_t a = (uint32_t)((uint64_t)sd >> 32), b = (uint32_t)((uint64_t)sd & 0xffffffffULL);
     at(0) = a; at(1) = b;
@@ -969,25 +980,21 @@ struct Well19937cSm {
       a = b; b = c;
     }
     index = 0;
+    c0 = at(0); cTop = at(623);
+    prefetch();
   }
   __device__ __forceinline__ uint32_t next(int bits) {
-    const int i0 = index;
-    const int iRm1 = i0 == 0 ? 623 : i0 - 1;
-    const int iRm2 = iRm1 == 0 ? 623 : iRm1 - 1;
-    int i1 = i0 + 70; if (i1 >= 624) i1 -= 624;
-    int i2 = i0 + 179; if (i2 >= 624) i2 -= 624;
-    int i3 = i0 + 449; if (i3 >= 624) i3 -= 624;
-    const uint32_t v0 = at(i0), vM1 = at(i1), vM2 = at(i2), vM3 = at(i3);
-    const uint32_t vR1 = at(iRm1), vR2 = at(iRm2);
-    const uint32_t z0 = (0x80000000u & vR1) ^ (0x7FFFFFFFu & vR2);
+    const uint32_t v0 = c0, vM1 = pM1, vM2 = pM2, vM3 = pM3, vR2 = pR2;
+    const uint32_t z0 = (0x80000000u & cTop) ^ (0x7FFFFFFFu & vR2);
     const uint32_t z1 = (v0 ^ (v0 << 25)) ^ (vM1 ^ (vM1 >> 27));
     const uint32_t z2 = (vM2 >> 9) ^ (vM3 ^ (vM3 >> 1));
     const uint32_t z3 = z1 ^ z2;
     uint32_t z4 = z0 ^ (z1 ^ (z1 << 9)) ^ (z2 ^ (z2 << 21)) ^ (z3 ^ (z3 >> 21));
-    at(i0) = z3;
-    at(iRm1) = z4;
-    at(iRm2) = vR2 & 0x80000000u;
-    index = iRm1;
+    at(index) = z3;               // v[index-1] = z4 and v[index-2] &= 0x80000000 are dead stores: both words are rewritten
+    c0 = z4;                      // (as z3 of the next two steps) before they are read from memory
+    cTop = vR2;
+    index = index == 0 ? 623 : index - 1;
+    prefetch();
     z4 ^= (z4 << 7) & 0xe46e1700u;
     z4 ^= (z4 << 15) & 0x9b868000u;
     return z4 >> (32 - bits);
@@ -1042,14 +1049,27 @@ __global__ void __launch_bounds__(BAG_THREADS) bag_kernel(int64_t seed, const in
     rng.v = bag_state + threadIdx.x;
     rng.seed(seed + (int64_t)(part0 + p) + 1);
     const double lim = 1000 * rate;
-    for (int64_t i = r0; i < r1; i++)
-      for (int t = 0; t < T; t++) {
-        long n = 0; double r = 1.0;
-        while ((double)n < lim) { r *= rng.nextDouble(); if (r >= expNegRate) n++; else break; }
+    // One uniform per loop trip for every lane: PoissonDistribution.sample() consumes a data-dependent number of uniforms, and
+    // a per-sample inner loop would make each warp pay for its slowest lane on every sample.  Flattened, lanes only diverge
+    // on the short "sample finished" branch.
+    int64_t i = r0;
+    int t = 0;
+    long n = 0;
+    double r = 1.0;
+    while (i < r1) {
+      bool finished = true;
+      if ((double)n < lim) {
+        r *= rng.nextDouble();
+        if (r >= expNegRate) { n++; finished = false; }
+      }
+      if (finished) {
         const int c = n > 255 ? 255 : (int)n;
         w[(size_t)t * ldw + i] = (uint8_t)c;
-        node[(size_t)t * ldn + i] = c > 0 ? 0 : -1;
+        if (node != nullptr) node[(size_t)t * ldn + i] = c > 0 ? 0 : -1;
+        n = 0; r = 1.0;
+        if (++t == T) { t = 0; i++; }
       }
+    }
   } else if (mode == 1) {
     XorShiftDev rng;
     rng.seed(seed + (int64_t)(part0 + p) + 1);
@@ -1057,14 +1077,14 @@ __global__ void __launch_bounds__(BAG_THREADS) bag_kernel(int64_t seed, const in
       for (int t = 0; t < T; t++) {
         const int c = rng.nextDouble() < rate ? 1 : 0;
         w[(size_t)t * ldw + i] = (uint8_t)c;
-        node[(size_t)t * ldn + i] = c > 0 ? 0 : -1;
+        if (node != nullptr) node[(size_t)t * ldn + i] = c > 0 ? 0 : -1;
       }
   }
 }
 __global__ void bag_ones_kernel(int64_t n, int T, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
-  for (int t = 0; t < T; t++) { w[(size_t)t * ldw + i] = 1; node[(size_t)t * ldn + i] = 0; }
+  for (int t = 0; t < T; t++) { w[(size_t)t * ldw + i] = 1; if (node != nullptr) node[(size_t)t * ldn + i] = 0; }
 }
 
 // =================================================================================================
