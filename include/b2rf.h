@@ -97,7 +97,8 @@ int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const do
 
 /* ---- K3: BaggedPoint.convertToBaggedRDD (row a4) ------------------------------------------------------------- */
 /* One emulated Spark partition per thread: partition p (global index part0 + p) covers local rows
- * [h_part_offsets[p], h_part_offsets[p+1]).  Writes d_w[t][row] and the initial d_node[t][row] (0 if w > 0 else -1). */
+ * [h_part_offsets[p], h_part_offsets[p+1]).  Writes d_w[t][row] and, when d_node is not NULL, the initial d_node[t][row]
+ * (0 if w > 0 else -1; only the sort / scan histogram modes need it). */
 int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t part0, int32_t T, double subsamplingRate,
              int32_t bootstrap, uint8_t* d_w, int64_t ldw, int32_t* d_node, int64_t ldn, void* stream);
 

@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -126,29 +127,69 @@ inline int level_of(int id) { return 31 - __builtin_clz((unsigned)id); }
 inline double vimp(const double* c) { if (c[0] == 0) return 0; const double sl = c[2] - (c[1] * c[1]) / c[0]; return sl / c[0]; }
 inline double vpred(const double* c) { return c[0] == 0 ? 0.0 : c[1] / c[0]; }
 
+// Library-owned scratch comes from two small process-wide pools (device memory / pinned host memory): a fit allocates dozens
+// of descriptor buffers, and cudaMalloc / cudaMallocHost / cudaFree each cost 0.1-10 ms and synchronise the device, which
+// would otherwise be paid again by every fit (CrossValidator runs many).  Blocks return to the pool when a trainer dies.
+struct BlockPool {
+  struct Block { void* p; size_t bytes; int dev; };   // device blocks are only reused on the device that owns them
+  std::mutex mu;
+  std::vector<Block> free_;
+  bool pinned;
+  explicit BlockPool(bool pin) : pinned(pin) {}
+  static int current_device() { int d = 0; cudaGetDevice(&d); return d; }
+  void* take(size_t bytes, size_t* got) {
+    const int dev = pinned ? -1 : current_device();
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      int best = -1;
+      for (int i = 0; i < (int)free_.size(); i++)
+        if (free_[i].dev == dev && free_[i].bytes >= bytes && free_[i].bytes <= bytes * 4 + 4096 && (best < 0 || free_[i].bytes < free_[best].bytes)) best = i;
+      if (best >= 0) { Block b = free_[best]; free_.erase(free_.begin() + best); *got = b.bytes; return b.p; }
+    }
+    void* p = nullptr;
+    const cudaError_t e = pinned ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
+    if (!cuda_ok(e, pinned ? "trainer pinned alloc" : "trainer device alloc")) return nullptr;
+    *got = bytes;
+    return p;
+  }
+  void give(void* p, size_t bytes) {
+    if (!p) return;
+    std::lock_guard<std::mutex> lk(mu);
+    const int dev = pinned ? -1 : current_device();
+    if (free_.size() >= 96) { if (pinned) cudaFreeHost(p); else cudaFree(p); return; }
+    free_.push_back({p, bytes, dev});
+  }
+};
+BlockPool& device_pool() { static BlockPool* p = new BlockPool(false); return *p; }
+BlockPool& pinned_pool() { static BlockPool* p = new BlockPool(true); return *p; }
+
 template <class T> struct DevBuf {
-  T* p = nullptr; size_t cap = 0;
+  T* p = nullptr; size_t cap = 0; size_t bytes = 0;
   bool ensure(size_t n) {
     if (n <= cap) return true;
-    size_t nc = std::max(n, cap * 2);
-    if (p) cudaFree(p);
-    p = nullptr; cap = 0;
-    if (!cuda_ok(cudaMalloc((void**)&p, nc * sizeof(T)), "trainer device alloc")) return false;
-    cap = nc; return true;
+    const size_t nc = std::max(n, cap * 2);
+    device_pool().give(p, bytes);
+    p = nullptr; cap = 0; bytes = 0;
+    size_t got = 0;
+    void* q = device_pool().take(nc * sizeof(T), &got);
+    if (!q) return false;
+    p = static_cast<T*>(q); bytes = got; cap = got / sizeof(T); return true;
   }
-  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  void release() { device_pool().give(p, bytes); p = nullptr; cap = 0; bytes = 0; }
 };
 template <class T> struct PinBuf {
-  T* p = nullptr; size_t cap = 0;
+  T* p = nullptr; size_t cap = 0; size_t bytes = 0;
   bool ensure(size_t n) {
     if (n <= cap) return true;
-    size_t nc = std::max(n, cap * 2);
-    if (p) cudaFreeHost(p);
-    p = nullptr; cap = 0;
-    if (!cuda_ok(cudaMallocHost((void**)&p, nc * sizeof(T)), "trainer pinned alloc")) return false;
-    cap = nc; return true;
+    const size_t nc = std::max(n, cap * 2);
+    pinned_pool().give(p, bytes);
+    p = nullptr; cap = 0; bytes = 0;
+    size_t got = 0;
+    void* q = pinned_pool().take(nc * sizeof(T), &got);
+    if (!q) return false;
+    p = static_cast<T*>(q); bytes = got; cap = got / sizeof(T); return true;
   }
-  void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
+  void release() { pinned_pool().give(p, bytes); p = nullptr; cap = 0; bytes = 0; }
 };
 
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
@@ -353,7 +394,7 @@ int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t) {
 
 int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const uint8_t* d_bins_rm, int64_t ldr, const double* d_y,
                       const uint8_t* d_w, int64_t ldw, int32_t* d_node, int64_t ldn, int64_t n_rows_local, double* d_hist, int64_t hist_cells) {
-  if (!t || !d_bins || !d_y || !d_w || !d_node || !d_hist || n_rows_local < 0 || (ldb & 15) || ldb < n_rows_local || ldw < n_rows_local || ldn < n_rows_local) {
+  if (!t || !d_bins || !d_y || !d_w || !d_hist || n_rows_local < 0 || (ldb & 15) || ldb < n_rows_local || ldw < n_rows_local || (d_node && ldn < n_rows_local)) {
     set_error("b2rf_trainer_bind: bad argument (ldb must be a multiple of 16 and every leading dimension >= n_rows)"); return B2RF_ERR_ARG;
   }
   t->d_bins = d_bins; t->ldb = ldb; t->d_y = d_y; t->d_w = d_w; t->ldw = ldw; t->d_node = d_node; t->ldn = ldn; t->nLocal = n_rows_local;
@@ -371,6 +412,7 @@ int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const
   // device node table: one stride per tree
   const int64_t full = (int64_t)1 << std::min(t->p.maxDepth + 1, 17);
   t->nodeStride = full;
+  if (!t->segMode && d_node == nullptr) { set_error("b2rf_trainer_bind: d_node is required unless the segment histogram mode is used"); return B2RF_ERR_ARG; }
   if (t->bucketMode) {
     // in-bag rows per tree; in segment mode also the initial row lists (ascending rows, packed row | weight << 27)
     const int nb = (int)((n_rows_local + COMPACT_ROWS - 1) / COMPACT_ROWS);

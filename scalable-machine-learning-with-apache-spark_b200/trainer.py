@@ -96,16 +96,17 @@ def bin_features(X: torch.Tensor, thresholds: torch.Tensor, nsplits: torch.Tenso
     return bins
 
 
-def bag(seed: int, part_offsets, part0: int, T: int, rate: float, bootstrap: bool, device, ld: int = None):
-    """K3.  Returns (w uint8 [T, ld], node int32 [T, ld])."""
+def bag(seed: int, part_offsets, part0: int, T: int, rate: float, bootstrap: bool, device, ld: int = None, want_node: bool = True):
+    """K3.  Returns (w uint8 [T, ld], node int32 [T, ld] or None).  The per-row node cache is only needed by the "sort" and
+    "scan" histogram modes; segment mode keeps per-tree row lists instead."""
     po = np.ascontiguousarray(part_offsets, np.int64)
     n = int(po[-1])
     ld = ld or _pad(n)
     w = torch.zeros((T, ld), dtype=torch.uint8, device=device)
-    node = torch.full((T, ld), -1, dtype=torch.int32, device=device)
+    node = torch.full((T, ld), -1, dtype=torch.int32, device=device) if want_node else None
     with torch.cuda.device(device):
         check(lib().b2rf_bag(int(seed), po.ctypes.data_as(C.c_void_p), len(po) - 1, int(part0), T, float(rate), int(bool(bootstrap)),
-                             w.data_ptr(), w.stride(0), node.data_ptr(), node.stride(0), _stream()))
+                             w.data_ptr(), w.stride(0), 0 if node is None else node.data_ptr(), ld if node is None else node.stride(0), _stream()))
     return w, node
 
 
@@ -219,7 +220,8 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
             bins = torch.empty((F, ld), dtype=torch.uint8, device=dev)
             bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=torch.uint8, device=dev) if hist_mode != "scan" else None
             bin_features(X, thr, ns, arity_d, bins=bins, row0=0, bins_rm=bins_rm)
-        w, node = bag(params.seed, po, part0, T, params.subsamplingRate, params.bootstrap, dev, ld=ld)
+        w, node = bag(params.seed, po, part0, T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
+                      want_node=(hist_mode not in ("segment", "bucket") or bins_rm is None))
         torch.cuda.synchronize(dev)
         t2 = time.perf_counter()
 
@@ -231,8 +233,9 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
             cells = int(L.b2rf_trainer_max_group_cells(h))
             hist = torch.empty(cells * 4, dtype=torch.float64, device=dev)
             check(L.b2rf_trainer_bind(h, bins.data_ptr(), bins.stride(0), 0 if bins_rm is None else bins_rm.data_ptr(),
-                                      0 if bins_rm is None else bins_rm.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0), node.data_ptr(),
-                                      node.stride(0), n_local, hist.data_ptr(), cells))
+                                      0 if bins_rm is None else bins_rm.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0),
+                                      0 if node is None else node.data_ptr(), ld if node is None else node.stride(0), n_local,
+                                      hist.data_ptr(), cells))
             ncell = C.c_int64()
             st = _stream()
             t_comm = 0.0
