@@ -286,16 +286,44 @@ __global__ void __launch_bounds__(256) scatter_rows_kernel(const int32_t* node, 
 }
 
 constexpr int BUCKET_THREADS = 256;
+// Rows [0, n) of one (slot, chunk) task, one warp row-block at a time.  Lane k of a warp owns row k of the current 32-row
+// block: it fetches the packed entry and the label once and forms (w, w*y, w*y*y); the values are then broadcast row by row
+// while every lane (== feature) gathers its own bin code and updates its own histogram column.
 template <bool DIRECT>
-__device__ __forceinline__ void bucket_update(double* hb, double* ssum, double* ssq, unsigned* scnt, uint32_t cell, uint32_t w, double yv) {
-  const double dw = (double)w;
-  const double wy = dw * yv;
-  const double wyy = wy * yv;
-  if (DIRECT) {
-    double* c = hb + (size_t)cell * 4;
-    atomicAdd(c, dw); atomicAdd(c + 1, wy); atomicAdd(c + 2, wyy);
-  } else {
-    atomicAdd(&scnt[cell], w); atomicAdd(&ssum[cell], wy); atomicAdd(&ssq[cell], wyy);
+__device__ __forceinline__ void bucket_rows(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
+                                            double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep) {
+  constexpr int W = BUCKET_THREADS / 32;
+  const unsigned FULL = 0xffffffffu;
+  for (int base = warp * 32; base < n; base += W * 32) {
+    const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;          // w == 0 marks padding
+    const uint32_t myw = mine >> 27;
+    const double myy = myw ? a.y[mine & 0x7ffffffu] : 0.0;
+    const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
+    const double mywyy = mywy * myy;
+    const int nb = min(32, n - base);
+    for (int q = 0; q < nb; q += 4) {
+      uint32_t bin[4], wv[4]; double wy[4], wyy[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const uint32_t p = __shfl_sync(FULL, mine, (q + u) & 31);
+        wy[u] = __shfl_sync(FULL, mywy, (q + u) & 31);
+        wyy[u] = __shfl_sync(FULL, mywyy, (q + u) & 31);
+        wv[u] = (q + u) < nb ? (p >> 27) : 0u;
+        bin[u] = (wv[u] && active) ? a.bins_rm[(size_t)(p & 0x7ffffffu) * a.ldr + featCol] : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        if (wv[u] != 0u && active) {
+          if (DIRECT) {
+            double* c = hb + (size_t)(gbase + bin[u]) * 4;
+            atomicAdd(c, (double)wv[u]); atomicAdd(c + 1, wy[u]); atomicAdd(c + 2, wyy[u]);
+          } else {
+            const uint32_t cell = sbase + bin[u] * sstep;
+            atomicAdd(&scnt[cell], wv[u]); atomicAdd(&ssum[cell], wy[u]); atomicAdd(&ssq[cell], wyy[u]);
+          }
+        }
+      }
+    }
   }
 }
 
@@ -305,8 +333,6 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
   double* ssq = ssum + a.maxCells;
   unsigned* scnt = reinterpret_cast<unsigned*>(ssq + a.maxCells);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  constexpr int W = BUCKET_THREADS / 32;
-  const unsigned FULL = 0xffffffffu;
   const uint32_t total = a.chunk_prefix[a.nSlots];
   for (uint32_t task = blockIdx.x; task < total; task += gridDim.x) {
     int lo = 0, hi = a.nSlots;
@@ -342,29 +368,8 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
       const uint32_t sbase = padB > 0 ? (uint32_t)((j0 >> 5) * padB * 32 + lane) : e.y;   // shared-memory cell of bin 0
       const uint32_t sstep = padB > 0 ? 32u : 1u;
-      for (int base = warp * 32; base < n; base += W * 32) {
-        const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;
-        const int nb = min(32, n - base);
-        for (int q = 0; q < nb; q += 4) {
-          uint32_t bin[4], wv[4]; double yv[4];
-#pragma unroll
-          for (int u = 0; u < 4; u++) {
-            const uint32_t p = __shfl_sync(FULL, mine, (q + u) & 31);
-            const bool valid = (q + u) < nb;
-            const uint32_t row = p & 0x7ffffffu;
-            wv[u] = valid ? (p >> 27) : 0u;
-            bin[u] = (valid && active) ? a.bins_rm[(size_t)row * a.ldr + e.x] : 0u;
-            yv[u] = valid ? a.y[row] : 0.0;
-          }
-#pragma unroll
-          for (int u = 0; u < 4; u++) {
-            if (wv[u] != 0u && active) {
-              if (direct) bucket_update<true>(hb, ssum, ssq, scnt, e.y + bin[u], wv[u], yv[u]);
-              else bucket_update<false>(hb, ssum, ssq, scnt, sbase + bin[u] * sstep, wv[u], yv[u]);
-            }
-          }
-        }
-      }
+      if (direct) bucket_rows<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep);
+      else bucket_rows<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep);
     }
     if (!direct) {
       __syncthreads();
