@@ -69,6 +69,9 @@ double b2rf_samples_fraction(int64_t numExamples, int32_t metaMaxBins);
  * kept rows of X[row0_global + i] (i < n_rows) to d_sample_out [cap][F]; *d_count (device int64, caller-zeroed) counts them. */
 int b2rf_sample_rows(const double* d_X, int64_t ldx, int64_t n_rows, int64_t row0_global, int32_t F, int64_t seed,
                      double fraction, double* d_sample_out, int64_t cap, int64_t* d_count, void* stream);
+/* Host twin of b2rf_sample_rows: the local indices (ascending) of the rows it keeps, so a host-side caller can gather the
+ * sample before any feature data reaches the device.  Returns the number kept (may exceed cap: then only cap are written). */
+int64_t b2rf_sample_indices(int64_t seed, int64_t row0_global, int64_t n_rows, double fraction, int64_t* h_idx_out, int64_t cap);
 size_t b2rf_find_splits_workspace_bytes(int64_t n_sample, int32_t F);
 /* d_sample [n_sample][F]; d_arity[F] (0 = continuous); out: d_thresholds [F][maxPossibleBins-1], d_nsplits[F]. */
 int b2rf_find_splits(const double* d_sample, int64_t n_sample, int32_t F, const int32_t* d_arity, int32_t maxPossibleBins,

@@ -1170,6 +1170,16 @@ int b2rf_sample_rows(const double* d_X, int64_t ldx, int64_t n_rows, int64_t row
   return cuda_ok(cudaGetLastError(), "b2rf_sample_rows") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
+int64_t b2rf_sample_indices(int64_t seed, int64_t row0_global, int64_t n_rows, double fraction, int64_t* h_idx_out, int64_t cap) {
+  const uint64_t seedWord = ((uint64_t)(uint32_t)xorshift_first_int(seed) << 32) | 0x9E3779B9u;
+  int64_t k = 0;
+  for (int64_t i = 0; i < n_rows; i++) {
+    const uint64_t h = mix64(seedWord + (uint64_t)(row0_global + i) * 0x9E3779B97F4A7C15ULL);
+    if (((double)(h >> 11) * 0x1.0p-53) < fraction) { if (k < cap) h_idx_out[k] = i; k++; }
+  }
+  return k;
+}
+
 static int64_t next_pow2(int64_t n) { int64_t p = 1; while (p < n) p <<= 1; return p; }
 
 size_t b2rf_find_splits_workspace_bytes(int64_t n_sample, int32_t F) { return (size_t)next_pow2(n_sample < 2 ? 2 : n_sample) * (size_t)F * 8; }
@@ -1282,8 +1292,7 @@ int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t par
                                                                              bootstrap ? 0 : 1, d_w, ldw, d_node, ldn);
     ok = cuda_ok(cudaGetLastError(), "b2rf_bag");
   }
-  cudaStreamSynchronize(s);  // h_part_offsets may be pageable: finish the copy before returning
-  cudaFreeAsync(d_po, s);
+  cudaFreeAsync(d_po, s);   // stream-ordered.  No host sync: cudaMemcpyAsync from pageable memory stages h_part_offsets before returning
   return ok ? B2RF_OK : B2RF_ERR_CUDA;
 }
 

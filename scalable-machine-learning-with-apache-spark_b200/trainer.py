@@ -73,8 +73,25 @@ def sample_rows(X: torch.Tensor, row0_global: int, seed: int, fraction: float) -
     return out[:k]
 
 
+_bin_err = {}
+
+
+def _raise_bin_errors(arity):
+    """Raises MLlib's invalid-categorical-value error if any K2 launch on this device flagged one (deferred check)."""
+    err = _bin_err.get(arity.device)
+    if err is None:
+        return
+    e = int(err.item())
+    err.zero_()
+    if e:
+        from ._lib import ERR_DATA, IllegalArgumentException
+        f = e - 1
+        raise IllegalArgumentException(ERR_DATA, f"DecisionTree given invalid data: Feature {f} is categorical with values in "
+                                       f"{{0,...,{int(arity[f].item()) - 1}}}, but a data point gives it an out-of-range value.")
+
+
 def bin_features(X: torch.Tensor, thresholds: torch.Tensor, nsplits: torch.Tensor, arity: torch.Tensor, bins: torch.Tensor = None,
-                 row0: int = 0, bins_rm: torch.Tensor = None) -> torch.Tensor:
+                 row0: int = 0, bins_rm: torch.Tensor = None, check_errors: bool = True) -> torch.Tensor:
     """K2.  X f64 [n, F] row-major CUDA -> column-major uint8 bins [F, ldb] (rows row0..row0+n); optionally also the
     row-major twin bins_rm [rows, ldr] that the bucket-mode histogram kernel gathers from."""
     _require_cuda(X, "X")
@@ -83,16 +100,14 @@ def bin_features(X: torch.Tensor, thresholds: torch.Tensor, nsplits: torch.Tenso
         X = X.contiguous()
     if bins is None:
         bins = torch.zeros((F, _pad(row0 + n)), dtype=torch.uint8, device=X.device)
-    err = torch.zeros(1, dtype=torch.int32, device=X.device)
+    err = _bin_err.get(X.device)
+    if err is None:
+        err = _bin_err[X.device] = torch.zeros(1, dtype=torch.int32, device=X.device)
     check(lib().b2rf_bin(X.data_ptr(), X.stride(0), n, F, thresholds.data_ptr(), nsplits.data_ptr(), arity.data_ptr(), thresholds.shape[1],
                          bins.data_ptr(), bins.stride(0), row0, err.data_ptr(), 0 if bins_rm is None else bins_rm.data_ptr(),
                          0 if bins_rm is None else bins_rm.stride(0), _stream()))
-    e = int(err.item())
-    if e:
-        from ._lib import ERR_DATA, IllegalArgumentException
-        f = e - 1
-        raise IllegalArgumentException(ERR_DATA, f"DecisionTree given invalid data: Feature {f} is categorical with values in "
-                                       f"{{0,...,{int(arity[f].item()) - 1}}}, but a data point gives it an out-of-range value.")
+    if check_errors:
+        _raise_bin_errors(arity)
     return bins
 
 
@@ -160,6 +175,60 @@ def default_partitions(n_rows: int, rows_per_partition: int = 4096):
     return np.minimum(np.arange(P + 1, dtype=np.int64) * rows_per_partition, n_rows)
 
 
+_HIST_MODES = {"segment": 0, "bucket": 0, "sort": 1, "scan": 2}
+
+
+def _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode):
+    """Metadata checks and global numbering shared by the device- and host-input entry points (rows a1, e)."""
+    L = lib()
+    arity_np = np.ascontiguousarray(arity, np.int32)
+    if arity_np.shape != (F,):
+        raise ValueError("arity must have one entry per feature")
+    dist, rank, world = _dist_info(group)
+    if part_offsets is None:
+        part_offsets = default_partitions(n_local)
+    po = np.ascontiguousarray(part_offsets, np.int64)
+    if po[0] != 0 or po[-1] != n_local:
+        raise ValueError("part_offsets must start at 0 and end at the local row count")
+    N, row0, part0 = global_numbering(n_local, len(po) - 1, dist, group, dev, part0)
+    cp = params.to_c(F)
+    cp.histMode = _HIST_MODES[hist_mode]
+    meta_max_bins = check(L.b2rf_check_metadata(C.byref(cp), F, arity_np.ctypes.data_as(C.c_void_p), N))
+    fraction = L.b2rf_samples_fraction(N, meta_max_bins)
+    return dict(arity_np=arity_np, dist=dist, world=world, po=po, N=N, row0=row0, part0=part0, cp=cp, mpb=min(params.maxBins, N),
+                fraction=fraction, arity_d=torch.as_tensor(arity_np, device=dev))
+
+
+def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace):
+    """RandomForest.run's while (nodeStack.nonEmpty) loop: one begin_group / [all_reduce] / end_group per node group."""
+    L = lib()
+    dev = y.device
+    h = C.c_void_p()
+    check(L.b2rf_trainer_create(C.byref(S["cp"]), F, S["arity_np"].ctypes.data_as(C.c_void_p), ns_h.ctypes.data_as(C.c_void_p),
+                                thr_h.ctypes.data_as(C.c_void_p), S["N"], C.byref(h)))
+    try:
+        cells = int(L.b2rf_trainer_max_group_cells(h))
+        hist = torch.empty(cells * 4, dtype=torch.float64, device=dev)
+        ld = w.stride(0)
+        check(L.b2rf_trainer_bind(h, bins.data_ptr(), bins.stride(0), 0 if bins_rm is None else bins_rm.data_ptr(),
+                                  0 if bins_rm is None else bins_rm.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0),
+                                  0 if node is None else node.data_ptr(), ld if node is None else node.stride(0), n_local,
+                                  hist.data_ptr(), cells))
+        ncell = C.c_int64()
+        st = _stream()
+        while check(L.b2rf_trainer_begin_group(h, C.byref(ncell), st)) == 1:
+            if S["world"] > 1:
+                S["dist"].all_reduce(hist[: ncell.value * 4], group=group)   # DTStatsAggregator.merge (reduceByKey), row a7
+            check(L.b2rf_trainer_end_group(h, st))
+        torch.cuda.synchronize(dev)
+        forest = _export(h, F, keep_trace)
+    finally:
+        L.b2rf_trainer_destroy(h)
+    forest.thresholds, forest.nsplits = thr_h, ns_h
+    forest.counters.update(rows=S["N"], rows_local=n_local, partitions=len(S["po"]) - 1, world=S["world"], fraction=S["fraction"])
+    return forest
+
+
 def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, part_offsets=None, part0: int = None, group=None,
                 keep_trace: bool = False, prebinned=None, hist_mode: str = "segment") -> Forest:
     """Train a forest on this rank's rows.
@@ -175,38 +244,20 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
     _require_cuda(X, "X")
     _require_cuda(y, "y")
     dev = X.device
-    L = lib()
     t_start = time.perf_counter()
     with torch.cuda.device(dev):
         y = y.to(torch.float64).contiguous()
         n_local, F = X.shape
-        arity_np = np.ascontiguousarray(arity, np.int32)
-        if arity_np.shape != (F,):
-            raise ValueError("arity must have one entry per feature")
-        dist, rank, world = _dist_info(group)
-        if part_offsets is None:
-            part_offsets = default_partitions(n_local)
-        po = np.ascontiguousarray(part_offsets, np.int64)
-        if po[0] != 0 or po[-1] != n_local:
-            raise ValueError("part_offsets must start at 0 and end at the local row count")
-        N, row0, part0 = global_numbering(n_local, len(po) - 1, dist, group, dev, part0)
-        cp = params.to_c(F)
-        cp.histMode = {"segment": 0, "bucket": 0, "sort": 1, "scan": 2}[hist_mode]
-        meta_max_bins = check(L.b2rf_check_metadata(C.byref(cp), F, arity_np.ctypes.data_as(C.c_void_p), N))
-        mpb = min(params.maxBins, N)
+        S = _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode)
         T = params.numTrees
-        arity_d = torch.as_tensor(arity_np, device=dev)
         torch.cuda.synchronize(dev)
         t0 = time.perf_counter()
 
         # ---- findSplits (K1) ----
-        fraction = L.b2rf_samples_fraction(N, meta_max_bins)
-        if fraction < 1.0:
-            samp = sample_rows(X, row0, params.seed, fraction)
-        else:
-            samp = X
-        samp = gather_samples(samp, dist, group)
-        thr, ns = find_splits(samp, arity_d, mpb, fraction * float(N))
+        fraction = S["fraction"]
+        samp = sample_rows(X, S["row0"], params.seed, fraction) if fraction < 1.0 else X
+        samp = gather_samples(samp, S["dist"], group)
+        thr, ns = find_splits(samp, S["arity_d"], S["mpb"], fraction * float(S["N"]))
         thr_h = thr.cpu().numpy()
         ns_h = ns.cpu().numpy()
         torch.cuda.synchronize(dev)
@@ -219,56 +270,101 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         else:
             bins = torch.empty((F, ld), dtype=torch.uint8, device=dev)
             bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=torch.uint8, device=dev) if hist_mode != "scan" else None
-            bin_features(X, thr, ns, arity_d, bins=bins, row0=0, bins_rm=bins_rm)
-        w, node = bag(params.seed, po, part0, T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
+            bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm)
+        w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
                       want_node=(hist_mode not in ("segment", "bucket") or bins_rm is None))
         torch.cuda.synchronize(dev)
         t2 = time.perf_counter()
 
-        # ---- RandomForest.run loop ----
-        h = C.c_void_p()
-        check(L.b2rf_trainer_create(C.byref(cp), F, arity_np.ctypes.data_as(C.c_void_p), ns_h.ctypes.data_as(C.c_void_p),
-                                    thr_h.ctypes.data_as(C.c_void_p), N, C.byref(h)))
-        try:
-            cells = int(L.b2rf_trainer_max_group_cells(h))
-            hist = torch.empty(cells * 4, dtype=torch.float64, device=dev)
-            check(L.b2rf_trainer_bind(h, bins.data_ptr(), bins.stride(0), 0 if bins_rm is None else bins_rm.data_ptr(),
-                                      0 if bins_rm is None else bins_rm.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0),
-                                      0 if node is None else node.data_ptr(), ld if node is None else node.stride(0), n_local,
-                                      hist.data_ptr(), cells))
-            ncell = C.c_int64()
-            st = _stream()
-            t_comm = 0.0
-            while check(L.b2rf_trainer_begin_group(h, C.byref(ncell), st)) == 1:
-                if world > 1:
-                    dist.all_reduce(hist[: ncell.value * 4], group=group)   # DTStatsAggregator.merge (reduceByKey), row a7
-                check(L.b2rf_trainer_end_group(h, st))
-            torch.cuda.synchronize(dev)
-            t3 = time.perf_counter()
-            forest = _export(h, F, keep_trace)
-        finally:
-            L.b2rf_trainer_destroy(h)
-        forest.thresholds, forest.nsplits = thr_h, ns_h
-        tm = forest.timers
-        tm.update(init=(t0 - t_start) + (t2 - t1), findSplits=t1 - t0, total=t3 - t_start, loop=t3 - t2, comm=t_comm)
-        forest.counters.update(rows=N, rows_local=n_local, partitions=len(po) - 1, world=world, fraction=fraction)
+        forest = _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace)
+        t3 = time.perf_counter()
+        forest.timers.update(init=(t0 - t_start) + (t2 - t1), findSplits=t1 - t0, total=t3 - t_start, loop=t3 - t2)
         # stage kernels outside the trainer: sample_rows (if sampling), find_splits, bin, bag
         forest.counters["kernel_launches"] += (1 if fraction < 1.0 else 0) + 3 - (1 if prebinned is not None else 0)
         return forest
 
 
-def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", **kw) -> Forest:
+def sample_indices(seed: int, row0_global: int, n_rows: int, fraction: float) -> np.ndarray:
+    """Local indices of the rows the findSplits sampler keeps (host twin of sample_rows: same hash of the global row index)."""
+    if fraction >= 1.0:
+        return np.arange(n_rows, dtype=np.int64)
+    cap = int(n_rows * fraction + 6.0 * (n_rows * fraction * (1 - fraction)) ** 0.5 + 64)
+    out = np.empty(cap, np.int64)
+    k = lib().b2rf_sample_indices(int(seed), int(row0_global), int(n_rows), float(fraction), out.ctypes.data_as(C.c_void_p), cap)
+    if k < 0 or k > cap:
+        raise RuntimeError("b2rf_sample_indices: capacity exceeded")
+    return out[:k]
+
+
+def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_offsets=None, part0: int = None, group=None,
+             keep_trace: bool = False, hist_mode: str = "segment", chunk_rows: int = 1 << 20) -> Forest:
     """Public host-buffer entry point (what the Spark adapter calls): X_host f64 [n, F] / y_host f64 [n] are HOST arrays
-    (numpy or CPU torch tensors, ideally pinned).  Copies them to the device, trains, returns the Forest (host arrays)."""
+    (numpy or CPU torch tensors; pinned memory makes the copies asynchronous).
+
+    The raw feature matrix never has to be resident on the GPU: the findSplits row sample is gathered on the host (5 MB),
+    then X streams through two staging buffers in `chunk_rows` pieces — copy on one stream, K2 binning of the previous
+    piece on another — while K3 bagging, which does not depend on X, runs concurrently on a third stream."""
     dev = torch.device(device)
     Xh = torch.as_tensor(X_host, dtype=torch.float64)
     yh = torch.as_tensor(y_host, dtype=torch.float64)
+    if Xh.is_cuda:
+        return fit_tensors(Xh, yh.to(Xh.device), arity, params, part_offsets=part_offsets, part0=part0, group=group,
+                           keep_trace=keep_trace, hist_mode=hist_mode)
+    if not Xh.is_contiguous():
+        Xh = Xh.contiguous()
+    t_start = time.perf_counter()
     with torch.cuda.device(dev):
-        Xd = torch.empty(Xh.shape, dtype=torch.float64, device=dev)
-        Xd.copy_(Xh, non_blocking=True)
-        yd = torch.empty(yh.shape, dtype=torch.float64, device=dev)
+        n_local, F = Xh.shape
+        S = _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode)
+        T = params.numTrees
+        main = torch.cuda.current_stream()
+        copy_s, bag_s = torch.cuda.Stream(), torch.cuda.Stream()
+        yd = torch.empty(n_local, dtype=torch.float64, device=dev)
         yd.copy_(yh, non_blocking=True)
-        return fit_tensors(Xd, yd, arity, params, **kw)
+        ld = _pad(n_local)
+        # K3 first: it only needs the partition layout
+        bag_s.wait_stream(main)
+        with torch.cuda.stream(bag_s):
+            w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
+                          want_node=(hist_mode not in ("segment", "bucket")))
+        t0 = time.perf_counter()
+        # K1 on the host-gathered sample
+        fraction = S["fraction"]
+        idx = sample_indices(params.seed, S["row0"], n_local, fraction)
+        samp = Xh[torch.as_tensor(idx)].to(dev) if fraction < 1.0 else Xh.to(dev)
+        samp = gather_samples(samp, S["dist"], group)
+        thr, ns = find_splits(samp, S["arity_d"], S["mpb"], fraction * float(S["N"]))
+        thr_h = thr.cpu().numpy()
+        ns_h = ns.cpu().numpy()
+        t1 = time.perf_counter()
+        # K2 streamed over row chunks
+        bins = torch.empty((F, ld), dtype=torch.uint8, device=dev)
+        bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=torch.uint8, device=dev) if hist_mode != "scan" else None
+        chunk_rows = max(1, min(chunk_rows, n_local))
+        stage = [torch.empty((chunk_rows, F), dtype=torch.float64, device=dev) for _ in range(2)]
+        copied = [torch.cuda.Event() for _ in range(2)]
+        binned = [torch.cuda.Event() for _ in range(2)]
+        copy_s.wait_stream(main)
+        for k, r0 in enumerate(range(0, n_local, chunk_rows)):
+            b = k & 1
+            r1 = min(n_local, r0 + chunk_rows)
+            with torch.cuda.stream(copy_s):
+                if k >= 2:
+                    copy_s.wait_event(binned[b])
+                stage[b][: r1 - r0].copy_(Xh[r0:r1], non_blocking=True)
+                copied[b].record(copy_s)
+            main.wait_event(copied[b])
+            bin_features(stage[b][: r1 - r0], thr, ns, S["arity_d"], bins=bins, row0=r0, bins_rm=bins_rm, check_errors=False)
+            binned[b].record(main)
+        main.wait_stream(bag_s)
+        _raise_bin_errors(S["arity_d"])
+        torch.cuda.synchronize(dev)
+        t2 = time.perf_counter()
+        forest = _train_loop(S, params, F, n_local, yd, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace)
+        t3 = time.perf_counter()
+        forest.timers.update(init=(t0 - t_start) + (t2 - t1), findSplits=t1 - t0, total=t3 - t_start, loop=t3 - t2)
+        forest.counters["kernel_launches"] += 2 + (n_local + chunk_rows - 1) // chunk_rows
+        return forest
 
 
 def _export(h, F: int, keep_trace: bool) -> Forest:

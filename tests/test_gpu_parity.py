@@ -350,3 +350,27 @@ def test_spark_adapter_pipeline_flow(b2rf, oracle, cuda):
     # ML 08: float-valued params through copy
     m = rf.copy({rf.maxDepth: 3.0, rf.numTrees: 4.0}).fit(train)
     assert m.getNumTrees == 4 and len(m.trees) == 4 and m.trees[0].depth <= 3
+
+
+def test_fit_host_streams_and_matches_fit_tensors(b2rf, oracle, cuda):
+    """The host-buffer entry point (chunked copy + K2 per chunk, K3 on a side stream) trains the same forest as the
+    device-resident one, for ragged chunk sizes, with and without row sampling."""
+    from b2rf import trainer
+    X, y, arity = b2rf.synth.airbnb(5000)
+    p = b2rf.TreeParams(maxDepth=6, maxBins=40, numTrees=7, bootstrap=True, seed=3)
+    po = trainer.default_partitions(5000, 700)
+    ref = trainer.fit_tensors(X.to(cuda), y.to(cuda), arity, p, part_offsets=po)
+    for chunk in (5000, 1777, 64):
+        f = trainer.fit_host(X.numpy(), y.numpy(), arity, p, device=cuda, part_offsets=po, chunk_rows=chunk)
+        assert np.array_equal(f.feature, ref.feature) and np.array_equal(f.threshold, ref.threshold)
+        assert np.array_equal(f.stats[:, 0], ref.stats[:, 0]) and np.array_equal(f.prediction, ref.prediction)   # integer labels: exact
+    Xc, yc, ar = b2rf.synth.c3(40000, device="cpu")      # fraction < 1: host-side sample indices == device sampler
+    p = b2rf.TreeParams(maxDepth=5, maxBins=64, numTrees=3, bootstrap=True, seed=42)
+    a = trainer.fit_tensors(Xc.to(cuda), yc.to(cuda), ar, p)
+    b = trainer.fit_host(Xc.pin_memory(), yc, ar, p, device=cuda, chunk_rows=9000)
+    assert np.array_equal(a.thresholds, b.thresholds) and np.array_equal(a.feature, b.feature) and np.array_equal(a.threshold, b.threshold)
+    idx = trainer.sample_indices(42, 0, 40000, a.counters["fraction"])
+    assert np.array_equal(idx, np.nonzero(oracle.sample_keep(42, np.arange(40000), a.counters["fraction"]))[0])
+    bad = X.numpy().copy(); bad[4321, 5] = 99.0
+    with pytest.raises(b2rf.IllegalArgumentException, match="Feature 5 is categorical"):
+        trainer.fit_host(bad, y.numpy(), arity, b2rf.TreeParams(maxBins=40), device=cuda, chunk_rows=1000)
