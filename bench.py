@@ -32,6 +32,8 @@ WORKLOADS = {
     "C4-shard": dict(rows=12_500_000, F=128, numTrees=100, maxDepth=12, maxBins=256, gen="c4"),
 }
 ROWS_PER_PARTITION = 4096   # emulated Spark partition size (bagging streams are per partition; stated in config)
+# ncu --set full capture of the dominant kernel (profiles/r01_ncu_bucket_hist_c3.md): DRAM bytes of one whole-level launch
+NCU_TRAFFIC = {"C3": {"traffic": 100.898e9, "algorithmic": 3.765e9}}
 
 
 class ClockSampler(threading.Thread):
@@ -179,7 +181,7 @@ def main():
         return float(ms.item()), outs
 
     # ---- device-resident arm -------------------------------------------------------------------------------
-    step = lambda: trainer.fit_tensors(X, y, arity, params, part_offsets=po)
+    step = lambda: trainer.fit_tensors(X, y, arity, params, part_offsets=po, keep_trace=True)
     for _ in range(args.warmup):
         step()
     sampler = ClockSampler(local_rank)
@@ -195,7 +197,10 @@ def main():
     hist_launches = f0.counters["hist_launches"]
     peak, peak_src = measured_peak_gbs()
     achieved = hist_bytes / hist_s / 1e9 if hist_s > 0 else 0.0
-    updates = None
+    # bin updates of one fit: every in-bag row of every evaluated node x features per node (from the forest's own node counts)
+    fsub = params.features_per_node(F)
+    internal_or_evaluated = f0.trace_d[:, 2].sum() if f0.trace_d is not None else None
+    updates_per_fit = float(internal_or_evaluated) * fsub if internal_or_evaluated is not None else float("nan")
     phases = {k: round(sum(f.timers[k] for f in forests) / len(forests), 4) for k in ("init", "findSplits", "findBestSplits", "chooseSplits", "total")}
 
     # ---- end-to-end arm: host buffers in, forest arrays out, through the public API --------------------------
@@ -240,11 +245,17 @@ def main():
                        "l2": "inputs (bin matrix 0.64 GB + per-tree arrays 5 GB) exceed the 126 MB L2; no explicit flush",
                        "node_groups": f0.counters["groups"], "forest_nodes": int(f0.num_nodes())},
             "phases_s": phases,
-            "roofline": {"bound": "hbm", "kernel": "hist_kernel<true> (K4 histogram build + fused K6 routing)", "achieved": achieved, "peak": peak,
-                         "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_fit": hist_bytes, "launches_per_fit": hist_launches, "kernel_seconds_per_fit": hist_s,
-                         "kernel_share_of_step": hist_s / (ms_per_step * 1e-3),
-                         "note": "K4 is bound by L2 atomic (RED) issue rate, not HBM: see DESIGN.md; traffic from ncu is in profiles/"},
+            "roofline": {"bound": "hbm", "kernel": "bucket_hist_kernel (K4: per-node shared-memory histograms over row segments)",
+                         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         # dram__bytes_read+write of ONE whole-level launch (100 trees, 1600 nodes) from profiles/r01_ncu_bucket_hist_c3.md;
+                         # the same launch's algorithmic bytes are given beside it
+                         "traffic": NCU_TRAFFIC.get(args.workload, {}).get("traffic"),
+                         "traffic_launch_algorithmic_bytes": NCU_TRAFFIC.get(args.workload, {}).get("algorithmic"),
+                         "peak_source": peak_src, "algorithmic_bytes_per_fit": hist_bytes, "launches_per_fit": hist_launches,
+                         "kernel_seconds_per_fit": hist_s, "kernel_share_of_step": hist_s / (ms_per_step * 1e-3),
+                         "weighted_bin_updates_per_s": updates_per_fit / hist_s if hist_s > 0 else None,   # sum over evaluated nodes of (sum of bag weights) x features per node
+                         "note": "K4 is bound by shared-memory atomic throughput (71% of the smem wavefront peak in ncu), not HBM: "
+                                 "22 atomic bin updates per 37 algorithmic bytes; see DESIGN.md section 2 and profiles/"},
             "e2e": e2e, "cpu_baseline": cpu,
             "gpu_launches": int(sum(f.counters["kernel_launches"] for f in forests)),
             "clocks": sampler.summary(),
