@@ -63,7 +63,8 @@ struct BucketLaunch {
   int32_t nSlots, CH;
   const uint2* slot_fo; const int64_t* slot_base; const int32_t* slot_cells; int32_t Fsub;
   int32_t maxCells;                      // shared-memory histogram capacity in cells
-  int32_t padB;                          // > 0: padded [32-feature group][bin][lane] shared layout with padB bins per group; 0: compact
+  int32_t padB;                          // > 0: padded [bin][feature-in-group] shared layout with padB bins; 0: compact cells
+  int32_t G;                             // padded layout: features per group / task (power of two <= 32)
   double* hist;
   // segment mode (dseg != nullptr): slot s owns rows idx[seg.buf][seg.start ...] with seg = dseg[slot_pos[s]]
   const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;

@@ -291,7 +291,8 @@ constexpr int BUCKET_THREADS = 256;
 // while every lane (== feature) gathers its own bin code and updates its own histogram column.
 template <bool DIRECT>
 __device__ __forceinline__ void bucket_rows(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
-                                            double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep) {
+                                            double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
+                                            int R, int r) {   // R rows per warp instruction (32 / feature-group width); r = this lane's row slot
   constexpr int W = BUCKET_THREADS / 32;
   const unsigned FULL = 0xffffffffu;
   for (int base = warp * 32; base < n; base += W * 32) {
@@ -301,14 +302,15 @@ __device__ __forceinline__ void bucket_rows(const BucketLaunch& a, const uint32_
     const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
     const double mywyy = mywy * myy;
     const int nb = min(32, n - base);
-    for (int q = 0; q < nb; q += 4) {
+    for (int q = 0; q < nb; q += 4 * R) {
       uint32_t bin[4], wv[4]; double wy[4], wyy[4];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
-        const uint32_t p = __shfl_sync(FULL, mine, (q + u) & 31);
-        wy[u] = __shfl_sync(FULL, mywy, (q + u) & 31);
-        wyy[u] = __shfl_sync(FULL, mywyy, (q + u) & 31);
-        wv[u] = (q + u) < nb ? (p >> 27) : 0u;
+        const int ri = q + u * R + r;
+        const uint32_t p = __shfl_sync(FULL, mine, ri & 31);
+        wy[u] = __shfl_sync(FULL, mywy, ri & 31);
+        wyy[u] = __shfl_sync(FULL, mywyy, ri & 31);
+        wv[u] = ri < nb ? (p >> 27) : 0u;
         bin[u] = (wv[u] && active) ? a.bins_rm[(size_t)(p & 0x7ffffffu) * a.ldr + featCol] : 0u;
       }
 #pragma unroll
@@ -333,12 +335,22 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
   double* ssq = ssum + a.maxCells;
   unsigned* scnt = reinterpret_cast<unsigned*>(ssq + a.maxCells);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const uint32_t total = a.chunk_prefix[a.nSlots];
+  // Shared layout.  padded (padB > 0): the slot's features are cut into groups of G (a power of two <= 32); one task handles one
+  // group and keeps cell (feature fl of the group, bin b) at b*G + fl.  A warp instruction then covers 32/G rows x G features
+  // with bank == lane for G == 32 (no conflict possible) and at most 32/G-way conflicts otherwise, and the task's histogram is
+  // padB*G cells whatever the feature count, so several CTAs fit per SM even for 256 bins.  compact (padB == 0): one task per
+  // (slot, chunk) with cell = feature offset + bin.
+  const int padB = a.padB;
+  const int G = padB > 0 ? a.G : 32;
+  const int nG = padB > 0 ? (a.Fsub + G - 1) / G : 1;
+  const uint32_t total = a.chunk_prefix[a.nSlots] * (uint32_t)nG;
   for (uint32_t task = blockIdx.x; task < total; task += gridDim.x) {
+    const uint32_t bt = task / (uint32_t)nG;
+    const int g = (int)(task % (uint32_t)nG);
     int lo = 0, hi = a.nSlots;
-    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.chunk_prefix[mid] <= task) lo = mid; else hi = mid; }
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.chunk_prefix[mid] <= bt) lo = mid; else hi = mid; }
     const int slot = lo;
-    const uint32_t chunk = task - a.chunk_prefix[slot];
+    const uint32_t chunk = bt - a.chunk_prefix[slot];
     uint32_t cnt; const uint32_t* rl;
     const uint32_t begin = chunk * (uint32_t)a.CH;
     if (a.dseg != nullptr) {
@@ -353,23 +365,27 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
     const int ncell = a.slot_cells[slot];
     const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
     double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
-    // Shared layout.  padded (padB > 0): cell (feature j, bin b) sits at ((j/32)*padB + b)*32 + j%32, i.e. bank == lane: the
-    // lanes of a warp (lane == feature) can never conflict, whatever their bins.  compact: cell = feature offset + bin.
-    const int padB = a.padB;
-    const int scells = padB > 0 ? ((a.Fsub + 31) / 32) * padB * 32 : ncell;
+    const int scells = padB > 0 ? padB * G : ncell;
     const bool direct = (int64_t)n * a.Fsub < (int64_t)ncell || scells > a.maxCells;   // few rows: skip the shared-memory round trip
     if (!direct) {
       for (int c = tid; c < scells; c += BUCKET_THREADS) { ssum[c] = 0.0; ssq[c] = 0.0; scnt[c] = 0u; }
       __syncthreads();
     }
-    for (int j0 = 0; j0 < a.Fsub; j0 += 32) {
-      const int j = j0 + lane;
+    if (padB > 0) {
+      const int fl = lane & (G - 1), r = lane / G;
+      const int j = g * G + fl;
       const bool active = j < a.Fsub;
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
-      const uint32_t sbase = padB > 0 ? (uint32_t)((j0 >> 5) * padB * 32 + lane) : e.y;   // shared-memory cell of bin 0
-      const uint32_t sstep = padB > 0 ? 32u : 1u;
-      if (direct) bucket_rows<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep);
-      else bucket_rows<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep);
+      if (direct) bucket_rows<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r);
+      else bucket_rows<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r);
+    } else {
+      for (int j0 = 0; j0 < a.Fsub; j0 += 32) {
+        const int j = j0 + lane;
+        const bool active = j < a.Fsub;
+        const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
+        if (direct) bucket_rows<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0);
+        else bucket_rows<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0);
+      }
     }
     if (!direct) {
       __syncthreads();
@@ -377,9 +393,9 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
         const unsigned k = scnt[c];
         if (!k) continue;
         size_t gc = (size_t)c;
-        if (padB > 0) { const int jj = (c / (padB * 32)) * 32 + (c & 31); gc = (size_t)fo[jj].y + (size_t)((c >> 5) % padB); }   // untouched cells of idle lanes stay 0
-        double* g = hb + gc * 4;
-        atomicAdd(g, (double)k); atomicAdd(g + 1, ssum[c]); atomicAdd(g + 2, ssq[c]);
+        if (padB > 0) gc = (size_t)fo[g * G + (c & (G - 1))].y + (size_t)(c / G);   // cells of idle lanes are never touched, so k == 0 there
+        double* gp = hb + gc * 4;
+        atomicAdd(gp, (double)k); atomicAdd(gp + 1, ssum[c]); atomicAdd(gp + 2, ssq[c]);
       }
       __syncthreads();
     }

@@ -630,12 +630,13 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       t->hSlotCells.p[sl] = c;
       maxCells = std::max(maxCells, c);
     }
-    // shared-memory layout: the bank-conflict-free padded layout when at least two CTAs per SM still fit, else compact cells
+    // shared-memory layout: padded [bin][feature-in-group] with the widest power-of-two feature group G that keeps a task's
+    // histogram (maxBins * G cells) within ~48 KB, i.e. four or more CTAs per SM; compact cells only if even G = 4 is too big
     const int32_t maxBinsAll = *std::max_element(t->numBins.begin(), t->numBins.end());
-    const int64_t paddedCells = (int64_t)((t->Fsub + 31) / 32) * maxBinsAll * 32;
-    int32_t padB = 0;
+    int32_t padB = 0, G = 32;
     static const bool noPad = [] { const char* m = std::getenv("B2RF_NO_PAD"); return m && *m == '1'; }();
-    if (!noPad && paddedCells * 20 + 16 <= (int64_t)100 * 1024) { padB = maxBinsAll; maxCells = (int32_t)paddedCells; }
+    while (G > 4 && ((int64_t)maxBinsAll * G * 20 + 16 > (int64_t)48 * 1024 || G / 2 >= t->Fsub)) G /= 2;
+    if (!noPad && (int64_t)maxBinsAll * G * 20 + 16 <= (int64_t)100 * 1024) { padB = maxBinsAll; maxCells = maxBinsAll * G; }
     if ((size_t)maxCells * 20 + 16 > (size_t)220 * 1024) maxCells = (int32_t)(((size_t)220 * 1024 - 16) / 20);   // larger slots take the direct path
     ok &= cuda_ok(cudaMemcpyAsync(t->dSlotCells.p, t->hSlotCells.p, nSlots * 4, cudaMemcpyHostToDevice, s), "upload slot cells");
     if (!t->segMode) ok &= cuda_ok(cudaMemsetAsync(t->dSlotCount.p, 0, nSlots * 4, s), "zero slot counts");
@@ -644,7 +645,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     BucketLaunch b;
     b.bins_rm = t->d_bins_rm; b.ldr = t->ldr; b.y = t->d_y; b.rowlist = t->dRowList.p; b.slot_start = t->dSlotStart.p; b.slot_count = t->dSlotCount.p;
     b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->segMode ? SEG_CH : t->chunkRows; b.slot_fo = t->dSlotFo.p;
-    b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.padB = padB; b.hist = t->d_hist;
+    b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.padB = padB; b.G = G; b.hist = t->d_hist;
     b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr;
     std::string err;
     cudaError_t e;
