@@ -374,3 +374,32 @@ def test_fit_host_streams_and_matches_fit_tensors(b2rf, oracle, cuda):
     bad = X.numpy().copy(); bad[4321, 5] = 99.0
     with pytest.raises(b2rf.IllegalArgumentException, match="Feature 5 is categorical"):
         trainer.fit_host(bad, y.numpy(), arity, b2rf.TreeParams(maxBins=40), device=cuda, chunk_rows=1000)
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_randomized_small_problems_exact_ties(b2rf, oracle, cuda, seed):
+    """Random small problems with integer-valued features and labels: every sum is exact, so equal gains are EXACT ties and
+    the forest only matches the oracle if every first-maximum rule (split index, subset position, centroid order, prune,
+    Scala map order of the driver tail) is reproduced.  Mixed categorical / continuous, all parameter axes."""
+    rng = np.random.default_rng(1000 + seed)
+    N = int(rng.integers(30, 900))
+    F = int(rng.integers(1, 12))
+    arity = np.array([int(rng.choice([0, 0, 2, 3, 5, 9])) for _ in range(F)], np.int32)
+    X = np.zeros((N, F))
+    for f in range(F):
+        X[:, f] = rng.integers(0, arity[f], N) if arity[f] else rng.integers(-3, 4, N) * (0.5 if rng.random() < 0.3 else 1.0)
+    y = rng.integers(0, 4, N).astype(float) + (X[:, 0] > 0) * 2.0
+    T = int(rng.choice([1, 1, 3, 8]))
+    kw = dict(maxDepth=int(rng.integers(1, 9)), maxBins=int(rng.choice([9, 16, 32])), numTrees=T, bootstrap=bool(T > 1 and rng.random() < 0.8),
+              seed=int(rng.integers(0, 2 ** 31)), minInstancesPerNode=int(rng.choice([1, 1, 2, 7])), minInfoGain=float(rng.choice([0.0, 0.0, 0.05])),
+              subsamplingRate=float(rng.choice([1.0, 1.0, 0.6])), maxMemoryInMB=int(rng.choice([256, 0])),
+              featureSubsetStrategy=str(rng.choice(["auto", "all", "sqrt", "0.5"])))
+    if T == 1:
+        kw["featureSubsetStrategy"] = str(rng.choice(["auto", "all"]))
+    cuts = np.unique(np.concatenate([[0, N], rng.integers(0, N, int(rng.integers(0, 4)))]))
+    for mode in ("segment", "scan"):
+        g, o = _fit_both(b2rf, oracle, cuda, X, y, arity, part_offsets=cuts, hist_mode=mode, **kw)
+        assert_trace_parity(g, o)
+        assert_forest_parity(g, o)
+        Xt = X[rng.integers(0, N, 50)]
+        np.testing.assert_array_equal(g.predict(torch.as_tensor(Xt, device=cuda)).cpu().numpy(), o.predict(Xt))
