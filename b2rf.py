@@ -8,7 +8,7 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 _REAL = "scalable-machine-learning-with-apache-spark_b200"
 _pkg = importlib.import_module(_REAL)
-for _sub in ("_build", "_lib", "params", "forest", "synth", "trainer", "spark"):
+for _sub in ("_build", "_lib", "params", "forest", "synth", "trainer", "spark", "persistence"):
     try:
         _m = importlib.import_module(f"{_REAL}.{_sub}")
     except ModuleNotFoundError as _e:          # optional submodules (spark adapter needs pyspark or the stub)

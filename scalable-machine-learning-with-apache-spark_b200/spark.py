@@ -176,6 +176,39 @@ class _ForestModelBase(Model, _TreeRegressorParams):
         self._forest.uid = self.uid
         return self._forest.to_debug_string(ensemble=self._ensemble)
 
+    # ---- MLWritable / MLReadable (MLlib 3.1.2 directory layout, persistence.py) ----
+    def write(self):
+        from .persistence import ModelWriter
+        return ModelWriter(self)
+
+    def save(self, path):
+        self.write().save(path)
+
+    @classmethod
+    def load(cls, path):
+        from .persistence import load_forest
+        meta, forest = load_forest(path)
+        m = cls(forest)
+        m.uid = meta["uid"]
+        for p in list(m.params):
+            setattr(m, p.name, p._copy_new_parent(m)) if hasattr(p, "_copy_new_parent") else None
+        m._paramMap, m._defaultParamMap = {}, {}
+        m._base_defaults()
+        if isinstance(m, B200RandomForestRegressionModel):
+            m._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True)
+        for k, v in meta.get("paramMap", {}).items():
+            if m.hasParam(k):
+                m._set(**{k: v})
+        return m
+
+    @classmethod
+    def read(cls):
+        class _R:
+            @staticmethod
+            def load(path):
+                return cls.load(path)
+        return _R()
+
     def predict(self, value):
         import torch
         v = np.asarray(value.toArray() if hasattr(value, "toArray") else value, np.float64).reshape(1, -1)

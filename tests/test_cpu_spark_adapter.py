@@ -81,3 +81,39 @@ def test_model_copy_carries_forest_and_api(sp, b2rf, oracle):
     assert m.toDebugString.startswith(f"DecisionTreeRegressionModel: uid={est.uid}, depth=1, numNodes=3, numFeatures=1\n  If (feature 0 <= 0.5)")
     m2 = m.copy({m.predictionCol: "p2"})
     assert m2._forest is m._forest and m2.getPredictionCol() == "p2" and m.getPredictionCol() == "prediction"
+
+
+def test_persistence_round_trip_mllib_layout(sp, b2rf, oracle, tmp_path):
+    """model.write().overwrite().save(path) (`Labs/ML 07L - Hyperparameter Tuning Lab.py:209`) writes MLlib 3.1.2's directory
+    layout; load() restores an identical forest, params and uid."""
+    import json
+    import pyarrow.parquet as pq
+    X, y, arity = b2rf.synth.airbnb(1500)
+    for T in (1, 4):
+        o = oracle.fit(X.numpy(), y.numpy(), arity, maxDepth=5, maxBins=40, numTrees=T, bootstrap=T > 1, seed=3)
+        fo = b2rf.Forest(33, o.tree_off, o.feature, o.threshold, o.left, o.right, o.prediction, o.impurity, o.gain, o.stats, o.ncat, o.cat_off,
+                         o.cat_len, o.cats)
+        est = (sp.B200DecisionTreeRegressor if T == 1 else sp.B200RandomForestRegressor)(maxDepth=5, maxBins=40, labelCol="price")
+        m = est._make_model(fo)
+        path = str(tmp_path / f"model{T}")
+        m.write().overwrite().save(path)
+        with pytest.raises(IOError, match="already exists"):
+            m.write().save(path)
+        meta = json.loads(open(path + "/metadata/part-00000").readline())
+        assert meta["class"].endswith("DecisionTreeRegressionModel" if T == 1 else "RandomForestRegressionModel")
+        assert meta["uid"] == m.uid and meta["numFeatures"] == 33 and meta["paramMap"]["maxBins"] == 40 and meta["sparkVersion"] == "3.1.2"
+        tbl = pq.read_table(path + "/data/part-00000.parquet")
+        names = tbl.schema.names
+        assert names == (["id", "prediction", "impurity", "impurityStats", "rawCount", "gain", "leftChild", "rightChild", "split"] if T == 1
+                         else ["treeID", "nodeData"])
+        assert tbl.num_rows == len(o.feature)
+        if T > 1:
+            assert meta["numTrees"] == T and pq.read_table(path + "/treesMetadata/part-00000.parquet").num_rows == T
+        m2 = type(m).load(path)
+        f2 = m2._forest
+        assert m2.uid == m.uid and m2.getMaxBins() == 40 and m2.getLabelCol() == "price"
+        for a in ("tree_off", "feature", "threshold", "left", "right", "prediction", "ncat", "cat_len"):
+            assert np.array_equal(getattr(f2, a), getattr(fo, a)), a
+        assert np.array_equal(f2.stats[:, :3], fo.stats[:, :3]) and np.array_equal(f2.gain, fo.gain)
+        assert [sorted(f2.cats[o_:o_ + n]) for o_, n in zip(f2.cat_off, f2.cat_len)] == [sorted(fo.cats[o_:o_ + n]) for o_, n in zip(fo.cat_off, fo.cat_len)]
+        assert m2.toDebugString == m.toDebugString
