@@ -14,7 +14,8 @@
  *    Pointers named h_* are host pointers.  `stream` is a cudaStream_t passed as void*; calls are asynchronous on it
  *    unless stated otherwise.
  *  - No CPU fallback exists: without a CUDA device every compute entry point fails with B2RF_ERR_CUDA.
- *  - Layouts: X is row-major f64 [rows][ldx]; the bin matrix is COLUMN-major uint8 bins[F][ldb] (ldb % 128 == 0);
+ *  - Layouts: X is row-major f64 [rows][ldx]; the bin matrix is COLUMN-major bins[F][ldb] (ldb % 128 == 0) of uint8 codes,
+ *    or uint16 codes when min(maxBins, numExamples) > 256;
  *    bag weights w[T][ldw] uint8; per-tree row->node ids node[T][ldn] int32 (-1 = row inactive for that tree);
  *    histograms hist[cells][4] f64 = (weight-sum, sum w*y, sum w*y*y, raw count) per (node-slot, feature, bin).
  */
@@ -95,8 +96,9 @@ int b2rf_find_splits_noalloc(const double* d_sample, int64_t n_sample, int32_t F
 /* Bins rows [0,n_rows) of d_X into d_bins[f][row0 + i].  *d_err (int32, caller-zeroed) becomes feature+1 on an invalid
  * categorical value. */
 int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const double* d_thresholds, const int32_t* d_nsplits,
-             const int32_t* d_arity, int32_t maxSplits, uint8_t* d_bins, int64_t ldb, int64_t row0, int32_t* d_err,
-             uint8_t* d_bins_rm /* optional row-major twin [row][ldr], may be NULL */, int64_t ldr, void* stream);
+             const int32_t* d_arity, int32_t maxSplits, void* d_bins, int64_t ldb, int64_t row0, int32_t* d_err,
+             void* d_bins_rm /* optional row-major twin [row][ldr], may be NULL */, int64_t ldr,
+             int32_t code_bytes /* 1: uint8 codes (maxBins <= 256); 2: uint16.  ldb / ldr count codes */, void* stream);
 
 /* ---- K3: BaggedPoint.convertToBaggedRDD (row a4) ------------------------------------------------------------- */
 /* One emulated Spark partition per thread: partition p (global index part0 + p) covers local rows
@@ -118,7 +120,8 @@ int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t);
 /* d_bins_rm (optional, may be NULL): row-major twin of the bin matrix written by b2rf_bin.  With it the trainer buckets each
  * group's rows by node (counting sort) and builds the histograms in shared memory; without it, it scans the column-major
  * matrix and accumulates with global reductions (also selectable with B2RF_HIST_MODE=scan). */
-int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const uint8_t* d_bins_rm, int64_t ldr, const double* d_y,
+int b2rf_trainer_code_bytes(const b2rf_trainer* t);   /* 1 or 2: the bin-code width this fit needs (min(maxBins, N) > 256 => 2) */
+int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins, int64_t ldb, const void* d_bins_rm, int64_t ldr, const double* d_y,
                       const uint8_t* d_w, int64_t ldw, int32_t* d_node, int64_t ldn, int64_t n_rows_local, double* d_hist,
                       int64_t hist_cells);
 /* selectNodesToSplit + K4 (findBestSplits.binSeqOp, row a6) with the fused K6 row routing (row a10).
@@ -144,7 +147,7 @@ int b2rf_trainer_trace(const b2rf_trainer* t, int32_t* h_ints, double* h_dbls);
 /* ---- stand-alone kernels (same code the trainer launches), for testing and for callers with their own driver -- */
 /* K4: histogram of one node group.  d_slot_of_row [Tg][ldn] gives the group slot of each row per listed tree (-1 = skip);
  * d_tree_ids[Tg]; d_slot_fo [slots][Fsub] pairs (feature, cell offset inside the slot); d_slot_base[slots] cells. */
-int b2rf_hist_build(const uint8_t* d_bins, int64_t ldb, int32_t F, const double* d_y, const uint8_t* d_w, int64_t ldw,
+int b2rf_hist_build(const void* d_bins, int64_t ldb, int32_t code_bytes, int32_t F, const double* d_y, const uint8_t* d_w, int64_t ldw,
                     const int32_t* d_slot_of_row, int64_t ldn, const int32_t* d_tree_ids, int32_t Tg, int64_t n_rows,
                     const uint32_t* d_slot_fo, const int64_t* d_slot_base, int32_t Fsub, double* d_hist, void* stream);
 /* K7: TreeEnsembleModel.predict on raw features (rows a11): mean over trees, tree-order summation. */

@@ -43,11 +43,12 @@ _SIGS = {
     "b2rf_find_splits": (C.c_int, [vp, i64, i32, vp, i32, f64, vp, vp, vp, sz, vp]),
     "b2rf_find_splits_noalloc_max_bytes": (sz, []),
     "b2rf_find_splits_noalloc": (C.c_int, [vp, i64, i32, vp, i32, f64, vp, vp, vp]),
-    "b2rf_bin": (C.c_int, [vp, i64, i64, i32, vp, vp, vp, i32, vp, i64, i64, vp, vp, i64, vp]),
+    "b2rf_bin": (C.c_int, [vp, i64, i64, i32, vp, vp, vp, i32, vp, i64, i64, vp, vp, i64, i32, vp]),
     "b2rf_bag": (C.c_int, [i64, vp, i32, i32, i32, f64, i32, vp, i64, vp, i64, vp]),
     "b2rf_trainer_create": (C.c_int, [vp, i32, vp, vp, vp, i64, vp]),
     "b2rf_trainer_destroy": (None, [vp]),
     "b2rf_trainer_max_group_cells": (i64, [vp]),
+    "b2rf_trainer_code_bytes": (C.c_int, [vp]),
     "b2rf_trainer_bind": (C.c_int, [vp, vp, i64, vp, i64, vp, vp, i64, vp, i64, i64, vp, i64]),
     "b2rf_trainer_begin_group": (C.c_int, [vp, vp, vp]),
     "b2rf_trainer_end_group": (C.c_int, [vp, vp]),
@@ -56,7 +57,7 @@ _SIGS = {
     "b2rf_trainer_export": (C.c_int, [vp] * 14),
     "b2rf_trainer_trace_size": (i64, [vp]),
     "b2rf_trainer_trace": (C.c_int, [vp, vp, vp]),
-    "b2rf_hist_build": (C.c_int, [vp, i64, i32, vp, vp, i64, vp, i64, vp, i32, i64, vp, vp, i32, vp, vp]),
+    "b2rf_hist_build": (C.c_int, [vp, i64, i32, i32, vp, vp, i64, vp, i64, vp, i32, i64, vp, vp, i32, vp, vp]),
     "b2rf_predict": (C.c_int, [vp, i64, i64, i32] + [vp] * 12),
 }
 

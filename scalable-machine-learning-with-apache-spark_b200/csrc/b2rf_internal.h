@@ -30,11 +30,10 @@ struct __align__(8) SplitRec {
   double gain, impurity, leftImp, rightImp;
   double parent[4], left[4], right[4];
   int32_t feature, splitIdx, valid, pad;
-  uint32_t catmask[8];
-};
+};   // the left-category set of a categorical best split goes to SplitLaunch::catmask_out[slot][maskWords]
 
 struct HistLaunch {
-  const uint8_t* bins; int64_t ldb; int32_t F;
+  const uint8_t* bins; int64_t ldb; int32_t F;   // ldb counts codes (elements), not bytes
   const double* y;
   const uint8_t* w; int64_t ldw;
   int32_t* node; int64_t ldn;       // traverse mode: tree-local node index per (tree,row); direct mode: slot per (g,row)
@@ -44,6 +43,8 @@ struct HistLaunch {
   const uint2* slot_fo; const int64_t* slot_base; int32_t Fsub;
   double* hist;
   uint32_t* slot_count;             // MODE 2 only: rows per slot
+  int32_t codeBytes;                // 1: uint8 bin codes (maxBins <= 256), 2: uint16
+  int32_t maskWords;                // 32-bit words per categorical left-set mask
 };
 
 // Row segment of one node in a tree's row list (segment mode): rows [start, start+count) of list `buf` (0/1 ping-pong).
@@ -65,6 +66,7 @@ struct BucketLaunch {
   int32_t maxCells;                      // shared-memory histogram capacity in cells
   int32_t padB;                          // > 0: padded [bin][feature-in-group] shared layout with padB bins; 0: compact cells
   int32_t G;                             // padded layout: features per group / task (power of two <= 32)
+  int32_t codeBytes;                     // 1 / 2 bytes per bin code; ldr counts codes
   double* hist;
   // segment mode (dseg != nullptr): slot s owns rows idx[seg.buf][seg.start ...] with seg = dseg[slot_pos[s]]
   const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;
@@ -81,6 +83,7 @@ struct PartLaunch {                      // stable partition of the row segments
   uint32_t* chunk_prefix;                              // [nSplits + 1]
   uint32_t* left_cnt; uint32_t* left_off;              // [tasks]
   uint32_t* predbits;                                  // [tasks][SEG_CH / 32]
+  int32_t codeBytes, maskWords;
 };
 cudaError_t launch_partition(const PartLaunch& p, cudaStream_t s);
 cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s);
@@ -103,6 +106,9 @@ struct SplitLaunch {
   const int32_t* isCat;       // [F]
   double minInstances, minWeight, minInfoGain;
   SplitRec* out;
+  uint32_t* catmask_out;      // [slots][maskWords]
+  int32_t maxB;               // largest numBins of any feature (sizes the per-warp shared arrays)
+  int32_t maskWords;
 };
 cudaError_t launch_best_split(const SplitLaunch& a, cudaStream_t s);
 

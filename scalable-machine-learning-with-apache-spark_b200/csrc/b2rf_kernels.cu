@@ -57,6 +57,14 @@ __device__ __forceinline__ void bulk_g2s(void* dst_smem, const void* src_gmem, u
                : "memory");
 }
 
+// Bin codes are uint8 when maxBins <= 256 and uint16 otherwise (codeBytes = 1 / 2, uniform per launch).
+__device__ __forceinline__ uint32_t load_code(const void* base, size_t idx, int codeBytes) {
+  return codeBytes == 2 ? (uint32_t) reinterpret_cast<const uint16_t*>(base)[idx] : (uint32_t) reinterpret_cast<const uint8_t*>(base)[idx];
+}
+__device__ __forceinline__ bool in_cat_mask(const uint32_t* masks, uint32_t aux, int maskWords, uint32_t bin) {
+  return (masks[(size_t)(aux & 0x7fffffffu) * maskWords + (bin >> 5)] >> (bin & 31)) & 1u;
+}
+
 // =================================================================================================
 // K4 (+K6): histogram build over TMA-staged column tiles of the bin matrix
 // =================================================================================================
@@ -97,10 +105,11 @@ __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k
     // warp 0: one bulk copy per feature column segment
     const int64_t r0 = tile * k.R;
     int64_t rem = a.n_rows - r0;
-    uint32_t nb = (uint32_t)(rem < k.R ? ((rem + 15) & ~(int64_t)15) : k.R);
+    uint32_t nb = (uint32_t)(rem < k.R ? ((rem + 15) & ~(int64_t)15) : k.R) * (uint32_t)a.codeBytes;   // bytes per column segment
     if (tid == 0) mbar_expect_tx(&bars[buf], nb * (uint32_t)a.F);
     __syncwarp();
-    for (int f = tid; f < a.F; f += 32) bulk_g2s(tiles + buf * bufBytes + (size_t)f * k.pitch, a.bins + (size_t)f * a.ldb + r0, nb, &bars[buf]);
+    for (int f = tid; f < a.F; f += 32)
+      bulk_g2s(tiles + buf * bufBytes + (size_t)f * k.pitch, a.bins + ((size_t)f * a.ldb + r0) * a.codeBytes, nb, &bars[buf]);
   };
 
   int64_t it = 0;
@@ -139,9 +148,9 @@ __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k
               DNode d = tn[n];
               bool moved = false;
               while (d.feature >= 0) {
-                const uint32_t bin = tb[(size_t)d.feature * k.pitch + r];
+                const uint32_t bin = load_code(tb + (size_t)d.feature * k.pitch, r, a.codeBytes);
                 bool left;
-                if (d.aux & 0x80000000u) left = (a.catmasks[(size_t)(d.aux & 0x7fffffffu) * 8 + (bin >> 5)] >> (bin & 31)) & 1u;
+                if (d.aux & 0x80000000u) left = in_cat_mask(a.catmasks, d.aux, a.maskWords, bin);
                 else left = bin <= d.aux;
                 n = d.left + (left ? 0 : 1);
                 d = tn[n];
@@ -164,9 +173,9 @@ __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k
           DNode d = tn[n];
           bool moved = false;
           while (d.feature >= 0) {  // K6: LearningNode.predictImpl on binned features, resumed from the cached node
-            const uint32_t bin = tb[(size_t)d.feature * k.pitch + r];
+            const uint32_t bin = load_code(tb + (size_t)d.feature * k.pitch, r, a.codeBytes);
             bool left;
-            if (d.aux & 0x80000000u) left = (a.catmasks[(size_t)(d.aux & 0x7fffffffu) * 8 + (bin >> 5)] >> (bin & 31)) & 1u;
+            if (d.aux & 0x80000000u) left = in_cat_mask(a.catmasks, d.aux, a.maskWords, bin);
             else left = bin <= d.aux;
             n = d.left + (left ? 0 : 1);
             d = tn[n];
@@ -189,7 +198,7 @@ __global__ void __launch_bounds__(HIST_THREADS, 1) hist_kernel(const HistKArgs k
         double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
         for (int j = 0; j < a.Fsub; j++) {
           const uint2 e = fo[j];
-          const uint32_t bin = tb[(size_t)e.x * k.pitch + r];
+          const uint32_t bin = load_code(tb + (size_t)e.x * k.pitch, r, a.codeBytes);
           double* c = hb + ((size_t)e.y + bin) * 4;
           atomicAdd(c, dw);
           atomicAdd(c + 1, wy);
@@ -209,13 +218,14 @@ cudaError_t launch_hist(const HistLaunch& a, int mode, cudaStream_t s, std::stri
   // tile geometry: largest R (multiple of 128, <= 1024) whose staging fits; double-buffer when possible
   const size_t budget = 200 * 1024;
   int R = HIST_R, nbuf = 2;
-  while (R > 128 && (size_t)2 * a.F * (R + HIST_PAD) > budget) R -= 128;
-  if ((size_t)2 * a.F * (R + HIST_PAD) > budget) { nbuf = 1; R = HIST_R; while (R > 128 && (size_t)a.F * (R + HIST_PAD) > budget) R -= 128; }
-  if ((size_t)nbuf * a.F * (R + HIST_PAD) > budget) {
+  const int cb = a.codeBytes;
+  while (R > 128 && (size_t)2 * a.F * (R * cb + HIST_PAD) > budget) R -= 128;
+  if ((size_t)2 * a.F * (R * cb + HIST_PAD) > budget) { nbuf = 1; R = HIST_R; while (R > 128 && (size_t)a.F * (R * cb + HIST_PAD) > budget) R -= 128; }
+  if ((size_t)nbuf * a.F * (R * cb + HIST_PAD) > budget) {
     if (err) *err = "hist: too many features for one shared-memory tile (F > 1400 unsupported)";
     return cudaErrorInvalidValue;
   }
-  k.R = R; k.pitch = R + HIST_PAD; k.nbuf = nbuf;
+  k.R = R; k.pitch = R * cb + HIST_PAD; k.nbuf = nbuf;
   k.numTiles = (a.n_rows + R - 1) / R;
   const size_t smem = 128 + (size_t)nbuf * a.F * k.pitch;
   auto kern = mode == 0 ? hist_kernel<0> : (mode == 1 ? hist_kernel<1> : hist_kernel<2>);
@@ -311,7 +321,7 @@ __device__ __forceinline__ void bucket_rows(const BucketLaunch& a, const uint32_
         wy[u] = __shfl_sync(FULL, mywy, ri & 31);
         wyy[u] = __shfl_sync(FULL, mywyy, ri & 31);
         wv[u] = ri < nb ? (p >> 27) : 0u;
-        bin[u] = (wv[u] && active) ? a.bins_rm[(size_t)(p & 0x7ffffffu) * a.ldr + featCol] : 0u;
+        bin[u] = (wv[u] && active) ? load_code(a.bins_rm, (size_t)(p & 0x7ffffffu) * a.ldr + featCol, a.codeBytes) : 0u;
       }
 #pragma unroll
       for (int u = 0; u < 4; u++) {
@@ -521,14 +531,14 @@ __global__ void __launch_bounds__(256) part_count_kernel(const PartLaunch p) {
     const uint32_t c = task - p.chunk_prefix[k];
     const uint32_t* src = (sg.buf ? p.idx1 : p.idx0) + sg.start + (size_t)c * SEG_CH;
     const int n = (int)min((uint32_t)SEG_CH, sg.count - c * SEG_CH);
-    const uint8_t* col = p.bins + (size_t)d.feature * p.ldb;
+    const uint8_t* col = p.bins + (size_t)d.feature * p.ldb * p.codeBytes;
     const bool cat = (d.aux & 0x80000000u) != 0;
-    const uint32_t* mask = cat ? p.catmasks + (size_t)(d.aux & 0x7fffffffu) * 8 : nullptr;
+    const uint32_t* mask = cat ? p.catmasks + (size_t)(d.aux & 0x7fffffffu) * p.maskWords : nullptr;
     uint32_t cnt = 0;
     for (int i = tid; i < SEG_CH; i += 256) {
       bool left = false;
       if (i < n) {
-        const uint32_t bin = col[src[i] & 0x7ffffffu];
+        const uint32_t bin = load_code(col, src[i] & 0x7ffffffu, p.codeBytes);
         left = cat ? ((mask[bin >> 5] >> (bin & 31)) & 1u) : (bin <= d.aux);
       }
       const unsigned bal = __ballot_sync(0xffffffffu, left);
@@ -662,14 +672,13 @@ cudaError_t launch_scatter_dnodes(DNode* dnodes, const DNodeUpdate* upd, int64_t
 // =================================================================================================
 // K5: binsToBestSplit — one warp per node slot
 // =================================================================================================
-constexpr int SPLIT_WARPS = 4;
-constexpr int SPLIT_MAXB = 256;
-struct SplitSmem {
-  double raw[SPLIT_MAXB][3];
-  double cum[SPLIT_MAXB][3];
-  double key[SPLIT_MAXB];
-  uint16_t order[SPLIT_MAXB];
-};
+constexpr int SPLIT_WARPS = 4;   // at most; fewer when a warp's shared arrays (58 B per bin) would not fit
+// per-warp shared arrays, carved from dynamic shared memory: raw[maxB][3], cum[maxB][3], key[maxB] (f64), mask[maskWords] (u32),
+// order[maxB] (u16)
+__host__ __device__ inline size_t split_warp_bytes(int maxB, int maskWords) {
+  size_t b = (size_t)maxB * (3 + 3 + 1) * 8 + (size_t)maskWords * 4 + (size_t)maxB * 2;
+  return (b + 15) & ~(size_t)15;
+}
 
 __device__ __forceinline__ double variance_calc(double cnt, double sum, double sq) {  // Variance.calculate
   if (cnt == 0) return 0.0;
@@ -677,12 +686,29 @@ __device__ __forceinline__ double variance_calc(double cnt, double sum, double s
   return sl / cnt;
 }
 
+struct SplitView {   // one warp's shared arrays
+  double (*raw)[3];
+  double (*cum)[3];
+  double* key;
+  uint32_t* mask;
+  uint16_t* order;
+};
+
 __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const SplitLaunch a) {
   extern __shared__ __align__(16) unsigned char smraw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int slot = blockIdx.x * SPLIT_WARPS + warp;
+  const int warpsPerBlock = blockDim.x >> 5;
+  const int slot = blockIdx.x * warpsPerBlock + warp;
   if (slot >= a.nSlots) return;
-  SplitSmem& sm = reinterpret_cast<SplitSmem*>(smraw)[warp];
+  SplitView sm;
+  {
+    unsigned char* base = smraw + (size_t)warp * split_warp_bytes(a.maxB, a.maskWords);
+    sm.raw = reinterpret_cast<double (*)[3]>(base);
+    sm.cum = reinterpret_cast<double (*)[3]>(base + (size_t)a.maxB * 24);
+    sm.key = reinterpret_cast<double*>(base + (size_t)a.maxB * 48);
+    sm.mask = reinterpret_cast<uint32_t*>(base + (size_t)a.maxB * 56);
+    sm.order = reinterpret_cast<uint16_t*>(base + (size_t)a.maxB * 56 + (size_t)a.maskWords * 4);
+  }
   const unsigned FULL = 0xffffffffu;
 
   double P[3] = {0, 0, 0};
@@ -695,7 +721,7 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
   bool any = false;
   double bestGain = 0; int bestF = -1, bestS = -1, bestJ = -1;
   double bL[3] = {0, 0, 0}, bR[3] = {0, 0, 0};
-  uint32_t bmask[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int q = lane; q < a.maskWords; q += 32) sm.mask[q] = 0u;
   int firstF = -1;
   const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
   const double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
@@ -770,8 +796,12 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
       any = true; bestGain = lg; bestF = f; bestS = ls; bestJ = j;
       bL[0] = sm.cum[ls][0]; bL[1] = sm.cum[ls][1]; bL[2] = sm.cum[ls][2];
       bR[0] = T0 - bL[0]; bR[1] = T1 - bL[1]; bR[2] = T2 - bL[2];
-      for (int q = 0; q < 8; q++) bmask[q] = 0;
-      if (cat) for (int q = 0; q <= ls; q++) { const int c = sm.order[q]; bmask[c >> 5] |= 1u << (c & 31); }
+      // left set of the split = the first ls + 1 categories in centroid order (kept as a bit mask in shared memory)
+      __syncwarp();
+      for (int q = lane; q < a.maskWords; q += 32) sm.mask[q] = 0u;
+      __syncwarp();
+      if (cat) for (int q = lane; q <= ls; q += 32) { const int c = sm.order[q]; atomicOr(&sm.mask[c >> 5], 1u << (c & 31)); }
+      __syncwarp();
     }
   }
   (void)bestJ;
@@ -792,20 +822,25 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
       r.left[3] = bL[0]; r.right[3] = bR[0];
       r.leftImp = variance_calc(bL[0], bL[1], bL[2]);
       r.rightImp = variance_calc(bR[0], bR[1], bR[2]);
-      for (int q = 0; q < 8; q++) r.catmask[q] = bmask[q];
     }
     r.impurity = Pimp;
     r.parent[0] = P[0]; r.parent[1] = P[1]; r.parent[2] = P[2]; r.parent[3] = P[0];
     a.out[slot] = r;
   }
+  __syncwarp();
+  for (int q = lane; q < a.maskWords; q += 32) a.catmask_out[(size_t)slot * a.maskWords + q] = any ? sm.mask[q] : 0u;
 }
 
 cudaError_t launch_best_split(const SplitLaunch& a, cudaStream_t s) {
   if (a.nSlots <= 0) return cudaSuccess;
-  const size_t smem = sizeof(SplitSmem) * SPLIT_WARPS;
+  const size_t per = split_warp_bytes(a.maxB, a.maskWords);
+  int warps = (int)(((size_t)200 * 1024) / per);
+  if (warps > SPLIT_WARPS) warps = SPLIT_WARPS;
+  if (warps < 1) return cudaErrorInvalidValue;   // maxBins too large for one warp's shared arrays (checked by the trainer)
+  const size_t smem = per * warps;
   cudaError_t e = cudaFuncSetAttribute(best_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  best_split_kernel<<<(a.nSlots + SPLIT_WARPS - 1) / SPLIT_WARPS, SPLIT_WARPS * 32, smem, s>>>(a);
+  best_split_kernel<<<(a.nSlots + warps - 1) / warps, warps * 32, smem, s>>>(a);
   return cudaGetLastError();
 }
 
@@ -917,27 +952,29 @@ __global__ void __launch_bounds__(1024) find_splits_kernel(const double* sample,
 // =================================================================================================
 // K2: binning (row-major f64 -> column-major u8)
 // =================================================================================================
-constexpr int BIN_FT = 32;    // features per block
+constexpr int BIN_FT = 32;    // features per block (lanes); large maxBins use fewer so the thresholds still fit shared memory
 constexpr int BIN_RT = 128;   // rows per block
+template <typename CodeT>
 __global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, int64_t n_rows, int F, const double* thresholds,
-                                                   const int32_t* nsplits, const int32_t* arity, int maxSplits, uint8_t* bins, int64_t ldb,
-                                                   int64_t row0, int32_t* err, uint8_t* bins_rm, int64_t ldr) {
+                                                   const int32_t* nsplits, const int32_t* arity, int maxSplits, CodeT* bins, int64_t ldb,
+                                                   int64_t row0, int32_t* err, CodeT* bins_rm, int64_t ldr, int FT) {
   extern __shared__ __align__(16) unsigned char smraw[];
-  double* thr = reinterpret_cast<double*>(smraw);                                   // [BIN_FT][maxSplits]
-  uint8_t* tile = smraw + (size_t)BIN_FT * (maxSplits > 0 ? maxSplits : 1) * 8;     // [BIN_FT][BIN_RT]
-  const int f0 = blockIdx.y * BIN_FT;
+  double* thr = reinterpret_cast<double*>(smraw);                                                  // [FT][maxSplits]
+  CodeT* tile = reinterpret_cast<CodeT*>(smraw + (size_t)FT * (maxSplits > 0 ? maxSplits : 1) * 8);  // [FT][BIN_RT]
+  const int f0 = blockIdx.y * FT;
   const int64_t r0 = (int64_t)blockIdx.x * BIN_RT;
-  const int nf = min(BIN_FT, F - f0);
+  const int nf = min(FT, F - f0);
   for (int i = threadIdx.x; i < nf * maxSplits; i += blockDim.x) {
     const int ff = i / maxSplits, q = i % maxSplits;
     thr[ff * maxSplits + q] = (q < nsplits[f0 + ff]) ? thresholds[(size_t)(f0 + ff) * maxSplits + q] : INFINITY;
   }
   __syncthreads();
-  const int fl = threadIdx.x & 31;  // feature lane
-  const int rl = threadIdx.x >> 5;  // 8 rows per pass
-  for (int rr = rl; rr < BIN_RT; rr += 8) {
+  const int fl = threadIdx.x % FT;   // feature lane
+  const int rl = threadIdx.x / FT;   // 256 / FT rows per pass
+  const int rstep = 256 / FT;
+  for (int rr = rl; rr < BIN_RT; rr += rstep) {
     const int64_t row = r0 + rr;
-    uint8_t b = 0;
+    CodeT b = 0;
     if (row < n_rows && fl < nf) {
       const int f = f0 + fl;
       const double x = X[(size_t)row * ldx + f];
@@ -947,10 +984,10 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, 
         const double* t = thr + fl * maxSplits;
         int lo = 0, hi = nsplits[f];
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (t[mid] < x) lo = mid + 1; else hi = mid; }
-        b = (uint8_t)lo;
+        b = (CodeT)lo;
       } else {
         if (x < 0 || x >= (double)ar) atomicMax(err, f + 1);
-        b = (uint8_t)(int)x;
+        b = (CodeT)(int)x;
       }
     }
     tile[fl * BIN_RT + rr] = b;
@@ -958,14 +995,15 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, 
   }
   __syncthreads();
   // coalesced column-major stores: 32-bit words
-  const int words = nf * (BIN_RT / 4);
+  constexpr int PER = 4 / (int)sizeof(CodeT);   // codes per word
+  const int words = nf * (BIN_RT / PER);
   for (int i = threadIdx.x; i < words; i += blockDim.x) {
-    const int ff = i / (BIN_RT / 4), wq = i % (BIN_RT / 4);
-    const int64_t row = r0 + wq * 4;
-    if (row + 3 < n_rows && ((row0 + row) & 3) == 0) {
-      *reinterpret_cast<uint32_t*>(bins + (size_t)(f0 + ff) * ldb + row0 + row) = *reinterpret_cast<const uint32_t*>(tile + ff * BIN_RT + wq * 4);
+    const int ff = i / (BIN_RT / PER), wq = i % (BIN_RT / PER);
+    const int64_t row = r0 + wq * PER;
+    if (row + PER - 1 < n_rows && ((row0 + row) % PER) == 0) {
+      *reinterpret_cast<uint32_t*>(bins + (size_t)(f0 + ff) * ldb + row0 + row) = *reinterpret_cast<const uint32_t*>(tile + ff * BIN_RT + wq * PER);
     } else {
-      for (int q = 0; q < 4; q++) if (row + q < n_rows) bins[(size_t)(f0 + ff) * ldb + row0 + row + q] = tile[ff * BIN_RT + wq * 4 + q];
+      for (int q = 0; q < PER; q++) if (row + q < n_rows) bins[(size_t)(f0 + ff) * ldb + row0 + row + q] = tile[ff * BIN_RT + wq * PER + q];
     }
   }
 }
@@ -1276,15 +1314,28 @@ int b2rf_find_splits_noalloc(const double* d_sample, int64_t n_sample, int32_t F
 }
 
 int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const double* d_thresholds, const int32_t* d_nsplits,
-             const int32_t* d_arity, int32_t maxSplits, uint8_t* d_bins, int64_t ldb, int64_t row0, int32_t* d_err, uint8_t* d_bins_rm,
-             int64_t ldr, void* stream) {
-  if (F <= 0 || maxSplits < 0 || maxSplits > 255) { set_error("b2rf_bin: maxBins must be <= 256 for uint8 bin codes"); return B2RF_ERR_ARG; }
+             const int32_t* d_arity, int32_t maxSplits, void* d_bins, int64_t ldb, int64_t row0, int32_t* d_err, void* d_bins_rm,
+             int64_t ldr, int32_t code_bytes, void* stream) {
+  if (F <= 0 || maxSplits < 0 || (code_bytes != 1 && code_bytes != 2) || (code_bytes == 1 && maxSplits > 255) || maxSplits > 65534) {
+    set_error("b2rf_bin: code_bytes must be 1 (maxBins <= 256) or 2 (maxBins <= 65535)"); return B2RF_ERR_ARG;
+  }
   if (n_rows <= 0) return B2RF_OK;
   const int ms = maxSplits > 0 ? maxSplits : 1;
-  const size_t smem = (size_t)BIN_FT * ms * 8 + (size_t)BIN_FT * BIN_RT;
-  if (!cuda_ok(cudaFuncSetAttribute(bin_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bin attr")) return B2RF_ERR_CUDA;
-  dim3 grid((unsigned)((n_rows + BIN_RT - 1) / BIN_RT), (unsigned)((F + BIN_FT - 1) / BIN_FT));
-  bin_kernel<<<grid, 256, smem, (cudaStream_t)stream>>>(d_X, ldx, n_rows, F, d_thresholds, d_nsplits, d_arity, ms, d_bins, ldb, row0, d_err, d_bins_rm, ldr);
+  int FT = BIN_FT;
+  while (FT > 1 && (size_t)FT * ms * 8 + (size_t)FT * BIN_RT * code_bytes > (size_t)160 * 1024) FT /= 2;
+  const size_t smem = (size_t)FT * ms * 8 + (size_t)FT * BIN_RT * code_bytes;
+  if (smem > (size_t)220 * 1024) { set_error("b2rf_bin: maxBins too large for the shared-memory threshold table"); return B2RF_ERR_ARG; }
+  dim3 grid((unsigned)((n_rows + BIN_RT - 1) / BIN_RT), (unsigned)((F + FT - 1) / FT));
+  cudaStream_t s = (cudaStream_t)stream;
+  if (code_bytes == 1) {
+    if (!cuda_ok(cudaFuncSetAttribute(bin_kernel<uint8_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bin attr")) return B2RF_ERR_CUDA;
+    bin_kernel<uint8_t><<<grid, 256, smem, s>>>(d_X, ldx, n_rows, F, d_thresholds, d_nsplits, d_arity, ms, (uint8_t*)d_bins, ldb, row0, d_err,
+                                               (uint8_t*)d_bins_rm, ldr, FT);
+  } else {
+    if (!cuda_ok(cudaFuncSetAttribute(bin_kernel<uint16_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bin attr")) return B2RF_ERR_CUDA;
+    bin_kernel<uint16_t><<<grid, 256, smem, s>>>(d_X, ldx, n_rows, F, d_thresholds, d_nsplits, d_arity, ms, (uint16_t*)d_bins, ldb, row0, d_err,
+                                                (uint16_t*)d_bins_rm, ldr, FT);
+  }
   return cuda_ok(cudaGetLastError(), "b2rf_bin") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
@@ -1312,12 +1363,13 @@ int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t par
   return ok ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
-int b2rf_hist_build(const uint8_t* d_bins, int64_t ldb, int32_t F, const double* d_y, const uint8_t* d_w, int64_t ldw,
+int b2rf_hist_build(const void* d_bins, int64_t ldb, int32_t code_bytes, int32_t F, const double* d_y, const uint8_t* d_w, int64_t ldw,
                     const int32_t* d_slot_of_row, int64_t ldn, const int32_t* d_tree_ids, int32_t Tg, int64_t n_rows,
                     const uint32_t* d_slot_fo, const int64_t* d_slot_base, int32_t Fsub, double* d_hist, void* stream) {
+  if (code_bytes != 1 && code_bytes != 2) { set_error("b2rf_hist_build: code_bytes must be 1 or 2"); return B2RF_ERR_ARG; }
   if ((ldb & 15) != 0 || ldb < n_rows) { set_error("b2rf_hist_build: ldb must be a multiple of 16 and >= n_rows (128 recommended)"); return B2RF_ERR_ARG; }
   HistLaunch a;
-  a.bins = d_bins; a.ldb = ldb; a.F = F; a.y = d_y; a.w = d_w; a.ldw = ldw;
+  a.bins = static_cast<const uint8_t*>(d_bins); a.ldb = ldb; a.F = F; a.y = d_y; a.w = d_w; a.ldw = ldw; a.codeBytes = code_bytes; a.maskWords = 8;
   a.node = const_cast<int32_t*>(d_slot_of_row); a.ldn = ldn; a.tree_ids = d_tree_ids; a.Tg = Tg; a.n_rows = n_rows;
   a.dnodes = nullptr; a.nodeStride = 0; a.catmasks = nullptr;
   a.slot_fo = reinterpret_cast<const uint2*>(d_slot_fo); a.slot_base = d_slot_base; a.Fsub = Fsub; a.hist = d_hist; a.slot_count = nullptr;

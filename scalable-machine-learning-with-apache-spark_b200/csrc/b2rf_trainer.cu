@@ -201,6 +201,8 @@ struct b2rf_trainer {
   int32_t F = 0, T = 0;
   int64_t numExamples = 0;
   int32_t maxPossibleBins = 0, maxSplits = 0, Fsub = 0;
+  int32_t codeBytes = 1;    // bytes per bin code: 1 (maxBins <= 256) or 2
+  int32_t maskWords = 8;    // 32-bit words per categorical left-set mask = ceil(max arity / 32)
   bool subsampling = false;
   double minWeightPerNode = 0;
   std::vector<int32_t> arity, numBins;
@@ -236,6 +238,8 @@ struct b2rf_trainer {
   DevBuf<double> dParent;
   DevBuf<int32_t> dHasParent, dNumBins, dIsCat, dTreeIds;
   DevBuf<SplitRec> dRec;
+  DevBuf<uint32_t> dRecMask;
+  PinBuf<uint32_t> hRecMask;
   DevBuf<uint32_t> dSlotCount, dCursor, dChunkPrefix, dRowList;
   DevBuf<uint64_t> dSlotStart;
   DevBuf<int32_t> dSlotCells;
@@ -283,6 +287,7 @@ struct b2rf_trainer {
     dHasParent.release(); dNumBins.release(); dIsCat.release(); dTreeIds.release(); dRec.release();
     dSeg.release(); dIdx0.release(); dIdx1.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
     dSlotPos.release(); dSplitPos.release(); hSlotPos.release(); hSplitPos.release();
+    dRecMask.release(); hRecMask.release();
     dSlotCount.release(); dCursor.release(); dChunkPrefix.release(); dRowList.release(); dSlotStart.release(); dSlotCells.release(); hSlotCells.release();
     hUpd.release(); hSlotFo.release(); hSlotBase.release(); hParent.release(); hHasParent.release(); hTreeIds.release(); hRec.release();
     if (ev0) cudaEventDestroy(ev0);
@@ -359,7 +364,9 @@ int b2rf_trainer_create(const b2rf_params* params, int32_t F, const int32_t* h_a
   { int mpb = 0; const int rc = check_arity(params->maxBins, F, h_arity, numExamples, &mpb); if (rc) { delete t; return rc; } t->maxPossibleBins = mpb; }
   t->maxSplits = std::max(t->maxPossibleBins - 1, 1);
   t->arity.assign(h_arity, h_arity + F);
-  if (t->maxPossibleBins > 256) { set_error("b2rf: maxBins > 256 needs uint16 bin codes, not built yet"); delete t; return B2RF_ERR_ARG; }
+  if (t->maxPossibleBins > 2048) { set_error("b2rf: maxBins > 2048 is not supported (split-scan shared-memory arrays)"); delete t; return B2RF_ERR_ARG; }
+  t->codeBytes = t->maxPossibleBins > 256 ? 2 : 1;
+  { int maxAr = 1; for (int f = 0; f < F; f++) maxAr = std::max(maxAr, h_arity[f]); t->maskWords = std::max(1, (std::max(maxAr, t->maxPossibleBins) + 31) / 32); }
   t->numBins.assign(F, t->maxPossibleBins);
   for (int f = 0; f < F; f++) {
     if (h_arity[f] > 1) t->numBins[f] = h_arity[f];
@@ -392,9 +399,13 @@ int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t) {
   return std::max<int64_t>(worstNode, std::min<int64_t>(byMem, maxNodesTotal * worstNode));
 }
 
-int b2rf_trainer_bind(b2rf_trainer* t, const uint8_t* d_bins, int64_t ldb, const uint8_t* d_bins_rm, int64_t ldr, const double* d_y,
+int b2rf_trainer_code_bytes(const b2rf_trainer* t) { return t ? t->codeBytes : 0; }
+
+int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const void* d_bins_rm_v, int64_t ldr, const double* d_y,
                       const uint8_t* d_w, int64_t ldw, int32_t* d_node, int64_t ldn, int64_t n_rows_local, double* d_hist, int64_t hist_cells) {
-  if (!t || !d_bins || !d_y || !d_w || !d_hist || n_rows_local < 0 || (ldb & 15) || ldb < n_rows_local || ldw < n_rows_local || (d_node && ldn < n_rows_local)) {
+  const uint8_t* d_bins = static_cast<const uint8_t*>(d_bins_v);
+  const uint8_t* d_bins_rm = static_cast<const uint8_t*>(d_bins_rm_v);
+  if (!t || !d_bins || !d_y || !d_w || !d_hist || n_rows_local < 0 || ((ldb * (t ? t->codeBytes : 1)) & 15) || ldb < n_rows_local || ldw < n_rows_local || (d_node && ldn < n_rows_local)) {
     set_error("b2rf_trainer_bind: bad argument (ldb must be a multiple of 16 and every leading dimension >= n_rows)"); return B2RF_ERR_ARG;
   }
   t->d_bins = d_bins; t->ldb = ldb; t->d_y = d_y; t->d_w = d_w; t->ldw = ldw; t->d_node = d_node; t->ldn = ldn; t->nLocal = n_rows_local;
@@ -562,7 +573,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   // ---- descriptors ----
   if (!t->hSlotFo.ensure(nSlots * t->Fsub) || !t->hSlotBase.ensure(nSlots) || !t->hParent.ensure(nSlots * 4) || !t->hHasParent.ensure(nSlots) ||
       !t->dSlotFo.ensure(nSlots * t->Fsub) || !t->dSlotBase.ensure(nSlots) || !t->dParent.ensure(nSlots * 4) || !t->dHasParent.ensure(nSlots) ||
-      !t->dRec.ensure(nSlots) || !t->hRec.ensure(nSlots) || !t->hTreeIds.ensure(t->T) || !t->dTreeIds.ensure(t->T))
+      !t->dRec.ensure(nSlots) || !t->hRec.ensure(nSlots) || !t->dRecMask.ensure(nSlots * t->maskWords) || !t->hRecMask.ensure(nSlots * t->maskWords) || !t->hTreeIds.ensure(t->T) || !t->dTreeIds.ensure(t->T))
     return B2RF_ERR_CUDA;
   int64_t maxNodes = 0;
   for (size_t sl = 0; sl < nSlots; sl++) {
@@ -610,6 +621,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   a.bins = t->d_bins; a.ldb = t->ldb; a.F = t->F; a.y = t->d_y; a.w = t->d_w; a.ldw = t->ldw; a.node = t->d_node; a.ldn = t->ldn;
   a.n_rows = t->nLocal; a.dnodes = t->dn.p; a.nodeStride = t->nodeStride; a.catmasks = t->dCat.p;
   a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.hist = t->d_hist; a.slot_count = nullptr;
+  a.codeBytes = t->codeBytes; a.maskWords = t->maskWords;
   if (t->bucketMode) {
     // shared-memory histograms per (slot, chunk).  Segment mode: every pending node already owns a contiguous row segment
     // (kept by the stable partitions launched from end_group).  Sort mode: counting sort of the group's rows by slot.
@@ -645,7 +657,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     BucketLaunch b;
     b.bins_rm = t->d_bins_rm; b.ldr = t->ldr; b.y = t->d_y; b.rowlist = t->dRowList.p; b.slot_start = t->dSlotStart.p; b.slot_count = t->dSlotCount.p;
     b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->segMode ? SEG_CH : t->chunkRows; b.slot_fo = t->dSlotFo.p;
-    b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.padB = padB; b.G = G; b.hist = t->d_hist;
+    b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.padB = padB; b.G = G; b.codeBytes = t->codeBytes; b.hist = t->d_hist;
     b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr;
     std::string err;
     cudaError_t e;
@@ -693,10 +705,12 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   a.hist = t->d_hist; a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.nSlots = (int32_t)nSlots;
   a.parent4 = t->dParent.p; a.hasParent = t->dHasParent.p; a.numBins = t->dNumBins.p; a.isCat = t->dIsCat.p;
   a.minInstances = (double)t->p.minInstancesPerNode; a.minWeight = t->minWeightPerNode; a.minInfoGain = t->p.minInfoGain;
-  a.out = t->dRec.p;
+  a.out = t->dRec.p; a.catmask_out = t->dRecMask.p; a.maskWords = t->maskWords;
+  a.maxB = *std::max_element(t->numBins.begin(), t->numBins.end());
   if (!cuda_ok(launch_best_split(a, s), "best_split launch")) return B2RF_ERR_CUDA;
   t->nKernels++;
   if (!cuda_ok(cudaMemcpyAsync(t->hRec.p, t->dRec.p, nSlots * sizeof(SplitRec), cudaMemcpyDeviceToHost, s), "download split records")) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaMemcpyAsync(t->hRecMask.p, t->dRecMask.p, nSlots * t->maskWords * 4, cudaMemcpyDeviceToHost, s), "download split masks")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
   const double tc0 = now_s();
   if (t->evPending) { float ms = 0; if (cudaEventElapsedTime(&ms, t->ev0, t->ev1) == cudaSuccess) t->tHist += ms * 1e-3; t->evPending = false; }
@@ -725,7 +739,12 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
       if (!isLeaf) {
         n.hasSplit = true; n.feature = r.feature;
         if (t->arity[r.feature] == 0) { n.splitBin = r.splitIdx; n.threshold = t->thresholds[(size_t)r.feature * t->maxSplits + r.splitIdx]; }
-        else { n.catMaskIdx = (int32_t)(t->catPool.size() / 8); t->catPool.insert(t->catPool.end(), r.catmask, r.catmask + 8); n.splitBin = r.splitIdx; }
+        else {
+          const uint32_t* m = t->hRecMask.p + (size_t)sl * t->maskWords;
+          n.catMaskIdx = (int32_t)(t->catPool.size() / t->maskWords);
+          t->catPool.insert(t->catPool.end(), m, m + t->maskWords);
+          n.splitBin = r.splitIdx;
+        }
         const bool childLeaf = (lvl + 1) == t->p.maxDepth;
         const bool lLeaf = childLeaf || std::fabs(r.leftImp) < 0x1.0p-52;
         const bool rLeaf = childLeaf || std::fabs(r.rightImp) < 0x1.0p-52;
@@ -766,7 +785,7 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
     PartLaunch pl;
     pl.split_pos = t->dSplitPos.p; pl.nSplits = (int32_t)k; pl.dnodes = t->dn.p; pl.dseg = t->dSeg.p; pl.catmasks = t->dCat.p;
     pl.bins = t->d_bins; pl.ldb = t->ldb; pl.idx0 = t->dIdx0.p; pl.idx1 = t->dIdx1.p; pl.chunk_prefix = t->dPartPrefix.p;
-    pl.left_cnt = t->dLeftCnt.p; pl.left_off = t->dLeftOff.p; pl.predbits = t->dPredBits.p;
+    pl.left_cnt = t->dLeftCnt.p; pl.left_off = t->dLeftOff.p; pl.predbits = t->dPredBits.p; pl.codeBytes = t->codeBytes; pl.maskWords = t->maskWords;
     if (!cuda_ok(launch_partition(pl, s), "partition launch")) return B2RF_ERR_CUDA;
     t->nKernels += 4;
   }
@@ -818,9 +837,9 @@ static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
     if (n.catMaskIdx >= 0) {
       t->x_ncat[at] = t->numBins[n.feature];
       t->x_cat_off[at] = (int32_t)t->x_cats.size();
-      const uint32_t* m = &t->catPool[(size_t)n.catMaskIdx * 8];
+      const uint32_t* m = &t->catPool[(size_t)n.catMaskIdx * t->maskWords];
       int cnt = 0;
-      for (int c = 0; c < 256; c++) if ((m[c >> 5] >> (c & 31)) & 1u) { t->x_cats.push_back((double)c); cnt++; }
+      for (int c = 0; c < t->maskWords * 32; c++) if ((m[c >> 5] >> (c & 31)) & 1u) { t->x_cats.push_back((double)c); cnt++; }
       t->x_cat_len[at] = cnt;
     }
     return me;

@@ -98,14 +98,17 @@ def bin_features(X: torch.Tensor, thresholds: torch.Tensor, nsplits: torch.Tenso
     n, F = X.shape
     if X.stride(1) != 1:
         X = X.contiguous()
+    code_dt = torch.uint8 if thresholds.shape[1] <= 255 else torch.int16      # uint16 codes are stored in int16 tensors
     if bins is None:
-        bins = torch.zeros((F, _pad(row0 + n)), dtype=torch.uint8, device=X.device)
+        bins = torch.zeros((F, _pad(row0 + n)), dtype=code_dt, device=X.device)
+    if bins.dtype != code_dt or (bins_rm is not None and bins_rm.dtype != code_dt):
+        raise TypeError(f"bin matrices must be {code_dt} for maxBins = {thresholds.shape[1] + 1}")
     err = _bin_err.get(X.device)
     if err is None:
         err = _bin_err[X.device] = torch.zeros(1, dtype=torch.int32, device=X.device)
     check(lib().b2rf_bin(X.data_ptr(), X.stride(0), n, F, thresholds.data_ptr(), nsplits.data_ptr(), arity.data_ptr(), thresholds.shape[1],
                          bins.data_ptr(), bins.stride(0), row0, err.data_ptr(), 0 if bins_rm is None else bins_rm.data_ptr(),
-                         0 if bins_rm is None else bins_rm.stride(0), _stream()))
+                         0 if bins_rm is None else bins_rm.stride(0), bins.element_size(), _stream()))
     if check_errors:
         _raise_bin_errors(arity)
     return bins
@@ -128,7 +131,7 @@ def bag(seed: int, part_offsets, part0: int, T: int, rate: float, bootstrap: boo
 def hist_build(bins, y, w, slot_of_row, tree_ids, slot_fo, slot_base, n_rows, total_cells):
     """K4 stand-alone.  Returns hist f64 [total_cells, 4]."""
     hist = torch.zeros((total_cells, 4), dtype=torch.float64, device=bins.device)
-    check(lib().b2rf_hist_build(bins.data_ptr(), bins.stride(0), bins.shape[0], y.data_ptr(), w.data_ptr(), w.stride(0), slot_of_row.data_ptr(),
+    check(lib().b2rf_hist_build(bins.data_ptr(), bins.stride(0), bins.element_size(), bins.shape[0], y.data_ptr(), w.data_ptr(), w.stride(0), slot_of_row.data_ptr(),
                                 slot_of_row.stride(0), tree_ids.data_ptr(), tree_ids.numel(), n_rows, slot_fo.data_ptr(), slot_base.data_ptr(),
                                 slot_fo.shape[1], hist.data_ptr(), _stream()))
     return hist
@@ -268,8 +271,9 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         if prebinned is not None:
             bins, bins_rm = prebinned
         else:
-            bins = torch.empty((F, ld), dtype=torch.uint8, device=dev)
-            bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=torch.uint8, device=dev) if hist_mode != "scan" else None
+            code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
+            bins = torch.empty((F, ld), dtype=code_dt, device=dev)
+            bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
             bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm)
         w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
                       want_node=(hist_mode not in ("segment", "bucket") or bins_rm is None))
@@ -338,8 +342,9 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
         ns_h = ns.cpu().numpy()
         t1 = time.perf_counter()
         # K2 streamed over row chunks
-        bins = torch.empty((F, ld), dtype=torch.uint8, device=dev)
-        bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=torch.uint8, device=dev) if hist_mode != "scan" else None
+        code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
+        bins = torch.empty((F, ld), dtype=code_dt, device=dev)
+        bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
         chunk_rows = max(1, min(chunk_rows, n_local))
         stage = [torch.empty((chunk_rows, F), dtype=torch.float64, device=dev) for _ in range(2)]
         copied = [torch.cuda.Event() for _ in range(2)]

