@@ -30,6 +30,7 @@ WORKLOADS = {
     "C3": dict(rows=10_000_000, F=64, numTrees=100, maxDepth=10, maxBins=64, gen="c3"),
     "C3-small": dict(rows=1_000_000, F=64, numTrees=20, maxDepth=8, maxBins=64, gen="c3"),
     "C4-shard": dict(rows=12_500_000, F=128, numTrees=100, maxDepth=12, maxBins=256, gen="c4"),
+    "C4-cont": dict(rows=12_500_000, F=128, numTrees=50, maxDepth=10, maxBins=256, gen="c3"),   # C4's shape without categorical features
 }
 ROWS_PER_PARTITION = 4096   # emulated Spark partition size (bagging streams are per partition; stated in config)
 # ncu --set full capture of the dominant kernel (profiles/r01_ncu_bucket_hist_c3.md): DRAM bytes of one whole-level launch

@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO = os.path.join(HERE, "libb2rf.so")
+SO = os.environ.get("B2RF_LIB") or os.path.join(HERE, "libb2rf.so")   # B2RF_LIB: A/B-test another build of the library
 
 B2RF_OK, ERR_ARG, ERR_MAXBINS, ERR_DATA, ERR_CUDA, ERR_STATE = 0, -1, -2, -3, -4, -5
 

@@ -295,14 +295,16 @@ __global__ void __launch_bounds__(256) scatter_rows_kernel(const int32_t* node, 
   }
 }
 
-constexpr int BUCKET_THREADS = 256;
+constexpr int BUCKET_THREADS = 256;   // default; tasks whose histogram leaves room for only one or two CTAs per SM run 512 threads
+// ---- dedicated instantiation for the common case: uint8 codes, at most 32 features per node, lane == feature ----
+// (kept as its own small kernel: the general kernel below handles feature groups, uint16 codes and 512-thread CTAs, and
+// folding this case into it cost 5-10 % of K4 time in same-box A/B runs: 0.657 s vs 0.69-0.73 s per C3 fit)
 // Rows [0, n) of one (slot, chunk) task, one warp row-block at a time.  Lane k of a warp owns row k of the current 32-row
 // block: it fetches the packed entry and the label once and forms (w, w*y, w*y*y); the values are then broadcast row by row
 // while every lane (== feature) gathers its own bin code and updates its own histogram column.
 template <bool DIRECT>
-__device__ __forceinline__ void bucket_rows(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
-                                            double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
-                                            int R, int r) {   // R rows per warp instruction (32 / feature-group width); r = this lane's row slot
+__device__ __forceinline__ void bucket_rows32(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
+                                            double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep) {
   constexpr int W = BUCKET_THREADS / 32;
   const unsigned FULL = 0xffffffffu;
   for (int base = warp * 32; base < n; base += W * 32) {
@@ -312,16 +314,15 @@ __device__ __forceinline__ void bucket_rows(const BucketLaunch& a, const uint32_
     const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
     const double mywyy = mywy * myy;
     const int nb = min(32, n - base);
-    for (int q = 0; q < nb; q += 4 * R) {
+    for (int q = 0; q < nb; q += 4) {
       uint32_t bin[4], wv[4]; double wy[4], wyy[4];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
-        const int ri = q + u * R + r;
-        const uint32_t p = __shfl_sync(FULL, mine, ri & 31);
-        wy[u] = __shfl_sync(FULL, mywy, ri & 31);
-        wyy[u] = __shfl_sync(FULL, mywyy, ri & 31);
-        wv[u] = ri < nb ? (p >> 27) : 0u;
-        bin[u] = (wv[u] && active) ? load_code(a.bins_rm, (size_t)(p & 0x7ffffffu) * a.ldr + featCol, a.codeBytes) : 0u;
+        const uint32_t p = __shfl_sync(FULL, mine, (q + u) & 31);
+        wy[u] = __shfl_sync(FULL, mywy, (q + u) & 31);
+        wyy[u] = __shfl_sync(FULL, mywyy, (q + u) & 31);
+        wv[u] = (q + u) < nb ? (p >> 27) : 0u;
+        bin[u] = (wv[u] && active) ? a.bins_rm[(size_t)(p & 0x7ffffffu) * a.ldr + featCol] : 0u;
       }
 #pragma unroll
       for (int u = 0; u < 4; u++) {
@@ -339,7 +340,113 @@ __device__ __forceinline__ void bucket_rows(const BucketLaunch& a, const uint32_
   }
 }
 
-__global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const BucketLaunch a) {
+__global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist32_kernel(const BucketLaunch a) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  double* ssum = reinterpret_cast<double*>(smraw);
+  double* ssq = ssum + a.maxCells;
+  unsigned* scnt = reinterpret_cast<unsigned*>(ssq + a.maxCells);
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const uint32_t total = a.chunk_prefix[a.nSlots];
+  for (uint32_t task = blockIdx.x; task < total; task += gridDim.x) {
+    int lo = 0, hi = a.nSlots;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.chunk_prefix[mid] <= task) lo = mid; else hi = mid; }
+    const int slot = lo;
+    const uint32_t chunk = task - a.chunk_prefix[slot];
+    uint32_t cnt; const uint32_t* rl;
+    const uint32_t begin = chunk * (uint32_t)a.CH;
+    if (a.dseg != nullptr) {
+      const DSeg sg = a.dseg[a.slot_pos[slot]];
+      cnt = sg.count;
+      rl = (sg.buf ? a.idx1 : a.idx0) + sg.start + begin;
+    } else {
+      cnt = a.slot_count[slot];
+      rl = a.rowlist + a.slot_start[slot] + begin;
+    }
+    const int n = (int)min((uint32_t)a.CH, cnt - begin);
+    const int ncell = a.slot_cells[slot];
+    const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
+    double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
+    // Shared layout.  padded (padB > 0): cell (feature j, bin b) sits at ((j/32)*padB + b)*32 + j%32, i.e. bank == lane: the
+    // lanes of a warp (lane == feature) can never conflict, whatever their bins.  compact: cell = feature offset + bin.
+    const int padB = a.padB;
+    const int scells = padB > 0 ? ((a.Fsub + 31) / 32) * padB * 32 : ncell;
+    const bool direct = (int64_t)n * a.Fsub < (int64_t)ncell || scells > a.maxCells;   // few rows: skip the shared-memory round trip
+    if (!direct) {
+      for (int c = tid; c < scells; c += BUCKET_THREADS) { ssum[c] = 0.0; ssq[c] = 0.0; scnt[c] = 0u; }
+      __syncthreads();
+    }
+    for (int j0 = 0; j0 < a.Fsub; j0 += 32) {
+      const int j = j0 + lane;
+      const bool active = j < a.Fsub;
+      const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
+      const uint32_t sbase = padB > 0 ? (uint32_t)((j0 >> 5) * padB * 32 + lane) : e.y;   // shared-memory cell of bin 0
+      const uint32_t sstep = padB > 0 ? 32u : 1u;
+      if (direct) bucket_rows32<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep);
+      else bucket_rows32<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep);
+    }
+    if (!direct) {
+      __syncthreads();
+      for (int c = tid; c < scells; c += BUCKET_THREADS) {
+        const unsigned k = scnt[c];
+        if (!k) continue;
+        size_t gc = (size_t)c;
+        if (padB > 0) { const int jj = (c / (padB * 32)) * 32 + (c & 31); gc = (size_t)fo[jj].y + (size_t)((c >> 5) % padB); }   // untouched cells of idle lanes stay 0
+        double* g = hb + gc * 4;
+        atomicAdd(g, (double)k); atomicAdd(g + 1, ssum[c]); atomicAdd(g + 2, ssq[c]);
+      }
+      __syncthreads();
+    }
+  }
+}
+
+// Rows [0, n) of one (slot, chunk) task, one warp row-block at a time.  Lane k of a warp owns row k of the current 32-row
+// block: it fetches the packed entry and the label once and forms (w, w*y, w*y*y); the values are then broadcast row by row
+// while every lane (row slot r = lane / G, feature fl = lane % G) gathers its own bin code and updates its own cell.
+// ONE_ROW (G == 32) and the code width CB are compile-time in the hot instantiations; CB == 0 reads a.codeBytes.
+template <bool DIRECT, int THREADS, bool ONE_ROW, int CB>
+__device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
+                                                 double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
+                                                 int Rrt, int rrt) {
+  const int R = ONE_ROW ? 1 : Rrt, r = ONE_ROW ? 0 : rrt;
+  constexpr int W = THREADS / 32;
+  const unsigned FULL = 0xffffffffu;
+  for (int base = warp * 32; base < n; base += W * 32) {
+    const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;          // w == 0 marks padding
+    const uint32_t myw = mine >> 27;
+    const double myy = myw ? a.y[mine & 0x7ffffffu] : 0.0;
+    const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
+    const double mywyy = mywy * myy;
+    const int nb = min(32, n - base);
+    for (int q = 0; q < nb; q += 4 * R) {
+      uint32_t bin[4], wv[4]; double wy[4], wyy[4];
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        const int ri = q + u * R + r;
+        const uint32_t p = __shfl_sync(FULL, mine, ri & 31);
+        wy[u] = __shfl_sync(FULL, mywy, ri & 31);
+        wyy[u] = __shfl_sync(FULL, mywyy, ri & 31);
+        wv[u] = ri < nb ? (p >> 27) : 0u;
+        bin[u] = (wv[u] && active) ? load_code(a.bins_rm, (size_t)(p & 0x7ffffffu) * a.ldr + featCol, CB ? CB : a.codeBytes) : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; u++) {
+        if (wv[u] != 0u && active) {
+          if (DIRECT) {
+            double* c = hb + (size_t)(gbase + bin[u]) * 4;
+            atomicAdd(c, (double)wv[u]); atomicAdd(c + 1, wy[u]); atomicAdd(c + 2, wyy[u]);
+          } else {
+            const uint32_t cell = sbase + bin[u] * sstep;
+            atomicAdd(&scnt[cell], wv[u]); atomicAdd(&ssum[cell], wy[u]); atomicAdd(&ssq[cell], wyy[u]);
+          }
+        }
+      }
+    }
+  }
+}
+// One instantiation per (block size, rows per warp instruction, code width, shared layout): each kernel carries exactly two
+// copies of the row loop (shared-memory path, direct path), which keeps the hot loop's instruction footprint small.
+template <int THREADS, bool ONE_ROW, int CB, bool PADDED>
+__global__ void __launch_bounds__(THREADS) bucket_hist_kernel(const BucketLaunch a) {
   extern __shared__ __align__(16) unsigned char smraw[];
   double* ssum = reinterpret_cast<double*>(smraw);
   double* ssq = ssum + a.maxCells;
@@ -350,9 +457,9 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
   // with bank == lane for G == 32 (no conflict possible) and at most 32/G-way conflicts otherwise, and the task's histogram is
   // padB*G cells whatever the feature count, so several CTAs fit per SM even for 256 bins.  compact (padB == 0): one task per
   // (slot, chunk) with cell = feature offset + bin.
-  const int padB = a.padB;
-  const int G = padB > 0 ? a.G : 32;
-  const int nG = padB > 0 ? (a.Fsub + G - 1) / G : 1;
+  const int padB = PADDED ? a.padB : 0;
+  const int G = PADDED ? (ONE_ROW ? 32 : a.G) : 32;
+  const int nG = PADDED ? (a.Fsub + G - 1) / G : 1;
   const uint32_t total = a.chunk_prefix[a.nSlots] * (uint32_t)nG;
   for (uint32_t task = blockIdx.x; task < total; task += gridDim.x) {
     const uint32_t bt = task / (uint32_t)nG;
@@ -375,41 +482,73 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist_kernel(const Bucke
     const int ncell = a.slot_cells[slot];
     const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
     double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
-    const int scells = padB > 0 ? padB * G : ncell;
+    const int scells = PADDED ? padB * G : ncell;
     const bool direct = (int64_t)n * a.Fsub < (int64_t)ncell || scells > a.maxCells;   // few rows: skip the shared-memory round trip
     if (!direct) {
-      for (int c = tid; c < scells; c += BUCKET_THREADS) { ssum[c] = 0.0; ssq[c] = 0.0; scnt[c] = 0u; }
+      for (int c = tid; c < scells; c += THREADS) { ssum[c] = 0.0; ssq[c] = 0.0; scnt[c] = 0u; }
       __syncthreads();
     }
-    if (padB > 0) {
+    if (PADDED) {
       const int fl = lane & (G - 1), r = lane / G;
       const int j = g * G + fl;
       const bool active = j < a.Fsub;
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
-      if (direct) bucket_rows<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r);
-      else bucket_rows<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r);
+      if (direct) bucket_rows_impl<true, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 32 / G, r);
+      else bucket_rows_impl<false, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r);
     } else {
       for (int j0 = 0; j0 < a.Fsub; j0 += 32) {
         const int j = j0 + lane;
         const bool active = j < a.Fsub;
         const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
-        if (direct) bucket_rows<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0);
-        else bucket_rows<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0);
+        if (direct) bucket_rows_impl<true, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 1, 0);
+        else bucket_rows_impl<false, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0);
       }
     }
     if (!direct) {
       __syncthreads();
-      for (int c = tid; c < scells; c += BUCKET_THREADS) {
+      for (int c = tid; c < scells; c += THREADS) {
         const unsigned k = scnt[c];
         if (!k) continue;
         size_t gc = (size_t)c;
-        if (padB > 0) gc = (size_t)fo[g * G + (c & (G - 1))].y + (size_t)(c / G);   // cells of idle lanes are never touched, so k == 0 there
+        if (PADDED) gc = (size_t)fo[g * G + (c & (G - 1))].y + (size_t)(c / G);   // cells of idle lanes are never touched, so k == 0 there
         double* gp = hb + gc * 4;
         atomicAdd(gp, (double)k); atomicAdd(gp + 1, ssum[c]); atomicAdd(gp + 2, ssq[c]);
       }
       __syncthreads();
     }
   }
+}
+
+// picks the instantiation whose hot loop matches the launch (block size, one row per instruction or several, code width, layout)
+static cudaError_t launch_bucket_kernel(const BucketLaunch& b, int grid, int threads, size_t smem, cudaStream_t s) {
+  if (b.padB > 0 && b.G == 32 && b.Fsub <= 32 && b.codeBytes == 1 && threads == BUCKET_THREADS) {
+    cudaError_t e = cudaFuncSetAttribute(bucket_hist32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    bucket_hist32_kernel<<<grid, BUCKET_THREADS, smem, s>>>(b);
+    return cudaGetLastError();
+  }
+  const bool padded = b.padB > 0;
+  const bool one = padded && b.G == 32;
+  const int cb = b.codeBytes;
+#define B2RF_LAUNCH_BUCKET(T, O, C, P)                                                                                 \
+  do {                                                                                                                 \
+    cudaError_t e_ = cudaFuncSetAttribute(bucket_hist_kernel<T, O, C, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+    if (e_ != cudaSuccess) return e_;                                                                                  \
+    bucket_hist_kernel<T, O, C, P><<<grid, T, smem, s>>>(b);                                                           \
+    return cudaGetLastError();                                                                                         \
+  } while (0)
+#define B2RF_PICK(T)                                                          \
+  do {                                                                        \
+    if (!padded) { if (cb == 1) B2RF_LAUNCH_BUCKET(T, true, 1, false); B2RF_LAUNCH_BUCKET(T, true, 2, false); } \
+    if (one && cb == 1) B2RF_LAUNCH_BUCKET(T, true, 1, true);                 \
+    if (one) B2RF_LAUNCH_BUCKET(T, true, 2, true);                            \
+    if (cb == 1) B2RF_LAUNCH_BUCKET(T, false, 1, true);                       \
+    B2RF_LAUNCH_BUCKET(T, false, 2, true);                                    \
+  } while (0)
+  if (threads == 512) B2RF_PICK(512);
+  B2RF_PICK(256);
+#undef B2RF_PICK
+#undef B2RF_LAUNCH_BUCKET
 }
 
 // ---- segment mode: task table from the nodes' row segments, then the same shared-memory histogram kernel ----
@@ -437,13 +576,10 @@ cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s) {
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
   const size_t smem = (size_t)b.maxCells * 20 + 16;
-  e = cudaFuncSetAttribute(bucket_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
   int perSM = (int)((size_t)200 * 1024 / (smem + 1024));
   if (perSM < 1) perSM = 1;
-  if (perSM > 8) perSM = 8;
-  bucket_hist_kernel<<<device_sm_count() * perSM, BUCKET_THREADS, smem, s>>>(b);
-  return cudaGetLastError();
+  if (perSM > 4) perSM = 4;                                   // 64 registers x 256 threads: four CTAs fill the register file
+  return launch_bucket_kernel(b, device_sm_count() * perSM, perSM <= 2 ? 512 : BUCKET_THREADS, smem, s);   // big histograms: fewer CTAs, 16 warps each
 }
 
 // ---- initial row lists: per tree, the in-bag rows in ascending order, packed row | weight << 27 ----
@@ -635,13 +771,10 @@ cudaError_t launch_bucket_pipeline(const HistLaunch& h, const BucketLaunch& b, u
   }
   // pass 3: per-(slot, chunk) shared-memory histograms
   const size_t smem = (size_t)b.maxCells * 20 + 16;
-  e = cudaFuncSetAttribute(bucket_hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
   int perSM = (int)((size_t)200 * 1024 / (smem + 1024));
   if (perSM < 1) perSM = 1;
-  if (perSM > 8) perSM = 8;
-  bucket_hist_kernel<<<device_sm_count() * perSM, BUCKET_THREADS, smem, s>>>(b);
-  return cudaGetLastError();
+  if (perSM > 4) perSM = 4;                                   // 64 registers x 256 threads: four CTAs fill the register file
+  return launch_bucket_kernel(b, device_sm_count() * perSM, perSM <= 2 ? 512 : BUCKET_THREADS, smem, s);   // big histograms: fewer CTAs, 16 warps each
 }
 
 __global__ void __launch_bounds__(256) count_active_kernel(const int32_t* node, int64_t ldn, int64_t n_rows, unsigned long long* out) {

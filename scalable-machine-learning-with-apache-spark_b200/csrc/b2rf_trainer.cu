@@ -647,8 +647,11 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     const int32_t maxBinsAll = *std::max_element(t->numBins.begin(), t->numBins.end());
     int32_t padB = 0, G = 32;
     static const bool noPad = [] { const char* m = std::getenv("B2RF_NO_PAD"); return m && *m == '1'; }();
-    while (G > 4 && ((int64_t)maxBinsAll * G * 20 + 16 > (int64_t)48 * 1024 || G / 2 >= t->Fsub)) G /= 2;
-    if (!noPad && (int64_t)maxBinsAll * G * 20 + 16 <= (int64_t)100 * 1024) { padB = maxBinsAll; maxCells = maxBinsAll * G; }
+    // budget: 48 KB (four 256-thread CTAs per SM); histograms with more than 128 bins get 100 KB (two 512-thread CTAs) — measured
+    // on 12.5M x 128, 256 bins: G = 8 / 16 / 32 -> K4 1.34 / 1.03 / 1.69 s
+    const int64_t histKB = maxBinsAll > 128 ? 100 : 48;
+    while (G > 4 && ((int64_t)maxBinsAll * G * 20 + 16 > histKB * 1024 || G / 2 >= t->Fsub)) G /= 2;
+    if (!noPad && (int64_t)maxBinsAll * G * 20 + 16 <= (int64_t)200 * 1024) { padB = maxBinsAll; maxCells = maxBinsAll * G; }
     if ((size_t)maxCells * 20 + 16 > (size_t)220 * 1024) maxCells = (int32_t)(((size_t)220 * 1024 - 16) / 20);   // larger slots take the direct path
     ok &= cuda_ok(cudaMemcpyAsync(t->dSlotCells.p, t->hSlotCells.p, nSlots * 4, cudaMemcpyHostToDevice, s), "upload slot cells");
     if (!t->segMode) ok &= cuda_ok(cudaMemsetAsync(t->dSlotCount.p, 0, nSlots * 4, s), "zero slot counts");
