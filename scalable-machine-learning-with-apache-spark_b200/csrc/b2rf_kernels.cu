@@ -1273,6 +1273,169 @@ __global__ void __launch_bounds__(BAG_THREADS) bag_kernel(int64_t seed, const in
       }
   }
 }
+// ---------------------------------------------------------------------------------------------------------------------
+// K3, warp-parallel form: ONE WARP per emulated partition instead of one thread.
+//
+// Well19937c is serial only through one 32-bit word: with x_k the word the step at ring index i-k reads from v[i-k],
+//     x_{k+1} = M(x_k) ^ d_k,   M(x) = L(x ^ (x << 25)),  L(t) = (t << 9) ^ (t >>> 21),
+//     d_k = L(a_k) ^ z0_k ^ (z2_k << 21) ^ (z2_k >>> 21)        (the z1 and z2 terms of z3 ^ (z3 >>> 21) cancel in z4)
+// where a_k, z0_k, z2_k only involve ring words written at least 70 steps earlier.  M is linear over GF(2), so 32 consecutive
+// steps are a prefix scan of affine maps: five shuffle stages, stage s applying M^(2^s) through four 256-entry byte tables.
+// The Poisson sampler consumes a data-dependent number of uniforms per sample; it is parallelised exactly (same products in
+// the same order as PoissonDistribution.sample): every lane computes the sample that WOULD start at its uniform, lane 0
+// finishes the sample carried in from the previous window and walks the start positions, marked lanes emit.
+// ---------------------------------------------------------------------------------------------------------------------
+constexpr int BAGW_WARPS = 4;
+__device__ __forceinline__ uint32_t well_M(uint32_t x) { const uint32_t t = x ^ (x << 25); return (t << 9) ^ (t >> 21); }
+
+struct BagWarpSmem {
+  uint32_t v[624];
+  double u[32];
+  uint32_t len[32];
+};
+
+__device__ __forceinline__ uint32_t well_apply(const uint32_t* tab /* [4][256] */, uint32_t y) {
+  return tab[y & 255u] ^ tab[256 + ((y >> 8) & 255u)] ^ tab[512 + ((y >> 16) & 255u)] ^ tab[768 + (y >> 24)];
+}
+
+// 32 generator steps; returns this lane's tempered 32-bit output (step `lane`), updates ring, index and the carried word.
+__device__ __forceinline__ uint32_t well_batch32(uint32_t* v, int& index, uint32_t& c0, const uint32_t* tabs, int lane) {
+  int i = index - lane; if (i < 0) i += 624;
+  int i1 = i + 70;  if (i1 >= 624) i1 -= 624;
+  int i2 = i + 179; if (i2 >= 624) i2 -= 624;
+  int i3 = i + 449; if (i3 >= 624) i3 -= 624;
+  int r1 = i - 1;   if (r1 < 0) r1 += 624;
+  int r2 = i - 2;   if (r2 < 0) r2 += 624;
+  const uint32_t vM1 = v[i1], vM2 = v[i2], vM3 = v[i3];
+  const uint32_t z0 = (0x80000000u & v[r1]) ^ (0x7FFFFFFFu & v[r2]);
+  const uint32_t a = vM1 ^ (vM1 >> 27);
+  const uint32_t z2 = (vM2 >> 9) ^ (vM3 ^ (vM3 >> 1));
+  const uint32_t la = (a << 9) ^ (a >> 21);
+  uint32_t b = la ^ z0 ^ (z2 << 21) ^ (z2 >> 21);          // d_k
+  if (lane == 0) b ^= well_M(c0);                           // fold the carried word into the first element
+#pragma unroll
+  for (int st = 0; st < 5; st++) {
+    const int o = 1 << st;
+    const uint32_t y = __shfl_up_sync(0xffffffffu, b, o);
+    if (lane >= o) b ^= well_apply(tabs + st * 1024, y);
+  }
+  // b == x_{k+1} == z4 of step k
+  uint32_t x = __shfl_up_sync(0xffffffffu, b, 1);
+  if (lane == 0) x = c0;
+  const uint32_t z1 = (x ^ (x << 25)) ^ a;
+  __syncwarp();
+  v[i] = z1 ^ z2;                                            // z3; the other two words a step writes are dead (see Well19937cSm)
+  __syncwarp();
+  c0 = __shfl_sync(0xffffffffu, b, 31);
+  index -= 32; if (index < 0) index += 624;
+  uint32_t z4 = b;
+  z4 ^= (z4 << 7) & 0xe46e1700u;
+  z4 ^= (z4 << 15) & 0x9b868000u;
+  return z4;
+}
+
+__global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed, const int64_t* part_offsets, int P, int part0, int T, double rate,
+                                                                   double expNegRate, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
+  __shared__ uint32_t tabs[5 * 1024];              // M^(2^s), s = 0..4, as 4 x 256 byte tables
+  __shared__ BagWarpSmem sm_all[BAGW_WARPS];
+  // tables: entry (s, byte, val) = M^(2^s)(val << 8*byte)
+  for (int e = threadIdx.x; e < 5 * 1024; e += blockDim.x) {
+    const int st = e >> 10, byte = (e >> 8) & 3, val = e & 255;
+    uint32_t x = (uint32_t)val << (8 * byte);
+    for (int r = 0; r < (1 << st); r++) x = well_M(x);
+    tabs[e] = x;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int p = blockIdx.x * BAGW_WARPS + warp;
+  if (p >= P) return;
+  BagWarpSmem& sm = sm_all[warp];
+  const unsigned FULL = 0xffffffffu;
+  // AbstractWell.setSeed: v[0..1] = (hi, lo); v[i] = 1812433253 * (l ^ (l >> 30)) + i with l = (long) v[i - 2]: two serial chains
+  {
+    const int64_t sd = seed + (int64_t)(part0 + p) + 1;
+    if (lane < 2) {
+      uint32_t cur = lane == 0 ? (uint32_t)((uint64_t)sd >> 32) : (uint32_t)((uint64_t)sd & 0xffffffffULL);
+      sm.v[lane] = cur;
+      for (int i = lane + 2; i < 624; i += 2) {
+        const int64_t l = (int64_t)(int32_t)cur;
+        cur = (uint32_t)((1812433253LL * (l ^ (l >> 30)) + i) & 0xffffffffLL);
+        sm.v[i] = cur;
+      }
+    }
+  }
+  __syncwarp();
+  int index = 0;
+  uint32_t c0 = sm.v[0];
+  const int64_t r0 = part_offsets[p], r1 = part_offsets[p + 1];
+  const int64_t total = (r1 - r0) * (int64_t)T;     // samples of this partition, row-major over trees
+  const long limI = (long)ceil(1000 * rate);
+  int64_t ord = 0;                                   // samples emitted so far
+  double rc = 1.0; long nc = 0;                      // the sample that is in progress across windows
+  auto emit = [&](int64_t o, long n) {
+    const int64_t row = r0 + o / T;
+    const int t = (int)(o % T);
+    const int c = n > 255 ? 255 : (int)n;
+    w[(size_t)t * ldw + row] = (uint8_t)c;
+    if (node != nullptr) node[(size_t)t * ldn + row] = c > 0 ? 0 : -1;
+  };
+  while (ord < total) {
+    // ---- 64 generator steps -> 32 uniforms (BitsStreamGenerator.nextDouble: two 26-bit halves) ----
+#pragma unroll
+    for (int half = 0; half < 2; half++) {
+      const uint32_t out = well_batch32(sm.v, index, c0, tabs, lane) >> 6;
+      const uint32_t hi = __shfl_sync(FULL, out, (2 * lane) & 31), lo = __shfl_sync(FULL, out, (2 * lane + 1) & 31);
+      if (lane < 16) sm.u[half * 16 + lane] = (double)(((int64_t)hi << 26) | (int64_t)lo) * 0x1.0p-52;
+    }
+    __syncwarp();
+    // ---- every lane: the sample that would START at uniform `lane` (r = 1; r *= u; ends when r < p) ----
+    uint32_t mylen = 0; double myr = 1.0;            // mylen == 0: runs past the window (myr = product so far)
+    for (int k = lane; k < 32; k++) { myr *= sm.u[k]; if (!(myr >= expNegRate)) { mylen = (uint32_t)(k - lane + 1); break; } }
+    sm.len[lane] = mylen;
+    __syncwarp();
+    // ---- lane 0: finish the carried-in sample, then walk the start positions ----
+    uint32_t marks = 0; int first_done = 0; long first_n = 0; int carry_pos = -1;
+    if (lane == 0) {
+      int pos = 0; bool open = true;
+      while (pos < 32) {
+        if (nc >= limI) { open = false; break; }      // iteration cap of sample(): ends without consuming (practically never)
+        rc *= sm.u[pos]; pos++;
+        if (rc >= expNegRate) nc++; else { open = false; break; }
+      }
+      if (!open) {
+        first_done = 1; first_n = nc; rc = 1.0; nc = 0;
+        while (pos < 32) {
+          const uint32_t l = sm.len[pos];
+          if (l == 0) { carry_pos = pos; break; }
+          marks |= 1u << pos;
+          pos += (int)l;
+        }
+      }
+    }
+    marks = __shfl_sync(FULL, marks, 0);
+    first_done = __shfl_sync(FULL, first_done, 0);
+    carry_pos = __shfl_sync(FULL, carry_pos, 0);
+    // ---- emit ----
+    if (first_done) {
+      if (lane == 0 && ord < total) emit(ord, first_n);
+      const int64_t base = ord + 1;
+      if ((marks >> lane) & 1u) {
+        const int64_t o = base + __popc(marks & ((1u << lane) - 1u));
+        if (o < total) emit(o, (long)mylen - 1);
+      }
+      ord = base + __popc(marks);
+      // the sample left open at the window's end (if any) continues in the next window
+      const double cr = __shfl_sync(FULL, myr, carry_pos < 0 ? 0 : carry_pos);
+      if (carry_pos >= 0) { rc = cr; nc = 32 - carry_pos; } else { rc = 1.0; nc = 0; }
+    }
+    // lane 0 holds the authoritative in-progress sample in both cases (it alone advanced it when the carried-in sample did
+    // not finish inside the window)
+    rc = __shfl_sync(FULL, rc, 0);
+    nc = (long)__shfl_sync(FULL, (long long)nc, 0);
+    __syncwarp();
+  }
+}
+
 __global__ void bag_ones_kernel(int64_t n, int T, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n) return;
@@ -1485,12 +1648,20 @@ int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t par
   if (!cuda_ok(cudaMallocAsync((void**)&d_po, (size_t)(P + 1) * 8, s), "b2rf_bag alloc")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpyAsync(d_po, h_part_offsets, (size_t)(P + 1) * 8, cudaMemcpyHostToDevice, s), "b2rf_bag copy")) return B2RF_ERR_CUDA;
   // exp(-rate) is evaluated once on the host so that every consumer of the stream compares against the same constant
-  const size_t smem = (size_t)624 * BAG_THREADS * 4;
-  bool ok = cuda_ok(cudaFuncSetAttribute(bag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bag attr");
-  if (ok) {
-    bag_kernel<<<(P + BAG_THREADS - 1) / BAG_THREADS, BAG_THREADS, smem, s>>>(seed, d_po, P, part0, T, subsamplingRate, std::exp(-subsamplingRate),
-                                                                             bootstrap ? 0 : 1, d_w, ldw, d_node, ldn);
+  static const bool serialOnly = [] { const char* m = std::getenv("B2RF_BAG_SERIAL"); return m && *m == '1'; }();
+  bool ok = true;
+  if (bootstrap && 1000 * subsamplingRate >= 64 && !serialOnly) {   // warp per partition (window of 32 uniforms < iteration cap)
+    bag_warp_kernel<<<(P + BAGW_WARPS - 1) / BAGW_WARPS, BAGW_WARPS * 32, 0, s>>>(seed, d_po, P, part0, T, subsamplingRate, std::exp(-subsamplingRate),
+                                                                                d_w, ldw, d_node, ldn);
     ok = cuda_ok(cudaGetLastError(), "b2rf_bag");
+  } else {
+    const size_t smem = (size_t)624 * BAG_THREADS * 4;
+    ok = cuda_ok(cudaFuncSetAttribute(bag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bag attr");
+    if (ok) {
+      bag_kernel<<<(P + BAG_THREADS - 1) / BAG_THREADS, BAG_THREADS, smem, s>>>(seed, d_po, P, part0, T, subsamplingRate, std::exp(-subsamplingRate),
+                                                                               bootstrap ? 0 : 1, d_w, ldw, d_node, ldn);
+      ok = cuda_ok(cudaGetLastError(), "b2rf_bag");
+    }
   }
   cudaFreeAsync(d_po, s);   // stream-ordered.  No host sync: cudaMemcpyAsync from pageable memory stages h_part_offsets before returning
   return ok ? B2RF_OK : B2RF_ERR_CUDA;
