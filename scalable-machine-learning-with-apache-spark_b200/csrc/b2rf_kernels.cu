@@ -1370,11 +1370,13 @@ __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed,
   const int64_t r0 = part_offsets[p], r1 = part_offsets[p + 1];
   const int64_t total = (r1 - r0) * (int64_t)T;     // samples of this partition, row-major over trees
   const long limI = (long)ceil(1000 * rate);
-  int64_t ord = 0;                                   // samples emitted so far
+  int64_t ord = 0;                                   // samples emitted so far == ordRow * T + ordT (kept split: no 64-bit divisions)
+  int64_t ordRow = 0; uint32_t ordT = 0;
   double rc = 1.0; long nc = 0;                      // the sample that is in progress across windows
-  auto emit = [&](int64_t o, long n) {
-    const int64_t row = r0 + o / T;
-    const int t = (int)(o % T);
+  auto emit = [&](uint32_t k, long n) {              // sample number ord + k (k <= 32)
+    const uint32_t tt = ordT + k;
+    const int64_t row = r0 + ordRow + (int64_t)(tt / (uint32_t)T);
+    const uint32_t t = tt % (uint32_t)T;
     const int c = n > 255 ? 255 : (int)n;
     w[(size_t)t * ldw + row] = (uint8_t)c;
     if (node != nullptr) node[(size_t)t * ldn + row] = c > 0 ? 0 : -1;
@@ -1393,8 +1395,8 @@ __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed,
     for (int k = lane; k < 32; k++) { myr *= sm.u[k]; if (!(myr >= expNegRate)) { mylen = (uint32_t)(k - lane + 1); break; } }
     sm.len[lane] = mylen;
     __syncwarp();
-    // ---- lane 0: finish the carried-in sample, then walk the start positions ----
-    uint32_t marks = 0; int first_done = 0; long first_n = 0; int carry_pos = -1;
+    // ---- lane 0 finishes the carried-in sample; the start positions after it are found by pointer doubling ----
+    int first_done = 0; long first_n = 0; int s0 = 32;
     if (lane == 0) {
       int pos = 0; bool open = true;
       while (pos < 32) {
@@ -1402,28 +1404,34 @@ __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed,
         rc *= sm.u[pos]; pos++;
         if (rc >= expNegRate) nc++; else { open = false; break; }
       }
-      if (!open) {
-        first_done = 1; first_n = nc; rc = 1.0; nc = 0;
-        while (pos < 32) {
-          const uint32_t l = sm.len[pos];
-          if (l == 0) { carry_pos = pos; break; }
-          marks |= 1u << pos;
-          pos += (int)l;
-        }
-      }
+      if (!open) { first_done = 1; first_n = nc; rc = 1.0; nc = 0; s0 = pos; }
     }
-    marks = __shfl_sync(FULL, marks, 0);
     first_done = __shfl_sync(FULL, first_done, 0);
-    carry_pos = __shfl_sync(FULL, carry_pos, 0);
+    s0 = __shfl_sync(FULL, s0, 0);
+    // samples start at s0, s0 + len[s0], ... until a chain runs past the window.  J = position after this lane's chain
+    // (>= 32: leaves the window, 64: chain incomplete); S = set of reached starts, doubled five times (up to 31 hops).
+    uint32_t J = mylen == 0 ? 64u : (uint32_t)lane + mylen;
+    uint32_t S = (first_done && s0 < 32) ? (1u << s0) : 0u;
+#pragma unroll
+    for (int rnd = 0; rnd < 5; rnd++) {
+      const uint32_t contrib = (((S >> lane) & 1u) && J < 32u) ? (1u << J) : 0u;
+      S |= __reduce_or_sync(FULL, contrib);
+      const uint32_t Jn = __shfl_sync(FULL, J, J & 31u);
+      if (J < 32u) J = Jn;
+    }
+    const uint32_t openMask = __ballot_sync(FULL, ((S >> lane) & 1u) && mylen == 0);   // at most one reached chain is incomplete
+    const int carry_pos = openMask ? (__ffs(openMask) - 1) : -1;
+    const uint32_t marks = S & ~openMask;
     // ---- emit ----
     if (first_done) {
-      if (lane == 0 && ord < total) emit(ord, first_n);
-      const int64_t base = ord + 1;
+      if (lane == 0 && ord < total) emit(0u, first_n);
       if ((marks >> lane) & 1u) {
-        const int64_t o = base + __popc(marks & ((1u << lane) - 1u));
-        if (o < total) emit(o, (long)mylen - 1);
+        const uint32_t k = 1u + (uint32_t)__popc(marks & ((1u << lane) - 1u));
+        if (ord + k < total) emit(k, (long)mylen - 1);
       }
-      ord = base + __popc(marks);
+      const uint32_t done = 1u + (uint32_t)__popc(marks);
+      ord += done;
+      ordT += done; ordRow += ordT / (uint32_t)T; ordT %= (uint32_t)T;
       // the sample left open at the window's end (if any) continues in the next window
       const double cr = __shfl_sync(FULL, myr, carry_pos < 0 ? 0 : carry_pos);
       if (carry_pos >= 0) { rc = cr; nc = 32 - carry_pos; } else { rc = 1.0; nc = 0; }
