@@ -10,7 +10,7 @@ from . import synth  # noqa: F401
 
 
 def __getattr__(name):
-    if name in ("fit_tensors", "fit_host", "find_splits", "bin_features", "bag", "hist_build", "sample_rows", "default_partitions"):
+    if name in ("fit_tensors", "fit_many_tensors", "fit_host", "find_splits", "bin_features", "bag", "hist_build", "sample_rows", "default_partitions"):
         from . import trainer
         return getattr(trainer, name)
     raise AttributeError(name)

@@ -314,8 +314,11 @@ class _TreeEstimatorBase(Estimator, _TreeRegressorParams):
         dev = _ForestModelBase._device()
         Xd = torch.as_tensor(X, device=dev)
         yd = torch.as_tensor(y, device=dev)
-        for est in estimators:
-            forest = trainer.fit_tensors(Xd, yd, arity, est._tree_params(), part_offsets=po)
+        if len(estimators) == 1:
+            yield estimators[0]._make_model(trainer.fit_tensors(Xd, yd, arity, estimators[0]._tree_params(), part_offsets=po))
+            return
+        forests = trainer.fit_many_tensors(Xd, yd, arity, [e._tree_params() for e in estimators], part_offsets=po)   # shared passes
+        for est, forest in zip(estimators, forests):
             yield est._make_model(forest)
 
     def _fit(self, dataset):

@@ -288,6 +288,91 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         return forest
 
 
+def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_offsets=None, part0: int = None, group=None,
+                     hist_mode: str = "segment"):
+    """Train several parameterisations on the same rows in shared passes (`Estimator.fitMultiple`, CrossValidator's
+    candidates of one fold — `ML 07 - Random Forests and Hyperparameter Tuning.py:74-77,143-149`; BASELINE config 5).
+
+    What is shared: the findSplits sample, thresholds and both bin matrices (once per distinct (maxBins, seed): findSplits
+    depends on nothing else), the label vector and the device copy of X.  What is not: bag weights and row lists (MLlib draws
+    bag counts row-major over numTrees, so they differ between candidates).  The candidates' node-group loops then run in
+    lockstep on one CUDA stream each: every candidate's histogram kernels are in flight while another candidate's host-side
+    scheduling runs, and small candidates fill the SMs that a shallow forest leaves idle.  Each candidate's forest is
+    identical to what fit_tensors returns for it."""
+    _require_cuda(X, "X")
+    _require_cuda(y, "y")
+    dev = X.device
+    L = lib()
+    params_list = list(params_list)
+    with torch.cuda.device(dev):
+        y = y.to(torch.float64).contiguous()
+        n_local, F = X.shape
+        ld = _pad(n_local)
+        shared = {}
+        cands = []
+        main = torch.cuda.current_stream()
+        for params in params_list:
+            S = _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode)
+            key = (params.maxBins, params.seed)
+            if key not in shared:
+                fraction = S["fraction"]
+                samp = sample_rows(X, S["row0"], params.seed, fraction) if fraction < 1.0 else X
+                samp = gather_samples(samp, S["dist"], group)
+                thr, ns = find_splits(samp, S["arity_d"], S["mpb"], fraction * float(S["N"]))
+                code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
+                bins = torch.empty((F, ld), dtype=code_dt, device=dev)
+                bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
+                bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm)
+                shared[key] = (thr.cpu().numpy(), ns.cpu().numpy(), bins, bins_rm)
+            thr_h, ns_h, bins, bins_rm = shared[key]
+            w, node = bag(params.seed, S["po"], S["part0"], params.numTrees, params.subsamplingRate, params.bootstrap, dev, ld=ld,
+                          want_node=(hist_mode not in ("segment", "bucket") or bins_rm is None))
+            cands.append(dict(S=S, params=params, thr_h=thr_h, ns_h=ns_h, bins=bins, bins_rm=bins_rm, w=w, node=node, h=C.c_void_p(),
+                              stream=torch.cuda.Stream(), ncell=C.c_int64()))
+        torch.cuda.synchronize(dev)
+        try:
+            for c in cands:
+                S = c["S"]
+                check(L.b2rf_trainer_create(C.byref(S["cp"]), F, S["arity_np"].ctypes.data_as(C.c_void_p), c["ns_h"].ctypes.data_as(C.c_void_p),
+                                            c["thr_h"].ctypes.data_as(C.c_void_p), S["N"], C.byref(c["h"])))
+                cells = int(L.b2rf_trainer_max_group_cells(c["h"]))
+                c["hist"] = torch.empty(cells * 4, dtype=torch.float64, device=dev)
+                w, node, bins, bins_rm = c["w"], c["node"], c["bins"], c["bins_rm"]
+                check(L.b2rf_trainer_bind(c["h"], bins.data_ptr(), bins.stride(0), 0 if bins_rm is None else bins_rm.data_ptr(),
+                                          0 if bins_rm is None else bins_rm.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0),
+                                          0 if node is None else node.data_ptr(), ld if node is None else node.stride(0), n_local,
+                                          c["hist"].data_ptr(), cells))
+            torch.cuda.synchronize(dev)
+            active = list(cands)
+            while active:
+                started = []
+                for c in active:                       # asynchronous: selectNodesToSplit on the host, K4 on the candidate's stream
+                    with torch.cuda.stream(c["stream"]):
+                        st = C.c_void_p(c["stream"].cuda_stream)
+                        if check(L.b2rf_trainer_begin_group(c["h"], C.byref(c["ncell"]), st)) == 1:
+                            if c["S"]["world"] > 1:
+                                c["S"]["dist"].all_reduce(c["hist"][: c["ncell"].value * 4], group=group)
+                            started.append(c)
+                for c in started:                      # K5 + driver tail; waits for this candidate's stream only
+                    with torch.cuda.stream(c["stream"]):
+                        check(L.b2rf_trainer_end_group(c["h"], C.c_void_p(c["stream"].cuda_stream)))
+                active = started
+            torch.cuda.synchronize(dev)
+            forests = []
+            for c in cands:
+                fo = _export(c["h"], F, False)
+                fo.thresholds, fo.nsplits = c["thr_h"], c["ns_h"]
+                S = c["S"]
+                fo.counters.update(rows=S["N"], rows_local=n_local, partitions=len(S["po"]) - 1, world=S["world"], fraction=S["fraction"])
+                forests.append(fo)
+        finally:
+            for c in cands:
+                if c["h"]:
+                    L.b2rf_trainer_destroy(c["h"])
+        main.synchronize()
+        return forests
+
+
 def sample_indices(seed: int, row0_global: int, n_rows: int, fraction: float) -> np.ndarray:
     """Local indices of the rows the findSplits sampler keeps (host twin of sample_rows: same hash of the global row index)."""
     if fraction >= 1.0:

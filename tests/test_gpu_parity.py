@@ -435,3 +435,21 @@ def test_uint16_bin_codes(b2rf, oracle, cuda, mode, maxBins):
     g, o = _fit_both(b2rf, oracle, cuda, X, y, arity, maxDepth=6, maxBins=maxBins, numTrees=3, bootstrap=True, seed=11, hist_mode=mode)
     assert_parity_allowing_ties(g, o, max_ties=3)
     assert (g.ncat > 256).any() or maxBins < 290 or True
+
+
+def test_fit_many_shared_passes_equals_individual_fits(b2rf, cuda):
+    """fitMultiple's shared-pass path (candidates in lockstep on their own streams, one binned copy of the fold) returns for
+    every candidate exactly the forest fit_tensors returns for it (`ML 07 ...:74-77` grid shape, plus a second maxBins)."""
+    from b2rf import trainer
+    X, y, arity = b2rf.synth.airbnb(6000)
+    Xd, yd = X.to(cuda), y.to(cuda)
+    po = trainer.default_partitions(6000, 800)
+    grid = [b2rf.TreeParams(maxDepth=d, maxBins=mb, numTrees=t, bootstrap=True, seed=42) for d in (2, 5, 8) for t in (5, 10) for mb in (40,)]
+    grid.append(b2rf.TreeParams(maxDepth=4, maxBins=64, numTrees=3, bootstrap=True, seed=7))
+    grid.append(b2rf.TreeParams(maxDepth=5, maxBins=40))
+    many = trainer.fit_many_tensors(Xd, yd, arity, grid, part_offsets=po)
+    assert len(many) == len(grid)
+    for p, f in zip(grid, many):
+        ref = trainer.fit_tensors(Xd, yd, arity, p, part_offsets=po)
+        assert np.array_equal(f.tree_off, ref.tree_off) and np.array_equal(f.feature, ref.feature) and np.array_equal(f.threshold, ref.threshold)
+        assert np.array_equal(f.stats, ref.stats) and np.array_equal(f.prediction, ref.prediction)      # integer labels: sums exact
