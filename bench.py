@@ -132,8 +132,11 @@ def main():
     ap.add_argument("--cpu-sample-rows", type=int, default=100_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--rows-per-gpu", type=int, default=0, help="override the workload's rows per GPU (e.g. strong scaling of C4: 100M / N)")
     args = ap.parse_args()
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.rows_per_gpu > 0:
+        wl["rows"] = args.rows_per_gpu
     if args.impl == "reference":
         return run_reference(args, wl, args.workload)
     if args.warmup < 3:
