@@ -1,4 +1,4 @@
-// Internal declarations shared by b2rf_kernels.cu (device code + launchers) and b2rf_trainer.cu (host driver).
+// Internal declarations shared by the kernel files (k1_find_splits.cu ... k7_predict.cu: device code + launchers) and b2rf_trainer.cu (host driver).
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -87,6 +87,8 @@ struct PartLaunch {                      // stable partition of the row segments
 };
 cudaError_t launch_partition(const PartLaunch& p, cudaStream_t s);
 cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s);
+// chunkPrefix[i] = exclusive prefix of ceil(count_i / CH) over the row segments dseg[pos[i]], i < n; chunkPrefix[n] = total
+cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s);
 cudaError_t launch_compact_count(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, uint32_t* blockCnt, unsigned long long* totals, cudaStream_t s);
 cudaError_t launch_compact_write(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, const uint32_t* blockOff, const uint64_t* treeBase, uint32_t* idx,
                                  cudaStream_t s);
@@ -114,6 +116,7 @@ cudaError_t launch_best_split(const SplitLaunch& a, cudaStream_t s);
 
 int device_sm_count();
 void set_error(const std::string& m);
+const char* last_error_cstr();
 bool cuda_ok(cudaError_t e, const char* what);
 
 }  // namespace b2rf

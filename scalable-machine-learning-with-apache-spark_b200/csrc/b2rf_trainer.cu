@@ -124,7 +124,6 @@ struct HNode {  // LearningNode
 struct GNode { int32_t tree, nidx; };
 
 inline int level_of(int id) { return 31 - __builtin_clz((unsigned)id); }
-inline double vimp(const double* c) { if (c[0] == 0) return 0; const double sl = c[2] - (c[1] * c[1]) / c[0]; return sl / c[0]; }
 inline double vpred(const double* c) { return c[0] == 0 ? 0.0 : c[1] / c[0]; }
 
 // Library-owned scratch comes from two small process-wide pools (device memory / pinned host memory): a fit allocates dozens

@@ -1,0 +1,62 @@
+// b2rf (sm_100a) — K7 forest prediction on raw features (TreeEnsembleModel.predict).
+// Compiled with -fmad=false: MLlib's arithmetic is unfused JVM double arithmetic.
+#include "b2rf_internal.h"
+#include "b2rf_device.cuh"
+#include "../../include/b2rf.h"
+
+#include <cfloat>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+namespace b2rf {
+
+// =================================================================================================
+// K7: predict
+// =================================================================================================
+__global__ void predict_kernel(const double* X, int64_t ldx, int64_t n_rows, int T, const int64_t* tree_off, const int32_t* feature,
+                               const double* threshold, const int32_t* left, const int32_t* right, const double* prediction,
+                               const int32_t* ncat, const int32_t* cat_off, const int32_t* cat_len, const double* cats, double* out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows) return;
+  const double* x = X + (size_t)i * ldx;
+  double acc = 0.0;
+  for (int t = 0; t < T; t++) {
+    const int64_t base = tree_off[t];
+    int n = 0;
+    int f;
+    while ((f = feature[base + n]) >= 0) {
+      const double xv = x[f];
+      bool l;
+      if (ncat[base + n] == 0) l = xv <= threshold[base + n];
+      else {
+        l = false;
+        const int co = cat_off[base + n], cl = cat_len[base + n];
+        for (int c = 0; c < cl; c++) if (cats[co + c] == xv) { l = true; break; }
+      }
+      n = l ? left[base + n] : right[base + n];
+    }
+    acc += prediction[base + n];
+  }
+  out[i] = acc / (double)T;
+}
+
+
+}  // namespace b2rf
+
+using namespace b2rf;
+
+extern "C" {
+
+int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,
+                 const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_prediction, const int32_t* d_ncat,
+                 const int32_t* d_cat_off, const int32_t* d_cat_len, const double* d_cats, double* d_out, void* stream) {
+  if (n_rows <= 0) return B2RF_OK;
+  predict_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, d_feature, d_threshold, d_left, d_right,
+                                                                                     d_prediction, d_ncat, d_cat_off, d_cat_len, d_cats, d_out);
+  return cuda_ok(cudaGetLastError(), "b2rf_predict") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+}  // extern "C"

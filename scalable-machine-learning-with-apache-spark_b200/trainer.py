@@ -8,6 +8,7 @@ pass over rows is a hand-written kernel behind the C-ABI in include/b2rf.h.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import time
 
 import numpy as np
@@ -268,17 +269,24 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
 
         # ---- TreePoint (K2) + BaggedPoint (K3) ----
         ld = _pad(n_local)
+        dbg = os.environ.get("B2RF_TIMING") == "1"
         if prebinned is not None:
             bins, bins_rm = prebinned
         else:
             code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
             bins = torch.empty((F, ld), dtype=code_dt, device=dev)
             bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
+            if dbg:
+                torch.cuda.synchronize(dev); ta = time.perf_counter()
             bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm)
+            if dbg:
+                torch.cuda.synchronize(dev); tb = time.perf_counter()
         w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
                       want_node=(hist_mode not in ("segment", "bucket") or bins_rm is None))
         torch.cuda.synchronize(dev)
         t2 = time.perf_counter()
+        if dbg and prebinned is None:
+            print(f"[b2rf timing] setup {t0 - t_start:.4f} findSplits {t1 - t0:.4f} alloc {ta - t1:.4f} bin {tb - ta:.4f} bag(+alloc) {t2 - tb:.4f}", flush=True)
 
         forest = _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace)
         t3 = time.perf_counter()
