@@ -648,10 +648,10 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     static const bool noPad = [] { const char* m = std::getenv("B2RF_NO_PAD"); return m && *m == '1'; }();
     // budget: 48 KB (four 256-thread CTAs per SM); histograms with more than 128 bins get 100 KB (two 512-thread CTAs) — measured
     // on 12.5M x 128, 256 bins: G = 8 / 16 / 32 -> K4 1.34 / 1.03 / 1.69 s
-    const int64_t histKB = maxBinsAll > 128 ? 100 : 48;
+    const int64_t histKB = maxBinsAll > 128 ? 96 : 48;   // + staging tables + 1 KB reserve: 2 resp. 4 CTAs per SM
     while (G > 4 && ((int64_t)maxBinsAll * G * 20 + 16 > histKB * 1024 || G / 2 >= t->Fsub)) G /= 2;
     if (!noPad && (int64_t)maxBinsAll * G * 20 + 16 <= (int64_t)200 * 1024) { padB = maxBinsAll; maxCells = maxBinsAll * G; }
-    if ((size_t)maxCells * 20 + 16 > (size_t)220 * 1024) maxCells = (int32_t)(((size_t)220 * 1024 - 16) / 20);   // larger slots take the direct path
+    if ((size_t)maxCells * 20 + 16 > (size_t)208 * 1024) maxCells = (int32_t)(((size_t)208 * 1024 - 16) / 20);   // larger slots take the direct path
     ok &= cuda_ok(cudaMemcpyAsync(t->dSlotCells.p, t->hSlotCells.p, nSlots * 4, cudaMemcpyHostToDevice, s), "upload slot cells");
     if (!t->segMode) ok &= cuda_ok(cudaMemsetAsync(t->dSlotCount.p, 0, nSlots * 4, s), "zero slot counts");
     if (!ok) return B2RF_ERR_CUDA;

@@ -247,28 +247,47 @@ constexpr int BUCKET_THREADS = 256;   // default; tasks whose histogram leaves r
 // ---- dedicated instantiation for the common case: uint8 codes, at most 32 features per node, lane == feature ----
 // (kept as its own small kernel: the general kernel below handles feature groups, uint16 codes and 512-thread CTAs, and
 // folding this case into it cost 5-10 % of K4 time in same-box A/B runs: 0.657 s vs 0.69-0.73 s per C3 fit)
+// Per-warp staging table for the row broadcast: lane k publishes row k's (packed entry, w*y, w*y*y) as two 16-byte words and
+// every lane reads row r back with two 128-bit loads.  All lanes of a row slot read the same address, so each load is one
+// broadcast wavefront; the five 32-bit shuffles this replaces go through the same shared-memory pipe as the histogram atomics
+// and cost five (measured on C3: K4 0.657 s -> 0.616 s per fit).
+constexpr int STAGE_BYTES_PER_WARP = 32 * 32;
+__host__ __device__ __forceinline__ size_t bucket_stage_offset(int maxCells) { return ((size_t)maxCells * 20 + 15) & ~(size_t)15; }
+__device__ __forceinline__ void stage_row(uint4* st, int lane, uint32_t entry, double wy, double wyy) {
+  __syncwarp();                                                                // the previous block's readers are done
+  st[lane * 2] = make_uint4(entry, 0u, (uint32_t)__double2loint(wy), (uint32_t)__double2hiint(wy));
+  st[lane * 2 + 1] = make_uint4((uint32_t)__double2loint(wyy), (uint32_t)__double2hiint(wyy), 0u, 0u);
+  __syncwarp();
+}
+__device__ __forceinline__ void staged_row(const uint4* st, int r, uint32_t& entry, double& wy, double& wyy) {
+  const uint4 v0 = st[r * 2], v1 = st[r * 2 + 1];
+  entry = v0.x;
+  wy = __hiloint2double((int)v0.w, (int)v0.z);
+  wyy = __hiloint2double((int)v1.y, (int)v1.x);
+}
+
 // Rows [0, n) of one (slot, chunk) task, one warp row-block at a time.  Lane k of a warp owns row k of the current 32-row
 // block: it fetches the packed entry and the label once and forms (w, w*y, w*y*y); the values are then broadcast row by row
 // while every lane (== feature) gathers its own bin code and updates its own histogram column.
 template <bool DIRECT>
 __device__ __forceinline__ void bucket_rows32(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
-                                            double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep) {
+                                            double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
+                                            uint4* st) {
   constexpr int W = BUCKET_THREADS / 32;
-  const unsigned FULL = 0xffffffffu;
   for (int base = warp * 32; base < n; base += W * 32) {
     const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;          // w == 0 marks padding
     const uint32_t myw = mine >> 27;
     const double myy = myw ? a.y[mine & 0x7ffffffu] : 0.0;
     const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
     const double mywyy = mywy * myy;
+    stage_row(st, lane, mine, mywy, mywyy);
     const int nb = min(32, n - base);
     for (int q = 0; q < nb; q += 4) {
       uint32_t bin[4], wv[4]; double wy[4], wyy[4];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
-        const uint32_t p = __shfl_sync(FULL, mine, (q + u) & 31);
-        wy[u] = __shfl_sync(FULL, mywy, (q + u) & 31);
-        wyy[u] = __shfl_sync(FULL, mywyy, (q + u) & 31);
+        uint32_t p;
+        staged_row(st, (q + u) & 31, p, wy[u], wyy[u]);
         wv[u] = (q + u) < nb ? (p >> 27) : 0u;
         bin[u] = (wv[u] && active) ? a.bins_rm[(size_t)(p & 0x7ffffffu) * a.ldr + featCol] : 0u;
       }
@@ -294,6 +313,7 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist32_kernel(const Buc
   double* ssq = ssum + a.maxCells;
   unsigned* scnt = reinterpret_cast<unsigned*>(ssq + a.maxCells);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  uint4* st = reinterpret_cast<uint4*>(smraw + bucket_stage_offset(a.maxCells)) + warp * (STAGE_BYTES_PER_WARP / 16);
   const uint32_t total = a.chunk_prefix[a.nSlots];
   for (uint32_t task = blockIdx.x; task < total; task += gridDim.x) {
     int lo = 0, hi = a.nSlots;
@@ -329,8 +349,8 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist32_kernel(const Buc
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
       const uint32_t sbase = padB > 0 ? (uint32_t)((j0 >> 5) * padB * 32 + lane) : e.y;   // shared-memory cell of bin 0
       const uint32_t sstep = padB > 0 ? 32u : 1u;
-      if (direct) bucket_rows32<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep);
-      else bucket_rows32<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep);
+      if (direct) bucket_rows32<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep, st);
+      else bucket_rows32<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep, st);
     }
     if (!direct) {
       __syncthreads();
@@ -354,25 +374,24 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist32_kernel(const Buc
 template <bool DIRECT, int THREADS, bool ONE_ROW, int CB>
 __device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
                                                  double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
-                                                 int Rrt, int rrt) {
+                                                 int Rrt, int rrt, uint4* st) {
   const int R = ONE_ROW ? 1 : Rrt, r = ONE_ROW ? 0 : rrt;
   constexpr int W = THREADS / 32;
-  const unsigned FULL = 0xffffffffu;
   for (int base = warp * 32; base < n; base += W * 32) {
     const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;          // w == 0 marks padding
     const uint32_t myw = mine >> 27;
     const double myy = myw ? a.y[mine & 0x7ffffffu] : 0.0;
     const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
     const double mywyy = mywy * myy;
+    stage_row(st, lane, mine, mywy, mywyy);
     const int nb = min(32, n - base);
     for (int q = 0; q < nb; q += 4 * R) {
       uint32_t bin[4], wv[4]; double wy[4], wyy[4];
 #pragma unroll
       for (int u = 0; u < 4; u++) {
         const int ri = q + u * R + r;
-        const uint32_t p = __shfl_sync(FULL, mine, ri & 31);
-        wy[u] = __shfl_sync(FULL, mywy, ri & 31);
-        wyy[u] = __shfl_sync(FULL, mywyy, ri & 31);
+        uint32_t p;
+        staged_row(st, ri & 31, p, wy[u], wyy[u]);
         wv[u] = ri < nb ? (p >> 27) : 0u;
         bin[u] = (wv[u] && active) ? load_code(a.bins_rm, (size_t)(p & 0x7ffffffu) * a.ldr + featCol, CB ? CB : a.codeBytes) : 0u;
       }
@@ -400,6 +419,7 @@ __global__ void __launch_bounds__(THREADS) bucket_hist_kernel(const BucketLaunch
   double* ssq = ssum + a.maxCells;
   unsigned* scnt = reinterpret_cast<unsigned*>(ssq + a.maxCells);
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  uint4* st = reinterpret_cast<uint4*>(smraw + bucket_stage_offset(a.maxCells)) + warp * (STAGE_BYTES_PER_WARP / 16);
   // Shared layout.  padded (padB > 0): the slot's features are cut into groups of G (a power of two <= 32); one task handles one
   // group and keeps cell (feature fl of the group, bin b) at b*G + fl.  A warp instruction then covers 32/G rows x G features
   // with bank == lane for G == 32 (no conflict possible) and at most 32/G-way conflicts otherwise, and the task's histogram is
@@ -441,15 +461,15 @@ __global__ void __launch_bounds__(THREADS) bucket_hist_kernel(const BucketLaunch
       const int j = g * G + fl;
       const bool active = j < a.Fsub;
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
-      if (direct) bucket_rows_impl<true, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 32 / G, r);
-      else bucket_rows_impl<false, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r);
+      if (direct) bucket_rows_impl<true, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 32 / G, r, st);
+      else bucket_rows_impl<false, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r, st);
     } else {
       for (int j0 = 0; j0 < a.Fsub; j0 += 32) {
         const int j = j0 + lane;
         const bool active = j < a.Fsub;
         const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
-        if (direct) bucket_rows_impl<true, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 1, 0);
-        else bucket_rows_impl<false, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0);
+        if (direct) bucket_rows_impl<true, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 1, 0, st);
+        else bucket_rows_impl<false, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0, st);
       }
     }
     if (!direct) {
@@ -499,6 +519,25 @@ static cudaError_t launch_bucket_kernel(const BucketLaunch& b, int grid, int thr
 #undef B2RF_LAUNCH_BUCKET
 }
 
+// CTAs per SM and block size from the histogram size: the task histogram (20 bytes per cell) plus the warps' staging tables
+// must fit 228 KB per SM together with the 1 KB the runtime reserves per CTA.  Small histograms: 256 threads, up to four CTAs
+// (64 registers x 256 threads x 4 fills the register file); big ones: 16 warps per CTA, two CTAs or one.
+static cudaError_t launch_bucket_sized(const BucketLaunch& b, cudaStream_t s) {
+  const size_t hist = bucket_stage_offset(b.maxCells);
+  const size_t budget = (size_t)228 * 1024;
+  int perSM = (int)(budget / (hist + (BUCKET_THREADS / 32) * STAGE_BYTES_PER_WARP + 1024));
+  if (perSM > 4) perSM = 4;
+  int threads = BUCKET_THREADS;
+  if (perSM <= 2) {
+    threads = 512;
+    perSM = (int)(budget / (hist + (512 / 32) * STAGE_BYTES_PER_WARP + 1024));
+    if (perSM < 1) perSM = 1;
+    if (perSM > 2) perSM = 2;
+  }
+  const size_t smem = hist + (size_t)(threads / 32) * STAGE_BYTES_PER_WARP;
+  return launch_bucket_kernel(b, device_sm_count() * perSM, threads, smem, s);
+}
+
 // ---- segment mode: task table from the nodes' row segments, then the same shared-memory histogram kernel ----
 __global__ void __launch_bounds__(1024) seg_tasks_kernel(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix) {
   __shared__ uint32_t s_chunks[1024];
@@ -527,11 +566,7 @@ cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH
 cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s) {
   cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s);
   if (e != cudaSuccess) return e;
-  const size_t smem = (size_t)b.maxCells * 20 + 16;
-  int perSM = (int)((size_t)200 * 1024 / (smem + 1024));
-  if (perSM < 1) perSM = 1;
-  if (perSM > 4) perSM = 4;                                   // 64 registers x 256 threads: four CTAs fill the register file
-  return launch_bucket_kernel(b, device_sm_count() * perSM, perSM <= 2 ? 512 : BUCKET_THREADS, smem, s);   // big histograms: fewer CTAs, 16 warps each
+  return launch_bucket_sized(b, s);
 }
 
 
@@ -552,11 +587,7 @@ cudaError_t launch_bucket_pipeline(const HistLaunch& h, const BucketLaunch& b, u
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
   }
   // pass 3: per-(slot, chunk) shared-memory histograms
-  const size_t smem = (size_t)b.maxCells * 20 + 16;
-  int perSM = (int)((size_t)200 * 1024 / (smem + 1024));
-  if (perSM < 1) perSM = 1;
-  if (perSM > 4) perSM = 4;                                   // 64 registers x 256 threads: four CTAs fill the register file
-  return launch_bucket_kernel(b, device_sm_count() * perSM, perSM <= 2 ? 512 : BUCKET_THREADS, smem, s);   // big histograms: fewer CTAs, 16 warps each
+  return launch_bucket_sized(b, s);
 }
 
 
