@@ -224,6 +224,24 @@ struct b2rf_trainer {
   std::vector<std::vector<HNode>> trees;
   std::vector<std::pair<int32_t, int32_t>> stack;  // back() == head of MLlib's nodeStack
   JRandom rng{0};
+  // Feature subsets are a pure function of the position in the master stream (k-th popped node <- k-th nextLong), not of the tree
+  // state, so they are drawn ahead of need while the host waits for the GPU (end_group) and consumed in order by begin_group.
+  std::vector<uint32_t> drawFeats;   // [draw][Fsub]
+  std::vector<int64_t> drawBins;     // total bins of the draw's features
+  size_t drawHead = 0;               // next unconsumed draw
+  std::vector<uint32_t> updStamp, updSlot; uint32_t updGen = 0;   // flush_node_updates: last-writer-wins without hashing
+  void ensure_draws(size_t n) {      // at least n unconsumed draws
+    if (drawHead > 0 && drawHead == drawBins.size()) { drawFeats.clear(); drawBins.clear(); drawHead = 0; }
+    while (drawBins.size() - drawHead < n) {
+      const size_t k = drawBins.size();
+      drawFeats.resize((k + 1) * (size_t)Fsub);
+      uint32_t* out = drawFeats.data() + k * (size_t)Fsub;
+      reservoir_features(F, Fsub, rng.nextLong(), out);
+      int64_t tb = 0;
+      for (int j = 0; j < Fsub; j++) tb += numBins[out[j]];
+      drawBins.push_back(tb);
+    }
+  }
   std::vector<uint32_t> catPool;  // 8 words per categorical split
   size_t catUploaded = 0;
 
@@ -269,6 +287,7 @@ struct b2rf_trainer {
   struct Trace { int32_t g, t, id, f, s; double gain, imp, cnt, sum, sq; };
   std::vector<Trace> trace;
   double tHist = 0, tChoose = 0, tStart = 0, tTotal = 0;
+  double tSelect = 0, tTail = 0, tWait = 0;   // host shares of tChoose (begin_group / end_group) and the end_group wait; printed with B2RF_TIMING=1
   int64_t nHistLaunches = 0, nScanned = 0, nKernels = 0;
   double histAlgBytes = 0;  // SURVEY §8(d) algorithmic bytes summed over K4 launches
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
@@ -471,13 +490,15 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
 // Uploads the queued node-table changes (and new categorical masks) and applies them with one scatter launch.
 static int flush_node_updates(b2rf_trainer* t, cudaStream_t s) {
   {  // one scatter launch must not carry two records for the same node: keep the latest
-    std::unordered_map<int64_t, size_t> last;
-    last.reserve(t->pending.size() * 2);
+    const size_t tableSize = (size_t)t->nodeStride * (size_t)t->T;
+    if (t->updStamp.size() < tableSize) t->updStamp.resize(tableSize, 0);
+    if (++t->updGen == 0) { std::fill(t->updStamp.begin(), t->updStamp.end(), 0); t->updGen = 1; }
+    if (t->updSlot.size() < tableSize) t->updSlot.resize(tableSize);
     size_t w = 0;
     for (size_t i = 0; i < t->pending.size(); i++) {
-      auto it = last.find(t->pending[i].pos);
-      if (it == last.end()) { last.emplace(t->pending[i].pos, w); t->pending[w++] = t->pending[i]; }
-      else t->pending[it->second] = t->pending[i];
+      const size_t pos = (size_t)t->pending[i].pos;
+      if (t->updStamp[pos] != t->updGen) { t->updStamp[pos] = t->updGen; t->updSlot[pos] = (uint32_t)w; t->pending[w++] = t->pending[i]; }
+      else t->pending[t->updSlot[pos]] = t->pending[i];
     }
     t->pending.resize(w);
   }
@@ -533,7 +554,15 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   if (!t || !t->d_bins) { set_error("b2rf_trainer_begin_group: trainer not bound"); return B2RF_ERR_STATE; }
   if (t->inGroup) { set_error("b2rf_trainer_begin_group: previous group not finished"); return B2RF_ERR_STATE; }
   cudaStream_t s = (cudaStream_t)stream;
-  if (t->stack.empty()) { if (n_cells) *n_cells = 0; if (t->tTotal == 0) t->tTotal = now_s() - t->tStart; return 0; }
+  if (t->stack.empty()) {
+    if (n_cells) *n_cells = 0;
+    if (t->tTotal == 0) {
+      t->tTotal = now_s() - t->tStart;
+      static const bool timing = [] { const char* m = std::getenv("B2RF_TIMING"); return m && *m == '1'; }();
+      if (timing) fprintf(stderr, "[b2rf timing] groups %d host select %.4f tail %.4f wait-in-end_group %.4f total %.4f\n", t->groupNo, t->tSelect, t->tTail, t->tWait, t->tTotal);
+    }
+    return 0;
+  }
   const double tc0 = now_s();
 
   // ---- RandomForest.selectNodesToSplit ----
@@ -548,9 +577,10 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     const auto [tr, ni] = t->stack.back();
     int64_t totalBins;
     if (t->subsampling) {
-      reservoir_features(t->F, t->Fsub, t->rng.nextLong(), tmp.data());  // drawn before the memory check
-      totalBins = 0;
-      for (int j = 0; j < t->Fsub; j++) totalBins += t->numBins[tmp[j]];
+      t->ensure_draws(1);                                                  // drawn before the memory check, consumed either way
+      memcpy(tmp.data(), t->drawFeats.data() + t->drawHead * (size_t)t->Fsub, (size_t)t->Fsub * 4);
+      totalBins = t->drawBins[t->drawHead];
+      t->drawHead++;
     } else {
       for (int j = 0; j < t->Fsub; j++) tmp[j] = (uint32_t)j;
       totalBins = t->allBins;
@@ -612,7 +642,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   ok &= cuda_ok(cudaMemcpyAsync(t->dTreeIds.p, t->hTreeIds.p, (size_t)nTg * 4, cudaMemcpyHostToDevice, s), "upload tree ids");
   ok &= cuda_ok(cudaMemsetAsync(t->d_hist, 0, (size_t)cells * 32, s), "zero histogram");
   if (!ok) return B2RF_ERR_CUDA;
-  t->tChoose += now_s() - tc0;
+  t->tChoose += now_s() - tc0; t->tSelect += now_s() - tc0;
 
   // ---- K4 launches (findBestSplits.binSeqOp over all local rows) ----
   cudaEventRecord(t->ev0, s);
@@ -713,8 +743,16 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   t->nKernels++;
   if (!cuda_ok(cudaMemcpyAsync(t->hRec.p, t->dRec.p, nSlots * sizeof(SplitRec), cudaMemcpyDeviceToHost, s), "download split records")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpyAsync(t->hRecMask.p, t->dRecMask.p, nSlots * t->maskWords * 4, cudaMemcpyDeviceToHost, s), "download split masks")) return B2RF_ERR_CUDA;
+  const double tw0 = now_s();
+  if (t->subsampling) {   // the next groups pop at most two children per node of this one (+1 rejected draw); the GPU is busy with K4 anyway
+    size_t kids = 1;
+    for (size_t sl = 0; sl < nSlots; sl++)
+      if (level_of(t->trees[t->group[sl].tree][t->group[sl].nidx].id) + 1 < t->p.maxDepth) kids += 2;
+    t->ensure_draws(kids + t->stack.size());
+  }
   if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
   const double tc0 = now_s();
+  t->tWait += tc0 - tw0;
   if (t->evPending) { float ms = 0; if (cudaEventElapsedTime(&ms, t->ev0, t->ev1) == cudaSuccess) t->tHist += ms * 1e-3; t->evPending = false; }
 
   // ---- driver tail of findBestSplits: trees in Scala map order, nodes in pop order ----
@@ -794,7 +832,7 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   t->inGroup = false;
   t->groupNo++;
   t->exported = false;
-  t->tChoose += now_s() - tc0;
+  t->tChoose += now_s() - tc0; t->tTail += now_s() - tc0;
   return B2RF_OK;
 }
 

@@ -208,6 +208,8 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
     L = lib()
     dev = y.device
     h = C.c_void_p()
+    dbg = os.environ.get("B2RF_TIMING") == "1"
+    tc = time.perf_counter()
     check(L.b2rf_trainer_create(C.byref(S["cp"]), F, S["arity_np"].ctypes.data_as(C.c_void_p), ns_h.ctypes.data_as(C.c_void_p),
                                 thr_h.ctypes.data_as(C.c_void_p), S["N"], C.byref(h)))
     try:
@@ -220,14 +222,20 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
                                   hist.data_ptr(), cells))
         ncell = C.c_int64()
         st = _stream()
+        if dbg:
+            torch.cuda.synchronize(dev); tb = time.perf_counter()
         while check(L.b2rf_trainer_begin_group(h, C.byref(ncell), st)) == 1:
             if S["world"] > 1:
                 S["dist"].all_reduce(hist[: ncell.value * 4], group=group)   # DTStatsAggregator.merge (reduceByKey), row a7
             check(L.b2rf_trainer_end_group(h, st))
         torch.cuda.synchronize(dev)
+        tl = time.perf_counter()
         forest = _export(h, F, keep_trace)
+        te = time.perf_counter()
     finally:
         L.b2rf_trainer_destroy(h)
+    if dbg:
+        print(f"[b2rf timing] create+bind {tb - tc:.4f} groups {tl - tb:.4f} export {te - tl:.4f} destroy {time.perf_counter() - te:.4f}", flush=True)
     forest.thresholds, forest.nsplits = thr_h, ns_h
     forest.counters.update(rows=S["N"], rows_local=n_local, partitions=len(S["po"]) - 1, world=S["world"], fraction=S["fraction"])
     return forest

@@ -1,0 +1,182 @@
+// Microbenchmark: per-(row, feature) histogram update mechanisms with lane == feature (the K4 mapping).
+//   P) production-like: CTA-shared histogram, shared-memory atomics (u32 native add + two fp64 CAS loops), 4 CTAs/SM
+//   E) warp-private fp64 histograms updated with plain load / add / store in batches of 8 rows; equal bins inside a batch are
+//      merged in registers first; counts go to a CTA-shared table with native u32 atomics
+// nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -fmad=false -o ubench_private ubench_private.cu
+#include <cstdio>
+#include <cstdlib>
+#include <cstdint>
+#include <vector>
+#include <cuda_runtime.h>
+#define CK(x) do{cudaError_t e=(x); if(e!=cudaSuccess){printf("CUDA error %s at %d\n",cudaGetErrorString(e),__LINE__); exit(1);} }while(0)
+
+constexpr int FS = 21;      // features per node (C3 onethird)
+constexpr int NB = 64;      // bins
+constexpr int LDR = 64;     // row-major code matrix pitch (bytes)
+
+__host__ __device__ __forceinline__ uint32_t hash32(uint32_t x){ x^=x>>16; x*=0x7feb352dU; x^=x>>15; x*=0x846ca68bU; x^=x>>16; return x; }
+
+__global__ void gen(uint8_t* bins_rm, double* y, int N){
+  int i = blockIdx.x*blockDim.x+threadIdx.x; if(i>=N) return;
+  for(int j=0;j<LDR;j++) bins_rm[(size_t)i*LDR+j] = hash32(i*37u+j*1000003u)%NB;
+  y[i] = (double)(hash32(i^0xabcdefu)%1000)/7.0;
+}
+
+__device__ __forceinline__ void stage_row(uint4* st, int lane, uint32_t entry, double wy, double wyy) {
+  __syncwarp();
+  st[lane * 2] = make_uint4(entry, 0u, (uint32_t)__double2loint(wy), (uint32_t)__double2hiint(wy));
+  st[lane * 2 + 1] = make_uint4((uint32_t)__double2loint(wyy), (uint32_t)__double2hiint(wyy), 0u, 0u);
+  __syncwarp();
+}
+__device__ __forceinline__ void staged_row(const uint4* st, int r, uint32_t& entry, double& wy, double& wyy) {
+  const uint4 v0 = st[r * 2], v1 = st[r * 2 + 1];
+  entry = v0.x; wy = __hiloint2double((int)v0.w, (int)v0.z); wyy = __hiloint2double((int)v1.y, (int)v1.x);
+}
+
+// P: one CTA per 4096-row chunk (grid-stride), lane = feature
+__global__ void __launch_bounds__(256) prod(const uint8_t* __restrict__ bins_rm, const double* __restrict__ y, const uint32_t* __restrict__ rl,
+                                            const int* __restrict__ cols, int n_rows, double* hist) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  double* ssum = (double*)smraw; double* ssq = ssum + NB*32; unsigned* scnt = (unsigned*)(ssq + NB*32);
+  const int tid = threadIdx.x, warp = tid>>5, lane = tid&31;
+  uint4* st = (uint4*)(smraw + NB*32*20) + warp*64;
+  const bool active = lane < FS; const int col = active ? cols[lane] : 0;
+  const int nchunks = (n_rows + 4095)/4096;
+  for (int ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    for (int c = tid; c < NB*32; c += 256) { ssum[c]=0; ssq[c]=0; scnt[c]=0; }
+    __syncthreads();
+    const uint32_t* r0 = rl + (size_t)ch*4096; const int n = min(4096, n_rows - ch*4096);
+    for (int base = warp*32; base < n; base += 8*32) {
+      const uint32_t mine = (base+lane<n) ? r0[base+lane] : 0u;
+      const uint32_t myw = mine>>27; const double myy = myw ? y[mine&0x7ffffffu] : 0.0;
+      const double mywy = (double)myw*myy, mywyy = mywy*myy;
+      stage_row(st, lane, mine, mywy, mywyy);
+      const int nb = min(32, n-base);
+      for (int q = 0; q < nb; q += 4) {
+        uint32_t bin[4], wv[4]; double wy[4], wyy[4];
+#pragma unroll
+        for (int u=0;u<4;u++){ uint32_t p; staged_row(st,(q+u)&31,p,wy[u],wyy[u]); wv[u] = (q+u)<nb ? (p>>27):0u;
+          bin[u] = (wv[u]&&active) ? bins_rm[(size_t)(p&0x7ffffffu)*LDR+col] : 0u; }
+#pragma unroll
+        for (int u=0;u<4;u++) if (wv[u]!=0u && active) { const uint32_t cell = lane + bin[u]*32u;
+          atomicAdd(&scnt[cell], wv[u]); atomicAdd(&ssum[cell], wy[u]); atomicAdd(&ssq[cell], wyy[u]); }
+      }
+    }
+    __syncthreads();
+    for (int c = tid; c < NB*32; c += 256) { const unsigned k = scnt[c]; if(!k || (c&31)>=FS) continue;
+      double* g = hist + ((size_t)(c&31)*NB + (c>>5))*4; atomicAdd(g,(double)k); atomicAdd(g+1,ssum[c]); atomicAdd(g+2,ssq[c]); }
+    __syncthreads();
+  }
+}
+
+// E: W warps per CTA, one CTA per SM; every warp owns [NB][32] fp64 sum / sumsq tables; counts shared per CTA
+template <int W, int B>
+__global__ void __launch_bounds__(W*32, 1) priv(const uint8_t* __restrict__ bins_rm, const double* __restrict__ y, const uint32_t* __restrict__ rl,
+                                                const int* __restrict__ cols, int n_rows, double* hist) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  const int tid = threadIdx.x, warp = tid>>5, lane = tid&31;
+  double* ssum = (double*)smraw + (size_t)warp*2*NB*32; double* ssq = ssum + NB*32;
+  unsigned* scnt = (unsigned*)(smraw + (size_t)W*2*NB*32*8);
+  uint4* st = (uint4*)(smraw + (size_t)W*2*NB*32*8 + NB*32*4) + warp*128;     // two staging tables per warp
+  const bool active = lane < FS; const int col = active ? cols[lane] : 0;
+  const int nchunks = (n_rows + 4095)/4096;
+  for (int ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    for (int c = lane; c < 2*NB*32; c += 32) ssum[c] = 0;
+    for (int c = tid; c < NB*32; c += W*32) scnt[c] = 0;
+    __syncthreads();
+    const uint32_t* r0 = rl + (size_t)ch*4096; const int n = min(4096, n_rows - ch*4096);
+    // software pipeline over this warp's 32-row blocks: block k+1's entries / labels / codes are fetched while block k is added
+    const int stride = W*32;
+    int base = warp*32;
+    uint32_t mineN = (base+lane<n) ? r0[base+lane] : 0u;
+    double yN = (mineN>>27) ? y[mineN&0x7ffffffu] : 0.0;
+    uint32_t codes[32], codesN[32];
+    int buf = 0;
+    // prologue: stage block 0, fetch its codes
+    { const uint32_t w0 = mineN>>27; const double wy0=(double)w0*yN; stage_row(st+buf*64, lane, mineN, wy0, wy0*yN);
+#pragma unroll
+      for (int r=0;r<32;r++){ const uint32_t p = st[buf*64 + r*2].x; codesN[r] = ((p>>27)&&active) ? bins_rm[(size_t)(p&0x7ffffffu)*LDR+col] : 0u; }
+      const int nb2 = base+stride; mineN = (nb2+lane<n) ? r0[nb2+lane] : 0u; yN = (mineN>>27) ? y[mineN&0x7ffffffu] : 0.0; }
+    for (; base < n; base += stride) {
+#pragma unroll
+      for (int r=0;r<32;r++) codes[r] = codesN[r];
+      const uint4* cur = st + buf*64;
+      // next block: stage + issue code loads (consumed next iteration)
+      const int nbase = base + stride;
+      if (nbase < n) {
+        const uint32_t w0 = mineN>>27; const double wy0=(double)w0*yN; stage_row(st+(buf^1)*64, lane, mineN, wy0, wy0*yN);
+#pragma unroll
+        for (int r=0;r<32;r++){ const uint32_t p = st[(buf^1)*64 + r*2].x; codesN[r] = ((p>>27)&&active) ? bins_rm[(size_t)(p&0x7ffffffu)*LDR+col] : 0u; }
+        const int nb2 = nbase+stride; mineN = (nb2+lane<n) ? r0[nb2+lane] : 0u; yN = (mineN>>27) ? y[mineN&0x7ffffffu] : 0.0;
+      }
+#pragma unroll
+      for (int q = 0; q < 32; q += B) {
+        uint32_t wv[B], cell[B]; double wy[B], wyy[B]; bool alive[B];
+#pragma unroll
+        for (int u=0;u<B;u++){ uint32_t p; staged_row(cur,q+u,p,wy[u],wyy[u]); wv[u]=p>>27; alive[u] = wv[u]!=0u && active; cell[u] = lane + codes[q+u]*32u; }
+#pragma unroll
+        for (int u=1;u<B;u++)
+#pragma unroll
+          for (int v=0;v<u;v++) if (alive[u] && alive[v] && cell[u]==cell[v]) { wy[v]+=wy[u]; wyy[v]+=wyy[u]; wv[v]+=wv[u]; alive[u]=false; }
+        double s[B], sq[B];
+#pragma unroll
+        for (int u=0;u<B;u++) if (alive[u]) { s[u]=ssum[cell[u]]; sq[u]=ssq[cell[u]]; }
+#pragma unroll
+        for (int u=0;u<B;u++) if (alive[u]) { ssum[cell[u]] = s[u]+wy[u]; ssq[cell[u]] = sq[u]+wyy[u]; atomicAdd(&scnt[cell[u]], wv[u]); }
+      }
+      buf ^= 1;
+    }
+    __syncthreads();
+    for (int c = tid; c < NB*32; c += W*32) { const unsigned k = scnt[c]; if(!k || (c&31)>=FS) continue;
+      double a=0,b=0; for (int w2=0; w2<W; w2++){ a += ((double*)smraw)[(size_t)w2*2*NB*32 + c]; b += ((double*)smraw)[(size_t)w2*2*NB*32 + NB*32 + c]; }
+      double* g = hist + ((size_t)(c&31)*NB + (c>>5))*4; atomicAdd(g,(double)k); atomicAdd(g+1,a); atomicAdd(g+2,b); }
+    __syncthreads();
+  }
+}
+
+template<class F> float timeit(F f, int reps=5){
+  cudaEvent_t a,b; cudaEventCreate(&a); cudaEventCreate(&b);
+  f(); CK(cudaDeviceSynchronize());
+  float best=1e30f;
+  for(int r=0;r<reps;r++){ cudaEventRecord(a); f(); cudaEventRecord(b); CK(cudaEventSynchronize(b)); float ms; cudaEventElapsedTime(&ms,a,b); if(ms<best) best=ms; }
+  return best;
+}
+
+template <int W, int B> void run_priv(const char* tag, const uint8_t* bins, const double* y, const uint32_t* rl, const int* cols, int n, double* hist, const std::vector<double>& ref) {
+  const size_t sm = (size_t)W*2*NB*32*8 + NB*32*4 + (size_t)W*2048;
+  if (sm > 227*1024) { printf("E W=%d does not fit\n", W); return; }
+  CK(cudaFuncSetAttribute(priv<W,B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  float ms = timeit([&]{ priv<W,B><<<148, W*32, sm>>>(bins,y,rl,cols,n,hist); });
+  CK(cudaMemset(hist,0,FS*NB*32)); priv<W,B><<<148, W*32, sm>>>(bins,y,rl,cols,n,hist);
+  std::vector<double> h(FS*NB*4); CK(cudaMemcpy(h.data(),hist,FS*NB*32,cudaMemcpyDeviceToHost));
+  double maxrel=0; for (size_t i=0;i<h.size();i++){ double d=fabs(h[i]-ref[i]); double m=fabs(ref[i]); if (m>0) d/=m; if (d>maxrel) maxrel=d; }
+  printf("E priv W=%d B=%d %s smem=%zuKB: %.3f ms  %.2f Gupd/s  maxrel %.2e\n", W, B, tag, sm/1024, ms, (double)n*FS/ms/1e6, maxrel);
+}
+
+int main(){
+  const int N = 10'000'000;
+  uint8_t* bins; double* y; uint32_t* rl; int* cols; double* hist;
+  CK(cudaMalloc(&bins,(size_t)LDR*N)); CK(cudaMalloc(&y,(size_t)N*8)); CK(cudaMalloc(&rl,(size_t)N*4)); CK(cudaMalloc(&cols,32*4)); CK(cudaMalloc(&hist,FS*NB*32));
+  gen<<<(N+255)/256,256>>>(bins,y,N); CK(cudaDeviceSynchronize());
+  { std::vector<int> c(32); for(int j=0;j<32;j++) c[j]=(j*3+1)%LDR; CK(cudaMemcpy(cols,c.data(),32*4,cudaMemcpyHostToDevice)); }
+  for (int mode = 0; mode < 2; mode++) {
+    // mode 0: dense list (every row, weight 1..3); mode 1: sparse ascending list (1 row in 8)
+    std::vector<uint32_t> h; h.reserve(N);
+    for (int i=0;i<N;i++) { if (mode==1 && (hash32(i*2654435761u)&7)!=0) continue; h.push_back((uint32_t)i | ((1u + (hash32(i)%3u))<<27)); }
+    const int n = (int)h.size();
+    CK(cudaMemcpy(rl,h.data(),(size_t)n*4,cudaMemcpyHostToDevice));
+    const char* tag = mode==0 ? "dense" : "sparse1/8";
+    const size_t smP = (size_t)NB*32*20 + 8192;
+    CK(cudaFuncSetAttribute(prod, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smP));
+    float ms = timeit([&]{ prod<<<148*4,256,smP>>>(bins,y,rl,cols,n,hist); });
+    CK(cudaMemset(hist,0,FS*NB*32)); prod<<<148*4,256,smP>>>(bins,y,rl,cols,n,hist);
+    std::vector<double> ref(FS*NB*4); CK(cudaMemcpy(ref.data(),hist,FS*NB*32,cudaMemcpyDeviceToHost));
+    printf("P prod %s n=%d: %.3f ms  %.2f Gupd/s\n", tag, n, ms, (double)n*FS/ms/1e6);
+    run_priv<5,8>(tag,bins,y,rl,cols,n,hist,ref);
+    run_priv<5,4>(tag,bins,y,rl,cols,n,hist,ref);
+    run_priv<6,8>(tag,bins,y,rl,cols,n,hist,ref);
+    run_priv<4,8>(tag,bins,y,rl,cols,n,hist,ref);
+    run_priv<5,16>(tag,bins,y,rl,cols,n,hist,ref);
+  }
+  return 0;
+}
