@@ -753,7 +753,13 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
   const double tc0 = now_s();
   t->tWait += tc0 - tw0;
-  if (t->evPending) { float ms = 0; if (cudaEventElapsedTime(&ms, t->ev0, t->ev1) == cudaSuccess) t->tHist += ms * 1e-3; t->evPending = false; }
+  if (t->evPending) {
+    float ms = 0;
+    if (cudaEventElapsedTime(&ms, t->ev0, t->ev1) == cudaSuccess) t->tHist += ms * 1e-3;
+    t->evPending = false;
+    static const bool timing = [] { const char* m = std::getenv("B2RF_TIMING"); return m && *m == '2'; }();
+    if (timing) fprintf(stderr, "[b2rf timing] group %d slots %zu cells %lld K4 %.3f ms\n", t->groupNo, nSlots, (long long)t->groupCells, ms);
+  }
 
   // ---- driver tail of findBestSplits: trees in Scala map order, nodes in pop order ----
   std::vector<int> order;

@@ -274,6 +274,7 @@ __device__ __forceinline__ void bucket_rows32(const BucketLaunch& a, const uint3
                                             double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
                                             uint4* st) {
   constexpr int W = BUCKET_THREADS / 32;
+  constexpr uint32_t NONE = 0xffffffffu;
   for (int base = warp * 32; base < n; base += W * 32) {
     const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;          // w == 0 marks padding
     const uint32_t myw = mine >> 27;
@@ -281,26 +282,27 @@ __device__ __forceinline__ void bucket_rows32(const BucketLaunch& a, const uint3
     const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
     const double mywyy = mywy * myy;
     stage_row(st, lane, mine, mywy, mywyy);
-    const int nb = min(32, n - base);
-    for (int q = 0; q < nb; q += 4) {
-      uint32_t bin[4], wv[4]; double wy[4], wyy[4];
+    // All 32 bin-code gathers of the block are issued before the first atomic: the loop is bound by the latency of these
+    // loads and of the atomics' read-modify-write chains, so the more loads in flight per warp the better (microbenchmark
+    // scratch/ubench_private.cu: 4 / 8 / 16 / 32 rows in flight -> 212 / 229 / 239 / 243 G updates/s).
+    uint32_t bin[32];
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
-        uint32_t p;
-        staged_row(st, (q + u) & 31, p, wy[u], wyy[u]);
-        wv[u] = (q + u) < nb ? (p >> 27) : 0u;
-        bin[u] = (wv[u] && active) ? a.bins_rm[(size_t)(p & 0x7ffffffu) * a.ldr + featCol] : 0u;
-      }
+    for (int u = 0; u < 32; u++) {
+      const uint32_t p = st[u * 2].x;                                          // rows past the end carry w == 0
+      bin[u] = ((p >> 27) && active) ? a.bins_rm[(size_t)(p & 0x7ffffffu) * a.ldr + featCol] : NONE;
+    }
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
-        if (wv[u] != 0u && active) {
-          if (DIRECT) {
-            double* c = hb + (size_t)(gbase + bin[u]) * 4;
-            atomicAdd(c, (double)wv[u]); atomicAdd(c + 1, wy[u]); atomicAdd(c + 2, wyy[u]);
-          } else {
-            const uint32_t cell = sbase + bin[u] * sstep;
-            atomicAdd(&scnt[cell], wv[u]); atomicAdd(&ssum[cell], wy[u]); atomicAdd(&ssq[cell], wyy[u]);
-          }
+    for (int u = 0; u < 32; u++) {
+      if (bin[u] != NONE) {
+        uint32_t p; double wy, wyy;
+        staged_row(st, u, p, wy, wyy);
+        const uint32_t wv = p >> 27;
+        if (DIRECT) {
+          double* c = hb + (size_t)(gbase + bin[u]) * 4;
+          atomicAdd(c, (double)wv); atomicAdd(c + 1, wy); atomicAdd(c + 2, wyy);
+        } else {
+          const uint32_t cell = sbase + bin[u] * sstep;
+          atomicAdd(&scnt[cell], wv); atomicAdd(&ssum[cell], wy); atomicAdd(&ssq[cell], wyy);
         }
       }
     }
@@ -377,6 +379,8 @@ __device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const ui
                                                  int Rrt, int rrt, uint4* st) {
   const int R = ONE_ROW ? 1 : Rrt, r = ONE_ROW ? 0 : rrt;
   constexpr int W = THREADS / 32;
+  constexpr int U = ONE_ROW ? 16 : 8;                                          // row groups in flight (gathers issued before the first atomic)
+  constexpr uint32_t NONE = 0xffffffffu;
   for (int base = warp * 32; base < n; base += W * 32) {
     const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;          // w == 0 marks padding
     const uint32_t myw = mine >> 27;
@@ -385,25 +389,26 @@ __device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const ui
     const double mywyy = mywy * myy;
     stage_row(st, lane, mine, mywy, mywyy);
     const int nb = min(32, n - base);
-    for (int q = 0; q < nb; q += 4 * R) {
-      uint32_t bin[4], wv[4]; double wy[4], wyy[4];
+    for (int q = 0; q < nb; q += U * R) {
+      uint32_t bin[U];
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
+      for (int u = 0; u < U; u++) {
         const int ri = q + u * R + r;
-        uint32_t p;
-        staged_row(st, ri & 31, p, wy[u], wyy[u]);
-        wv[u] = ri < nb ? (p >> 27) : 0u;
-        bin[u] = (wv[u] && active) ? load_code(a.bins_rm, (size_t)(p & 0x7ffffffu) * a.ldr + featCol, CB ? CB : a.codeBytes) : 0u;
+        const uint32_t p = ri < 32 ? st[ri * 2].x : 0u;                        // rows past the end of the list carry w == 0
+        bin[u] = ((p >> 27) && active) ? load_code(a.bins_rm, (size_t)(p & 0x7ffffffu) * a.ldr + featCol, CB ? CB : a.codeBytes) : NONE;
       }
 #pragma unroll
-      for (int u = 0; u < 4; u++) {
-        if (wv[u] != 0u && active) {
+      for (int u = 0; u < U; u++) {
+        if (bin[u] != NONE) {
+          uint32_t p; double wy, wyy;
+          staged_row(st, q + u * R + r, p, wy, wyy);
+          const uint32_t wv = p >> 27;
           if (DIRECT) {
             double* c = hb + (size_t)(gbase + bin[u]) * 4;
-            atomicAdd(c, (double)wv[u]); atomicAdd(c + 1, wy[u]); atomicAdd(c + 2, wyy[u]);
+            atomicAdd(c, (double)wv); atomicAdd(c + 1, wy); atomicAdd(c + 2, wyy);
           } else {
             const uint32_t cell = sbase + bin[u] * sstep;
-            atomicAdd(&scnt[cell], wv[u]); atomicAdd(&ssum[cell], wy[u]); atomicAdd(&ssq[cell], wyy[u]);
+            atomicAdd(&scnt[cell], wv); atomicAdd(&ssum[cell], wy); atomicAdd(&ssq[cell], wyy);
           }
         }
       }

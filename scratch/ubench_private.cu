@@ -69,6 +69,148 @@ __global__ void __launch_bounds__(256) prod(const uint8_t* __restrict__ bins_rm,
   }
 }
 
+// PU: P with U rows in flight per warp (U bin-code loads issued before the first atomic of the group)
+template <int U, int T = 256>
+__global__ void __launch_bounds__(T) produ(const uint8_t* __restrict__ bins_rm, const double* __restrict__ y, const uint32_t* __restrict__ rl,
+                                            const int* __restrict__ cols, int n_rows, double* hist) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  double* ssum = (double*)smraw; double* ssq = ssum + NB*32; unsigned* scnt = (unsigned*)(ssq + NB*32);
+  const int tid = threadIdx.x, warp = tid>>5, lane = tid&31;
+  uint4* st = (uint4*)(smraw + NB*32*20) + warp*64;
+  const bool active = lane < FS; const int col = active ? cols[lane] : 0;
+  const int nchunks = (n_rows + 4095)/4096;
+  for (int ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    for (int c = tid; c < NB*32; c += T) { ssum[c]=0; ssq[c]=0; scnt[c]=0; }
+    __syncthreads();
+    const uint32_t* r0 = rl + (size_t)ch*4096; const int n = min(4096, n_rows - ch*4096);
+    for (int base = warp*32; base < n; base += T) {
+      const uint32_t mine = (base+lane<n) ? r0[base+lane] : 0u;
+      const uint32_t myw = mine>>27; const double myy = myw ? y[mine&0x7ffffffu] : 0.0;
+      const double mywy = (double)myw*myy, mywyy = mywy*myy;
+      stage_row(st, lane, mine, mywy, mywyy);
+      const int nb = min(32, n-base);
+      for (int q = 0; q < nb; q += U) {
+        uint32_t bin[U];
+#pragma unroll
+        for (int u=0;u<U;u++){ const uint32_t p = (q+u)<nb ? st[((q+u)&31)*2].x : 0u;
+          bin[u] = ((p>>27)&&active) ? bins_rm[(size_t)(p&0x7ffffffu)*LDR+col] : 0xffffffffu; }
+#pragma unroll
+        for (int u=0;u<U;u++) if (bin[u] != 0xffffffffu) { uint32_t p; double wy, wyy; staged_row(st,(q+u)&31,p,wy,wyy); const uint32_t cell = lane + bin[u]*32u;
+          atomicAdd(&scnt[cell], p>>27); atomicAdd(&ssum[cell], wy); atomicAdd(&ssq[cell], wyy); }
+      }
+    }
+    __syncthreads();
+    for (int c = tid; c < NB*32; c += T) { const unsigned k = scnt[c]; if(!k || (c&31)>=FS) continue;
+      double* g = hist + ((size_t)(c&31)*NB + (c>>5))*4; atomicAdd(g,(double)k); atomicAdd(g+1,ssum[c]); atomicAdd(g+2,ssq[c]); }
+    __syncthreads();
+  }
+}
+
+// PP: PU<32> plus cross-block software pipelining: block k+1's entries, labels and bin codes are in flight while block k is added
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) prodp(const uint8_t* __restrict__ bins_rm, const double* __restrict__ y, const uint32_t* __restrict__ rl,
+                                            const int* __restrict__ cols, int n_rows, double* hist) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  double* ssum = (double*)smraw; double* ssq = ssum + NB*32; unsigned* scnt = (unsigned*)(ssq + NB*32);
+  const int tid = threadIdx.x, warp = tid>>5, lane = tid&31;
+  uint4* st = (uint4*)(smraw + NB*32*20) + warp*128;       // two staging tables per warp
+  const bool active = lane < FS; const int col = active ? cols[lane] : 0;
+  const int nchunks = (n_rows + 4095)/4096;
+  for (int ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    for (int c = tid; c < NB*32; c += 256) { ssum[c]=0; ssq[c]=0; scnt[c]=0; }
+    __syncthreads();
+    const uint32_t* r0 = rl + (size_t)ch*4096; const int n = min(4096, n_rows - ch*4096);
+    const int stride = 8*32;
+    int base = warp*32;
+    uint32_t mineN = (base+lane<n) ? r0[base+lane] : 0u;
+    double yN = (mineN>>27) ? y[mineN&0x7ffffffu] : 0.0;
+    uint32_t codesN[8];                                     // 32 one-byte codes
+    int buf = 0;
+    { const uint32_t w0 = mineN>>27; const double wy0=(double)w0*yN; stage_row(st+buf*64, lane, mineN, wy0, wy0*yN);
+#pragma unroll
+      for (int r=0;r<32;r++){ const uint32_t p = st[buf*64 + r*2].x; const uint32_t c = ((p>>27)&&active) ? bins_rm[(size_t)(p&0x7ffffffu)*LDR+col] : 0xffu;
+        if ((r&3)==0) codesN[r>>2] = c; else codesN[r>>2] |= c << (8*(r&3)); }
+      const int nb2 = base+stride; mineN = (nb2+lane<n) ? r0[nb2+lane] : 0u; yN = (mineN>>27) ? y[mineN&0x7ffffffu] : 0.0; }
+    for (; base < n; base += stride) {
+      uint32_t codes[8];
+#pragma unroll
+      for (int r=0;r<8;r++) codes[r] = codesN[r];
+      const uint4* cur = st + buf*64;
+      const int nbase = base + stride;
+      if (nbase < n) {
+        const uint32_t w0 = mineN>>27; const double wy0=(double)w0*yN; stage_row(st+(buf^1)*64, lane, mineN, wy0, wy0*yN);
+#pragma unroll
+        for (int r=0;r<32;r++){ const uint32_t p = st[(buf^1)*64 + r*2].x; const uint32_t c = ((p>>27)&&active) ? bins_rm[(size_t)(p&0x7ffffffu)*LDR+col] : 0xffu;
+          if ((r&3)==0) codesN[r>>2] = c; else codesN[r>>2] |= c << (8*(r&3)); }
+        const int nb2 = nbase+stride; mineN = (nb2+lane<n) ? r0[nb2+lane] : 0u; yN = (mineN>>27) ? y[mineN&0x7ffffffu] : 0.0;
+      }
+#pragma unroll
+      for (int r=0;r<32;r++) {
+        const uint32_t b = (codes[r>>2] >> (8*(r&3))) & 0xffu;
+        if (b != 0xffu) { uint32_t p; double wy, wyy; staged_row(cur,r,p,wy,wyy); const uint32_t cell = lane + b*32u;
+          atomicAdd(&scnt[cell], p>>27); atomicAdd(&ssum[cell], wy); atomicAdd(&ssq[cell], wyy); }
+      }
+      buf ^= 1;
+    }
+    __syncthreads();
+    for (int c = tid; c < NB*32; c += 256) { const unsigned k = scnt[c]; if(!k || (c&31)>=FS) continue;
+      double* g = hist + ((size_t)(c&31)*NB + (c>>5))*4; atomicAdd(g,(double)k); atomicAdd(g+1,ssum[c]); atomicAdd(g+2,ssq[c]); }
+    __syncthreads();
+  }
+}
+
+// M: cost model of the shared-memory operations: same loop as P, the update replaced by
+//   MODE 0: count only (1 native add)          MODE 1: NA non-returning native u32 adds to distinct tables
+//   MODE 2: NA returning native adds (chained) MODE 3: count + one fp64 CAS add      MODE 4: no update at all (loads + staging only)
+template <int MODE, int NA>
+__global__ void __launch_bounds__(256) model(const uint8_t* __restrict__ bins_rm, const double* __restrict__ y, const uint32_t* __restrict__ rl,
+                                            const int* __restrict__ cols, int n_rows, double* hist) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  unsigned* tab = (unsigned*)smraw;                       // up to 7 tables of NB*32 words (MODE 3: table 0 = count, 1-2 = one double plane)
+  const int tid = threadIdx.x, warp = tid>>5, lane = tid&31;
+  uint4* st = (uint4*)(smraw + NB*32*28) + warp*64;
+  const bool active = lane < FS; const int col = active ? cols[lane] : 0;
+  const int nchunks = (n_rows + 4095)/4096;
+  unsigned sink = 0;
+  for (int ch = blockIdx.x; ch < nchunks; ch += gridDim.x) {
+    for (int c = tid; c < NB*32*7; c += 256) tab[c]=0;
+    __syncthreads();
+    const uint32_t* r0 = rl + (size_t)ch*4096; const int n = min(4096, n_rows - ch*4096);
+    for (int base = warp*32; base < n; base += 8*32) {
+      const uint32_t mine = (base+lane<n) ? r0[base+lane] : 0u;
+      const uint32_t myw = mine>>27; const double myy = myw ? y[mine&0x7ffffffu] : 0.0;
+      const double mywy = (double)myw*myy, mywyy = mywy*myy;
+      stage_row(st, lane, mine, mywy, mywyy);
+      const int nb = min(32, n-base);
+      for (int q = 0; q < nb; q += 4) {
+        uint32_t bin[4], wv[4]; double wy[4], wyy[4];
+#pragma unroll
+        for (int u=0;u<4;u++){ uint32_t p; staged_row(st,(q+u)&31,p,wy[u],wyy[u]); wv[u] = (q+u)<nb ? (p>>27):0u;
+          bin[u] = (wv[u]&&active) ? bins_rm[(size_t)(p&0x7ffffffu)*LDR+col] : 0u; }
+#pragma unroll
+        for (int u=0;u<4;u++) if (wv[u]!=0u && active) { const uint32_t cell = lane + bin[u]*32u;
+          if (MODE == 0) atomicAdd(&tab[cell], wv[u]);
+          else if (MODE == 1) {
+#pragma unroll
+            for (int k2=0;k2<NA;k2++) atomicAdd(&tab[k2*NB*32 + cell], wv[u] + (uint32_t)__double2loint(wy[u]) + k2);
+          } else if (MODE == 2) {
+            uint32_t carry = wv[u] + (uint32_t)__double2loint(wyy[u]);
+#pragma unroll
+            for (int k2=0;k2<NA;k2++) carry = atomicAdd(&tab[k2*NB*32 + cell], carry) & 1u;
+            sink += carry;
+          } else if (MODE == 3) { atomicAdd(&tab[cell], wv[u]); atomicAdd((double*)(tab + NB*32) + cell, wy[u]); }
+          else sink += cell + (uint32_t)__double2loint(wy[u]) + (uint32_t)__double2loint(wyy[u]);
+        }
+      }
+    }
+    __syncthreads();
+    for (int c = tid; c < NB*32; c += 256) { const unsigned k2 = tab[c]; if(!k2 || (c&31)>=FS) continue;
+      double* g = hist + ((size_t)(c&31)*NB + (c>>5))*4; atomicAdd(g,(double)k2); }
+    __syncthreads();
+  }
+  if (sink == 0x12345678u) hist[0] = 1.0;
+}
+
 // E: W warps per CTA, one CTA per SM; every warp owns [NB][32] fp64 sum / sumsq tables; counts shared per CTA
 template <int W, int B>
 __global__ void __launch_bounds__(W*32, 1) priv(const uint8_t* __restrict__ bins_rm, const double* __restrict__ y, const uint32_t* __restrict__ rl,
@@ -172,11 +314,43 @@ int main(){
     CK(cudaMemset(hist,0,FS*NB*32)); prod<<<148*4,256,smP>>>(bins,y,rl,cols,n,hist);
     std::vector<double> ref(FS*NB*4); CK(cudaMemcpy(ref.data(),hist,FS*NB*32,cudaMemcpyDeviceToHost));
     printf("P prod %s n=%d: %.3f ms  %.2f Gupd/s\n", tag, n, ms, (double)n*FS/ms/1e6);
-    run_priv<5,8>(tag,bins,y,rl,cols,n,hist,ref);
+#define RUNU(U) do { CK(cudaFuncSetAttribute(produ<U>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smP)); int per_=0; \
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_, produ<U>, 256, smP)); \
+      float t_ = timeit([&]{ produ<U><<<148*per_,256,smP>>>(bins,y,rl,cols,n,hist); }); \
+      CK(cudaMemset(hist,0,FS*NB*32)); produ<U><<<148*per_,256,smP>>>(bins,y,rl,cols,n,hist); \
+      std::vector<double> h_(FS*NB*4); CK(cudaMemcpy(h_.data(),hist,FS*NB*32,cudaMemcpyDeviceToHost)); \
+      double mr_=0; for (size_t i_=0;i_<h_.size();i_++){ double d_=fabs(h_[i_]-ref[i_]); double m_=fabs(ref[i_]); if (m_>0) d_/=m_; if (d_>mr_) mr_=d_; } \
+      printf("PU U=%d (%d CTAs/SM) %s: %.3f ms  %.2f Gupd/s  maxrel %.2e\n", U, per_, tag, t_, (double)n*FS/t_/1e6, mr_); } while(0)
+    RUNU(4); RUNU(32);
+#define RUNT(U, T) do { const size_t smT = (size_t)NB*32*20 + (T/32)*1024; CK(cudaFuncSetAttribute(produ<U,T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smT)); int per_=0; \
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_, produ<U,T>, T, smT)); \
+      float t_ = timeit([&]{ produ<U,T><<<148*per_,T,smT>>>(bins,y,rl,cols,n,hist); }); \
+      printf("PU U=%d T=%d (%d CTAs/SM, %d warps/SM) %s: %.3f ms  %.2f Gupd/s\n", U, T, per_, per_*T/32, tag, t_, (double)n*FS/t_/1e6); } while(0)
+    RUNT(32,384); RUNT(16,384); RUNT(16,512); RUNT(8,512); RUNT(32,512); RUNT(16,128); RUNT(32,128);
+#define RUNP(MB) do { const size_t smQ = (size_t)NB*32*20 + 16384; CK(cudaFuncSetAttribute(prodp<MB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smQ)); int per_=0; \
+      CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_, prodp<MB>, 256, smQ)); \
+      float t_ = timeit([&]{ prodp<MB><<<148*per_,256,smQ>>>(bins,y,rl,cols,n,hist); }); \
+      CK(cudaMemset(hist,0,FS*NB*32)); prodp<MB><<<148*per_,256,smQ>>>(bins,y,rl,cols,n,hist); \
+      std::vector<double> h_(FS*NB*4); CK(cudaMemcpy(h_.data(),hist,FS*NB*32,cudaMemcpyDeviceToHost)); \
+      double mr_=0; for (size_t i_=0;i_<h_.size();i_++){ double d_=fabs(h_[i_]-ref[i_]); double m_=fabs(ref[i_]); if (m_>0) d_/=m_; if (d_>mr_) mr_=d_; } \
+      printf("PP minb=%d (%d CTAs/SM) %s: %.3f ms  %.2f Gupd/s  maxrel %.2e\n", MB, per_, tag, t_, (double)n*FS/t_/1e6, mr_); } while(0)
+
+    { const size_t smM = (size_t)NB*32*28 + 8192;
+#define RUNM(MODE, NA, what) do { CK(cudaFuncSetAttribute(model<MODE,NA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smM)); \
+      float t_ = timeit([&]{ model<MODE,NA><<<148*3,256,smM>>>(bins,y,rl,cols,n,hist); }); \
+      printf("M %-44s %s: %.3f ms  %.2f Gupd/s\n", what, tag, t_, (double)n*FS/t_/1e6); } while(0)
+      RUNM(4,1,"no update (loads + staging), 3 CTAs/SM");
+      RUNM(0,1,"count only");
+      RUNM(1,2,"2 non-returning native adds");
+      RUNM(1,4,"4 non-returning native adds");
+      RUNM(1,7,"7 non-returning native adds");
+      RUNM(2,2,"2 returning native adds (chained)");
+      RUNM(2,4,"4 returning native adds (chained)");
+      RUNM(2,7,"7 returning native adds (chained)");
+      RUNM(3,1,"count + one fp64 CAS add");
+    }
     run_priv<5,4>(tag,bins,y,rl,cols,n,hist,ref);
-    run_priv<6,8>(tag,bins,y,rl,cols,n,hist,ref);
-    run_priv<4,8>(tag,bins,y,rl,cols,n,hist,ref);
-    run_priv<5,16>(tag,bins,y,rl,cols,n,hist,ref);
+    run_priv<5,4>(tag,bins,y,rl,cols,n,hist,ref);
   }
   return 0;
 }
