@@ -130,6 +130,7 @@ def main():
     ap.add_argument("--impl", default="b2rf", choices=["b2rf", "reference"])
     ap.add_argument("--workload", default="C3", choices=sorted(WORKLOADS))
     ap.add_argument("--cpu-sample-rows", type=int, default=100_000)
+    ap.add_argument("--sklearn-sample-rows", type=int, default=100_000, help="rows for the scikit-learn RF baseline (0 = skip)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--rows-per-gpu", type=int, default=0, help="override the workload's rows per GPU (e.g. strong scaling of C4: 100M / N)")
@@ -237,6 +238,24 @@ def main():
                          f"{fo.updates / dt / 1e6:.0f} M bin-updates/s",
                "seconds": dt}
 
+    # ---- second CPU baseline: scikit-learn's RandomForestRegressor, the reference's own single-node RF
+    # (ML 12 trains exactly T=100, depth 10), all host cores, on a bounded row sample; a different algorithm (exact splits,
+    # bootstrap by index), so it is context, not a parity target
+    skl = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline and args.sklearn_sample_rows > 0:
+        try:
+            from sklearn.ensemble import RandomForestRegressor
+            ns_ = min(args.sklearn_sample_rows, n_local)
+            Xs_, ys_, _ = getattr(b2rf.synth, wl["gen"])(ns_, device="cpu", F=wl["F"])
+            Xs_, ys_ = np.asarray(Xs_), np.asarray(ys_)
+            t_sk = time.perf_counter()
+            RandomForestRegressor(n_estimators=wl["numTrees"], max_depth=wl["maxDepth"], max_features=1 / 3, n_jobs=-1, random_state=42).fit(Xs_, ys_)
+            t_sk = time.perf_counter() - t_sk
+            skl = {"value": ns_ * wl["numTrees"] / t_sk, "unit": UNIT, "cores": os.cpu_count() or 1, "kind": "scikit-learn RandomForestRegressor (exact splits)",
+                   "sample": f"{ns_} rows of the same generator, n_estimators={wl['numTrees']} max_depth={wl['maxDepth']} max_features=1/3 n_jobs=-1; {t_sk:.1f} s"}
+        except Exception as e:   # a missing or broken sklearn must not cost the bench line
+            skl = {"unavailable": f"{type(e).__name__}: {e}"}
+
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -260,7 +279,7 @@ def main():
                          "weighted_bin_updates_per_s": updates_per_fit / hist_s if hist_s > 0 else None,   # sum over evaluated nodes of (sum of bag weights) x features per node
                          "note": "K4 is bound by shared-memory atomic throughput (71% of the smem wavefront peak in ncu), not HBM: "
                                  "22 atomic bin updates per 37 algorithmic bytes; see DESIGN.md section 2 and profiles/"},
-            "e2e": e2e, "cpu_baseline": cpu,
+            "e2e": e2e, "cpu_baseline": cpu, "cpu_baseline_sklearn": skl,
             "gpu_launches": int(sum(f.counters["kernel_launches"] for f in forests)),
             "clocks": sampler.summary(),
         }
