@@ -52,6 +52,10 @@ typedef struct b2rf_params {
   double minWeightFractionPerNode;
   double subsamplingRate;
   int64_t seed;
+  int32_t impurity;  /* 0 = variance (regression); 1 = gini, 2 = entropy: binary classification (labels 0.0 / 1.0, numClasses == 2).
+                      * Class counts ride on the regression statistics: with y in {0,1}, sum(w*y) is the class-1 count and
+                      * sum(w) - sum(w*y) the class-0 count, both exact integers in fp64.  numClasses > 2 is not implemented. */
+  int32_t reserved;  /* must be 0 */
 } b2rf_params;
 
 /* DecisionTreeMetadata.buildMetadata featureSubsetStrategy table.  strategy: "auto","all","sqrt","log2","onethird",
@@ -155,6 +159,14 @@ int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, cons
                  const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_prediction,
                  const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, const double* d_cats,
                  double* d_out, void* stream);
+/* K7, classification (reference call sites `Solutions/Labs/ML 07L:80-82,105-108`): rawPrediction of a binary
+ * tree-ensemble classifier, d_out2[n_rows][2].  d_stats4[node][4] are the exported node statistics (sum w, sum w*y, ., .), i.e.
+ * class counts (stats[0] - stats[1], stats[1]).  mode 0 = RandomForestClassificationModel.predictRaw (per-tree normalised class
+ * counts summed in tree order), mode 1 = DecisionTreeClassificationModel.predictRaw (class counts of tree 0's leaf). */
+int b2rf_predict_raw(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,
+                     const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_stats4,
+                     const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, const double* d_cats,
+                     int32_t mode, double* d_out2, void* stream);
 
 #ifdef __cplusplus
 }

@@ -211,6 +211,7 @@ struct Params {
   int bootstrap = 0;
   int64_t seed = 0;
   int featuresPerNode = 0;  // resolved by the caller (featureSubsetStrategy table, Appendix A.1)
+  int impurity = 0;         // 0 variance (regression), 1 gini, 2 entropy (binary classification: numClasses == 2)
 };
 
 struct Meta {
@@ -307,13 +308,37 @@ inline int find_bin(double x, const double* thr, int nthr) {
 // ----------------------------------------------------------------------------------------------
 // Trees under construction (LearningNode) and finished (Node)
 // ----------------------------------------------------------------------------------------------
-struct Calc { double cnt = 0, sum = 0, sq = 0, raw = 0; };  // VarianceCalculator stats(0..2) + rawCount
-inline double calc_impurity(const Calc& c) {                // Variance.calculate
-  if (c.cnt == 0) return 0;
-  const double sl = c.sq - (c.sum * c.sum) / c.cnt;
-  return sl / c.cnt;
+// Regression (VarianceCalculator): stats = (weight, sum w*y, sum w*y*y) + rawCount.
+// Classification (GiniCalculator / EntropyCalculator, numClasses == 2): stats = class counts; here cnt = count of class 0,
+// sum = count of class 1, sq unused, raw = rawCount.  The weighted count of a calculator is stats.sum == cnt + sum.
+struct Calc { double cnt = 0, sum = 0, sq = 0, raw = 0; };
+static int g_impurity = 0;   // set by b2rf_oracle_fit for the duration of one fit (the oracle is test infrastructure, one fit at a time)
+inline double calc_count(const Calc& c) { return g_impurity == 0 ? c.cnt : c.cnt + c.sum; }
+inline double calc_impurity(const Calc& c) {
+  if (g_impurity == 0) {               // Variance.calculate
+    if (c.cnt == 0) return 0;
+    const double sl = c.sq - (c.sum * c.sum) / c.cnt;
+    return sl / c.cnt;
+  }
+  const double counts[2] = {c.cnt, c.sum};
+  const double total = counts[0] + counts[1];
+  if (total == 0) return 0;
+  if (g_impurity == 1) {               // Gini.calculate(counts, totalCount)
+    double imp = 1.0;
+    for (int k = 0; k < 2; k++) { const double freq = counts[k] / total; imp -= freq * freq; }
+    return imp;
+  }
+  double imp = 0.0;                    // Entropy.calculate: log2(x) = log(x) / log(2)
+  for (int k = 0; k < 2; k++) if (counts[k] != 0) { const double freq = counts[k] / total; imp -= freq * (std::log(freq) / std::log(2.0)); }
+  return imp;
 }
-inline double calc_predict(const Calc& c) { return c.cnt == 0 ? 0.0 : c.sum / c.cnt; }
+// regression: mean label; classification: indexOfLargestArrayElement(stats) (first maximum), 0 for an empty calculator
+inline double calc_predict(const Calc& c) {
+  if (g_impurity == 0) return c.cnt == 0 ? 0.0 : c.sum / c.cnt;
+  return c.sum > c.cnt ? 1.0 : 0.0;
+}
+// ordering key of a category in binsToBestSplit: regression -> predict; binary classification -> stats(1), the count of class 1
+inline double calc_centroid(const Calc& c) { return g_impurity == 0 ? calc_predict(c) : c.sum; }
 
 struct Stats {  // ImpurityStats
   double gain = 0, impurity = 0;
@@ -368,12 +393,13 @@ inline void calc_impurity_stats(Stats& st, const Calc& L, const Calc& R, const M
   } else { parent = st.calc; imp = st.impurity; }
   Stats out;
   out.has = true; out.calc = parent; out.impurity = imp;
-  const double total = L.cnt + R.cnt;
-  const bool bad = (L.raw < p.minInstancesPerNode) || (R.raw < p.minInstancesPerNode) || (L.cnt < m.minWeightPerNode) ||
-                   (R.cnt < m.minWeightPerNode);
+  const double lc = calc_count(L), rcn = calc_count(R);
+  const double total = lc + rcn;
+  const bool bad = (L.raw < p.minInstancesPerNode) || (R.raw < p.minInstancesPerNode) || (lc < m.minWeightPerNode) ||
+                   (rcn < m.minWeightPerNode);
   if (bad) { out.gain = -1.7976931348623157e308; out.valid = false; st = out; return; }
   const double li = calc_impurity(L), ri = calc_impurity(R);
-  const double lw = L.cnt / total, rw = R.cnt / total;
+  const double lw = lc / total, rw = rcn / total;
   const double gain = imp - lw * li - rw * ri;
   if (gain < p.minInfoGain) { out.gain = -1.7976931348623157e308; out.valid = false; st = out; return; }
   out.gain = gain; out.left = L; out.right = R; out.valid = true;
@@ -413,7 +439,7 @@ void bins_to_best_split(double* hist, const std::vector<int64_t>& foff, const st
       std::vector<std::pair<double, int>> cen(nc);
       for (int c = 0; c < nc; c++) {
         Calc cs{h[c * 4], h[c * 4 + 1], h[c * 4 + 2], h[c * 4 + 3]};
-        cen[c] = {cs.cnt != 0 ? calc_predict(cs) : 1.7976931348623157e308, c};
+        cen[c] = {calc_count(cs) != 0 ? calc_centroid(cs) : 1.7976931348623157e308, c};
       }
       std::stable_sort(cen.begin(), cen.end(), [](const std::pair<double, int>& a, const std::pair<double, int>& b) { return a.first < b.first; });
       order.resize(nc);
@@ -633,6 +659,8 @@ struct B2rfOracleParams {
   int32_t maxDepth, maxBins, minInstancesPerNode, numTrees, featuresPerNode, maxMemoryInMB, bootstrap, numThreads;
   double minInfoGain, minWeightFractionPerNode, subsamplingRate;
   int64_t seed;
+  int32_t impurity;   // 0 variance, 1 gini, 2 entropy (labels must be 0.0 / 1.0)
+  int32_t reserved;
 };
 
 // X [N][F] row-major f64; arity[F] (0 = continuous); part_offsets[P+1]; sample_idx: rows used by findSplits (n_sample of them,
@@ -645,7 +673,10 @@ int b2rf_oracle_fit(const double* X, int64_t N, int F, const double* y, const in
   p.maxDepth = pp->maxDepth; p.maxBins = pp->maxBins; p.minInstancesPerNode = pp->minInstancesPerNode; p.numTrees = pp->numTrees;
   p.featuresPerNode = pp->featuresPerNode; p.maxMemoryInMB = pp->maxMemoryInMB; p.bootstrap = pp->bootstrap;
   p.minInfoGain = pp->minInfoGain; p.minWeightFractionPerNode = pp->minWeightFractionPerNode; p.subsamplingRate = pp->subsamplingRate;
-  p.seed = pp->seed;
+  p.seed = pp->seed; p.impurity = pp->impurity;
+  if (p.impurity < 0 || p.impurity > 2) { g_err = "impurity must be 0 (variance), 1 (gini) or 2 (entropy)"; delete fo; return -1; }
+  if (p.impurity != 0) for (int64_t i = 0; i < N; i++) if (!(y[i] == 0.0 || y[i] == 1.0)) { g_err = "classification labels must be 0.0 or 1.0 (numClasses == 2)"; delete fo; return -1; }
+  g_impurity = p.impurity;
   const int nthreads = std::max(1, pp->numThreads);
   const double t0 = now_s();
   Meta& m = fo->meta;
@@ -793,11 +824,13 @@ int b2rf_oracle_fit(const double* X, int64_t N, int F, const double* y, const in
           const GNode& g = group[it->second];
           const double w = (double)counts[i * T + t];
           const double wy = w * yy, wyy = w * yy * yy;
+          const int cls = (int)yy;   // classification: allStats(offset + label) += numSamples * sampleWeight
           double* base = H + g.base * 4;
           const int nf = (int)g.feats.size();
           for (int j = 0; j < nf; j++) {
             double* c = base + (g.foff[j] + b[g.feats[j]]) * 4;
-            c[0] += w; c[1] += wy; c[2] += wyy; c[3] += w;
+            if (p.impurity == 0) { c[0] += w; c[1] += wy; c[2] += wyy; c[3] += w; }
+            else { c[cls] += w; c[3] += w; }
           }
           upd += nf;
         }
@@ -924,6 +957,32 @@ int b2rf_oracle_predict(void* h, const double* X, int64_t N, int F, double* out)
       acc += f.prediction[base + n];
     }
     out[i] = acc / T;
+  }
+  return 0;
+}
+
+// ---- classification: rawPrediction.  mode 0: RandomForestClassificationModel.predictRaw (votes(k) += classCounts(k) / total per
+// tree, in tree order); mode 1: DecisionTreeClassificationModel.predictRaw (the leaf's class counts of tree 0) ----
+int b2rf_oracle_predict_raw(void* h, const double* X, int64_t N, int F, int mode, double* out2) {
+  const FlatForest& f = ((Forest*)h)->flat;
+  const int T = (int)f.tree_off.size() - 1;
+  for (int64_t i = 0; i < N; i++) {
+    double v0 = 0, v1 = 0;
+    for (int t = 0; t < (mode == 1 ? 1 : T); t++) {
+      int64_t base = f.tree_off[t]; int n = 0;
+      while (f.feature[base + n] >= 0) {
+        const int ft = f.feature[base + n];
+        const double x = X[i * F + ft];
+        bool l;
+        if (f.ncat[base + n] == 0) l = x <= f.threshold[base + n];
+        else { l = false; for (int c = 0; c < f.cat_len[base + n]; c++) if (f.cats[f.cat_off[base + n] + c] == x) { l = true; break; } }
+        n = l ? f.left[base + n] : f.right[base + n];
+      }
+      const double c0 = f.stats[(base + n) * 4], c1 = f.stats[(base + n) * 4 + 1];
+      if (mode == 1) { v0 = c0; v1 = c1; }
+      else { const double total = c0 + c1; if (total != 0) { v0 += c0 / total; v1 += c1 / total; } }
+    }
+    out2[i * 2] = v0; out2[i * 2 + 1] = v1;
   }
   return 0;
 }

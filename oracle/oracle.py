@@ -51,7 +51,10 @@ class Params(C.Structure):
     _fields_ = [("maxDepth", C.c_int32), ("maxBins", C.c_int32), ("minInstancesPerNode", C.c_int32), ("numTrees", C.c_int32),
                 ("featuresPerNode", C.c_int32), ("maxMemoryInMB", C.c_int32), ("bootstrap", C.c_int32), ("numThreads", C.c_int32),
                 ("minInfoGain", C.c_double), ("minWeightFractionPerNode", C.c_double), ("subsamplingRate", C.c_double),
-                ("seed", C.c_int64)]
+                ("seed", C.c_int64), ("impurity", C.c_int32), ("reserved", C.c_int32)]
+
+
+IMPURITIES = {"variance": 0, "gini": 1, "entropy": 2}
 
 
 # ---------------- RNG known-answer hooks ----------------
@@ -175,6 +178,8 @@ class OracleForest:
     timers: dict = field(default_factory=dict)
     updates: int = 0
     _h: object = None
+    impurity_kind: str = "variance"
+    is_single_tree: bool = False
 
     @property
     def num_trees(self):
@@ -182,8 +187,19 @@ class OracleForest:
 
     def predict(self, X):
         X = np.ascontiguousarray(X, np.float64)
+        if self.impurity_kind != "variance":   # raw2prediction: argmax of rawPrediction (first maximum)
+            return np.argmax(self.predict_raw(X), axis=1).astype(np.float64)
         out = np.zeros(X.shape[0])
         lib().b2rf_oracle_predict(C.c_void_p(self._h), _p(X), C.c_int64(X.shape[0]), C.c_int(X.shape[1]), _p(out))
+        return out
+
+    def predict_raw(self, X, single_tree=None):
+        """Classification rawPrediction [n, 2]: RandomForestClassificationModel.predictRaw (per-tree normalised votes summed in
+        tree order) or, for a single DecisionTreeClassificationModel (single_tree=True), the leaf's class counts."""
+        X = np.ascontiguousarray(X, np.float64)
+        out = np.zeros((X.shape[0], 2))
+        mode = 1 if (self.is_single_tree if single_tree is None else single_tree) else 0
+        lib().b2rf_oracle_predict_raw(C.c_void_p(self._h), _p(X), C.c_int64(X.shape[0]), C.c_int(X.shape[1]), C.c_int(mode), _p(out))
         return out
 
     def __del__(self):
@@ -226,15 +242,18 @@ def features_per_node(strategy: str, F: int, num_trees: int, regression: bool = 
 
 def fit(X, y, arity, *, maxDepth=5, maxBins=32, minInstancesPerNode=1, numTrees=1, featureSubsetStrategy="auto",
         maxMemoryInMB=256, bootstrap=False, minInfoGain=0.0, minWeightFractionPerNode=0.0, subsamplingRate=1.0, seed=0,
-        part_offsets=None, sample_idx=None, fraction=1.0, numThreads=1) -> OracleForest:
+        part_offsets=None, sample_idx=None, fraction=1.0, numThreads=1, impurity="variance", single_tree=None) -> OracleForest:
+    """impurity: "variance" (regression) or "gini" / "entropy" (binary classification, labels 0.0 / 1.0; featureSubsetStrategy
+    "auto" then resolves to sqrt for numTrees > 1).  single_tree: the model is a DecisionTree*Model (default: numTrees == 1)."""
     X = np.ascontiguousarray(X, np.float64); y = np.ascontiguousarray(y, np.float64)
     N, F = X.shape
+    kind = impurity
     arity = np.ascontiguousarray(arity, np.int32)
     if part_offsets is None:
         part_offsets = np.array([0, N], np.int64)
     po = np.ascontiguousarray(part_offsets, np.int64)
-    pr = Params(maxDepth, maxBins, minInstancesPerNode, numTrees, features_per_node(featureSubsetStrategy, F, numTrees),
-                maxMemoryInMB, int(bootstrap), numThreads, minInfoGain, minWeightFractionPerNode, subsamplingRate, seed)
+    pr = Params(maxDepth, maxBins, minInstancesPerNode, numTrees, features_per_node(featureSubsetStrategy, F, numTrees, regression=(kind == "variance")),
+                maxMemoryInMB, int(bootstrap), numThreads, minInfoGain, minWeightFractionPerNode, subsamplingRate, seed, IMPURITIES[kind], 0)
     h = C.c_void_p()
     si = None if sample_idx is None else np.ascontiguousarray(sample_idx, np.int64)
     rc = lib().b2rf_oracle_fit(_p(X), C.c_int64(N), C.c_int(F), _p(y), _p(arity), C.byref(pr), _p(po), C.c_int(len(po) - 1),
@@ -258,4 +277,4 @@ def fit(X, y, arity, *, maxDepth=5, maxBins=32, minInstancesPerNode=1, numTrees=
     tm = np.zeros(5); L.b2rf_oracle_timers(h, _p(tm))
     return OracleForest(tree_off, feature, threshold, left, right, prediction, impurity, gain, stats, ncat, cat_off, cat_len, cats[:nc],
                         thr, ns, gs, ti, td, dict(init=tm[0], findSplits=tm[1], findBestSplits=tm[2], chooseSplits=tm[3], total=tm[4]),
-                        int(L.b2rf_oracle_updates(h)), h.value)
+                        int(L.b2rf_oracle_updates(h)), h.value, kind, (numTrees == 1) if single_tree is None else bool(single_tree))

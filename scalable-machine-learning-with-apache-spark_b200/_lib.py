@@ -15,7 +15,7 @@ class B2rfParams(C.Structure):
     _fields_ = [("maxDepth", C.c_int32), ("maxBins", C.c_int32), ("minInstancesPerNode", C.c_int32), ("numTrees", C.c_int32),
                 ("featuresPerNode", C.c_int32), ("maxMemoryInMB", C.c_int32), ("bootstrap", C.c_int32), ("histMode", C.c_int32),
                 ("minInfoGain", C.c_double), ("minWeightFractionPerNode", C.c_double), ("subsamplingRate", C.c_double),
-                ("seed", C.c_int64)]
+                ("seed", C.c_int64), ("impurity", C.c_int32), ("reserved", C.c_int32)]
 
 
 class B2rfError(RuntimeError):
@@ -59,6 +59,7 @@ _SIGS = {
     "b2rf_trainer_trace": (C.c_int, [vp, vp, vp]),
     "b2rf_hist_build": (C.c_int, [vp, i64, i32, i32, vp, vp, i64, vp, i64, vp, i32, i64, vp, vp, i32, vp, vp]),
     "b2rf_predict": (C.c_int, [vp, i64, i64, i32] + [vp] * 12),
+    "b2rf_predict_raw": (C.c_int, [vp, i64, i64, i32] + [vp] * 10 + [i32, vp, vp]),
 }
 
 EXPORTS = tuple(_SIGS)

@@ -124,7 +124,12 @@ struct HNode {  // LearningNode
 struct GNode { int32_t tree, nidx; };
 
 inline int level_of(int id) { return 31 - __builtin_clz((unsigned)id); }
-inline double vpred(const double* c) { return c[0] == 0 ? 0.0 : c[1] / c[0]; }
+// ImpurityCalculator.predict: regression -> mean label; binary classification -> indexOfLargestArrayElement(class counts), the
+// first maximum, i.e. class 1 only when its count (c[1]) strictly exceeds class 0's (c[0] - c[1])
+inline double vpred(const double* c, int impurity) {
+  if (impurity == 0) return c[0] == 0 ? 0.0 : c[1] / c[0];
+  return c[1] > c[0] - c[1] ? 1.0 : 0.0;
+}
 
 // Library-owned scratch comes from two small process-wide pools (device memory / pinned host memory): a fit allocates dozens
 // of descriptor buffers, and cudaMalloc / cudaMallocHost / cudaFree each cost 0.1-10 ms and synchronise the device, which
@@ -377,6 +382,7 @@ int b2rf_trainer_create(const b2rf_params* params, int32_t F, const int32_t* h_a
   if (!params || !out || F <= 0 || numExamples <= 0 || params->numTrees <= 0 || params->maxDepth < 0 || params->maxDepth > 30) {
     set_error("b2rf_trainer_create: bad argument"); return B2RF_ERR_ARG;
   }
+  if (params->impurity < 0 || params->impurity > 2 || params->reserved != 0) { set_error("b2rf_trainer_create: impurity must be 0 (variance), 1 (gini) or 2 (entropy)"); return B2RF_ERR_ARG; }
   b2rf_trainer* t = new b2rf_trainer();
   t->p = *params; t->F = F; t->T = params->numTrees; t->numExamples = numExamples;
   { int mpb = 0; const int rc = check_arity(params->maxBins, F, h_arity, numExamples, &mpb); if (rc) { delete t; return rc; } t->maxPossibleBins = mpb; }
@@ -737,7 +743,7 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   a.hist = t->d_hist; a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.nSlots = (int32_t)nSlots;
   a.parent4 = t->dParent.p; a.hasParent = t->dHasParent.p; a.numBins = t->dNumBins.p; a.isCat = t->dIsCat.p;
   a.minInstances = (double)t->p.minInstancesPerNode; a.minWeight = t->minWeightPerNode; a.minInfoGain = t->p.minInfoGain;
-  a.out = t->dRec.p; a.catmask_out = t->dRecMask.p; a.maskWords = t->maskWords;
+  a.out = t->dRec.p; a.catmask_out = t->dRecMask.p; a.maskWords = t->maskWords; a.impurity = t->p.impurity;
   a.maxB = *std::max_element(t->numBins.begin(), t->numBins.end());
   if (!cuda_ok(launch_best_split(a, s), "best_split launch")) return B2RF_ERR_CUDA;
   t->nKernels++;
@@ -879,7 +885,7 @@ static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
       return me;
     }
     t->x_feature[at] = n.feature; t->x_left[at] = l; t->x_right[at] = r; t->x_threshold[at] = n.threshold;
-    t->x_prediction[at] = vpred(n.stats.calc); t->x_impurity[at] = n.stats.impurity; t->x_gain[at] = n.stats.gain;
+    t->x_prediction[at] = vpred(n.stats.calc, t->p.impurity); t->x_impurity[at] = n.stats.impurity; t->x_gain[at] = n.stats.gain;
     if (n.catMaskIdx >= 0) {
       t->x_ncat[at] = t->numBins[n.feature];
       t->x_cat_off[at] = (int32_t)t->x_cats.size();
@@ -890,7 +896,7 @@ static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
     }
     return me;
   }
-  t->x_prediction[at] = vpred(n.stats.calc);
+  t->x_prediction[at] = vpred(n.stats.calc, t->p.impurity);
   t->x_impurity[at] = n.stats.valid ? n.stats.impurity : -1.0;
   return me;
 }

@@ -24,10 +24,26 @@ __host__ __device__ inline size_t split_warp_bytes(int maxB, int maskWords) {
   return (b + 15) & ~(size_t)15;
 }
 
-__device__ __forceinline__ double variance_calc(double cnt, double sum, double sq) {  // Variance.calculate
+// Variance.calculate / Gini.calculate / Entropy.calculate on one calculator's statistics (cnt = sum w, sum = sum w*y, sq = sum w*y*y).
+// Classification (kind 1, 2) is binary: the class counts are (cnt - sum, sum), exact integers, and stats.sum == cnt.
+__device__ __forceinline__ double impurity_calc(int kind, double cnt, double sum, double sq) {
   if (cnt == 0) return 0.0;
-  const double sl = sq - (sum * sum) / cnt;
-  return sl / cnt;
+  if (kind == 0) {
+    const double sl = sq - (sum * sum) / cnt;
+    return sl / cnt;
+  }
+  const double c0 = cnt - sum, c1 = sum;
+  const double total = c0 + c1;
+  if (kind == 1) {                                // impurity = 1 - sum_k (count_k / total)^2, classes in index order
+    double imp = 1.0;
+    const double f0 = c0 / total; imp -= f0 * f0;
+    const double f1 = c1 / total; imp -= f1 * f1;
+    return imp;
+  }
+  double imp = 0.0;                               // impurity = - sum_k freq_k * log2(freq_k), log2(x) = log(x) / log(2), empty classes skipped
+  if (c0 != 0) { const double f0 = c0 / total; imp -= f0 * (log(f0) / log(2.0)); }
+  if (c1 != 0) { const double f1 = c1 / total; imp -= f1 * (log(f1) / log(2.0)); }
+  return imp;
 }
 
 struct SplitView {   // one warp's shared arrays
@@ -60,7 +76,7 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
   bool haveP = a.hasParent[slot] != 0;
   if (haveP) {
     P[0] = a.parent4[(size_t)slot * 4]; P[1] = a.parent4[(size_t)slot * 4 + 1]; P[2] = a.parent4[(size_t)slot * 4 + 2];
-    Pimp = variance_calc(P[0], P[1], P[2]);
+    Pimp = impurity_calc(a.impurity, P[0], P[1], P[2]);
   }
   bool any = false;
   double bestGain = 0; int bestF = -1, bestS = -1;
@@ -85,7 +101,8 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
     __syncwarp();
     const bool cat = a.isCat[f] != 0;
     if (cat) {
-      for (int b = lane; b < nb; b += 32) sm.key[b] = sm.raw[b][0] != 0 ? sm.raw[b][1] / sm.raw[b][0] : DBL_MAX;
+      // ordering key of a category: regression -> its mean label; binary classification -> its class-1 count (categoryStats.stats(1))
+      for (int b = lane; b < nb; b += 32) sm.key[b] = sm.raw[b][0] != 0 ? (a.impurity == 0 ? sm.raw[b][1] / sm.raw[b][0] : sm.raw[b][1]) : DBL_MAX;
       __syncwarp();
       for (int b = lane; b < nb; b += 32) {  // stable rank by counting == List.sortBy(_._2)
         const double kb = sm.key[b];
@@ -112,7 +129,7 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
     if (!haveP) {  // root: parent = left + right of the first evaluated candidate (calculateImpurityStats, stats == null)
       const double l0 = sm.cum[0][0], l1 = sm.cum[0][1], l2 = sm.cum[0][2];
       P[0] = l0 + (T0 - l0); P[1] = l1 + (T1 - l1); P[2] = l2 + (T2 - l2);
-      Pimp = variance_calc(P[0], P[1], P[2]);
+      Pimp = impurity_calc(a.impurity, P[0], P[1], P[2]);
       haveP = true;
     }
     double lg = 0; int ls = -1;
@@ -123,7 +140,7 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
       if (L0 < a.minInstances || R0 < a.minInstances || L0 < a.minWeight || R0 < a.minWeight) gain = -DBL_MAX;
       else {
         const double total = L0 + R0;
-        const double li = variance_calc(L0, L1, L2), ri = variance_calc(R0, R1, R2);
+        const double li = impurity_calc(a.impurity, L0, L1, L2), ri = impurity_calc(a.impurity, R0, R1, R2);
         const double lw = L0 / total, rw = R0 / total;
         gain = Pimp - lw * li - rw * ri;
         if (gain < a.minInfoGain) gain = -DBL_MAX;
@@ -156,15 +173,15 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
         const double* cells = hb + (size_t)fo[0].y * 4;
         const int nb = a.numBins[firstF];
         for (int b = 0; b < nb; b++) { P[0] += cells[(size_t)b * 4]; P[1] += cells[(size_t)b * 4 + 1]; P[2] += cells[(size_t)b * 4 + 2]; }
-        Pimp = variance_calc(P[0], P[1], P[2]);
+        Pimp = impurity_calc(a.impurity, P[0], P[1], P[2]);
       }
       r.gain = -DBL_MAX; r.valid = 0; r.feature = firstF < 0 ? 0 : firstF; r.splitIdx = 0;
     } else {
       r.gain = bestGain; r.valid = bestGain != -DBL_MAX; r.feature = bestF; r.splitIdx = bestS;
       for (int q = 0; q < 3; q++) { r.left[q] = bL[q]; r.right[q] = bR[q]; }
       r.left[3] = bL[0]; r.right[3] = bR[0];
-      r.leftImp = variance_calc(bL[0], bL[1], bL[2]);
-      r.rightImp = variance_calc(bR[0], bR[1], bR[2]);
+      r.leftImp = impurity_calc(a.impurity, bL[0], bL[1], bL[2]);
+      r.rightImp = impurity_calc(a.impurity, bR[0], bR[1], bR[2]);
     }
     r.impurity = Pimp;
     r.parent[0] = P[0]; r.parent[1] = P[1]; r.parent[2] = P[2]; r.parent[3] = P[0];

@@ -43,6 +43,43 @@ __global__ void predict_kernel(const double* X, int64_t ldx, int64_t n_rows, int
   out[i] = acc / (double)T;
 }
 
+// Classification rawPrediction (numClasses == 2).  stats4[node] = (sum w, sum w*y, ., .): class counts (c0, c1) = (stats[0] - stats[1], stats[1]).
+// mode 0: RandomForestClassificationModel.predictRaw — votes(k) += classCounts(k) / total for every tree, in tree order;
+// mode 1: DecisionTreeClassificationModel.predictRaw — the class counts of tree 0's leaf.
+__global__ void predict_raw_kernel(const double* X, int64_t ldx, int64_t n_rows, int T, const int64_t* tree_off, const int32_t* feature,
+                                   const double* threshold, const int32_t* left, const int32_t* right, const double* stats4,
+                                   const int32_t* ncat, const int32_t* cat_off, const int32_t* cat_len, const double* cats, int mode, double* out2) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows) return;
+  const double* x = X + (size_t)i * ldx;
+  double v0 = 0.0, v1 = 0.0;
+  const int nt = mode == 1 ? 1 : T;
+  for (int t = 0; t < nt; t++) {
+    const int64_t base = tree_off[t];
+    int n = 0;
+    int f;
+    while ((f = feature[base + n]) >= 0) {
+      const double xv = x[f];
+      bool l;
+      if (ncat[base + n] == 0) l = xv <= threshold[base + n];
+      else {
+        l = false;
+        const int co = cat_off[base + n], cl = cat_len[base + n];
+        for (int c = 0; c < cl; c++) if (cats[co + c] == xv) { l = true; break; }
+      }
+      n = l ? left[base + n] : right[base + n];
+    }
+    const double c1 = stats4[(size_t)(base + n) * 4 + 1];
+    const double c0 = stats4[(size_t)(base + n) * 4] - c1;
+    if (mode == 1) { v0 = c0; v1 = c1; }
+    else {
+      const double total = c0 + c1;
+      if (total != 0) { v0 += c0 / total; v1 += c1 / total; }
+    }
+  }
+  out2[(size_t)i * 2] = v0; out2[(size_t)i * 2 + 1] = v1;
+}
+
 
 }  // namespace b2rf
 
@@ -57,6 +94,16 @@ int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, cons
   predict_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, d_feature, d_threshold, d_left, d_right,
                                                                                      d_prediction, d_ncat, d_cat_off, d_cat_len, d_cats, d_out);
   return cuda_ok(cudaGetLastError(), "b2rf_predict") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+int b2rf_predict_raw(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,
+                     const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_stats4, const int32_t* d_ncat,
+                     const int32_t* d_cat_off, const int32_t* d_cat_len, const double* d_cats, int32_t mode, double* d_out2, void* stream) {
+  if (mode != 0 && mode != 1) { set_error("b2rf_predict_raw: mode must be 0 (forest votes) or 1 (single-tree class counts)"); return B2RF_ERR_ARG; }
+  if (n_rows <= 0) return B2RF_OK;
+  predict_raw_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, d_feature, d_threshold, d_left,
+                                                                                         d_right, d_stats4, d_ncat, d_cat_off, d_cat_len, d_cats, mode, d_out2);
+  return cuda_ok(cudaGetLastError(), "b2rf_predict_raw") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
 }  // extern "C"

@@ -64,12 +64,29 @@ class Forest:
     trace_i: np.ndarray = None
     trace_d: np.ndarray = None
     uid: str = ""
+    impurity_kind: str = "variance"   # "variance": regression; "gini" / "entropy": binary classification (stats hold class counts, see class_counts)
     _dev: dict = field(default_factory=dict, repr=False)
 
     # ---- structure ----
     @property
     def num_trees(self) -> int:
         return len(self.tree_off) - 1
+
+    @property
+    def is_classification(self) -> bool:
+        return self.impurity_kind != "variance"
+
+    @property
+    def num_classes(self) -> int:
+        return 2 if self.is_classification else 0
+
+    @property
+    def class_counts(self) -> np.ndarray:
+        """impurityStats of a classification node: [n, 2] class counts.  The trainer accumulates (sum w, sum w*y) with y in {0, 1},
+        so count(class 1) = stats[:, 1] and count(class 0) = stats[:, 0] - stats[:, 1], both exact integers."""
+        if not self.is_classification:
+            raise ValueError("class_counts: this is a regression model")
+        return np.stack([self.stats[:, 0] - self.stats[:, 1], self.stats[:, 1]], axis=1)
 
     def tree_slice(self, t: int) -> slice:
         return slice(int(self.tree_off[t]), int(self.tree_off[t + 1]))
@@ -125,12 +142,14 @@ class Forest:
     def to_debug_string(self, ensemble: bool | None = None) -> str:
         ensemble = self.num_trees > 1 if ensemble is None else ensemble
         out = []
+        kind = "Classification" if self.is_classification else "Regression"
+        ncls = f"numClasses={self.num_classes}, " if self.is_classification else ""
         if not ensemble:
-            out.append(f"DecisionTreeRegressionModel: uid={self.uid}, depth={self.depth(0)}, numNodes={self.num_nodes(0)}, "
-                       f"numFeatures={self.num_features}\n")
+            out.append(f"DecisionTree{kind}Model: uid={self.uid}, depth={self.depth(0)}, numNodes={self.num_nodes(0)}, "
+                       f"{ncls}numFeatures={self.num_features}\n")
             self._subtree(0, 0, 2, out)
         else:
-            out.append(f"RandomForestRegressionModel: uid={self.uid}, numTrees={self.num_trees}, numFeatures={self.num_features}\n")
+            out.append(f"RandomForest{kind}Model: uid={self.uid}, numTrees={self.num_trees}, {ncls}numFeatures={self.num_features}\n")
             for t in range(self.num_trees):
                 out.append(f"  Tree {t} (weight 1.0):\n")
                 self._subtree(int(self.tree_off[t]), 0, 4, out)
@@ -147,7 +166,8 @@ class Forest:
             self._dev[key] = dict(tree_off=T(self.tree_off, torch.int64), feature=T(self.feature, torch.int32),
                                   threshold=T(self.threshold, torch.float64), left=T(self.left, torch.int32), right=T(self.right, torch.int32),
                                   prediction=T(self.prediction, torch.float64), ncat=T(self.ncat, torch.int32),
-                                  cat_off=T(self.cat_off, torch.int32), cat_len=T(self.cat_len, torch.int32), cats=T(cats, torch.float64))
+                                  cat_off=T(self.cat_off, torch.int32), cat_len=T(self.cat_len, torch.int32), cats=T(cats, torch.float64),
+                                  stats=T(self.stats, torch.float64))
         return self._dev[key]
 
     def predict(self, X):
@@ -156,6 +176,9 @@ class Forest:
         from ._lib import check, lib
         if not (isinstance(X, torch.Tensor) and X.is_cuda):
             raise TypeError("Forest.predict needs a CUDA tensor: this package has no CPU path")
+        if self.is_classification:   # raw2prediction without thresholds: argmax of rawPrediction, first maximum
+            raw = self.predict_raw(X)
+            return (raw[:, 1] > raw[:, 0]).to(torch.float64)
         X = X.to(torch.float64).contiguous()
         d = self._device_arrays(X.device)
         out = torch.empty(X.shape[0], dtype=torch.float64, device=X.device)
@@ -166,3 +189,31 @@ class Forest:
                                      d["ncat"].data_ptr(), d["cat_off"].data_ptr(), d["cat_len"].data_ptr(), d["cats"].data_ptr(),
                                      out.data_ptr(), C.c_void_p(st)))
         return out
+
+    def predict_raw(self, X, single_tree: bool | None = None):
+        """Classification rawPrediction, torch.float64 [n, 2] on X's device (K7, b2rf_predict_raw): for an ensemble the per-tree
+        normalised class counts summed in tree order (RandomForestClassificationModel.predictRaw); for a single
+        DecisionTreeClassificationModel (single_tree, default numTrees == 1) the leaf's class counts."""
+        import torch
+        from ._lib import check, lib
+        if not self.is_classification:
+            raise ValueError("predict_raw: this is a regression model")
+        if not (isinstance(X, torch.Tensor) and X.is_cuda):
+            raise TypeError("Forest.predict_raw needs a CUDA tensor: this package has no CPU path")
+        X = X.to(torch.float64).contiguous()
+        d = self._device_arrays(X.device)
+        out = torch.empty((X.shape[0], 2), dtype=torch.float64, device=X.device)
+        mode = 1 if ((self.num_trees == 1) if single_tree is None else single_tree) else 0
+        with torch.cuda.device(X.device):
+            st = torch.cuda.current_stream().cuda_stream
+            check(lib().b2rf_predict_raw(X.data_ptr(), X.stride(0), X.shape[0], self.num_trees, d["tree_off"].data_ptr(), d["feature"].data_ptr(),
+                                         d["threshold"].data_ptr(), d["left"].data_ptr(), d["right"].data_ptr(), d["stats"].data_ptr(),
+                                         d["ncat"].data_ptr(), d["cat_off"].data_ptr(), d["cat_len"].data_ptr(), d["cats"].data_ptr(),
+                                         mode, out.data_ptr(), C.c_void_p(st)))
+        return out
+
+    def predict_proba(self, X, single_tree: bool | None = None):
+        """ProbabilisticClassificationModel.normalizeToProbabilitiesInPlace on rawPrediction (rows whose raw sum is 0 stay 0)."""
+        raw = self.predict_raw(X, single_tree)
+        tot = raw.sum(dim=1, keepdim=True)
+        return raw / tot.where(tot != 0, tot.new_ones(()))

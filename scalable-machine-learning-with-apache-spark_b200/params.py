@@ -46,9 +46,15 @@ class TreeParams:
     def copy(self, **kw) -> "TreeParams":
         return replace(self, **kw)
 
+    IMPURITIES = {"variance": 0, "gini": 1, "entropy": 2}
+
+    @property
+    def is_classification(self) -> bool:
+        return self.impurity != "variance"
+
     def validate(self):
-        if self.impurity != "variance":
-            raise ValueError(f"impurity must be 'variance' for regression, got {self.impurity!r}")
+        if self.impurity not in self.IMPURITIES:
+            raise ValueError(f"impurity must be 'variance' (regression) or 'gini' / 'entropy' (classification), got {self.impurity!r}")
         if self.maxDepth < 0 or self.maxDepth > 30:
             raise ValueError(f"DecisionTree currently only supports maxDepth <= 30, but was given maxDepth = {self.maxDepth}.")
         if self.maxBins < 2:
@@ -61,11 +67,14 @@ class TreeParams:
             raise ValueError("minWeightFractionPerNode must be in [0, 0.5)")
 
     def features_per_node(self, F: int) -> int:
-        return check(lib().b2rf_features_per_node(str(self.featureSubsetStrategy).encode(), int(F), _to_int(self.numTrees, 'numTrees')))
+        strategy = str(self.featureSubsetStrategy)
+        if strategy == "auto" and self.is_classification:   # DecisionTreeMetadata: classification forests default to sqrt
+            strategy = "all" if _to_int(self.numTrees, "numTrees") == 1 else "sqrt"
+        return check(lib().b2rf_features_per_node(strategy.encode(), int(F), _to_int(self.numTrees, 'numTrees')))
 
     def to_c(self, F: int) -> B2rfParams:
         self.validate()
         return B2rfParams(_to_int(self.maxDepth, "maxDepth"), _to_int(self.maxBins, "maxBins"),
                           _to_int(self.minInstancesPerNode, "minInstancesPerNode"), _to_int(self.numTrees, "numTrees"),
                           self.features_per_node(F), int(self.maxMemoryInMB), int(bool(self.bootstrap)), 0, float(self.minInfoGain),
-                          float(self.minWeightFractionPerNode), float(self.subsamplingRate), int(self.seed))
+                          float(self.minWeightFractionPerNode), float(self.subsamplingRate), int(self.seed), self.IMPURITIES[self.impurity], 0)

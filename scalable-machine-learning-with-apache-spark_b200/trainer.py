@@ -203,6 +203,15 @@ def _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode
                 fraction=fraction, arity_d=torch.as_tensor(arity_np, device=dev))
 
 
+def _check_labels(y, params):
+    """Classification (gini / entropy) is binary here: labels must be exactly 0.0 or 1.0 (MLlib: 'Classification labels should be
+    in [0 to numClasses - 1]'); numClasses > 2 needs per-class statistics that K4 does not build."""
+    if params.is_classification and y.numel() and not bool(((y == 0) | (y == 1)).all()):
+        from ._lib import IllegalArgumentException
+        raise IllegalArgumentException(-3, "requirement failed: Classification labels should be in [0 to 1] (this build trains binary "
+                                       "classifiers only: numClasses == 2). Found labels other than 0.0 / 1.0.")
+
+
 def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace):
     """RandomForest.run's while (nodeStack.nonEmpty) loop: one begin_group / [all_reduce] / end_group per node group."""
     L = lib()
@@ -237,6 +246,7 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
     if dbg:
         print(f"[b2rf timing] create+bind {tb - tc:.4f} groups {tl - tb:.4f} export {te - tl:.4f} destroy {time.perf_counter() - te:.4f}", flush=True)
     forest.thresholds, forest.nsplits = thr_h, ns_h
+    forest.impurity_kind = params.impurity
     forest.counters.update(rows=S["N"], rows_local=n_local, partitions=len(S["po"]) - 1, world=S["world"], fraction=S["fraction"])
     return forest
 
@@ -259,6 +269,7 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
     t_start = time.perf_counter()
     with torch.cuda.device(dev):
         y = y.to(torch.float64).contiguous()
+        _check_labels(y, params)
         n_local, F = X.shape
         S = _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode)
         T = params.numTrees
@@ -322,6 +333,8 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
     params_list = list(params_list)
     with torch.cuda.device(dev):
         y = y.to(torch.float64).contiguous()
+        for params in params_list:
+            _check_labels(y, params)
         n_local, F = X.shape
         ld = _pad(n_local)
         shared = {}
@@ -378,6 +391,7 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
             for c in cands:
                 fo = _export(c["h"], F, False)
                 fo.thresholds, fo.nsplits = c["thr_h"], c["ns_h"]
+                fo.impurity_kind = c["params"].impurity
                 S = c["S"]
                 fo.counters.update(rows=S["N"], rows_local=n_local, partitions=len(S["po"]) - 1, world=S["world"], fraction=S["fraction"])
                 forests.append(fo)
@@ -420,6 +434,7 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
     t_start = time.perf_counter()
     with torch.cuda.device(dev):
         n_local, F = Xh.shape
+        _check_labels(yh, params)
         S = _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode)
         T = params.numTrees
         main = torch.cuda.current_stream()

@@ -111,3 +111,30 @@ def assert_parity_allowing_ties(g, o, max_ties):
         print(f"documented gain ties (tree, heap node id): {ties}")
         assert_forest_parity_with_ties(g, o, set(ties))
     return ties
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Binary classification (gini / entropy).  The product keeps (sum w, sum w*y) with y in {0, 1}; the oracle accumulates
+# genuine per-class counts.  Both are exact integers, so everything except Entropy's log must agree bit for bit.
+# ---------------------------------------------------------------------------------------------------------------
+def assert_classifier_parity(g, o, exact=True):
+    assert np.array_equal(g.tree_off, o.tree_off), f"tree sizes differ: {np.diff(g.tree_off)[:10]} vs {np.diff(o.tree_off)[:10]}"
+    assert np.array_equal(g.feature, o.feature), _first_diff("feature", g, o, g.feature, o.feature)
+    assert np.array_equal(g.left, o.left) and np.array_equal(g.right, o.right)
+    assert np.array_equal(g.threshold, o.threshold), _first_diff("threshold", g, o, g.threshold, o.threshold)
+    assert np.array_equal(g.ncat, o.ncat)
+    for i in np.nonzero(g.ncat > 0)[0]:
+        gs = sorted(g.cats[g.cat_off[i]:g.cat_off[i] + g.cat_len[i]])
+        os_ = sorted(o.cats[o.cat_off[i]:o.cat_off[i] + o.cat_len[i]])
+        assert gs == os_, f"node {i}: left categories differ {gs} vs {os_}"
+    assert np.array_equal(g.class_counts, o.stats[:, :2]), "class counts differ"
+    assert np.array_equal(g.prediction, o.prediction), "class predictions differ"
+    m = o.impurity >= 0
+    assert np.array_equal(m, g.impurity >= 0)
+    if exact:      # gini: divisions, products and differences of exact integers, -fmad=false on the device
+        assert np.array_equal(g.impurity[m], o.impurity[m]) and np.array_equal(g.gain, o.gain)
+    else:          # entropy: device log vs libm log, each within an ulp or so
+        np.testing.assert_allclose(g.impurity[m], o.impurity[m], rtol=1e-12, atol=1e-15)
+        np.testing.assert_allclose(g.gain, o.gain, rtol=1e-9, atol=1e-13)
+    if getattr(g, "trace_i", None) is not None and len(g.trace_i):
+        assert np.array_equal(g.trace_i, o.trace_i), "nodes evaluated in a different order or with different decisions"

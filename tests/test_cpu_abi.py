@@ -67,7 +67,10 @@ def test_params_validation(b2rf):
     with pytest.raises(ValueError):
         b2rf.TreeParams(maxDepth=31).to_c(4)
     with pytest.raises(ValueError):
-        b2rf.TreeParams(impurity="gini").to_c(4)
+        b2rf.TreeParams(impurity="mse").to_c(4)
+    g = b2rf.TreeParams(impurity="gini", numTrees=10).to_c(16)     # classification forests: featureSubsetStrategy auto -> sqrt
+    assert g.impurity == 1 and g.featuresPerNode == 4
+    assert b2rf.TreeParams(impurity="entropy").to_c(16).impurity == 2 and b2rf.TreeParams(impurity="entropy").to_c(16).featuresPerNode == 16
     with pytest.raises(ValueError):
         b2rf.TreeParams(subsamplingRate=0.0).to_c(4)
     c = b2rf.TreeParams(maxDepth=4.0, numTrees=37.0).to_c(4)      # `ML 08 - Hyperopt.py:97`: integral floats from hp.quniform

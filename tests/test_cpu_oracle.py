@@ -122,3 +122,23 @@ def test_golden_fixtures(oracle, b2rf):
         assert [float(v).hex() for v in f.threshold] == gold["threshold_hex"]
         assert [float(v).hex() for v in f.prediction] == gold["prediction_hex"]
         assert f.stats[:, 0].tolist() == gold["count"]
+
+
+def test_classifier_known_answers(oracle):
+    """Binary classification restatement against the values available without a JVM: the pyspark DecisionTreeClassifier doctest
+    (two rows -> depth 1, 3 nodes, rawPrediction [1, 0] / [0, 1]) and the upstream 600/400 categorical stump data (root gini
+    1 - 0.6^2 - 0.4^2 = 0.48, categories ordered by their class-1 count so category 1 goes left)."""
+    X = np.array([[1.0], [0.0]]); y = np.array([1.0, 0.0])
+    f = oracle.fit(X, y, [0], maxDepth=2, impurity="gini")
+    assert len(f.feature) == 3 and f.threshold[0] == 0.5
+    assert f.predict_raw(np.array([[-1.0], [1.0]])).tolist() == [[1.0, 0.0], [0.0, 1.0]]
+    assert f.predict(np.array([[-1.0], [1.0]])).tolist() == [0.0, 1.0]
+    Xs = np.array([[0.0, 1.0]] * 600 + [[1.0, 0.0]] * 400); ys = np.array([1.0] * 600 + [0.0] * 400)
+    g = oracle.fit(Xs, ys, [3, 3], maxDepth=2, maxBins=100, impurity="gini")
+    assert g.feature.tolist() == [0, -1, -1] and g.cats.tolist() == [1.0]
+    assert g.impurity[0] == pytest.approx(0.48, rel=1e-15) and g.gain[0] == pytest.approx(0.48, rel=1e-15)
+    assert g.stats[:, :2].tolist() == [[400.0, 600.0], [400.0, 0.0], [0.0, 600.0]] and g.prediction.tolist() == [1.0, 0.0, 1.0]
+    e = oracle.fit(Xs, ys, [3, 3], maxDepth=2, maxBins=100, impurity="entropy")
+    assert e.impurity[0] == pytest.approx(-(0.6 * np.log2(0.6) + 0.4 * np.log2(0.4)), rel=1e-14)
+    with pytest.raises(oracle.OracleError):
+        oracle.fit(np.zeros((3, 1)), np.array([0.0, 1.0, 2.0]), [0], impurity="gini")

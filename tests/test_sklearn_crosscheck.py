@@ -52,3 +52,16 @@ def test_cuda_path_matches_sklearn_exact_search(b2rf, cuda, seed, depth):
     np.testing.assert_allclose(f.predict(torch.as_tensor(X, device=cuda)).cpu().numpy(), m.predict(X), rtol=1e-9, atol=1e-9)
     assert int((f.left < 0).sum()) == m.get_n_leaves()
     assert _node_signature_ours(f) == _node_signature_sklearn(m)
+
+
+@pytest.mark.parametrize("crit", ["gini", "entropy"])
+def test_oracle_classifier_matches_sklearn_exact_search(oracle, crit):
+    """Binary classification: same predictions on the training rows as sklearn's exhaustive search (MLlib additionally merges
+    sibling leaves that predict the same class, so leaf counts differ)."""
+    rng = np.random.default_rng(5); n = 20000
+    X = rng.integers(0, 12, size=(n, 6)).astype(np.float64)
+    logit = 1.2 * (X[:, 0] > 4) + 0.8 * (X[:, 1] > 7) - 1.0 * (X[:, 2] <= 2) * (X[:, 3] > 5) + 0.05 * X[:, 4] - 0.6
+    y = (rng.random(n) < 1 / (1 + np.exp(-logit))).astype(np.float64)
+    o = oracle.fit(X, y, [0] * 6, maxDepth=4, maxBins=32, impurity=crit)
+    m = sklearn_tree.DecisionTreeClassifier(max_depth=4, criterion=crit, random_state=0).fit(X, y)
+    assert np.array_equal(o.predict(X), m.predict(X))
