@@ -31,6 +31,12 @@ class TypeConverters:
         return float(v)
 
     @staticmethod
+    def toListFloat(v):
+        if v is None:
+            return None
+        return [TypeConverters.toFloat(x) for x in list(v)]
+
+    @staticmethod
     def toString(v):
         if isinstance(v, str):
             return v
@@ -226,6 +232,29 @@ class SparseVector:
 
     def __repr__(self):
         return f"SparseVector({self.size}, {{{', '.join(f'{i}: {v}' for i, v in zip(self.indices, self.values))}}})"
+
+
+class DenseVector:
+    def __init__(self, values):
+        self.values = np.asarray(values, np.float64)
+
+    def toArray(self):
+        return self.values
+
+    def __iter__(self):
+        return iter(self.values)
+
+    def __len__(self):
+        return len(self.values)
+
+    def __getitem__(self, i):
+        return self.values[i]
+
+    def __eq__(self, other):
+        return np.array_equal(self.values, np.asarray(other.toArray() if hasattr(other, "toArray") else other, np.float64))
+
+    def __repr__(self):
+        return f"DenseVector([{', '.join(repr(float(v)) for v in self.values)}])"
 
 
 class _Field:

@@ -24,6 +24,8 @@ from .forest import Forest
 SPARK_VERSION = "3.1.2"
 _DT_CLASS = "org.apache.spark.ml.regression.DecisionTreeRegressionModel"
 _RF_CLASS = "org.apache.spark.ml.regression.RandomForestRegressionModel"
+_DTC_CLASS = "org.apache.spark.ml.classification.DecisionTreeClassificationModel"
+_RFC_CLASS = "org.apache.spark.ml.classification.RandomForestClassificationModel"
 
 
 def _node_rows(fo: Forest, t: int):
@@ -41,8 +43,10 @@ def _node_rows(fo: Forest, t: int):
                      "numCategories": int(fo.ncat[a])}
         else:
             split = {"featureIndex": int(fo.feature[a]), "leftCategoriesOrThreshold": [float(fo.threshold[a])], "numCategories": -1}
+        # impurityStats: regression (weight, sum, sum of squares); classification the class counts
+        ist = [float(fo.stats[a, 0] - fo.stats[a, 1]), float(fo.stats[a, 1])] if fo.is_classification else [float(v) for v in fo.stats[a, :3]]
         rows.append({"id": i, "prediction": float(fo.prediction[a]), "impurity": float(fo.impurity[a]),
-                     "impurityStats": [float(v) for v in fo.stats[a, :3]], "rawCount": int(fo.stats[a, 3]),
+                     "impurityStats": ist, "rawCount": int(fo.stats[a, 3]),
                      "gain": -1.0 if leaf else float(fo.gain[a]), "leftChild": -1 if leaf else int(fo.left[a]),
                      "rightChild": -1 if leaf else int(fo.right[a]), "split": split})
     return rows
@@ -75,8 +79,11 @@ def save_model(model, path: str, overwrite: bool = False):
     os.makedirs(os.path.join(path, "metadata"))
     os.makedirs(os.path.join(path, "data"))
     pm, dm = _param_maps(model)
-    meta = {"class": _RF_CLASS if ensemble else _DT_CLASS, "timestamp": int(time.time() * 1000), "sparkVersion": SPARK_VERSION,
+    cls_dt, cls_rf = (_DTC_CLASS, _RFC_CLASS) if fo.is_classification else (_DT_CLASS, _RF_CLASS)
+    meta = {"class": cls_rf if ensemble else cls_dt, "timestamp": int(time.time() * 1000), "sparkVersion": SPARK_VERSION,
             "uid": model.uid, "paramMap": pm, "defaultParamMap": dm, "numFeatures": int(fo.num_features)}
+    if fo.is_classification:
+        meta["numClasses"] = int(fo.num_classes)
     if ensemble:
         meta["numTrees"] = int(fo.num_trees)
     with open(os.path.join(path, "metadata", "part-00000"), "w") as f:
@@ -89,8 +96,8 @@ def save_model(model, path: str, overwrite: bool = False):
         rows = [{"treeID": t, "nodeData": r} for t in range(fo.num_trees) for r in _node_rows(fo, t)]
         tbl = pa.Table.from_pylist(rows, schema=pa.schema([("treeID", pa.int32()), ("nodeData", node_t)]))
         os.makedirs(os.path.join(path, "treesMetadata"))
-        tm = [{"treeID": t, "metadata": json.dumps({"class": _DT_CLASS, "timestamp": meta["timestamp"], "sparkVersion": SPARK_VERSION,
-                                                    "uid": f"dtr_{model.uid}_{t}", "paramMap": {}, "defaultParamMap": dm,
+        tm = [{"treeID": t, "metadata": json.dumps({"class": cls_dt, "timestamp": meta["timestamp"], "sparkVersion": SPARK_VERSION,
+                                                    "uid": f"{'dtc' if fo.is_classification else 'dtr'}_{model.uid}_{t}", "paramMap": {}, "defaultParamMap": dm,
                                                     "numFeatures": int(fo.num_features)}), "weights": 1.0} for t in range(fo.num_trees)]
         pq.write_table(pa.Table.from_pylist(tm, schema=pa.schema([("treeID", pa.int32()), ("metadata", pa.string()), ("weights", pa.float64())])),
                        os.path.join(path, "treesMetadata", "part-00000.parquet"))
@@ -108,7 +115,10 @@ def load_forest(path: str):
     rows = []
     for fn in files:
         rows += pq.read_table(fn).to_pylist()
-    ensemble = meta["class"].endswith("RandomForestRegressionModel")
+    ensemble = meta["class"].endswith(("RandomForestRegressionModel", "RandomForestClassificationModel"))
+    classification = meta["class"].endswith("ClassificationModel")
+    if classification and int(meta.get("numClasses", 2)) != 2:
+        raise ValueError(f"{path}: numClasses = {meta.get('numClasses')}; only binary classification models can be loaded")
     if ensemble:
         T = int(meta["numTrees"])
         per = [[] for _ in range(T)]
@@ -130,7 +140,10 @@ def load_forest(path: str):
             cols["left"].append(r["leftChild"]); cols["right"].append(r["rightChild"])
             cols["prediction"].append(r["prediction"]); cols["impurity"].append(r["impurity"]); cols["gain"].append(0.0 if leaf else r["gain"])
             st = list(r["impurityStats"]) + [0.0] * 3
-            cols["stats"].append([st[0], st[1], st[2], float(r["rawCount"])])
+            if classification:     # class counts (c0, c1) -> the trainer's (sum w, sum w*y, sum w*y*y) with y in {0, 1}
+                cols["stats"].append([st[0] + st[1], st[1], st[1], float(r["rawCount"])])
+            else:
+                cols["stats"].append([st[0], st[1], st[2], float(r["rawCount"])])
             cols["ncat"].append(sp["numCategories"] if cat else 0)
             cols["cat_off"].append(len(cats))
             cols["cat_len"].append(len(sp["leftCategoriesOrThreshold"]) if cat else 0)
@@ -141,6 +154,9 @@ def load_forest(path: str):
                 np.array(cols["left"], np.int32), np.array(cols["right"], np.int32), np.array(cols["prediction"]), np.array(cols["impurity"]),
                 np.array(cols["gain"]), np.array(cols["stats"]).reshape(-1, 4), np.array(cols["ncat"], np.int32),
                 np.array(cols["cat_off"], np.int32), np.array(cols["cat_len"], np.int32), np.array(cats, np.float64), uid=meta["uid"])
+    if classification:
+        imp = meta.get("paramMap", {}).get("impurity", meta.get("defaultParamMap", {}).get("impurity", "gini"))
+        fo.impurity_kind = str(imp).lower()
     return meta, fo
 
 

@@ -20,11 +20,11 @@ import numpy as np
 
 try:  # real Spark
     from pyspark.ml import Estimator, Model
-    from pyspark.ml.linalg import SparseVector
+    from pyspark.ml.linalg import DenseVector, SparseVector
     from pyspark.ml.param import Param, Params, TypeConverters
     HAVE_PYSPARK = True
 except ImportError:  # this image
-    from ._pyspark_stub import Estimator, Model, Param, Params, SparseVector, TypeConverters
+    from ._pyspark_stub import DenseVector, Estimator, Model, Param, Params, SparseVector, TypeConverters
     HAVE_PYSPARK = False
 
 from .forest import Forest
@@ -60,7 +60,8 @@ class _TreeRegressorParams(Params):
     cacheNodeIds = Param(Params, "cacheNodeIds", "If false, the algorithm will pass trees to executors to match instances with nodes. If "
                          "true, the algorithm will cache node IDs for each instance.", TypeConverters.toBoolean)
     checkpointInterval = Param(Params, "checkpointInterval", "set checkpoint interval (>= 1) or disable checkpoint (-1).", TypeConverters.toInt)
-    impurity = Param(Params, "impurity", "Criterion used for information gain calculation (case-insensitive). Supported options: variance",
+    impurity = Param(Params, "impurity", "Criterion used for information gain calculation (case-insensitive). Supported options: variance "
+                     "(regressors); entropy, gini (classifiers)",
                      TypeConverters.toString)
     seed = Param(Params, "seed", "random seed.", TypeConverters.toInt)
     leafCol = Param(Params, "leafCol", "Leaf indices column name. Predicted leaf index of each instance in each tree by preorder.",
@@ -135,18 +136,34 @@ def _extract(dataset, featuresCol, labelCol=None):
     return X, y, sizes
 
 
-def _append_prediction(dataset, predictionCol, pred):
+def _append_columns(dataset, cols: dict):
+    """Appends output columns: 1-D arrays become double columns, 2-D arrays vector columns (rawPrediction, probability)."""
     if HAVE_PYSPARK and hasattr(dataset, "sparkSession"):
         import pandas as pd
+        from pyspark.ml.functions import array_to_vector
         from pyspark.sql import functions as F
         from pyspark.sql.window import Window
         spark = dataset.sparkSession
         idx = dataset.withColumn("__b2rf_i", F.monotonically_increasing_id())
         w = Window.orderBy("__b2rf_i")
         idx = idx.withColumn("__b2rf_r", F.row_number().over(w) - 1)
-        p = spark.createDataFrame(pd.DataFrame({"__b2rf_r": np.arange(len(pred)), predictionCol: pred}))
+        n = len(next(iter(cols.values())))
+        data = {"__b2rf_r": np.arange(n)}
+        for name, v in cols.items():
+            v = np.asarray(v, np.float64)
+            data[name] = v if v.ndim == 1 else list(map(list, v))
+        p = spark.createDataFrame(pd.DataFrame(data))
+        for name, v in cols.items():
+            if np.asarray(v).ndim == 2:
+                p = p.withColumn(name, array_to_vector(F.col(name)))
         return idx.join(p, "__b2rf_r").drop("__b2rf_r", "__b2rf_i")
-    return dataset.withColumn(predictionCol, np.asarray(pred, np.float64))
+    for name, v in cols.items():
+        dataset = dataset.withColumn(name, np.asarray(v, np.float64))
+    return dataset
+
+
+def _append_prediction(dataset, predictionCol, pred):
+    return _append_columns(dataset, {predictionCol: pred})
 
 
 class _ForestModelBase(Model, _TreeRegressorParams):
@@ -194,7 +211,7 @@ class _ForestModelBase(Model, _TreeRegressorParams):
             setattr(m, p.name, p._copy_new_parent(m)) if hasattr(p, "_copy_new_parent") else None
         m._paramMap, m._defaultParamMap = {}, {}
         m._base_defaults()
-        if isinstance(m, B200RandomForestRegressionModel):
+        if getattr(m, "_ensemble", False):
             m._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True)
         for k, v in meta.get("paramMap", {}).items():
             if m.hasParam(k):
@@ -244,6 +261,7 @@ class B200DecisionTreeRegressionModel(_ForestModelBase):
 
 class B200RandomForestRegressionModel(_ForestModelBase):
     _ensemble = True
+    _tree_model_cls = B200DecisionTreeRegressionModel
     numTrees = Param(Params, "numTrees", "Number of trees to train (>= 1).", TypeConverters.toInt)
     featureSubsetStrategy = Param(Params, "featureSubsetStrategy", "The number of features to consider for splits at each tree node.",
                                   TypeConverters.toString)
@@ -274,8 +292,9 @@ class B200RandomForestRegressionModel(_ForestModelBase):
         for t in range(fo.num_trees):
             s = fo.tree_slice(t)
             sub = Forest(fo.num_features, np.array([0, s.stop - s.start], np.int64), fo.feature[s], fo.threshold[s], fo.left[s], fo.right[s],
-                         fo.prediction[s], fo.impurity[s], fo.gain[s], fo.stats[s], fo.ncat[s], fo.cat_off[s], fo.cat_len[s], fo.cats)
-            out.append(B200DecisionTreeRegressionModel(sub))
+                         fo.prediction[s], fo.impurity[s], fo.gain[s], fo.stats[s], fo.ncat[s], fo.cat_off[s], fo.cat_len[s], fo.cats,
+                         impurity_kind=fo.impurity_kind)
+            out.append(self._tree_model_cls(sub))
         return out
 
 
@@ -296,7 +315,7 @@ class _TreeEstimatorBase(Estimator, _TreeRegressorParams):
         m._paramMap = {}
         m._defaultParamMap = {}
         m._base_defaults()
-        if isinstance(m, B200RandomForestRegressionModel):
+        if getattr(m, "_ensemble", False):
             m._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True)
         self._copyValues(m)
         return m
@@ -383,6 +402,149 @@ class B200RandomForestRegressor(_TreeEstimatorBase):
                     bootstrap=g("bootstrap"))
 
 
+# ------------------------------------------------------------------------------------------------------------------
+# Binary classifiers: pyspark.ml.classification.DecisionTreeClassifier / RandomForestClassifier as the labs'
+# `Solutions/Labs/ML 07L - Hyperparameter Tuning Lab.py:80-82,105-108,140-155` use them (label priceClass in {0, 1}).
+# numClasses > 2 is rejected at fit time: K4 builds (sum w, sum w*y) only, which holds exactly two class counts.
+# ------------------------------------------------------------------------------------------------------------------
+class _ClassifierParams:
+    rawPredictionCol = Param(Params, "rawPredictionCol", "raw prediction (a.k.a. confidence) column name.", TypeConverters.toString)
+    probabilityCol = Param(Params, "probabilityCol", "Column name for predicted class conditional probabilities. Note: Not all models output "
+                           "well-calibrated probability estimates! These probabilities should be treated as confidences, not precise "
+                           "probabilities.", TypeConverters.toString)
+    thresholds = Param(Params, "thresholds", "Thresholds in multi-class classification to adjust the probability of predicting each class. "
+                       "Array must have length equal to the number of classes, with values > 0, excepting that at most one value may be 0. "
+                       "The class with largest value p/t is predicted, where p is the original probability of that class and t is the "
+                       "class's threshold.", TypeConverters.toListFloat)
+
+    def _base_defaults(self):
+        super()._base_defaults()
+        self._setDefault(impurity="gini", rawPredictionCol="rawPrediction", probabilityCol="probability")
+
+
+class _ClassifierModelBase(_ClassifierParams, _ForestModelBase):
+    @property
+    def numClasses(self):
+        return self._forest.num_classes
+
+    def _raw(self, X):
+        import torch
+        return self._forest.predict_raw(torch.as_tensor(X, device=self._device()), single_tree=not self._ensemble).cpu().numpy()
+
+    @staticmethod
+    def _normalize(raw):      # ProbabilisticClassificationModel.normalizeToProbabilitiesInPlace
+        tot = raw.sum(axis=1, keepdims=True)
+        return raw / np.where(tot != 0, tot, 1.0)
+
+    def _predict_from_probability(self, prob):
+        """probability2prediction: argmax p (first maximum), or argmax p / t when thresholds are set."""
+        if self.isDefined("thresholds") and self.getOrDefault("thresholds") is not None:
+            t = np.asarray(self.getOrDefault("thresholds"), np.float64)
+            if t.shape != (2,) or (t < 0).any() or (t == 0).sum() > 1:
+                raise ValueError(f"thresholds must have length numClasses = 2, values >= 0, at most one 0; got {t.tolist()}")
+            with np.errstate(divide="ignore", invalid="ignore"):
+                scaled = prob / t
+            scaled = np.where(np.isnan(scaled), -np.inf, scaled)
+            return np.argmax(scaled, axis=1).astype(np.float64)
+        return np.argmax(prob, axis=1).astype(np.float64)
+
+    def _one(self, value):
+        return np.asarray(value.toArray() if hasattr(value, "toArray") else value, np.float64).reshape(1, -1)
+
+    def predictRaw(self, value):
+        return DenseVector(self._raw(self._one(value))[0])
+
+    def predictProbability(self, value):
+        return DenseVector(self._normalize(self._raw(self._one(value)))[0])
+
+    def predict(self, value):
+        return float(self._predict_from_probability(self._normalize(self._raw(self._one(value))))[0])
+
+    def _transform(self, dataset):
+        X, _, _ = _extract(dataset, self.getOrDefault("featuresCol"))
+        raw = self._raw(X) if X.shape[0] else np.zeros((0, 2))
+        prob = self._normalize(raw)
+        cols = {}
+        if self.getOrDefault("rawPredictionCol"):
+            cols[self.getOrDefault("rawPredictionCol")] = raw
+        if self.getOrDefault("probabilityCol"):
+            cols[self.getOrDefault("probabilityCol")] = prob
+        if self.getOrDefault("predictionCol"):
+            cols[self.getOrDefault("predictionCol")] = self._predict_from_probability(prob)
+        return _append_columns(dataset, cols)
+
+
+class B200DecisionTreeClassificationModel(_ClassifierModelBase):
+    _ensemble = False
+
+    @property
+    def depth(self):
+        return self._forest.depth(0)
+
+    @property
+    def numNodes(self):
+        return self._forest.num_nodes(0)
+
+
+class B200RandomForestClassificationModel(_ClassifierModelBase):
+    _ensemble = True
+    _tree_model_cls = B200DecisionTreeClassificationModel
+    numTrees = B200RandomForestRegressionModel.numTrees
+    featureSubsetStrategy = B200RandomForestRegressionModel.featureSubsetStrategy
+    subsamplingRate = B200RandomForestRegressionModel.subsamplingRate
+    bootstrap = B200RandomForestRegressionModel.bootstrap
+
+    def __init__(self, forest=None):
+        super().__init__(forest)
+        self._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True)
+
+    getNumTrees = B200RandomForestRegressionModel.getNumTrees
+    treeWeights = B200RandomForestRegressionModel.treeWeights
+    totalNumNodes = B200RandomForestRegressionModel.totalNumNodes
+    trees = B200RandomForestRegressionModel.trees
+
+
+class B200DecisionTreeClassifier(_ClassifierParams, _TreeEstimatorBase):
+    """pyspark.ml.classification.DecisionTreeClassifier (binary labels), trained on the GPU."""
+    _model_cls = B200DecisionTreeClassificationModel
+
+    def __init__(self, **kwargs):
+        super().__init__()
+        self._base_defaults()
+        self.setParams(**kwargs)
+
+    def setParams(self, **kwargs):
+        return self._set(**kwargs)
+
+    def _ensemble_params(self):
+        return dict(numTrees=1, featureSubsetStrategy="all", subsamplingRate=1.0, bootstrap=False)
+
+
+class B200RandomForestClassifier(_ClassifierParams, _TreeEstimatorBase):
+    """pyspark.ml.classification.RandomForestClassifier (binary labels), trained on the GPU (`Solutions/Labs/ML 07L:80-82`)."""
+    _model_cls = B200RandomForestClassificationModel
+    numTrees = B200RandomForestRegressionModel.numTrees
+    featureSubsetStrategy = B200RandomForestRegressionModel.featureSubsetStrategy
+    subsamplingRate = B200RandomForestRegressionModel.subsamplingRate
+    bootstrap = B200RandomForestRegressionModel.bootstrap
+
+    def __init__(self, **kwargs):
+        super().__init__()
+        self._base_defaults()
+        self._setDefault(numTrees=20, featureSubsetStrategy="auto", subsamplingRate=1.0, bootstrap=True)
+        self.setParams(**kwargs)
+
+    def setParams(self, **kwargs):
+        return self._set(**kwargs)
+
+    _ensemble_params = B200RandomForestRegressor._ensemble_params
+
+
+_CLS = ["rawPredictionCol", "probabilityCol", "thresholds"]
+for _c in (B200DecisionTreeClassifier, B200DecisionTreeClassificationModel):
+    _accessors(_c, _COMMON + _CLS)
+for _c in (B200RandomForestClassifier, B200RandomForestClassificationModel):
+    _accessors(_c, _COMMON + _CLS + ["numTrees", "featureSubsetStrategy", "subsamplingRate", "bootstrap"])
 for _c in (B200DecisionTreeRegressor, B200DecisionTreeRegressionModel):
     _accessors(_c, _COMMON)
 for _c in (B200RandomForestRegressor, B200RandomForestRegressionModel):

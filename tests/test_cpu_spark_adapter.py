@@ -117,3 +117,66 @@ def test_persistence_round_trip_mllib_layout(sp, b2rf, oracle, tmp_path):
         assert np.array_equal(f2.stats[:, :3], fo.stats[:, :3]) and np.array_equal(f2.gain, fo.gain)
         assert [sorted(f2.cats[o_:o_ + n]) for o_, n in zip(f2.cat_off, f2.cat_len)] == [sorted(fo.cats[o_:o_ + n]) for o_, n in zip(fo.cat_off, fo.cat_len)]
         assert m2.toDebugString == m.toDebugString
+
+
+def _classifier_forest(b2rf, o, F):
+    """Product-side Forest from the oracle's classification arrays: the trainer's statistics are (sum w, sum w*y, sum w*y*y, raw)
+    with y in {0, 1}; the oracle keeps (count0, count1, 0, raw)."""
+    st = np.stack([o.stats[:, 0] + o.stats[:, 1], o.stats[:, 1], o.stats[:, 1], o.stats[:, 3]], axis=1)
+    return b2rf.Forest(F, o.tree_off, o.feature, o.threshold, o.left, o.right, o.prediction, o.impurity, o.gain, st, o.ncat, o.cat_off,
+                       o.cat_len, o.cats, impurity_kind=o.impurity_kind)
+
+
+def test_classifier_defaults_and_params(sp):
+    """pyspark 3.1.2 DecisionTreeClassifier / RandomForestClassifier defaults (`Solutions/Labs/ML 07L:80-82`)."""
+    dt = sp.B200DecisionTreeClassifier()
+    assert (dt.getImpurity(), dt.getMaxDepth(), dt.getMaxBins(), dt.getRawPredictionCol(), dt.getProbabilityCol(), dt.getPredictionCol()) == \
+        ("gini", 5, 32, "rawPrediction", "probability", "prediction")
+    rf = sp.B200RandomForestClassifier(labelCol="priceClass", maxBins=40, seed=42)
+    assert (rf.getNumTrees(), rf.getFeatureSubsetStrategy(), rf.getBootstrap(), rf.getImpurity()) == (20, "auto", True, "gini")
+    p = rf.copy({rf.maxDepth: 4.0, rf.numTrees: 10, rf.impurity: "Entropy"})._tree_params()
+    assert (p.maxDepth, p.numTrees, p.impurity, p.bootstrap) == (4, 10, "entropy", True)
+    assert p.features_per_node(33) == 6                               # classification forests: auto -> sqrt
+    assert "thresholds:" in rf.explainParams() and "rawPredictionCol:" in rf.explainParams()
+    rf.setThresholds([0.3, 0.7])
+    assert rf.getThresholds() == [0.3, 0.7]
+
+
+def test_classifier_model_api_and_persistence(sp, b2rf, oracle, tmp_path):
+    import json
+    X, y, arity = b2rf.synth.airbnb(1500)
+    X, y = X.numpy(), (y.numpy() > np.median(y.numpy())).astype(np.float64)
+    for T in (1, 4):
+        o = oracle.fit(X, y, arity, maxDepth=4, maxBins=40, numTrees=T, bootstrap=T > 1, seed=3, impurity="gini")
+        fo = _classifier_forest(b2rf, o, 33)
+        est = (sp.B200DecisionTreeClassifier if T == 1 else sp.B200RandomForestClassifier)(maxDepth=4, maxBins=40, labelCol="priceClass")
+        m = est._make_model(fo)
+        assert m.numClasses == 2 and m.numFeatures == 33 and abs(sum(m.featureImportances) - 1.0) < 1e-12
+        head = "DecisionTreeClassificationModel: uid=" if T == 1 else "RandomForestClassificationModel: uid="
+        assert m.toDebugString.startswith(head) and "numClasses=2, numFeatures=33" in m.toDebugString.splitlines()[0]
+        if T > 1:
+            assert len(m.trees) == T and m.trees[0].numClasses == 2 and m.treeWeights == [1.0] * T
+        path = str(tmp_path / f"cls{T}")
+        m.write().overwrite().save(path)
+        meta = json.loads(open(path + "/metadata/part-00000").readline())
+        assert meta["class"] == "org.apache.spark.ml.classification." + ("DecisionTreeClassificationModel" if T == 1 else "RandomForestClassificationModel")
+        assert meta["numClasses"] == 2 and meta["paramMap"]["maxBins"] == 40
+        m2 = type(m).load(path)
+        f2 = m2._forest
+        assert f2.is_classification and f2.impurity_kind == "gini" and m2.getLabelCol() == "priceClass"
+        assert np.array_equal(f2.class_counts, fo.class_counts) and np.array_equal(f2.class_counts, o.stats[:, :2])
+        for a in ("tree_off", "feature", "threshold", "left", "right", "prediction"):
+            assert np.array_equal(getattr(f2, a), getattr(fo, a)), a
+        assert m2.toDebugString == m.toDebugString
+
+
+def test_classifier_thresholds_rule(sp, b2rf, oracle):
+    """probability2prediction: argmax of p / t; without thresholds the first maximum of p."""
+    o = oracle.fit(np.array([[1.0], [0.0]]), np.array([1.0, 0.0]), [0], maxDepth=2, impurity="gini")
+    m = sp.B200DecisionTreeClassifier()._make_model(_classifier_forest(b2rf, o, 1))
+    prob = np.array([[0.5, 0.5], [0.6, 0.4], [0.2, 0.8]])
+    assert m._predict_from_probability(prob).tolist() == [0.0, 0.0, 1.0]
+    m.setThresholds([0.8, 0.2])
+    assert m._predict_from_probability(prob).tolist() == [1.0, 1.0, 1.0]
+    m.setThresholds([0.0, 1.0])
+    assert m._predict_from_probability(np.array([[0.1, 0.9], [0.0, 1.0]])).tolist() == [0.0, 1.0]   # 0.1 / 0 = inf wins; 0 / 0 is skipped

@@ -103,3 +103,44 @@ def test_classifier_matches_sklearn_exact_search(b2rf, cuda):
         g = _fit(b2rf, cuda, X, y, [0] * 6, maxDepth=4, maxBins=32, impurity=crit)
         m = sk.DecisionTreeClassifier(max_depth=4, criterion=crit, random_state=0).fit(X, y)
         assert np.array_equal(g.predict(torch.as_tensor(X, device=cuda)).cpu().numpy(), m.predict(X))
+
+
+def test_spark_adapter_classifier_flow(b2rf, oracle, cuda, tmp_path):
+    """`Solutions/Labs/ML 07L`: RandomForestClassifier(labelCol="priceClass", maxBins=40, seed=42) inside a grid over maxDepth / numTrees,
+    evaluated on the transformed test frame; then the best model is saved and loaded back."""
+    from b2rf import spark as sp
+    from b2rf._pyspark_stub import LocalFrame, ml_attr_metadata
+    X, y, arity = _airbnb_binary(b2rf, 7146)
+    ntr = 5716
+    meta = {"features": ml_attr_metadata(arity)}
+    train = LocalFrame({"features": X[:ntr], "priceClass": y[:ntr]}, meta, num_partitions=4)
+    test = LocalFrame({"features": X[ntr:], "priceClass": y[ntr:]}, meta)
+    po = np.array([0, 1429, 2858, 4287, 5716])
+    rf = sp.B200RandomForestClassifier(labelCol="priceClass", maxBins=40, seed=42)
+    grid = [{rf.maxDepth: d, rf.numTrees: t} for d in (2, 5) for t in (5, 10)]
+    got = dict(rf.fitMultiple(train, grid))
+    assert sorted(got) == [0, 1, 2, 3]
+    for i, pm in enumerate(grid):
+        m = got[i]
+        o = oracle.fit(X[:ntr], y[:ntr], arity, maxDepth=pm[rf.maxDepth], maxBins=40, numTrees=pm[rf.numTrees], bootstrap=True, seed=42,
+                       part_offsets=po, impurity="gini")
+        assert m.getNumTrees == pm[rf.numTrees] and m.totalNumNodes == len(o.feature) and m.numClasses == 2
+        out = m.transform(test)
+        np.testing.assert_allclose(out.col("rawPrediction"), o.predict_raw(X[ntr:]), rtol=1e-15, atol=0)
+        assert np.array_equal(out.col("prediction"), o.predict(X[ntr:]))
+        np.testing.assert_allclose(out.col("probability").sum(1), 1.0, rtol=1e-12)
+    best = got[3]
+    acc = float((best.transform(test).col("prediction") == y[ntr:]).mean())
+    assert acc > 0.6                                                       # held-out rows of the synthetic listing data
+    v = X[ntr]
+    assert best.predict(v) == best.transform(test).col("prediction")[0]
+    assert list(best.predictProbability(v)) == list(best.transform(test).col("probability")[0])
+    path = str(tmp_path / "rfc")
+    best.write().overwrite().save(path)
+    again = sp.B200RandomForestClassificationModel.load(path)
+    assert np.array_equal(again.transform(test).col("rawPrediction"), best.transform(test).col("rawPrediction"))
+    dt = sp.B200DecisionTreeClassifier(labelCol="priceClass", maxBins=40, impurity="entropy").fit(train)
+    od = oracle.fit(X[:ntr], y[:ntr], arity, maxDepth=5, maxBins=40, part_offsets=po, impurity="entropy")
+    assert dt.numNodes == len(od.feature) and np.array_equal(dt.transform(test).col("rawPrediction"), od.predict_raw(X[ntr:]))
+    with pytest.raises(b2rf.IllegalArgumentException, match="numClasses == 2"):
+        sp.B200DecisionTreeClassifier(labelCol="priceClass").fit(LocalFrame({"features": X[:30], "priceClass": np.arange(30) % 3.0}))
