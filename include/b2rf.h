@@ -159,6 +159,16 @@ int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, cons
                  const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_prediction,
                  const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, const double* d_cats,
                  double* d_out, void* stream);
+/* K7, packed form (the `_transform` fast path): the forest arrays are first packed into one 16-byte record per
+ * node (b2rf_forest_pack, once per model and device; d_packed holds b2rf_forest_pack_bytes(n_nodes) bytes and is caller-owned),
+ * after which a prediction visits one record per node.  Requires the pre-order numbering MLlib's NodeData uses (left child =
+ * next node); the caller checks that and otherwise stays on b2rf_predict.  d_out[n_rows] (mean over trees, tree-order sum) and
+ * d_leaf[n_rows][T] (tree-local index of the leaf each row reaches: leafCol / varianceCol) are each optional, not both NULL. */
+size_t b2rf_forest_pack_bytes(int64_t n_nodes);
+int b2rf_forest_pack(int64_t n_nodes, const int32_t* d_feature, const double* d_threshold, const int32_t* d_right, const double* d_prediction,
+                     const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, void* d_packed, void* stream);
+int b2rf_predict_packed(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const void* d_packed,
+                        const double* d_cats, double* d_out, int32_t* d_leaf, void* stream);
 /* K7, classification (reference call sites `Solutions/Labs/ML 07L:80-82,105-108`): rawPrediction of a binary
  * tree-ensemble classifier, d_out2[n_rows][2].  d_stats4[node][4] are the exported node statistics (sum w, sum w*y, ., .), i.e.
  * class counts (stats[0] - stats[1], stats[1]).  mode 0 = RandomForestClassificationModel.predictRaw (per-tree normalised class

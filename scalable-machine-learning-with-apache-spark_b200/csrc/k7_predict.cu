@@ -43,6 +43,85 @@ __global__ void predict_kernel(const double* X, int64_t ldx, int64_t n_rows, int
   out[i] = acc / (double)T;
 }
 
+// ---- packed-node traversal -------------------------------------------------------------------------------------------
+// One 16-byte record per node, read with a single 128-bit load per visit (the plain kernel above reads five arrays):
+//   leaf:                feat = -1,      v = prediction
+//   continuous split:    feat = f >= 0,  v = threshold,                     left child = next record (pre-order), right = `right`
+//   categorical split:   feat = -2 - f,  v = bits of (cat_off, cat_len)
+// TREES_IN_FLIGHT trees are walked at once per row so several dependent load chains overlap; their leaf values are then
+// added in tree order, which keeps MLlib's summation order.
+struct __align__(16) PackedNode { double v; int32_t feat; int32_t right; };
+
+__global__ void pack_forest_kernel(int64_t n_nodes, const int32_t* feature, const double* threshold, const int32_t* right, const double* prediction,
+                                   const int32_t* ncat, const int32_t* cat_off, const int32_t* cat_len, PackedNode* out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_nodes) return;
+  PackedNode p;
+  const int f = feature[i];
+  if (f < 0) { p.v = prediction[i]; p.feat = -1; p.right = -1; }
+  else if (ncat[i] == 0) { p.v = threshold[i]; p.feat = f; p.right = right[i]; }
+  else { p.v = __hiloint2double(cat_len[i], cat_off[i]); p.feat = -2 - f; p.right = right[i]; }
+  out[i] = p;
+}
+
+constexpr int TREES_IN_FLIGHT = 4;
+template <bool LEAVES>
+__global__ void __launch_bounds__(256) predict_packed_kernel(const double* __restrict__ X, int64_t ldx, int64_t n_rows, int T, const int64_t* __restrict__ tree_off,
+                                                             const PackedNode* __restrict__ nodes, const double* __restrict__ cats, double* out, int32_t* leaf_out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows) return;
+  const double* x = X + (size_t)i * ldx;
+  double acc = 0.0;
+  for (int t0 = 0; t0 < T; t0 += TREES_IN_FLIGHT) {
+    const PackedNode* base[TREES_IN_FLIGHT];
+    int n[TREES_IN_FLIGHT];
+    PackedNode cur[TREES_IN_FLIGHT];
+    bool live[TREES_IN_FLIGHT];
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < TREES_IN_FLIGHT; k++) {
+      live[k] = t0 + k < T;
+      base[k] = nodes + (live[k] ? tree_off[t0 + k] : 0);
+      n[k] = 0;
+      if (live[k]) { cur[k] = base[k][0]; live[k] = cur[k].feat != -1; }
+      else { cur[k].v = 0.0; cur[k].feat = -1; cur[k].right = -1; }
+      any |= live[k];
+    }
+    while (any) {
+      double xv[TREES_IN_FLIGHT];
+#pragma unroll
+      for (int k = 0; k < TREES_IN_FLIGHT; k++) {
+        const int f = cur[k].feat >= 0 ? cur[k].feat : -2 - cur[k].feat;
+        xv[k] = live[k] ? x[f] : 0.0;
+      }
+      any = false;
+#pragma unroll
+      for (int k = 0; k < TREES_IN_FLIGHT; k++) {
+        if (!live[k]) continue;
+        bool l;
+        if (cur[k].feat >= 0) l = xv[k] <= cur[k].v;
+        else {
+          const int co = __double2loint(cur[k].v), cl = __double2hiint(cur[k].v);
+          l = false;
+          for (int c = 0; c < cl; c++) if (cats[co + c] == xv[k]) { l = true; break; }
+        }
+        n[k] = l ? n[k] + 1 : cur[k].right;
+        cur[k] = base[k][n[k]];
+        live[k] = cur[k].feat != -1;
+        any |= live[k];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < TREES_IN_FLIGHT; k++) {
+      if (t0 + k < T) {
+        acc += cur[k].v;
+        if (LEAVES) leaf_out[(size_t)i * T + t0 + k] = n[k];
+      }
+    }
+  }
+  if (out != nullptr) out[i] = acc / (double)T;
+}
+
 // Classification rawPrediction (numClasses == 2).  stats4[node] = (sum w, sum w*y, ., .): class counts (c0, c1) = (stats[0] - stats[1], stats[1]).
 // mode 0: RandomForestClassificationModel.predictRaw — votes(k) += classCounts(k) / total for every tree, in tree order;
 // mode 1: DecisionTreeClassificationModel.predictRaw — the class counts of tree 0's leaf.
@@ -94,6 +173,27 @@ int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, cons
   predict_kernel<<<(unsigned)((n_rows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, d_feature, d_threshold, d_left, d_right,
                                                                                      d_prediction, d_ncat, d_cat_off, d_cat_len, d_cats, d_out);
   return cuda_ok(cudaGetLastError(), "b2rf_predict") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+size_t b2rf_forest_pack_bytes(int64_t n_nodes) { return (size_t)(n_nodes > 0 ? n_nodes : 0) * sizeof(PackedNode); }
+
+int b2rf_forest_pack(int64_t n_nodes, const int32_t* d_feature, const double* d_threshold, const int32_t* d_right, const double* d_prediction,
+                     const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, void* d_packed, void* stream) {
+  if (n_nodes <= 0) return B2RF_OK;
+  if (!d_packed) { set_error("b2rf_forest_pack: no output buffer"); return B2RF_ERR_ARG; }
+  pack_forest_kernel<<<(unsigned)((n_nodes + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n_nodes, d_feature, d_threshold, d_right, d_prediction, d_ncat,
+                                                                                         d_cat_off, d_cat_len, (PackedNode*)d_packed);
+  return cuda_ok(cudaGetLastError(), "b2rf_forest_pack") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+int b2rf_predict_packed(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const void* d_packed,
+                        const double* d_cats, double* d_out, int32_t* d_leaf, void* stream) {
+  if (n_rows <= 0) return B2RF_OK;
+  if (!d_out && !d_leaf) { set_error("b2rf_predict_packed: neither d_out nor d_leaf given"); return B2RF_ERR_ARG; }
+  const unsigned grid = (unsigned)((n_rows + 255) / 256);
+  if (d_leaf) predict_packed_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, (const PackedNode*)d_packed, d_cats, d_out, d_leaf);
+  else predict_packed_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, (const PackedNode*)d_packed, d_cats, d_out, d_leaf);
+  return cuda_ok(cudaGetLastError(), "b2rf_predict_packed") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
 int b2rf_predict_raw(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,

@@ -170,6 +170,60 @@ class Forest:
                                   stats=T(self.stats, torch.float64))
         return self._dev[key]
 
+    # ---- packed nodes (b2rf_forest_pack): one 16-byte record per node, built once per device ----
+    def is_preorder(self) -> bool:
+        """True when every internal node's left child is the next node of its tree (MLlib NodeData numbering; always true for
+        forests exported by the trainer)."""
+        idx = np.arange(len(self.feature)) - np.repeat(self.tree_off[:-1], np.diff(self.tree_off))
+        internal = self.feature >= 0
+        return bool(np.all(self.left[internal] == idx[internal] + 1))
+
+    def _packed(self, device):
+        import torch
+        from ._lib import check, lib
+        key = "packed:" + str(device)
+        if key not in self._dev:
+            d = self._device_arrays(device)
+            n = len(self.feature)
+            buf = torch.empty(max(int(lib().b2rf_forest_pack_bytes(n)), 16), dtype=torch.uint8, device=device)
+            with torch.cuda.device(device):
+                st = torch.cuda.current_stream().cuda_stream
+                check(lib().b2rf_forest_pack(n, d["feature"].data_ptr(), d["threshold"].data_ptr(), d["right"].data_ptr(), d["prediction"].data_ptr(),
+                                             d["ncat"].data_ptr(), d["cat_off"].data_ptr(), d["cat_len"].data_ptr(), buf.data_ptr(), C.c_void_p(st)))
+            self._dev[key] = buf
+        return self._dev[key]
+
+    def _predict_packed(self, X, want_pred: bool, want_leaves: bool):
+        import torch
+        from ._lib import check, lib
+        d = self._device_arrays(X.device)
+        pk = self._packed(X.device)
+        out = torch.empty(X.shape[0], dtype=torch.float64, device=X.device) if want_pred else None
+        leaves = torch.empty((X.shape[0], self.num_trees), dtype=torch.int32, device=X.device) if want_leaves else None
+        with torch.cuda.device(X.device):
+            st = torch.cuda.current_stream().cuda_stream
+            check(lib().b2rf_predict_packed(X.data_ptr(), X.stride(0), X.shape[0], self.num_trees, d["tree_off"].data_ptr(), pk.data_ptr(),
+                                            d["cats"].data_ptr(), 0 if out is None else out.data_ptr(), 0 if leaves is None else leaves.data_ptr(),
+                                            C.c_void_p(st)))
+        return out, leaves
+
+    def predict_leaves(self, X):
+        """Tree-local node index of the leaf every row reaches in every tree: torch.int32 [n, T] (K7, packed form)."""
+        import torch
+        if not (isinstance(X, torch.Tensor) and X.is_cuda):
+            raise TypeError("Forest.predict_leaves needs a CUDA tensor: this package has no CPU path")
+        if not self.is_preorder():
+            raise ValueError("predict_leaves needs pre-order node numbering (MLlib's NodeData order)")
+        return self._predict_packed(X.to(torch.float64).contiguous(), False, True)[1]
+
+    def leaf_ordinals(self) -> np.ndarray:
+        """DecisionTreeModel.leafIndices: for every node, its rank among the leaves of its tree in left-to-right order (-1 for internal
+        nodes).  With pre-order numbering that is the count of leaves before it."""
+        leaf = self.feature < 0
+        before = np.cumsum(leaf) - leaf
+        start = np.repeat(before[self.tree_off[:-1]], np.diff(self.tree_off))
+        return np.where(leaf, before - start, -1).astype(np.int64)
+
     def predict(self, X):
         """X: torch.float64 CUDA tensor [n, F] (row-major).  Returns torch.float64 [n] on the same device."""
         import torch
@@ -180,6 +234,8 @@ class Forest:
             raw = self.predict_raw(X)
             return (raw[:, 1] > raw[:, 0]).to(torch.float64)
         X = X.to(torch.float64).contiguous()
+        if self.is_preorder():
+            return self._predict_packed(X, True, False)[0]
         d = self._device_arrays(X.device)
         out = torch.empty(X.shape[0], dtype=torch.float64, device=X.device)
         with torch.cuda.device(X.device):

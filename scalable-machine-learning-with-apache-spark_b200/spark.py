@@ -66,6 +66,8 @@ class _TreeRegressorParams(Params):
     seed = Param(Params, "seed", "random seed.", TypeConverters.toInt)
     leafCol = Param(Params, "leafCol", "Leaf indices column name. Predicted leaf index of each instance in each tree by preorder.",
                     TypeConverters.toString)
+    weightCol = Param(Params, "weightCol", "weight column name. If this is not set or empty, we treat all instance weights as 1.0.",
+                      TypeConverters.toString)
 
     def _base_defaults(self):
         self._setDefault(featuresCol="features", labelCol="label", predictionCol="prediction", maxDepth=5, maxBins=32, minInstancesPerNode=1,
@@ -90,7 +92,7 @@ def _accessors(cls, names):
 
 
 _COMMON = ["featuresCol", "labelCol", "predictionCol", "maxDepth", "maxBins", "minInstancesPerNode", "minWeightFractionPerNode", "minInfoGain",
-           "maxMemoryInMB", "cacheNodeIds", "checkpointInterval", "impurity", "seed", "leafCol"]
+           "maxMemoryInMB", "cacheNodeIds", "checkpointInterval", "impurity", "seed", "leafCol", "weightCol"]
 
 
 # ------------------------------------------------------------------------------------------------------------------
@@ -238,17 +240,57 @@ class _ForestModelBase(Model, _TreeRegressorParams):
             raise RuntimeError("b2rf models predict on the GPU: no CUDA device is visible and there is no CPU fallback")
         return torch.device("cuda", torch.cuda.current_device())
 
+    def _leaf_columns(self, X):
+        """leafCol (every tree model: DecisionTreeModel.predictLeaf, the leaf's rank among its tree's leaves, a double for a single
+        tree and a vector for an ensemble) and varianceCol (DecisionTreeRegressionModel.predictVariance: the leaf's impurity)."""
+        import torch
+        cols = {}
+        leaf_col = self.getOrDefault("leafCol") if self.hasParam("leafCol") and self.isDefined("leafCol") else ""
+        var_col = self.getOrDefault("varianceCol") if self.hasParam("varianceCol") and self.isDefined("varianceCol") else ""
+        if not leaf_col and not var_col:
+            return cols
+        fo = self._forest
+        if X.shape[0] == 0:
+            leaves = np.zeros((0, fo.num_trees), np.int64)
+        else:
+            leaves = fo.predict_leaves(torch.as_tensor(X, device=self._device())).cpu().numpy().astype(np.int64)
+        flat = leaves + fo.tree_off[:-1][None, :]
+        if leaf_col:
+            ords = fo.leaf_ordinals()[flat].astype(np.float64)
+            cols[leaf_col] = ords if self._ensemble else ords[:, 0]
+        if var_col:
+            cols[var_col] = fo.impurity[flat[:, 0]]
+        return cols
+
     def _transform(self, dataset):
         import torch
         X, _, _ = _extract(dataset, self.getOrDefault("featuresCol"))
-        if X.shape[0] == 0:
-            return _append_prediction(dataset, self.getOrDefault("predictionCol"), np.zeros(0))
-        pred = self._forest.predict(torch.as_tensor(X, device=self._device())).cpu().numpy()
-        return _append_prediction(dataset, self.getOrDefault("predictionCol"), pred)
+        cols = {}
+        if self.getOrDefault("predictionCol"):
+            cols[self.getOrDefault("predictionCol")] = (self._forest.predict(torch.as_tensor(X, device=self._device())).cpu().numpy()
+                                                        if X.shape[0] else np.zeros(0))
+        cols.update(self._leaf_columns(X))
+        return _append_columns(dataset, cols)
+
+
+_VARIANCE_COL = Param(Params, "varianceCol", "column name for the biased sample variance of prediction.", TypeConverters.toString)
 
 
 class B200DecisionTreeRegressionModel(_ForestModelBase):
     _ensemble = False
+    varianceCol = _VARIANCE_COL
+
+    def predictVariance(self, value):
+        import torch
+        v = np.asarray(value.toArray() if hasattr(value, "toArray") else value, np.float64).reshape(1, -1)
+        leaf = int(self._forest.predict_leaves(torch.as_tensor(v, device=self._device()))[0, 0].item())
+        return float(self._forest.impurity[leaf])
+
+    def predictLeaf(self, value):
+        import torch
+        v = np.asarray(value.toArray() if hasattr(value, "toArray") else value, np.float64).reshape(1, -1)
+        leaf = int(self._forest.predict_leaves(torch.as_tensor(v, device=self._device()))[0, 0].item())
+        return float(self._forest.leaf_ordinals()[leaf])
 
     @property
     def depth(self):
@@ -325,6 +367,10 @@ class _TreeEstimatorBase(Estimator, _TreeRegressorParams):
         import torch
         from . import trainer
         est0 = estimators[0]
+        for e in estimators:
+            if e.isDefined("weightCol") and e.getOrDefault("weightCol"):
+                raise NotImplementedError("weightCol is not supported: K4 accumulates integer bag counts (every instance weight 1.0), "
+                                          "which is what every tree fit of the reference uses")
         X, y, sizes = _extract(dataset, est0.getOrDefault("featuresCol"), est0.getOrDefault("labelCol"))
         if X.shape[0] == 0:
             raise ValueError("DecisionTree requires size of input RDD > 0, but was given by empty one.")
@@ -366,6 +412,7 @@ class _TreeEstimatorBase(Estimator, _TreeRegressorParams):
 class B200DecisionTreeRegressor(_TreeEstimatorBase):
     """pyspark.ml.regression.DecisionTreeRegressor, trained on the GPU (`ML 06 - Decision Trees.py:73-75,118,126`)."""
     _model_cls = B200DecisionTreeRegressionModel
+    varianceCol = _VARIANCE_COL
 
     def __init__(self, **kwargs):
         super().__init__()
@@ -471,6 +518,7 @@ class _ClassifierModelBase(_ClassifierParams, _ForestModelBase):
             cols[self.getOrDefault("probabilityCol")] = prob
         if self.getOrDefault("predictionCol"):
             cols[self.getOrDefault("predictionCol")] = self._predict_from_probability(prob)
+        cols.update(self._leaf_columns(X))
         return _append_columns(dataset, cols)
 
 
@@ -546,6 +594,6 @@ for _c in (B200DecisionTreeClassifier, B200DecisionTreeClassificationModel):
 for _c in (B200RandomForestClassifier, B200RandomForestClassificationModel):
     _accessors(_c, _COMMON + _CLS + ["numTrees", "featureSubsetStrategy", "subsamplingRate", "bootstrap"])
 for _c in (B200DecisionTreeRegressor, B200DecisionTreeRegressionModel):
-    _accessors(_c, _COMMON)
+    _accessors(_c, _COMMON + ["varianceCol"])
 for _c in (B200RandomForestRegressor, B200RandomForestRegressionModel):
     _accessors(_c, _COMMON + ["numTrees", "featureSubsetStrategy", "subsamplingRate", "bootstrap"])
