@@ -33,8 +33,8 @@ WORKLOADS = {
     "C4-cont": dict(rows=12_500_000, F=128, numTrees=50, maxDepth=10, maxBins=256, gen="c3"),   # C4's shape without categorical features
 }
 ROWS_PER_PARTITION = 4096   # emulated Spark partition size (bagging streams are per partition; stated in config)
-# ncu --set full capture of the dominant kernel (profiles/r01_ncu_bucket_hist_c3.md): DRAM bytes of one whole-level launch
-NCU_TRAFFIC = {"C3": {"traffic": 100.898e9, "algorithmic": 3.765e9}}
+# ncu --set full capture of the dominant kernel (profiles/r01_ncu_bucket_hist32_final.md): DRAM bytes of one whole-level launch
+NCU_TRAFFIC = {"C3": {"traffic": 109.988e9, "algorithmic": 3.765e9}}
 
 
 class ClockSampler(threading.Thread):
@@ -268,16 +268,16 @@ def main():
                        "l2": "inputs (bin matrix 0.64 GB + per-tree arrays 5 GB) exceed the 126 MB L2; no explicit flush",
                        "node_groups": f0.counters["groups"], "forest_nodes": int(f0.num_nodes())},
             "phases_s": phases,
-            "roofline": {"bound": "hbm", "kernel": "bucket_hist_kernel (K4: per-node shared-memory histograms over row segments)",
+            "roofline": {"bound": "hbm", "kernel": "bucket_hist32_kernel (K4: per-node shared-memory histograms over row segments)",
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         # dram__bytes_read+write of ONE whole-level launch (100 trees, 1600 nodes) from profiles/r01_ncu_bucket_hist_c3.md;
+                         # dram__bytes_read+write of ONE whole-level launch (100 trees, 1600 nodes) from profiles/r01_ncu_bucket_hist32_final.md;
                          # the same launch's algorithmic bytes are given beside it
                          "traffic": NCU_TRAFFIC.get(args.workload, {}).get("traffic"),
                          "traffic_launch_algorithmic_bytes": NCU_TRAFFIC.get(args.workload, {}).get("algorithmic"),
                          "peak_source": peak_src, "algorithmic_bytes_per_fit": hist_bytes, "launches_per_fit": hist_launches,
                          "kernel_seconds_per_fit": hist_s, "kernel_share_of_step": hist_s / (ms_per_step * 1e-3),
                          "weighted_bin_updates_per_s": updates_per_fit / hist_s if hist_s > 0 else None,   # sum over evaluated nodes of (sum of bag weights) x features per node
-                         "note": "K4 is bound by shared-memory atomic throughput (71% of the smem wavefront peak in ncu), not HBM: "
+                         "note": "K4 is bound by shared-memory atomic throughput (83% of the smem wavefront peak in ncu), not HBM: "
                                  "22 atomic bin updates per 37 algorithmic bytes; see DESIGN.md section 2 and profiles/"},
             "e2e": e2e, "cpu_baseline": cpu, "cpu_baseline_sklearn": skl,
             "gpu_launches": int(sum(f.counters["kernel_launches"] for f in forests)),

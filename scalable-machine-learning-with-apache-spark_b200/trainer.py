@@ -481,6 +481,9 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
         _raise_bin_errors(S["arity_d"])
         torch.cuda.synchronize(dev)
         t2 = time.perf_counter()
+        if os.environ.get("B2RF_TIMING") == "1":
+            print(f"[b2rf timing] fit_host: setup+bag launch {t0 - t_start:.4f} sample+findSplits {t1 - t0:.4f} stream+bin+bag wait {t2 - t1:.4f} "
+                  f"({Xh.nbytes / max(t2 - t1, 1e-9) / 1e9:.1f} GB/s host->device)", flush=True)
         forest = _train_loop(S, params, F, n_local, yd, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace)
         t3 = time.perf_counter()
         forest.timers.update(init=(t0 - t_start) + (t2 - t1), findSplits=t1 - t0, total=t3 - t_start, loop=t3 - t2)
