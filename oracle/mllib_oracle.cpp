@@ -772,7 +772,7 @@ int b2rf_oracle_fit(const double* X, int64_t N, int F, const double* y, const in
         reservoir(F, m.featuresPerNode, rng.nextLong(), g.feats);
         totalBins = 0; for (int f : g.feats) totalBins += m.numBins[f];
       } else { g.feats = allFeats; totalBins = allBins; }
-      const int64_t nodeMem = 3 * totalBins * 8;
+      const int64_t nodeMem = (p.impurity == 0 ? 3 : 2) * totalBins * 8;   // aggregateSizeForNode: 3 (regression) or numClasses (= 2)
       if (mem + nodeMem <= maxMem || mem == 0) {
         stack.pop_back();
         if (std::find(treeInsertOrder.begin(), treeInsertOrder.end(), t) == treeInsertOrder.end()) treeInsertOrder.push_back(t);

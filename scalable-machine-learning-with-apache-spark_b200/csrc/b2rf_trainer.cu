@@ -412,13 +412,14 @@ int b2rf_trainer_create(const b2rf_params* params, int32_t F, const int32_t* h_a
 void b2rf_trainer_destroy(b2rf_trainer* t) { delete t; }
 
 int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t) {
-  // selectNodesToSplit admits nodes while 3*totalBins*8 bytes fit maxMemoryInMB; always at least one node
+  // selectNodesToSplit admits nodes while statsSize*totalBins*8 bytes fit maxMemoryInMB; always at least one node
   const int64_t maxMem = (int64_t)t->p.maxMemoryInMB * 1024 * 1024;
+  const int64_t statsSize = t->p.impurity == 0 ? 3 : 2;   // aggregateSizeForNode: 3 for regression, numClasses for classification
   std::vector<int32_t> nb(t->numBins);
   std::sort(nb.begin(), nb.end(), std::greater<int32_t>());
   int64_t worstNode = 0;
   for (int j = 0; j < t->Fsub; j++) worstNode += nb[j];
-  const int64_t byMem = maxMem / 24 + worstNode;
+  const int64_t byMem = maxMem / (statsSize * 8) + worstNode;
   const int64_t maxNodesTotal = (int64_t)t->T << std::min(t->p.maxDepth, 24);
   return std::max<int64_t>(worstNode, std::min<int64_t>(byMem, maxNodesTotal * worstNode));
 }
@@ -591,7 +592,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       for (int j = 0; j < t->Fsub; j++) tmp[j] = (uint32_t)j;
       totalBins = t->allBins;
     }
-    const int64_t nodeMem = 3 * totalBins * 8;
+    const int64_t nodeMem = (t->p.impurity == 0 ? 3 : 2) * totalBins * 8;   // aggregateSizeForNode * 8: 3 stats (regression) or numClasses = 2
     if (!(mem + nodeMem <= maxMem || mem == 0)) break;
     t->stack.pop_back();
     if (!treeSeen[tr]) { treeSeen[tr] = 1; t->groupTreeInsertOrder.push_back(tr); }

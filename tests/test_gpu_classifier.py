@@ -71,15 +71,18 @@ def test_decision_tree_classifier_parity(b2rf, oracle, cuda, impurity):
     assert float((g.predict(Xd).cpu().numpy() == y).mean()) > 0.7
 
 
-@pytest.mark.parametrize("impurity,strategy", [("gini", "auto"), ("entropy", "log2"), ("gini", "0.5")])
-def test_random_forest_classifier_parity(b2rf, oracle, cuda, impurity, strategy):
+@pytest.mark.parametrize("impurity,strategy,mem", [("gini", "auto", 256), ("entropy", "log2", 256), ("gini", "0.5", 256), ("gini", "all", 1)])
+def test_random_forest_classifier_parity(b2rf, oracle, cuda, impurity, strategy, mem):
+    """mem = 1: node groups are cut by maxMemoryInMB, where classification counts numClasses (not 3) statistics per bin."""
     X, y, arity = _airbnb_binary(b2rf, 5716)
     po = list(range(0, 5716, 1429)) + [5716]
-    kw = dict(maxDepth=5, maxBins=40, numTrees=20, bootstrap=True, seed=42, featureSubsetStrategy=strategy, impurity=impurity,
-              minInstancesPerNode=2)
+    kw = dict(maxDepth=7 if mem == 1 else 5, maxBins=40, numTrees=20, bootstrap=True, seed=42, featureSubsetStrategy=strategy, impurity=impurity,
+              minInstancesPerNode=2, maxMemoryInMB=mem)
     g = _fit(b2rf, cuda, X, y, arity, part_offsets=po, **kw)
     o = oracle.fit(X, y, arity, part_offsets=np.array(po), **kw)
     assert_classifier_parity(g, o, exact=(impurity == "gini"))
+    if mem == 1:
+        assert g.counters["groups"] == len(o.group_sizes) > 8
     Xd = torch.as_tensor(X, device=cuda)
     np.testing.assert_allclose(g.predict_raw(Xd).cpu().numpy(), o.predict_raw(X), rtol=1e-15, atol=0)
     assert np.array_equal(g.predict(Xd).cpu().numpy(), o.predict(X))
