@@ -55,7 +55,9 @@ typedef struct b2rf_params {
   int32_t impurity;  /* 0 = variance (regression); 1 = gini, 2 = entropy: binary classification (labels 0.0 / 1.0, numClasses == 2).
                       * Class counts ride on the regression statistics: with y in {0,1}, sum(w*y) is the class-1 count and
                       * sum(w) - sum(w*y) the class-0 count, both exact integers in fp64.  numClasses > 2 is not implemented. */
-  int32_t reserved;  /* must be 0 */
+  int32_t numClasses;  /* 0: regression, or binary classification on the regression statistics (impurity != 0); 3..32: multiclass
+                        * classification with per-class count histograms, impurity-ordered and unordered categorical splits
+                        * (segment histogram mode only); 2 is accepted and means the same as 0 */
 } b2rf_params;
 
 /* DecisionTreeMetadata.buildMetadata featureSubsetStrategy table.  strategy: "auto","all","sqrt","log2","onethird",
@@ -145,6 +147,10 @@ int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature
                         int32_t* h_ncat, int32_t* h_cat_off, int32_t* h_cat_len, double* h_cats);
 /* per-node decision trace in processing order: ints [n][5] = group, tree, heap node id, feature, split index;
  * doubles [n][5] = gain, impurity, count, sum, sumsq */
+/* Classification: numClasses of the fit (2 for the binary form) and the class counts of every exported node,
+ * h_counts[n_nodes][numClasses] (the model's impurityStats).  0 / B2RF_ERR_STATE for a regression trainer. */
+int b2rf_trainer_num_classes(const b2rf_trainer* t);
+int b2rf_trainer_export_class_counts(b2rf_trainer* t, double* h_counts);
 int64_t b2rf_trainer_trace_size(const b2rf_trainer* t);
 int b2rf_trainer_trace(const b2rf_trainer* t, int32_t* h_ints, double* h_dbls);
 
@@ -169,6 +175,11 @@ int b2rf_forest_pack(int64_t n_nodes, const int32_t* d_feature, const double* d_
                      const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, void* d_packed, void* stream);
 int b2rf_predict_packed(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const void* d_packed,
                         const double* d_cats, double* d_out, int32_t* d_leaf, void* stream);
+/* K7 for any numClasses >= 2: d_class_counts[node][numClasses] are the exported class counts; d_out[n_rows][numClasses]. */
+int b2rf_predict_raw_mc(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,
+                        const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_class_counts,
+                        int32_t numClasses, const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len,
+                        const double* d_cats, int32_t mode, double* d_out, void* stream);
 /* K7, classification (reference call sites `Solutions/Labs/ML 07L:80-82,105-108`): rawPrediction of a binary
  * tree-ensemble classifier, d_out2[n_rows][2].  d_stats4[node][4] are the exported node statistics (sum w, sum w*y, ., .), i.e.
  * class counts (stats[0] - stats[1], stats[1]).  mode 0 = RandomForestClassificationModel.predictRaw (per-tree normalised class

@@ -15,7 +15,7 @@ class B2rfParams(C.Structure):
     _fields_ = [("maxDepth", C.c_int32), ("maxBins", C.c_int32), ("minInstancesPerNode", C.c_int32), ("numTrees", C.c_int32),
                 ("featuresPerNode", C.c_int32), ("maxMemoryInMB", C.c_int32), ("bootstrap", C.c_int32), ("histMode", C.c_int32),
                 ("minInfoGain", C.c_double), ("minWeightFractionPerNode", C.c_double), ("subsamplingRate", C.c_double),
-                ("seed", C.c_int64), ("impurity", C.c_int32), ("reserved", C.c_int32)]
+                ("seed", C.c_int64), ("impurity", C.c_int32), ("numClasses", C.c_int32)]
 
 
 class B2rfError(RuntimeError):
@@ -62,6 +62,9 @@ _SIGS = {
     "b2rf_forest_pack_bytes": (C.c_size_t, [i64]),
     "b2rf_forest_pack": (C.c_int, [i64] + [vp] * 9),
     "b2rf_predict_packed": (C.c_int, [vp, i64, i64, i32] + [vp] * 6),
+    "b2rf_predict_raw_mc": (C.c_int, [vp, i64, i64, i32] + [vp] * 6 + [i32] + [vp] * 4 + [i32, vp, vp]),
+    "b2rf_trainer_num_classes": (C.c_int, [vp]),
+    "b2rf_trainer_export_class_counts": (C.c_int, [vp, vp]),
     "b2rf_predict_raw": (C.c_int, [vp, i64, i64, i32] + [vp] * 10 + [i32, vp, vp]),
 }
 

@@ -115,6 +115,35 @@ struct SplitLaunch {
 };
 cudaError_t launch_best_split(const SplitLaunch& a, cudaStream_t s);
 
+// ---- multiclass classification (numClasses > 2): per-class counts, k8_multiclass.cu ----
+struct ClsHistLaunch {                   // segment mode only
+  const void* bins_rm; int64_t ldr; int32_t codeBytes;
+  const double* y;                       // labels 0 .. C-1
+  const uint32_t* chunk_prefix; int32_t nSlots, CH;
+  const uint2* slot_fo; const int64_t* slot_base; int32_t Fsub;
+  int32_t padB;                          // bins per feature plane in shared memory (largest cell count of any feature)
+  int32_t C, M;                          // classes; a global histogram cell is 4*M doubles, the first C of them the class counts
+  int32_t direct;                        // set by the launcher when C * padB * 32 counters do not fit shared memory
+  double* hist;
+  const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;
+};
+cudaError_t launch_cls_hist(const ClsHistLaunch& a, cudaStream_t s);
+
+struct ClsSplitLaunch {
+  const double* hist;
+  const uint2* slot_fo; const int64_t* slot_base; int32_t Fsub; int32_t nSlots;
+  const double* parentCls;    // [slots][Cp] class counts of the node (from its parent's split); ignored for roots
+  const int32_t* hasParent;   // [slots]
+  const int32_t* cellBins;    // [F] histogram cells of the feature: splits + 1 (continuous) or arity (categorical)
+  const int32_t* kind;        // [F] 0 continuous, 1 ordered categorical, 2 unordered categorical
+  double minInstances, minWeight, minInfoGain;
+  SplitRec* out;              // gain, impurities, feature, split index; parent[0] / left[0] / right[0] = weighted counts
+  double* clsOut;             // [slots][3][Cp]: class counts of the node, of the best split's left and right child
+  uint32_t* catmask_out;      // [slots][maskWords] left categories of a categorical best split
+  int32_t maxB, maskWords, impurity, C, Cp, M;
+};
+cudaError_t launch_best_split_cls(const ClsSplitLaunch& a, cudaStream_t s);
+
 int device_sm_count();
 void set_error(const std::string& m);
 const char* last_error_cstr();

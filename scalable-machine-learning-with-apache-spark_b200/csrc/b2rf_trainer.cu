@@ -119,6 +119,7 @@ struct HNode {  // LearningNode
   int32_t splitBin = -1;
   double threshold = 0;
   int32_t catMaskIdx = -1;
+  int64_t cls = -1;   // multiclass: offset of this node's class counts in b2rf_trainer::clsPool
   NodeStats stats;
 };
 struct GNode { int32_t tree, nidx; };
@@ -210,6 +211,14 @@ struct b2rf_trainer {
   bool subsampling = false;
   double minWeightPerNode = 0;
   std::vector<int32_t> arity, numBins;
+  // Multiclass classification (C >= 3, k8_multiclass.cu); C == 0 otherwise.  numBins stays MLlib's metadata.numBins (an unordered
+  // categorical feature counts 2^(arity-1) - 1 of them: node-group memory accounting), cellBins is what the histogram really holds
+  // (splits + 1, or one cell per category), kind = 0 continuous / 1 ordered categorical / 2 unordered categorical.
+  int32_t C = 0, M = 1, Cp = 4;
+  std::vector<int32_t> cellBins, kind;
+  std::vector<double> clsPool;
+  std::vector<int64_t> drawCells;    // histogram cells of a draw's features
+  std::vector<double> x_cls;         // flat export: [node][C]
   std::vector<double> thresholds;  // [F][maxSplits]
   int64_t allBins = 0;
 
@@ -236,15 +245,15 @@ struct b2rf_trainer {
   size_t drawHead = 0;               // next unconsumed draw
   std::vector<uint32_t> updStamp, updSlot; uint32_t updGen = 0;   // flush_node_updates: last-writer-wins without hashing
   void ensure_draws(size_t n) {      // at least n unconsumed draws
-    if (drawHead > 0 && drawHead == drawBins.size()) { drawFeats.clear(); drawBins.clear(); drawHead = 0; }
+    if (drawHead > 0 && drawHead == drawBins.size()) { drawFeats.clear(); drawBins.clear(); drawCells.clear(); drawHead = 0; }
     while (drawBins.size() - drawHead < n) {
       const size_t k = drawBins.size();
       drawFeats.resize((k + 1) * (size_t)Fsub);
       uint32_t* out = drawFeats.data() + k * (size_t)Fsub;
       reservoir_features(F, Fsub, rng.nextLong(), out);
-      int64_t tb = 0;
-      for (int j = 0; j < Fsub; j++) tb += numBins[out[j]];
-      drawBins.push_back(tb);
+      int64_t tb = 0, tc = 0;
+      for (int j = 0; j < Fsub; j++) { tb += numBins[out[j]]; tc += cellBins[out[j]]; }
+      drawBins.push_back(tb); drawCells.push_back(tc);
     }
   }
   std::vector<uint32_t> catPool;  // 8 words per categorical split
@@ -258,7 +267,9 @@ struct b2rf_trainer {
   DevBuf<uint2> dSlotFo;
   DevBuf<int64_t> dSlotBase;
   DevBuf<double> dParent;
-  DevBuf<int32_t> dHasParent, dNumBins, dIsCat, dTreeIds;
+  DevBuf<int32_t> dHasParent, dNumBins, dIsCat, dTreeIds, dCellBins, dKind;
+  DevBuf<double> dParentCls, dClsOut;
+  PinBuf<double> hParentCls, hClsOut;
   DevBuf<SplitRec> dRec;
   DevBuf<uint32_t> dRecMask;
   PinBuf<uint32_t> hRecMask;
@@ -308,6 +319,7 @@ struct b2rf_trainer {
   ~b2rf_trainer() {
     dn.release(); dnUpd.release(); dCat.release(); dSlotFo.release(); dSlotBase.release(); dParent.release();
     dHasParent.release(); dNumBins.release(); dIsCat.release(); dTreeIds.release(); dRec.release();
+    dCellBins.release(); dKind.release(); dParentCls.release(); dClsOut.release(); hParentCls.release(); hClsOut.release();
     dSeg.release(); dIdx0.release(); dIdx1.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
     dSlotPos.release(); dSplitPos.release(); hSlotPos.release(); hSplitPos.release();
     dRecMask.release(); hRecMask.release();
@@ -327,6 +339,13 @@ struct b2rf_trainer {
     return d;
   }
   int state_slot(const HNode& n) const { return (n.isLeaf && !n.hasSplit) ? SLOT_DEAD : SLOT_PENDING; }
+  double node_pred(const HNode& n) const {   // ImpurityCalculator.predict
+    if (!C) return vpred(n.stats.calc, p.impurity);
+    if (n.cls < 0) return 0.0;
+    int best = 0;
+    for (int k = 1; k < C; k++) if (clsPool[(size_t)n.cls + k] > clsPool[(size_t)n.cls + best]) best = k;   // indexOfLargestArrayElement: first maximum
+    return (double)best;
+  }
 };
 
 extern "C" {
@@ -382,7 +401,10 @@ int b2rf_trainer_create(const b2rf_params* params, int32_t F, const int32_t* h_a
   if (!params || !out || F <= 0 || numExamples <= 0 || params->numTrees <= 0 || params->maxDepth < 0 || params->maxDepth > 30) {
     set_error("b2rf_trainer_create: bad argument"); return B2RF_ERR_ARG;
   }
-  if (params->impurity < 0 || params->impurity > 2 || params->reserved != 0) { set_error("b2rf_trainer_create: impurity must be 0 (variance), 1 (gini) or 2 (entropy)"); return B2RF_ERR_ARG; }
+  if (params->impurity < 0 || params->impurity > 2) { set_error("b2rf_trainer_create: impurity must be 0 (variance), 1 (gini) or 2 (entropy)"); return B2RF_ERR_ARG; }
+  if (params->numClasses != 0 && (params->impurity == 0 || params->numClasses < 2 || params->numClasses > 32)) {
+    set_error("b2rf_trainer_create: numClasses must be 0 (regression / binary default) or 2..32 with impurity gini / entropy"); return B2RF_ERR_ARG;
+  }
   b2rf_trainer* t = new b2rf_trainer();
   t->p = *params; t->F = F; t->T = params->numTrees; t->numExamples = numExamples;
   { int mpb = 0; const int rc = check_arity(params->maxBins, F, h_arity, numExamples, &mpb); if (rc) { delete t; return rc; } t->maxPossibleBins = mpb; }
@@ -395,6 +417,17 @@ int b2rf_trainer_create(const b2rf_params* params, int32_t F, const int32_t* h_a
   for (int f = 0; f < F; f++) {
     if (h_arity[f] > 1) t->numBins[f] = h_arity[f];
     else if (h_arity[f] == 0) t->numBins[f] = h_nsplits[f] + 1;
+  }
+  t->cellBins = t->numBins;
+  t->kind.assign(F, 0);
+  for (int f = 0; f < F; f++) t->kind[f] = h_arity[f] > 1 ? 1 : 0;
+  if (params->impurity != 0 && params->numClasses >= 3) {
+    // DecisionTreeMetadata.buildMetadata, numClasses > 2: categorical features with few categories are UNORDERED (every subset of
+    // categories is a candidate split): arity <= floor(log2(maxPossibleBins / 2 + 1) + 1), with numBins = 2^(arity-1) - 1
+    t->C = params->numClasses; t->M = (t->C + 3) / 4; t->Cp = 4 * t->M;
+    const int maxCatUnordered = (int)std::floor(std::log((double)(t->maxPossibleBins / 2 + 1)) / std::log(2.0) + 1);
+    for (int f = 0; f < F; f++)
+      if (h_arity[f] > 1 && h_arity[f] <= maxCatUnordered) { t->kind[f] = 2; t->numBins[f] = (1 << (h_arity[f] - 1)) - 1; }
   }
   t->thresholds.assign(h_thresholds, h_thresholds + (size_t)F * t->maxSplits);
   t->allBins = 0;
@@ -414,14 +447,15 @@ void b2rf_trainer_destroy(b2rf_trainer* t) { delete t; }
 int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t) {
   // selectNodesToSplit admits nodes while statsSize*totalBins*8 bytes fit maxMemoryInMB; always at least one node
   const int64_t maxMem = (int64_t)t->p.maxMemoryInMB * 1024 * 1024;
-  const int64_t statsSize = t->p.impurity == 0 ? 3 : 2;   // aggregateSizeForNode: 3 for regression, numClasses for classification
-  std::vector<int32_t> nb(t->numBins);
+  const int64_t statsSize = t->p.impurity == 0 ? 3 : (t->C ? t->C : 2);   // aggregateSizeForNode: 3 for regression, numClasses for classification
+  std::vector<int32_t> nb(t->cellBins);
   std::sort(nb.begin(), nb.end(), std::greater<int32_t>());
   int64_t worstNode = 0;
   for (int j = 0; j < t->Fsub; j++) worstNode += nb[j];
-  const int64_t byMem = maxMem / (statsSize * 8) + worstNode;
+  // admitted MLlib bins <= maxMem / (statsSize * 8) + one node; an unordered feature can hold up to 2x more cells than bins (arity 2)
+  const int64_t byMem = (maxMem / (statsSize * 8)) * (t->C ? 2 : 1) + worstNode;
   const int64_t maxNodesTotal = (int64_t)t->T << std::min(t->p.maxDepth, 24);
-  return std::max<int64_t>(worstNode, std::min<int64_t>(byMem, maxNodesTotal * worstNode));
+  return t->M * std::max<int64_t>(worstNode, std::min<int64_t>(byMem, maxNodesTotal * worstNode));   // in units of 4 doubles
 }
 
 int b2rf_trainer_code_bytes(const b2rf_trainer* t) { return t ? t->codeBytes : 0; }
@@ -481,8 +515,11 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
     blockCnt.release();
     if (!ok) return B2RF_ERR_CUDA;
   }
+  if (t->C && !t->segMode) { set_error("b2rf: multiclass classification needs the segment histogram mode (row-major bin matrix, histMode 0)"); return B2RF_ERR_ARG; }
   if (!t->dn.ensure((size_t)t->nodeStride * t->T)) return B2RF_ERR_CUDA;
-  if (!t->dNumBins.ensure(t->F) || !t->dIsCat.ensure(t->F)) return B2RF_ERR_CUDA;
+  if (!t->dNumBins.ensure(t->F) || !t->dIsCat.ensure(t->F) || !t->dCellBins.ensure(t->F) || !t->dKind.ensure(t->F)) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaMemcpy(t->dCellBins.p, t->cellBins.data(), t->F * 4, cudaMemcpyHostToDevice), "bind copy")) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaMemcpy(t->dKind.p, t->kind.data(), t->F * 4, cudaMemcpyHostToDevice), "bind copy")) return B2RF_ERR_CUDA;
   std::vector<int32_t> isCat(t->F);
   for (int f = 0; f < t->F; f++) isCat[f] = t->arity[f] != 0;
   if (!cuda_ok(cudaMemcpy(t->dNumBins.p, t->numBins.data(), t->F * 4, cudaMemcpyHostToDevice), "bind copy")) return B2RF_ERR_CUDA;
@@ -582,33 +619,38 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   std::vector<int64_t> slotBase;
   while (!t->stack.empty()) {
     const auto [tr, ni] = t->stack.back();
-    int64_t totalBins;
+    int64_t totalBins, nodeCells;
     if (t->subsampling) {
       t->ensure_draws(1);                                                  // drawn before the memory check, consumed either way
       memcpy(tmp.data(), t->drawFeats.data() + t->drawHead * (size_t)t->Fsub, (size_t)t->Fsub * 4);
       totalBins = t->drawBins[t->drawHead];
+      nodeCells = t->drawCells[t->drawHead];
       t->drawHead++;
     } else {
       for (int j = 0; j < t->Fsub; j++) tmp[j] = (uint32_t)j;
       totalBins = t->allBins;
+      nodeCells = 0;
+      for (int f = 0; f < t->F; f++) nodeCells += t->cellBins[f];
     }
-    const int64_t nodeMem = (t->p.impurity == 0 ? 3 : 2) * totalBins * 8;   // aggregateSizeForNode * 8: 3 stats (regression) or numClasses = 2
+    const int64_t nodeMem = (t->p.impurity == 0 ? 3 : (t->C ? t->C : 2)) * totalBins * 8;   // aggregateSizeForNode * 8: 3 stats (regression) or numClasses
     if (!(mem + nodeMem <= maxMem || mem == 0)) break;
     t->stack.pop_back();
     if (!treeSeen[tr]) { treeSeen[tr] = 1; t->groupTreeInsertOrder.push_back(tr); }
     t->group.push_back({tr, ni});
     feats.insert(feats.end(), tmp.begin(), tmp.end());
     slotBase.push_back(cells);
-    cells += totalBins;
+    cells += nodeCells;
     mem += nodeMem;
   }
   const size_t nSlots = t->group.size();
-  if (cells > t->histCells) { set_error("b2rf_trainer_begin_group: histogram buffer too small for this node group"); return B2RF_ERR_ARG; }
+  if (cells * t->M > t->histCells) { set_error("b2rf_trainer_begin_group: histogram buffer too small for this node group"); return B2RF_ERR_ARG; }
   t->groupCells = cells;
 
   // ---- descriptors ----
   if (!t->hSlotFo.ensure(nSlots * t->Fsub) || !t->hSlotBase.ensure(nSlots) || !t->hParent.ensure(nSlots * 4) || !t->hHasParent.ensure(nSlots) ||
       !t->dSlotFo.ensure(nSlots * t->Fsub) || !t->dSlotBase.ensure(nSlots) || !t->dParent.ensure(nSlots * 4) || !t->dHasParent.ensure(nSlots) ||
+      (t->C && (!t->hParentCls.ensure(nSlots * t->Cp) || !t->dParentCls.ensure(nSlots * t->Cp) || !t->hClsOut.ensure(nSlots * 3 * t->Cp) ||
+                !t->dClsOut.ensure(nSlots * 3 * t->Cp))) ||
       !t->dRec.ensure(nSlots) || !t->hRec.ensure(nSlots) || !t->dRecMask.ensure(nSlots * t->maskWords) || !t->hRecMask.ensure(nSlots * t->maskWords) || !t->hTreeIds.ensure(t->T) || !t->dTreeIds.ensure(t->T))
     return B2RF_ERR_CUDA;
   int64_t maxNodes = 0;
@@ -619,12 +661,13 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     for (int j = 0; j < t->Fsub; j++) {
       const uint32_t f = feats[sl * t->Fsub + j];
       t->hSlotFo.p[sl * t->Fsub + j] = make_uint2(f, off);
-      off += (uint32_t)t->numBins[f];
+      off += (uint32_t)t->cellBins[f];
     }
     t->hSlotBase.p[sl] = slotBase[sl];
     const bool hasParent = level_of(n.id) > 0;
     t->hHasParent.p[sl] = hasParent;
     for (int q = 0; q < 4; q++) t->hParent.p[sl * 4 + q] = hasParent ? n.stats.calc[q] : 0.0;
+    if (t->C) for (int k = 0; k < t->Cp; k++) t->hParentCls.p[sl * t->Cp + k] = (hasParent && k < t->C && n.cls >= 0) ? t->clsPool[(size_t)n.cls + k] : 0.0;
     t->pending.push_back({(int64_t)g.tree * t->nodeStride + g.nidx, t->mirror(g.tree, g.nidx, (int)sl)});
     maxNodes = std::max<int64_t>(maxNodes, (int64_t)t->trees[g.tree].size());
   }
@@ -633,7 +676,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   std::vector<int64_t> cellsPerTree(t->T, 0);
   for (size_t sl = 0; sl < nSlots; sl++) {
     int64_t c = 0;
-    for (int j = 0; j < t->Fsub; j++) c += t->numBins[feats[sl * t->Fsub + j]];
+    for (int j = 0; j < t->Fsub; j++) c += t->cellBins[feats[sl * t->Fsub + j]];
     cellsPerTree[t->group[sl].tree] += c;
   }
   int nTg = 0;
@@ -647,7 +690,8 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   ok &= cuda_ok(cudaMemcpyAsync(t->dParent.p, t->hParent.p, nSlots * 32, cudaMemcpyHostToDevice, s), "upload parent stats");
   ok &= cuda_ok(cudaMemcpyAsync(t->dHasParent.p, t->hHasParent.p, nSlots * 4, cudaMemcpyHostToDevice, s), "upload hasParent");
   ok &= cuda_ok(cudaMemcpyAsync(t->dTreeIds.p, t->hTreeIds.p, (size_t)nTg * 4, cudaMemcpyHostToDevice, s), "upload tree ids");
-  ok &= cuda_ok(cudaMemsetAsync(t->d_hist, 0, (size_t)cells * 32, s), "zero histogram");
+  if (t->C) ok &= cuda_ok(cudaMemcpyAsync(t->dParentCls.p, t->hParentCls.p, nSlots * t->Cp * 8, cudaMemcpyHostToDevice, s), "upload parent class counts");
+  ok &= cuda_ok(cudaMemsetAsync(t->d_hist, 0, (size_t)cells * 32 * t->M, s), "zero histogram");
   if (!ok) return B2RF_ERR_CUDA;
   t->tChoose += now_s() - tc0; t->tSelect += now_s() - tc0;
 
@@ -674,13 +718,13 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       return B2RF_ERR_CUDA;
     for (size_t sl = 0; sl < nSlots; sl++) {
       int32_t c = 0;
-      for (int j = 0; j < t->Fsub; j++) c += t->numBins[feats[sl * t->Fsub + j]];
+      for (int j = 0; j < t->Fsub; j++) c += t->cellBins[feats[sl * t->Fsub + j]];
       t->hSlotCells.p[sl] = c;
       maxCells = std::max(maxCells, c);
     }
     // shared-memory layout: padded [bin][feature-in-group] with the widest power-of-two feature group G that keeps a task's
     // histogram (maxBins * G cells) within ~48 KB, i.e. four or more CTAs per SM; compact cells only if even G = 4 is too big
-    const int32_t maxBinsAll = *std::max_element(t->numBins.begin(), t->numBins.end());
+    const int32_t maxBinsAll = *std::max_element(t->cellBins.begin(), t->cellBins.end());
     int32_t padB = 0, G = 32;
     static const bool noPad = [] { const char* m = std::getenv("B2RF_NO_PAD"); return m && *m == '1'; }();
     // budget: 48 KB (four 256-thread CTAs per SM); histograms with more than 128 bins get 100 KB (two 512-thread CTAs) — measured
@@ -700,7 +744,15 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr;
     std::string err;
     cudaError_t e;
-    if (t->segMode) {
+    if (t->C) {   // multiclass: class-count histograms (segment mode only, checked in bind)
+      ClsHistLaunch c;
+      c.bins_rm = t->d_bins_rm; c.ldr = t->ldr; c.codeBytes = t->codeBytes; c.y = t->d_y; c.chunk_prefix = t->dChunkPrefix.p;
+      c.nSlots = (int32_t)nSlots; c.CH = SEG_CH; c.slot_fo = t->dSlotFo.p; c.slot_base = t->dSlotBase.p; c.Fsub = t->Fsub;
+      c.padB = maxBinsAll; c.C = t->C; c.M = t->M; c.direct = 0; c.hist = t->d_hist;
+      c.dseg = t->dSeg.p; c.slot_pos = t->dSlotPos.p; c.idx0 = t->dIdx0.p; c.idx1 = t->dIdx1.p;
+      e = launch_cls_hist(c, s);
+      t->nKernels += 2;
+    } else if (t->segMode) {
       b.dseg = t->dSeg.p; b.slot_pos = t->dSlotPos.p; b.idx0 = t->dIdx0.p; b.idx1 = t->dIdx1.p;
       e = launch_segment_hist(b, s);
       t->nKernels += 2;
@@ -731,7 +783,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   cudaEventRecord(t->ev1, s);
   t->evPending = true;
   t->inGroup = true;
-  if (n_cells) *n_cells = cells;
+  if (n_cells) *n_cells = cells * t->M;   // in units of 4 doubles: what the caller sums across ranks
   return 1;
 }
 
@@ -745,8 +797,17 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   a.parent4 = t->dParent.p; a.hasParent = t->dHasParent.p; a.numBins = t->dNumBins.p; a.isCat = t->dIsCat.p;
   a.minInstances = (double)t->p.minInstancesPerNode; a.minWeight = t->minWeightPerNode; a.minInfoGain = t->p.minInfoGain;
   a.out = t->dRec.p; a.catmask_out = t->dRecMask.p; a.maskWords = t->maskWords; a.impurity = t->p.impurity;
-  a.maxB = *std::max_element(t->numBins.begin(), t->numBins.end());
-  if (!cuda_ok(launch_best_split(a, s), "best_split launch")) return B2RF_ERR_CUDA;
+  a.maxB = *std::max_element(t->cellBins.begin(), t->cellBins.end());
+  if (t->C) {
+    ClsSplitLaunch c;
+    c.hist = t->d_hist; c.slot_fo = t->dSlotFo.p; c.slot_base = t->dSlotBase.p; c.Fsub = t->Fsub; c.nSlots = (int32_t)nSlots;
+    c.parentCls = t->dParentCls.p; c.hasParent = t->dHasParent.p; c.cellBins = t->dCellBins.p; c.kind = t->dKind.p;
+    c.minInstances = a.minInstances; c.minWeight = a.minWeight; c.minInfoGain = a.minInfoGain;
+    c.out = t->dRec.p; c.clsOut = t->dClsOut.p; c.catmask_out = t->dRecMask.p;
+    c.maxB = a.maxB; c.maskWords = t->maskWords; c.impurity = t->p.impurity; c.C = t->C; c.Cp = t->Cp; c.M = t->M;
+    if (!cuda_ok(launch_best_split_cls(c, s), "best_split_cls launch")) return B2RF_ERR_CUDA;
+    if (!cuda_ok(cudaMemcpyAsync(t->hClsOut.p, t->dClsOut.p, nSlots * 3 * t->Cp * 8, cudaMemcpyDeviceToHost, s), "download class counts")) return B2RF_ERR_CUDA;
+  } else if (!cuda_ok(launch_best_split(a, s), "best_split launch")) return B2RF_ERR_CUDA;
   t->nKernels++;
   if (!cuda_ok(cudaMemcpyAsync(t->hRec.p, t->dRec.p, nSlots * sizeof(SplitRec), cudaMemcpyDeviceToHost, s), "download split records")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpyAsync(t->hRecMask.p, t->dRecMask.p, nSlots * t->maskWords * 4, cudaMemcpyDeviceToHost, s), "download split masks")) return B2RF_ERR_CUDA;
@@ -788,6 +849,8 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
       n.isLeaf = isLeaf;
       n.stats.gain = r.gain; n.stats.impurity = r.impurity; n.stats.valid = r.valid != 0;
       for (int q = 0; q < 4; q++) n.stats.calc[q] = r.parent[q];
+      const double* cls3 = t->C ? t->hClsOut.p + (size_t)sl * 3 * t->Cp : nullptr;
+      if (t->C) { n.cls = (int64_t)t->clsPool.size(); t->clsPool.insert(t->clsPool.end(), cls3, cls3 + t->C); }
       t->trace.push_back({t->groupNo, tr, id, r.feature, r.splitIdx, r.gain, r.impurity, r.parent[0], r.parent[1], r.parent[2]});
       if (!isLeaf) {
         n.hasSplit = true; n.feature = r.feature;
@@ -804,6 +867,10 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
         HNode L, R;
         L.id = 2 * id; L.isLeaf = lLeaf; L.stats.gain = NAN; L.stats.impurity = r.leftImp; for (int q = 0; q < 4; q++) L.stats.calc[q] = r.left[q];
         R.id = 2 * id + 1; R.isLeaf = rLeaf; R.stats.gain = NAN; R.stats.impurity = r.rightImp; for (int q = 0; q < 4; q++) R.stats.calc[q] = r.right[q];
+        if (t->C) {
+          L.cls = (int64_t)t->clsPool.size(); t->clsPool.insert(t->clsPool.end(), cls3 + t->Cp, cls3 + t->Cp + t->C);
+          R.cls = (int64_t)t->clsPool.size(); t->clsPool.insert(t->clsPool.end(), cls3 + 2 * t->Cp, cls3 + 2 * t->Cp + t->C);
+        }
         const int li = (int)nodes.size();
         nodes.push_back(L); nodes.push_back(R);
         nodes[ni].left = li;
@@ -870,6 +937,7 @@ static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
   t->x_cat_off.push_back((int32_t)t->x_cats.size()); t->x_cat_len.push_back(0);
   t->x_threshold.push_back(0); t->x_prediction.push_back(0); t->x_impurity.push_back(0); t->x_gain.push_back(0);
   for (int q = 0; q < 4; q++) t->x_stats.push_back(n.stats.calc[q]);
+  if (t->C) for (int k = 0; k < t->C; k++) t->x_cls.push_back(n.cls >= 0 ? t->clsPool[(size_t)n.cls + k] : 0.0);
   const size_t at = base + me;
   if (n.left >= 0) {
     const size_t catMark = t->x_cats.size();
@@ -882,13 +950,14 @@ static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
       t->x_feature.resize(keep); t->x_left.resize(keep); t->x_right.resize(keep); t->x_ncat.resize(keep); t->x_cat_off.resize(keep);
       t->x_cat_len.resize(keep); t->x_threshold.resize(keep); t->x_prediction.resize(keep); t->x_impurity.resize(keep); t->x_gain.resize(keep);
       t->x_stats.resize(keep * 4); t->x_cats.resize(catMark);
+      if (t->C) t->x_cls.resize(keep * (size_t)t->C);
       t->x_prediction[at] = pred; t->x_impurity[at] = n.stats.impurity;
       return me;
     }
     t->x_feature[at] = n.feature; t->x_left[at] = l; t->x_right[at] = r; t->x_threshold[at] = n.threshold;
-    t->x_prediction[at] = vpred(n.stats.calc, t->p.impurity); t->x_impurity[at] = n.stats.impurity; t->x_gain[at] = n.stats.gain;
+    t->x_prediction[at] = t->node_pred(n); t->x_impurity[at] = n.stats.impurity; t->x_gain[at] = n.stats.gain;
     if (n.catMaskIdx >= 0) {
-      t->x_ncat[at] = t->numBins[n.feature];
+      t->x_ncat[at] = t->arity[n.feature];
       t->x_cat_off[at] = (int32_t)t->x_cats.size();
       const uint32_t* m = &t->catPool[(size_t)n.catMaskIdx * t->maskWords];
       int cnt = 0;
@@ -897,7 +966,7 @@ static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
     }
     return me;
   }
-  t->x_prediction[at] = vpred(n.stats.calc, t->p.impurity);
+  t->x_prediction[at] = t->node_pred(n);
   t->x_impurity[at] = n.stats.valid ? n.stats.impurity : -1.0;
   return me;
 }
@@ -905,7 +974,7 @@ static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
 static void do_export(b2rf_trainer* t) {
   if (t->exported) return;
   t->x_tree_off.clear(); t->x_feature.clear(); t->x_left.clear(); t->x_right.clear(); t->x_ncat.clear(); t->x_cat_off.clear(); t->x_cat_len.clear();
-  t->x_threshold.clear(); t->x_prediction.clear(); t->x_impurity.clear(); t->x_gain.clear(); t->x_stats.clear(); t->x_cats.clear();
+  t->x_threshold.clear(); t->x_prediction.clear(); t->x_impurity.clear(); t->x_gain.clear(); t->x_stats.clear(); t->x_cats.clear(); t->x_cls.clear();
   t->x_tree_off.push_back(0);
   for (int tr = 0; tr < t->T; tr++) {
     // categorical lists are appended after the subtree, so a node's cat_off is only final for kept nodes
@@ -936,6 +1005,18 @@ int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature
   memcpy(h_stats4, t->x_stats.data(), n * 32);
   memcpy(h_ncat, t->x_ncat.data(), n * 4); memcpy(h_cat_off, t->x_cat_off.data(), n * 4); memcpy(h_cat_len, t->x_cat_len.data(), n * 4);
   if (!t->x_cats.empty()) memcpy(h_cats, t->x_cats.data(), t->x_cats.size() * 8);
+  return B2RF_OK;
+}
+
+int b2rf_trainer_num_classes(const b2rf_trainer* t) { return t ? (t->C ? t->C : (t->p.impurity != 0 ? 2 : 0)) : 0; }
+
+int b2rf_trainer_export_class_counts(b2rf_trainer* t, double* h_counts) {
+  if (!t || !h_counts) { set_error("b2rf_trainer_export_class_counts: bad argument"); return B2RF_ERR_ARG; }
+  if (t->p.impurity == 0) { set_error("b2rf_trainer_export_class_counts: this trainer fits a regression forest"); return B2RF_ERR_STATE; }
+  do_export(t);
+  const size_t n = t->x_feature.size();
+  if (t->C) memcpy(h_counts, t->x_cls.data(), n * (size_t)t->C * 8);
+  else for (size_t i = 0; i < n; i++) { h_counts[i * 2] = t->x_stats[i * 4] - t->x_stats[i * 4 + 1]; h_counts[i * 2 + 1] = t->x_stats[i * 4 + 1]; }
   return B2RF_OK;
 }
 

@@ -64,7 +64,8 @@ class Forest:
     trace_i: np.ndarray = None
     trace_d: np.ndarray = None
     uid: str = ""
-    impurity_kind: str = "variance"   # "variance": regression; "gini" / "entropy": binary classification (stats hold class counts, see class_counts)
+    impurity_kind: str = "variance"   # "variance": regression; "gini" / "entropy": classification
+    counts: np.ndarray = None         # multiclass only: f64 [n, numClasses] class counts per node (binary models derive them from stats)
     _dev: dict = field(default_factory=dict, repr=False)
 
     # ---- structure ----
@@ -78,7 +79,9 @@ class Forest:
 
     @property
     def num_classes(self) -> int:
-        return 2 if self.is_classification else 0
+        if not self.is_classification:
+            return 0
+        return 2 if self.counts is None else int(self.counts.shape[1])
 
     @property
     def class_counts(self) -> np.ndarray:
@@ -86,6 +89,8 @@ class Forest:
         so count(class 1) = stats[:, 1] and count(class 0) = stats[:, 0] - stats[:, 1], both exact integers."""
         if not self.is_classification:
             raise ValueError("class_counts: this is a regression model")
+        if self.counts is not None:
+            return self.counts
         return np.stack([self.stats[:, 0] - self.stats[:, 1], self.stats[:, 1]], axis=1)
 
     def tree_slice(self, t: int) -> slice:
@@ -232,7 +237,12 @@ class Forest:
             raise TypeError("Forest.predict needs a CUDA tensor: this package has no CPU path")
         if self.is_classification:   # raw2prediction without thresholds: argmax of rawPrediction, first maximum
             raw = self.predict_raw(X)
-            return (raw[:, 1] > raw[:, 0]).to(torch.float64)
+            best, idx = raw[:, 0].clone(), torch.zeros(raw.shape[0], dtype=torch.float64, device=raw.device)
+            for k in range(1, raw.shape[1]):
+                m = raw[:, k] > best
+                idx[m] = float(k)
+                best = torch.where(m, raw[:, k], best)
+            return idx
         X = X.to(torch.float64).contiguous()
         if self.is_preorder():
             return self._predict_packed(X, True, False)[0]
@@ -258,8 +268,21 @@ class Forest:
             raise TypeError("Forest.predict_raw needs a CUDA tensor: this package has no CPU path")
         X = X.to(torch.float64).contiguous()
         d = self._device_arrays(X.device)
-        out = torch.empty((X.shape[0], 2), dtype=torch.float64, device=X.device)
         mode = 1 if ((self.num_trees == 1) if single_tree is None else single_tree) else 0
+        if self.counts is not None:     # multiclass (K7c)
+            key = "counts:" + str(X.device)
+            if key not in self._dev:
+                self._dev[key] = torch.as_tensor(np.ascontiguousarray(self.counts), dtype=torch.float64).to(X.device)
+            C_ = self.num_classes
+            out = torch.empty((X.shape[0], C_), dtype=torch.float64, device=X.device)
+            with torch.cuda.device(X.device):
+                st = torch.cuda.current_stream().cuda_stream
+                check(lib().b2rf_predict_raw_mc(X.data_ptr(), X.stride(0), X.shape[0], self.num_trees, d["tree_off"].data_ptr(), d["feature"].data_ptr(),
+                                                d["threshold"].data_ptr(), d["left"].data_ptr(), d["right"].data_ptr(), self._dev[key].data_ptr(), C_,
+                                                d["ncat"].data_ptr(), d["cat_off"].data_ptr(), d["cat_len"].data_ptr(), d["cats"].data_ptr(),
+                                                mode, out.data_ptr(), C.c_void_p(st)))
+            return out
+        out = torch.empty((X.shape[0], 2), dtype=torch.float64, device=X.device)
         with torch.cuda.device(X.device):
             st = torch.cuda.current_stream().cuda_stream
             check(lib().b2rf_predict_raw(X.data_ptr(), X.stride(0), X.shape[0], self.num_trees, d["tree_off"].data_ptr(), d["feature"].data_ptr(),

@@ -42,6 +42,7 @@ class TreeParams:
     featureSubsetStrategy: str = "auto"
     bootstrap: bool = False           # DecisionTreeRegressor: False; RandomForestRegressor default: True
     seed: int = 0
+    numClasses: int = 0               # classification only: 0 / 2 = binary; 3..32 = multiclass (per-class histograms)
 
     def copy(self, **kw) -> "TreeParams":
         return replace(self, **kw)
@@ -52,9 +53,16 @@ class TreeParams:
     def is_classification(self) -> bool:
         return self.impurity != "variance"
 
+    @property
+    def num_classes(self) -> int:
+        return 0 if not self.is_classification else max(2, int(self.numClasses))
+
     def validate(self):
         if self.impurity not in self.IMPURITIES:
             raise ValueError(f"impurity must be 'variance' (regression) or 'gini' / 'entropy' (classification), got {self.impurity!r}")
+        if self.numClasses and (not self.is_classification or not (2 <= int(self.numClasses) <= 32)):
+            raise ValueError(f"numClasses = {self.numClasses}: tree classifiers here support 2..32 classes (MLlib allows up to 100), and "
+                             f"regression takes none")
         if self.maxDepth < 0 or self.maxDepth > 30:
             raise ValueError(f"DecisionTree currently only supports maxDepth <= 30, but was given maxDepth = {self.maxDepth}.")
         if self.maxBins < 2:
@@ -77,4 +85,5 @@ class TreeParams:
         return B2rfParams(_to_int(self.maxDepth, "maxDepth"), _to_int(self.maxBins, "maxBins"),
                           _to_int(self.minInstancesPerNode, "minInstancesPerNode"), _to_int(self.numTrees, "numTrees"),
                           self.features_per_node(F), int(self.maxMemoryInMB), int(bool(self.bootstrap)), 0, float(self.minInfoGain),
-                          float(self.minWeightFractionPerNode), float(self.subsamplingRate), int(self.seed), self.IMPURITIES[self.impurity], 0)
+                          float(self.minWeightFractionPerNode), float(self.subsamplingRate), int(self.seed), self.IMPURITIES[self.impurity],
+                          int(self.numClasses) if int(self.numClasses) >= 3 else 0)

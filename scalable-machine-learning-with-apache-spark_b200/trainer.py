@@ -204,12 +204,14 @@ def _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode
 
 
 def _check_labels(y, params):
-    """Classification (gini / entropy) is binary here: labels must be exactly 0.0 or 1.0 (MLlib: 'Classification labels should be
-    in [0 to numClasses - 1]'); numClasses > 2 needs per-class statistics that K4 does not build."""
-    if params.is_classification and y.numel() and not bool(((y == 0) | (y == 1)).all()):
+    """Classification labels must be the integers 0 .. numClasses - 1 (MLlib: 'Classification labels should be in [0 to ...]')."""
+    if not params.is_classification or not y.numel():
+        return
+    C_ = params.num_classes
+    if not bool(((y >= 0) & (y < C_) & (y == y.floor())).all()):
         from ._lib import IllegalArgumentException
-        raise IllegalArgumentException(-3, "requirement failed: Classification labels should be in [0 to 1] (this build trains binary "
-                                       "classifiers only: numClasses == 2). Found labels other than 0.0 / 1.0.")
+        raise IllegalArgumentException(-3, f"requirement failed: Classification labels should be in [0 to {C_ - 1}] (numClasses == {C_}; pass "
+                                           f"TreeParams(numClasses=...) for more than two classes). Found invalid labels.")
 
 
 def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace):
@@ -519,6 +521,11 @@ def _export(h, F: int, keep_trace: bool) -> Forest:
     T = int(np.nonzero(tree_off == n)[0][0])
     tree_off = tree_off[: T + 1].copy()
     fo = Forest(F, tree_off, feature, threshold, left, right, prediction, impurity, gain, stats, ncat_a, cat_off, cat_len, cats[:ncat])
+    ncls = int(L.b2rf_trainer_num_classes(h))
+    if ncls > 2:      # multiclass: the per-class counts are the node statistics (binary models derive theirs from stats)
+        cc = Z((max(n, 1), ncls), np.float64)
+        check(L.b2rf_trainer_export_class_counts(h, P(cc)))
+        fo.counts = cc[:n]
     fo.timers = dict(findBestSplits=float(sec[2]), chooseSplits=float(sec[3]))
     fo.counters = dict(groups=int(cnt[0]), hist_launches=int(cnt[1]), rows_trees_scanned=int(cnt[2]), learning_nodes=int(cnt[3]),
                        kernel_launches=int(cnt[4]), hist_alg_bytes=int(cnt[5]))

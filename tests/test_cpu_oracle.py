@@ -142,3 +142,42 @@ def test_classifier_known_answers(oracle):
     assert e.impurity[0] == pytest.approx(-(0.6 * np.log2(0.6) + 0.4 * np.log2(0.4)), rel=1e-14)
     with pytest.raises(oracle.OracleError):
         oracle.fit(np.zeros((3, 1)), np.array([0.0, 1.0, 2.0]), [0], impurity="gini")
+
+
+def test_numpy_multiclass_restatement_matches_cpp_oracle_on_binary(oracle, b2rf):
+    """oracle/multiclass.py (any numClasses, unordered categorical splits) is an independent restatement of the training loop; for
+    numClasses == 2 it must reproduce the C++ oracle bit for bit (trees, class counts, impurities, gains, evaluation order, groups)."""
+    from oracle import multiclass as M
+    X, y, arity = b2rf.synth.airbnb(3000)
+    X, y = X.numpy(), y.numpy()
+    yb = (y > np.median(y)).astype(np.float64)
+    po = np.array([0, 750, 1500, 2250, 3000])
+    for kw in [dict(maxDepth=5, maxBins=40, impurity="gini"),
+               dict(maxDepth=4, maxBins=40, numTrees=6, bootstrap=True, seed=42, part_offsets=po, impurity="entropy"),
+               dict(maxDepth=6, maxBins=40, numTrees=5, bootstrap=True, seed=7, part_offsets=po, impurity="gini", featureSubsetStrategy="all",
+                    maxMemoryInMB=1, minInstancesPerNode=3)]:
+        m = M.fit(X, yb, arity, 2, **kw)
+        o = oracle.fit(X, yb, arity, **kw)
+        for a in ("tree_off", "feature", "threshold", "left", "right", "prediction", "impurity", "gain", "trace_i"):
+            assert np.array_equal(getattr(m, a), getattr(o, a)), a
+        assert np.array_equal(m.class_counts, o.stats[:, :2]) and list(m.group_sizes) == list(o.group_sizes)
+        assert np.array_equal(m.predict_raw(X[:100]), o.predict_raw(X[:100]))
+
+
+def test_multiclass_metadata_and_subset_splits(b2rf):
+    """DecisionTreeMetadata: with maxBins = 32 categorical features of arity <= floor(log2(32/2 + 1) + 1) = 5 are unordered and count
+    2^(arity-1) - 1 bins; RandomForest.extractMultiClassCategories(splitIndex + 1, arity) lists the set bits."""
+    from oracle import multiclass as M
+    assert M.unordered_left_categories(0, 3) == [0] and M.unordered_left_categories(1, 3) == [1] and M.unordered_left_categories(2, 3) == [0, 1]
+    rng = np.random.default_rng(1)
+    n = 600
+    X = np.stack([rng.integers(0, 3, n), rng.integers(0, 5, n), rng.integers(0, 6, n), rng.normal(size=n)], axis=1).astype(np.float64)
+    y = ((X[:, 0] == 1) * 1 + (X[:, 1] >= 3) * 1 + (X[:, 3] > 0.5) * 1).astype(np.float64) % 3
+    m = M.fit(X, y, [3, 5, 6, 0], 3, maxDepth=3, maxBins=32)
+    assert m.unordered == [0, 1]                                   # arity 6 > 5 stays ordered (sorted by category impurity)
+    assert (m.predict(X) == y).mean() > 0.6
+    # the three-class toy: a pure split on an unordered feature must be found at the root when one exists
+    Xp = np.array([[0.0], [1.0], [2.0]] * 30); yp = np.array([0.0, 1.0, 2.0] * 30)
+    t = M.fit(Xp, yp, [3], 3, maxDepth=2, maxBins=32)
+    assert t.feature[0] == 0 and t.ncat[0] == 3 and len(t.feature) == 5 and (t.predict(Xp) == yp).all()
+    assert t.impurity[0] == pytest.approx(1 - 3 * (1 / 3) ** 2)
