@@ -44,7 +44,7 @@ def _node_rows(fo: Forest, t: int):
         else:
             split = {"featureIndex": int(fo.feature[a]), "leftCategoriesOrThreshold": [float(fo.threshold[a])], "numCategories": -1}
         # impurityStats: regression (weight, sum, sum of squares); classification the class counts
-        ist = [float(fo.stats[a, 0] - fo.stats[a, 1]), float(fo.stats[a, 1])] if fo.is_classification else [float(v) for v in fo.stats[a, :3]]
+        ist = [float(v) for v in fo.class_counts[a]] if fo.is_classification else [float(v) for v in fo.stats[a, :3]]
         rows.append({"id": i, "prediction": float(fo.prediction[a]), "impurity": float(fo.impurity[a]),
                      "impurityStats": ist, "rawCount": int(fo.stats[a, 3]),
                      "gain": -1.0 if leaf else float(fo.gain[a]), "leftChild": -1 if leaf else int(fo.left[a]),
@@ -117,8 +117,10 @@ def load_forest(path: str):
         rows += pq.read_table(fn).to_pylist()
     ensemble = meta["class"].endswith(("RandomForestRegressionModel", "RandomForestClassificationModel"))
     classification = meta["class"].endswith("ClassificationModel")
-    if classification and int(meta.get("numClasses", 2)) != 2:
-        raise ValueError(f"{path}: numClasses = {meta.get('numClasses')}; only binary classification models can be loaded")
+    num_classes = int(meta.get("numClasses", 2)) if classification else 0
+    if classification and not (2 <= num_classes <= 32):
+        raise ValueError(f"{path}: numClasses = {num_classes}; classification models with 2..32 classes can be loaded")
+    counts = []
     if ensemble:
         T = int(meta["numTrees"])
         per = [[] for _ in range(T)]
@@ -140,7 +142,11 @@ def load_forest(path: str):
             cols["left"].append(r["leftChild"]); cols["right"].append(r["rightChild"])
             cols["prediction"].append(r["prediction"]); cols["impurity"].append(r["impurity"]); cols["gain"].append(0.0 if leaf else r["gain"])
             st = list(r["impurityStats"]) + [0.0] * 3
-            if classification:     # class counts (c0, c1) -> the trainer's (sum w, sum w*y, sum w*y*y) with y in {0, 1}
+            if classification and num_classes > 2:
+                cc = [float(v) for v in r["impurityStats"]][:num_classes]
+                counts.append(cc + [0.0] * (num_classes - len(cc)))
+                cols["stats"].append([float(sum(counts[-1])), 0.0, 0.0, float(r["rawCount"])])
+            elif classification:   # class counts (c0, c1) -> the trainer's (sum w, sum w*y, sum w*y*y) with y in {0, 1}
                 cols["stats"].append([st[0] + st[1], st[1], st[1], float(r["rawCount"])])
             else:
                 cols["stats"].append([st[0], st[1], st[2], float(r["rawCount"])])
@@ -157,6 +163,8 @@ def load_forest(path: str):
     if classification:
         imp = meta.get("paramMap", {}).get("impurity", meta.get("defaultParamMap", {}).get("impurity", "gini"))
         fo.impurity_kind = str(imp).lower()
+        if num_classes > 2:
+            fo.counts = np.array(counts, np.float64).reshape(-1, num_classes)
     return meta, fo
 
 

@@ -335,7 +335,7 @@ class B200RandomForestRegressionModel(_ForestModelBase):
             s = fo.tree_slice(t)
             sub = Forest(fo.num_features, np.array([0, s.stop - s.start], np.int64), fo.feature[s], fo.threshold[s], fo.left[s], fo.right[s],
                          fo.prediction[s], fo.impurity[s], fo.gain[s], fo.stats[s], fo.ncat[s], fo.cat_off[s], fo.cat_len[s], fo.cats,
-                         impurity_kind=fo.impurity_kind)
+                         impurity_kind=fo.impurity_kind, counts=None if fo.counts is None else fo.counts[s])
             out.append(self._tree_model_cls(sub))
         return out
 
@@ -379,10 +379,21 @@ class _TreeEstimatorBase(Estimator, _TreeRegressorParams):
         dev = _ForestModelBase._device()
         Xd = torch.as_tensor(X, device=dev)
         yd = torch.as_tensor(y, device=dev)
+        plist = [e._tree_params() for e in estimators]
+        if plist[0].is_classification:
+            # Classifier.getNumClasses without label metadata: max label + 1 (MLlib stops at 100 classes, this build at 32)
+            ok = len(y) > 0 and bool(np.all((y >= 0) & (y == np.floor(y))))
+            nc = int(y.max()) + 1 if ok else 0
+            if not ok or nc > 32:
+                from ._lib import IllegalArgumentException
+                raise IllegalArgumentException(-3, "requirement failed: Classifier inferred " + str(nc) + " from label values in column "
+                                               + est0.getOrDefault("labelCol") + ", but labels must be the integers 0 .. numClasses - 1 with "
+                                               "numClasses <= 32 here (MLlib: <= 100).")
+            plist = [p.copy(numClasses=max(nc, 2)) for p in plist]
         if len(estimators) == 1:
-            yield estimators[0]._make_model(trainer.fit_tensors(Xd, yd, arity, estimators[0]._tree_params(), part_offsets=po))
+            yield estimators[0]._make_model(trainer.fit_tensors(Xd, yd, arity, plist[0], part_offsets=po))
             return
-        forests = trainer.fit_many_tensors(Xd, yd, arity, [e._tree_params() for e in estimators], part_offsets=po)   # shared passes
+        forests = trainer.fit_many_tensors(Xd, yd, arity, plist, part_offsets=po)   # shared passes
         for est, forest in zip(estimators, forests):
             yield est._make_model(forest)
 
@@ -452,7 +463,8 @@ class B200RandomForestRegressor(_TreeEstimatorBase):
 # ------------------------------------------------------------------------------------------------------------------
 # Binary classifiers: pyspark.ml.classification.DecisionTreeClassifier / RandomForestClassifier as the labs'
 # `Solutions/Labs/ML 07L - Hyperparameter Tuning Lab.py:80-82,105-108,140-155` use them (label priceClass in {0, 1}).
-# numClasses > 2 is rejected at fit time: K4 builds (sum w, sum w*y) only, which holds exactly two class counts.
+# Binary labels ride on the regression statistics (sum w, sum w*y); three or more classes take the per-class kernels of
+# k8_multiclass.cu (numClasses = max label + 1 as Classifier.getNumClasses infers it, at most 32 here).
 # ------------------------------------------------------------------------------------------------------------------
 class _ClassifierParams:
     rawPredictionCol = Param(Params, "rawPredictionCol", "raw prediction (a.k.a. confidence) column name.", TypeConverters.toString)
@@ -487,8 +499,8 @@ class _ClassifierModelBase(_ClassifierParams, _ForestModelBase):
         """probability2prediction: argmax p (first maximum), or argmax p / t when thresholds are set."""
         if self.isDefined("thresholds") and self.getOrDefault("thresholds") is not None:
             t = np.asarray(self.getOrDefault("thresholds"), np.float64)
-            if t.shape != (2,) or (t < 0).any() or (t == 0).sum() > 1:
-                raise ValueError(f"thresholds must have length numClasses = 2, values >= 0, at most one 0; got {t.tolist()}")
+            if t.shape != (prob.shape[1],) or (t < 0).any() or (t == 0).sum() > 1:
+                raise ValueError(f"thresholds must have length numClasses = {prob.shape[1]}, values >= 0, at most one 0; got {t.tolist()}")
             with np.errstate(divide="ignore", invalid="ignore"):
                 scaled = prob / t
             scaled = np.where(np.isnan(scaled), -np.inf, scaled)
@@ -509,7 +521,7 @@ class _ClassifierModelBase(_ClassifierParams, _ForestModelBase):
 
     def _transform(self, dataset):
         X, _, _ = _extract(dataset, self.getOrDefault("featuresCol"))
-        raw = self._raw(X) if X.shape[0] else np.zeros((0, 2))
+        raw = self._raw(X) if X.shape[0] else np.zeros((0, self.numClasses))
         prob = self._normalize(raw)
         cols = {}
         if self.getOrDefault("rawPredictionCol"):

@@ -55,6 +55,40 @@ def main():
             except AssertionError as e:
                 ok = False
                 print(f"[mgpu] {name}: FAILED {e}", flush=True)
+    # ---- classifiers: binary (class counts ride on the regression statistics) and three classes (per-class histograms, all-reduced
+    # as cells of 4 * ceil(C / 4) doubles); integer statistics, so the sharded fit must equal the restatement exactly ----
+    from helpers import assert_classifier_parity
+    from oracle import multiclass as M
+    n = 6001
+    cuts = [n * r // world for r in range(world + 1)]
+    cuts[1] += 7 if world > 1 else 0
+    lo, hi = cuts[rank], cuts[rank + 1]
+    Xa, ya, arity = b2rf.synth.airbnb(n, row0=0)
+    Xa, ya = Xa.numpy(), ya.numpy()
+    po = [0]
+    for r in range(world):
+        m_ = cuts[r + 1] - cuts[r]
+        po += [cuts[r] + int(v) for v in np.minimum(np.arange(0, m_ + 512, 512), m_)[1:]]
+    po_local = np.minimum(np.arange(0, hi - lo + 512, 512), hi - lo).astype(np.int64)
+    for name, C_ in [("airbnb-rf-binary", 2), ("airbnb-rf-3class", 3)]:
+        qs = np.quantile(ya, np.linspace(0, 1, C_ + 1)[1:-1])
+        lab = np.digitize(ya, qs).astype(np.float64)
+        kw = dict(maxDepth=5, maxBins=40, numTrees=8, bootstrap=True, seed=42)
+        p = b2rf.TreeParams(impurity="gini", numClasses=C_, **kw)
+        g = trainer.fit_tensors(torch.as_tensor(Xa[lo:hi], device=dev), torch.as_tensor(lab[lo:hi], device=dev), arity, p, part_offsets=po_local,
+                                keep_trace=True)
+        if rank == 0:
+            try:
+                if C_ == 2:
+                    assert_classifier_parity(g, O.fit(Xa, lab, arity, part_offsets=po, impurity="gini", **kw))
+                else:
+                    m = M.fit(Xa, lab, arity, C_, part_offsets=np.array(po), impurity="gini", **kw)
+                    for a in ("tree_off", "feature", "threshold", "left", "right", "prediction", "impurity", "gain", "class_counts", "trace_i"):
+                        assert np.array_equal(getattr(g, a), getattr(m, a)), a
+                print(f"[mgpu] {name}: world={world} OK ({g.num_nodes()} nodes, groups={g.counters['groups']})", flush=True)
+            except AssertionError as e:
+                ok = False
+                print(f"[mgpu] {name}: FAILED {e}", flush=True)
     flag = torch.tensor([1 if ok else 0], device=dev)
     dist.broadcast(flag, 0)
     dist.barrier()

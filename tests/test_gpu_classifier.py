@@ -145,5 +145,5 @@ def test_spark_adapter_classifier_flow(b2rf, oracle, cuda, tmp_path):
     dt = sp.B200DecisionTreeClassifier(labelCol="priceClass", maxBins=40, impurity="entropy").fit(train)
     od = oracle.fit(X[:ntr], y[:ntr], arity, maxDepth=5, maxBins=40, part_offsets=po, impurity="entropy")
     assert dt.numNodes == len(od.feature) and np.array_equal(dt.transform(test).col("rawPrediction"), od.predict_raw(X[ntr:]))
-    with pytest.raises(b2rf.IllegalArgumentException, match="numClasses == 2"):
-        sp.B200DecisionTreeClassifier(labelCol="priceClass").fit(LocalFrame({"features": X[:30], "priceClass": np.arange(30) % 3.0}))
+    with pytest.raises(b2rf.IllegalArgumentException, match="labels must be the integers"):
+        sp.B200DecisionTreeClassifier(labelCol="priceClass").fit(LocalFrame({"features": X[:30], "priceClass": np.arange(30) * 0.5}))

@@ -64,3 +64,40 @@ def test_multiclass_label_check(b2rf, cuda):
     X = np.random.default_rng(0).normal(size=(60, 3)); y = np.arange(60) % 4.0
     with pytest.raises(b2rf.IllegalArgumentException, match="numClasses == 3"):
         b2rf.trainer.fit_tensors(torch.as_tensor(X, device=cuda), torch.as_tensor(y, device=cuda), [0, 0, 0], b2rf.TreeParams(impurity="gini", numClasses=3))
+
+
+def test_multiclass_adapter_and_persistence(b2rf, cuda, tmp_path):
+    """pyspark-style flow with a three-level label: numClasses is inferred as max label + 1, the model emits rawPrediction /
+    probability vectors of that length, honours thresholds, and survives save / load in MLlib's layout (impurityStats = class counts)."""
+    import json
+    from b2rf import spark as sp
+    from b2rf._pyspark_stub import LocalFrame, ml_attr_metadata
+    from oracle import multiclass as M
+    X, y, arity = _data(b2rf, 3000, 3)
+    meta = {"features": ml_attr_metadata(arity)}
+    train = LocalFrame({"features": X[:2400], "tier": y[:2400]}, meta, num_partitions=3)
+    test = LocalFrame({"features": X[2400:], "tier": y[2400:]}, meta)
+    po = np.array([0, 800, 1600, 2400])
+    rf = sp.B200RandomForestClassifier(labelCol="tier", maxBins=40, maxDepth=4, numTrees=6, seed=11)
+    model = rf.fit(train)
+    m = M.fit(X[:2400], y[:2400], arity, 3, part_offsets=po, maxDepth=4, maxBins=40, numTrees=6, bootstrap=True, seed=11, impurity="gini")
+    assert model.numClasses == 3 and model.totalNumNodes == len(m.feature)
+    out = model.transform(test)
+    np.testing.assert_allclose(out.col("rawPrediction"), m.predict_raw(X[2400:]), rtol=1e-15, atol=0)
+    assert np.array_equal(out.col("prediction"), m.predict(X[2400:]))
+    assert out.col("probability").shape == (600, 3)
+    np.testing.assert_allclose(out.col("probability").sum(1), 1.0, rtol=1e-12)
+    biased = model.copy({model.thresholds: [1.0, 1.0, 0.01]}).transform(test).col("prediction")
+    assert (biased == 2.0).mean() > (out.col("prediction") == 2.0).mean()
+    assert len(model.trees) == 6 and model.trees[0].numClasses == 3
+    path = str(tmp_path / "rfc3")
+    model.write().overwrite().save(path)
+    md = json.loads(open(path + "/metadata/part-00000").readline())
+    assert md["numClasses"] == 3 and md["class"].endswith("RandomForestClassificationModel")
+    again = sp.B200RandomForestClassificationModel.load(path)
+    assert again.numClasses == 3 and np.array_equal(again._forest.class_counts, model._forest.class_counts)
+    assert np.array_equal(again.transform(test).col("rawPrediction"), out.col("rawPrediction"))
+    assert "numClasses=3" in model.toDebugString.splitlines()[0]
+    dt = sp.B200DecisionTreeClassifier(labelCol="tier", maxBins=40, maxDepth=3, impurity="entropy").fit(train)
+    md_ = M.fit(X[:2400], y[:2400], arity, 3, part_offsets=po, maxDepth=3, maxBins=40, impurity="entropy")
+    assert np.array_equal(dt.transform(test).col("rawPrediction"), md_.predict_raw(X[2400:]))
