@@ -10,7 +10,9 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <atomic>
 #include <mutex>
+#include <thread>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -929,57 +931,89 @@ int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_cou
 }
 
 // LearningNode.toNode(prune = true): pre-order flattening; an internal node whose children are leaves with equal
-// predictions collapses into a leaf.
-static int flatten_node(b2rf_trainer* t, int tr, int ni, int64_t base) {
+// predictions collapses into a leaf.  Trees are flattened independently (a few worker threads), then concatenated.
+struct FlatTree {
+  std::vector<int32_t> feature, left, right, ncat, cat_off, cat_len;
+  std::vector<double> threshold, prediction, impurity, gain, stats, cats, cls;
+};
+
+static int flatten_node(const b2rf_trainer* t, FlatTree& x, int tr, int ni) {
   const HNode& n = t->trees[tr][ni];
-  const int me = (int)(t->x_feature.size() - base);
-  t->x_feature.push_back(-1); t->x_left.push_back(-1); t->x_right.push_back(-1); t->x_ncat.push_back(0);
-  t->x_cat_off.push_back((int32_t)t->x_cats.size()); t->x_cat_len.push_back(0);
-  t->x_threshold.push_back(0); t->x_prediction.push_back(0); t->x_impurity.push_back(0); t->x_gain.push_back(0);
-  for (int q = 0; q < 4; q++) t->x_stats.push_back(n.stats.calc[q]);
-  if (t->C) for (int k = 0; k < t->C; k++) t->x_cls.push_back(n.cls >= 0 ? t->clsPool[(size_t)n.cls + k] : 0.0);
-  const size_t at = base + me;
+  const int me = (int)x.feature.size();
+  x.feature.push_back(-1); x.left.push_back(-1); x.right.push_back(-1); x.ncat.push_back(0);
+  x.cat_off.push_back((int32_t)x.cats.size()); x.cat_len.push_back(0);
+  x.threshold.push_back(0); x.prediction.push_back(0); x.impurity.push_back(0); x.gain.push_back(0);
+  for (int q = 0; q < 4; q++) x.stats.push_back(n.stats.calc[q]);
+  if (t->C) for (int k = 0; k < t->C; k++) x.cls.push_back(n.cls >= 0 ? t->clsPool[(size_t)n.cls + k] : 0.0);
+  const size_t at = (size_t)me;
   if (n.left >= 0) {
-    const size_t catMark = t->x_cats.size();
-    const int l = flatten_node(t, tr, n.left, base);
-    const int r = flatten_node(t, tr, n.left + 1, base);
-    const bool bothLeaves = t->x_feature[base + l] < 0 && t->x_feature[base + r] < 0;
-    if (bothLeaves && t->x_prediction[base + l] == t->x_prediction[base + r]) {
-      const double pred = t->x_prediction[base + l];
+    const size_t catMark = x.cats.size();
+    const int l = flatten_node(t, x, tr, n.left);
+    const int r = flatten_node(t, x, tr, n.left + 1);
+    const bool bothLeaves = x.feature[l] < 0 && x.feature[r] < 0;
+    if (bothLeaves && x.prediction[l] == x.prediction[r]) {
+      const double pred = x.prediction[l];
       const size_t keep = at + 1;
-      t->x_feature.resize(keep); t->x_left.resize(keep); t->x_right.resize(keep); t->x_ncat.resize(keep); t->x_cat_off.resize(keep);
-      t->x_cat_len.resize(keep); t->x_threshold.resize(keep); t->x_prediction.resize(keep); t->x_impurity.resize(keep); t->x_gain.resize(keep);
-      t->x_stats.resize(keep * 4); t->x_cats.resize(catMark);
-      if (t->C) t->x_cls.resize(keep * (size_t)t->C);
-      t->x_prediction[at] = pred; t->x_impurity[at] = n.stats.impurity;
+      x.feature.resize(keep); x.left.resize(keep); x.right.resize(keep); x.ncat.resize(keep); x.cat_off.resize(keep);
+      x.cat_len.resize(keep); x.threshold.resize(keep); x.prediction.resize(keep); x.impurity.resize(keep); x.gain.resize(keep);
+      x.stats.resize(keep * 4); x.cats.resize(catMark);
+      if (t->C) x.cls.resize(keep * (size_t)t->C);
+      x.prediction[at] = pred; x.impurity[at] = n.stats.impurity;
       return me;
     }
-    t->x_feature[at] = n.feature; t->x_left[at] = l; t->x_right[at] = r; t->x_threshold[at] = n.threshold;
-    t->x_prediction[at] = t->node_pred(n); t->x_impurity[at] = n.stats.impurity; t->x_gain[at] = n.stats.gain;
+    x.feature[at] = n.feature; x.left[at] = l; x.right[at] = r; x.threshold[at] = n.threshold;
+    x.prediction[at] = t->node_pred(n); x.impurity[at] = n.stats.impurity; x.gain[at] = n.stats.gain;
     if (n.catMaskIdx >= 0) {
-      t->x_ncat[at] = t->arity[n.feature];
-      t->x_cat_off[at] = (int32_t)t->x_cats.size();
+      x.ncat[at] = t->arity[n.feature];
+      x.cat_off[at] = (int32_t)x.cats.size();
       const uint32_t* m = &t->catPool[(size_t)n.catMaskIdx * t->maskWords];
       int cnt = 0;
-      for (int c = 0; c < t->maskWords * 32; c++) if ((m[c >> 5] >> (c & 31)) & 1u) { t->x_cats.push_back((double)c); cnt++; }
-      t->x_cat_len[at] = cnt;
+      for (int c = 0; c < t->maskWords * 32; c++) if ((m[c >> 5] >> (c & 31)) & 1u) { x.cats.push_back((double)c); cnt++; }
+      x.cat_len[at] = cnt;
     }
     return me;
   }
-  t->x_prediction[at] = t->node_pred(n);
-  t->x_impurity[at] = n.stats.valid ? n.stats.impurity : -1.0;
+  x.prediction[at] = t->node_pred(n);
+  x.impurity[at] = n.stats.valid ? n.stats.impurity : -1.0;
   return me;
 }
 
 static void do_export(b2rf_trainer* t) {
   if (t->exported) return;
+  std::vector<FlatTree> flat(t->T);
+  {
+    size_t total = 0;
+    for (int tr = 0; tr < t->T; tr++) total += t->trees[tr].size();
+    const int workers = (int)std::max<size_t>(1, std::min<size_t>({(size_t)t->T, (size_t)8, total / 4096 + 1}));
+    std::atomic<int> next{0};
+    auto work = [&]() {
+      for (int tr = next.fetch_add(1); tr < t->T; tr = next.fetch_add(1)) {
+        FlatTree& x = flat[tr];
+        const size_t m = t->trees[tr].size();
+        for (auto* vec : {&x.feature, &x.left, &x.right, &x.ncat, &x.cat_off, &x.cat_len}) vec->reserve(m);
+        for (auto* vec : {&x.threshold, &x.prediction, &x.impurity, &x.gain}) vec->reserve(m);
+        x.stats.reserve(m * 4);
+        flatten_node(t, x, tr, 0);
+      }
+    };
+    std::vector<std::thread> pool;
+    for (int w = 1; w < workers; w++) pool.emplace_back(work);
+    work();
+    for (auto& th : pool) th.join();
+  }
   t->x_tree_off.clear(); t->x_feature.clear(); t->x_left.clear(); t->x_right.clear(); t->x_ncat.clear(); t->x_cat_off.clear(); t->x_cat_len.clear();
   t->x_threshold.clear(); t->x_prediction.clear(); t->x_impurity.clear(); t->x_gain.clear(); t->x_stats.clear(); t->x_cats.clear(); t->x_cls.clear();
   t->x_tree_off.push_back(0);
   for (int tr = 0; tr < t->T; tr++) {
-    // categorical lists are appended after the subtree, so a node's cat_off is only final for kept nodes
-    flatten_node(t, tr, 0, (int64_t)t->x_feature.size());
+    FlatTree& x = flat[tr];
+    const int32_t catBase = (int32_t)t->x_cats.size();
+    for (auto& o : x.cat_off) o += catBase;          // a node's category list lives in the forest-wide pool
+    auto app = [](auto& dst, const auto& src) { dst.insert(dst.end(), src.begin(), src.end()); };
+    app(t->x_feature, x.feature); app(t->x_left, x.left); app(t->x_right, x.right); app(t->x_ncat, x.ncat); app(t->x_cat_off, x.cat_off);
+    app(t->x_cat_len, x.cat_len); app(t->x_threshold, x.threshold); app(t->x_prediction, x.prediction); app(t->x_impurity, x.impurity);
+    app(t->x_gain, x.gain); app(t->x_stats, x.stats); app(t->x_cats, x.cats); app(t->x_cls, x.cls);
     t->x_tree_off.push_back((int64_t)t->x_feature.size());
+    x = FlatTree();
   }
   t->exported = true;
 }
