@@ -38,33 +38,75 @@ NCU_TRAFFIC = {"C3": {"traffic": 109.988e9, "algorithmic": 3.765e9}}
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+    """Samples SM clocks and clock-event (throttle) reasons while the timed region runs.
+
+    The values are the ones `nvidia-smi --query-gpu=clocks.sm,clocks.max.sm,clocks_event_reasons.*` prints, read through NVML
+    in-process (nvidia_ml_py): spawning nvidia-smi five times a second from inside the timed region stalls the CUDA driver for tens of
+    milliseconds per call and showed up as occasional 0.1-0.3 s outliers in the short host-synchronous phases of a step.  If NVML
+    cannot be loaded the sampler falls back to the nvidia-smi subprocess at a lower rate."""
+
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
     def __init__(self, index: int):
         super().__init__(daemon=True)
         self.index = index
-        self.rows = []
+        self.rows = []          # [sm_mhz, sm_max_mhz, hw_slowdown, hw_thermal_slowdown, sw_thermal_slowdown, sw_power_cap] (booleans)
         self.stop_flag = threading.Event()
+        self.source = "nvml"
+        self._nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = index
+            if vis:
+                ids = [v.strip() for v in vis.split(",") if v.strip()]
+                if index < len(ids) and ids[index].isdigit():
+                    phys = int(ids[index])
+            self._h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self._nvml = pynvml
+            self.index = phys
+        except Exception:
+            self.source = "nvidia-smi"
 
-    def run(self):
+    def _sample_nvml(self):
+        n = self._nvml
+        sm = n.nvmlDeviceGetClockInfo(self._h, n.NVML_CLOCK_SM)
+        mx = n.nvmlDeviceGetMaxClockInfo(self._h, n.NVML_CLOCK_SM)
+        try:
+            r = n.nvmlDeviceGetCurrentClocksEventReasons(self._h)
+        except Exception:
+            r = n.nvmlDeviceGetCurrentClocksThrottleReasons(self._h)
+        bits = [n.nvmlClocksEventReasonHwSlowdown, n.nvmlClocksEventReasonHwThermalSlowdown, n.nvmlClocksEventReasonSwThermalSlowdown,
+                n.nvmlClocksEventReasonSwPowerCap]
+        self.rows.append([int(sm), int(mx)] + [bool(r & b) for b in bits])
+
+    def _sample_smi(self):
         q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                             capture_output=True, text=True, timeout=5).stdout.strip()
+        c = [v.strip() for v in out.split(",")]
+        if len(c) >= 6 and c[0].isdigit():
+            self.rows.append([int(c[0]), int(c[1]) if c[1].isdigit() else 0] + [v.lower().startswith("active") for v in c[2:6]])
+
+    def run(self):
         while not self.stop_flag.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
-                                     capture_output=True, text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if self._nvml is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self.stop_flag.wait(0.2)
+            self.stop_flag.wait(0.1 if self._nvml is not None else 1.0)
 
     def summary(self):
-        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) > 2 + i and r[2 + i].lower().startswith("active")})
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm)}
+        sm = sorted(r[0] for r in self.rows)
+        mx = [r[1] for r in self.rows if r[1]]
+        reasons = sorted({self.NAMES[i] for r in self.rows for i in range(4) if r[2 + i]})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons, "samples": len(sm),
+                "source": self.source}
 
 
 def measured_peak_gbs():

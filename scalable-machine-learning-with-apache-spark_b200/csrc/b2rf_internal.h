@@ -67,6 +67,7 @@ struct BucketLaunch {
   int32_t padB;                          // > 0: padded [bin][feature-in-group] shared layout with padB bins; 0: compact cells
   int32_t G;                             // padded layout: features per group / task (power of two <= 32)
   int32_t codeBytes;                     // 1 / 2 bytes per bin code; ldr counts codes
+  int32_t zeroReg;                       // generic kernel: accumulate bin 0 of every feature in registers, one add per task
   double* hist;
   // segment mode (dseg != nullptr): slot s owns rows idx[seg.buf][seg.start ...] with seg = dseg[slot_pos[s]]
   const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;

@@ -743,6 +743,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     b.bins_rm = t->d_bins_rm; b.ldr = t->ldr; b.y = t->d_y; b.rowlist = t->dRowList.p; b.slot_start = t->dSlotStart.p; b.slot_count = t->dSlotCount.p;
     b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->segMode ? SEG_CH : t->chunkRows; b.slot_fo = t->dSlotFo.p;
     b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.padB = padB; b.G = G; b.codeBytes = t->codeBytes; b.hist = t->d_hist;
+    { static const bool zr = [] { const char* m = std::getenv("B2RF_ZERO_REG"); return !(m && *m == '0'); }(); b.zeroReg = zr ? 1 : 0; }
     b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr;
     std::string err;
     cudaError_t e;

@@ -376,7 +376,7 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist32_kernel(const Buc
 template <bool DIRECT, int THREADS, bool ONE_ROW, int CB>
 __device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
                                                  double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
-                                                 int Rrt, int rrt, uint4* st) {
+                                                 int Rrt, int rrt, uint4* st, uint32_t& z_c, double& z_s, double& z_q) {
   const int R = ONE_ROW ? 1 : Rrt, r = ONE_ROW ? 0 : rrt;
   constexpr int W = THREADS / 32;
   constexpr int U = ONE_ROW ? 16 : 8;                                          // row groups in flight (gathers issued before the first atomic)
@@ -406,6 +406,11 @@ __device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const ui
           if (DIRECT) {
             double* c = hb + (size_t)(gbase + bin[u]) * 4;
             atomicAdd(c, (double)wv); atomicAdd(c + 1, wy); atomicAdd(c + 2, wyy);
+          } else if (a.zeroReg && bin[u] == 0u) {
+            // bin 0 of every feature is kept in registers and added once per task: for categorical features indexed by
+            // frequency (StringIndexer) and for zero-heavy counts it is the hottest cell of the column, the one every warp of
+            // the CTA would otherwise fight over with compare-and-swap loops
+            z_c += wv; z_s += wy; z_q += wyy;
           } else {
             const uint32_t cell = sbase + bin[u] * sstep;
             atomicAdd(&scnt[cell], wv); atomicAdd(&ssum[cell], wy); atomicAdd(&ssq[cell], wyy);
@@ -466,15 +471,23 @@ __global__ void __launch_bounds__(THREADS) bucket_hist_kernel(const BucketLaunch
       const int j = g * G + fl;
       const bool active = j < a.Fsub;
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
-      if (direct) bucket_rows_impl<true, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 32 / G, r, st);
-      else bucket_rows_impl<false, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r, st);
+      uint32_t z_c = 0u; double z_s = 0.0, z_q = 0.0;
+      if (direct) bucket_rows_impl<true, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 32 / G, r, st, z_c, z_s, z_q);
+      else {
+        bucket_rows_impl<false, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r, st, z_c, z_s, z_q);
+        if (z_c) { atomicAdd(&scnt[fl], z_c); atomicAdd(&ssum[fl], z_s); atomicAdd(&ssq[fl], z_q); }
+      }
     } else {
       for (int j0 = 0; j0 < a.Fsub; j0 += 32) {
         const int j = j0 + lane;
         const bool active = j < a.Fsub;
         const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
-        if (direct) bucket_rows_impl<true, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 1, 0, st);
-        else bucket_rows_impl<false, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0, st);
+        uint32_t z_c = 0u; double z_s = 0.0, z_q = 0.0;
+        if (direct) bucket_rows_impl<true, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 1, 0, st, z_c, z_s, z_q);
+        else {
+          bucket_rows_impl<false, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0, st, z_c, z_s, z_q);
+          if (z_c) { atomicAdd(&scnt[e.y], z_c); atomicAdd(&ssum[e.y], z_s); atomicAdd(&ssq[e.y], z_q); }
+        }
       }
     }
     if (!direct) {
