@@ -339,6 +339,22 @@ int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t par
     return cuda_ok(cudaGetLastError(), "b2rf_bag") ? B2RF_OK : B2RF_ERR_CUDA;
   }
   int64_t* d_po = nullptr;
+  {   // keep the stream-ordered pool's memory across synchronisations: with the default release threshold (0) the driver returns
+      // the pool's backing memory to the OS at the next synchronize and maps it again on the next call
+    static std::mutex mu;
+    static bool tuned[64] = {false};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    std::lock_guard<std::mutex> g(mu);
+    if (dev >= 0 && dev < 64 && !tuned[dev]) {
+      cudaMemPool_t pool;
+      if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+        uint64_t keep = (uint64_t)64 << 20;
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+      }
+      tuned[dev] = true;
+    }
+  }
   if (!cuda_ok(cudaMallocAsync((void**)&d_po, (size_t)(P + 1) * 8, s), "b2rf_bag alloc")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpyAsync(d_po, h_part_offsets, (size_t)(P + 1) * 8, cudaMemcpyHostToDevice, s), "b2rf_bag copy")) return B2RF_ERR_CUDA;
   // exp(-rate) is evaluated once on the host so that every consumer of the stream compares against the same constant
