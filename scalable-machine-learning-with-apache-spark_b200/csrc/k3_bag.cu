@@ -245,10 +245,13 @@ __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed,
   int64_t ord = 0;                                   // samples emitted so far == ordRow * T + ordT (kept split: no 64-bit divisions)
   int64_t ordRow = 0; uint32_t ordT = 0;
   double rc = 1.0; long nc = 0;                      // the sample that is in progress across windows
+  const bool wideT = T > 32;                         // then ordT + k < 2 T: one conditional subtraction replaces the division
   auto emit = [&](uint32_t k, long n) {              // sample number ord + k (k <= 32)
     const uint32_t tt = ordT + k;
-    const int64_t row = r0 + ordRow + (int64_t)(tt / (uint32_t)T);
-    const uint32_t t = tt % (uint32_t)T;
+    uint32_t q, t;
+    if (wideT) { q = tt >= (uint32_t)T ? 1u : 0u; t = tt - q * (uint32_t)T; }
+    else { q = tt / (uint32_t)T; t = tt - q * (uint32_t)T; }
+    const int64_t row = r0 + ordRow + (int64_t)q;
     const int c = n > 255 ? 255 : (int)n;
     w[(size_t)t * ldw + row] = (uint8_t)c;
     if (node != nullptr) node[(size_t)t * ldn + row] = c > 0 ? 0 : -1;
@@ -303,7 +306,9 @@ __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed,
       }
       const uint32_t done = 1u + (uint32_t)__popc(marks);
       ord += done;
-      ordT += done; ordRow += ordT / (uint32_t)T; ordT %= (uint32_t)T;
+      ordT += done;
+      if (wideT) { if (ordT >= (uint32_t)T) { ordT -= (uint32_t)T; ordRow++; } }     // done <= 33 <= T
+      else { ordRow += ordT / (uint32_t)T; ordT %= (uint32_t)T; }
       // the sample left open at the window's end (if any) continues in the next window
       const double cr = __shfl_sync(FULL, myr, carry_pos < 0 ? 0 : carry_pos);
       if (carry_pos >= 0) { rc = cr; nc = 32 - carry_pos; } else { rc = 1.0; nc = 0; }
