@@ -189,7 +189,9 @@ __device__ __forceinline__ uint32_t well_batch32(uint32_t* v, int& index, uint32
   for (int st = 0; st < 5; st++) {
     const int o = 1 << st;
     const uint32_t y = __shfl_up_sync(0xffffffffu, b, o);
-    if (lane >= o) b ^= well_apply(tabs + st * 1024, y);
+    // M and M^2 are a handful of shifts and xors; from M^4 on the byte tables are cheaper
+    const uint32_t my = st == 0 ? well_M(y) : (st == 1 ? well_M(well_M(y)) : well_apply(tabs + st * 1024, y));
+    if (lane >= o) b ^= my;
   }
   // b == x_{k+1} == z4 of step k
   uint32_t x = __shfl_up_sync(0xffffffffu, b, 1);
