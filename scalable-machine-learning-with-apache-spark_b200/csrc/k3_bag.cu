@@ -170,9 +170,8 @@ __device__ __forceinline__ uint32_t well_apply(const uint32_t* tab /* [4][256] *
   return tab[y & 255u] ^ tab[256 + ((y >> 8) & 255u)] ^ tab[512 + ((y >> 16) & 255u)] ^ tab[768 + (y >> 24)];
 }
 
-// 32 generator steps; returns this lane's tempered 32-bit output (step `lane`), updates ring, index and the carried word.
-__device__ __forceinline__ uint32_t well_batch32(uint32_t* v, int& index, uint32_t& c0, const uint32_t* tabs, int lane) {
-  int i = index - lane; if (i < 0) i += 624;
+// d_k of the step that reads ring index i (see the header comment), and its a_k / z2_k for the ring write-back
+__device__ __forceinline__ uint32_t well_d(const uint32_t* v, int i, uint32_t& a, uint32_t& z2) {
   int i1 = i + 70;  if (i1 >= 624) i1 -= 624;
   int i2 = i + 179; if (i2 >= 624) i2 -= 624;
   int i3 = i + 449; if (i3 >= 624) i3 -= 624;
@@ -180,40 +179,57 @@ __device__ __forceinline__ uint32_t well_batch32(uint32_t* v, int& index, uint32
   int r2 = i - 2;   if (r2 < 0) r2 += 624;
   const uint32_t vM1 = v[i1], vM2 = v[i2], vM3 = v[i3];
   const uint32_t z0 = (0x80000000u & v[r1]) ^ (0x7FFFFFFFu & v[r2]);
-  const uint32_t a = vM1 ^ (vM1 >> 27);
-  const uint32_t z2 = (vM2 >> 9) ^ (vM3 ^ (vM3 >> 1));
+  a = vM1 ^ (vM1 >> 27);
+  z2 = (vM2 >> 9) ^ (vM3 ^ (vM3 >> 1));
   const uint32_t la = (a << 9) ^ (a >> 21);
-  uint32_t b = la ^ z0 ^ (z2 << 21) ^ (z2 >> 21);          // d_k
-  if (lane == 0) b ^= well_M(c0);                           // fold the carried word into the first element
-#pragma unroll
-  for (int st = 0; st < 5; st++) {
-    const int o = 1 << st;
-    const uint32_t y = __shfl_up_sync(0xffffffffu, b, o);
-    // M and M^2 are a handful of shifts and xors; from M^4 on the byte tables are cheaper
-    const uint32_t my = st == 0 ? well_M(y) : (st == 1 ? well_M(well_M(y)) : well_apply(tabs + st * 1024, y));
-    if (lane >= o) b ^= my;
-  }
-  // b == x_{k+1} == z4 of step k
-  uint32_t x = __shfl_up_sync(0xffffffffu, b, 1);
-  if (lane == 0) x = c0;
-  const uint32_t z1 = (x ^ (x << 25)) ^ a;
-  __syncwarp();
-  v[i] = z1 ^ z2;                                            // z3; the other two words a step writes are dead (see Well19937cSm)
-  __syncwarp();
-  c0 = __shfl_sync(0xffffffffu, b, 31);
-  index -= 32; if (index < 0) index += 624;
-  uint32_t z4 = b;
+  return la ^ z0 ^ (z2 << 21) ^ (z2 >> 21);
+}
+__device__ __forceinline__ uint32_t well_temper(uint32_t z4) {
   z4 ^= (z4 << 7) & 0xe46e1700u;
   z4 ^= (z4 << 15) & 0x9b868000u;
   return z4;
 }
 
+// 64 generator steps at once: lane l owns steps 2l and 2l+1.  With X_k the word step k reads (X_0 = carried word) and
+// x_{k+1} = M X_k ^ d_k, the pair is the affine map X_{2l+2} = M^2 X_{2l} ^ (M d_{2l} ^ d_{2l+1}); one 32-lane scan over the pairs
+// (powers M^2, M^4, ..., M^32) gives every X_{2l+2}, and X_{2l+1} = M X_{2l} ^ d_{2l} follows locally.  None of the ring words a step
+// reads is written inside the same 64 steps (offsets 70 / 179 / 449 ahead; i-1 and i-2 are still the old revolution).
+// Returns the tempered outputs of steps 2l (hi) and 2l+1 (lo) — exactly the two next(26) calls of one nextDouble().
+__device__ __forceinline__ void well_batch64(uint32_t* v, int& index, uint32_t& c0, const uint32_t* tabs, int lane, uint32_t& out_a, uint32_t& out_b) {
+  int ia = index - 2 * lane; if (ia < 0) ia += 624;
+  int ib = ia - 1;           if (ib < 0) ib += 624;
+  uint32_t aa, z2a, ab, z2b;
+  const uint32_t da = well_d(v, ia, aa, z2a);
+  const uint32_t db = well_d(v, ib, ab, z2b);
+  uint32_t e = well_M(da) ^ db;
+  if (lane == 0) e ^= well_M(well_M(c0));
+#pragma unroll
+  for (int st = 0; st < 5; st++) {
+    const int o = 1 << st;
+    const uint32_t y = __shfl_up_sync(0xffffffffu, e, o);
+    // (M^2)^(2^st) = M^(2^(st+1)): M^2 and M^4 by shifts and xors, M^8 / M^16 / M^32 by byte tables
+    const uint32_t my = st == 0 ? well_M(well_M(y)) : (st == 1 ? well_M(well_M(well_M(well_M(y)))) : well_apply(tabs + (st + 1) * 1024, y));
+    if (lane >= o) e ^= my;
+  }
+  uint32_t xa = __shfl_up_sync(0xffffffffu, e, 1);         // X_{2l}
+  if (lane == 0) xa = c0;
+  const uint32_t xb = well_M(xa) ^ da;                     // X_{2l+1} == z4 of step 2l
+  __syncwarp();
+  v[ia] = ((xa ^ (xa << 25)) ^ aa) ^ z2a;                  // z3 of each step; the other two words a step writes are dead
+  v[ib] = ((xb ^ (xb << 25)) ^ ab) ^ z2b;
+  __syncwarp();
+  c0 = __shfl_sync(0xffffffffu, e, 31);
+  index -= 64; if (index < 0) index += 624;
+  out_a = well_temper(xb);
+  out_b = well_temper(e);
+}
+
 __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed, const int64_t* part_offsets, int P, int part0, int T, double rate,
                                                                    double expNegRate, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
-  __shared__ uint32_t tabs[5 * 1024];              // M^(2^s), s = 0..4, as 4 x 256 byte tables
+  __shared__ uint32_t tabs[6 * 1024];              // M^(2^s), s = 0..5, as 4 x 256 byte tables
   __shared__ BagWarpSmem sm_all[BAGW_WARPS];
   // tables: entry (s, byte, val) = M^(2^s)(val << 8*byte)
-  for (int e = threadIdx.x; e < 5 * 1024; e += blockDim.x) {
+  for (int e = threadIdx.x; e < 6 * 1024; e += blockDim.x) {
     const int st = e >> 10, byte = (e >> 8) & 3, val = e & 255;
     uint32_t x = (uint32_t)val << (8 * byte);
     for (int r = 0; r < (1 << st); r++) x = well_M(x);
@@ -260,16 +276,24 @@ __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed,
   };
   while (ord < total) {
     // ---- 64 generator steps -> 32 uniforms (BitsStreamGenerator.nextDouble: two 26-bit halves) ----
-#pragma unroll
-    for (int half = 0; half < 2; half++) {
-      const uint32_t out = well_batch32(sm.v, index, c0, tabs, lane) >> 6;
-      const uint32_t hi = __shfl_sync(FULL, out, (2 * lane) & 31), lo = __shfl_sync(FULL, out, (2 * lane + 1) & 31);
-      if (lane < 16) sm.u[half * 16 + lane] = (double)(((int64_t)hi << 26) | (int64_t)lo) * 0x1.0p-52;
+    {
+      uint32_t oa, ob;
+      well_batch64(sm.v, index, c0, tabs, lane, oa, ob);
+      sm.u[lane] = (double)(((int64_t)(oa >> 6) << 26) | (int64_t)(ob >> 6)) * 0x1.0p-52;
     }
     __syncwarp();
     // ---- every lane: the sample that would START at uniform `lane` (r = 1; r *= u; ends when r < p) ----
     uint32_t mylen = 0; double myr = 1.0;            // mylen == 0: runs past the window (myr = product so far)
-    for (int k = lane; k < 32; k++) { myr *= sm.u[k]; if (!(myr >= expNegRate)) { mylen = (uint32_t)(k - lane + 1); break; } }
+    {   // the first four uniforms of the chain are loaded together (most samples end within them); same products, same order
+      double uu[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) uu[j] = sm.u[min(lane + j, 31)];
+#pragma unroll
+      for (int j = 0; j < 4; j++)
+        if (mylen == 0u && lane + j < 32) { myr *= uu[j]; if (!(myr >= expNegRate)) mylen = (uint32_t)(j + 1); }
+      if (mylen == 0u)
+        for (int k = lane + 4; k < 32; k++) { myr *= sm.u[k]; if (!(myr >= expNegRate)) { mylen = (uint32_t)(k - lane + 1); break; } }
+    }
     sm.len[lane] = mylen;
     __syncwarp();
     // ---- lane 0 finishes the carried-in sample; the start positions after it are found by pointer doubling ----
