@@ -175,6 +175,12 @@ int b2rf_forest_pack(int64_t n_nodes, const int32_t* d_feature, const double* d_
                      const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, void* d_packed, void* stream);
 int b2rf_predict_packed(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const void* d_packed,
                         const double* d_cats, double* d_out, int32_t* d_leaf, void* stream);
+/* K7 on bin codes (all-continuous forests): d_codes[n_rows][ldr] are the rows binned by b2rf_bin against the forest's OWN per-feature
+ * threshold tables (sorted distinct split thresholds; d_bins may be NULL in that b2rf_bin call, d_bins_rm receives the codes);
+ * d_nodes8[node] = { feature | split code << 16 (0xffff = leaf), right child }, pre-order numbering; leaf values from d_prediction.
+ * x <= threshold <=> code(x) <= split code, so the leaves and the sums equal b2rf_predict's. */
+int b2rf_predict_coded(const void* d_codes, int64_t ldr, int32_t code_bytes, int64_t n_rows, int32_t T, const int64_t* d_tree_off,
+                       const void* d_nodes8, const double* d_prediction, double* d_out, int32_t* d_leaf, void* stream);
 /* K7 for any numClasses >= 2: d_class_counts[node][numClasses] are the exported class counts; d_out[n_rows][numClasses]. */
 int b2rf_predict_raw_mc(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,
                         const double* d_threshold, const int32_t* d_left, const int32_t* d_right, const double* d_class_counts,

@@ -62,6 +62,7 @@ _SIGS = {
     "b2rf_forest_pack_bytes": (C.c_size_t, [i64]),
     "b2rf_forest_pack": (C.c_int, [i64] + [vp] * 9),
     "b2rf_predict_packed": (C.c_int, [vp, i64, i64, i32] + [vp] * 6),
+    "b2rf_predict_coded": (C.c_int, [vp, i64, i32, i64, i32] + [vp] * 6),
     "b2rf_predict_raw_mc": (C.c_int, [vp, i64, i64, i32] + [vp] * 6 + [i32] + [vp] * 4 + [i32, vp, vp]),
     "b2rf_trainer_num_classes": (C.c_int, [vp]),
     "b2rf_trainer_export_class_counts": (C.c_int, [vp, vp]),

@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, 
     if (bins_rm != nullptr && row < n_rows && fl < nf) bins_rm[(size_t)(row0 + row) * ldr + f0 + fl] = b;   // row-major twin for gathers
   }
   __syncthreads();
+  if (bins == nullptr) return;     // row-major codes only (K7 on bin codes)
   // coalesced column-major stores: 32-bit words
   constexpr int PER = 4 / (int)sizeof(CodeT);   // codes per word
   const int words = nf * (BIN_RT / PER);

@@ -122,6 +122,62 @@ __global__ void __launch_bounds__(256) predict_packed_kernel(const double* __res
   if (out != nullptr) out[i] = acc / (double)T;
 }
 
+// ---- traversal on bin codes ---------------------------------------------------------------------------------------------
+// For a forest whose splits are all continuous, `x <= threshold` only asks how many of the forest's own thresholds of that feature
+// lie strictly below x: with tab[f] the sorted distinct thresholds the forest uses on feature f and code(x) = #{t in tab[f] : t < x}
+// (what K2 computes), x <= tab[f][c] <=> code(x) <= c.  Rows shrink from 8 bytes per feature to one code, so a block's rows stay in
+// L1 while every tree is walked, and a node is 8 bytes: (feature | split code << 16, right child); leaves are feature 0xffff and take
+// their value from the prediction array.  Exactly the same leaves as the f64 traversal, so the same sums.
+struct __align__(8) CodedNode { uint32_t fc; int32_t right; };
+
+template <typename CodeT, bool LEAVES>
+__global__ void __launch_bounds__(256) predict_coded_kernel(const CodeT* __restrict__ codes, int64_t ldr, int64_t n_rows, int T, const int64_t* __restrict__ tree_off,
+                                                            const CodedNode* __restrict__ nodes, const double* __restrict__ prediction, double* out,
+                                                            int32_t* leaf_out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_rows) return;
+  const CodeT* x = codes + (size_t)i * ldr;
+  double acc = 0.0;
+  for (int t0 = 0; t0 < T; t0 += TREES_IN_FLIGHT) {
+    int64_t base[TREES_IN_FLIGHT];
+    int n[TREES_IN_FLIGHT];
+    CodedNode cur[TREES_IN_FLIGHT];
+    bool live[TREES_IN_FLIGHT];
+    bool any = false;
+#pragma unroll
+    for (int k = 0; k < TREES_IN_FLIGHT; k++) {
+      live[k] = t0 + k < T;
+      base[k] = live[k] ? tree_off[t0 + k] : 0;
+      n[k] = 0;
+      if (live[k]) { cur[k] = nodes[base[k]]; live[k] = (cur[k].fc & 0xffffu) != 0xffffu; }
+      else { cur[k].fc = 0xffffu; cur[k].right = -1; }
+      any |= live[k];
+    }
+    while (any) {
+      uint32_t c[TREES_IN_FLIGHT];
+#pragma unroll
+      for (int k = 0; k < TREES_IN_FLIGHT; k++) c[k] = live[k] ? (uint32_t)x[cur[k].fc & 0xffffu] : 0u;
+      any = false;
+#pragma unroll
+      for (int k = 0; k < TREES_IN_FLIGHT; k++) {
+        if (!live[k]) continue;
+        n[k] = c[k] <= (cur[k].fc >> 16) ? n[k] + 1 : cur[k].right;
+        cur[k] = nodes[base[k] + n[k]];
+        live[k] = (cur[k].fc & 0xffffu) != 0xffffu;
+        any |= live[k];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < TREES_IN_FLIGHT; k++) {
+      if (t0 + k < T) {
+        acc += prediction[base[k] + n[k]];
+        if (LEAVES) leaf_out[(size_t)i * T + t0 + k] = n[k];
+      }
+    }
+  }
+  if (out != nullptr) out[i] = acc / (double)T;
+}
+
 // Classification rawPrediction (numClasses == 2).  stats4[node] = (sum w, sum w*y, ., .): class counts (c0, c1) = (stats[0] - stats[1], stats[1]).
 // mode 0: RandomForestClassificationModel.predictRaw — votes(k) += classCounts(k) / total for every tree, in tree order;
 // mode 1: DecisionTreeClassificationModel.predictRaw — the class counts of tree 0's leaf.
@@ -194,6 +250,24 @@ int b2rf_predict_packed(const double* d_X, int64_t ldx, int64_t n_rows, int32_t 
   if (d_leaf) predict_packed_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, (const PackedNode*)d_packed, d_cats, d_out, d_leaf);
   else predict_packed_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, (const PackedNode*)d_packed, d_cats, d_out, d_leaf);
   return cuda_ok(cudaGetLastError(), "b2rf_predict_packed") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+int b2rf_predict_coded(const void* d_codes, int64_t ldr, int32_t code_bytes, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const void* d_nodes8,
+                       const double* d_prediction, double* d_out, int32_t* d_leaf, void* stream) {
+  if (code_bytes != 1 && code_bytes != 2) { set_error("b2rf_predict_coded: code_bytes must be 1 or 2"); return B2RF_ERR_ARG; }
+  if (!d_out && !d_leaf) { set_error("b2rf_predict_coded: neither d_out nor d_leaf given"); return B2RF_ERR_ARG; }
+  if (n_rows <= 0) return B2RF_OK;
+  const unsigned grid = (unsigned)((n_rows + 255) / 256);
+  cudaStream_t s = (cudaStream_t)stream;
+  const CodedNode* nd = (const CodedNode*)d_nodes8;
+  if (code_bytes == 1) {
+    if (d_leaf) predict_coded_kernel<uint8_t, true><<<grid, 256, 0, s>>>((const uint8_t*)d_codes, ldr, n_rows, T, d_tree_off, nd, d_prediction, d_out, d_leaf);
+    else predict_coded_kernel<uint8_t, false><<<grid, 256, 0, s>>>((const uint8_t*)d_codes, ldr, n_rows, T, d_tree_off, nd, d_prediction, d_out, d_leaf);
+  } else {
+    if (d_leaf) predict_coded_kernel<uint16_t, true><<<grid, 256, 0, s>>>((const uint16_t*)d_codes, ldr, n_rows, T, d_tree_off, nd, d_prediction, d_out, d_leaf);
+    else predict_coded_kernel<uint16_t, false><<<grid, 256, 0, s>>>((const uint16_t*)d_codes, ldr, n_rows, T, d_tree_off, nd, d_prediction, d_out, d_leaf);
+  }
+  return cuda_ok(cudaGetLastError(), "b2rf_predict_coded") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
 int b2rf_predict_raw(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const int32_t* d_feature,

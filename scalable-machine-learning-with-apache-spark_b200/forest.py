@@ -212,6 +212,62 @@ class Forest:
                                             C.c_void_p(st)))
         return out, leaves
 
+    # ---- K7 on bin codes (all-continuous forests) ----
+    def _coded(self, device):
+        """Per-feature tables of the forest's own split thresholds, the nodes' split codes, and the 8-byte node records of
+        b2rf_predict_coded; None when the forest has categorical splits, is not in pre-order or is too small to bother."""
+        import torch
+        key = "coded:" + str(device)
+        if key in self._dev:
+            return self._dev[key]
+        res = None
+        internal = self.feature >= 0
+        if self.is_preorder() and not (self.ncat[internal] > 0).any() and internal.any() and self.num_features < 0xffff:
+            F = self.num_features
+            feats, thr = self.feature[internal], self.threshold[internal]
+            tabs = [np.unique(thr[feats == f]) for f in range(F)]
+            L = max(1, max(len(t) for t in tabs))
+            if L <= 65534:
+                table = np.full((F, L), np.inf)
+                for f, t in enumerate(tabs):
+                    table[f, :len(t)] = t
+                ns = np.array([len(t) for t in tabs], np.int32)
+                code = np.zeros(len(self.feature), np.int64)
+                for f in range(F):
+                    m = internal & (self.feature == f)
+                    if m.any():
+                        code[m] = np.searchsorted(tabs[f], self.threshold[m])
+                fc = np.where(internal, self.feature.astype(np.int64) | (code << 16), 0xffff).astype(np.uint32)
+                rec = np.stack([fc.view(np.int32), np.where(internal, self.right, -1).astype(np.int32)], axis=1)
+                res = dict(table=torch.as_tensor(table).to(device), ns=torch.as_tensor(ns).to(device),
+                           arity=torch.zeros(F, dtype=torch.int32, device=device), nodes=torch.as_tensor(np.ascontiguousarray(rec)).to(device),
+                           code_dt=torch.uint8 if L <= 255 else torch.int16, L=L)
+        self._dev[key] = res
+        return res
+
+    def _predict_coded(self, X, want_pred: bool, want_leaves: bool, chunk_rows: int = 1 << 22):
+        """Bins X against the forest's threshold tables (K2) chunk by chunk, then walks the 8-byte nodes (K7 on codes)."""
+        import torch
+        from ._lib import check, lib
+        from .trainer import bin_features, _pad
+        cd = self._coded(X.device)
+        d = self._device_arrays(X.device)
+        n, F = X.shape
+        out = torch.empty(n, dtype=torch.float64, device=X.device) if want_pred else None
+        leaves = torch.empty((n, self.num_trees), dtype=torch.int32, device=X.device) if want_leaves else None
+        rows = min(n, chunk_rows)
+        codes = torch.empty((rows, _pad(F, 16)), dtype=cd["code_dt"], device=X.device)
+        with torch.cuda.device(X.device):
+            st = torch.cuda.current_stream().cuda_stream
+            for r0 in range(0, n, rows):
+                m = min(rows, n - r0)
+                check(lib().b2rf_bin(X[r0:r0 + m].data_ptr(), X.stride(0), m, F, cd["table"].data_ptr(), cd["ns"].data_ptr(), cd["arity"].data_ptr(),
+                                     cd["L"], 0, 0, 0, 0, codes.data_ptr(), codes.stride(0), codes.element_size(), C.c_void_p(st)))
+                check(lib().b2rf_predict_coded(codes.data_ptr(), codes.stride(0), codes.element_size(), m, self.num_trees, d["tree_off"].data_ptr(),
+                                               cd["nodes"].data_ptr(), d["prediction"].data_ptr(), 0 if out is None else out[r0:].data_ptr(),
+                                               0 if leaves is None else leaves[r0:].data_ptr(), C.c_void_p(st)))
+        return out, leaves
+
     def predict_leaves(self, X):
         """Tree-local node index of the leaf every row reaches in every tree: torch.int32 [n, T] (K7, packed form)."""
         import torch
@@ -244,6 +300,8 @@ class Forest:
                 best = torch.where(m, raw[:, k], best)
             return idx
         X = X.to(torch.float64).contiguous()
+        if X.shape[0] >= 4096 and self._coded(X.device) is not None:     # large batches of an all-continuous forest: walk bin codes
+            return self._predict_coded(X, True, False)[0]
         if self.is_preorder():
             return self._predict_packed(X, True, False)[0]
         d = self._device_arrays(X.device)

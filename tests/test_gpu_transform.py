@@ -87,3 +87,31 @@ def test_leaf_and_variance_columns(b2rf, oracle, cuda):
     assert got.shape == (1000, 5) and np.array_equal(got, ranks)
     with pytest.raises(NotImplementedError, match="weightCol"):
         sp.B200DecisionTreeRegressor(labelCol="price", weightCol="w").fit(train)
+
+
+def test_coded_traversal_equals_f64_traversal(b2rf, cuda):
+    """K7 on bin codes (all-continuous forests, large batches) reaches the same leaves as the f64 traversal: identical leaf indices and
+    bit-identical predictions, for uint8 codes and, with more than 255 distinct thresholds on a feature, uint16 codes."""
+    X, y, arity = b2rf.synth.c3(60000, device=cuda, F=16)
+    for maxBins, depth, T, want_dt in [(64, 8, 9, torch.uint8), (1000, 12, 3, torch.int16)]:
+        p = b2rf.TreeParams(maxDepth=depth, maxBins=maxBins, numTrees=T, bootstrap=True, seed=5)
+        f = b2rf.trainer.fit_tensors(X[:30000], y[:30000], arity, p)
+        cd = f._coded(cuda)
+        assert cd is not None and cd["code_dt"] == want_dt
+        a, la = f._predict_packed(X, True, True)
+        b, lb = f._predict_coded(X, True, True, chunk_rows=25000)        # three chunks, the last one ragged
+        assert torch.equal(la, lb)
+        assert torch.equal(a, b)
+        assert torch.equal(f.predict(X), a)                                # the public entry takes the coded path for this batch size
+        edge = X[:5000].clone()
+        thr = torch.as_tensor(f.threshold[f.feature >= 0][:16], device=cuda)
+        edge[:16, int(f.feature[0])] = thr[0]                              # values exactly on a threshold go left in both forms
+        assert torch.equal(f._predict_packed(edge, True, False)[0], f._predict_coded(edge, True, False)[0])
+
+
+def test_coded_traversal_not_used_with_categorical_splits(b2rf, oracle, cuda):
+    X, y, arity = b2rf.synth.airbnb(6000)
+    o = oracle.fit(X.numpy()[:3000], y.numpy()[:3000], arity, maxDepth=5, maxBins=40)
+    fo = _forest(b2rf, o, 33)
+    assert (fo.ncat > 0).any() and fo._coded(cuda) is None
+    np.testing.assert_array_equal(fo.predict(X.to(cuda)).cpu().numpy(), o.predict(X.numpy()))
