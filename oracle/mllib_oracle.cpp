@@ -299,7 +299,8 @@ void find_splits_feature(const double* vals, int64_t n, int64_t stride_elems, in
 
 // A.3 TreePoint.findBin
 inline int find_bin(double x, const double* thr, int nthr) {
-  // number of thresholds < x  (java.util.Arrays.binarySearch semantics: x == t_k -> k)
+  // number of thresholds < x  (java.util.Arrays.binarySearch semantics: x == t_k -> k; NaN orders above every double -> last bin)
+  if (x != x) return nthr;
   int lo = 0, hi = nthr;
   while (lo < hi) { int mid = (lo + hi) >> 1; if (thr[mid] < x) lo = mid + 1; else hi = mid; }
   return lo;

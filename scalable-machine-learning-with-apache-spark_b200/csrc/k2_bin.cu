@@ -48,6 +48,7 @@ __global__ void __launch_bounds__(256) bin_kernel(const double* X, int64_t ldx, 
         const double* t = thr + fl * maxSplits;
         int lo = 0, hi = nsplits[f];
         while (lo < hi) { const int mid = (lo + hi) >> 1; if (t[mid] < x) lo = mid + 1; else hi = mid; }
+        if (x != x) lo = nsplits[f];     // Arrays.binarySearch orders NaN above every double: last bin (and `NaN <= t` is false at predict time)
         b = (CodeT)lo;
       } else {
         if (x < 0 || x >= (double)ar) atomicMax(err, f + 1);

@@ -115,3 +115,20 @@ def test_coded_traversal_not_used_with_categorical_splits(b2rf, oracle, cuda):
     fo = _forest(b2rf, o, 33)
     assert (fo.ncat > 0).any() and fo._coded(cuda) is None
     np.testing.assert_array_equal(fo.predict(X.to(cuda)).cpu().numpy(), o.predict(X.numpy()))
+
+
+def test_nan_features_take_the_last_bin_and_go_right(b2rf, oracle, cuda):
+    """TreePoint.findBin uses java.util.Arrays.binarySearch, which orders NaN above every double: a NaN feature lands in the last bin;
+    at predict time `NaN <= threshold` is false, so both K7 forms send it right."""
+    X = np.array([[0.0], [1.0], [2.0], [3.0], [np.nan]]); arity = [0]
+    thr, ns = oracle.find_splits(X[:4], arity, 32, 4.0)
+    want = np.asarray(oracle.bin_features(X, thr, ns, arity)).reshape(-1)
+    assert want[-1] == ns[0]
+    tr = b2rf.trainer
+    got = tr.bin_features(torch.as_tensor(X, device=cuda), torch.as_tensor(thr, device=cuda), torch.as_tensor(ns, device=cuda),
+                          torch.as_tensor(np.asarray(arity, np.int32), device=cuda))
+    assert got[0, :5].cpu().numpy().tolist() == want.tolist()
+    Xc, yc, ar = b2rf.synth.c3(20000, device=cuda, F=8)
+    f = tr.fit_tensors(Xc, yc, ar, b2rf.TreeParams(maxDepth=5, maxBins=32, numTrees=3, bootstrap=True, seed=1))
+    Xn = Xc.clone(); Xn[::7, 3] = float("nan"); Xn[::11, 0] = float("nan")
+    assert torch.equal(f._predict_packed(Xn, True, False)[0], f._predict_coded(Xn, True, False)[0])
