@@ -171,10 +171,13 @@ int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, cons
  * next node); the caller checks that and otherwise stays on b2rf_predict.  d_out[n_rows] (mean over trees, tree-order sum) and
  * d_leaf[n_rows][T] (tree-local index of the leaf each row reaches: leafCol / varianceCol) are each optional, not both NULL. */
 size_t b2rf_forest_pack_bytes(int64_t n_nodes);
+/* d_mask_idx (optional): for categorical nodes the row of d_masks that holds the node's left categories as a bit mask; with it
+ * b2rf_predict_packed tests membership with one bit test (pass the same d_masks / maskWords there), without it it scans d_cats. */
 int b2rf_forest_pack(int64_t n_nodes, const int32_t* d_feature, const double* d_threshold, const int32_t* d_right, const double* d_prediction,
-                     const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, void* d_packed, void* stream);
+                     const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, const int32_t* d_mask_idx, void* d_packed,
+                     void* stream);
 int b2rf_predict_packed(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const void* d_packed,
-                        const double* d_cats, double* d_out, int32_t* d_leaf, void* stream);
+                        const double* d_cats, const uint32_t* d_masks, int32_t maskWords, double* d_out, int32_t* d_leaf, void* stream);
 /* K7 on bin codes (all-continuous forests): d_codes[n_rows][ldr] are the rows binned by b2rf_bin against the forest's OWN per-feature
  * threshold tables (sorted distinct split thresholds; d_bins may be NULL in that b2rf_bin call, d_bins_rm receives the codes);
  * d_nodes8[node] = { feature | split code << 16 (0xffff = leaf), right child }, pre-order numbering; leaf values from d_prediction.

@@ -60,8 +60,8 @@ _SIGS = {
     "b2rf_hist_build": (C.c_int, [vp, i64, i32, i32, vp, vp, i64, vp, i64, vp, i32, i64, vp, vp, i32, vp, vp]),
     "b2rf_predict": (C.c_int, [vp, i64, i64, i32] + [vp] * 12),
     "b2rf_forest_pack_bytes": (C.c_size_t, [i64]),
-    "b2rf_forest_pack": (C.c_int, [i64] + [vp] * 9),
-    "b2rf_predict_packed": (C.c_int, [vp, i64, i64, i32] + [vp] * 6),
+    "b2rf_forest_pack": (C.c_int, [i64] + [vp] * 10),
+    "b2rf_predict_packed": (C.c_int, [vp, i64, i64, i32] + [vp] * 4 + [i32] + [vp] * 3),
     "b2rf_predict_coded": (C.c_int, [vp, i64, i32, i64, i32] + [vp] * 6),
     "b2rf_predict_raw_mc": (C.c_int, [vp, i64, i64, i32] + [vp] * 6 + [i32] + [vp] * 4 + [i32, vp, vp]),
     "b2rf_trainer_num_classes": (C.c_int, [vp]),

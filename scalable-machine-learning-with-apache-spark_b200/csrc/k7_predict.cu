@@ -53,13 +53,14 @@ __global__ void predict_kernel(const double* X, int64_t ldx, int64_t n_rows, int
 struct __align__(16) PackedNode { double v; int32_t feat; int32_t right; };
 
 __global__ void pack_forest_kernel(int64_t n_nodes, const int32_t* feature, const double* threshold, const int32_t* right, const double* prediction,
-                                   const int32_t* ncat, const int32_t* cat_off, const int32_t* cat_len, PackedNode* out) {
+                                   const int32_t* ncat, const int32_t* cat_off, const int32_t* cat_len, const int32_t* mask_idx, PackedNode* out) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_nodes) return;
   PackedNode p;
   const int f = feature[i];
   if (f < 0) { p.v = prediction[i]; p.feat = -1; p.right = -1; }
   else if (ncat[i] == 0) { p.v = threshold[i]; p.feat = f; p.right = right[i]; }
+  else if (mask_idx != nullptr) { p.v = __hiloint2double(ncat[i], mask_idx[i]); p.feat = -2 - f; p.right = right[i]; }   // (arity, bit-mask index)
   else { p.v = __hiloint2double(cat_len[i], cat_off[i]); p.feat = -2 - f; p.right = right[i]; }
   out[i] = p;
 }
@@ -67,7 +68,8 @@ __global__ void pack_forest_kernel(int64_t n_nodes, const int32_t* feature, cons
 constexpr int TREES_IN_FLIGHT = 4;
 template <bool LEAVES>
 __global__ void __launch_bounds__(256) predict_packed_kernel(const double* __restrict__ X, int64_t ldx, int64_t n_rows, int T, const int64_t* __restrict__ tree_off,
-                                                             const PackedNode* __restrict__ nodes, const double* __restrict__ cats, double* out, int32_t* leaf_out) {
+                                                             const PackedNode* __restrict__ nodes, const double* __restrict__ cats, double* out, int32_t* leaf_out,
+                                                             const uint32_t* __restrict__ masks, int maskWords) {
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_rows) return;
   const double* x = X + (size_t)i * ldx;
@@ -103,7 +105,12 @@ __global__ void __launch_bounds__(256) predict_packed_kernel(const double* __res
         else {
           const int co = __double2loint(cur[k].v), cl = __double2hiint(cur[k].v);
           l = false;
-          for (int c = 0; c < cl; c++) if (cats[co + c] == xv[k]) { l = true; break; }
+          if (masks != nullptr) {      // (bit-mask index, arity): categories.contains(x) as one bit test; non-integral or out-of-range x -> right
+            const int xi = (int)xv[k];
+            if (xv[k] == (double)xi && xi >= 0 && xi < cl) l = (masks[(size_t)co * maskWords + (xi >> 5)] >> (xi & 31)) & 1u;
+          } else {
+            for (int c = 0; c < cl; c++) if (cats[co + c] == xv[k]) { l = true; break; }
+          }
         }
         n[k] = l ? n[k] + 1 : cur[k].right;
         cur[k] = base[k][n[k]];
@@ -234,21 +241,22 @@ int b2rf_predict(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, cons
 size_t b2rf_forest_pack_bytes(int64_t n_nodes) { return (size_t)(n_nodes > 0 ? n_nodes : 0) * sizeof(PackedNode); }
 
 int b2rf_forest_pack(int64_t n_nodes, const int32_t* d_feature, const double* d_threshold, const int32_t* d_right, const double* d_prediction,
-                     const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, void* d_packed, void* stream) {
+                     const int32_t* d_ncat, const int32_t* d_cat_off, const int32_t* d_cat_len, const int32_t* d_mask_idx, void* d_packed, void* stream) {
   if (n_nodes <= 0) return B2RF_OK;
   if (!d_packed) { set_error("b2rf_forest_pack: no output buffer"); return B2RF_ERR_ARG; }
   pack_forest_kernel<<<(unsigned)((n_nodes + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n_nodes, d_feature, d_threshold, d_right, d_prediction, d_ncat,
-                                                                                         d_cat_off, d_cat_len, (PackedNode*)d_packed);
+                                                                                         d_cat_off, d_cat_len, d_mask_idx, (PackedNode*)d_packed);
   return cuda_ok(cudaGetLastError(), "b2rf_forest_pack") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
 int b2rf_predict_packed(const double* d_X, int64_t ldx, int64_t n_rows, int32_t T, const int64_t* d_tree_off, const void* d_packed,
-                        const double* d_cats, double* d_out, int32_t* d_leaf, void* stream) {
+                        const double* d_cats, const uint32_t* d_masks, int32_t maskWords, double* d_out, int32_t* d_leaf, void* stream) {
   if (n_rows <= 0) return B2RF_OK;
   if (!d_out && !d_leaf) { set_error("b2rf_predict_packed: neither d_out nor d_leaf given"); return B2RF_ERR_ARG; }
+  if (d_masks && maskWords <= 0) { set_error("b2rf_predict_packed: maskWords must be positive with d_masks"); return B2RF_ERR_ARG; }
   const unsigned grid = (unsigned)((n_rows + 255) / 256);
-  if (d_leaf) predict_packed_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, (const PackedNode*)d_packed, d_cats, d_out, d_leaf);
-  else predict_packed_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, (const PackedNode*)d_packed, d_cats, d_out, d_leaf);
+  if (d_leaf) predict_packed_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, (const PackedNode*)d_packed, d_cats, d_out, d_leaf, d_masks, maskWords);
+  else predict_packed_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, T, d_tree_off, (const PackedNode*)d_packed, d_cats, d_out, d_leaf, d_masks, maskWords);
   return cuda_ok(cudaGetLastError(), "b2rf_predict_packed") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 

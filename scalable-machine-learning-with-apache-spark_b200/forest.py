@@ -191,11 +191,28 @@ class Forest:
             d = self._device_arrays(device)
             n = len(self.feature)
             buf = torch.empty(max(int(lib().b2rf_forest_pack_bytes(n)), 16), dtype=torch.uint8, device=device)
+            # left-category sets of the categorical nodes as bit masks (one row per categorical node)
+            catn = np.nonzero((self.feature >= 0) & (self.ncat > 0))[0]
+            mw = max(1, (int(self.ncat.max()) + 31) // 32) if len(catn) else 1
+            masks = np.zeros((max(len(catn), 1), mw), np.uint32)
+            midx = np.full(n, -1, np.int32)
+            midx[catn] = np.arange(len(catn), dtype=np.int32)
+            if len(catn):
+                lens = self.cat_len[catn].astype(np.int64)
+                rows = np.repeat(np.arange(len(catn)), lens)
+                pos = np.repeat(self.cat_off[catn].astype(np.int64), lens) + (np.arange(lens.sum()) - np.repeat(np.cumsum(lens) - lens, lens))
+                c = self.cats[pos].astype(np.int64)
+                np.bitwise_or.at(masks, (rows, c >> 5), (np.uint32(1) << (c & 31).astype(np.uint32)))
+            masks_d = torch.as_tensor(masks.view(np.int32)).to(device)
+            midx_d = torch.as_tensor(midx).to(device)
             with torch.cuda.device(device):
                 st = torch.cuda.current_stream().cuda_stream
                 check(lib().b2rf_forest_pack(n, d["feature"].data_ptr(), d["threshold"].data_ptr(), d["right"].data_ptr(), d["prediction"].data_ptr(),
-                                             d["ncat"].data_ptr(), d["cat_off"].data_ptr(), d["cat_len"].data_ptr(), buf.data_ptr(), C.c_void_p(st)))
+                                             d["ncat"].data_ptr(), d["cat_off"].data_ptr(), d["cat_len"].data_ptr(), midx_d.data_ptr(), buf.data_ptr(),
+                                             C.c_void_p(st)))
+                torch.cuda.current_stream().synchronize()      # midx_d is only needed by the pack kernel
             self._dev[key] = buf
+            self._dev["masks:" + str(device)] = (masks_d, mw)
         return self._dev[key]
 
     def _predict_packed(self, X, want_pred: bool, want_leaves: bool):
@@ -207,9 +224,10 @@ class Forest:
         leaves = torch.empty((X.shape[0], self.num_trees), dtype=torch.int32, device=X.device) if want_leaves else None
         with torch.cuda.device(X.device):
             st = torch.cuda.current_stream().cuda_stream
+            masks_d, mw = self._dev["masks:" + str(X.device)]
             check(lib().b2rf_predict_packed(X.data_ptr(), X.stride(0), X.shape[0], self.num_trees, d["tree_off"].data_ptr(), pk.data_ptr(),
-                                            d["cats"].data_ptr(), 0 if out is None else out.data_ptr(), 0 if leaves is None else leaves.data_ptr(),
-                                            C.c_void_p(st)))
+                                            d["cats"].data_ptr(), masks_d.data_ptr(), mw, 0 if out is None else out.data_ptr(),
+                                            0 if leaves is None else leaves.data_ptr(), C.c_void_p(st)))
         return out, leaves
 
     # ---- K7 on bin codes (all-continuous forests) ----

@@ -132,3 +132,20 @@ def test_nan_features_take_the_last_bin_and_go_right(b2rf, oracle, cuda):
     f = tr.fit_tensors(Xc, yc, ar, b2rf.TreeParams(maxDepth=5, maxBins=32, numTrees=3, bootstrap=True, seed=1))
     Xn = Xc.clone(); Xn[::7, 3] = float("nan"); Xn[::11, 0] = float("nan")
     assert torch.equal(f._predict_packed(Xn, True, False)[0], f._predict_coded(Xn, True, False)[0])
+
+
+def test_packed_categorical_bit_masks(b2rf, oracle, cuda):
+    """Categorical splits in the packed kernel are one bit test; values that are not a category (non-integral, negative, beyond the
+    arity) go right, as `categories.contains(x)` does."""
+    X, y, arity = b2rf.synth.airbnb(4000)
+    X, y = X.numpy(), y.numpy()
+    o = oracle.fit(X[:3000], y[:3000], arity, maxDepth=7, maxBins=40, numTrees=5, bootstrap=True, seed=2)
+    fo = _forest(b2rf, o, 33)
+    assert (fo.ncat > 0).sum() > 10
+    Xt = X[3000:].copy()
+    cat_cols = [j for j, a in enumerate(arity) if a > 1]
+    Xt[::5, cat_cols[0]] = 2.5
+    Xt[::7, cat_cols[1]] = -1.0
+    Xt[::9, cat_cols[2]] = 1000.0
+    np.testing.assert_array_equal(fo.predict(torch.as_tensor(Xt, device=cuda)).cpu().numpy(), o.predict(Xt))
+    assert np.array_equal(fo.predict_leaves(torch.as_tensor(Xt, device=cuda)).cpu().numpy(), _walk(o, Xt))
