@@ -136,6 +136,16 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins, int64_t ldb, const vo
 int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream);
 /* K5 binsToBestSplit (row a8) on the (reduced) histogram, then the driver tail (row a9).  Synchronises the stream. */
 int b2rf_trainer_end_group(b2rf_trainer* t, void* stream);
+/* Introspection of the group in flight (valid between begin_group and end_group; debug / parity tests: the reduced histogram the
+ * caller holds can then be compared cell by cell with DTStatsAggregator's contents).  Slot s is node h_node_id[s] (heap numbering,
+ * root = 1) of tree h_tree[s]; its j-th drawn feature and that feature's first cell inside the slot are h_slot_fo[s][j][0..1]; the
+ * slot's first cell in d_hist is h_slot_base[s].  Arrays may be NULL (pass only n_slots first to size them). */
+int b2rf_trainer_group_info(const b2rf_trainer* t, int64_t* n_slots, int32_t* h_tree, int32_t* h_node_id, uint32_t* h_slot_fo,
+                            int64_t* h_slot_base);
+/* Process-wide switches, for A/B runs and tests: "k4_fp64" (1: segment mode uses the fp64 compare-and-swap histogram kernels
+ * instead of the limb kernel; env B2RF_K4=fp64), "carry_labels" (0: row lists do not carry labels, K4 gathers them; env
+ * B2RF_CARRY_Y=0).  Takes effect at the next b2rf_trainer_bind / begin_group. */
+int b2rf_set_option(const char* name, int64_t value);
 /* h_seconds5: init(0), findSplits(0), findBestSplits (K4 device time from CUDA events), chooseSplits (K5 + driver tail),
  * total — MLlib TimeTracker phase names.  h_counts6: node groups, K4 launches, rows*trees scanned, learning nodes,
  * kernels launched by the trainer, algorithmic bytes summed over K4 launches (SURVEY.md §8d formula). */
@@ -152,6 +162,10 @@ int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature
 int b2rf_trainer_num_classes(const b2rf_trainer* t);
 int b2rf_trainer_export_class_counts(b2rf_trainer* t, double* h_counts);
 int64_t b2rf_trainer_trace_size(const b2rf_trainer* t);
+/* Evidence / test hook: how many times this process launched each K4 implementation, h_counts[i] for i < n:
+ * 0 limb kernel (native 32-bit shared-memory adds on fixed-point limbs; default of the segment mode), 1 fp64 kernel for
+ * <= 32 features per node, 2 general fp64 kernel, 3 multiclass class-count kernel, 4 column-scan kernels. */
+int b2rf_k4_launch_counts(int64_t* h_counts, int32_t n);
 int b2rf_trainer_trace(const b2rf_trainer* t, int32_t* h_ints, double* h_dbls);
 
 /* ---- stand-alone kernels (same code the trainer launches), for testing and for callers with their own driver -- */

@@ -7,7 +7,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libb2rf.so")
-SOURCES = ["b2rf_core.cu", "k1_find_splits.cu", "k2_bin.cu", "k3_bag.cu", "k4_hist.cu", "k5_split.cu", "k6_partition.cu", "k7_predict.cu", "k8_multiclass.cu",
+SOURCES = ["b2rf_core.cu", "k1_find_splits.cu", "k2_bin.cu", "k3_bag.cu", "k4_hist.cu", "k4_limb.cu", "k5_split.cu", "k6_partition.cu", "k7_predict.cu", "k8_multiclass.cu",
            "b2rf_trainer.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo", "-fmad=false",
               "--shared", "-Xcompiler", "-fPIC"]

@@ -71,7 +71,19 @@ struct BucketLaunch {
   double* hist;
   // segment mode (dseg != nullptr): slot s owns rows idx[seg.buf][seg.start ...] with seg = dseg[slot_pos[s]]
   const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;
+  // labels carried with the row lists (same positions as idx0 / idx1); nullptr: gather a.y[row]
+  const double* y0; const double* y1;
 };
+
+// Which K4 implementation a launch used (b2rf_k4_launch_counts; tests assert on it).
+enum { B2RF_K4_LIMB = 0, B2RF_K4_FP64_32 = 1, B2RF_K4_FP64_GENERAL = 2, B2RF_K4_CLASS_COUNTS = 3, B2RF_K4_SCAN = 4, B2RF_K4_VARIANTS = 5 };
+void count_k4_variant(int v);
+long long k4_variant_count(int v);
+
+// Limb kernel (k4_limb.cu): launch shape chosen by limb_plan from the histogram size and the code-row width.
+struct LimbPlan { int G, BR, threads, padB; };
+bool limb_plan(const BucketLaunch& b, int maxBinsAll, LimbPlan* p);
+cudaError_t launch_limb_hist(const BucketLaunch& b, const LimbPlan& p, cudaStream_t s);
 
 constexpr int SEG_CH = 4096;            // rows per (node, chunk) task
 constexpr int COMPACT_ROWS = 2048;      // rows per compaction block
@@ -81,6 +93,7 @@ struct PartLaunch {                      // stable partition of the row segments
   const DNode* dnodes; DSeg* dseg; const uint32_t* catmasks;
   const uint8_t* bins; int64_t ldb;                    // column-major bin matrix
   uint32_t* idx0; uint32_t* idx1;
+  double* y0; double* y1;                              // labels carried with the lists (nullptr: not carried)
   uint32_t* chunk_prefix;                              // [nSplits + 1]
   uint32_t* left_cnt; uint32_t* left_off;              // [tasks]
   uint32_t* predbits;                                  // [tasks][SEG_CH / 32]
@@ -89,10 +102,11 @@ struct PartLaunch {                      // stable partition of the row segments
 cudaError_t launch_partition(const PartLaunch& p, cudaStream_t s);
 cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s);
 // chunkPrefix[i] = exclusive prefix of ceil(count_i / CH) over the row segments dseg[pos[i]], i < n; chunkPrefix[n] = total
-cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s);
+// ticket: also clears chunkPrefix[n + 1], the work counter of kernels that hand out tasks dynamically
+cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s, bool ticket = false);
 cudaError_t launch_compact_count(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, uint32_t* blockCnt, unsigned long long* totals, cudaStream_t s);
 cudaError_t launch_compact_write(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, const uint32_t* blockOff, const uint64_t* treeBase, uint32_t* idx,
-                                 cudaStream_t s);
+                                 const double* y, double* ylist, cudaStream_t s);
 cudaError_t launch_regrow_segs(const DSeg* src, int64_t oldStride, DSeg* dst, int64_t newStride, int T, cudaStream_t s);
 
 cudaError_t launch_hist(const HistLaunch& a, int mode, cudaStream_t s, std::string* err);

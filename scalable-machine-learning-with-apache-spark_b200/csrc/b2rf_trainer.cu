@@ -201,6 +201,10 @@ template <class T> struct PinBuf {
 
 double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
 
+// Process-wide switches (b2rf_set_option; initial values from the environment: B2RF_K4=fp64, B2RF_CARRY_Y=0).
+std::atomic<int>& opt_k4_fp64() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_K4"); return (m && std::string(m) == "fp64") ? 1 : 0; }()}; return v; }
+std::atomic<int>& opt_carry_labels() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_CARRY_Y"); return (m && *m == '0') ? 0 : 1; }()}; return v; }
+
 }  // namespace
 
 struct b2rf_trainer {
@@ -283,6 +287,9 @@ struct b2rf_trainer {
   // segment mode
   DevBuf<DSeg> dSeg;
   DevBuf<uint32_t> dIdx0, dIdx1, dPartPrefix, dLeftCnt, dLeftOff, dPredBits;
+  DevBuf<double> dY0, dY1;      // labels carried with the row lists (same positions), when memory allows: K4 then reads them as a stream
+  bool carryY = false;
+  DevBuf<unsigned long long> dBindTmp;
   DevBuf<int64_t> dSlotPos, dSplitPos;
   PinBuf<int64_t> hSlotPos, hSplitPos;
   std::vector<uint64_t> treeBase;
@@ -322,7 +329,7 @@ struct b2rf_trainer {
     dn.release(); dnUpd.release(); dCat.release(); dSlotFo.release(); dSlotBase.release(); dParent.release();
     dHasParent.release(); dNumBins.release(); dIsCat.release(); dTreeIds.release(); dRec.release();
     dCellBins.release(); dKind.release(); dParentCls.release(); dClsOut.release(); hParentCls.release(); hClsOut.release();
-    dSeg.release(); dIdx0.release(); dIdx1.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
+    dSeg.release(); dIdx0.release(); dIdx1.release(); dY0.release(); dY1.release(); dBindTmp.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
     dSlotPos.release(); dSplitPos.release(); hSlotPos.release(); hSplitPos.release();
     dRecMask.release(); hRecMask.release();
     dSlotCount.release(); dCursor.release(); dChunkPrefix.release(); dRowList.release(); dSlotStart.release(); dSlotCells.release(); hSlotCells.release();
@@ -489,11 +496,11 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
     // in-bag rows per tree; in segment mode also the initial row lists (ascending rows, packed row | weight << 27)
     const int nb = (int)((n_rows_local + COMPACT_ROWS - 1) / COMPACT_ROWS);
     DevBuf<uint32_t> blockCnt;
-    unsigned long long* d_tot = nullptr;
     std::vector<unsigned long long> h_tot(t->T, 0);
-    if (!blockCnt.ensure((size_t)std::max(nb, 1) * t->T)) return B2RF_ERR_CUDA;
-    if (!cuda_ok(cudaMalloc((void**)&d_tot, (size_t)t->T * 8), "bind alloc")) { blockCnt.release(); return B2RF_ERR_CUDA; }
-    bool ok = cuda_ok(cudaMemset(d_tot, 0, (size_t)t->T * 8), "bind memset");
+    // scratch from the trainer's pool (no cudaMalloc / cudaFree per fit): [0, T) in-bag totals, [T, 2T + 1) list bases
+    if (!blockCnt.ensure((size_t)std::max(nb, 1) * t->T) || !t->dBindTmp.ensure((size_t)2 * t->T + 1)) { blockCnt.release(); return B2RF_ERR_CUDA; }
+    unsigned long long* d_tot = t->dBindTmp.p;
+    bool ok = cuda_ok(cudaMemsetAsync(d_tot, 0, (size_t)t->T * 8, 0), "bind memset");
     ok = ok && cuda_ok(launch_compact_count(d_w, ldw, t->T, n_rows_local, blockCnt.p, d_tot, 0), "count in-bag rows");
     ok = ok && cuda_ok(cudaMemcpy(h_tot.data(), d_tot, (size_t)t->T * 8, cudaMemcpyDeviceToHost), "bind copy");
     t->inBag.assign(h_tot.begin(), h_tot.end());
@@ -501,19 +508,28 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
       t->treeBase.assign(t->T + 1, 0);
       for (int i = 0; i < t->T; i++) t->treeBase[i + 1] = t->treeBase[i] + h_tot[i];
       const size_t total = std::max<uint64_t>(t->treeBase[t->T], 1);
-      uint64_t* d_base = nullptr;
+      uint64_t* d_base = reinterpret_cast<uint64_t*>(t->dBindTmp.p + t->T);
       ok = ok && t->dIdx0.ensure(total) && t->dIdx1.ensure(total) && t->dSeg.ensure((size_t)t->nodeStride * t->T);
-      ok = ok && cuda_ok(cudaMalloc((void**)&d_base, (size_t)(t->T + 1) * 8), "bind alloc");
+      // Labels ride with the row lists (two more lists of 8 bytes per in-bag row) unless that would not leave room on the device:
+      // K4 then streams them instead of gathering a 32-byte sector per (row, tree).  B2RF_CARRY_Y=0 keeps the gathers.
+      t->carryY = false;
+      if (ok) {
+        const bool want = opt_carry_labels().load() != 0;
+        size_t freeB = 0, totB = 0;
+        const size_t have = t->dY0.bytes + t->dY1.bytes;
+        if (want && cudaMemGetInfo(&freeB, &totB) == cudaSuccess && (have >= 2 * total * 8 || freeB + have > 2 * total * 8 + ((size_t)4 << 30)))
+          t->carryY = t->dY0.ensure(total) && t->dY1.ensure(total);
+        if (!t->carryY) { t->dY0.release(); t->dY1.release(); }
+      }
       ok = ok && cuda_ok(cudaMemcpy(d_base, t->treeBase.data(), (size_t)(t->T + 1) * 8, cudaMemcpyHostToDevice), "bind copy");
-      ok = ok && cuda_ok(launch_compact_write(d_w, ldw, t->T, n_rows_local, blockCnt.p, d_base, t->dIdx0.p, 0), "build row lists");
+      ok = ok && cuda_ok(launch_compact_write(d_w, ldw, t->T, n_rows_local, blockCnt.p, d_base, t->dIdx0.p, d_y, t->carryY ? t->dY0.p : nullptr, 0),
+                         "build row lists");
       std::vector<DSeg> roots(t->T);
       for (int i = 0; i < t->T; i++) { roots[i].start = t->treeBase[i]; roots[i].count = (uint32_t)h_tot[i]; roots[i].buf = 0; }
       ok = ok && cuda_ok(cudaMemcpy2D(t->dSeg.p, (size_t)t->nodeStride * sizeof(DSeg), roots.data(), sizeof(DSeg), sizeof(DSeg), t->T,
                                       cudaMemcpyHostToDevice), "bind copy root segments");
       ok = ok && cuda_ok(cudaDeviceSynchronize(), "bind sync");
-      if (d_base) cudaFree(d_base);
     }
-    cudaFree(d_tot);
     blockCnt.release();
     if (!ok) return B2RF_ERR_CUDA;
   }
@@ -710,7 +726,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     int64_t listCap = 0;
     for (int i = 0; i < nTg; i++) listCap += t->inBag[t->hTreeIds.p[i]];
     int32_t maxCells = 0;
-    if (!t->hSlotCells.ensure(nSlots) || !t->dSlotCells.ensure(nSlots) || !t->dChunkPrefix.ensure(nSlots + 1)) return B2RF_ERR_CUDA;
+    if (!t->hSlotCells.ensure(nSlots) || !t->dSlotCells.ensure(nSlots) || !t->dChunkPrefix.ensure(nSlots + 2)) return B2RF_ERR_CUDA;
     if (t->segMode) {
       if (!t->hSlotPos.ensure(nSlots) || !t->dSlotPos.ensure(nSlots)) return B2RF_ERR_CUDA;
       for (size_t sl = 0; sl < nSlots; sl++) t->hSlotPos.p[sl] = (int64_t)t->group[sl].tree * t->nodeStride + t->group[sl].nidx;
@@ -744,7 +760,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->segMode ? SEG_CH : t->chunkRows; b.slot_fo = t->dSlotFo.p;
     b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.padB = padB; b.G = G; b.codeBytes = t->codeBytes; b.hist = t->d_hist;
     { static const bool zr = [] { const char* m = std::getenv("B2RF_ZERO_REG"); return !(m && *m == '0'); }(); b.zeroReg = zr ? 1 : 0; }
-    b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr;
+    b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr; b.y0 = nullptr; b.y1 = nullptr;
     std::string err;
     cudaError_t e;
     if (t->C) {   // multiclass: class-count histograms (segment mode only, checked in bind)
@@ -757,7 +773,13 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       t->nKernels += 2;
     } else if (t->segMode) {
       b.dseg = t->dSeg.p; b.slot_pos = t->dSlotPos.p; b.idx0 = t->dIdx0.p; b.idx1 = t->dIdx1.p;
-      e = launch_segment_hist(b, s);
+      if (t->carryY) { b.y0 = t->dY0.p; b.y1 = t->dY1.p; }
+      // default: limb kernel (native 32-bit shared-memory adds on fixed-point limbs, k4_limb.cu); B2RF_K4=fp64 keeps the
+      // compare-and-swap kernels, which also serve what the limb kernel does not (uint16 codes, labels not carried, huge histograms)
+      const bool fp64Only = opt_k4_fp64().load() != 0;
+      LimbPlan plan;
+      if (!fp64Only && limb_plan(b, maxBinsAll, &plan)) e = launch_limb_hist(b, plan, s);
+      else e = launch_segment_hist(b, s);
       t->nKernels += 2;
     } else {
       e = launch_bucket_pipeline(a, b, t->dCursor.p, s, &err);
@@ -908,6 +930,7 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
     PartLaunch pl;
     pl.split_pos = t->dSplitPos.p; pl.nSplits = (int32_t)k; pl.dnodes = t->dn.p; pl.dseg = t->dSeg.p; pl.catmasks = t->dCat.p;
     pl.bins = t->d_bins; pl.ldb = t->ldb; pl.idx0 = t->dIdx0.p; pl.idx1 = t->dIdx1.p; pl.chunk_prefix = t->dPartPrefix.p;
+    pl.y0 = t->carryY ? t->dY0.p : nullptr; pl.y1 = t->carryY ? t->dY1.p : nullptr;
     pl.left_cnt = t->dLeftCnt.p; pl.left_off = t->dLeftOff.p; pl.predbits = t->dPredBits.p; pl.codeBytes = t->codeBytes; pl.maskWords = t->maskWords;
     if (!cuda_ok(launch_partition(pl, s), "partition launch")) return B2RF_ERR_CUDA;
     t->nKernels += 4;
@@ -916,6 +939,27 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   t->groupNo++;
   t->exported = false;
   t->tChoose += now_s() - tc0; t->tTail += now_s() - tc0;
+  return B2RF_OK;
+}
+
+int b2rf_set_option(const char* name, int64_t value) {
+  const std::string n = name ? name : "";
+  if (n == "k4_fp64") { opt_k4_fp64().store(value ? 1 : 0); return B2RF_OK; }
+  if (n == "carry_labels") { opt_carry_labels().store(value ? 1 : 0); return B2RF_OK; }
+  set_error("b2rf_set_option: unknown option \"" + n + "\" (k4_fp64, carry_labels)");
+  return B2RF_ERR_ARG;
+}
+
+int b2rf_trainer_group_info(const b2rf_trainer* t, int64_t* n_slots, int32_t* h_tree, int32_t* h_node_id, uint32_t* h_slot_fo, int64_t* h_slot_base) {
+  if (!t || !t->inGroup) { set_error("b2rf_trainer_group_info: no group in flight"); return B2RF_ERR_STATE; }
+  const size_t nSlots = t->group.size();
+  if (n_slots) *n_slots = (int64_t)nSlots;
+  for (size_t sl = 0; sl < nSlots; sl++) {
+    if (h_tree) h_tree[sl] = t->group[sl].tree;
+    if (h_node_id) h_node_id[sl] = t->trees[t->group[sl].tree][t->group[sl].nidx].id;
+    if (h_slot_base) h_slot_base[sl] = t->hSlotBase.p[sl];
+  }
+  if (h_slot_fo) memcpy(h_slot_fo, t->hSlotFo.p, nSlots * (size_t)t->Fsub * sizeof(uint2));
   return B2RF_OK;
 }
 

@@ -181,6 +181,7 @@ cudaError_t launch_hist(const HistLaunch& a, int mode, cudaStream_t s, std::stri
   if (e != cudaSuccess) return e;
   int64_t grid = device_sm_count();
   if (grid > k.numTiles) grid = k.numTiles;
+  count_k4_variant(B2RF_K4_SCAN);
   kern<<<(unsigned)grid, HIST_THREADS, smem, s>>>(k);
   return cudaGetLastError();
 }
@@ -270,7 +271,7 @@ __device__ __forceinline__ void staged_row(const uint4* st, int r, uint32_t& ent
 // block: it fetches the packed entry and the label once and forms (w, w*y, w*y*y); the values are then broadcast row by row
 // while every lane (== feature) gathers its own bin code and updates its own histogram column.
 template <bool DIRECT>
-__device__ __forceinline__ void bucket_rows32(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
+__device__ __forceinline__ void bucket_rows32(const BucketLaunch& a, const uint32_t* rl, const double* yl, int n, int warp, int lane, bool active, uint32_t featCol,
                                             double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
                                             uint4* st) {
   constexpr int W = BUCKET_THREADS / 32;
@@ -278,7 +279,7 @@ __device__ __forceinline__ void bucket_rows32(const BucketLaunch& a, const uint3
   for (int base = warp * 32; base < n; base += W * 32) {
     const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;          // w == 0 marks padding
     const uint32_t myw = mine >> 27;
-    const double myy = myw ? a.y[mine & 0x7ffffffu] : 0.0;
+    const double myy = myw ? (yl ? yl[base + lane] : a.y[mine & 0x7ffffffu]) : 0.0;   // label from the list when it is carried there
     const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
     const double mywyy = mywy * myy;
     stage_row(st, lane, mine, mywy, mywyy);
@@ -322,12 +323,13 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist32_kernel(const Buc
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.chunk_prefix[mid] <= task) lo = mid; else hi = mid; }
     const int slot = lo;
     const uint32_t chunk = task - a.chunk_prefix[slot];
-    uint32_t cnt; const uint32_t* rl;
+    uint32_t cnt; const uint32_t* rl; const double* yl = nullptr;
     const uint32_t begin = chunk * (uint32_t)a.CH;
     if (a.dseg != nullptr) {
       const DSeg sg = a.dseg[a.slot_pos[slot]];
       cnt = sg.count;
       rl = (sg.buf ? a.idx1 : a.idx0) + sg.start + begin;
+      if (a.y0) yl = (sg.buf ? a.y1 : a.y0) + sg.start + begin;
     } else {
       cnt = a.slot_count[slot];
       rl = a.rowlist + a.slot_start[slot] + begin;
@@ -351,8 +353,8 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist32_kernel(const Buc
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
       const uint32_t sbase = padB > 0 ? (uint32_t)((j0 >> 5) * padB * 32 + lane) : e.y;   // shared-memory cell of bin 0
       const uint32_t sstep = padB > 0 ? 32u : 1u;
-      if (direct) bucket_rows32<true>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep, st);
-      else bucket_rows32<false>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep, st);
+      if (direct) bucket_rows32<true>(a, rl, yl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep, st);
+      else bucket_rows32<false>(a, rl, yl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, sbase, sstep, st);
     }
     if (!direct) {
       __syncthreads();
@@ -374,7 +376,7 @@ __global__ void __launch_bounds__(BUCKET_THREADS) bucket_hist32_kernel(const Buc
 // while every lane (row slot r = lane / G, feature fl = lane % G) gathers its own bin code and updates its own cell.
 // ONE_ROW (G == 32) and the code width CB are compile-time in the hot instantiations; CB == 0 reads a.codeBytes.
 template <bool DIRECT, int THREADS, bool ONE_ROW, int CB>
-__device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const uint32_t* rl, int n, int warp, int lane, bool active, uint32_t featCol,
+__device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const uint32_t* rl, const double* yl, int n, int warp, int lane, bool active, uint32_t featCol,
                                                  double* hb, uint32_t gbase, double* ssum, double* ssq, unsigned* scnt, uint32_t sbase, uint32_t sstep,
                                                  int Rrt, int rrt, uint4* st, uint32_t& z_c, double& z_s, double& z_q) {
   const int R = ONE_ROW ? 1 : Rrt, r = ONE_ROW ? 0 : rrt;
@@ -384,7 +386,7 @@ __device__ __forceinline__ void bucket_rows_impl(const BucketLaunch& a, const ui
   for (int base = warp * 32; base < n; base += W * 32) {
     const uint32_t mine = (base + lane < n) ? rl[base + lane] : 0u;          // w == 0 marks padding
     const uint32_t myw = mine >> 27;
-    const double myy = myw ? a.y[mine & 0x7ffffffu] : 0.0;
+    const double myy = myw ? (yl ? yl[base + lane] : a.y[mine & 0x7ffffffu]) : 0.0;   // label from the list when it is carried there
     const double mywy = (double)myw * myy;                                     // MLlib: instanceWeight * label * label == (w*y)*y
     const double mywyy = mywy * myy;
     stage_row(st, lane, mine, mywy, mywyy);
@@ -446,12 +448,13 @@ __global__ void __launch_bounds__(THREADS) bucket_hist_kernel(const BucketLaunch
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.chunk_prefix[mid] <= bt) lo = mid; else hi = mid; }
     const int slot = lo;
     const uint32_t chunk = bt - a.chunk_prefix[slot];
-    uint32_t cnt; const uint32_t* rl;
+    uint32_t cnt; const uint32_t* rl; const double* yl = nullptr;
     const uint32_t begin = chunk * (uint32_t)a.CH;
     if (a.dseg != nullptr) {
       const DSeg sg = a.dseg[a.slot_pos[slot]];
       cnt = sg.count;
       rl = (sg.buf ? a.idx1 : a.idx0) + sg.start + begin;
+      if (a.y0) yl = (sg.buf ? a.y1 : a.y0) + sg.start + begin;
     } else {
       cnt = a.slot_count[slot];
       rl = a.rowlist + a.slot_start[slot] + begin;
@@ -472,9 +475,9 @@ __global__ void __launch_bounds__(THREADS) bucket_hist_kernel(const BucketLaunch
       const bool active = j < a.Fsub;
       const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
       uint32_t z_c = 0u; double z_s = 0.0, z_q = 0.0;
-      if (direct) bucket_rows_impl<true, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 32 / G, r, st, z_c, z_s, z_q);
+      if (direct) bucket_rows_impl<true, THREADS, ONE_ROW, CB>(a, rl, yl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 32 / G, r, st, z_c, z_s, z_q);
       else {
-        bucket_rows_impl<false, THREADS, ONE_ROW, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r, st, z_c, z_s, z_q);
+        bucket_rows_impl<false, THREADS, ONE_ROW, CB>(a, rl, yl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, (uint32_t)fl, (uint32_t)G, 32 / G, r, st, z_c, z_s, z_q);
         if (z_c) { atomicAdd(&scnt[fl], z_c); atomicAdd(&ssum[fl], z_s); atomicAdd(&ssq[fl], z_q); }
       }
     } else {
@@ -483,9 +486,9 @@ __global__ void __launch_bounds__(THREADS) bucket_hist_kernel(const BucketLaunch
         const bool active = j < a.Fsub;
         const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
         uint32_t z_c = 0u; double z_s = 0.0, z_q = 0.0;
-        if (direct) bucket_rows_impl<true, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 1, 0, st, z_c, z_s, z_q);
+        if (direct) bucket_rows_impl<true, THREADS, true, CB>(a, rl, yl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, 0u, 0u, 1, 0, st, z_c, z_s, z_q);
         else {
-          bucket_rows_impl<false, THREADS, true, CB>(a, rl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0, st, z_c, z_s, z_q);
+          bucket_rows_impl<false, THREADS, true, CB>(a, rl, yl, n, warp, lane, active, e.x, hb, e.y, ssum, ssq, scnt, e.y, 1u, 1, 0, st, z_c, z_s, z_q);
           if (z_c) { atomicAdd(&scnt[e.y], z_c); atomicAdd(&ssum[e.y], z_s); atomicAdd(&ssq[e.y], z_q); }
         }
       }
@@ -510,9 +513,11 @@ static cudaError_t launch_bucket_kernel(const BucketLaunch& b, int grid, int thr
   if (b.padB > 0 && b.G == 32 && b.Fsub <= 32 && b.codeBytes == 1 && threads == BUCKET_THREADS) {
     cudaError_t e = cudaFuncSetAttribute(bucket_hist32_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
+    count_k4_variant(B2RF_K4_FP64_32);
     bucket_hist32_kernel<<<grid, BUCKET_THREADS, smem, s>>>(b);
     return cudaGetLastError();
   }
+  count_k4_variant(B2RF_K4_FP64_GENERAL);
   const bool padded = b.padB > 0;
   const bool one = padded && b.G == 32;
   const int cb = b.codeBytes;
@@ -557,7 +562,7 @@ static cudaError_t launch_bucket_sized(const BucketLaunch& b, cudaStream_t s) {
 }
 
 // ---- segment mode: task table from the nodes' row segments, then the same shared-memory histogram kernel ----
-__global__ void __launch_bounds__(1024) seg_tasks_kernel(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix) {
+__global__ void __launch_bounds__(1024) seg_tasks_kernel(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, int ticket) {
   __shared__ uint32_t s_chunks[1024];
   const int tid = threadIdx.x;
   const int per = (n + 1023) / 1024;
@@ -570,14 +575,15 @@ __global__ void __launch_bounds__(1024) seg_tasks_kernel(const DSeg* dseg, const
     uint32_t ac = 0;
     for (int i = 0; i < 1024; i++) { const uint32_t tc = s_chunks[i]; s_chunks[i] = ac; ac += tc; }
     chunkPrefix[n] = ac;
+    if (ticket) chunkPrefix[n + 1] = 0u;
   }
   __syncthreads();
   c = s_chunks[tid];
   for (int i = b; i < e; i++) { chunkPrefix[i] = c; c += (dseg[pos[i]].count + CH - 1) / CH; }
 }
 
-cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s) {
-  seg_tasks_kernel<<<1, 1024, 0, s>>>(dseg, pos, n, CH, chunkPrefix);
+cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s, bool ticket) {
+  seg_tasks_kernel<<<1, 1024, 0, s>>>(dseg, pos, n, CH, chunkPrefix, ticket ? 1 : 0);
   return cudaGetLastError();
 }
 

@@ -33,12 +33,13 @@ __global__ void compact_scan_kernel(uint32_t* blockCnt, int nb, unsigned long lo
   totals[t] = run;
 }
 __global__ void __launch_bounds__(256) compact_write_kernel(const uint8_t* w, int64_t ldw, int64_t n_rows, const uint32_t* blockOff, int nb,
-                                                             const uint64_t* treeBase, uint32_t* idx) {
+                                                             const uint64_t* treeBase, uint32_t* idx, const double* y, double* ylist) {
   const int t = blockIdx.y, b = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ uint32_t sw[8];
   uint32_t run = 0;
   uint32_t* out = idx + treeBase[t] + blockOff[(size_t)t * nb + b];
+  double* yout = ylist ? ylist + treeBase[t] + blockOff[(size_t)t * nb + b] : nullptr;
   for (int it = 0; it < COMPACT_ROWS / 256; it++) {
     const int64_t r = (int64_t)b * COMPACT_ROWS + it * 256 + threadIdx.x;
     uint32_t wv = (r < n_rows) ? w[(size_t)t * ldw + r] : 0u;
@@ -49,7 +50,9 @@ __global__ void __launch_bounds__(256) compact_write_kernel(const uint8_t* w, in
     for (int i = 0; i < 8; i++) { if (i < warp) before += sw[i]; total += sw[i]; }
     if (wv != 0) {
       if (wv > 31u) wv = 31u;   // packed in 5 bits
-      out[run + before + __popc(bal & ((1u << lane) - 1u))] = (uint32_t)r | (wv << 27);
+      const uint32_t at = run + before + __popc(bal & ((1u << lane) - 1u));
+      out[at] = (uint32_t)r | (wv << 27);
+      if (yout) yout[at] = y[r];
     }
     run += total;
     __syncthreads();
@@ -63,10 +66,10 @@ cudaError_t launch_compact_count(const uint8_t* w, int64_t ldw, int T, int64_t n
   return cudaGetLastError();
 }
 cudaError_t launch_compact_write(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, const uint32_t* blockOff, const uint64_t* treeBase, uint32_t* idx,
-                                 cudaStream_t s) {
+                                 const double* y, double* ylist, cudaStream_t s) {
   const int nb = (int)((n_rows + COMPACT_ROWS - 1) / COMPACT_ROWS);
   if (nb <= 0 || T <= 0) return cudaSuccess;
-  compact_write_kernel<<<dim3((unsigned)nb, (unsigned)T), 256, 0, s>>>(w, ldw, n_rows, blockOff, nb, treeBase, idx);
+  compact_write_kernel<<<dim3((unsigned)nb, (unsigned)T), 256, 0, s>>>(w, ldw, n_rows, blockOff, nb, treeBase, idx, y, ylist);
   return cudaGetLastError();
 }
 __global__ void regrow_segs_kernel(const DSeg* src, int64_t oldStride, DSeg* dst, int64_t newStride) {
@@ -147,6 +150,8 @@ __global__ void __launch_bounds__(256) part_scatter_kernel(const PartLaunch p) {
     const uint32_t c = task - p.chunk_prefix[k];
     const uint32_t* src = (sg.buf ? p.idx1 : p.idx0) + sg.start + (size_t)c * SEG_CH;
     uint32_t* dst = (sg.buf ? p.idx0 : p.idx1) + sg.start;
+    const double* ysrc = p.y0 ? (sg.buf ? p.y1 : p.y0) + sg.start + (size_t)c * SEG_CH : nullptr;
+    double* ydst = p.y0 ? (sg.buf ? p.y0 : p.y1) + sg.start : nullptr;
     const int n = (int)min((uint32_t)SEG_CH, sg.count - c * SEG_CH);
     const uint32_t nLeft = p.dseg[p.split_pos[p.nSplits + k]].count;
     const uint32_t lbase = p.left_off[task];
@@ -166,8 +171,9 @@ __global__ void __launch_bounds__(256) part_scatter_kernel(const PartLaunch p) {
       const uint32_t bits = sbits[i >> 5];
       const uint32_t lrank = spref[i >> 5] + __popc(bits & ((1u << (i & 31)) - 1u));
       const uint32_t e = src[i];
-      if ((bits >> (i & 31)) & 1u) dst[lbase + lrank] = e;
-      else dst[rbase + ((uint32_t)i - lrank)] = e;
+      const uint32_t at = ((bits >> (i & 31)) & 1u) ? lbase + lrank : rbase + ((uint32_t)i - lrank);
+      dst[at] = e;
+      if (ysrc) ydst[at] = ysrc[i];
     }
     __syncthreads();
   }

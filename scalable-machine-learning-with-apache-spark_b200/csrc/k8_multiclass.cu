@@ -101,6 +101,7 @@ cudaError_t launch_cls_hist(const ClsHistLaunch& a0, cudaStream_t s) {
   if (perSM > 4) perSM = 4;
   e = cudaFuncSetAttribute(bucket_hist_cls_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
+  count_k4_variant(B2RF_K4_CLASS_COUNTS);
   bucket_hist_cls_kernel<<<device_sm_count() * perSM, CLS_THREADS, smem, s>>>(a);
   return cudaGetLastError();
 }

@@ -214,7 +214,31 @@ def _check_labels(y, params):
                                            f"TreeParams(numClasses=...) for more than two classes). Found invalid labels.")
 
 
-def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace):
+def k4_launch_counts() -> dict:
+    """Launches of each K4 implementation by this process so far (b2rf_k4_launch_counts)."""
+    c = np.zeros(5, np.int64)
+    check(lib().b2rf_k4_launch_counts(c.ctypes.data_as(C.c_void_p), 5))
+    return dict(limb=int(c[0]), fp64_32=int(c[1]), fp64_general=int(c[2]), class_counts=int(c[3]), scan=int(c[4]))
+
+
+def set_option(name: str, value: int):
+    """Process-wide switch of the library (b2rf_set_option): "k4_fp64", "carry_labels"."""
+    check(lib().b2rf_set_option(name.encode(), int(value)))
+
+
+def _group_info(h, Fsub):
+    L = lib()
+    n = C.c_int64()
+    check(L.b2rf_trainer_group_info(h, C.byref(n), None, None, None, None))
+    n = n.value
+    tree, nid = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    fo, base = np.zeros((n, Fsub, 2), np.uint32), np.zeros(n, np.int64)
+    P = lambda a: a.ctypes.data_as(C.c_void_p)
+    check(L.b2rf_trainer_group_info(h, None, P(tree), P(nid), P(fo), P(base)))
+    return dict(tree=tree, node_id=nid, slot_fo=fo, slot_base=base)
+
+
+def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace, hist_hook=None):
     """RandomForest.run's while (nodeStack.nonEmpty) loop: one begin_group / [all_reduce] / end_group per node group."""
     L = lib()
     dev = y.device
@@ -238,6 +262,8 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
         while check(L.b2rf_trainer_begin_group(h, C.byref(ncell), st)) == 1:
             if S["world"] > 1:
                 S["dist"].all_reduce(hist[: ncell.value * 4], group=group)   # DTStatsAggregator.merge (reduceByKey), row a7
+            if hist_hook is not None:   # debug / parity tests: the reduced group histogram next to the group's slot table
+                hist_hook(_group_info(h, min(S["cp"].featuresPerNode, F) if S["cp"].featuresPerNode > 0 else F), hist[: ncell.value * 4].view(-1, 4))
             check(L.b2rf_trainer_end_group(h, st))
         torch.cuda.synchronize(dev)
         tl = time.perf_counter()
@@ -254,7 +280,7 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
 
 
 def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, part_offsets=None, part0: int = None, group=None,
-                keep_trace: bool = False, prebinned=None, hist_mode: str = "segment") -> Forest:
+                keep_trace: bool = False, prebinned=None, hist_mode: str = "segment", hist_hook=None) -> Forest:
     """Train a forest on this rank's rows.
 
     X: f64 [n_local, F] CUDA, row-major (the VectorAssembler `features` column); y: f64 [n_local];
@@ -309,7 +335,7 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         if dbg and prebinned is None:
             print(f"[b2rf timing] setup {t0 - t_start:.4f} findSplits {t1 - t0:.4f} alloc {ta - t1:.4f} bin {tb - ta:.4f} bag(+alloc) {t2 - tb:.4f}", flush=True)
 
-        forest = _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace)
+        forest = _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace, hist_hook)
         t3 = time.perf_counter()
         forest.timers.update(init=(t0 - t_start) + (t2 - t1), findSplits=t1 - t0, total=t3 - t_start, loop=t3 - t2)
         # stage kernels outside the trainer: sample_rows (if sampling), find_splits, bin, bag
