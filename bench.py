@@ -33,8 +33,27 @@ WORKLOADS = {
     "C4-cont": dict(rows=12_500_000, F=128, numTrees=50, maxDepth=10, maxBins=256, gen="c3"),   # C4's shape without categorical features
 }
 ROWS_PER_PARTITION = 4096   # emulated Spark partition size (bagging streams are per partition; stated in config)
-# ncu --set full capture of the dominant kernel (profiles/r01_ncu_bucket_hist32_final.md): DRAM bytes of one whole-level launch
-NCU_TRAFFIC = {"C3": {"traffic": 109.988e9, "algorithmic": 3.765e9}}
+K4_TRAFFIC_FILE = os.path.join(ROOT, "profiles", "k4_traffic.json")   # written from the ncu --set full capture of the dominant kernel
+
+
+def k4_traffic(workload):
+    """DRAM bytes (dram__bytes_read.sum + dram__bytes_write.sum) of one launch of the dominant kernel from the committed ncu capture,
+    with that launch's algorithmic bytes; None when no capture of this workload's kernel is on file."""
+    try:
+        return json.load(open(K4_TRAFFIC_FILE)).get(workload)
+    except Exception:
+        return None
+
+
+def make_config(wl_name, wl, n_local, world, extra=None):
+    cfg = {"workload": f"{wl_name}: synthetic {n_local} rows/GPU x {wl['F']} features, RandomForestRegressor numTrees={wl['numTrees']} "
+                       f"maxDepth={wl['maxDepth']} maxBins={wl['maxBins']} featureSubsetStrategy=auto seed=42",
+           "rows_global": n_local * world, "rows_per_gpu": n_local, "rows_per_partition": ROWS_PER_PARTITION,
+           "parallelism": f"rows sharded over {world} GPU(s); per-group histogram all-reduce (NCCL)" if world > 1 else "1 GPU",
+           "l2": "inputs (bin matrix 0.64 GB + per-tree arrays 5 GB) exceed the 126 MB L2; no explicit flush"}
+    if extra:
+        cfg.update(extra)
+    return cfg
 
 
 class ClockSampler(threading.Thread):
@@ -153,15 +172,42 @@ def run_reference(args, wl, wl_name):
             times.append(dt)
     t = sum(times) / len(times)
     value = sample * wl["numTrees"] / t
-    desc = f"{sample} rows of the {wl_name} generator (of {wl['rows']} per GPU), full numTrees={wl['numTrees']} maxDepth={wl['maxDepth']} maxBins={wl['maxBins']}"
+    world = int(os.environ.get("WORLD_SIZE", str(args.gpus)))
+    desc = (f"each step trains {sample} rows of the same generator (a bounded sample of the {wl['rows']} rows/GPU workload) with the full "
+            f"numTrees={wl['numTrees']} maxDepth={wl['maxDepth']} maxBins={wl['maxBins']}; rows*trees/s of that fit")
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": t * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": wl_name + " (bounded row sample, CPU)", "rows_per_step": sample, "features": wl["F"], "numTrees": wl["numTrees"],
-                       "maxDepth": wl["maxDepth"], "maxBins": wl["maxBins"], "rows_per_partition": ROWS_PER_PARTITION},
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc},
+            "config": make_config(wl_name, wl, wl["rows"], world),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": desc, "sample_rows": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "note": "MLlib itself (JVM) is unavailable on this box; this is the CPU restatement of MLlib 3.1.2 in oracle/ (OpenMP, all host threads)"}
     print(json.dumps(line), flush=True)
+
+
+def run_c4(args, b2rf, trainer, torch, dist, dev, rank, world, timed):
+    """C4 sub-record of an N > 1 run: the 100M-row dataset of BASELINE.json configs[3] sharded over the N GPUs."""
+    wl = WORKLOADS["C4-shard"]
+    n_local = args.c4_rows // world
+    try:
+        X, y, arity = getattr(b2rf.synth, wl["gen"])(n_local, row0=rank * n_local, seed=42, device=dev, F=wl["F"])
+        params = b2rf.TreeParams(maxDepth=wl["maxDepth"], maxBins=wl["maxBins"], numTrees=wl["numTrees"], bootstrap=True, seed=42,
+                                 featureSubsetStrategy="auto")
+        po = trainer.default_partitions(n_local, ROWS_PER_PARTITION)
+        step = lambda: trainer.fit_tensors(X, y, arity, params, part_offsets=po)
+        step()
+        ms, outs = timed(step, 1)
+        f = outs[-1]
+        rec = {"workload": f"C4: synthetic {n_local * world} rows x {wl['F']} features (96 continuous + 32 categorical), numTrees={wl['numTrees']} "
+                           f"maxDepth={wl['maxDepth']} maxBins={wl['maxBins']}, rows sharded over {world} GPUs ({n_local} each)",
+               "scaling": "strong", "ms_per_fit": ms, "value": n_local * world * wl["numTrees"] / (ms * 1e-3), "unit": UNIT, "steps": 1, "warmup": 1,
+               "phases_s": {k: round(f.timers[k], 4) for k in ("init", "findSplits", "findBestSplits", "chooseSplits", "total")},
+               "allreduce_s": round(f.timers.get("allreduce", 0.0), 4), "node_groups": f.counters["groups"], "forest_nodes": int(f.num_nodes()),
+               "kernel_seconds_per_fit": f.timers["findBestSplits"]}
+        del X, y
+        torch.cuda.empty_cache()
+        return rec
+    except Exception as e:   # noqa: BLE001 — e.g. out of memory at small N: report it, keep the headline line
+        return {"unavailable": f"{type(e).__name__}: {str(e)[:300]}"}
 
 
 def main():
@@ -176,6 +222,9 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--rows-per-gpu", type=int, default=0, help="override the workload's rows per GPU (e.g. strong scaling of C4: 100M / N)")
+    ap.add_argument("--no-mgpu-parity", action="store_true", help="N > 1: skip the sharded-fit parity cases run before the timed region")
+    ap.add_argument("--no-c4", action="store_true", help="N > 1: skip the C4 strong-scaling sub-record (100M x 128 rows sharded over the N GPUs)")
+    ap.add_argument("--c4-rows", type=int, default=100_000_000, help="global row count of the C4 sub-record")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.rows_per_gpu > 0:
@@ -201,6 +250,15 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=dev)
+    # ---- N > 1: sharded fits against the CPU oracle's whole-dataset fits, before anything is timed (tests/mgpu_check.py) ----
+    mgpu_parity = None
+    if world > 1 and not args.no_mgpu_parity:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        try:
+            import mgpu_check
+            mgpu_parity = mgpu_check.run_cases(dev, rank, world, log=lambda m: print(m, file=sys.stderr, flush=True) if rank == 0 else None)
+        except Exception as e:   # noqa: BLE001 — a broken check must show up in the line, not kill the bench
+            mgpu_parity = f"FAILED {type(e).__name__}: {e}"
     n_local = wl["rows"]
     F = wl["F"]
     X, y, arity = getattr(b2rf.synth, wl["gen"])(n_local, row0=rank * n_local, seed=42, device=dev, F=F)
@@ -249,6 +307,11 @@ def main():
     internal_or_evaluated = f0.trace_d[:, 2].sum() if f0.trace_d is not None else None
     updates_per_fit = float(internal_or_evaluated) * fsub if internal_or_evaluated is not None else float("nan")
     phases = {k: round(sum(f.timers[k] for f in forests) / len(forests), 4) for k in ("init", "findSplits", "findBestSplits", "chooseSplits", "total")}
+    phys_updates = float(f0.counters.get("bin_updates", 0))
+    traffic = k4_traffic(args.workload)
+    kc = trainer.k4_launch_counts()
+    k4_kernel = ("limb_hist_kernel (K4: per-node shared-memory histograms of fixed-point limbs over row segments, native 32-bit adds)"
+                 if kc["limb"] else "bucket_hist32_kernel (K4: per-node shared-memory fp64 histograms over row segments)")
 
     # ---- end-to-end arm: host buffers in, forest arrays out, through the public API --------------------------
     e2e = None
@@ -261,7 +324,7 @@ def main():
         torch.cuda.empty_cache()
         estep = lambda: trainer.fit_host(Xh, yh, arity, params, device=dev, part_offsets=po)
         estep()
-        n_e2e = max(1, min(args.steps, 2))
+        n_e2e = max(1, min(args.steps, 5))
         ems, eouts = timed(estep, n_e2e)
         ems /= n_e2e
         fe = eouts[-1]
@@ -269,6 +332,16 @@ def main():
                                       fe.ncat, fe.cat_off, fe.cat_len, fe.cats))
         e2e = {"value": N_global * wl["numTrees"] / (ems * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(Xh.nbytes + yh.nbytes),
                "d2h_bytes_per_step": int(d2h), "ms_per_step": ems, "steps": n_e2e}
+
+    # ---- N > 1: BASELINE.json configs[3] (C4: 100M x 128 mixed, maxBins 256, depth 12, 100 trees), rows sharded over the N GPUs
+    # (strong scaling of one dataset): one warm-up + one timed fit, device-timed, max over ranks ----------------------------------
+    c4 = None
+    if world > 1 and not args.no_c4:
+        X = y = Xh = yh = forests = eouts = fe = estep = step = None   # release the C3 tensors (device and pinned host)
+        import gc
+        gc.collect()
+        torch.cuda.empty_cache()
+        c4 = run_c4(args, b2rf, trainer, torch, dist, dev, rank, world, timed)
 
     # ---- CPU baseline (rank 0, N=1 only): the oracle on a bounded row sample ---------------------------------
     cpu = None
@@ -303,25 +376,24 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": f"{args.workload}: synthetic {n_local} rows/GPU x {F} features, RandomForestRegressor numTrees={wl['numTrees']} "
-                                   f"maxDepth={wl['maxDepth']} maxBins={wl['maxBins']} featureSubsetStrategy=auto seed=42",
-                       "rows_global": N_global, "rows_per_gpu": n_local, "rows_per_partition": ROWS_PER_PARTITION,
-                       "parallelism": f"rows sharded over {world} GPU(s); per-group histogram all-reduce (NCCL)" if world > 1 else "1 GPU",
-                       "l2": "inputs (bin matrix 0.64 GB + per-tree arrays 5 GB) exceed the 126 MB L2; no explicit flush",
-                       "node_groups": f0.counters["groups"], "forest_nodes": int(f0.num_nodes())},
+            "config": make_config(args.workload, wl, n_local, world, {"node_groups": f0.counters["groups"], "forest_nodes": int(f0.num_nodes())}),
             "phases_s": phases,
-            "roofline": {"bound": "hbm", "kernel": "bucket_hist32_kernel (K4: per-node shared-memory histograms over row segments)",
+            "roofline": {"bound": "hbm", "kernel": k4_kernel,
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         # dram__bytes_read+write of ONE whole-level launch (100 trees, 1600 nodes) from profiles/r01_ncu_bucket_hist32_final.md;
-                         # the same launch's algorithmic bytes are given beside it
-                         "traffic": NCU_TRAFFIC.get(args.workload, {}).get("traffic"),
-                         "traffic_launch_algorithmic_bytes": NCU_TRAFFIC.get(args.workload, {}).get("algorithmic"),
+                         # dram__bytes_read + dram__bytes_write of ONE launch of that kernel from the committed ncu --set full capture
+                         # (profiles/k4_traffic.json names the capture), next to the same launch's algorithmic bytes
+                         "traffic": (traffic or {}).get("dram_bytes_per_launch"),
+                         "traffic_launch_algorithmic_bytes": (traffic or {}).get("algorithmic_bytes_per_launch"),
+                         "traffic_source": (traffic or {}).get("source"),
                          "peak_source": peak_src, "algorithmic_bytes_per_fit": hist_bytes, "launches_per_fit": hist_launches,
                          "kernel_seconds_per_fit": hist_s, "kernel_share_of_step": hist_s / (ms_per_step * 1e-3),
-                         "weighted_bin_updates_per_s": updates_per_fit / hist_s if hist_s > 0 else None,   # sum over evaluated nodes of (sum of bag weights) x features per node
-                         "note": "K4 is bound by shared-memory atomic throughput (83% of the smem wavefront peak in ncu), not HBM: "
-                                 "22 atomic bin updates per 37 algorithmic bytes; see DESIGN.md section 2 and profiles/"},
-            "e2e": e2e, "cpu_baseline": cpu, "cpu_baseline_sklearn": skl,
+                         # physical: (row, feature) histogram updates actually executed (rows visited by the K4 launches x features per node);
+                         # weighted: the same with every row counted bag-weight times (what MLlib's per-instance loop would execute)
+                         "physical_bin_updates_per_s": phys_updates / hist_s if hist_s > 0 and phys_updates else None,
+                         "weighted_bin_updates_per_s": updates_per_fit / hist_s if hist_s > 0 else None,
+                         "note": "K4 is bound by shared-memory atomic throughput, not HBM: 22 bin updates (7 native 32-bit adds each) per 37 "
+                                 "algorithmic bytes; see DESIGN.md section 2 and profiles/"},
+            "e2e": e2e, "cpu_baseline": cpu, "cpu_baseline_sklearn": skl, "mgpu_parity": mgpu_parity, "c4": c4,
             "gpu_launches": int(sum(f.counters["kernel_launches"] for f in forests)),
             "clocks": sampler.summary(),
         }

@@ -73,6 +73,7 @@ struct BucketLaunch {
   const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;
   // labels carried with the row lists (same positions as idx0 / idx1); nullptr: gather a.y[row]
   const double* y0; const double* y1;
+  unsigned long long* rows_acc;          // optional device counter: += rows visited by this launch (segment mode; physical update count)
 };
 
 // Which K4 implementation a launch used (b2rf_k4_launch_counts; tests assert on it).
@@ -103,7 +104,8 @@ cudaError_t launch_partition(const PartLaunch& p, cudaStream_t s);
 cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s);
 // chunkPrefix[i] = exclusive prefix of ceil(count_i / CH) over the row segments dseg[pos[i]], i < n; chunkPrefix[n] = total
 // ticket: also clears chunkPrefix[n + 1], the work counter of kernels that hand out tasks dynamically
-cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s, bool ticket = false);
+cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s, bool ticket = false,
+                             unsigned long long* rows_acc = nullptr);
 cudaError_t launch_compact_count(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, uint32_t* blockCnt, unsigned long long* totals, cudaStream_t s);
 cudaError_t launch_compact_write(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, const uint32_t* blockOff, const uint64_t* treeBase, uint32_t* idx,
                                  const double* y, double* ylist, cudaStream_t s);
@@ -139,6 +141,7 @@ struct ClsHistLaunch {                   // segment mode only
   int32_t padB;                          // bins per feature plane in shared memory (largest cell count of any feature)
   int32_t C, M;                          // classes; a global histogram cell is 4*M doubles, the first C of them the class counts
   int32_t direct;                        // set by the launcher when C * padB * 32 counters do not fit shared memory
+  unsigned long long* rows_acc;          // optional device counter: += rows visited by this launch
   double* hist;
   const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;
 };

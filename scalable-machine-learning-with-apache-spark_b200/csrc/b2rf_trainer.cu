@@ -290,6 +290,8 @@ struct b2rf_trainer {
   DevBuf<double> dY0, dY1;      // labels carried with the row lists (same positions), when memory allows: K4 then reads them as a stream
   bool carryY = false;
   DevBuf<unsigned long long> dBindTmp;
+  DevBuf<unsigned long long> dRowsAcc;   // rows visited by the K4 launches of this fit (segment mode)
+  int64_t physRows = 0;
   DevBuf<int64_t> dSlotPos, dSplitPos;
   PinBuf<int64_t> hSlotPos, hSplitPos;
   std::vector<uint64_t> treeBase;
@@ -329,7 +331,7 @@ struct b2rf_trainer {
     dn.release(); dnUpd.release(); dCat.release(); dSlotFo.release(); dSlotBase.release(); dParent.release();
     dHasParent.release(); dNumBins.release(); dIsCat.release(); dTreeIds.release(); dRec.release();
     dCellBins.release(); dKind.release(); dParentCls.release(); dClsOut.release(); hParentCls.release(); hClsOut.release();
-    dSeg.release(); dIdx0.release(); dIdx1.release(); dY0.release(); dY1.release(); dBindTmp.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
+    dSeg.release(); dIdx0.release(); dIdx1.release(); dY0.release(); dY1.release(); dBindTmp.release(); dRowsAcc.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
     dSlotPos.release(); dSplitPos.release(); hSlotPos.release(); hSplitPos.release();
     dRecMask.release(); hRecMask.release();
     dSlotCount.release(); dCursor.release(); dChunkPrefix.release(); dRowList.release(); dSlotStart.release(); dSlotCells.release(); hSlotCells.release();
@@ -534,7 +536,8 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
     if (!ok) return B2RF_ERR_CUDA;
   }
   if (t->C && !t->segMode) { set_error("b2rf: multiclass classification needs the segment histogram mode (row-major bin matrix, histMode 0)"); return B2RF_ERR_ARG; }
-  if (!t->dn.ensure((size_t)t->nodeStride * t->T)) return B2RF_ERR_CUDA;
+  if (!t->dn.ensure((size_t)t->nodeStride * t->T) || !t->dRowsAcc.ensure(1)) return B2RF_ERR_CUDA;
+  if (!cuda_ok(cudaMemset(t->dRowsAcc.p, 0, 8), "bind memset")) return B2RF_ERR_CUDA;
   if (!t->dNumBins.ensure(t->F) || !t->dIsCat.ensure(t->F) || !t->dCellBins.ensure(t->F) || !t->dKind.ensure(t->F)) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpy(t->dCellBins.p, t->cellBins.data(), t->F * 4, cudaMemcpyHostToDevice), "bind copy")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpy(t->dKind.p, t->kind.data(), t->F * 4, cudaMemcpyHostToDevice), "bind copy")) return B2RF_ERR_CUDA;
@@ -619,6 +622,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   if (t->stack.empty()) {
     if (n_cells) *n_cells = 0;
     if (t->tTotal == 0) {
+      if (t->dRowsAcc.p) { unsigned long long r = 0; if (cudaMemcpy(&r, t->dRowsAcc.p, 8, cudaMemcpyDeviceToHost) == cudaSuccess) t->physRows = (int64_t)r; }
       t->tTotal = now_s() - t->tStart;
       static const bool timing = [] { const char* m = std::getenv("B2RF_TIMING"); return m && *m == '1'; }();
       if (timing) fprintf(stderr, "[b2rf timing] groups %d host select %.4f tail %.4f wait-in-end_group %.4f total %.4f\n", t->groupNo, t->tSelect, t->tTail, t->tWait, t->tTotal);
@@ -760,14 +764,14 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->segMode ? SEG_CH : t->chunkRows; b.slot_fo = t->dSlotFo.p;
     b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.padB = padB; b.G = G; b.codeBytes = t->codeBytes; b.hist = t->d_hist;
     { static const bool zr = [] { const char* m = std::getenv("B2RF_ZERO_REG"); return !(m && *m == '0'); }(); b.zeroReg = zr ? 1 : 0; }
-    b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr; b.y0 = nullptr; b.y1 = nullptr;
+    b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr; b.y0 = nullptr; b.y1 = nullptr; b.rows_acc = t->dRowsAcc.p;
     std::string err;
     cudaError_t e;
     if (t->C) {   // multiclass: class-count histograms (segment mode only, checked in bind)
       ClsHistLaunch c;
       c.bins_rm = t->d_bins_rm; c.ldr = t->ldr; c.codeBytes = t->codeBytes; c.y = t->d_y; c.chunk_prefix = t->dChunkPrefix.p;
       c.nSlots = (int32_t)nSlots; c.CH = SEG_CH; c.slot_fo = t->dSlotFo.p; c.slot_base = t->dSlotBase.p; c.Fsub = t->Fsub;
-      c.padB = maxBinsAll; c.C = t->C; c.M = t->M; c.direct = 0; c.hist = t->d_hist;
+      c.padB = maxBinsAll; c.C = t->C; c.M = t->M; c.direct = 0; c.hist = t->d_hist; c.rows_acc = t->dRowsAcc.p;
       c.dseg = t->dSeg.p; c.slot_pos = t->dSlotPos.p; c.idx0 = t->dIdx0.p; c.idx1 = t->dIdx1.p;
       e = launch_cls_hist(c, s);
       t->nKernels += 2;
@@ -964,13 +968,14 @@ int b2rf_trainer_group_info(const b2rf_trainer* t, int64_t* n_slots, int32_t* h_
 }
 
 int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts4) {
-  // h_counts4 has room for 6 entries: groups, hist launches, rows*trees scanned, learning nodes, kernel launches, hist algorithmic bytes
+  // h_counts4 has room for 8 entries: groups, hist launches, rows*trees scanned, learning nodes, kernel launches, hist algorithmic
+  // bytes, rows visited by the segment-mode K4 launches (x featuresPerNode = physical bin updates), featuresPerNode
   if (!t) return B2RF_ERR_ARG;
   if (h_seconds5) { h_seconds5[0] = 0; h_seconds5[1] = 0; h_seconds5[2] = t->tHist; h_seconds5[3] = t->tChoose; h_seconds5[4] = t->tTotal > 0 ? t->tTotal : now_s() - t->tStart; }
   if (h_counts4) {
     int64_t nodes = 0; for (auto& tr : t->trees) nodes += (int64_t)tr.size();
     h_counts4[0] = t->groupNo; h_counts4[1] = t->nHistLaunches; h_counts4[2] = t->nScanned; h_counts4[3] = nodes;
-    h_counts4[4] = t->nKernels; h_counts4[5] = (int64_t)t->histAlgBytes;
+    h_counts4[4] = t->nKernels; h_counts4[5] = (int64_t)t->histAlgBytes; h_counts4[6] = t->physRows; h_counts4[7] = t->Fsub;
   }
   return B2RF_OK;
 }

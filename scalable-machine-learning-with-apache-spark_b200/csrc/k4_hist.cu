@@ -562,13 +562,16 @@ static cudaError_t launch_bucket_sized(const BucketLaunch& b, cudaStream_t s) {
 }
 
 // ---- segment mode: task table from the nodes' row segments, then the same shared-memory histogram kernel ----
-__global__ void __launch_bounds__(1024) seg_tasks_kernel(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, int ticket) {
+__global__ void __launch_bounds__(1024) seg_tasks_kernel(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, int ticket,
+                                                         unsigned long long* rows_acc) {
   __shared__ uint32_t s_chunks[1024];
   const int tid = threadIdx.x;
   const int per = (n + 1023) / 1024;
   const int b = tid * per, e = min(n, b + per);
   uint32_t c = 0;
-  for (int i = b; i < e; i++) c += (dseg[pos[i]].count + CH - 1) / CH;
+  unsigned long long rows = 0;
+  for (int i = b; i < e; i++) { const uint32_t k = dseg[pos[i]].count; c += (k + CH - 1) / CH; rows += k; }
+  if (rows_acc && rows) atomicAdd(rows_acc, rows);
   s_chunks[tid] = c;
   __syncthreads();
   if (tid == 0) {
@@ -582,13 +585,14 @@ __global__ void __launch_bounds__(1024) seg_tasks_kernel(const DSeg* dseg, const
   for (int i = b; i < e; i++) { chunkPrefix[i] = c; c += (dseg[pos[i]].count + CH - 1) / CH; }
 }
 
-cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s, bool ticket) {
-  seg_tasks_kernel<<<1, 1024, 0, s>>>(dseg, pos, n, CH, chunkPrefix, ticket ? 1 : 0);
+cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s, bool ticket,
+                             unsigned long long* rows_acc) {
+  seg_tasks_kernel<<<1, 1024, 0, s>>>(dseg, pos, n, CH, chunkPrefix, ticket ? 1 : 0, rows_acc);
   return cudaGetLastError();
 }
 
 cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s) {
-  cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s);
+  cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s, false, b.rows_acc);
   if (e != cudaSuccess) return e;
   return launch_bucket_sized(b, s);
 }

@@ -29,7 +29,7 @@
 
 namespace b2rf {
 
-constexpr int LIMB_PLANES = 7;             // count, 3 limbs of sum w*q, 3 limbs of sum w*(q*q >> 53)
+constexpr int LIMB_PLANES = 7;             // count, 3 limbs of sum w*y, 3 limbs of sum w*y*y (both on the task's binary grid)
 constexpr uint32_t LIMB_MASK = (1u << 20) - 1u;
 constexpr int LIMB_EXP_MAX = 480;          // |exponent| of the task scale kept inside the range where 2^(2e-53) is a normal double
 
@@ -40,14 +40,17 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ double pow2d(int k) { return __hiloint2double((1023 + k) << 20, 0); }   // 2^k, k in the normal range
 
-// One row's fixed-point limbs: v0 = (w, a0, a1, a2), v1 = (b0, b1, b2, packed entry).
-__device__ __forceinline__ void limb_convert(uint32_t ent, double yv, double sY, uint4& v0, uint4& v1) {
+// One row's fixed-point limbs: v0 = (w, a0, a1, a2), v1 = (b0, b1, b2, packed entry).  The two products are MLlib's own
+// (instanceWeight * label, then * label, each rounded to fp64); what is cut into limbs is their exact value on the task's
+// binary grid: sY = 2^(53 - e), sP = 2^(53 - 2e) with 2^e <= max |y| < 2^(e+1), so |v| < 2^59 and u < 2^60, and every row in the
+// task's top binade converts without any rounding (a one-row node then gets sum = fl(w*y) and sumsq = fl(fl(w*y)*y) exactly as
+// MLlib computes them, hence impurity exactly 0).
+__device__ __forceinline__ void limb_convert(uint32_t ent, double yv, double sY, double sP, uint4& v0, uint4& v1) {
   const uint32_t w = ent >> 27;
-  const long long q = __double2ll_rn(yv * sY);                       // |q| < 2^54 (power-of-two scale: the product is exact)
-  const long long v = (long long)w * q;                              // |v| < 2^59
-  const unsigned long long aq = (unsigned long long)(q < 0 ? -q : q);
-  const unsigned long long t = (__umul64hi(aq, aq) << 11) | ((aq * aq) >> 53);   // floor(q*q / 2^53) < 2^55
-  const unsigned long long u = t * (unsigned long long)w;            // < 2^60
+  const double wy = (double)w * yv;
+  const double wyy = wy * yv;
+  const long long v = __double2ll_rn(wy * sY);
+  const unsigned long long u = __double2ull_rn(wyy * sP);
   v0 = make_uint4(w, (uint32_t)v & LIMB_MASK, (uint32_t)(v >> 20) & LIMB_MASK, (uint32_t)(int32_t)(v >> 40));
   v1 = make_uint4((uint32_t)u & LIMB_MASK, (uint32_t)(u >> 20) & LIMB_MASK, (uint32_t)(u >> 40), ent);
 }
@@ -136,7 +139,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
       continue;   // the next iteration's __syncthreads (ticket) separates the tasks
     }
 
-    const double sY = pow2d(53 - ey);
+    const double sY = pow2d(53 - ey), sP = pow2d(53 - 2 * ey);
     const int nblk = (n + BR - 1) / BR;
     uint32_t ent = 0u; double yv = 0.0;
     auto load = [&](int blk) {
@@ -150,7 +153,7 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
       uint4* vals = reinterpret_cast<uint4*>(tile + BR * ldr);
       if (lane < BR) {
         uint4 v0, v1;
-        limb_convert(ent, yv, sY, v0, v1);
+        limb_convert(ent, yv, sY, sP, v0, v1);
         vals[lane * 2] = v0; vals[lane * 2 + 1] = v1;
       }
       __syncwarp();
@@ -260,7 +263,7 @@ static cudaError_t launch_limb_g(const BucketLaunch& b, const LimbPlan& p, uint3
 cudaError_t launch_limb_hist(const BucketLaunch& b0, const LimbPlan& p, cudaStream_t s) {
   BucketLaunch b = b0;
   b.padB = p.padB; b.G = p.G;
-  cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s, /*ticket=*/true);
+  cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s, /*ticket=*/true, b.rows_acc);
   if (e != cudaSuccess) return e;
   uint32_t* ticket = const_cast<uint32_t*>(b.chunk_prefix) + b.nSlots + 1;
   const size_t smem = limb_smem(p.padB, p.G, (int)b.ldr, p.BR, p.threads);

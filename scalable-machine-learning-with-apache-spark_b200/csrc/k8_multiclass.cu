@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(CLS_THREADS) bucket_hist_cls_kernel(const ClsH
 }
 
 cudaError_t launch_cls_hist(const ClsHistLaunch& a0, cudaStream_t s) {
-  cudaError_t e = launch_seg_tasks(a0.dseg, a0.slot_pos, a0.nSlots, a0.CH, const_cast<uint32_t*>(a0.chunk_prefix), s);
+  cudaError_t e = launch_seg_tasks(a0.dseg, a0.slot_pos, a0.nSlots, a0.CH, const_cast<uint32_t*>(a0.chunk_prefix), s, false, a0.rows_acc);
   if (e != cudaSuccess) return e;
   ClsHistLaunch a = a0;
   size_t smem = (size_t)a.C * a.padB * 32 * 4;

@@ -59,7 +59,7 @@ def find_splits(sample: torch.Tensor, arity: torch.Tensor, max_possible_bins: in
     return thr, ns
 
 
-def sample_rows(X: torch.Tensor, row0_global: int, seed: int, fraction: float) -> torch.Tensor:
+def sample_rows(X: torch.Tensor, row0_global: int, seed: int, fraction: float, dist=None, group=None) -> torch.Tensor:
     """Row sample for findSplits when fraction < 1 (hash of the global row index)."""
     _require_cuda(X, "X")
     n, F = X.shape
@@ -69,7 +69,7 @@ def sample_rows(X: torch.Tensor, row0_global: int, seed: int, fraction: float) -
     check(lib().b2rf_sample_rows(X.data_ptr(), X.stride(0), n, row0_global, F, seed, float(fraction), out.data_ptr(), cap, cnt.data_ptr(),
                                  _stream()))
     k = int(cnt.item())
-    if k > cap:
+    if _agree_max(int(k > cap), dist, group, X.device):
         raise RuntimeError("b2rf sample_rows: capacity exceeded")
     return out[:k]
 
@@ -77,13 +77,26 @@ def sample_rows(X: torch.Tensor, row0_global: int, seed: int, fraction: float) -
 _bin_err = {}
 
 
-def _raise_bin_errors(arity):
-    """Raises MLlib's invalid-categorical-value error if any K2 launch on this device flagged one (deferred check)."""
+def _agree_max(code: int, dist, group, device) -> int:
+    """Largest `code` over the ranks of a sharded fit.  Data-dependent checks (labels, categorical values, sample capacity) sit
+    between collectives: if only the rank that holds the bad shard raised, the others would wait in NCCL forever, so every rank
+    learns the worst code first and all of them raise the same exception (MLlib: one IllegalArgumentException for the job)."""
+    if dist is None or dist.get_world_size(group) == 1:
+        return int(code)
+    t = torch.tensor([int(code)], dtype=torch.int64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
+    return int(t.item())
+
+
+def _raise_bin_errors(arity, dist=None, group=None):
+    """Raises MLlib's invalid-categorical-value error if any K2 launch on this device — or, in a sharded fit, on any rank —
+    flagged one (deferred check)."""
     err = _bin_err.get(arity.device)
-    if err is None:
-        return
-    e = int(err.item())
-    err.zero_()
+    e = 0
+    if err is not None:
+        e = int(err.item())
+        err.zero_()
+    e = _agree_max(e, dist, group, arity.device)
     if e:
         from ._lib import ERR_DATA, IllegalArgumentException
         f = e - 1
@@ -180,6 +193,14 @@ def default_partitions(n_rows: int, rows_per_partition: int = 4096):
 
 
 _HIST_MODES = {"segment": 0, "bucket": 0, "sort": 1, "scan": 2}
+MAX_LIST_ROWS = 1 << 27     # segment / sort mode pack (row, bag weight) into 32 bits: 27-bit row ids per GPU
+
+
+def _want_node(hist_mode, bins_rm, n_local) -> bool:
+    """The per-(tree, row) node cache is what the scan mode routes rows with.  Segment / sort mode keep packed row lists instead,
+    which hold 27-bit row ids: a shard of 2^27 (134M) rows or more on one GPU runs the scan mode (slower; shard the rows over
+    more GPUs to stay on the list-based kernels) and so needs the cache."""
+    return hist_mode not in ("segment", "bucket") or bins_rm is None or n_local >= MAX_LIST_ROWS
 
 
 def _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode):
@@ -203,12 +224,14 @@ def _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode
                 fraction=fraction, arity_d=torch.as_tensor(arity_np, device=dev))
 
 
-def _check_labels(y, params):
-    """Classification labels must be the integers 0 .. numClasses - 1 (MLlib: 'Classification labels should be in [0 to ...]')."""
-    if not params.is_classification or not y.numel():
+def _check_labels(y, params, dist=None, group=None, device=None):
+    """Classification labels must be the integers 0 .. numClasses - 1 (MLlib: 'Classification labels should be in [0 to ...]').
+    In a sharded fit every rank raises when any rank holds a bad label."""
+    if not params.is_classification:
         return
     C_ = params.num_classes
-    if not bool(((y >= 0) & (y < C_) & (y == y.floor())).all()):
+    bad = bool(y.numel()) and not bool(((y >= 0) & (y < C_) & (y == y.floor())).all())
+    if _agree_max(int(bad), dist, group, device if device is not None else y.device):
         from ._lib import IllegalArgumentException
         raise IllegalArgumentException(-3, f"requirement failed: Classification labels should be in [0 to {C_ - 1}] (numClasses == {C_}; pass "
                                            f"TreeParams(numClasses=...) for more than two classes). Found invalid labels.")
@@ -259,9 +282,14 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
         st = _stream()
         if dbg:
             torch.cuda.synchronize(dev); tb = time.perf_counter()
+        ar_events = []
         while check(L.b2rf_trainer_begin_group(h, C.byref(ncell), st)) == 1:
             if S["world"] > 1:
+                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                ev[0].record()
                 S["dist"].all_reduce(hist[: ncell.value * 4], group=group)   # DTStatsAggregator.merge (reduceByKey), row a7
+                ev[1].record()
+                ar_events.append(ev)
             if hist_hook is not None:   # debug / parity tests: the reduced group histogram next to the group's slot table
                 hist_hook(_group_info(h, min(S["cp"].featuresPerNode, F) if S["cp"].featuresPerNode > 0 else F), hist[: ncell.value * 4].view(-1, 4))
             check(L.b2rf_trainer_end_group(h, st))
@@ -275,6 +303,7 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
         print(f"[b2rf timing] create+bind {tb - tc:.4f} groups {tl - tb:.4f} export {te - tl:.4f} destroy {time.perf_counter() - te:.4f}", flush=True)
     forest.thresholds, forest.nsplits = thr_h, ns_h
     forest.impurity_kind = params.impurity
+    forest.timers["allreduce"] = sum(a.elapsed_time(b) for a, b in ar_events) * 1e-3     # device time of the histogram reductions
     forest.counters.update(rows=S["N"], rows_local=n_local, partitions=len(S["po"]) - 1, world=S["world"], fraction=S["fraction"])
     return forest
 
@@ -297,16 +326,16 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
     t_start = time.perf_counter()
     with torch.cuda.device(dev):
         y = y.to(torch.float64).contiguous()
-        _check_labels(y, params)
         n_local, F = X.shape
         S = _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode)
+        _check_labels(y, params, S["dist"], group, dev)
         T = params.numTrees
         torch.cuda.synchronize(dev)
         t0 = time.perf_counter()
 
         # ---- findSplits (K1) ----
         fraction = S["fraction"]
-        samp = sample_rows(X, S["row0"], params.seed, fraction) if fraction < 1.0 else X
+        samp = sample_rows(X, S["row0"], params.seed, fraction, S["dist"], group) if fraction < 1.0 else X
         samp = gather_samples(samp, S["dist"], group)
         thr, ns = find_splits(samp, S["arity_d"], S["mpb"], fraction * float(S["N"]))
         thr_h = thr.cpu().numpy()
@@ -325,11 +354,12 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
             bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
             if dbg:
                 torch.cuda.synchronize(dev); ta = time.perf_counter()
-            bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm)
+            bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm, check_errors=False)
+            _raise_bin_errors(S["arity_d"], S["dist"], group)
             if dbg:
                 torch.cuda.synchronize(dev); tb = time.perf_counter()
         w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
-                      want_node=(hist_mode not in ("segment", "bucket") or bins_rm is None))
+                      want_node=_want_node(hist_mode, bins_rm, n_local))
         torch.cuda.synchronize(dev)
         t2 = time.perf_counter()
         if dbg and prebinned is None:
@@ -361,8 +391,6 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
     params_list = list(params_list)
     with torch.cuda.device(dev):
         y = y.to(torch.float64).contiguous()
-        for params in params_list:
-            _check_labels(y, params)
         n_local, F = X.shape
         ld = _pad(n_local)
         shared = {}
@@ -370,20 +398,22 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
         main = torch.cuda.current_stream()
         for params in params_list:
             S = _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode)
+            _check_labels(y, params, S["dist"], group, dev)
             key = (params.maxBins, params.seed)
             if key not in shared:
                 fraction = S["fraction"]
-                samp = sample_rows(X, S["row0"], params.seed, fraction) if fraction < 1.0 else X
+                samp = sample_rows(X, S["row0"], params.seed, fraction, S["dist"], group) if fraction < 1.0 else X
                 samp = gather_samples(samp, S["dist"], group)
                 thr, ns = find_splits(samp, S["arity_d"], S["mpb"], fraction * float(S["N"]))
                 code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
                 bins = torch.empty((F, ld), dtype=code_dt, device=dev)
                 bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
-                bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm)
+                bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm, check_errors=False)
+                _raise_bin_errors(S["arity_d"], S["dist"], group)
                 shared[key] = (thr.cpu().numpy(), ns.cpu().numpy(), bins, bins_rm)
             thr_h, ns_h, bins, bins_rm = shared[key]
             w, node = bag(params.seed, S["po"], S["part0"], params.numTrees, params.subsamplingRate, params.bootstrap, dev, ld=ld,
-                          want_node=(hist_mode not in ("segment", "bucket") or bins_rm is None))
+                          want_node=_want_node(hist_mode, bins_rm, n_local))
             cands.append(dict(S=S, params=params, thr_h=thr_h, ns_h=ns_h, bins=bins, bins_rm=bins_rm, w=w, node=node, h=C.c_void_p(),
                               stream=torch.cuda.Stream(), ncell=C.c_int64()))
         torch.cuda.synchronize(dev)
@@ -462,8 +492,8 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
     t_start = time.perf_counter()
     with torch.cuda.device(dev):
         n_local, F = Xh.shape
-        _check_labels(yh, params)
         S = _setup(n_local, F, arity, params, part_offsets, part0, group, dev, hist_mode)
+        _check_labels(yh, params, S["dist"], group, dev)
         T = params.numTrees
         main = torch.cuda.current_stream()
         copy_s, bag_s = torch.cuda.Stream(), torch.cuda.Stream()
@@ -474,7 +504,7 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
         bag_s.wait_stream(main)
         with torch.cuda.stream(bag_s):
             w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
-                          want_node=(hist_mode not in ("segment", "bucket")))
+                          want_node=_want_node(hist_mode, True, n_local))
         t0 = time.perf_counter()
         # K1 on the host-gathered sample
         fraction = S["fraction"]
@@ -506,7 +536,7 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
             bin_features(stage[b][: r1 - r0], thr, ns, S["arity_d"], bins=bins, row0=r0, bins_rm=bins_rm, check_errors=False)
             binned[b].record(main)
         main.wait_stream(bag_s)
-        _raise_bin_errors(S["arity_d"])
+        _raise_bin_errors(S["arity_d"], S["dist"], group)
         torch.cuda.synchronize(dev)
         t2 = time.perf_counter()
         if os.environ.get("B2RF_TIMING") == "1":
@@ -525,7 +555,7 @@ def _export(h, F: int, keep_trace: bool) -> Forest:
     check(L.b2rf_trainer_forest_sizes(h, C.byref(nn), C.byref(nc)))
     n, ncat = nn.value, nc.value
     sec = np.zeros(5)
-    cnt = np.zeros(6, np.int64)
+    cnt = np.zeros(8, np.int64)
     L.b2rf_trainer_stats(h, sec.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p))
     T = None
     # number of trees = len(tree_off) - 1; query through a first export of tree_off sized generously
@@ -554,7 +584,8 @@ def _export(h, F: int, keep_trace: bool) -> Forest:
         fo.counts = cc[:n]
     fo.timers = dict(findBestSplits=float(sec[2]), chooseSplits=float(sec[3]))
     fo.counters = dict(groups=int(cnt[0]), hist_launches=int(cnt[1]), rows_trees_scanned=int(cnt[2]), learning_nodes=int(cnt[3]),
-                       kernel_launches=int(cnt[4]), hist_alg_bytes=int(cnt[5]))
+                       kernel_launches=int(cnt[4]), hist_alg_bytes=int(cnt[5]), k4_rows_visited=int(cnt[6]),
+                       bin_updates=int(cnt[6]) * int(cnt[7]))
     if keep_trace:
         nt = int(L.b2rf_trainer_trace_size(h))
         ti, td = Z((nt, 5), np.int32), Z((nt, 5), np.float64)

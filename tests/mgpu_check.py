@@ -13,16 +13,16 @@ sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
-def main():
-    rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
-    torch.cuda.set_device(lr)
-    dev = torch.device("cuda", lr)
-    dist.init_process_group("nccl", device_id=dev)
+def run_cases(dev, rank, world, log=print) -> str:
+    """Runs the sharded fits on an initialised process group and checks them on rank 0 against the CPU oracle's fit of the whole
+    dataset.  Returns "ok" or the first failure (the same string on every rank).  Used by main() below and by bench.py, which
+    runs it before its timed region whenever WORLD_SIZE > 1 and reports the result as "mgpu_parity"."""
     import b2rf
     from b2rf import trainer
     from helpers import assert_forest_parity, assert_parity_allowing_ties, assert_trace_parity
     from oracle import oracle as O
     ok = True
+    first = ""
     for name, gen, n, kw in [("airbnb-rf", b2rf.synth.airbnb, 6001, dict(maxDepth=7, maxBins=40, numTrees=12, bootstrap=True, seed=42)),
                              ("airbnb-dt", b2rf.synth.airbnb, 5716, dict(maxDepth=5, maxBins=40)),
                              ("c3-slice", lambda m, row0=0: b2rf.synth.c3(m, row0=row0, device="cpu"), 90000,
@@ -51,10 +51,11 @@ def main():
                       **{k: v for k, v in kw.items()})
             try:
                 assert_parity_allowing_ties(g, o, max_ties=2)
-                print(f"[mgpu] {name}: world={world} OK ({g.num_nodes()} nodes, groups={g.counters['groups']})", flush=True)
+                log(f"[mgpu] {name}: world={world} OK ({g.num_nodes()} nodes, groups={g.counters['groups']})")
             except AssertionError as e:
                 ok = False
-                print(f"[mgpu] {name}: FAILED {e}", flush=True)
+                first = first or f"{name}: {str(e)[:200]}"
+                log(f"[mgpu] {name}: FAILED {e}")
     # ---- classifiers: binary (class counts ride on the regression statistics) and three classes (per-class histograms, all-reduced
     # as cells of 4 * ceil(C / 4) doubles); integer statistics, so the sharded fit must equal the restatement exactly ----
     from helpers import assert_classifier_parity
@@ -85,15 +86,27 @@ def main():
                     m = M.fit(Xa, lab, arity, C_, part_offsets=np.array(po), impurity="gini", **kw)
                     for a in ("tree_off", "feature", "threshold", "left", "right", "prediction", "impurity", "gain", "class_counts", "trace_i"):
                         assert np.array_equal(getattr(g, a), getattr(m, a)), a
-                print(f"[mgpu] {name}: world={world} OK ({g.num_nodes()} nodes, groups={g.counters['groups']})", flush=True)
+                log(f"[mgpu] {name}: world={world} OK ({g.num_nodes()} nodes, groups={g.counters['groups']})")
             except AssertionError as e:
                 ok = False
-                print(f"[mgpu] {name}: FAILED {e}", flush=True)
-    flag = torch.tensor([1 if ok else 0], device=dev)
-    dist.broadcast(flag, 0)
+                first = first or f"{name}: {str(e)[:200]}"
+                log(f"[mgpu] {name}: FAILED {e}")
+    msg = [("ok" if ok else "FAILED " + first) if rank == 0 else ""]
+    dist.broadcast_object_list(msg, src=0)
     dist.barrier()
+    return msg[0]
+
+
+def main():
+    rank, world, lr = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(lr)
+    dev = torch.device("cuda", lr)
+    dist.init_process_group("nccl", device_id=dev)
+    res = run_cases(dev, rank, world, log=lambda m: print(m, flush=True))
+    if rank == 0:
+        print(f"[mgpu] result: {res}", flush=True)
     dist.destroy_process_group()
-    sys.exit(0 if int(flag.item()) else 1)
+    sys.exit(0 if res == "ok" else 1)
 
 
 if __name__ == "__main__":
