@@ -289,6 +289,7 @@ struct b2rf_trainer {
   DevBuf<uint32_t> dIdx0, dIdx1, dPartPrefix, dLeftCnt, dLeftOff, dPredBits;
   DevBuf<double> dY0, dY1;      // labels carried with the row lists (same positions), when memory allows: K4 then reads them as a stream
   bool carryY = false;
+  bool labelsInt = false;       // every local label is an integer of magnitude <= 2^24: the narrow (7-plane) limb kernel is exact
   DevBuf<unsigned long long> dBindTmp;
   DevBuf<unsigned long long> dRowsAcc;   // rows visited by the K4 launches of this fit (segment mode)
   int64_t physRows = 0;
@@ -522,6 +523,15 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
         if (want && cudaMemGetInfo(&freeB, &totB) == cudaSuccess && (have >= 2 * total * 8 || freeB + have > 2 * total * 8 + ((size_t)4 << 30)))
           t->carryY = t->dY0.ensure(total) && t->dY1.ensure(total);
         if (!t->carryY) { t->dY0.release(); t->dY1.release(); }
+      }
+      t->labelsInt = false;
+      if (ok && t->carryY) {   // one pass over the labels decides which limb form is exact for this fit
+        int32_t one = 1, flag = 0;
+        int32_t* d_flag = reinterpret_cast<int32_t*>(t->dBindTmp.p);    // the in-bag totals have been read back already
+        ok = ok && cuda_ok(cudaMemcpy(d_flag, &one, 4, cudaMemcpyHostToDevice), "bind copy");
+        ok = ok && cuda_ok(launch_labels_integer(d_y, n_rows_local, d_flag, 0), "label scan");
+        ok = ok && cuda_ok(cudaMemcpy(&flag, d_flag, 4, cudaMemcpyDeviceToHost), "bind copy");
+        t->labelsInt = ok && flag != 0;
       }
       ok = ok && cuda_ok(cudaMemcpy(d_base, t->treeBase.data(), (size_t)(t->T + 1) * 8, cudaMemcpyHostToDevice), "bind copy");
       ok = ok && cuda_ok(launch_compact_write(d_w, ldw, t->T, n_rows_local, blockCnt.p, d_base, t->dIdx0.p, d_y, t->carryY ? t->dY0.p : nullptr, 0),
@@ -782,7 +792,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       // compare-and-swap kernels, which also serve what the limb kernel does not (uint16 codes, labels not carried, huge histograms)
       const bool fp64Only = opt_k4_fp64().load() != 0;
       LimbPlan plan;
-      if (!fp64Only && limb_plan(b, maxBinsAll, &plan)) e = launch_limb_hist(b, plan, s);
+      if (!fp64Only && limb_plan(b, maxBinsAll, t->labelsInt, &plan)) e = launch_limb_hist(b, plan, s);
       else e = launch_segment_hist(b, s);
       t->nKernels += 2;
     } else {

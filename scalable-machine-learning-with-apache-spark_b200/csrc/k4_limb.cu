@@ -1,23 +1,27 @@
 // b2rf (sm_100a) — K4, limb form (DTStatsAggregator.update via binSeqOp): the default histogram kernel of segment mode.
 //
-// Why.  Shared memory has one native read-modify-write wide enough to be cheap: the 32-bit integer add (SASS ATOMS.ADD, one
-// wavefront, nothing returned).  An fp64 add is a load + compare-and-swap loop (ATOMS.CAST.SPIN.64), about seven wavefronts and
-// a dozen instructions, and the (count, sum w*y, sum w*y*y) update of the fp64 kernel (k4_hist.cu) spent 19 shared-memory
-// wavefronts and 51 warp instructions per row.  Here a task (node slot, <= 4096-row chunk, feature group) first takes the
-// largest label magnitude of its rows, which fixes one binary scale for the task, and every row's w*y and w*y*y become
-// fixed-point integers cut into three 20-bit limbs each.  4096 rows x 20 bits cannot overflow a 32-bit counter, so an update is
-// seven independent native adds (count + 3 + 3) with no carries, and the per-task sums are EXACT integers (order-independent);
-// they are converted to fp64 once per task and added to the global histogram with RED.ADD.F64, as before.
-//   * resolution: |y| <= Ymax_task maps to |q| < 2^54, so labels at the task's top binade keep all 53 mantissa bits and the
-//     absolute error of a task sum is below 2^-56 * Ymax_task per row — at or below what sequential fp64 summation commits.
-//   * integer-valued labels (and class indicators) give bit-exact sums.
-//   * tasks whose labels are not finite, or so large / small that y*y leaves the normal fp64 range (|y| beyond 2^+-480), take
-//     the plain fp64 path (global atomics, MLlib's own overflow / underflow behaviour), as do tasks with fewer updates than cells.
-// Data path.  Labels travel WITH the per-tree row lists (y list parallel to the packed row | weight list, moved by the K6
-// partitions), so a row visit costs one 64 B code-row gather instead of that plus a 32 B label sector; the code rows of the
-// next 32-row block are copied global -> shared asynchronously (cp.async, SASS LDGSTS, two stages per warp) while the warp adds
-// the current block, and a lane reads its feature's code with one LDS.U8 at an immediate offset: no 64-bit address arithmetic
-// and no load-to-use stall in the add loop.  Per row: 3 shared loads + 1 multiply-add + 7 adds.
+// Why.  Shared memory has one native read-modify-write that is cheap: the 32-bit integer add (SASS ATOMS.ADD, one wavefront,
+// nothing returned).  An fp64 add is a load + compare-and-swap loop (ATOMS.CAST.SPIN.64): the (count, sum w*y, sum w*y*y) update of
+// the fp64 kernels (k4_hist.cu) costs 19 shared-memory wavefronts and 51 warp instructions per row.  Here every row's two
+// products — MLlib's own fl(w*y) and fl(fl(w*y)*y) — are placed on a binary grid fixed per task (node slot, <= 4096-row chunk,
+// feature group) by the largest label magnitude of the task's rows, and cut into 20-bit limbs; 4096 rows x 20 bits cannot
+// overflow a 32-bit counter, so an update is a handful of independent native adds with no carries.
+//   * The grid is wide enough that a row converts WITHOUT rounding unless its label is more than ~2^-11 below the task's largest
+//     (80-bit windows, four limbs per sum: "wide" form, 9 adds per update), so a cell holds the EXACT sum of MLlib's per-row
+//     terms, rounded to fp64 once when the task's histogram is added to the global one (RED.ADD.F64).  Whatever MLlib computes
+//     exactly (one-row cells, equal labels, integer labels, class indicators) comes out bit-identical — which matters
+//     structurally: a child whose impurity is exactly 0 is a leaf and never draws a feature subset.
+//   * Rows that would need rounding (labels tiny next to the task's largest) are not put on the grid at all: their three fp64
+//     terms go straight to the global histogram, so a cell that holds only such a row is still exact.
+//   * When all labels of the fit are integers of modest size (classification; the labs' price labels) the 60-bit windows of
+//     the "narrow" form (three limbs per sum, 7 adds per update) are exact for every row, and that form runs.
+//   * Tasks whose labels are not finite or lie outside 2^+-460 take the plain fp64 path (global atomics: MLlib's own overflow /
+//     underflow behaviour), as do tasks with fewer updates than histogram cells.
+// Data path.  Labels travel WITH the per-tree row lists (a y list parallel to the packed row | weight list, moved by the K6
+// partitions): a row visit costs one code-row gather instead of that plus a 32 B label sector.  The code rows of the next block
+// are fetched by the TMA engine — one bulk async copy per row (cp.async.bulk, SASS UBLKCP) completing on an mbarrier, two
+// stages per warp — while the warp adds the current block; a lane reads its feature's code with one LDS.U8 and the row's packed
+// limbs with one or two broadcast loads at immediate offsets: no 64-bit address arithmetic and no load-to-use stall in the loop.
 // Compiled with -fmad=false like the rest of the library.
 #include "b2rf_internal.h"
 #include "b2rf_device.cuh"
@@ -29,36 +33,68 @@
 
 namespace b2rf {
 
-constexpr int LIMB_PLANES = 7;             // count, 3 limbs of sum w*y, 3 limbs of sum w*y*y (both on the task's binary grid)
 constexpr uint32_t LIMB_MASK = (1u << 20) - 1u;
-constexpr int LIMB_EXP_MAX = 480;          // |exponent| of the task scale kept inside the range where 2^(2e-53) is a normal double
+constexpr int LIMB_EXP_MAX = 460;          // |exponent| of the task scale kept inside the range where every scale factor is a normal double
+constexpr int LIMB_WBITS = 5;              // bag weights are packed in 5 bits (<= 31)
 
-__device__ __forceinline__ void cp_async16(uint32_t dst_smem, const void* src, uint32_t nbytes) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(nbytes) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N> __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 __device__ __forceinline__ double pow2d(int k) { return __hiloint2double((1023 + k) << 20, 0); }   // 2^k, k in the normal range
+__device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+               : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+  return ok != 0;
+}
 
-// One row's fixed-point limbs: v0 = (w, a0, a1, a2), v1 = (b0, b1, b2, packed entry).  The two products are MLlib's own
-// (instanceWeight * label, then * label, each rounded to fp64); what is cut into limbs is their exact value on the task's
-// binary grid: sY = 2^(53 - e), sP = 2^(53 - 2e) with 2^e <= max |y| < 2^(e+1), so |v| < 2^59 and u < 2^60, and every row in the
-// task's top binade converts without any rounding (a one-row node then gets sum = fl(w*y) and sumsq = fl(fl(w*y)*y) exactly as
-// MLlib computes them, hence impurity exactly 0).
-__device__ __forceinline__ void limb_convert(uint32_t ent, double yv, double sY, double sP, uint4& v0, uint4& v1) {
-  const uint32_t w = ent >> 27;
-  const double wy = (double)w * yv;
-  const double wyy = wy * yv;
-  const long long v = __double2ll_rn(wy * sY);
-  const unsigned long long u = __double2ull_rn(wyy * sP);
-  v0 = make_uint4(w, (uint32_t)v & LIMB_MASK, (uint32_t)(v >> 20) & LIMB_MASK, (uint32_t)(int32_t)(v >> 40));
-  v1 = make_uint4((uint32_t)u & LIMB_MASK, (uint32_t)(u >> 20) & LIMB_MASK, (uint32_t)(u >> 40), ent);
+// Per-task grid.  2^ey <= max |y| < 2^(ey+1); |w*y| < 2^Ea and w*y*y < 2^Eb with Ea = ey + 1 + 5, Eb = 2 ey + 2 + 5.
+//   narrow: v = w*y * 2^(59 - Ea) (|v| < 2^59), u = w*y*y * 2^(60 - Eb) (u < 2^60): three 20-bit limbs each
+//   wide  : w*y * 2^(39 - Ea) = hi + lo / 2^40 with |hi| < 2^39, 0 <= lo < 2^40 (four limbs), likewise w*y*y * 2^(40 - Eb)
+struct LimbScale { double sa, sb; };
+
+// Packed values of one row.  Narrow form, one 16-byte word:
+//   x = (v mod 2^59) | w << 59 ;  y = u | slow << 63          (slow rows: x = label bits, y = w | 1 << 63)
+__device__ __forceinline__ uint4 limb_pack_narrow(uint32_t w, double yv, LimbScale sc) {
+  const double wy = (double)w * yv, wyy = wy * yv;                     // MLlib: instanceWeight * label, then * label
+  const double ta = wy * sc.sa, tb = wyy * sc.sb;
+  const long long v = __double2ll_rn(ta);
+  const unsigned long long u = __double2ull_rn(tb);
+  unsigned long long x, y;
+  if ((double)v == ta && (double)u == tb) {                            // on the grid: exact
+    x = ((unsigned long long)v & ((1ull << 59) - 1ull)) | ((unsigned long long)w << 59);
+    y = u;
+  } else {
+    x = (unsigned long long)__double_as_longlong(yv);
+    y = (unsigned long long)w | (1ull << 63);
+  }
+  return make_uint4((uint32_t)x, (uint32_t)(x >> 32), (uint32_t)y, (uint32_t)(y >> 32));
+}
+// Wide form, 24 bytes: x0 = loA | w << 40 | slow << 47 | (hiB >> 24) << 48 ;  x1 = hiA (two's complement) ;  x2 = loB | (hiB & 0xffffff) << 40
+// (slow rows: x0 = w << 40 | 1 << 47, x1 = label bits)
+__device__ __forceinline__ void limb_pack_wide(uint32_t w, double yv, LimbScale sc, uint4& p0, uint2& p1) {
+  const double wy = (double)w * yv, wyy = wy * yv;
+  const double ta = wy * sc.sa, tb = wyy * sc.sb;                       // |ta| < 2^39, 0 <= tb < 2^40 (power-of-two scales: exact)
+  const double ta40 = ta * 0x1p40, tb40 = tb * 0x1p40;
+  unsigned long long x0, x1, x2;
+  if (ta40 == rint(ta40) && tb40 == rint(tb40)) {                      // no bits below the window: the row is on the grid
+    const double fa = floor(ta), fb = floor(tb);
+    const long long hiA = __double2ll_rz(fa);                           // fractional parts: exact (their exact values are representable)
+    const unsigned long long loA = __double2ull_rz((ta - fa) * 0x1p40), hiB = __double2ull_rz(fb), loB = __double2ull_rz((tb - fb) * 0x1p40);
+    x0 = loA | ((unsigned long long)w << 40) | ((hiB >> 24) << 48);
+    x1 = (unsigned long long)hiA;
+    x2 = loB | ((hiB & 0xffffffull) << 40);
+  } else {
+    x0 = ((unsigned long long)w << 40) | (1ull << 47);
+    x1 = (unsigned long long)__double_as_longlong(yv);
+    x2 = 0ull;
+  }
+  p0 = make_uint4((uint32_t)x0, (uint32_t)(x0 >> 32), (uint32_t)x1, (uint32_t)(x1 >> 32));
+  p1 = make_uint2((uint32_t)x2, (uint32_t)(x2 >> 32));
 }
 
 // G    features per task group = lanes per row (32, 16 or 8); a warp instruction covers 32/G rows
 // LDR  bytes per row of the row-major code matrix (0: read a.ldr)
-// BR   rows per staged block (32, or 16 when rows are wide and shared memory is short)
-template <int G, int LDR, int BR, int THREADS>
+// BR   rows per staged block (32 or 16)
+// NP   planes per cell: 7 = count + 3 + 3 limbs (narrow), 9 = count + 4 + 4 (wide)
+template <int G, int LDR, int BR, int THREADS, int NP>
 __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_kernel(const BucketLaunch a, uint32_t* ticket) {
   extern __shared__ __align__(16) unsigned char smraw[];
   __shared__ uint32_t s_red[THREADS / 32];
@@ -66,19 +102,30 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
   constexpr int W = THREADS / 32;
   constexpr int R = 32 / G;                  // rows per warp instruction
   constexpr int NU = BR / R;                 // warp instructions per staged block
+  constexpr bool WIDE = NP == 9;
+  constexpr int VB = WIDE ? 32 : 16;         // bytes of packed values per row (wide: 24 used)
   constexpr unsigned FULL = 0xffffffffu;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ldr = LDR ? LDR : (int)a.ldr;
-  const int cpr = ldr >> 4;                  // 16-byte pieces per code row
   const int padB = a.padB;
-  uint32_t* hist = reinterpret_cast<uint32_t*>(smraw);                 // [padB][7][G]
-  const size_t histBytes = (size_t)padB * LIMB_PLANES * G * 4;
-  const int stageBytes = BR * ldr + BR * 32;
+  uint32_t* hist = reinterpret_cast<uint32_t*>(smraw);                 // [padB][NP][G]
+  const size_t histBytes = (size_t)padB * NP * G * 4;
+  const int stageBytes = BR * ldr + BR * VB;
   unsigned char* ring = smraw + histBytes + (size_t)warp * 2 * stageBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smraw + histBytes + (size_t)W * 2 * stageBytes) + warp * 2;
   const int fl = lane & (G - 1), r = lane / G;
   const int nG = (a.Fsub + G - 1) / G;
   const uint32_t total = a.chunk_prefix[a.nSlots] * (uint32_t)nG;
   const uint8_t* bins_rm = a.bins_rm;
+
+  // staged code rows of blocks that are not full keep whatever the slot held before; rows past the end of a chunk carry zero limbs,
+  // so such a code only has to be a valid bin index: start from zeros (and every later content is a real code row)
+  for (int c = lane; c < (2 * stageBytes) >> 4; c += 32) reinterpret_cast<uint4*>(ring)[c] = make_uint4(0u, 0u, 0u, 0u);
+  if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");          // generic-proxy zeros before the async proxy writes the same bytes
+  __syncthreads();
+  uint32_t phase = 0u;                                                   // bit s: parity the next wait on stage s expects
 
   for (;;) {
     if (tid == 0) s_task = atomicAdd(ticket, 1u);
@@ -139,7 +186,10 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
       continue;   // the next iteration's __syncthreads (ticket) separates the tasks
     }
 
-    const double sY = pow2d(53 - ey), sP = pow2d(53 - 2 * ey);
+    const int Ea = ey + 1 + LIMB_WBITS, Eb = 2 * ey + 2 + LIMB_WBITS;
+    LimbScale sc;
+    sc.sa = pow2d((WIDE ? 39 : 59) - Ea);
+    sc.sb = pow2d((WIDE ? 40 : 60) - Eb);
     const int nblk = (n + BR - 1) / BR;
     uint32_t ent = 0u; double yv = 0.0;
     auto load = [&](int blk) {
@@ -148,61 +198,104 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
       ent = in ? rl[i] : 0u;
       yv = in ? yl[i] : 0.0;
     };
-    auto stage = [&](int s) {
+    // stage block blk into slot s: packed values by plain stores, code rows by one bulk async copy per row (TMA engine)
+    auto stage = [&](int s, int blk) {
       unsigned char* tile = ring + s * stageBytes;
-      uint4* vals = reinterpret_cast<uint4*>(tile + BR * ldr);
+      unsigned char* vals = tile + BR * ldr;
+      const uint32_t w = ent >> 27;
       if (lane < BR) {
-        uint4 v0, v1;
-        limb_convert(ent, yv, sY, sP, v0, v1);
-        vals[lane * 2] = v0; vals[lane * 2 + 1] = v1;
+        if (WIDE) {
+          uint4 p0; uint2 p1;
+          limb_pack_wide(w, yv, sc, p0, p1);
+          *reinterpret_cast<uint4*>(vals + lane * VB) = p0;
+          *reinterpret_cast<uint2*>(vals + lane * VB + 16) = p1;
+        } else {
+          *reinterpret_cast<uint4*>(vals + lane * VB) = limb_pack_narrow(w, yv, sc);
+        }
       }
+      const int nvalid = min(BR, n - blk * BR);
+      if (lane == 0) mbar_expect_tx(&bars[s], (uint32_t)(nvalid * ldr));
       __syncwarp();
-      const uint32_t tile_s = smem_u32(tile);
-      for (int c = lane; c < BR * cpr; c += 32) {
-        const int row = c / cpr, seg = c - row * cpr;
-        const uint32_t e2 = reinterpret_cast<const uint32_t*>(vals)[row * 8 + 7];
-        const bool valid = (e2 >> 27) != 0u;                           // rows past the end of the chunk: zero-filled code row, zero limbs
-        const uint8_t* src = valid ? bins_rm + (size_t)(e2 & 0x7ffffffu) * ldr + seg * 16 : bins_rm;
-        cp_async16(tile_s + c * 16, src, valid ? 16u : 0u);
-      }
-      cp_async_commit();
+      if (lane < nvalid) bulk_g2s(tile + lane * ldr, bins_rm + (size_t)(ent & 0x7ffffffu) * ldr, (uint32_t)ldr, &bars[s]);
     };
     int b = warp;
-    if (b < nblk) { load(b); stage(0); load(b + W); }
+    if (b < nblk) { load(b); stage(0, b); load(b + W); }
     uint32_t* hcell = hist + fl;
     for (int k = 0; b < nblk; k++, b += W) {
       const int s = k & 1;
-      if (b + W < nblk) { stage(s ^ 1); load(b + 2 * W); cp_async_wait<1>(); }
-      else cp_async_wait<0>();
+      if (b + W < nblk) { stage(s ^ 1, b + W); load(b + 2 * W); }
+      while (!mbar_try(&bars[s], (phase >> s) & 1u)) { }
+      phase ^= 1u << s;
       __syncwarp();
       const unsigned char* tl = ring + s * stageBytes + r * ldr + e.x;
-      const uint4* vv = reinterpret_cast<const uint4*>(ring + s * stageBytes + BR * ldr) + r * 2;
+      const unsigned char* vv = ring + s * stageBytes + BR * ldr + r * VB;
       if (active) {
-        // one row ahead: the next row's code and limbs are loaded before this row's adds are issued (the compiler keeps shared
-        // loads behind earlier shared atomics, so the overlap has to be written out)
+        // one row ahead: the next row's code and packed limbs are loaded before this row's adds are issued (the compiler keeps
+        // shared loads behind earlier shared atomics, so the overlap has to be written out)
         uint32_t code = tl[0];
-        uint4 v0 = vv[0], v1 = vv[1];
+        uint4 q0 = *reinterpret_cast<const uint4*>(vv);
+        uint2 q1 = WIDE ? *reinterpret_cast<const uint2*>(vv + 16) : make_uint2(0u, 0u);
 #pragma unroll
         for (int u = 0; u < NU; u++) {
-          const uint32_t cc = code; const uint4 w0 = v0, w1 = v1;
-          if (u + 1 < NU) { code = tl[(u + 1) * R * ldr]; v0 = vv[(u + 1) * R * 2]; v1 = vv[(u + 1) * R * 2 + 1]; }
-          uint32_t* c = hcell + cc * (LIMB_PLANES * G);
-          atomicAdd(c, w0.x); atomicAdd(c + G, w0.y); atomicAdd(c + 2 * G, w0.z); atomicAdd(c + 3 * G, w0.w);
-          atomicAdd(c + 4 * G, w1.x); atomicAdd(c + 5 * G, w1.y); atomicAdd(c + 6 * G, w1.z);
+          const uint32_t cc = code; const uint4 p0 = q0; const uint2 p1 = q1;
+          if (u + 1 < NU) {
+            code = tl[(u + 1) * R * ldr];
+            q0 = *reinterpret_cast<const uint4*>(vv + (u + 1) * R * VB);
+            if (WIDE) q1 = *reinterpret_cast<const uint2*>(vv + (u + 1) * R * VB + 16);
+          }
+          uint32_t* c = hcell + cc * (NP * G);
+          const unsigned long long x0 = ((unsigned long long)p0.y << 32) | p0.x, x1 = ((unsigned long long)p0.w << 32) | p0.z;
+          if (WIDE) {
+            const uint32_t w = (p0.y >> 8) & 31u;
+            if (p0.y & (1u << 15)) {                                   // slow row: its fp64 terms go straight to the global histogram
+              const double ys = __longlong_as_double((long long)x1);
+              const double wy = (double)w * ys;
+              double* gc = hb + (size_t)(e.y + cc) * 4;
+              atomicAdd(gc, (double)w); atomicAdd(gc + 1, wy); atomicAdd(gc + 2, wy * ys);
+            } else {
+              const unsigned long long x2 = ((unsigned long long)p1.y << 32) | p1.x;
+              const uint32_t hiBl = (uint32_t)(x2 >> 40) | ((p0.y >> 16) << 24);          // low 32 bits of hiB (40 bits: the top 8 are in p0.y >> 24)
+              atomicAdd(c, w);
+              atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
+              atomicAdd(c + 3 * G, p0.z & LIMB_MASK); atomicAdd(c + 4 * G, (uint32_t)((long long)x1 >> 20));
+              atomicAdd(c + 5 * G, p1.x & LIMB_MASK); atomicAdd(c + 6 * G, (uint32_t)(x2 >> 20) & LIMB_MASK);
+              atomicAdd(c + 7 * G, hiBl & LIMB_MASK); atomicAdd(c + 8 * G, (hiBl >> 20) | ((p0.y >> 24) << 12));
+            }
+          } else {
+            if (p0.w & 0x80000000u) {                                  // slow row
+              const uint32_t w = p0.z & 31u;
+              const double ys = __longlong_as_double((long long)x0);
+              const double wy = (double)w * ys;
+              double* gc = hb + (size_t)(e.y + cc) * 4;
+              atomicAdd(gc, (double)w); atomicAdd(gc + 1, wy); atomicAdd(gc + 2, wy * ys);
+            } else {
+              atomicAdd(c, p0.y >> 27);
+              atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
+              atomicAdd(c + 3 * G, (uint32_t)((long long)(x0 << 5) >> 45));
+              atomicAdd(c + 4 * G, p0.z & LIMB_MASK); atomicAdd(c + 5 * G, (uint32_t)(x1 >> 20) & LIMB_MASK);
+              atomicAdd(c + 6 * G, (uint32_t)(x1 >> 40) & LIMB_MASK);
+            }
+          }
         }
       }
       __syncwarp();
     }
     __syncthreads();
-    // ---- flush: exact limb sums -> fp64, added to the global histogram ----
-    const double sA = pow2d(ey - 53), sB = pow2d(2 * ey - 53);
+    // ---- flush: exact limb sums -> fp64 (one rounding), added to the global histogram ----
+    const double sA = pow2d(Ea - (WIDE ? 79 : 59)), sB = pow2d(Eb - (WIDE ? 80 : 60));
     for (int c = tid; c < padB * G; c += THREADS) {
       const int bin = c / G, f2 = c & (G - 1);
-      const uint32_t* cell = hist + (size_t)bin * (LIMB_PLANES * G) + f2;
+      const uint32_t* cell = hist + (size_t)bin * (NP * G) + f2;
       const uint32_t cnt = cell[0];
       if (!cnt) continue;                                                // untouched cell (also every cell of an idle lane)
-      const double A = ((double)(int32_t)cell[3 * G] * 0x1p40 + (double)cell[2 * G] * 0x1p20) + (double)cell[G];
-      const double B = ((double)cell[6 * G] * 0x1p40 + (double)cell[5 * G] * 0x1p20) + (double)cell[4 * G];
+      double A, B;
+      if (WIDE) {
+        A = ((double)(int32_t)cell[4 * G] * 0x1p60 + (double)cell[3 * G] * 0x1p40) + ((double)cell[2 * G] * 0x1p20 + (double)cell[G]);
+        B = ((double)cell[8 * G] * 0x1p60 + (double)cell[7 * G] * 0x1p40) + ((double)cell[6 * G] * 0x1p20 + (double)cell[5 * G]);
+      } else {
+        A = ((double)(int32_t)cell[3 * G] * 0x1p40 + (double)cell[2 * G] * 0x1p20) + (double)cell[G];
+        B = ((double)cell[6 * G] * 0x1p40 + (double)cell[5 * G] * 0x1p20) + (double)cell[4 * G];
+      }
       double* gp = hb + ((size_t)fo[g * G + f2].y + (size_t)bin) * 4;
       atomicAdd(gp, (double)cnt); atomicAdd(gp + 1, A * sA); atomicAdd(gp + 2, B * sB);
     }
@@ -214,49 +307,53 @@ static std::atomic<long long> g_variant_count[B2RF_K4_VARIANTS];
 void count_k4_variant(int v) { if (v >= 0 && v < B2RF_K4_VARIANTS) g_variant_count[v].fetch_add(1, std::memory_order_relaxed); }
 long long k4_variant_count(int v) { return (v >= 0 && v < B2RF_K4_VARIANTS) ? g_variant_count[v].load(std::memory_order_relaxed) : 0; }
 
-// Shared memory of one CTA: the limb histogram plus two staged blocks per warp.
-static size_t limb_smem(int padB, int G, int ldr, int BR, int threads) {
-  return (size_t)padB * LIMB_PLANES * G * 4 + (size_t)(threads / 32) * 2 * ((size_t)BR * ldr + (size_t)BR * 32);
+// Shared memory of one CTA: the limb histogram, two staged blocks per warp (code rows + packed values) and two mbarriers per warp.
+static size_t limb_smem(int padB, int G, int ldr, int BR, int threads, int NP) {
+  const size_t vb = NP == 9 ? 32 : 16;
+  return (size_t)padB * NP * G * 4 + (size_t)(threads / 32) * 2 * ((size_t)BR * ldr + (size_t)BR * vb) + (size_t)(threads / 32) * 16;
 }
 
 // Picks (G, block rows, threads) for a launch, or returns false when the limb kernel does not apply (the caller then runs the
 // fp64 compare-and-swap kernel of k4_hist.cu): uint8 codes, labels carried in the row lists, 16-byte aligned code rows, and a
 // task histogram that leaves room for the staging ring.
-bool limb_plan(const BucketLaunch& b, int maxBinsAll, LimbPlan* p) {
+bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, LimbPlan* p) {
   if (b.codeBytes != 1 || b.dseg == nullptr || b.y0 == nullptr || b.y1 == nullptr) return false;
   if ((b.ldr & 15) != 0 || (reinterpret_cast<uintptr_t>(b.bins_rm) & 15) != 0 || b.ldr > 1024) return false;
   const size_t cap2 = (size_t)113 * 1024, cap1 = (size_t)226 * 1024;   // two CTAs per SM / one
+  const int NP = narrow ? 7 : 9;
   int G = 32;
   while (G > 8 && G / 2 >= b.Fsub) G /= 2;
   for (; G >= 8; G /= 2) {
-    if (limb_smem(maxBinsAll, G, (int)b.ldr, 32, 256) <= cap2) { *p = {G, 32, 256, maxBinsAll}; return true; }
-    if (limb_smem(maxBinsAll, G, (int)b.ldr, 32, 512) <= cap1) { *p = {G, 32, 512, maxBinsAll}; return true; }
-    if (limb_smem(maxBinsAll, G, (int)b.ldr, 16, 512) <= cap1) { *p = {G, 16, 512, maxBinsAll}; return true; }
+    if (limb_smem(maxBinsAll, G, (int)b.ldr, 32, 256, NP) <= cap2) { *p = {G, 32, 256, maxBinsAll, NP}; return true; }
+    if (limb_smem(maxBinsAll, G, (int)b.ldr, 16, 256, NP) <= cap2) { *p = {G, 16, 256, maxBinsAll, NP}; return true; }
+    if (limb_smem(maxBinsAll, G, (int)b.ldr, 32, 512, NP) <= cap1) { *p = {G, 32, 512, maxBinsAll, NP}; return true; }
+    if (limb_smem(maxBinsAll, G, (int)b.ldr, 16, 512, NP) <= cap1) { *p = {G, 16, 512, maxBinsAll, NP}; return true; }
   }
   return false;
 }
 
-template <int G, int LDR, int BR, int THREADS>
+template <int G, int LDR, int BR, int THREADS, int NP>
 static cudaError_t launch_limb_inst(const BucketLaunch& b, uint32_t* ticket, int grid, size_t smem, cudaStream_t s) {
-  cudaError_t e = cudaFuncSetAttribute(limb_hist_kernel<G, LDR, BR, THREADS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(limb_hist_kernel<G, LDR, BR, THREADS, NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  limb_hist_kernel<G, LDR, BR, THREADS><<<grid, THREADS, smem, s>>>(b, ticket);
+  limb_hist_kernel<G, LDR, BR, THREADS, NP><<<grid, THREADS, smem, s>>>(b, ticket);
   return cudaGetLastError();
 }
 
-template <int G>
+template <int G, int NP>
 static cudaError_t launch_limb_g(const BucketLaunch& b, const LimbPlan& p, uint32_t* ticket, int grid, size_t smem, cudaStream_t s) {
+  // the two row widths of the named configurations (64 / 128 features, uint8) get compile-time offsets; everything else reads a.ldr
   if (p.threads == 256) {
-    if (b.ldr == 64) return launch_limb_inst<G, 64, 32, 256>(b, ticket, grid, smem, s);
-    if (b.ldr == 128) return launch_limb_inst<G, 128, 32, 256>(b, ticket, grid, smem, s);
-    return launch_limb_inst<G, 0, 32, 256>(b, ticket, grid, smem, s);
+    if (p.BR == 32) {
+      if (b.ldr == 64) return launch_limb_inst<G, 64, 32, 256, NP>(b, ticket, grid, smem, s);
+      return launch_limb_inst<G, 0, 32, 256, NP>(b, ticket, grid, smem, s);
+    }
+    if (b.ldr == 64) return launch_limb_inst<G, 64, 16, 256, NP>(b, ticket, grid, smem, s);
+    return launch_limb_inst<G, 0, 16, 256, NP>(b, ticket, grid, smem, s);
   }
-  if (p.BR == 32) {
-    if (b.ldr == 128) return launch_limb_inst<G, 128, 32, 512>(b, ticket, grid, smem, s);
-    return launch_limb_inst<G, 0, 32, 512>(b, ticket, grid, smem, s);
-  }
-  if (b.ldr == 128) return launch_limb_inst<G, 128, 16, 512>(b, ticket, grid, smem, s);
-  return launch_limb_inst<G, 0, 16, 512>(b, ticket, grid, smem, s);
+  if (p.BR == 32) return launch_limb_inst<G, 0, 32, 512, NP>(b, ticket, grid, smem, s);
+  if (b.ldr == 128) return launch_limb_inst<G, 128, 16, 512, NP>(b, ticket, grid, smem, s);
+  return launch_limb_inst<G, 0, 16, 512, NP>(b, ticket, grid, smem, s);
 }
 
 // Task table (seg_tasks, which also zeroes the ticket behind the prefix array) + the limb kernel.
@@ -266,12 +363,35 @@ cudaError_t launch_limb_hist(const BucketLaunch& b0, const LimbPlan& p, cudaStre
   cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s, /*ticket=*/true, b.rows_acc);
   if (e != cudaSuccess) return e;
   uint32_t* ticket = const_cast<uint32_t*>(b.chunk_prefix) + b.nSlots + 1;
-  const size_t smem = limb_smem(p.padB, p.G, (int)b.ldr, p.BR, p.threads);
+  const size_t smem = limb_smem(p.padB, p.G, (int)b.ldr, p.BR, p.threads, p.NP);
   const int grid = device_sm_count() * (p.threads == 256 ? 2 : 1);
   count_k4_variant(B2RF_K4_LIMB);
-  if (p.G == 32) return launch_limb_g<32>(b, p, ticket, grid, smem, s);
-  if (p.G == 16) return launch_limb_g<16>(b, p, ticket, grid, smem, s);
-  return launch_limb_g<8>(b, p, ticket, grid, smem, s);
+  if (p.NP == 7) {
+    if (p.G == 32) return launch_limb_g<32, 7>(b, p, ticket, grid, smem, s);
+    if (p.G == 16) return launch_limb_g<16, 7>(b, p, ticket, grid, smem, s);
+    return launch_limb_g<8, 7>(b, p, ticket, grid, smem, s);
+  }
+  if (p.G == 32) return launch_limb_g<32, 9>(b, p, ticket, grid, smem, s);
+  if (p.G == 16) return launch_limb_g<16, 9>(b, p, ticket, grid, smem, s);
+  return launch_limb_g<8, 9>(b, p, ticket, grid, smem, s);
+}
+
+// 1 when every label is an integer of magnitude <= 2^24 (then w*y and w*y*y are integers below 2^53 and the narrow windows hold
+// every row exactly), else 0.  *flag must be 1 on entry.
+__global__ void labels_integer_kernel(const double* y, int64_t n, int32_t* flag) {
+  bool ok = true;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const double v = y[i];
+    ok = ok && (fabs(v) <= 16777216.0) && (v == rint(v));
+  }
+  if (!__all_sync(0xffffffffu, ok) && (threadIdx.x & 31) == 0) *flag = 0;
+}
+cudaError_t launch_labels_integer(const double* y, int64_t n, int32_t* d_flag, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  int64_t bx = (n + 255) / 256;
+  if (bx > 2048) bx = 2048;
+  labels_integer_kernel<<<(unsigned)bx, 256, 0, s>>>(y, n, d_flag);
+  return cudaGetLastError();
 }
 
 }  // namespace b2rf

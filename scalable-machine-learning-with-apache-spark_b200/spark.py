@@ -117,18 +117,22 @@ def categorical_arities(dataset, featuresCol: str, num_features: int) -> np.ndar
 
 
 def _extract(dataset, featuresCol, labelCol=None):
-    """(X f64 [n, F] host, y f64 [n] host or None, partition sizes).  Real Spark: Arrow via toPandas(); stub: LocalFrame."""
+    """(X f64 [n, F] host, y f64 [n] host or None, partition sizes).  Real Spark: ONE job — Arrow toPandas() of (features array,
+    label, spark_partition_id()); rows arrive partition by partition, so the partition sizes bagging needs (A.4) come from the same
+    evaluation of the plan as the rows themselves.  Stub: LocalFrame."""
     if HAVE_PYSPARK and hasattr(dataset, "sparkSession"):
         from pyspark.ml.functions import vector_to_array
         from pyspark.sql import functions as F
-        cols = [vector_to_array(F.col(featuresCol)).alias("f")]
+        cols = [vector_to_array(F.col(featuresCol)).alias("f"), F.spark_partition_id().alias("p")]
         if labelCol:
             cols.append(F.col(labelCol).cast("double").alias("y"))
-        sel = dataset.select(*cols)
-        sizes = sel.rdd.mapPartitions(lambda it: [sum(1 for _ in it)]).collect()      # row order == partition order (A.4)
-        pdf = sel.toPandas()
+        pdf = dataset.select(*cols).toPandas()
         X = np.ascontiguousarray(np.stack(pdf["f"].to_numpy()), dtype=np.float64) if len(pdf) else np.zeros((0, 0))
         y = pdf["y"].to_numpy(np.float64) if labelCol else None
+        pid = pdf["p"].to_numpy(np.int64)
+        if len(pid) and (np.diff(pid) < 0).any():
+            raise RuntimeError("toPandas() did not return the rows in partition order; cannot reproduce MLlib's per-partition bagging streams")
+        sizes = np.bincount(pid, minlength=int(pid.max()) + 1 if len(pid) else 1).tolist()
         return X, y, sizes
     X = np.ascontiguousarray(dataset.col(featuresCol), dtype=np.float64)
     y = np.ascontiguousarray(dataset.col(labelCol), dtype=np.float64) if labelCol else None
@@ -138,34 +142,38 @@ def _extract(dataset, featuresCol, labelCol=None):
     return X, y, sizes
 
 
-def _append_columns(dataset, cols: dict):
-    """Appends output columns: 1-D arrays become double columns, 2-D arrays vector columns (rawPrediction, probability)."""
+def _score_dataset(dataset, featuresCol, num_features, score_fn):
+    """Model._transform: appends the columns `score_fn(X f64 [n, F]) -> {name: 1-D array (double column) | 2-D array (vector column)}`.
+
+    Real Spark: one pass over the data, no driver collect and no positional join — a scalar pandas UDF receives each Arrow batch of
+    vector_to_array(features), scores it on the executor's GPU and returns every output column as one struct, which is then
+    unpacked (asNondeterministic keeps Catalyst from inlining the UDF once per extracted field).  [Written against the pyspark 3.1
+    API; pyspark is unavailable in this image, so this branch is untested here — INTEGRATION.md.]  Stub: LocalFrame columns."""
     if HAVE_PYSPARK and hasattr(dataset, "sparkSession"):
         import pandas as pd
-        from pyspark.ml.functions import array_to_vector
+        from pyspark.ml.functions import array_to_vector, vector_to_array
         from pyspark.sql import functions as F
-        from pyspark.sql.window import Window
-        spark = dataset.sparkSession
-        idx = dataset.withColumn("__b2rf_i", F.monotonically_increasing_id())
-        w = Window.orderBy("__b2rf_i")
-        idx = idx.withColumn("__b2rf_r", F.row_number().over(w) - 1)
-        n = len(next(iter(cols.values())))
-        data = {"__b2rf_r": np.arange(n)}
-        for name, v in cols.items():
-            v = np.asarray(v, np.float64)
-            data[name] = v if v.ndim == 1 else list(map(list, v))
-        p = spark.createDataFrame(pd.DataFrame(data))
-        for name, v in cols.items():
-            if np.asarray(v).ndim == 2:
-                p = p.withColumn(name, array_to_vector(F.col(name)))
-        return idx.join(p, "__b2rf_r").drop("__b2rf_r", "__b2rf_i")
-    for name, v in cols.items():
+        from pyspark.sql import types as T
+        probe = score_fn(np.zeros((0, num_features)))
+        fields = [T.StructField(n, T.DoubleType() if np.asarray(v).ndim == 1 else T.ArrayType(T.DoubleType())) for n, v in probe.items()]
+        if not fields:
+            return dataset
+
+        def score(feats: pd.Series) -> pd.DataFrame:
+            X = np.ascontiguousarray(np.stack(feats.to_numpy()), np.float64) if len(feats) else np.zeros((0, num_features))
+            cols = score_fn(X)
+            return pd.DataFrame({n: (np.asarray(v, np.float64) if np.asarray(v).ndim == 1 else [list(map(float, r)) for r in np.asarray(v)])
+                                 for n, v in cols.items()})
+        udf = F.pandas_udf(score, returnType=T.StructType(fields)).asNondeterministic()
+        out = dataset.withColumn("__b2rf_s", udf(vector_to_array(F.col(featuresCol))))
+        for n, v in probe.items():
+            c = F.col("__b2rf_s")[n]
+            out = out.withColumn(n, c if np.asarray(v).ndim == 1 else array_to_vector(c))
+        return out.drop("__b2rf_s")
+    X = np.ascontiguousarray(dataset.col(featuresCol), dtype=np.float64)
+    for name, v in score_fn(X).items():
         dataset = dataset.withColumn(name, np.asarray(v, np.float64))
     return dataset
-
-
-def _append_prediction(dataset, predictionCol, pred):
-    return _append_columns(dataset, {predictionCol: pred})
 
 
 class _ForestModelBase(Model, _TreeRegressorParams):
@@ -262,15 +270,18 @@ class _ForestModelBase(Model, _TreeRegressorParams):
             cols[var_col] = fo.impurity[flat[:, 0]]
         return cols
 
-    def _transform(self, dataset):
+    def _score_columns(self, X):
+        """Output columns for a batch of feature rows (predictionCol, leafCol, varianceCol)."""
         import torch
-        X, _, _ = _extract(dataset, self.getOrDefault("featuresCol"))
         cols = {}
         if self.getOrDefault("predictionCol"):
             cols[self.getOrDefault("predictionCol")] = (self._forest.predict(torch.as_tensor(X, device=self._device())).cpu().numpy()
                                                         if X.shape[0] else np.zeros(0))
         cols.update(self._leaf_columns(X))
-        return _append_columns(dataset, cols)
+        return cols
+
+    def _transform(self, dataset):
+        return _score_dataset(dataset, self.getOrDefault("featuresCol"), self._forest.num_features, self._score_columns)
 
 
 _VARIANCE_COL = Param(Params, "varianceCol", "column name for the biased sample variance of prediction.", TypeConverters.toString)
@@ -519,8 +530,7 @@ class _ClassifierModelBase(_ClassifierParams, _ForestModelBase):
     def predict(self, value):
         return float(self._predict_from_probability(self._normalize(self._raw(self._one(value))))[0])
 
-    def _transform(self, dataset):
-        X, _, _ = _extract(dataset, self.getOrDefault("featuresCol"))
+    def _score_columns(self, X):
         raw = self._raw(X) if X.shape[0] else np.zeros((0, self.numClasses))
         prob = self._normalize(raw)
         cols = {}
@@ -531,7 +541,7 @@ class _ClassifierModelBase(_ClassifierParams, _ForestModelBase):
         if self.getOrDefault("predictionCol"):
             cols[self.getOrDefault("predictionCol")] = self._predict_from_probability(prob)
         cols.update(self._leaf_columns(X))
-        return _append_columns(dataset, cols)
+        return cols
 
 
 class B200DecisionTreeClassificationModel(_ClassifierModelBase):

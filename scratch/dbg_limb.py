@@ -6,7 +6,7 @@ import b2rf
 from b2rf import trainer
 
 dev = torch.device("cuda:0")
-N, T, depth, mem = 40000, 5, 10, 256
+N, T, depth, mem = 40000, 5, 10, int(os.environ.get("MEM", "1"))
 X, y, arity = b2rf.synth.c3(N, device="cpu")
 Xd, yd = X.to(dev), y.to(dev)
 po = trainer.default_partitions(N, 1024)
@@ -42,3 +42,29 @@ for gi, ((ia, ha), (ib, hb)) in enumerate(zip(ga, gb)):
         break
 else:
     print("all groups identical")
+
+# ---- first differing decision ----
+fa, fb = out["fp64"][0], out["limb"][0]
+m = min(len(fa.trace_i), len(fb.trace_i))
+dif = np.nonzero((fa.trace_i[:m] != fb.trace_i[:m]).any(1))[0]
+if len(dif):
+    k = int(dif[0])
+    print("first differing decision at trace row", k)
+    print(" fp64:", fa.trace_i[k], fa.trace_d[k])
+    print(" limb:", fb.trace_i[k], fb.trace_d[k])
+    gi = int(fa.trace_i[k][0]); tr = int(fa.trace_i[k][1]); nid = int(fa.trace_i[k][2])
+    (ia, ha), (ib, hb) = ga[gi], gb[gi]
+    s = [i for i in range(len(ia["tree"])) if ia["tree"][i] == tr and ia["node_id"][i] == nid][0]
+    fo = ia["slot_fo"][s]; base = ia["slot_base"][s]
+    nxt = ia["slot_base"][s + 1] if s + 1 < len(ia["tree"]) else ha.shape[0]
+    A, B = ha[base:nxt], hb[base:nxt]
+    print(" slot", s, "cells", nxt - base, "nan fp64", np.isnan(A).sum(), "nan limb", np.isnan(B).sum())
+    d = np.nonzero((A[:, :3] != B[:, :3]).any(1))[0]
+    print(" cells not bit-identical:", len(d), "of", len(A))
+    for c in d[:10]:
+        j = int(np.searchsorted(fo[:, 1], c, side="right") - 1)
+        print(f"   cell {c} feat {fo[j,0]} bin {c - fo[j,1]}: fp64 {A[c,:3]!r} limb {B[c,:3]!r}")
+    for nm, f_ in (("fp64", fa), ("limb", fb)):
+        r = f_.trace_i[k]
+        j = [q for q in range(len(fo)) if fo[q, 0] == r[3]]
+        print(nm, "chose feature", r[3], "split", r[4], "in subset" if j else "NOT IN SUBSET")

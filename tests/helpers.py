@@ -19,8 +19,8 @@ def assert_forest_parity(g, o, check_stats=True):
         assert np.array_equal(g.stats[:, 0], o.stats[:, 0]), "node counts differ"          # contract (1): counts bit-exact
         np.testing.assert_allclose(g.stats[:, 1:3], o.stats[:, 1:3], rtol=REL, atol=0)      # contract (2)
         np.testing.assert_allclose(g.prediction, o.prediction, rtol=REL, atol=1e-300)
-        m = o.impurity >= 0
-        assert np.array_equal(m, g.impurity >= 0)
+        m = o.impurity > -0.5          # -1 marks a leaf whose statistics are invalid; a valid impurity can be a rounding-level negative
+        assert np.array_equal(m, g.impurity > -0.5)
         np.testing.assert_allclose(g.impurity[m], o.impurity[m], rtol=1e-6, atol=1e-9)
         np.testing.assert_allclose(g.gain, o.gain, rtol=1e-6, atol=1e-9)
 
@@ -101,7 +101,48 @@ def assert_forest_parity_with_ties(g, o, ties):
                 stack.append((int(g.right[a]), int(o.right[b]), 2 * hid + 1))
 
 
-def assert_parity_allowing_ties(g, o, max_ties):
+def first_tie_in_order(g, o, rel=1e-12):
+    """Walks both decision traces in processing order (pop order of MLlib's node stack).  Returns None when they are identical, else
+    the index of the first differing row after checking that it is a genuine gain tie: the same node, the same count and sums, best
+    gains equal to `rel` — two candidate splits that separate the node's rows identically have the same gain in exact arithmetic,
+    and which one wins is decided by the last bits of fp64 sums (in MLlib itself: by partition layout).  With feature subsampling
+    every node popped after such a tie draws its subset from a master stream that the tie's subtree may have advanced differently,
+    so nothing after the tie can be compared node by node."""
+    n = min(len(g.trace_i), len(o.trace_i))
+    neq = np.nonzero((g.trace_i[:n] != o.trace_i[:n]).any(1))[0]
+    k = int(neq[0]) if len(neq) else (n if len(g.trace_i) != len(o.trace_i) else None)
+    upto = n if k is None else k
+    np.testing.assert_array_equal(g.trace_d[:upto, 2], o.trace_d[:upto, 2])                      # counts exact
+    np.testing.assert_allclose(g.trace_d[:upto, 3:5], o.trace_d[:upto, 3:5], rtol=REL, atol=0)   # sums
+    if k is None:
+        return None
+    assert k < n, "one side evaluated more nodes without any differing decision before"
+    a, b, da, db = g.trace_i[k], o.trace_i[k], g.trace_d[k], o.trace_d[k]
+    assert tuple(a[:3]) == tuple(b[:3]), f"trace row {k}: different nodes were evaluated: {a[:3]} vs {b[:3]}"
+    assert da[2] == db[2], f"trace row {k}: counts differ {da[2]} vs {db[2]}"
+    np.testing.assert_allclose(da[3:5], db[3:5], rtol=REL, atol=0)
+    assert abs(da[0] - db[0]) <= rel * max(1.0, abs(db[0])), f"trace row {k} node {a[:3]}: different split and gains differ: {da[0]!r} vs {db[0]!r}"
+    return k
+
+
+def assert_parity_allowing_ties(g, o, max_ties, subsampling=None, min_fraction=0.0):
+    """Forest parity up to documented gain ties.  Without feature subsampling (one tree, or featureSubsetStrategy=all) a tie only
+    changes its own subtree: everything outside the subtrees of at most `max_ties` tie nodes must match.  With subsampling the
+    comparison is exact up to the first genuine tie in processing order (see first_tie_in_order); `min_fraction` is the share of the
+    decision trace that must have been compared by then."""
+    if subsampling is None:
+        subsampling = g.num_trees > 1 and getattr(g, "subsampling", True)
+    if subsampling:
+        k = first_tie_in_order(g, o)
+        if k is None:
+            assert_trace_parity(g, o)
+            assert_forest_parity(g, o)
+            return []
+        frac = k / max(1, len(o.trace_i))
+        print(f"documented gain tie at decision {k} of {len(o.trace_i)} (group, tree, node) = {tuple(int(v) for v in o.trace_i[k][:3])}; "
+              f"{100 * frac:.1f}% of the decisions compared exactly before it")
+        assert frac >= min_fraction, f"first gain tie after only {100 * frac:.1f}% of the decisions"
+        return [(int(o.trace_i[k][1]), int(o.trace_i[k][2]))]
     ties = find_ties(g, o)
     assert len(ties) <= max_ties, f"too many gain ties: {ties}"
     if not ties:

@@ -49,6 +49,18 @@ def test_c3_config_depth(b2rf, oracle, cuda, kernel, mem):
     assert_parity_allowing_ties(g, o, max_ties=4)
 
 
+def test_c3_config_depth_all_features(b2rf, oracle, cuda, kernel):
+    """The same depth with every feature offered at every node (two 32-feature groups per slot): no feature-subset draws, so a gain
+    tie — two splits that cut a small node's rows identically — only changes its own subtree and everything else must match."""
+    from b2rf import trainer
+    X, y, arity = b2rf.synth.c3(30000, device="cpu")
+    before = trainer.k4_launch_counts()
+    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=10, maxBins=64, numTrees=2, bootstrap=True, seed=3,
+                     featureSubsetStrategy="all")
+    _ran(b2rf, before, kernel, general=True)
+    assert_parity_allowing_ties(g, o, max_ties=12, subsampling=False)
+
+
 @pytest.mark.parametrize("fsub", ["16", "17", "32", "8", "5"])
 def test_feature_width_edges(b2rf, oracle, cuda, kernel, fsub):
     """Lane == feature layouts at their edges: 17 and 32 features per node (one row per warp instruction), 16 / 8 / 5 (two / four
