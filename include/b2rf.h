@@ -143,7 +143,8 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream);
 int b2rf_trainer_group_info(const b2rf_trainer* t, int64_t* n_slots, int32_t* h_tree, int32_t* h_node_id, uint32_t* h_slot_fo,
                             int64_t* h_slot_base);
 /* Process-wide switches, for A/B runs and tests: "k4_fp64" (1: segment mode uses the fp64 compare-and-swap histogram kernels
- * instead of the limb kernel; env B2RF_K4=fp64), "carry_labels" (0: row lists do not carry labels, K4 gathers them; env
+ * instead of the limb kernel; env B2RF_K4=fp64), "k4_tma" (1: the limb kernel stages code rows with one bulk async copy per row on
+ * the TMA engine instead of register-staged 128-bit loads; env B2RF_K4_STAGE=tma), "carry_labels" (0: row lists do not carry labels, K4 gathers them; env
  * B2RF_CARRY_Y=0).  Takes effect at the next b2rf_trainer_bind / begin_group. */
 int b2rf_set_option(const char* name, int64_t value);
 /* h_seconds5: init(0), findSplits(0), findBestSplits (K4 device time from CUDA events), chooseSplits (K5 + driver tail),

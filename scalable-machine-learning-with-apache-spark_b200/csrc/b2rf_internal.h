@@ -83,8 +83,8 @@ long long k4_variant_count(int v);
 
 // Limb kernel (k4_limb.cu): launch shape chosen by limb_plan from the histogram size and the code-row width.
 // NP = planes per cell: 9 (wide windows, exact for any realistic label range) or 7 (narrow: fits whose labels are all modest integers).
-struct LimbPlan { int G, BR, threads, padB, NP; };
-bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, LimbPlan* p);
+struct LimbPlan { int G, BR, threads, padB, NP, tma; };
+bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, bool wantTma, LimbPlan* p);
 cudaError_t launch_limb_hist(const BucketLaunch& b, const LimbPlan& p, cudaStream_t s);
 cudaError_t launch_labels_integer(const double* y, int64_t n, int32_t* d_flag, cudaStream_t s);   // *d_flag (preset to 1) cleared unless every label is an integer, |y| <= 2^24
 

@@ -203,6 +203,7 @@ double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock:
 
 // Process-wide switches (b2rf_set_option; initial values from the environment: B2RF_K4=fp64, B2RF_CARRY_Y=0).
 std::atomic<int>& opt_k4_fp64() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_K4"); return (m && std::string(m) == "fp64") ? 1 : 0; }()}; return v; }
+std::atomic<int>& opt_k4_tma() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_K4_STAGE"); return (m && std::string(m) == "tma") ? 1 : 0; }()}; return v; }
 std::atomic<int>& opt_carry_labels() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_CARRY_Y"); return (m && *m == '0') ? 0 : 1; }()}; return v; }
 
 }  // namespace
@@ -478,6 +479,10 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
   const uint8_t* d_bins_rm = static_cast<const uint8_t*>(d_bins_rm_v);
   if (!t || !d_bins || !d_y || !d_w || !d_hist || n_rows_local < 0 || ((ldb * (t ? t->codeBytes : 1)) & 15) || ldb < n_rows_local || ldw < n_rows_local || (d_node && ldn < n_rows_local)) {
     set_error("b2rf_trainer_bind: bad argument (ldb must be a multiple of 16 and every leading dimension >= n_rows)"); return B2RF_ERR_ARG;
+  }
+  {   // experiment hook: L2 fetch granularity (bytes) for the 64-byte code-row gathers; unset = driver default
+    static const int gran = [] { const char* m = std::getenv("B2RF_L2_FETCH"); return m ? atoi(m) : 0; }();
+    if (gran > 0) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)gran);
   }
   t->d_bins = d_bins; t->ldb = ldb; t->d_y = d_y; t->d_w = d_w; t->ldw = ldw; t->d_node = d_node; t->ldn = ldn; t->nLocal = n_rows_local;
   t->d_hist = d_hist; t->histCells = hist_cells;
@@ -792,7 +797,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       // compare-and-swap kernels, which also serve what the limb kernel does not (uint16 codes, labels not carried, huge histograms)
       const bool fp64Only = opt_k4_fp64().load() != 0;
       LimbPlan plan;
-      if (!fp64Only && limb_plan(b, maxBinsAll, t->labelsInt, &plan)) e = launch_limb_hist(b, plan, s);
+      if (!fp64Only && limb_plan(b, maxBinsAll, t->labelsInt, opt_k4_tma().load() != 0, &plan)) e = launch_limb_hist(b, plan, s);
       else e = launch_segment_hist(b, s);
       t->nKernels += 2;
     } else {
@@ -960,7 +965,8 @@ int b2rf_set_option(const char* name, int64_t value) {
   const std::string n = name ? name : "";
   if (n == "k4_fp64") { opt_k4_fp64().store(value ? 1 : 0); return B2RF_OK; }
   if (n == "carry_labels") { opt_carry_labels().store(value ? 1 : 0); return B2RF_OK; }
-  set_error("b2rf_set_option: unknown option \"" + n + "\" (k4_fp64, carry_labels)");
+  if (n == "k4_tma") { opt_k4_tma().store(value ? 1 : 0); return B2RF_OK; }
+  set_error("b2rf_set_option: unknown option \"" + n + "\" (k4_fp64, k4_tma, carry_labels)");
   return B2RF_ERR_ARG;
 }
 

@@ -94,8 +94,13 @@ __device__ __forceinline__ void limb_pack_wide(uint32_t w, double yv, LimbScale 
 // LDR  bytes per row of the row-major code matrix (0: read a.ldr)
 // BR   rows per staged block (32 or 16)
 // NP   planes per cell: 7 = count + 3 + 3 limbs (narrow), 9 = count + 4 + 4 (wide)
-template <int G, int LDR, int BR, int THREADS, int NP>
-__global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_kernel(const BucketLaunch a, uint32_t* ticket) {
+// TMA  how a block's code rows reach shared memory.  true: one bulk async copy per row on the TMA engine (UBLKCP + mbarrier, two
+//      tile slots per warp); costs no LSU wavefronts, but UBLKCP is a uniform-datapath instruction — one copy per warp instruction —
+//      so a block is BR serialized R2UR / UBLKCP sequences, ~12 issue slots per row (ncu: profiles/r02_ncu_limb.md).  false (needs a
+//      compile-time LDR): every lane fetches 16-byte pieces with LDG.128 one block ahead, holds them in registers while the warp adds
+//      the current block, and stores them with STS.128 (0.5 wavefronts and ~1 issue slot per row; one tile slot per warp).
+template <int G, int LDR, int BR, int THREADS, int NP, bool TMA>
+__global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_kernel(const BucketLaunch a, uint32_t* ticket) {
   extern __shared__ __align__(16) unsigned char smraw[];
   __shared__ uint32_t s_red[THREADS / 32];
   __shared__ uint32_t s_task;
@@ -110,9 +115,15 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
   const int padB = a.padB;
   uint32_t* hist = reinterpret_cast<uint32_t*>(smraw);                 // [padB][NP][G]
   const size_t histBytes = (size_t)padB * NP * G * 4;
-  const int stageBytes = BR * ldr + BR * VB;
-  unsigned char* ring = smraw + histBytes + (size_t)warp * 2 * stageBytes;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smraw + histBytes + (size_t)W * 2 * stageBytes) + warp * 2;
+  static_assert(TMA || LDR > 0, "register staging needs a compile-time row width");
+  constexpr int NPC = TMA ? 1 : (BR * (LDR > 0 ? LDR : 16)) / 512;   // 16-byte pieces of a block's code rows per lane
+  static_assert(TMA || (BR * LDR) % 512 == 0, "a block's code rows must be a whole number of 512-byte warp stores");
+  // per-warp ring: [tile slots: 2 (TMA) or 1][packed values: 2 slots]
+  const int tileBytes = BR * ldr, valBytes = BR * VB;
+  const int warpBytes = (TMA ? 2 : 1) * tileBytes + 2 * valBytes;
+  unsigned char* ring = smraw + histBytes + (size_t)warp * warpBytes;
+  unsigned char* valsBase = ring + (TMA ? 2 : 1) * tileBytes;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smraw + histBytes + (size_t)W * warpBytes) + warp * 2;
   const int fl = lane & (G - 1), r = lane / G;
   const int nG = (a.Fsub + G - 1) / G;
   const uint32_t total = a.chunk_prefix[a.nSlots] * (uint32_t)nG;
@@ -120,10 +131,12 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
 
   // staged code rows of blocks that are not full keep whatever the slot held before; rows past the end of a chunk carry zero limbs,
   // so such a code only has to be a valid bin index: start from zeros (and every later content is a real code row)
-  for (int c = lane; c < (2 * stageBytes) >> 4; c += 32) reinterpret_cast<uint4*>(ring)[c] = make_uint4(0u, 0u, 0u, 0u);
-  if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
-  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");          // generic-proxy zeros before the async proxy writes the same bytes
+  for (int c = lane; c < warpBytes >> 4; c += 32) reinterpret_cast<uint4*>(ring)[c] = make_uint4(0u, 0u, 0u, 0u);
+  if (TMA) {
+    if (lane == 0) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");        // generic-proxy zeros before the async proxy writes the same bytes
+  }
   __syncthreads();
   uint32_t phase = 0u;                                                   // bit s: parity the next wait on stage s expects
 
@@ -198,10 +211,10 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
       ent = in ? rl[i] : 0u;
       yv = in ? yl[i] : 0.0;
     };
-    // stage block blk into slot s: packed values by plain stores, code rows by one bulk async copy per row (TMA engine)
-    auto stage = [&](int s, int blk) {
-      unsigned char* tile = ring + s * stageBytes;
-      unsigned char* vals = tile + BR * ldr;
+    uint32_t* hcell = hist + fl;
+    // packed values of the block held in (ent, yv) -> value slot s
+    auto put_vals = [&](int s) {
+      unsigned char* vals = valsBase + s * valBytes;
       const uint32_t w = ent >> 27;
       if (lane < BR) {
         if (WIDE) {
@@ -213,72 +226,104 @@ __global__ void __launch_bounds__(THREADS, THREADS == 256 ? 2 : 1) limb_hist_ker
           *reinterpret_cast<uint4*>(vals + lane * VB) = limb_pack_narrow(w, yv, sc);
         }
       }
-      const int nvalid = min(BR, n - blk * BR);
-      if (lane == 0) mbar_expect_tx(&bars[s], (uint32_t)(nvalid * ldr));
-      __syncwarp();
-      if (lane < nvalid) bulk_g2s(tile + lane * ldr, bins_rm + (size_t)(ent & 0x7ffffffu) * ldr, (uint32_t)ldr, &bars[s]);
     };
-    int b = warp;
-    if (b < nblk) { load(b); stage(0, b); load(b + W); }
-    uint32_t* hcell = hist + fl;
-    for (int k = 0; b < nblk; k++, b += W) {
-      const int s = k & 1;
-      if (b + W < nblk) { stage(s ^ 1, b + W); load(b + 2 * W); }
-      while (!mbar_try(&bars[s], (phase >> s) & 1u)) { }
-      phase ^= 1u << s;
-      __syncwarp();
-      const unsigned char* tl = ring + s * stageBytes + r * ldr + e.x;
-      const unsigned char* vv = ring + s * stageBytes + BR * ldr + r * VB;
-      if (active) {
-        // one row ahead: the next row's code and packed limbs are loaded before this row's adds are issued (the compiler keeps
-        // shared loads behind earlier shared atomics, so the overlap has to be written out)
-        uint32_t code = tl[0];
-        uint4 q0 = *reinterpret_cast<const uint4*>(vv);
-        uint2 q1 = WIDE ? *reinterpret_cast<const uint2*>(vv + 16) : make_uint2(0u, 0u);
+    // the adds of one staged block: lane = (row slot r, feature fl); tile / vals point at the block's code rows and packed values
+    auto consume = [&](const unsigned char* tile, const unsigned char* vals) {
+      const unsigned char* tl = tile + r * ldr + e.x;
+      const unsigned char* vv = vals + r * VB;
+      if (!active) return;
+      // one row ahead: the next row's code and packed limbs are loaded before this row's adds are issued (the compiler keeps
+      // shared loads behind earlier shared atomics, so the overlap has to be written out)
+      uint32_t code = tl[0];
+      uint4 q0 = *reinterpret_cast<const uint4*>(vv);
+      uint2 q1 = WIDE ? *reinterpret_cast<const uint2*>(vv + 16) : make_uint2(0u, 0u);
 #pragma unroll
-        for (int u = 0; u < NU; u++) {
-          const uint32_t cc = code; const uint4 p0 = q0; const uint2 p1 = q1;
-          if (u + 1 < NU) {
-            code = tl[(u + 1) * R * ldr];
-            q0 = *reinterpret_cast<const uint4*>(vv + (u + 1) * R * VB);
-            if (WIDE) q1 = *reinterpret_cast<const uint2*>(vv + (u + 1) * R * VB + 16);
-          }
-          uint32_t* c = hcell + cc * (NP * G);
-          const unsigned long long x0 = ((unsigned long long)p0.y << 32) | p0.x, x1 = ((unsigned long long)p0.w << 32) | p0.z;
-          if (WIDE) {
-            const uint32_t w = (p0.y >> 8) & 31u;
-            if (p0.y & (1u << 15)) {                                   // slow row: its fp64 terms go straight to the global histogram
-              const double ys = __longlong_as_double((long long)x1);
-              const double wy = (double)w * ys;
-              double* gc = hb + (size_t)(e.y + cc) * 4;
-              atomicAdd(gc, (double)w); atomicAdd(gc + 1, wy); atomicAdd(gc + 2, wy * ys);
-            } else {
-              const unsigned long long x2 = ((unsigned long long)p1.y << 32) | p1.x;
-              const uint32_t hiBl = (uint32_t)(x2 >> 40) | ((p0.y >> 16) << 24);          // low 32 bits of hiB (40 bits: the top 8 are in p0.y >> 24)
-              atomicAdd(c, w);
-              atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
-              atomicAdd(c + 3 * G, p0.z & LIMB_MASK); atomicAdd(c + 4 * G, (uint32_t)((long long)x1 >> 20));
-              atomicAdd(c + 5 * G, p1.x & LIMB_MASK); atomicAdd(c + 6 * G, (uint32_t)(x2 >> 20) & LIMB_MASK);
-              atomicAdd(c + 7 * G, hiBl & LIMB_MASK); atomicAdd(c + 8 * G, (hiBl >> 20) | ((p0.y >> 24) << 12));
-            }
+      for (int u = 0; u < NU; u++) {
+        const uint32_t cc = code; const uint4 p0 = q0; const uint2 p1 = q1;
+        if (u + 1 < NU) {
+          code = tl[(u + 1) * R * ldr];
+          q0 = *reinterpret_cast<const uint4*>(vv + (u + 1) * R * VB);
+          if (WIDE) q1 = *reinterpret_cast<const uint2*>(vv + (u + 1) * R * VB + 16);
+        }
+        uint32_t* c = hcell + cc * (NP * G);
+        const unsigned long long x0 = ((unsigned long long)p0.y << 32) | p0.x, x1 = ((unsigned long long)p0.w << 32) | p0.z;
+        if (WIDE) {
+          const uint32_t w = (p0.y >> 8) & 31u;
+          if (p0.y & (1u << 15)) {                                   // slow row: its fp64 terms go straight to the global histogram
+            const double ys = __longlong_as_double((long long)x1);
+            const double wy = (double)w * ys;
+            double* gc = hb + (size_t)(e.y + cc) * 4;
+            atomicAdd(gc, (double)w); atomicAdd(gc + 1, wy); atomicAdd(gc + 2, wy * ys);
           } else {
-            if (p0.w & 0x80000000u) {                                  // slow row
-              const uint32_t w = p0.z & 31u;
-              const double ys = __longlong_as_double((long long)x0);
-              const double wy = (double)w * ys;
-              double* gc = hb + (size_t)(e.y + cc) * 4;
-              atomicAdd(gc, (double)w); atomicAdd(gc + 1, wy); atomicAdd(gc + 2, wy * ys);
-            } else {
-              atomicAdd(c, p0.y >> 27);
-              atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
-              atomicAdd(c + 3 * G, (uint32_t)((long long)(x0 << 5) >> 45));
-              atomicAdd(c + 4 * G, p0.z & LIMB_MASK); atomicAdd(c + 5 * G, (uint32_t)(x1 >> 20) & LIMB_MASK);
-              atomicAdd(c + 6 * G, (uint32_t)(x1 >> 40) & LIMB_MASK);
-            }
+            const unsigned long long x2 = ((unsigned long long)p1.y << 32) | p1.x;
+            const uint32_t hiBl = (uint32_t)(x2 >> 40) | ((p0.y >> 16) << 24);          // low 32 bits of hiB (40 bits: the top 8 are in p0.y >> 24)
+            atomicAdd(c, w);
+            atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
+            atomicAdd(c + 3 * G, p0.z & LIMB_MASK); atomicAdd(c + 4 * G, (uint32_t)((long long)x1 >> 20));
+            atomicAdd(c + 5 * G, p1.x & LIMB_MASK); atomicAdd(c + 6 * G, (uint32_t)(x2 >> 20) & LIMB_MASK);
+            atomicAdd(c + 7 * G, hiBl & LIMB_MASK); atomicAdd(c + 8 * G, (hiBl >> 20) | ((p0.y >> 24) << 12));
+          }
+        } else {
+          if (p0.w & 0x80000000u) {                                  // slow row
+            const uint32_t w = p0.z & 31u;
+            const double ys = __longlong_as_double((long long)x0);
+            const double wy = (double)w * ys;
+            double* gc = hb + (size_t)(e.y + cc) * 4;
+            atomicAdd(gc, (double)w); atomicAdd(gc + 1, wy); atomicAdd(gc + 2, wy * ys);
+          } else {
+            atomicAdd(c, p0.y >> 27);
+            atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
+            atomicAdd(c + 3 * G, (uint32_t)((long long)(x0 << 5) >> 45));
+            atomicAdd(c + 4 * G, p0.z & LIMB_MASK); atomicAdd(c + 5 * G, (uint32_t)(x1 >> 20) & LIMB_MASK);
+            atomicAdd(c + 6 * G, (uint32_t)(x1 >> 40) & LIMB_MASK);
           }
         }
       }
-      __syncwarp();
+    };
+    int b = warp;
+    if (TMA) {
+      // tile slot s <- the block held in (ent, yv): one bulk async copy per row, completion on the slot's mbarrier
+      auto stage_tma = [&](int s, int blk) {
+        put_vals(s);
+        unsigned char* tile = ring + s * tileBytes;
+        const int nvalid = min(BR, n - blk * BR);
+        if (lane == 0) mbar_expect_tx(&bars[s], (uint32_t)(nvalid * ldr));
+        __syncwarp();
+        if (lane < nvalid) bulk_g2s(tile + lane * ldr, bins_rm + (size_t)(ent & 0x7ffffffu) * ldr, (uint32_t)ldr, &bars[s]);
+      };
+      if (b < nblk) { load(b); stage_tma(0, b); load(b + W); }
+      for (int k = 0; b < nblk; k++, b += W) {
+        const int s = k & 1;
+        if (b + W < nblk) { stage_tma(s ^ 1, b + W); load(b + 2 * W); }
+        while (!mbar_try(&bars[s], (phase >> s) & 1u)) { }
+        phase ^= 1u << s;
+        __syncwarp();
+        consume(ring + s * tileBytes, valsBase + s * valBytes);
+        __syncwarp();
+      }
+    } else {
+      // register staging: the 16-byte pieces of the NEXT block's code rows are in flight (LDG.128) while the warp adds the current one
+      constexpr int CPR = (LDR > 0 ? LDR : 16) / 16;               // pieces per row
+      uint4 creg[NPC];
+      auto fetch = [&](int blk) {                                  // (ent, yv) hold block blk
+        const int nvalid = min(BR, n - blk * BR);
+#pragma unroll
+        for (int q = 0; q < NPC; q++) {
+          const int c = lane + 32 * q, row = c / CPR, seg = c - row * CPR;
+          const uint32_t e2 = __shfl_sync(FULL, ent, row);
+          creg[q] = row < nvalid ? *reinterpret_cast<const uint4*>(bins_rm + (size_t)(e2 & 0x7ffffffu) * ldr + seg * 16) : make_uint4(0u, 0u, 0u, 0u);
+        }
+      };
+      if (b < nblk) { load(b); fetch(b); put_vals(0); load(b + W); }
+      for (int k = 0; b < nblk; k++, b += W) {
+        const int s = k & 1;
+#pragma unroll
+        for (int q = 0; q < NPC; q++) reinterpret_cast<uint4*>(ring)[lane + 32 * q] = creg[q];
+        __syncwarp();
+        if (b + W < nblk) { fetch(b + W); put_vals(s ^ 1); load(b + 2 * W); }
+        consume(ring, valsBase + s * valBytes);
+        __syncwarp();
+      }
     }
     __syncthreads();
     // ---- flush: exact limb sums -> fp64 (one rounding), added to the global histogram ----
@@ -307,53 +352,71 @@ static std::atomic<long long> g_variant_count[B2RF_K4_VARIANTS];
 void count_k4_variant(int v) { if (v >= 0 && v < B2RF_K4_VARIANTS) g_variant_count[v].fetch_add(1, std::memory_order_relaxed); }
 long long k4_variant_count(int v) { return (v >= 0 && v < B2RF_K4_VARIANTS) ? g_variant_count[v].load(std::memory_order_relaxed) : 0; }
 
-// Shared memory of one CTA: the limb histogram, two staged blocks per warp (code rows + packed values) and two mbarriers per warp.
-static size_t limb_smem(int padB, int G, int ldr, int BR, int threads, int NP) {
+// Shared memory of one CTA: the limb histogram, the warps' staging rings (code-row tile slots + two packed-value slots) and, for the
+// TMA form, two mbarriers per warp.
+static size_t limb_smem(int padB, int G, int ldr, int BR, int threads, int NP, bool tma) {
   const size_t vb = NP == 9 ? 32 : 16;
-  return (size_t)padB * NP * G * 4 + (size_t)(threads / 32) * 2 * ((size_t)BR * ldr + (size_t)BR * vb) + (size_t)(threads / 32) * 16;
+  const size_t warp = (size_t)(tma ? 2 : 1) * BR * ldr + 2 * (size_t)BR * vb;
+  return (size_t)padB * NP * G * 4 + (size_t)(threads / 32) * warp + (size_t)(threads / 32) * 16;
 }
 
-// Picks (G, block rows, threads) for a launch, or returns false when the limb kernel does not apply (the caller then runs the
-// fp64 compare-and-swap kernel of k4_hist.cu): uint8 codes, labels carried in the row lists, 16-byte aligned code rows, and a
+// Picks (G, block rows, threads, staging) for a launch, or returns false when the limb kernel does not apply (the caller then runs
+// the fp64 compare-and-swap kernel of k4_hist.cu): uint8 codes, labels carried in the row lists, 16-byte aligned code rows, and a
 // task histogram that leaves room for the staging ring.
-bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, LimbPlan* p) {
+bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, bool wantTma, LimbPlan* p) {
   if (b.codeBytes != 1 || b.dseg == nullptr || b.y0 == nullptr || b.y1 == nullptr) return false;
   if ((b.ldr & 15) != 0 || (reinterpret_cast<uintptr_t>(b.bins_rm) & 15) != 0 || b.ldr > 1024) return false;
   const size_t cap2 = (size_t)113 * 1024, cap1 = (size_t)226 * 1024;   // two CTAs per SM / one
   const int NP = narrow ? 7 : 9;
+  const bool tma = wantTma || !(b.ldr == 64 || b.ldr == 128);          // register staging is compiled for the 64- and 128-byte rows
+  const int ldr = (int)b.ldr;
   int G = 32;
   while (G > 8 && G / 2 >= b.Fsub) G /= 2;
   for (; G >= 8; G /= 2) {
-    if (limb_smem(maxBinsAll, G, (int)b.ldr, 32, 256, NP) <= cap2) { *p = {G, 32, 256, maxBinsAll, NP}; return true; }
-    if (limb_smem(maxBinsAll, G, (int)b.ldr, 16, 256, NP) <= cap2) { *p = {G, 16, 256, maxBinsAll, NP}; return true; }
-    if (limb_smem(maxBinsAll, G, (int)b.ldr, 32, 512, NP) <= cap1) { *p = {G, 32, 512, maxBinsAll, NP}; return true; }
-    if (limb_smem(maxBinsAll, G, (int)b.ldr, 16, 512, NP) <= cap1) { *p = {G, 16, 512, maxBinsAll, NP}; return true; }
+    // two CTAs per SM: 12 warps each when the ring fits (register staging; 384 threads x 2 fill the register file), else 8
+    if (!tma && limb_smem(maxBinsAll, G, ldr, 32, 384, NP, false) <= cap2) { *p = {G, 32, 384, maxBinsAll, NP, 0}; return true; }
+    if (!tma && limb_smem(maxBinsAll, G, ldr, 16, 384, NP, false) <= cap2) { *p = {G, 16, 384, maxBinsAll, NP, 0}; return true; }
+    if (limb_smem(maxBinsAll, G, ldr, 32, 256, NP, tma) <= cap2) { *p = {G, 32, 256, maxBinsAll, NP, tma}; return true; }
+    if (limb_smem(maxBinsAll, G, ldr, 16, 256, NP, tma) <= cap2) { *p = {G, 16, 256, maxBinsAll, NP, tma}; return true; }
+    if (limb_smem(maxBinsAll, G, ldr, 32, 512, NP, tma) <= cap1) { *p = {G, 32, 512, maxBinsAll, NP, tma}; return true; }
+    if (limb_smem(maxBinsAll, G, ldr, 16, 512, NP, tma) <= cap1) { *p = {G, 16, 512, maxBinsAll, NP, tma}; return true; }
   }
   return false;
 }
 
-template <int G, int LDR, int BR, int THREADS, int NP>
+template <int G, int LDR, int BR, int THREADS, int NP, bool TMA>
 static cudaError_t launch_limb_inst(const BucketLaunch& b, uint32_t* ticket, int grid, size_t smem, cudaStream_t s) {
-  cudaError_t e = cudaFuncSetAttribute(limb_hist_kernel<G, LDR, BR, THREADS, NP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(limb_hist_kernel<G, LDR, BR, THREADS, NP, TMA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  limb_hist_kernel<G, LDR, BR, THREADS, NP><<<grid, THREADS, smem, s>>>(b, ticket);
+  limb_hist_kernel<G, LDR, BR, THREADS, NP, TMA><<<grid, THREADS, smem, s>>>(b, ticket);
   return cudaGetLastError();
 }
 
-template <int G, int NP>
+template <int G, int NP, int BR>
 static cudaError_t launch_limb_g(const BucketLaunch& b, const LimbPlan& p, uint32_t* ticket, int grid, size_t smem, cudaStream_t s) {
-  // the two row widths of the named configurations (64 / 128 features, uint8) get compile-time offsets; everything else reads a.ldr
-  if (p.threads == 256) {
-    if (p.BR == 32) {
-      if (b.ldr == 64) return launch_limb_inst<G, 64, 32, 256, NP>(b, ticket, grid, smem, s);
-      return launch_limb_inst<G, 0, 32, 256, NP>(b, ticket, grid, smem, s);
+  if (!p.tma) {   // register staging: 64- or 128-byte rows
+    if (b.ldr == 64) {
+      if (p.threads == 384) return launch_limb_inst<G, 64, BR, 384, NP, false>(b, ticket, grid, smem, s);
+      if (p.threads == 256) return launch_limb_inst<G, 64, BR, 256, NP, false>(b, ticket, grid, smem, s);
+      return launch_limb_inst<G, 64, BR, 512, NP, false>(b, ticket, grid, smem, s);
     }
-    if (b.ldr == 64) return launch_limb_inst<G, 64, 16, 256, NP>(b, ticket, grid, smem, s);
-    return launch_limb_inst<G, 0, 16, 256, NP>(b, ticket, grid, smem, s);
+    if (p.threads == 384) return launch_limb_inst<G, 128, BR, 384, NP, false>(b, ticket, grid, smem, s);
+    if (p.threads == 256) return launch_limb_inst<G, 128, BR, 256, NP, false>(b, ticket, grid, smem, s);
+    return launch_limb_inst<G, 128, BR, 512, NP, false>(b, ticket, grid, smem, s);
   }
-  if (p.BR == 32) return launch_limb_inst<G, 0, 32, 512, NP>(b, ticket, grid, smem, s);
-  if (b.ldr == 128) return launch_limb_inst<G, 128, 16, 512, NP>(b, ticket, grid, smem, s);
-  return launch_limb_inst<G, 0, 16, 512, NP>(b, ticket, grid, smem, s);
+  // TMA staging: any row width; the two named widths get compile-time offsets in the add loop
+  if (p.threads == 256) {
+    if (b.ldr == 64) return launch_limb_inst<G, 64, BR, 256, NP, true>(b, ticket, grid, smem, s);
+    return launch_limb_inst<G, 0, BR, 256, NP, true>(b, ticket, grid, smem, s);
+  }
+  if (b.ldr == 128) return launch_limb_inst<G, 128, BR, 512, NP, true>(b, ticket, grid, smem, s);
+  return launch_limb_inst<G, 0, BR, 512, NP, true>(b, ticket, grid, smem, s);
+}
+
+template <int G, int NP>
+static cudaError_t launch_limb_br(const BucketLaunch& b, const LimbPlan& p, uint32_t* ticket, int grid, size_t smem, cudaStream_t s) {
+  if (p.BR == 32) return launch_limb_g<G, NP, 32>(b, p, ticket, grid, smem, s);
+  return launch_limb_g<G, NP, 16>(b, p, ticket, grid, smem, s);
 }
 
 // Task table (seg_tasks, which also zeroes the ticket behind the prefix array) + the limb kernel.
@@ -363,17 +426,17 @@ cudaError_t launch_limb_hist(const BucketLaunch& b0, const LimbPlan& p, cudaStre
   cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s, /*ticket=*/true, b.rows_acc);
   if (e != cudaSuccess) return e;
   uint32_t* ticket = const_cast<uint32_t*>(b.chunk_prefix) + b.nSlots + 1;
-  const size_t smem = limb_smem(p.padB, p.G, (int)b.ldr, p.BR, p.threads, p.NP);
-  const int grid = device_sm_count() * (p.threads == 256 ? 2 : 1);
+  const size_t smem = limb_smem(p.padB, p.G, (int)b.ldr, p.BR, p.threads, p.NP, p.tma != 0);
+  const int grid = device_sm_count() * (p.threads <= 384 ? 2 : 1);
   count_k4_variant(B2RF_K4_LIMB);
   if (p.NP == 7) {
-    if (p.G == 32) return launch_limb_g<32, 7>(b, p, ticket, grid, smem, s);
-    if (p.G == 16) return launch_limb_g<16, 7>(b, p, ticket, grid, smem, s);
-    return launch_limb_g<8, 7>(b, p, ticket, grid, smem, s);
+    if (p.G == 32) return launch_limb_br<32, 7>(b, p, ticket, grid, smem, s);
+    if (p.G == 16) return launch_limb_br<16, 7>(b, p, ticket, grid, smem, s);
+    return launch_limb_br<8, 7>(b, p, ticket, grid, smem, s);
   }
-  if (p.G == 32) return launch_limb_g<32, 9>(b, p, ticket, grid, smem, s);
-  if (p.G == 16) return launch_limb_g<16, 9>(b, p, ticket, grid, smem, s);
-  return launch_limb_g<8, 9>(b, p, ticket, grid, smem, s);
+  if (p.G == 32) return launch_limb_br<32, 9>(b, p, ticket, grid, smem, s);
+  if (p.G == 16) return launch_limb_br<16, 9>(b, p, ticket, grid, smem, s);
+  return launch_limb_br<8, 9>(b, p, ticket, grid, smem, s);
 }
 
 // 1 when every label is an integer of magnitude <= 2^24 (then w*y and w*y*y are integers below 2^53 and the narrow windows hold
