@@ -308,6 +308,8 @@ def main():
     updates_per_fit = float(internal_or_evaluated) * fsub if internal_or_evaluated is not None else float("nan")
     phases = {k: round(sum(f.timers[k] for f in forests) / len(forests), 4) for k in ("init", "findSplits", "findBestSplits", "chooseSplits", "total")}
     phys_updates = float(f0.counters.get("bin_updates", 0))
+    gpu_launches = int(sum(f.counters["kernel_launches"] for f in forests))
+    cfg_extra = {"node_groups": f0.counters["groups"], "forest_nodes": int(f0.num_nodes())}
     traffic = k4_traffic(args.workload)
     kc = trainer.k4_launch_counts()
     k4_kernel = ("limb_hist_kernel (K4: per-node shared-memory histograms of fixed-point limbs over row segments, native 32-bit adds)"
@@ -337,7 +339,7 @@ def main():
     # (strong scaling of one dataset): one warm-up + one timed fit, device-timed, max over ranks ----------------------------------
     c4 = None
     if world > 1 and not args.no_c4:
-        X = y = Xh = yh = forests = eouts = fe = estep = step = None   # release the C3 tensors (device and pinned host)
+        X = y = Xh = yh = forests = eouts = fe = estep = step = f0 = None   # release the C3 tensors (device and pinned host)
         import gc
         gc.collect()
         torch.cuda.empty_cache()
@@ -376,7 +378,7 @@ def main():
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": make_config(args.workload, wl, n_local, world, {"node_groups": f0.counters["groups"], "forest_nodes": int(f0.num_nodes())}),
+            "config": make_config(args.workload, wl, n_local, world, cfg_extra),
             "phases_s": phases,
             "roofline": {"bound": "hbm", "kernel": k4_kernel,
                          "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -394,7 +396,7 @@ def main():
                          "note": "K4 is bound by shared-memory atomic throughput, not HBM: 22 bin updates (7 native 32-bit adds each) per 37 "
                                  "algorithmic bytes; see DESIGN.md section 2 and profiles/"},
             "e2e": e2e, "cpu_baseline": cpu, "cpu_baseline_sklearn": skl, "mgpu_parity": mgpu_parity, "c4": c4,
-            "gpu_launches": int(sum(f.counters["kernel_launches"] for f in forests)),
+            "gpu_launches": gpu_launches,
             "clocks": sampler.summary(),
         }
         print(json.dumps(line), flush=True)

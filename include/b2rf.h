@@ -136,6 +136,14 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins, int64_t ldb, const vo
 int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream);
 /* K5 binsToBestSplit (row a8) on the (reduced) histogram, then the driver tail (row a9).  Synchronises the stream. */
 int b2rf_trainer_end_group(b2rf_trainer* t, void* stream);
+/* fitMultiple shared passes (reference: CrossValidator around the tree estimator, `ML 07 - Random Forests and
+ * Hyperparameter Tuning.py:74-77,143-149`): the candidates of one fold are separate trainers bound to the SAME bin matrices.
+ * b2rf_trainers_begin_group_shared = begin_group of every listed trainer (started[i] = 1 / 0, n_cells[i] as there) with ONE K4
+ * launch whose task table spans the node slots of all of them (trainers whose launch shape differs get their own launch);
+ * b2rf_trainers_end_group_shared = end_group of every listed trainer that started a group, with one stream synchronisation.
+ * Every trainer ends with exactly the forest it builds alone. */
+int b2rf_trainers_begin_group_shared(b2rf_trainer** ts, int32_t n, int64_t* n_cells, int32_t* started, void* stream);
+int b2rf_trainers_end_group_shared(b2rf_trainer** ts, int32_t n, void* stream);
 /* Introspection of the group in flight (valid between begin_group and end_group; debug / parity tests: the reduced histogram the
  * caller holds can then be compared cell by cell with DTStatsAggregator's contents).  Slot s is node h_node_id[s] (heap numbering,
  * root = 1) of tree h_tree[s]; its j-th drawn feature and that feature's first cell inside the slot are h_slot_fo[s][j][0..1]; the

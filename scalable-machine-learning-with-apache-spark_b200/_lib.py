@@ -59,6 +59,8 @@ _SIGS = {
     "b2rf_trainer_trace": (C.c_int, [vp, vp, vp]),
     "b2rf_k4_launch_counts": (C.c_int, [vp, i32]),
     "b2rf_trainer_group_info": (C.c_int, [vp] * 6),
+    "b2rf_trainers_begin_group_shared": (C.c_int, [vp, i32, vp, vp, vp]),
+    "b2rf_trainers_end_group_shared": (C.c_int, [vp, i32, vp]),
     "b2rf_set_option": (C.c_int, [C.c_char_p, i64]),
     "b2rf_hist_build": (C.c_int, [vp, i64, i32, i32, vp, vp, i64, vp, i64, vp, i32, i64, vp, vp, i32, vp, vp]),
     "b2rf_predict": (C.c_int, [vp, i64, i64, i32] + [vp] * 12),

@@ -54,6 +54,17 @@ struct __align__(16) DSeg {
   uint32_t buf;
 };
 
+// Everything a segment-mode K4 task needs to know about its node slot, resolved on the host: lets one launch serve slots of
+// several trainers (fitMultiple's shared passes: every candidate forest of a fold rides in the same K4 launch).
+struct __align__(16) SlotSrc {
+  const DSeg* seg;                              // the node's row segment
+  const uint32_t* idx0; const uint32_t* idx1;   // the owning trainer's packed row lists (both ping-pong buffers)
+  const double* y0; const double* y1;           // ... and label lists
+  const uint2* fo;                              // [Fsub] (feature, first cell of that feature inside the slot)
+  double* hb;                                   // first cell of the slot in its trainer's histogram
+  int32_t cells; int32_t pad;
+};
+
 struct BucketLaunch {
   const uint8_t* bins_rm; int64_t ldr;   // row-major bin codes [row][ldr]
   const double* y;
@@ -74,6 +85,7 @@ struct BucketLaunch {
   // labels carried with the row lists (same positions as idx0 / idx1); nullptr: gather a.y[row]
   const double* y0; const double* y1;
   unsigned long long* rows_acc;          // optional device counter: += rows visited by this launch (segment mode; physical update count)
+  const SlotSrc* slots;                  // limb kernel only: per-slot sources (overrides dseg / slot_pos / idx / y / slot_fo / slot_base / hist)
 };
 
 // Which K4 implementation a launch used (b2rf_k4_launch_counts; tests assert on it).
@@ -86,6 +98,7 @@ long long k4_variant_count(int v);
 struct LimbPlan { int G, BR, threads, padB, NP, tma; };
 bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, bool wantTma, LimbPlan* p);
 cudaError_t launch_limb_hist(const BucketLaunch& b, const LimbPlan& p, cudaStream_t s);
+cudaError_t launch_seg_tasks_slots(const SlotSrc* slots, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s);   // task table + ticket from SlotSrc segments
 cudaError_t launch_labels_integer(const double* y, int64_t n, int32_t* d_flag, cudaStream_t s);   // *d_flag (preset to 1) cleared unless every label is an integer, |y| <= 2^24
 
 constexpr int SEG_CH = 4096;            // rows per (node, chunk) task

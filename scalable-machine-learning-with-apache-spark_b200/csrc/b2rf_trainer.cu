@@ -290,6 +290,10 @@ struct b2rf_trainer {
   DevBuf<uint32_t> dIdx0, dIdx1, dPartPrefix, dLeftCnt, dLeftOff, dPredBits;
   DevBuf<double> dY0, dY1;      // labels carried with the row lists (same positions), when memory allows: K4 then reads them as a stream
   bool carryY = false;
+  // fitMultiple shared passes: begin_group can leave its (limb) K4 launch to the caller, who merges the slots of several trainers
+  bool deferK4 = false, deferred = false;
+  BucketLaunch deferB; LimbPlan deferPlan;
+  DevBuf<SlotSrc> dShared; PinBuf<SlotSrc> hShared; DevBuf<uint32_t> dSharedPrefix;
   bool labelsInt = false;       // every local label is an integer of magnitude <= 2^24: the narrow (7-plane) limb kernel is exact
   DevBuf<unsigned long long> dBindTmp;
   DevBuf<unsigned long long> dRowsAcc;   // rows visited by the K4 launches of this fit (segment mode)
@@ -333,7 +337,7 @@ struct b2rf_trainer {
     dn.release(); dnUpd.release(); dCat.release(); dSlotFo.release(); dSlotBase.release(); dParent.release();
     dHasParent.release(); dNumBins.release(); dIsCat.release(); dTreeIds.release(); dRec.release();
     dCellBins.release(); dKind.release(); dParentCls.release(); dClsOut.release(); hParentCls.release(); hClsOut.release();
-    dSeg.release(); dIdx0.release(); dIdx1.release(); dY0.release(); dY1.release(); dBindTmp.release(); dRowsAcc.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
+    dSeg.release(); dIdx0.release(); dIdx1.release(); dY0.release(); dY1.release(); dBindTmp.release(); dRowsAcc.release(); dShared.release(); hShared.release(); dSharedPrefix.release(); dPartPrefix.release(); dLeftCnt.release(); dLeftOff.release(); dPredBits.release();
     dSlotPos.release(); dSplitPos.release(); hSlotPos.release(); hSplitPos.release();
     dRecMask.release(); hRecMask.release();
     dSlotCount.release(); dCursor.release(); dChunkPrefix.release(); dRowList.release(); dSlotStart.release(); dSlotCells.release(); hSlotCells.release();
@@ -479,10 +483,6 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
   const uint8_t* d_bins_rm = static_cast<const uint8_t*>(d_bins_rm_v);
   if (!t || !d_bins || !d_y || !d_w || !d_hist || n_rows_local < 0 || ((ldb * (t ? t->codeBytes : 1)) & 15) || ldb < n_rows_local || ldw < n_rows_local || (d_node && ldn < n_rows_local)) {
     set_error("b2rf_trainer_bind: bad argument (ldb must be a multiple of 16 and every leading dimension >= n_rows)"); return B2RF_ERR_ARG;
-  }
-  {   // experiment hook: L2 fetch granularity (bytes) for the 64-byte code-row gathers; unset = driver default
-    static const int gran = [] { const char* m = std::getenv("B2RF_L2_FETCH"); return m ? atoi(m) : 0; }();
-    if (gran > 0) cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)gran);
   }
   t->d_bins = d_bins; t->ldb = ldb; t->d_y = d_y; t->d_w = d_w; t->ldw = ldw; t->d_node = d_node; t->ldn = ldn; t->nLocal = n_rows_local;
   t->d_hist = d_hist; t->histCells = hist_cells;
@@ -779,7 +779,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     b.chunk_prefix = t->dChunkPrefix.p; b.nSlots = (int32_t)nSlots; b.CH = t->segMode ? SEG_CH : t->chunkRows; b.slot_fo = t->dSlotFo.p;
     b.slot_base = t->dSlotBase.p; b.slot_cells = t->dSlotCells.p; b.Fsub = t->Fsub; b.maxCells = maxCells; b.padB = padB; b.G = G; b.codeBytes = t->codeBytes; b.hist = t->d_hist;
     { static const bool zr = [] { const char* m = std::getenv("B2RF_ZERO_REG"); return !(m && *m == '0'); }(); b.zeroReg = zr ? 1 : 0; }
-    b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr; b.y0 = nullptr; b.y1 = nullptr; b.rows_acc = t->dRowsAcc.p;
+    b.dseg = nullptr; b.slot_pos = nullptr; b.idx0 = nullptr; b.idx1 = nullptr; b.y0 = nullptr; b.y1 = nullptr; b.rows_acc = t->dRowsAcc.p; b.slots = nullptr;
     std::string err;
     cudaError_t e;
     if (t->C) {   // multiclass: class-count histograms (segment mode only, checked in bind)
@@ -797,8 +797,11 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       // compare-and-swap kernels, which also serve what the limb kernel does not (uint16 codes, labels not carried, huge histograms)
       const bool fp64Only = opt_k4_fp64().load() != 0;
       LimbPlan plan;
-      if (!fp64Only && limb_plan(b, maxBinsAll, t->labelsInt, opt_k4_tma().load() != 0, &plan)) e = launch_limb_hist(b, plan, s);
-      else e = launch_segment_hist(b, s);
+      t->deferred = false;
+      if (!fp64Only && limb_plan(b, maxBinsAll, t->labelsInt, opt_k4_tma().load() != 0, &plan)) {
+        if (t->deferK4) { t->deferB = b; t->deferPlan = plan; t->deferred = true; e = cudaSuccess; }   // launched by b2rf_trainers_begin_group_shared
+        else e = launch_limb_hist(b, plan, s);
+      } else e = launch_segment_hist(b, s);
       t->nKernels += 2;
     } else {
       e = launch_bucket_pipeline(a, b, t->dCursor.p, s, &err);
@@ -831,9 +834,10 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
   return 1;
 }
 
-int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
-  if (!t || !t->inGroup) { set_error("b2rf_trainer_end_group: no group in flight"); return B2RF_ERR_STATE; }
-  cudaStream_t s = (cudaStream_t)stream;
+}  // extern "C"
+
+// end_group, first half: K5 + the copies of its results, all asynchronous on the stream.
+static int end_group_launch(b2rf_trainer* t, cudaStream_t s) {
   const size_t nSlots = t->group.size();
   // ---- K5 ----
   SplitLaunch a;
@@ -862,9 +866,15 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
       if (level_of(t->trees[t->group[sl].tree][t->group[sl].nidx].id) + 1 < t->p.maxDepth) kids += 2;
     t->ensure_draws(kids + t->stack.size());
   }
-  if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
+  t->tWait -= tw0;   // completed by end_group_tail
+  return B2RF_OK;
+}
+
+// end_group, second half (after the stream has been synchronised): driver tail + K6 partitions.
+static int end_group_tail(b2rf_trainer* t, cudaStream_t s) {
+  const size_t nSlots = t->group.size();
   const double tc0 = now_s();
-  t->tWait += tc0 - tw0;
+  t->tWait += tc0;
   if (t->evPending) {
     float ms = 0;
     if (cudaEventElapsedTime(&ms, t->ev0, t->ev1) == cudaSuccess) t->tHist += ms * 1e-3;
@@ -958,6 +968,84 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   t->groupNo++;
   t->exported = false;
   t->tChoose += now_s() - tc0; t->tTail += now_s() - tc0;
+  return B2RF_OK;
+}
+
+extern "C" {
+
+int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
+  if (!t || !t->inGroup) { set_error("b2rf_trainer_end_group: no group in flight"); return B2RF_ERR_STATE; }
+  cudaStream_t s = (cudaStream_t)stream;
+  { const int rc = end_group_launch(t, s); if (rc) return rc; }
+  if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
+  return end_group_tail(t, s);
+}
+
+// ---- fitMultiple shared passes (`ML 07 - Random Forests and Hyperparameter Tuning.py:74-77,143-149`) ----
+// begin_group of every listed trainer (host scheduling + descriptor uploads), then ONE K4 launch whose task table spans the node
+// slots of all of them: a shallow candidate's few nodes ride with the deep one's.  Trainers whose launch shape differs (other bin
+// matrix, features per node, bin count, label form) or that do not run the limb kernel get their own launch.
+int b2rf_trainers_begin_group_shared(b2rf_trainer** ts, int32_t n, int64_t* n_cells, int32_t* started, void* stream) {
+  if (!ts || n <= 0 || !n_cells || !started) { set_error("b2rf_trainers_begin_group_shared: bad argument"); return B2RF_ERR_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  std::vector<b2rf_trainer*> def;
+  for (int i = 0; i < n; i++) {
+    b2rf_trainer* t = ts[i];
+    if (!t) { set_error("b2rf_trainers_begin_group_shared: null trainer"); return B2RF_ERR_ARG; }
+    t->deferK4 = true; t->deferred = false;
+    const int rc = b2rf_trainer_begin_group(t, &n_cells[i], stream);
+    t->deferK4 = false;
+    if (rc < 0) return rc;
+    started[i] = rc;
+    if (rc == 1 && t->deferred) def.push_back(t);
+  }
+  auto same = [](const b2rf_trainer* a, const b2rf_trainer* b) {
+    const BucketLaunch &x = a->deferB, &y = b->deferB; const LimbPlan &p = a->deferPlan, &q = b->deferPlan;
+    return x.bins_rm == y.bins_rm && x.ldr == y.ldr && x.Fsub == y.Fsub && x.CH == y.CH && p.G == q.G && p.BR == q.BR && p.threads == q.threads &&
+           p.padB == q.padB && p.NP == q.NP && p.tma == q.tma;
+  };
+  std::vector<char> done(def.size(), 0);
+  for (size_t i = 0; i < def.size(); i++) {
+    if (done[i]) continue;
+    std::vector<b2rf_trainer*> cls{def[i]};
+    done[i] = 1;
+    for (size_t j = i + 1; j < def.size(); j++) if (!done[j] && same(def[i], def[j])) { cls.push_back(def[j]); done[j] = 1; }
+    b2rf_trainer* o = cls[0];                       // owner of the merged slot table
+    cudaError_t e;
+    if (cls.size() == 1) e = launch_limb_hist(o->deferB, o->deferPlan, s);
+    else {
+      size_t total = 0;
+      for (auto* t : cls) total += t->group.size();
+      if (!o->hShared.ensure(total) || !o->dShared.ensure(total) || !o->dSharedPrefix.ensure(total + 2)) return B2RF_ERR_CUDA;
+      size_t k = 0;
+      for (auto* t : cls)
+        for (size_t sl = 0; sl < t->group.size(); sl++) {
+          SlotSrc& ss = o->hShared.p[k++];
+          ss.seg = t->dSeg.p + t->hSlotPos.p[sl];
+          ss.idx0 = t->dIdx0.p; ss.idx1 = t->dIdx1.p; ss.y0 = t->dY0.p; ss.y1 = t->dY1.p;
+          ss.fo = t->dSlotFo.p + sl * (size_t)t->Fsub;
+          ss.hb = t->d_hist + (size_t)t->hSlotBase.p[sl] * 4;
+          ss.cells = t->hSlotCells.p[sl]; ss.pad = 0;
+        }
+      if (!cuda_ok(cudaMemcpyAsync(o->dShared.p, o->hShared.p, total * sizeof(SlotSrc), cudaMemcpyHostToDevice, s), "upload merged slot table")) return B2RF_ERR_CUDA;
+      BucketLaunch b = o->deferB;
+      b.slots = o->dShared.p; b.nSlots = (int32_t)total; b.chunk_prefix = o->dSharedPrefix.p; b.rows_acc = nullptr;
+      e = launch_limb_hist(b, o->deferPlan, s);
+    }
+    if (!cuda_ok(e, "shared histogram launch")) return B2RF_ERR_CUDA;
+    for (auto* t : cls) { cudaEventRecord(t->ev1, s); t->deferred = false; }   // each member's K4 time = the merged launch (shared, not additive)
+  }
+  return B2RF_OK;
+}
+
+// end_group of every listed trainer that has a group in flight: all K5 launches and result copies first, ONE synchronisation, then
+// the driver tails (each followed by its K6 partitions, which run while the next tail is computed on the host).
+int b2rf_trainers_end_group_shared(b2rf_trainer** ts, int32_t n, void* stream) {
+  if (!ts || n <= 0) { set_error("b2rf_trainers_end_group_shared: bad argument"); return B2RF_ERR_ARG; }
+  cudaStream_t s = (cudaStream_t)stream;
+  for (int i = 0; i < n; i++) if (ts[i] && ts[i]->inGroup) { const int rc = end_group_launch(ts[i], s); if (rc) return rc; }
+  if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
+  for (int i = 0; i < n; i++) if (ts[i] && ts[i]->inGroup) { const int rc = end_group_tail(ts[i], s); if (rc) return rc; }
   return B2RF_OK;
 }
 

@@ -591,6 +591,30 @@ cudaError_t launch_seg_tasks(const DSeg* dseg, const int64_t* pos, int n, int CH
   return cudaGetLastError();
 }
 
+__global__ void __launch_bounds__(1024) seg_tasks_slots_kernel(const SlotSrc* slots, int n, int CH, uint32_t* chunkPrefix) {
+  __shared__ uint32_t s_chunks[1024];
+  const int tid = threadIdx.x;
+  const int per = (n + 1023) / 1024;
+  const int b = tid * per, e = min(n, b + per);
+  uint32_t c = 0;
+  for (int i = b; i < e; i++) c += (slots[i].seg->count + CH - 1) / CH;
+  s_chunks[tid] = c;
+  __syncthreads();
+  if (tid == 0) {
+    uint32_t ac = 0;
+    for (int i = 0; i < 1024; i++) { const uint32_t tc = s_chunks[i]; s_chunks[i] = ac; ac += tc; }
+    chunkPrefix[n] = ac;
+    chunkPrefix[n + 1] = 0u;   // work ticket
+  }
+  __syncthreads();
+  c = s_chunks[tid];
+  for (int i = b; i < e; i++) { chunkPrefix[i] = c; c += (slots[i].seg->count + CH - 1) / CH; }
+}
+cudaError_t launch_seg_tasks_slots(const SlotSrc* slots, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s) {
+  seg_tasks_slots_kernel<<<1, 1024, 0, s>>>(slots, n, CH, chunkPrefix);
+  return cudaGetLastError();
+}
+
 cudaError_t launch_segment_hist(const BucketLaunch& b, cudaStream_t s) {
   cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s, false, b.rows_acc);
   if (e != cudaSuccess) return e;

@@ -151,12 +151,22 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
     while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.chunk_prefix[mid] <= bt) lo = mid; else hi = mid; }
     const int slot = lo;
     const uint32_t begin = (bt - a.chunk_prefix[slot]) * (uint32_t)a.CH;
-    const DSeg sg = a.dseg[a.slot_pos[slot]];
-    const uint32_t* rl = (sg.buf ? a.idx1 : a.idx0) + sg.start + begin;
-    const double* yl = (sg.buf ? a.y1 : a.y0) + sg.start + begin;
+    DSeg sg; const uint32_t* rl; const double* yl; const uint2* fo; double* hb; int slotCells;
+    if (a.slots) {   // slots of several trainers in one launch (fitMultiple shared passes)
+      const SlotSrc ss = a.slots[slot];
+      sg = *ss.seg;
+      rl = (sg.buf ? ss.idx1 : ss.idx0) + sg.start + begin;
+      yl = (sg.buf ? ss.y1 : ss.y0) + sg.start + begin;
+      fo = ss.fo; hb = ss.hb; slotCells = ss.cells;
+    } else {
+      sg = a.dseg[a.slot_pos[slot]];
+      rl = (sg.buf ? a.idx1 : a.idx0) + sg.start + begin;
+      yl = (sg.buf ? a.y1 : a.y0) + sg.start + begin;
+      fo = a.slot_fo + (size_t)slot * a.Fsub;
+      hb = a.hist + (size_t)a.slot_base[slot] * 4;
+      slotCells = a.slot_cells[slot];
+    }
     const int n = (int)min((uint32_t)a.CH, sg.count - begin);
-    const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
-    double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
     const int j = g * G + fl;
     const bool active = j < a.Fsub;
     const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
@@ -165,7 +175,7 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
     for (int i = tid; i < n; i += THREADS) ex = max(ex, (uint32_t)__double2hiint(yl[i]) & 0x7fffffffu);
     ex = __reduce_max_sync(FULL, ex);
     if (lane == 0) s_red[warp] = ex;
-    bool direct = (int64_t)n * a.Fsub < (int64_t)a.slot_cells[slot];   // fewer updates than cells: skip the shared-memory round trip
+    bool direct = (int64_t)n * a.Fsub < (int64_t)slotCells;   // fewer updates than cells: skip the shared-memory round trip
     if (!direct) {
       uint4* h4 = reinterpret_cast<uint4*>(hist);
       for (int c = tid; c < (int)(histBytes >> 4); c += THREADS) h4[c] = make_uint4(0u, 0u, 0u, 0u);
@@ -364,7 +374,7 @@ static size_t limb_smem(int padB, int G, int ldr, int BR, int threads, int NP, b
 // the fp64 compare-and-swap kernel of k4_hist.cu): uint8 codes, labels carried in the row lists, 16-byte aligned code rows, and a
 // task histogram that leaves room for the staging ring.
 bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, bool wantTma, LimbPlan* p) {
-  if (b.codeBytes != 1 || b.dseg == nullptr || b.y0 == nullptr || b.y1 == nullptr) return false;
+  if (b.codeBytes != 1 || ((b.dseg == nullptr || b.y0 == nullptr || b.y1 == nullptr) && b.slots == nullptr)) return false;
   if ((b.ldr & 15) != 0 || (reinterpret_cast<uintptr_t>(b.bins_rm) & 15) != 0 || b.ldr > 1024) return false;
   const size_t cap2 = (size_t)113 * 1024, cap1 = (size_t)226 * 1024;   // two CTAs per SM / one
   const int NP = narrow ? 7 : 9;
@@ -423,7 +433,8 @@ static cudaError_t launch_limb_br(const BucketLaunch& b, const LimbPlan& p, uint
 cudaError_t launch_limb_hist(const BucketLaunch& b0, const LimbPlan& p, cudaStream_t s) {
   BucketLaunch b = b0;
   b.padB = p.padB; b.G = p.G;
-  cudaError_t e = launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s, /*ticket=*/true, b.rows_acc);
+  cudaError_t e = b.slots ? launch_seg_tasks_slots(b.slots, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s)
+                          : launch_seg_tasks(b.dseg, b.slot_pos, b.nSlots, b.CH, const_cast<uint32_t*>(b.chunk_prefix), s, /*ticket=*/true, b.rows_acc);
   if (e != cudaSuccess) return e;
   uint32_t* ticket = const_cast<uint32_t*>(b.chunk_prefix) + b.nSlots + 1;
   const size_t smem = limb_smem(p.padB, p.G, (int)b.ldr, p.BR, p.threads, p.NP, p.tma != 0);

@@ -379,11 +379,11 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
     candidates of one fold — `ML 07 - Random Forests and Hyperparameter Tuning.py:74-77,143-149`; BASELINE config 5).
 
     What is shared: the findSplits sample, thresholds and both bin matrices (once per distinct (maxBins, seed): findSplits
-    depends on nothing else), the label vector and the device copy of X.  What is not: bag weights and row lists (MLlib draws
-    bag counts row-major over numTrees, so they differ between candidates).  The candidates' node-group loops then run in
-    lockstep on one CUDA stream each: every candidate's histogram kernels are in flight while another candidate's host-side
-    scheduling runs, and small candidates fill the SMs that a shallow forest leaves idle.  Each candidate's forest is
-    identical to what fit_tensors returns for it."""
+    depends on nothing else), the label vector, the device copy of X — and the histogram passes: the candidates' node-group
+    loops run in lockstep, and each round's K4 is ONE launch whose task table spans the node slots of every candidate still
+    growing (b2rf_trainers_begin_group_shared), so a shallow candidate's few nodes ride with the deep one's.  What is not
+    shared: bag weights and row lists (MLlib draws bag counts row-major over numTrees, so they differ between candidates).
+    Each candidate's forest is identical to what fit_tensors returns for it."""
     _require_cuda(X, "X")
     _require_cuda(y, "y")
     dev = X.device
@@ -414,8 +414,7 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
             thr_h, ns_h, bins, bins_rm = shared[key]
             w, node = bag(params.seed, S["po"], S["part0"], params.numTrees, params.subsamplingRate, params.bootstrap, dev, ld=ld,
                           want_node=_want_node(hist_mode, bins_rm, n_local))
-            cands.append(dict(S=S, params=params, thr_h=thr_h, ns_h=ns_h, bins=bins, bins_rm=bins_rm, w=w, node=node, h=C.c_void_p(),
-                              stream=torch.cuda.Stream(), ncell=C.c_int64()))
+            cands.append(dict(S=S, params=params, thr_h=thr_h, ns_h=ns_h, bins=bins, bins_rm=bins_rm, w=w, node=node, h=C.c_void_p()))
         torch.cuda.synchronize(dev)
         try:
             for c in cands:
@@ -431,19 +430,20 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
                                           c["hist"].data_ptr(), cells))
             torch.cuda.synchronize(dev)
             active = list(cands)
+            st = _stream()
             while active:
-                started = []
-                for c in active:                       # asynchronous: selectNodesToSplit on the host, K4 on the candidate's stream
-                    with torch.cuda.stream(c["stream"]):
-                        st = C.c_void_p(c["stream"].cuda_stream)
-                        if check(L.b2rf_trainer_begin_group(c["h"], C.byref(c["ncell"]), st)) == 1:
-                            if c["S"]["world"] > 1:
-                                c["S"]["dist"].all_reduce(c["hist"][: c["ncell"].value * 4], group=group)
-                            started.append(c)
-                for c in started:                      # K5 + driver tail; waits for this candidate's stream only
-                    with torch.cuda.stream(c["stream"]):
-                        check(L.b2rf_trainer_end_group(c["h"], C.c_void_p(c["stream"].cuda_stream)))
-                active = started
+                # one round = one node group of every candidate still growing: host scheduling for all of them, ONE K4 launch over
+                # the union of their node slots, [all-reduce per candidate], all K5 launches, one synchronisation, the driver tails
+                n = len(active)
+                hs = (C.c_void_p * n)(*[c["h"].value for c in active])
+                ncells = (C.c_int64 * n)()
+                started = (C.c_int32 * n)()
+                check(L.b2rf_trainers_begin_group_shared(hs, n, ncells, started, st))
+                for i, c in enumerate(active):
+                    if started[i] and c["S"]["world"] > 1:
+                        c["S"]["dist"].all_reduce(c["hist"][: ncells[i] * 4], group=group)
+                check(L.b2rf_trainers_end_group_shared(hs, n, st))
+                active = [c for i, c in enumerate(active) if started[i]]
             torch.cuda.synchronize(dev)
             forests = []
             for c in cands:
