@@ -144,7 +144,17 @@ struct BlockPool {
   bool pinned;
   explicit BlockPool(bool pin) : pinned(pin) {}
   static int current_device() { int d = 0; cudaGetDevice(&d); return d; }
+  // Requests are rounded up to a coarse size class (1/8 steps between powers of two, <= 12.5 % slack) so that fits whose row counts
+  // differ slightly — the folds of a cross-validation — reuse each other's blocks instead of paying cudaMalloc for gigabyte lists.
+  static size_t size_class(size_t bytes) {
+    if (bytes <= 4096) return 4096;
+    size_t p = 1;
+    while (p < bytes) p <<= 1;
+    const size_t step = p >> 4;               // 1/8 of the lower power of two
+    return (bytes + step - 1) / step * step;
+  }
   void* take(size_t bytes, size_t* got) {
+    bytes = size_class(bytes);
     const int dev = pinned ? -1 : current_device();
     {
       std::lock_guard<std::mutex> lk(mu);
@@ -163,7 +173,7 @@ struct BlockPool {
     if (!p) return;
     std::lock_guard<std::mutex> lk(mu);
     const int dev = pinned ? -1 : current_device();
-    if (free_.size() >= 96) { if (pinned) cudaFreeHost(p); else cudaFree(p); return; }
+    if (free_.size() >= 768) { if (pinned) cudaFreeHost(p); else cudaFree(p); return; }   // a 9-candidate fitMultiple round returns ~400 blocks
     free_.push_back({p, bytes, dev});
   }
 };
@@ -301,7 +311,7 @@ struct b2rf_trainer {
   DevBuf<int64_t> dSlotPos, dSplitPos;
   PinBuf<int64_t> hSlotPos, hSplitPos;
   std::vector<uint64_t> treeBase;
-  PinBuf<DNodeUpdate> hUpd;
+  PinBuf<DNodeUpdate> hUpd, hUpdTail;   // staging of node-table updates: one buffer per call site (begin_group / driver tail), see flush_node_updates
   PinBuf<uint2> hSlotFo;
   PinBuf<int64_t> hSlotBase;
   PinBuf<double> hParent;
@@ -341,7 +351,7 @@ struct b2rf_trainer {
     dSlotPos.release(); dSplitPos.release(); hSlotPos.release(); hSplitPos.release();
     dRecMask.release(); hRecMask.release();
     dSlotCount.release(); dCursor.release(); dChunkPrefix.release(); dRowList.release(); dSlotStart.release(); dSlotCells.release(); hSlotCells.release();
-    hUpd.release(); hSlotFo.release(); hSlotBase.release(); hParent.release(); hHasParent.release(); hTreeIds.release(); hRec.release();
+    hUpd.release(); hUpdTail.release(); hSlotFo.release(); hSlotBase.release(); hParent.release(); hHasParent.release(); hTreeIds.release(); hRec.release();
     if (ev0) cudaEventDestroy(ev0);
     if (ev1) cudaEventDestroy(ev1);
   }
@@ -567,8 +577,11 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
   return B2RF_OK;
 }
 
-// Uploads the queued node-table changes (and new categorical masks) and applies them with one scatter launch.
-static int flush_node_updates(b2rf_trainer* t, cudaStream_t s) {
+// Uploads the queued node-table changes (and new categorical masks) and applies them with one scatter launch.  The upload is an
+// asynchronous copy from a pinned staging buffer; begin_group and the driver tail each have their own, because the tail's copy can
+// still be queued behind other trainers' kernels on a shared stream when the next begin_group fills its buffer (a stream
+// synchronisation always separates two uses of the same buffer).
+static int flush_node_updates(b2rf_trainer* t, cudaStream_t s, bool tail = false) {
   {  // one scatter launch must not carry two records for the same node: keep the latest
     const size_t tableSize = (size_t)t->nodeStride * (size_t)t->T;
     if (t->updStamp.size() < tableSize) t->updStamp.resize(tableSize, 0);
@@ -585,10 +598,11 @@ static int flush_node_updates(b2rf_trainer* t, cudaStream_t s) {
   const size_t nUpd = t->pending.size();
   bool ok = true;
   if (nUpd) {
-    if (!t->hUpd.ensure(nUpd) || !t->dnUpd.ensure(nUpd)) return B2RF_ERR_CUDA;
-    memcpy(t->hUpd.p, t->pending.data(), nUpd * sizeof(DNodeUpdate));
+    PinBuf<DNodeUpdate>& hb = tail ? t->hUpdTail : t->hUpd;
+    if (!hb.ensure(nUpd) || !t->dnUpd.ensure(nUpd)) return B2RF_ERR_CUDA;
+    memcpy(hb.p, t->pending.data(), nUpd * sizeof(DNodeUpdate));
     t->pending.clear();
-    ok &= cuda_ok(cudaMemcpyAsync(t->dnUpd.p, t->hUpd.p, nUpd * sizeof(DNodeUpdate), cudaMemcpyHostToDevice, s), "upload node updates");
+    ok &= cuda_ok(cudaMemcpyAsync(t->dnUpd.p, hb.p, nUpd * sizeof(DNodeUpdate), cudaMemcpyHostToDevice, s), "upload node updates");
     ok &= cuda_ok(launch_scatter_dnodes(t->dn.p, t->dnUpd.p, (int64_t)nUpd, s), "scatter node updates");
     t->nKernels++;
   }
@@ -943,7 +957,7 @@ static int end_group_tail(b2rf_trainer* t, cudaStream_t s) {
   if (needStride > t->nodeStride) { const int rc = grow_node_table(t, needStride, s); if (rc) return rc; }
   if (t->segMode && !splits.empty()) {
     // K6 in segment mode: stable partition of every split node's row segment into its children's segments
-    { const int rc = flush_node_updates(t, s); if (rc) return rc; }   // the partition kernels read the parents' split descriptors
+    { const int rc = flush_node_updates(t, s, /*tail=*/true); if (rc) return rc; }   // the partition kernels read the parents' split descriptors
     const size_t k = splits.size();
     std::vector<char> seen(t->T, 0);
     for (auto& sp : splits) if (!seen[sp.first]) { seen[sp.first] = 1; splitRowsBound += t->inBag[sp.first]; }

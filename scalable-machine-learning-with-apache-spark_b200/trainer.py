@@ -431,6 +431,9 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
             torch.cuda.synchronize(dev)
             active = list(cands)
             st = _stream()
+            dbg = os.environ.get("B2RF_TIMING") == "1"
+            t_begin = t_end = 0.0
+            rounds = 0
             while active:
                 # one round = one node group of every candidate still growing: host scheduling for all of them, ONE K4 launch over
                 # the union of their node slots, [all-reduce per candidate], all K5 launches, one synchronisation, the driver tails
@@ -438,12 +441,19 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
                 hs = (C.c_void_p * n)(*[c["h"].value for c in active])
                 ncells = (C.c_int64 * n)()
                 started = (C.c_int32 * n)()
+                ta = time.perf_counter()
                 check(L.b2rf_trainers_begin_group_shared(hs, n, ncells, started, st))
+                tb = time.perf_counter()
                 for i, c in enumerate(active):
                     if started[i] and c["S"]["world"] > 1:
                         c["S"]["dist"].all_reduce(c["hist"][: ncells[i] * 4], group=group)
                 check(L.b2rf_trainers_end_group_shared(hs, n, st))
+                t_begin += tb - ta
+                t_end += time.perf_counter() - tb
+                rounds += 1
                 active = [c for i, c in enumerate(active) if started[i]]
+            if dbg:
+                print(f"[b2rf timing] fit_many: {rounds} rounds, begin (host scheduling + launches) {t_begin:.4f} s, end (K5, wait, tails, K6) {t_end:.4f} s", flush=True)
             torch.cuda.synchronize(dev)
             forests = []
             for c in cands:

@@ -58,6 +58,18 @@ def _worker(rank, world, port, q):
         dist.all_reduce(red)
         assert np.array_equal(red.numpy()[:, 0], full[:, 0])                         # counts exact
         np.testing.assert_allclose(red.numpy()[:, 1:3], full[:, 1:3], rtol=1e-9, atol=1e-9)
+        # data-dependent errors are agreed on across ranks before anyone raises: a bad label on rank 1 only must raise on BOTH ranks
+        # (a rank that raised alone would leave the others waiting in the next collective), and good labels raise on neither
+        p = b2rf.TreeParams(impurity="gini", numTrees=3)
+        cpu = torch.device("cpu")
+        trainer._check_labels(torch.tensor([0.0, 1.0, 1.0]), p, dist, None, cpu)
+        bad = torch.tensor([0.0, 1.0, 2.5]) if rank == 1 else torch.tensor([0.0, 1.0, 0.0])
+        try:
+            trainer._check_labels(bad, p, dist, None, cpu)
+            raise AssertionError("expected IllegalArgumentException on every rank")
+        except b2rf.IllegalArgumentException as e:
+            assert "Classification labels should be in" in str(e)
+        assert trainer._agree_max(7 if rank == 0 else 3, dist, None, cpu) == 7
         q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
         import traceback

@@ -451,9 +451,10 @@ def test_fit_many_shared_passes_equals_individual_fits(b2rf, cuda):
     many = trainer.fit_many_tensors(Xd, yd, arity, grid, part_offsets=po)
     after = trainer.k4_launch_counts()
     assert len(many) == len(grid)
-    # shared passes: one K4 launch per round and launch shape (two shapes here: maxBins 40 and 64), not one per candidate and group
+    # shared passes: one K4 launch per round and launch shape (three shapes here: forests with maxBins 40, the forest with maxBins 64,
+    # the single tree that is offered every feature), not one per candidate and group
     launches = sum(after[k] - before[k] for k in after)
-    assert launches <= 2 * max(f.counters["groups"] for f in many) < sum(f.counters["groups"] for f in many)
+    assert launches <= 3 * max(f.counters["groups"] for f in many) < sum(f.counters["groups"] for f in many)
     for p, f in zip(grid, many):
         ref = trainer.fit_tensors(Xd, yd, arity, p, part_offsets=po)
         assert np.array_equal(f.tree_off, ref.tree_off) and np.array_equal(f.feature, ref.feature) and np.array_equal(f.threshold, ref.threshold)
