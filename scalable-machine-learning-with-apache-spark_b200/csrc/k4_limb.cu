@@ -37,6 +37,10 @@ constexpr uint32_t LIMB_MASK = (1u << 20) - 1u;
 constexpr int LIMB_EXP_MAX = 460;          // |exponent| of the task scale kept inside the range where every scale factor is a normal double
 constexpr int LIMB_WBITS = 5;              // bag weights are packed in 5 bits (<= 31)
 
+// fp64 add to the GLOBAL histogram, no return value (SASS REDG.E.ADD.F64).  Written as PTX because the histogram pointer comes out of a
+// per-slot table: through atomicAdd() the compiler cannot prove the address space and emits a generic atomic — an address-space query
+// plus a shared-memory compare-and-swap path and a returning global ATOM per call site.
+__device__ __forceinline__ void red_add_f64(double* p, double v) { asm volatile("red.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory"); }
 __device__ __forceinline__ double pow2d(int k) { return __hiloint2double((1023 + k) << 20, 0); }   // 2^k, k in the normal range
 __device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
@@ -202,7 +206,7 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
           if (active && (e2 >> 27)) {
             const uint32_t code = bins_rm[(size_t)(e2 & 0x7ffffffu) * ldr + e.x];
             double* c = hb + (size_t)(e.y + code) * 4;
-            atomicAdd(c, (double)(e2 >> 27)); atomicAdd(c + 1, wy2); atomicAdd(c + 2, wyy2);
+            red_add_f64(c, (double)(e2 >> 27)); red_add_f64(c + 1, wy2); red_add_f64(c + 2, wyy2);
           }
         }
       }
@@ -263,7 +267,7 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
             const double ys = __longlong_as_double((long long)x1);
             const double wy = (double)w * ys;
             double* gc = hb + (size_t)(e.y + cc) * 4;
-            atomicAdd(gc, (double)w); atomicAdd(gc + 1, wy); atomicAdd(gc + 2, wy * ys);
+            red_add_f64(gc, (double)w); red_add_f64(gc + 1, wy); red_add_f64(gc + 2, wy * ys);
           } else {
             const unsigned long long x2 = ((unsigned long long)p1.y << 32) | p1.x;
             const uint32_t hiBl = (uint32_t)(x2 >> 40) | ((p0.y >> 16) << 24);          // low 32 bits of hiB (40 bits: the top 8 are in p0.y >> 24)
@@ -279,7 +283,7 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
             const double ys = __longlong_as_double((long long)x0);
             const double wy = (double)w * ys;
             double* gc = hb + (size_t)(e.y + cc) * 4;
-            atomicAdd(gc, (double)w); atomicAdd(gc + 1, wy); atomicAdd(gc + 2, wy * ys);
+            red_add_f64(gc, (double)w); red_add_f64(gc + 1, wy); red_add_f64(gc + 2, wy * ys);
           } else {
             atomicAdd(c, p0.y >> 27);
             atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
@@ -352,7 +356,7 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
         B = ((double)cell[6 * G] * 0x1p40 + (double)cell[5 * G] * 0x1p20) + (double)cell[4 * G];
       }
       double* gp = hb + ((size_t)fo[g * G + f2].y + (size_t)bin) * 4;
-      atomicAdd(gp, (double)cnt); atomicAdd(gp + 1, A * sA); atomicAdd(gp + 2, B * sB);
+      red_add_f64(gp, (double)cnt); red_add_f64(gp + 1, A * sA); red_add_f64(gp + 2, B * sB);
     }
     // the ticket __syncthreads at the top of the next iteration orders this flush before the next task's zeroing
   }
