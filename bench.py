@@ -286,7 +286,7 @@ def main():
         return float(ms.item()), outs
 
     # ---- device-resident arm -------------------------------------------------------------------------------
-    step = lambda: trainer.fit_tensors(X, y, arity, params, part_offsets=po, keep_trace=True)
+    step = lambda: trainer.fit_tensors(X, y, arity, params, part_offsets=po)
     for _ in range(args.warmup):
         step()
     sampler = ClockSampler(local_rank)
@@ -304,8 +304,7 @@ def main():
     achieved = hist_bytes / hist_s / 1e9 if hist_s > 0 else 0.0
     # bin updates of one fit: every in-bag row of every evaluated node x features per node (from the forest's own node counts)
     fsub = params.features_per_node(F)
-    internal_or_evaluated = f0.trace_d[:, 2].sum() if f0.trace_d is not None else None
-    updates_per_fit = float(internal_or_evaluated) * fsub if internal_or_evaluated is not None else float("nan")
+    updates_per_fit = float(f0.counters.get("weighted_bin_updates", 0))
     phases = {k: round(sum(f.timers[k] for f in forests) / len(forests), 4) for k in ("init", "findSplits", "findBestSplits", "chooseSplits", "total")}
     phys_updates = float(f0.counters.get("bin_updates", 0))
     gpu_launches = int(sum(f.counters["kernel_launches"] for f in forests))

@@ -156,10 +156,11 @@ int b2rf_trainer_group_info(const b2rf_trainer* t, int64_t* n_slots, int32_t* h_
  * B2RF_CARRY_Y=0).  Takes effect at the next b2rf_trainer_bind / begin_group. */
 int b2rf_set_option(const char* name, int64_t value);
 /* h_seconds5: init(0), findSplits(0), findBestSplits (K4 device time from CUDA events), chooseSplits (K5 + driver tail),
- * total — MLlib TimeTracker phase names.  h_counts8: node groups, K4 launches, rows*trees scanned, learning nodes,
+ * total — MLlib TimeTracker phase names.  h_counts9: node groups, K4 launches, rows*trees scanned, learning nodes,
  * kernels launched by the trainer, algorithmic bytes summed over K4 launches (SURVEY.md §8d formula), rows visited by the
- * segment-mode K4 launches (times featuresPerNode = physical (row, feature) bin updates), featuresPerNode. */
-int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts8);
+ * segment-mode K4 launches (times featuresPerNode = physical (row, feature) bin updates), featuresPerNode, weighted rows summed over
+ * all evaluated nodes (times featuresPerNode = the updates MLlib's per-instance loop executes). */
+int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts9);
 /* finished forest, LearningNode.toNode(prune=true) in pre-order (row a11) */
 int b2rf_trainer_forest_sizes(b2rf_trainer* t, int64_t* n_nodes, int64_t* n_cats);
 int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature, double* h_threshold, int32_t* h_left,

@@ -308,6 +308,7 @@ struct b2rf_trainer {
   DevBuf<unsigned long long> dBindTmp;
   DevBuf<unsigned long long> dRowsAcc;   // rows visited by the K4 launches of this fit (segment mode)
   int64_t physRows = 0;
+  double weightedRows = 0;      // sum over evaluated nodes of their weighted row count (x featuresPerNode = MLlib's per-instance updates)
   DevBuf<int64_t> dSlotPos, dSplitPos;
   PinBuf<int64_t> hSlotPos, hSplitPos;
   std::vector<uint64_t> treeBase;
@@ -702,7 +703,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       !t->dSlotFo.ensure(nSlots * t->Fsub) || !t->dSlotBase.ensure(nSlots) || !t->dParent.ensure(nSlots * 4) || !t->dHasParent.ensure(nSlots) ||
       (t->C && (!t->hParentCls.ensure(nSlots * t->Cp) || !t->dParentCls.ensure(nSlots * t->Cp) || !t->hClsOut.ensure(nSlots * 3 * t->Cp) ||
                 !t->dClsOut.ensure(nSlots * 3 * t->Cp))) ||
-      !t->dRec.ensure(nSlots) || !t->hRec.ensure(nSlots) || !t->dRecMask.ensure(nSlots * t->maskWords) || !t->hRecMask.ensure(nSlots * t->maskWords) || !t->hTreeIds.ensure(t->T) || !t->dTreeIds.ensure(t->T))
+      !t->hSlotCells.ensure(nSlots) || !t->dRec.ensure(nSlots) || !t->hRec.ensure(nSlots) || !t->dRecMask.ensure(nSlots * t->maskWords) || !t->hRecMask.ensure(nSlots * t->maskWords) || !t->hTreeIds.ensure(t->T) || !t->dTreeIds.ensure(t->T))
     return B2RF_ERR_CUDA;
   int64_t maxNodes = 0;
   for (size_t sl = 0; sl < nSlots; sl++) {
@@ -714,6 +715,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       t->hSlotFo.p[sl * t->Fsub + j] = make_uint2(f, off);
       off += (uint32_t)t->cellBins[f];
     }
+    t->hSlotCells.p[sl] = (int32_t)off;
     t->hSlotBase.p[sl] = slotBase[sl];
     const bool hasParent = level_of(n.id) > 0;
     t->hHasParent.p[sl] = hasParent;
@@ -723,12 +725,11 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     maxNodes = std::max<int64_t>(maxNodes, (int64_t)t->trees[g.tree].size());
   }
   (void)maxNodes;
-  // trees of this group, ascending, cut into launches whose histogram cells stay L2-resident
-  std::vector<int64_t> cellsPerTree(t->T, 0);
-  for (size_t sl = 0; sl < nSlots; sl++) {
-    int64_t c = 0;
-    for (int j = 0; j < t->Fsub; j++) c += t->cellBins[feats[sl * t->Fsub + j]];
-    cellsPerTree[t->group[sl].tree] += c;
+  // trees of this group, ascending; scan mode cuts them into launches whose histogram cells stay L2-resident
+  std::vector<int64_t> cellsPerTree;
+  if (!t->bucketMode) {
+    cellsPerTree.assign(t->T, 0);
+    for (size_t sl = 0; sl < nSlots; sl++) cellsPerTree[t->group[sl].tree] += (sl + 1 < nSlots ? slotBase[sl + 1] : cells) - slotBase[sl];
   }
   int nTg = 0;
   for (int i = 0; i < t->T; i++) if (treeSeen[i]) t->hTreeIds.p[nTg++] = i;
@@ -767,12 +768,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     } else if (!t->dSlotCount.ensure(nSlots) || !t->dCursor.ensure(nSlots) || !t->dSlotStart.ensure(nSlots + 1) ||
                !t->dRowList.ensure((size_t)std::max<int64_t>(listCap, 1)))
       return B2RF_ERR_CUDA;
-    for (size_t sl = 0; sl < nSlots; sl++) {
-      int32_t c = 0;
-      for (int j = 0; j < t->Fsub; j++) c += t->cellBins[feats[sl * t->Fsub + j]];
-      t->hSlotCells.p[sl] = c;
-      maxCells = std::max(maxCells, c);
-    }
+    for (size_t sl = 0; sl < nSlots; sl++) maxCells = std::max(maxCells, t->hSlotCells.p[sl]);
     // shared-memory layout: padded [bin][feature-in-group] with the widest power-of-two feature group G that keeps a task's
     // histogram (maxBins * G cells) within ~48 KB, i.e. four or more CTAs per SM; compact cells only if even G = 4 is too big
     const int32_t maxBinsAll = *std::max_element(t->cellBins.begin(), t->cellBins.end());
@@ -920,6 +916,7 @@ static int end_group_tail(b2rf_trainer* t, cudaStream_t s) {
       const double* cls3 = t->C ? t->hClsOut.p + (size_t)sl * 3 * t->Cp : nullptr;
       if (t->C) { n.cls = (int64_t)t->clsPool.size(); t->clsPool.insert(t->clsPool.end(), cls3, cls3 + t->C); }
       t->trace.push_back({t->groupNo, tr, id, r.feature, r.splitIdx, r.gain, r.impurity, r.parent[0], r.parent[1], r.parent[2]});
+      t->weightedRows += r.parent[0];
       if (!isLeaf) {
         n.hasSplit = true; n.feature = r.feature;
         if (t->arity[r.feature] == 0) { n.splitBin = r.splitIdx; n.threshold = t->thresholds[(size_t)r.feature * t->maxSplits + r.splitIdx]; }
@@ -1086,103 +1083,97 @@ int b2rf_trainer_group_info(const b2rf_trainer* t, int64_t* n_slots, int32_t* h_
 }
 
 int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_counts4) {
-  // h_counts4 has room for 8 entries: groups, hist launches, rows*trees scanned, learning nodes, kernel launches, hist algorithmic
+  // h_counts4 has room for 9 entries (the last: weighted rows of all evaluated nodes): groups, hist launches, rows*trees scanned, learning nodes, kernel launches, hist algorithmic
   // bytes, rows visited by the segment-mode K4 launches (x featuresPerNode = physical bin updates), featuresPerNode
   if (!t) return B2RF_ERR_ARG;
   if (h_seconds5) { h_seconds5[0] = 0; h_seconds5[1] = 0; h_seconds5[2] = t->tHist; h_seconds5[3] = t->tChoose; h_seconds5[4] = t->tTotal > 0 ? t->tTotal : now_s() - t->tStart; }
   if (h_counts4) {
     int64_t nodes = 0; for (auto& tr : t->trees) nodes += (int64_t)tr.size();
     h_counts4[0] = t->groupNo; h_counts4[1] = t->nHistLaunches; h_counts4[2] = t->nScanned; h_counts4[3] = nodes;
-    h_counts4[4] = t->nKernels; h_counts4[5] = (int64_t)t->histAlgBytes; h_counts4[6] = t->physRows; h_counts4[7] = t->Fsub;
+    h_counts4[4] = t->nKernels; h_counts4[5] = (int64_t)t->histAlgBytes; h_counts4[6] = t->physRows; h_counts4[7] = t->Fsub; h_counts4[8] = (int64_t)t->weightedRows;
   }
   return B2RF_OK;
 }
 
-// LearningNode.toNode(prune = true): pre-order flattening; an internal node whose children are leaves with equal
-// predictions collapses into a leaf.  Trees are flattened independently (a few worker threads), then concatenated.
-struct FlatTree {
-  std::vector<int32_t> feature, left, right, ncat, cat_off, cat_len;
-  std::vector<double> threshold, prediction, impurity, gain, stats, cats, cls;
-};
-
-static int flatten_node(const b2rf_trainer* t, FlatTree& x, int tr, int ni) {
-  const HNode& n = t->trees[tr][ni];
-  const int me = (int)x.feature.size();
-  x.feature.push_back(-1); x.left.push_back(-1); x.right.push_back(-1); x.ncat.push_back(0);
-  x.cat_off.push_back((int32_t)x.cats.size()); x.cat_len.push_back(0);
-  x.threshold.push_back(0); x.prediction.push_back(0); x.impurity.push_back(0); x.gain.push_back(0);
-  for (int q = 0; q < 4; q++) x.stats.push_back(n.stats.calc[q]);
-  if (t->C) for (int k = 0; k < t->C; k++) x.cls.push_back(n.cls >= 0 ? t->clsPool[(size_t)n.cls + k] : 0.0);
-  const size_t at = (size_t)me;
-  if (n.left >= 0) {
-    const size_t catMark = x.cats.size();
-    const int l = flatten_node(t, x, tr, n.left);
-    const int r = flatten_node(t, x, tr, n.left + 1);
-    const bool bothLeaves = x.feature[l] < 0 && x.feature[r] < 0;
-    if (bothLeaves && x.prediction[l] == x.prediction[r]) {
-      const double pred = x.prediction[l];
-      const size_t keep = at + 1;
-      x.feature.resize(keep); x.left.resize(keep); x.right.resize(keep); x.ncat.resize(keep); x.cat_off.resize(keep);
-      x.cat_len.resize(keep); x.threshold.resize(keep); x.prediction.resize(keep); x.impurity.resize(keep); x.gain.resize(keep);
-      x.stats.resize(keep * 4); x.cats.resize(catMark);
-      if (t->C) x.cls.resize(keep * (size_t)t->C);
-      x.prediction[at] = pred; x.impurity[at] = n.stats.impurity;
-      return me;
-    }
-    x.feature[at] = n.feature; x.left[at] = l; x.right[at] = r; x.threshold[at] = n.threshold;
-    x.prediction[at] = t->node_pred(n); x.impurity[at] = n.stats.impurity; x.gain[at] = n.stats.gain;
-    if (n.catMaskIdx >= 0) {
-      x.ncat[at] = t->arity[n.feature];
-      x.cat_off[at] = (int32_t)x.cats.size();
-      const uint32_t* m = &t->catPool[(size_t)n.catMaskIdx * t->maskWords];
-      int cnt = 0;
-      for (int c = 0; c < t->maskWords * 32; c++) if ((m[c >> 5] >> (c & 31)) & 1u) { x.cats.push_back((double)c); cnt++; }
-      x.cat_len[at] = cnt;
-    }
-    return me;
-  }
-  x.prediction[at] = t->node_pred(n);
-  x.impurity[at] = n.stats.valid ? n.stats.impurity : -1.0;
-  return me;
-}
-
+// LearningNode.toNode(prune = true): pre-order flattening; an internal node whose children are leaves with equal predictions
+// collapses into a leaf.  Two passes per tree, trees in parallel on a few host threads:
+//   1. bottom-up over the node vector (children always sit behind their parent): does the node end up a leaf, its prediction, the
+//      size of its flattened subtree and of its category lists;
+//   2. pre-order walk with an explicit stack that writes every field straight into the forest-wide arrays (node i of a subtree at
+//      position p has its left child at p + 1 and its right child at p + 1 + size(left)).
 static void do_export(b2rf_trainer* t) {
   if (t->exported) return;
-  std::vector<FlatTree> flat(t->T);
-  {
-    size_t total = 0;
-    for (int tr = 0; tr < t->T; tr++) total += t->trees[tr].size();
-    const int workers = (int)std::max<size_t>(1, std::min<size_t>({(size_t)t->T, (size_t)8, total / 4096 + 1}));
+  const int T = t->T;
+  struct TreePlan { std::vector<uint8_t> leaf; std::vector<double> pred; std::vector<int32_t> sz, csz; };
+  std::vector<TreePlan> plan(T);
+  size_t total = 0;
+  for (int tr = 0; tr < T; tr++) total += t->trees[tr].size();
+  const int workers = (int)std::max<size_t>(1, std::min<size_t>({(size_t)T, (size_t)8, total / 4096 + 1}));
+  auto run_parallel = [&](auto&& fn) {
     std::atomic<int> next{0};
-    auto work = [&]() {
-      for (int tr = next.fetch_add(1); tr < t->T; tr = next.fetch_add(1)) {
-        FlatTree& x = flat[tr];
-        const size_t m = t->trees[tr].size();
-        for (auto* vec : {&x.feature, &x.left, &x.right, &x.ncat, &x.cat_off, &x.cat_len}) vec->reserve(m);
-        for (auto* vec : {&x.threshold, &x.prediction, &x.impurity, &x.gain}) vec->reserve(m);
-        x.stats.reserve(m * 4);
-        flatten_node(t, x, tr, 0);
-      }
-    };
+    auto work = [&]() { for (int tr = next.fetch_add(1); tr < T; tr = next.fetch_add(1)) fn(tr); };
     std::vector<std::thread> pool;
     for (int w = 1; w < workers; w++) pool.emplace_back(work);
     work();
     for (auto& th : pool) th.join();
-  }
-  t->x_tree_off.clear(); t->x_feature.clear(); t->x_left.clear(); t->x_right.clear(); t->x_ncat.clear(); t->x_cat_off.clear(); t->x_cat_len.clear();
-  t->x_threshold.clear(); t->x_prediction.clear(); t->x_impurity.clear(); t->x_gain.clear(); t->x_stats.clear(); t->x_cats.clear(); t->x_cls.clear();
-  t->x_tree_off.push_back(0);
-  for (int tr = 0; tr < t->T; tr++) {
-    FlatTree& x = flat[tr];
-    const int32_t catBase = (int32_t)t->x_cats.size();
-    for (auto& o : x.cat_off) o += catBase;          // a node's category list lives in the forest-wide pool
-    auto app = [](auto& dst, const auto& src) { dst.insert(dst.end(), src.begin(), src.end()); };
-    app(t->x_feature, x.feature); app(t->x_left, x.left); app(t->x_right, x.right); app(t->x_ncat, x.ncat); app(t->x_cat_off, x.cat_off);
-    app(t->x_cat_len, x.cat_len); app(t->x_threshold, x.threshold); app(t->x_prediction, x.prediction); app(t->x_impurity, x.impurity);
-    app(t->x_gain, x.gain); app(t->x_stats, x.stats); app(t->x_cats, x.cats); app(t->x_cls, x.cls);
-    t->x_tree_off.push_back((int64_t)t->x_feature.size());
-    x = FlatTree();
-  }
+  };
+  run_parallel([&](int tr) {
+    const std::vector<HNode>& nodes = t->trees[tr];
+    const int n = (int)nodes.size();
+    TreePlan& p = plan[tr];
+    p.leaf.resize(n); p.pred.resize(n); p.sz.resize(n); p.csz.resize(n);
+    for (int i = n - 1; i >= 0; i--) {
+      const HNode& nd = nodes[i];
+      if (nd.left < 0) { p.leaf[i] = 1; p.pred[i] = t->node_pred(nd); p.sz[i] = 1; p.csz[i] = 0; continue; }
+      const int l = nd.left, r = l + 1;
+      if (p.leaf[l] && p.leaf[r] && p.pred[l] == p.pred[r]) { p.leaf[i] = 1; p.pred[i] = p.pred[l]; p.sz[i] = 1; p.csz[i] = 0; continue; }
+      int own = 0;
+      if (nd.catMaskIdx >= 0) { const uint32_t* m = &t->catPool[(size_t)nd.catMaskIdx * t->maskWords]; for (int q = 0; q < t->maskWords; q++) own += __builtin_popcount(m[q]); }
+      p.leaf[i] = 0; p.pred[i] = t->node_pred(nd); p.sz[i] = 1 + p.sz[l] + p.sz[r]; p.csz[i] = own + p.csz[l] + p.csz[r];
+    }
+  });
+  t->x_tree_off.assign(T + 1, 0);
+  std::vector<int64_t> catBase(T + 1, 0);
+  for (int tr = 0; tr < T; tr++) { t->x_tree_off[tr + 1] = t->x_tree_off[tr] + plan[tr].sz[0]; catBase[tr + 1] = catBase[tr] + plan[tr].csz[0]; }
+  const size_t N = (size_t)t->x_tree_off[T];
+  t->x_feature.assign(N, -1); t->x_left.assign(N, -1); t->x_right.assign(N, -1); t->x_ncat.assign(N, 0); t->x_cat_off.assign(N, 0); t->x_cat_len.assign(N, 0);
+  t->x_threshold.assign(N, 0.0); t->x_prediction.assign(N, 0.0); t->x_impurity.assign(N, 0.0); t->x_gain.assign(N, 0.0);
+  t->x_stats.resize(N * 4); t->x_cats.resize((size_t)catBase[T]);
+  if (t->C) t->x_cls.resize(N * (size_t)t->C); else t->x_cls.clear();
+  run_parallel([&](int tr) {
+    const std::vector<HNode>& nodes = t->trees[tr];
+    const TreePlan& p = plan[tr];
+    const size_t base = (size_t)t->x_tree_off[tr];
+    int64_t catAt = catBase[tr];
+    std::vector<std::pair<int32_t, int32_t>> stack;   // (node index, tree-local flat position)
+    stack.reserve(64);
+    stack.push_back({0, 0});
+    while (!stack.empty()) {
+      const auto [ni, pos] = stack.back();
+      stack.pop_back();
+      const HNode& nd = nodes[ni];
+      const size_t at = base + (size_t)pos;
+      for (int q = 0; q < 4; q++) t->x_stats[at * 4 + q] = nd.stats.calc[q];
+      if (t->C) for (int k = 0; k < t->C; k++) t->x_cls[at * (size_t)t->C + k] = nd.cls >= 0 ? t->clsPool[(size_t)nd.cls + k] : 0.0;
+      t->x_cat_off[at] = (int32_t)catAt;
+      t->x_prediction[at] = p.pred[ni];
+      if (nd.left < 0) { t->x_impurity[at] = nd.stats.valid ? nd.stats.impurity : -1.0; continue; }   // a leaf of the learned tree
+      t->x_impurity[at] = nd.stats.impurity;
+      if (p.leaf[ni]) continue;                                                                       // collapsed by the prune rule
+      const int l = nd.left, r = l + 1;
+      t->x_feature[at] = nd.feature; t->x_left[at] = pos + 1; t->x_right[at] = pos + 1 + p.sz[l];
+      t->x_threshold[at] = nd.threshold; t->x_gain[at] = nd.stats.gain;
+      if (nd.catMaskIdx >= 0) {
+        t->x_ncat[at] = t->arity[nd.feature];
+        const uint32_t* m = &t->catPool[(size_t)nd.catMaskIdx * t->maskWords];
+        int cnt = 0;
+        for (int c = 0; c < t->maskWords * 32; c++) if ((m[c >> 5] >> (c & 31)) & 1u) { t->x_cats[(size_t)catAt++] = (double)c; cnt++; }
+        t->x_cat_len[at] = cnt;
+      }
+      stack.push_back({r, pos + 1 + p.sz[l]});   // right first: the left subtree is popped (and its category lists placed) before it
+      stack.push_back({l, pos + 1});
+    }
+  });
   t->exported = true;
 }
 

@@ -54,41 +54,33 @@ __device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
 //   wide  : w*y * 2^(39 - Ea) = hi + lo / 2^40 with |hi| < 2^39, 0 <= lo < 2^40 (four limbs), likewise w*y*y * 2^(40 - Eb)
 struct LimbScale { double sa, sb; };
 
-// Packed values of one row.  Narrow form, one 16-byte word:
-//   x = (v mod 2^59) | w << 59 ;  y = u | slow << 63          (slow rows: x = label bits, y = w | 1 << 63)
-__device__ __forceinline__ uint4 limb_pack_narrow(uint32_t w, double yv, LimbScale sc) {
+// Packed values of one row; `slow` = the row is not on the task's grid (its limbs are then all zero: the add loop adds nothing for it,
+// and the block's slow pass sends its fp64 terms to the global histogram).  Narrow form, one 16-byte word:
+//   x = (v mod 2^59) | w << 59 ;  y = u
+__device__ __forceinline__ uint4 limb_pack_narrow(uint32_t w, double yv, LimbScale sc, bool& slow) {
   const double wy = (double)w * yv, wyy = wy * yv;                     // MLlib: instanceWeight * label, then * label
   const double ta = wy * sc.sa, tb = wyy * sc.sb;
   const long long v = __double2ll_rn(ta);
   const unsigned long long u = __double2ull_rn(tb);
-  unsigned long long x, y;
-  if ((double)v == ta && (double)u == tb) {                            // on the grid: exact
-    x = ((unsigned long long)v & ((1ull << 59) - 1ull)) | ((unsigned long long)w << 59);
-    y = u;
-  } else {
-    x = (unsigned long long)__double_as_longlong(yv);
-    y = (unsigned long long)w | (1ull << 63);
-  }
-  return make_uint4((uint32_t)x, (uint32_t)(x >> 32), (uint32_t)y, (uint32_t)(y >> 32));
+  slow = !((double)v == ta && (double)u == tb);                        // on the grid <=> exact
+  if (slow) return make_uint4(0u, 0u, 0u, 0u);
+  const unsigned long long x = ((unsigned long long)v & ((1ull << 59) - 1ull)) | ((unsigned long long)w << 59);
+  return make_uint4((uint32_t)x, (uint32_t)(x >> 32), (uint32_t)u, (uint32_t)(u >> 32));
 }
-// Wide form, 24 bytes: x0 = loA | w << 40 | slow << 47 | (hiB >> 24) << 48 ;  x1 = hiA (two's complement) ;  x2 = loB | (hiB & 0xffffff) << 40
-// (slow rows: x0 = w << 40 | 1 << 47, x1 = label bits)
-__device__ __forceinline__ void limb_pack_wide(uint32_t w, double yv, LimbScale sc, uint4& p0, uint2& p1) {
+// Wide form, 24 bytes: x0 = loA | (hiB >> 24) << 40 | w << 56 ;  x1 = hiA (two's complement) ;  x2 = loB | (hiB & 0xffffff) << 40
+__device__ __forceinline__ void limb_pack_wide(uint32_t w, double yv, LimbScale sc, uint4& p0, uint2& p1, bool& slow) {
   const double wy = (double)w * yv, wyy = wy * yv;
   const double ta = wy * sc.sa, tb = wyy * sc.sb;                       // |ta| < 2^39, 0 <= tb < 2^40 (power-of-two scales: exact)
   const double ta40 = ta * 0x1p40, tb40 = tb * 0x1p40;
-  unsigned long long x0, x1, x2;
-  if (ta40 == rint(ta40) && tb40 == rint(tb40)) {                      // no bits below the window: the row is on the grid
+  slow = !(ta40 == rint(ta40) && tb40 == rint(tb40));                  // bits below the window
+  unsigned long long x0 = 0ull, x1 = 0ull, x2 = 0ull;
+  if (!slow) {
     const double fa = floor(ta), fb = floor(tb);
     const long long hiA = __double2ll_rz(fa);                           // fractional parts: exact (their exact values are representable)
     const unsigned long long loA = __double2ull_rz((ta - fa) * 0x1p40), hiB = __double2ull_rz(fb), loB = __double2ull_rz((tb - fb) * 0x1p40);
-    x0 = loA | ((unsigned long long)w << 40) | ((hiB >> 24) << 48);
+    x0 = loA | ((hiB >> 24) << 40) | ((unsigned long long)w << 56);
     x1 = (unsigned long long)hiA;
     x2 = loB | ((hiB & 0xffffffull) << 40);
-  } else {
-    x0 = ((unsigned long long)w << 40) | (1ull << 47);
-    x1 = (unsigned long long)__double_as_longlong(yv);
-    x2 = 0ull;
   }
   p0 = make_uint4((uint32_t)x0, (uint32_t)(x0 >> 32), (uint32_t)x1, (uint32_t)(x1 >> 32));
   p1 = make_uint2((uint32_t)x2, (uint32_t)(x2 >> 32));
@@ -226,79 +218,81 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
       yv = in ? yl[i] : 0.0;
     };
     uint32_t* hcell = hist + fl;
-    // packed values of the block held in (ent, yv) -> value slot s
-    auto put_vals = [&](int s) {
+    // packed values of the block held in (ent, yv) -> value slot s; returns the block's slow rows as a lane mask
+    auto put_vals = [&](int s) -> uint32_t {
       unsigned char* vals = valsBase + s * valBytes;
       const uint32_t w = ent >> 27;
+      bool slow = false;
       if (lane < BR) {
         if (WIDE) {
           uint4 p0; uint2 p1;
-          limb_pack_wide(w, yv, sc, p0, p1);
+          limb_pack_wide(w, yv, sc, p0, p1, slow);
           *reinterpret_cast<uint4*>(vals + lane * VB) = p0;
           *reinterpret_cast<uint2*>(vals + lane * VB + 16) = p1;
         } else {
-          *reinterpret_cast<uint4*>(vals + lane * VB) = limb_pack_narrow(w, yv, sc);
+          *reinterpret_cast<uint4*>(vals + lane * VB) = limb_pack_narrow(w, yv, sc, slow);
         }
       }
+      return __ballot_sync(FULL, slow && w != 0u);
     };
-    // the adds of one staged block: lane = (row slot r, feature fl); tile / vals point at the block's code rows and packed values
-    auto consume = [&](const unsigned char* tile, const unsigned char* vals) {
+    // the adds of one staged block: lane = (row slot r, feature fl); tile / vals point at the block's code rows and packed values;
+    // slowMask = rows of the block (first row: chunk row blk * BR) that are not on the grid
+    auto consume = [&](const unsigned char* tile, const unsigned char* vals, uint32_t slowMask, int blk) {
       const unsigned char* tl = tile + r * ldr + e.x;
       const unsigned char* vv = vals + r * VB;
-      if (!active) return;
-      // one row ahead: the next row's code and packed limbs are loaded before this row's adds are issued (the compiler keeps
-      // shared loads behind earlier shared atomics, so the overlap has to be written out)
-      uint32_t code = tl[0];
-      uint4 q0 = *reinterpret_cast<const uint4*>(vv);
-      uint2 q1 = WIDE ? *reinterpret_cast<const uint2*>(vv + 16) : make_uint2(0u, 0u);
+      if (active) {
+        // one row ahead: the next row's code and packed limbs are loaded before this row's adds are issued (the compiler keeps
+        // shared loads behind earlier shared atomics, so the overlap has to be written out)
+        uint32_t code = tl[0];
+        uint4 q0 = *reinterpret_cast<const uint4*>(vv);
+        uint2 q1 = WIDE ? *reinterpret_cast<const uint2*>(vv + 16) : make_uint2(0u, 0u);
 #pragma unroll
-      for (int u = 0; u < NU; u++) {
-        const uint32_t cc = code; const uint4 p0 = q0; const uint2 p1 = q1;
-        if (u + 1 < NU) {
-          code = tl[(u + 1) * R * ldr];
-          q0 = *reinterpret_cast<const uint4*>(vv + (u + 1) * R * VB);
-          if (WIDE) q1 = *reinterpret_cast<const uint2*>(vv + (u + 1) * R * VB + 16);
-        }
-        uint32_t* c = hcell + cc * (NP * G);
-        const unsigned long long x0 = ((unsigned long long)p0.y << 32) | p0.x, x1 = ((unsigned long long)p0.w << 32) | p0.z;
-        if (WIDE) {
-          const uint32_t w = (p0.y >> 8) & 31u;
-          if (p0.y & (1u << 15)) {                                   // slow row: its fp64 terms go straight to the global histogram
-            const double ys = __longlong_as_double((long long)x1);
-            const double wy = (double)w * ys;
-            double* gc = hb + (size_t)(e.y + cc) * 4;
-            red_add_f64(gc, (double)w); red_add_f64(gc + 1, wy); red_add_f64(gc + 2, wy * ys);
-          } else {
+        for (int u = 0; u < NU; u++) {
+          const uint32_t cc = code; const uint4 p0 = q0; const uint2 p1 = q1;
+          if (u + 1 < NU) {
+            code = tl[(u + 1) * R * ldr];
+            q0 = *reinterpret_cast<const uint4*>(vv + (u + 1) * R * VB);
+            if (WIDE) q1 = *reinterpret_cast<const uint2*>(vv + (u + 1) * R * VB + 16);
+          }
+          uint32_t* c = hcell + cc * (NP * G);
+          const unsigned long long x0 = ((unsigned long long)p0.y << 32) | p0.x, x1 = ((unsigned long long)p0.w << 32) | p0.z;
+          if (WIDE) {
             const unsigned long long x2 = ((unsigned long long)p1.y << 32) | p1.x;
-            const uint32_t hiBl = (uint32_t)(x2 >> 40) | ((p0.y >> 16) << 24);          // low 32 bits of hiB (40 bits: the top 8 are in p0.y >> 24)
-            atomicAdd(c, w);
+            const uint32_t hiBl = (uint32_t)(x2 >> 40) | ((p0.y & 0xff00u) << 16);         // low 32 bits of hiB: bits 24..31 come from x0 bits 40..47
+            atomicAdd(c, p0.y >> 24);
             atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
             atomicAdd(c + 3 * G, p0.z & LIMB_MASK); atomicAdd(c + 4 * G, (uint32_t)((long long)x1 >> 20));
             atomicAdd(c + 5 * G, p1.x & LIMB_MASK); atomicAdd(c + 6 * G, (uint32_t)(x2 >> 20) & LIMB_MASK);
-            atomicAdd(c + 7 * G, hiBl & LIMB_MASK); atomicAdd(c + 8 * G, (hiBl >> 20) | ((p0.y >> 24) << 12));
-          }
-        } else {
-          if (p0.w & 0x80000000u) {                                  // slow row
-            const uint32_t w = p0.z & 31u;
-            const double ys = __longlong_as_double((long long)x0);
-            const double wy = (double)w * ys;
-            double* gc = hb + (size_t)(e.y + cc) * 4;
-            red_add_f64(gc, (double)w); red_add_f64(gc + 1, wy); red_add_f64(gc + 2, wy * ys);
+            atomicAdd(c + 7 * G, hiBl & LIMB_MASK); atomicAdd(c + 8 * G, (hiBl >> 20) | (((p0.y >> 16) & 0xffu) << 12));
           } else {
             atomicAdd(c, p0.y >> 27);
             atomicAdd(c + G, p0.x & LIMB_MASK); atomicAdd(c + 2 * G, (uint32_t)(x0 >> 20) & LIMB_MASK);
             atomicAdd(c + 3 * G, (uint32_t)((long long)(x0 << 5) >> 45));
             atomicAdd(c + 4 * G, p0.z & LIMB_MASK); atomicAdd(c + 5 * G, (uint32_t)(x1 >> 20) & LIMB_MASK);
-            atomicAdd(c + 6 * G, (uint32_t)(x1 >> 40) & LIMB_MASK);
+            atomicAdd(c + 6 * G, (uint32_t)(x1 >> 40));
           }
+        }
+      }
+      // slow pass (rare): rows whose labels are tiny next to the task's largest go to the global histogram as MLlib's own fp64 terms
+      while (slowMask) {
+        const int k = __ffs(slowMask) - 1;
+        slowMask &= slowMask - 1u;
+        const uint32_t e2 = rl[blk * BR + k];
+        const double ys = yl[blk * BR + k];
+        if (active && r == 0) {
+          const uint32_t w = e2 >> 27;
+          const double wy = (double)w * ys;
+          double* gc = hb + (size_t)(e.y + tile[k * ldr + e.x]) * 4;
+          red_add_f64(gc, (double)w); red_add_f64(gc + 1, wy); red_add_f64(gc + 2, wy * ys);
         }
       }
     };
     int b = warp;
     if (TMA) {
       // tile slot s <- the block held in (ent, yv): one bulk async copy per row, completion on the slot's mbarrier
+      uint32_t slowM[2] = {0u, 0u};
       auto stage_tma = [&](int s, int blk) {
-        put_vals(s);
+        slowM[s] = put_vals(s);
         unsigned char* tile = ring + s * tileBytes;
         const int nvalid = min(BR, n - blk * BR);
         if (lane == 0) mbar_expect_tx(&bars[s], (uint32_t)(nvalid * ldr));
@@ -312,7 +306,7 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
         while (!mbar_try(&bars[s], (phase >> s) & 1u)) { }
         phase ^= 1u << s;
         __syncwarp();
-        consume(ring + s * tileBytes, valsBase + s * valBytes);
+        consume(ring + s * tileBytes, valsBase + s * valBytes, slowM[s], b);
         __syncwarp();
       }
     } else {
@@ -328,14 +322,15 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
           creg[q] = row < nvalid ? *reinterpret_cast<const uint4*>(bins_rm + (size_t)(e2 & 0x7ffffffu) * ldr + seg * 16) : make_uint4(0u, 0u, 0u, 0u);
         }
       };
-      if (b < nblk) { load(b); fetch(b); put_vals(0); load(b + W); }
+      uint32_t slowM[2] = {0u, 0u};
+      if (b < nblk) { load(b); fetch(b); slowM[0] = put_vals(0); load(b + W); }
       for (int k = 0; b < nblk; k++, b += W) {
         const int s = k & 1;
 #pragma unroll
         for (int q = 0; q < NPC; q++) reinterpret_cast<uint4*>(ring)[lane + 32 * q] = creg[q];
         __syncwarp();
-        if (b + W < nblk) { fetch(b + W); put_vals(s ^ 1); load(b + 2 * W); }
-        consume(ring, valsBase + s * valBytes);
+        if (b + W < nblk) { fetch(b + W); slowM[s ^ 1] = put_vals(s ^ 1); load(b + 2 * W); }
+        consume(ring, valsBase + s * valBytes, slowM[s], b);
         __syncwarp();
       }
     }
