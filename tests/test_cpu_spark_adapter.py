@@ -180,3 +180,19 @@ def test_classifier_thresholds_rule(sp, b2rf, oracle):
     assert m._predict_from_probability(prob).tolist() == [1.0, 1.0, 1.0]
     m.setThresholds([0.0, 1.0])
     assert m._predict_from_probability(np.array([[0.1, 0.9], [0.0, 1.0]])).tolist() == [0.0, 1.0]   # 0.1 / 0 = inf wins; 0 / 0 is skipped
+
+
+def test_persistence_schema_matches_committed_fixture(sp, b2rf, tmp_path):
+    """The written model directory (Parquet schemas of data/ and treesMetadata/, metadata keys, class names) against the committed
+    fixture tests/golden/persistence_schema.json, which restates MLlib 3.1.2's NodeData / SplitData / EnsembleNodeData layout.
+    Spark is unavailable on this box, so this pins the format that only this package has read back so far."""
+    import importlib.util
+    import json
+    import os
+    here = os.path.dirname(os.path.abspath(__file__))
+    spec = importlib.util.spec_from_file_location("make_persistence_schema", os.path.join(here, "golden", "make_persistence_schema.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    got = mod.describe(str(tmp_path))
+    want = json.load(open(os.path.join(here, "golden", "persistence_schema.json")))
+    assert got == want
