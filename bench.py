@@ -306,6 +306,7 @@ def main():
     fsub = params.features_per_node(F)
     updates_per_fit = float(f0.counters.get("weighted_bin_updates", 0))
     phases = {k: round(sum(f.timers[k] for f in forests) / len(forests), 4) for k in ("init", "findSplits", "findBestSplits", "chooseSplits", "total")}
+    phases["allreduce"] = round(sum(f.timers.get("allreduce", 0.0) for f in forests) / len(forests), 4)   # device time of the histogram merges (N > 1)
     phys_updates = float(f0.counters.get("bin_updates", 0))
     gpu_launches = int(sum(f.counters["kernel_launches"] for f in forests))
     cfg_extra = {"node_groups": f0.counters["groups"], "forest_nodes": int(f0.num_nodes())}

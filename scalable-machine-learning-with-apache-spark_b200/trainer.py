@@ -333,16 +333,6 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         torch.cuda.synchronize(dev)
         t0 = time.perf_counter()
 
-        # ---- BaggedPoint (K3) first, on a side stream: it needs only the partition layout, is bound by instruction issue, and so
-        # overlaps well with the memory-bound findSplits sample + TreePoint binning below ----
-        ld = _pad(n_local)
-        main = torch.cuda.current_stream()
-        bag_s = torch.cuda.Stream()
-        bag_s.wait_stream(main)
-        with torch.cuda.stream(bag_s):
-            w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
-                          want_node=_want_node(hist_mode, prebinned[1] if prebinned is not None else (None if hist_mode == "scan" else True), n_local))
-
         # ---- findSplits (K1) ----
         fraction = S["fraction"]
         samp = sample_rows(X, S["row0"], params.seed, fraction, S["dist"], group) if fraction < 1.0 else X
@@ -350,9 +340,13 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         thr, ns = find_splits(samp, S["arity_d"], S["mpb"], fraction * float(S["N"]))
         thr_h = thr.cpu().numpy()
         ns_h = ns.cpu().numpy()
+        torch.cuda.synchronize(dev)
         t1 = time.perf_counter()
 
-        # ---- TreePoint (K2) ----
+        # ---- TreePoint (K2) + BaggedPoint (K3) ----
+        # (K3 on a side stream next to K1 / K2 was measured: no gain on one GPU — its one wave of long-lived warps leaves the 7 ms of
+        # K1 + K2 nothing to hide behind — and a loss on several, where the collectives of findSplits queue behind it)
+        ld = _pad(n_local)
         dbg = os.environ.get("B2RF_TIMING") == "1"
         if prebinned is not None:
             bins, bins_rm = prebinned
@@ -360,16 +354,18 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
             code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
             bins = torch.empty((F, ld), dtype=code_dt, device=dev)
             bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
+            if dbg:
+                torch.cuda.synchronize(dev); ta = time.perf_counter()
             bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm, check_errors=False)
             _raise_bin_errors(S["arity_d"], S["dist"], group)
-        main.wait_stream(bag_s)
-        w.record_stream(main)
-        if node is not None:
-            node.record_stream(main)
+            if dbg:
+                torch.cuda.synchronize(dev); tb = time.perf_counter()
+        w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
+                      want_node=_want_node(hist_mode, bins_rm, n_local))
         torch.cuda.synchronize(dev)
         t2 = time.perf_counter()
         if dbg and prebinned is None:
-            print(f"[b2rf timing] setup {t0 - t_start:.4f} findSplits {t1 - t0:.4f} bin + bag {t2 - t1:.4f}", flush=True)
+            print(f"[b2rf timing] setup {t0 - t_start:.4f} findSplits {t1 - t0:.4f} alloc {ta - t1:.4f} bin {tb - ta:.4f} bag(+alloc) {t2 - tb:.4f}", flush=True)
 
         forest = _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace, hist_hook)
         t3 = time.perf_counter()
