@@ -11,6 +11,10 @@
  *  - Every function returns 0 on success, <0 on error; b2rf_last_error() gives the thread-local message.
  *    Messages for user errors repeat MLlib's text (e.g. the maxBins requirement `ML 06:81,110-118` expects).
  *  - Pointers named d_* are DEVICE pointers owned by the caller (e.g. torch tensors); the library never frees them.
+ *    The stage kernels (K1, K2, K4 stand-alone, K7) take caller-provided outputs / workspaces and allocate nothing.  The trainer
+ *    object is different: it owns small descriptor buffers and, in segment mode, the per-tree row / label lists (12-24 bytes per
+ *    in-bag row and tree), taken from a process-wide pool of device and pinned-host blocks that grows with cudaMalloc /
+ *    cudaMallocHost on first use and is reused by later fits (blocks return to the pool when a trainer is destroyed).
  *    Pointers named h_* are host pointers.  `stream` is a cudaStream_t passed as void*; calls are asynchronous on it
  *    unless stated otherwise.
  *  - No CPU fallback exists: without a CUDA device every compute entry point fails with B2RF_ERR_CUDA.
@@ -54,7 +58,7 @@ typedef struct b2rf_params {
   int64_t seed;
   int32_t impurity;  /* 0 = variance (regression); 1 = gini, 2 = entropy: binary classification (labels 0.0 / 1.0, numClasses == 2).
                       * Class counts ride on the regression statistics: with y in {0,1}, sum(w*y) is the class-1 count and
-                      * sum(w) - sum(w*y) the class-0 count, both exact integers in fp64.  numClasses > 2 is not implemented. */
+                      * sum(w) - sum(w*y) the class-0 count, both exact integers in fp64 (more than two classes: numClasses below). */
   int32_t numClasses;  /* 0: regression, or binary classification on the regression statistics (impurity != 0); 3..32: multiclass
                         * classification with per-class count histograms, impurity-ordered and unordered categorical splits
                         * (segment histogram mode only); 2 is accepted and means the same as 0 */
@@ -107,7 +111,7 @@ int b2rf_bin(const double* d_X, int64_t ldx, int64_t n_rows, int32_t F, const do
              int32_t code_bytes /* 1: uint8 codes (maxBins <= 256); 2: uint16.  ldb / ldr count codes */, void* stream);
 
 /* ---- K3: BaggedPoint.convertToBaggedRDD (row a4) ------------------------------------------------------------- */
-/* One emulated Spark partition per thread: partition p (global index part0 + p) covers local rows
+/* One emulated Spark partition per WARP (Bernoulli sampling and tiny rates: per thread): partition p (global index part0 + p) covers local rows
  * [h_part_offsets[p], h_part_offsets[p+1]).  Writes d_w[t][row] and, when d_node is not NULL, the initial d_node[t][row]
  * (0 if w > 0 else -1; only the sort / scan histogram modes need it). */
 int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t part0, int32_t T, double subsamplingRate,
