@@ -325,7 +325,8 @@ def main():
         del X
         torch.cuda.empty_cache()
         estep = lambda: trainer.fit_host(Xh, yh, arity, params, device=dev, part_offsets=po)
-        estep()
+        for _ in range(min(3, max(2, args.warmup))):   # warm-up: allocator pools (device blocks were just released) and pinned staging
+            estep()
         n_e2e = max(1, min(args.steps, 5))
         ems, eouts = timed(estep, n_e2e)
         ems /= n_e2e
@@ -393,7 +394,7 @@ def main():
                          # weighted: the same with every row counted bag-weight times (what MLlib's per-instance loop would execute)
                          "physical_bin_updates_per_s": phys_updates / hist_s if hist_s > 0 and phys_updates else None,
                          "weighted_bin_updates_per_s": updates_per_fit / hist_s if hist_s > 0 else None,
-                         "note": "K4 is bound by shared-memory atomic throughput, not HBM: 22 bin updates (7 native 32-bit adds each) per 37 "
+                         "note": "K4 is bound by shared-memory atomic throughput, not HBM: 22 bin updates (9 native 32-bit adds each; 7 for integer labels) per 37 "
                                  "algorithmic bytes; see DESIGN.md section 2 and profiles/"},
             "e2e": e2e, "cpu_baseline": cpu, "cpu_baseline_sklearn": skl, "mgpu_parity": mgpu_parity, "c4": c4,
             "gpu_launches": gpu_launches,
