@@ -144,6 +144,7 @@ struct SplitLaunch {
   int32_t maxB;               // largest numBins of any feature (sizes the per-warp shared arrays)
   int32_t maskWords;
   int32_t impurity;           // 0 variance, 1 gini, 2 entropy (binary classification on the regression statistics, see b2rf.h)
+  int32_t allHaveParent;      // every slot has parent statistics (no root node in the group): several warps may share a slot
 };
 cudaError_t launch_best_split(const SplitLaunch& a, cudaStream_t s);
 

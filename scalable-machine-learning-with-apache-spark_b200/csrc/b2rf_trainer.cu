@@ -856,6 +856,8 @@ static int end_group_launch(b2rf_trainer* t, cudaStream_t s) {
   a.minInstances = (double)t->p.minInstancesPerNode; a.minWeight = t->minWeightPerNode; a.minInfoGain = t->p.minInfoGain;
   a.out = t->dRec.p; a.catmask_out = t->dRecMask.p; a.maskWords = t->maskWords; a.impurity = t->p.impurity;
   a.maxB = *std::max_element(t->cellBins.begin(), t->cellBins.end());
+  a.allHaveParent = 1;
+  for (size_t sl = 0; sl < nSlots; sl++) if (!t->hHasParent.p[sl]) { a.allHaveParent = 0; break; }
   if (t->C) {
     ClsSplitLaunch c;
     c.hist = t->d_hist; c.slot_fo = t->dSlotFo.p; c.slot_base = t->dSlotBase.p; c.Fsub = t->Fsub; c.nSlots = (int32_t)nSlots;

@@ -54,11 +54,19 @@ struct SplitView {   // one warp's shared arrays
   uint16_t* order;
 };
 
+// WPS = warps per node slot.  1: a warp walks the slot's features in subset order.  > 1 (every slot of the launch has its parent's
+// statistics, i.e. no root node): the block's warps share ONE slot, warp w takes features w, w + WPS, ... of the subset, and the
+// block keeps the candidate with the largest gain, ties to the earliest subset position — the same winner as the sequential
+// strict-'>' scan (maxBy keeps the first maximum).  Groups of a few hundred wide slots (C4: 43 features x 256 bins) otherwise leave
+// most SMs idle behind one warp's serial prefix sums.
+template <int WPS>
 __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const SplitLaunch a) {
   extern __shared__ __align__(16) unsigned char smraw[];
+  __shared__ double s_gain[SPLIT_WARPS];
+  __shared__ int s_pos[SPLIT_WARPS];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int warpsPerBlock = blockDim.x >> 5;
-  const int slot = blockIdx.x * warpsPerBlock + warp;
+  const int slot = WPS > 1 ? blockIdx.x : blockIdx.x * warpsPerBlock + warp;
   if (slot >= a.nSlots) return;
   SplitView sm;
   {
@@ -79,14 +87,15 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
     Pimp = impurity_calc(a.impurity, P[0], P[1], P[2]);
   }
   bool any = false;
-  double bestGain = 0; int bestF = -1, bestS = -1;
+  double bestGain = 0; int bestF = -1, bestS = -1, bestJ = -1;
   double bL[3] = {0, 0, 0}, bR[3] = {0, 0, 0};
   for (int q = lane; q < a.maskWords; q += 32) sm.mask[q] = 0u;
   int firstF = -1;
   const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
   const double* hb = a.hist + (size_t)a.slot_base[slot] * 4;
 
-  for (int j = 0; j < a.Fsub; j++) {
+  if (WPS > 1) firstF = (int)fo[0].x;
+  for (int j = (WPS > 1 ? warp : 0); j < a.Fsub; j += WPS) {
     const uint2 e = fo[j];
     const int f = (int)e.x;
     if (firstF < 0) firstF = f;
@@ -154,7 +163,7 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
       if (os >= 0 && (ls < 0 || og > lg || (og == lg && os < ls))) { lg = og; ls = os; }
     }
     if (!any || lg > bestGain) {  // strict >: the earliest feature in subset order wins ties
-      any = true; bestGain = lg; bestF = f; bestS = ls;
+      any = true; bestGain = lg; bestF = f; bestS = ls; bestJ = j;
       bL[0] = sm.cum[ls][0]; bL[1] = sm.cum[ls][1]; bL[2] = sm.cum[ls][2];
       bR[0] = T0 - bL[0]; bR[1] = T1 - bL[1]; bR[2] = T2 - bL[2];
       // left set of the split = the first ls + 1 categories in centroid order (kept as a bit mask in shared memory)
@@ -164,6 +173,18 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
       if (cat) for (int q = lane; q <= ls; q += 32) { const int c = sm.order[q]; atomicOr(&sm.mask[c >> 5], 1u << (c & 31)); }
       __syncwarp();
     }
+  }
+  bool writer = true;
+  if (WPS > 1) {   // the block's winner: largest gain, then earliest subset position; a warp without candidates never wins
+    if (lane == 0) { s_gain[warp] = bestGain; s_pos[warp] = any ? bestJ : -1; }
+    __syncthreads();
+    int win = -1;
+    for (int w = 0; w < WPS; w++) {
+      if (s_pos[w] < 0) continue;
+      if (win < 0 || s_gain[w] > s_gain[win] || (s_gain[w] == s_gain[win] && s_pos[w] < s_pos[win])) win = w;
+    }
+    writer = (win < 0) ? (warp == 0) : (warp == win);   // no candidate anywhere: warp 0 reports the dummy split
+    if (!writer) return;
   }
   if (lane == 0) {
     SplitRec r;
@@ -198,9 +219,16 @@ cudaError_t launch_best_split(const SplitLaunch& a, cudaStream_t s) {
   if (warps > SPLIT_WARPS) warps = SPLIT_WARPS;
   if (warps < 1) return cudaErrorInvalidValue;   // maxBins too large for one warp's shared arrays (checked by the trainer)
   const size_t smem = per * warps;
-  cudaError_t e = cudaFuncSetAttribute(best_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(best_split_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  best_split_kernel<<<(a.nSlots + warps - 1) / warps, warps * 32, smem, s>>>(a);
+  // several warps per slot when no slot is a root (their parent statistics come with the launch) and the per-warp arrays fit
+  if (a.allHaveParent && warps == SPLIT_WARPS && a.Fsub >= 2 * SPLIT_WARPS) {
+    e = cudaFuncSetAttribute(best_split_kernel<SPLIT_WARPS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    best_split_kernel<SPLIT_WARPS><<<a.nSlots, SPLIT_WARPS * 32, smem, s>>>(a);
+    return cudaGetLastError();
+  }
+  best_split_kernel<1><<<(a.nSlots + warps - 1) / warps, warps * 32, smem, s>>>(a);
   return cudaGetLastError();
 }
 

@@ -192,3 +192,26 @@ def test_labels_gathered_when_not_carried(b2rf, oracle, cuda):
     finally:
         trainer.set_option("carry_labels", 1)
     assert_parity_allowing_ties(g, o, max_ties=4)
+
+
+def test_constant_nominal_column(b2rf, oracle, cuda):
+    """A nominal feature with ONE category (a constant StringIndexer output).  MLlib 3.1.2 only overwrites numBins for categorical
+    features with more than one category but keeps the feature in featureArity: it stays categorical (no continuous splits are
+    sampled, values must be 0), keeps maxPossibleBins bins in the group-memory accounting, and never yields a valid split.  Trainer
+    and oracle must agree on that, including under a memory limit that cuts groups (bins of the feature count towards the limit)."""
+    rng = np.random.default_rng(11)
+    N = 4000
+    X, y, arity = b2rf.synth.airbnb(N)
+    X = X.numpy().copy()
+    arity = arity.copy()
+    X[:, 2] = 0.0
+    arity[2] = 1
+    for mem in (256, 1):
+        g, o = _fit_both(b2rf, oracle, cuda, X, y.numpy(), arity, maxDepth=6, maxBins=40, numTrees=4, bootstrap=True, seed=9, maxMemoryInMB=mem)
+        assert_trace_parity(g, o)
+        assert_forest_parity(g, o)
+        assert not (g.feature == 2).any()
+    bad = X.copy(); bad[17, 2] = 1.0
+    from b2rf import trainer
+    with pytest.raises(b2rf.IllegalArgumentException, match="Feature 2 is categorical"):
+        trainer.fit_tensors(torch.as_tensor(bad, device=cuda), y.to(cuda), arity, b2rf.TreeParams(maxBins=40))
