@@ -510,7 +510,11 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
   // device node table: one stride per tree
   const int64_t full = (int64_t)1 << std::min(t->p.maxDepth + 1, 17);
   t->nodeStride = full;
-  if (!t->segMode && d_node == nullptr) { set_error("b2rf_trainer_bind: d_node is required unless the segment histogram mode is used"); return B2RF_ERR_ARG; }
+  if (!t->segMode && d_node == nullptr) { set_error(n_rows_local >= ((int64_t)1 << 27)
+                ? "b2rf_trainer_bind: a shard of 2^27 (134,217,728) rows or more cannot use the packed row lists of the segment / sort modes (27-bit row ids); "
+                  "pass d_node so the scan mode can run, or shard the rows over more GPUs"
+                : "b2rf_trainer_bind: d_node is required unless the segment histogram mode is used");
+    return B2RF_ERR_ARG; }
   if (t->bucketMode) {
     // in-bag rows per tree; in segment mode also the initial row lists (ascending rows, packed row | weight << 27)
     const int nb = (int)((n_rows_local + COMPACT_ROWS - 1) / COMPACT_ROWS);

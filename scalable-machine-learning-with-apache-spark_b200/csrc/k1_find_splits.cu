@@ -10,6 +10,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <thread>
+#include <vector>
+#include <algorithm>
 
 namespace b2rf {
 
@@ -163,11 +166,25 @@ int b2rf_sample_rows(const double* d_X, int64_t ldx, int64_t n_rows, int64_t row
 
 int64_t b2rf_sample_indices(int64_t seed, int64_t row0_global, int64_t n_rows, double fraction, int64_t* h_idx_out, int64_t cap) {
   const uint64_t seedWord = ((uint64_t)(uint32_t)xorshift_first_int(seed) << 32) | 0x9E3779B9u;
+  // hash of every row index: a few host threads over contiguous row ranges, kept rows concatenated in range order (ascending)
+  const int nt = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)8, (int64_t)std::thread::hardware_concurrency(), n_rows / 262144 + 1}));
+  std::vector<std::vector<int64_t>> part(nt);
+  auto work = [&](int t) {
+    const int64_t lo = n_rows * t / nt, hi = n_rows * (t + 1) / nt;
+    std::vector<int64_t>& out = part[t];
+    out.reserve((size_t)((double)(hi - lo) * fraction * 1.2) + 64);
+    for (int64_t i = lo; i < hi; i++) {
+      const uint64_t h = mix64(seedWord + (uint64_t)(row0_global + i) * 0x9E3779B97F4A7C15ULL);
+      if (((double)(h >> 11) * 0x1.0p-53) < fraction) out.push_back(i);
+    }
+  };
+  std::vector<std::thread> pool;
+  for (int t = 1; t < nt; t++) pool.emplace_back(work, t);
+  work(0);
+  for (auto& th : pool) th.join();
   int64_t k = 0;
-  for (int64_t i = 0; i < n_rows; i++) {
-    const uint64_t h = mix64(seedWord + (uint64_t)(row0_global + i) * 0x9E3779B97F4A7C15ULL);
-    if (((double)(h >> 11) * 0x1.0p-53) < fraction) { if (k < cap) h_idx_out[k] = i; k++; }
-  }
+  for (int t = 0; t < nt; t++)
+    for (int64_t i : part[t]) { if (k < cap) h_idx_out[k] = i; k++; }
   return k;
 }
 

@@ -123,15 +123,11 @@ __global__ void __launch_bounds__(SPLIT_WARPS * 32) best_split_kernel(const Spli
       for (int b = lane; b < nb; b += 32) sm.order[b] = (uint16_t)b;
     }
     __syncwarp();
-    if (lane == 0) {  // sequential prefix in MLlib's association order: h[next] += h[cur]
-      int o = sm.order[0];
-      double c0 = sm.raw[o][0], c1 = sm.raw[o][1], c2 = sm.raw[o][2];
-      sm.cum[0][0] = c0; sm.cum[0][1] = c1; sm.cum[0][2] = c2;
-      for (int q = 1; q < nb; q++) {
-        o = sm.order[q];
-        c0 = sm.raw[o][0] + c0; c1 = sm.raw[o][1] + c1; c2 = sm.raw[o][2] + c2;
-        sm.cum[q][0] = c0; sm.cum[q][1] = c1; sm.cum[q][2] = c2;
-      }
+    if (lane < 3) {  // sequential prefix in MLlib's association order (h[next] += h[cur]); lanes 0..2 each run one statistic's chain
+      double c = sm.raw[cat ? sm.order[0] : 0][lane];
+      sm.cum[0][lane] = c;
+      if (cat) for (int q = 1; q < nb; q++) { c = sm.raw[sm.order[q]][lane] + c; sm.cum[q][lane] = c; }
+      else for (int q = 1; q < nb; q++) { c = sm.raw[q][lane] + c; sm.cum[q][lane] = c; }
     }
     __syncwarp();
     const double T0 = sm.cum[nb - 1][0], T1 = sm.cum[nb - 1][1], T2 = sm.cum[nb - 1][2];

@@ -388,8 +388,6 @@ class _TreeEstimatorBase(Estimator, _TreeRegressorParams):
         arity = categorical_arities(dataset, est0.getOrDefault("featuresCol"), X.shape[1])
         po = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
         dev = _ForestModelBase._device()
-        Xd = torch.as_tensor(X, device=dev)
-        yd = torch.as_tensor(y, device=dev)
         plist = [e._tree_params() for e in estimators]
         if plist[0].is_classification:
             # Classifier.getNumClasses without label metadata: max label + 1 (MLlib stops at 100 classes, this build at 32)
@@ -402,8 +400,13 @@ class _TreeEstimatorBase(Estimator, _TreeRegressorParams):
                                                "numClasses <= 32 here (MLlib: <= 100).")
             plist = [p.copy(numClasses=max(nc, 2)) for p in plist]
         if len(estimators) == 1:
-            yield estimators[0]._make_model(trainer.fit_tensors(Xd, yd, arity, plist[0], part_offsets=po))
+            # one fit: the host-buffer entry point streams X through two staging buffers (copy of one row chunk while the previous one is
+            # binned), so the f64 feature matrix is never resident on the GPU
+            yield estimators[0]._make_model(trainer.fit_host(X, y, arity, plist[0], device=dev, part_offsets=po))
             return
+        # several candidates (fitMultiple): one device copy of the fold, binned once, histogram passes shared (fit_many_tensors)
+        Xd = torch.as_tensor(X, device=dev)
+        yd = torch.as_tensor(y, device=dev)
         forests = trainer.fit_many_tensors(Xd, yd, arity, plist, part_offsets=po)   # shared passes
         for est, forest in zip(estimators, forests):
             yield est._make_model(forest)

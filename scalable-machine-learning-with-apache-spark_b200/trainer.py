@@ -487,7 +487,7 @@ def sample_indices(seed: int, row0_global: int, n_rows: int, fraction: float) ->
 
 def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_offsets=None, part0: int = None, group=None,
              keep_trace: bool = False, hist_mode: str = "segment", chunk_rows: int = 1 << 20) -> Forest:
-    """Public host-buffer entry point (what the Spark adapter calls): X_host f64 [n, F] / y_host f64 [n] are HOST arrays
+    """Public host-buffer entry point (what the Spark adapter's single-estimator fit calls): X_host f64 [n, F] / y_host f64 [n] are HOST arrays
     (numpy or CPU torch tensors; pinned memory makes the copies asynchronous).
 
     The raw feature matrix never has to be resident on the GPU: the findSplits row sample is gathered on the host (5 MB),
