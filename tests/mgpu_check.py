@@ -91,6 +91,24 @@ def run_cases(dev, rank, world, log=print) -> str:
                 ok = False
                 first = first or f"{name}: {str(e)[:200]}"
                 log(f"[mgpu] {name}: FAILED {e}")
+    # ---- fitMultiple shared passes on sharded rows: every candidate's forest equals its own sharded fit_tensors fit (the merged K4
+    # launch serves all candidates; each candidate's histogram is all-reduced separately) ----
+    Xl = torch.as_tensor(Xa[lo:hi], device=dev)
+    yl = torch.as_tensor(ya[lo:hi], device=dev)
+    grid = [b2rf.TreeParams(maxDepth=d, maxBins=40, numTrees=t, bootstrap=True, seed=42) for d, t in ((2, 5), (5, 3), (6, 8))]
+    many = trainer.fit_many_tensors(Xl, yl, arity, grid, part_offsets=po_local)
+    same = True
+    for p_, f_ in zip(grid, many):
+        r_ = trainer.fit_tensors(Xl, yl, arity, p_, part_offsets=po_local)
+        same = same and np.array_equal(f_.feature, r_.feature) and np.array_equal(f_.threshold, r_.threshold) and np.array_equal(f_.stats[:, 0], r_.stats[:, 0]) \
+            and np.array_equal(f_.prediction, r_.prediction)
+    if rank == 0:
+        if same:
+            log(f"[mgpu] fit_many shared passes: world={world} OK ({[f_.num_nodes() for f_ in many]} nodes)")
+        else:
+            ok = False
+            first = first or "fit_many shared passes: a candidate differs from its fit_tensors fit"
+            log("[mgpu] fit_many shared passes: FAILED")
     msg = [("ok" if ok else "FAILED " + first) if rank == 0 else ""]
     dist.broadcast_object_list(msg, src=0)
     dist.barrier()
