@@ -215,3 +215,41 @@ def test_constant_nominal_column(b2rf, oracle, cuda):
     from b2rf import trainer
     with pytest.raises(b2rf.IllegalArgumentException, match="Feature 2 is categorical"):
         trainer.fit_tensors(torch.as_tensor(bad, device=cuda), y.to(cuda), arity, b2rf.TreeParams(maxBins=40))
+
+
+@pytest.mark.parametrize("tma", [0, 1])
+def test_integer_labels_64_byte_rows(b2rf, oracle, cuda, tma):
+    """Integer labels on 64-feature rows: the narrow (7-plane) limb form, with register-staged code rows (the default for 64- and
+    128-byte rows) and with TMA bulk copies.  Sums are exact, so the forest must equal the oracle's bit for bit (all features offered:
+    no subset draws, a tie stays local)."""
+    from b2rf import trainer
+    X, y, arity = b2rf.synth.c3(30000, device="cpu")
+    yi = torch.round(y * 3.0)
+    trainer.set_option("k4_tma", tma)
+    try:
+        before = trainer.k4_launch_counts()
+        g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), yi.numpy(), arity, maxDepth=9, maxBins=64, numTrees=3, bootstrap=True, seed=4)
+        assert trainer.k4_launch_counts()["limb"] > before["limb"]
+    finally:
+        trainer.set_option("k4_tma", 0)
+    k = first_tie = None
+    from helpers import first_tie_in_order
+    k = first_tie_in_order(g, o)
+    upto = len(o.trace_i) if k is None else k
+    assert upto > 0.5 * len(o.trace_i)
+    assert np.array_equal(g.trace_d[:upto, 2:5], o.trace_d[:upto, 2:5])      # counts AND both sums bit-identical
+    if k is None:
+        assert_forest_parity(g, o)
+        assert np.array_equal(g.stats[:, 1:3], o.stats[:, 1:3])
+
+
+def test_tma_staging_real_labels(b2rf, oracle, cuda):
+    """The TMA-staged form of the wide limb kernel (one bulk async copy per code row, mbarrier ring) on 64-byte rows."""
+    from b2rf import trainer
+    X, y, arity = b2rf.synth.c3(30000, device="cpu")
+    trainer.set_option("k4_tma", 1)
+    try:
+        g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=9, maxBins=64, numTrees=3, bootstrap=True, seed=4)
+    finally:
+        trainer.set_option("k4_tma", 0)
+    assert_parity_allowing_ties(g, o, max_ties=4)
