@@ -9,6 +9,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <mutex>
 
 namespace b2rf {
@@ -157,7 +158,6 @@ __global__ void __launch_bounds__(BAG_THREADS) bag_kernel(int64_t seed, const in
 // the same order as PoissonDistribution.sample): every lane computes the sample that WOULD start at its uniform, lane 0
 // finishes the sample carried in from the previous window and walks the start positions, marked lanes emit.
 // ---------------------------------------------------------------------------------------------------------------------
-constexpr int BAGW_WARPS = 4;
 __device__ __forceinline__ uint32_t well_M(uint32_t x) { const uint32_t t = x ^ (x << 25); return (t << 9) ^ (t >> 21); }
 
 struct BagWarpSmem {
@@ -224,10 +224,14 @@ __device__ __forceinline__ void well_batch64(uint32_t* v, int& index, uint32_t& 
   out_b = well_temper(e);
 }
 
-__global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed, const int64_t* part_offsets, int P, int part0, int T, double rate,
-                                                                   double expNegRate, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
+// One block per SM, blockDim / 32 warps each; warp w of block b takes partitions b + gridDim * (w + warps * i).  The kernel is bound by
+// instruction issue, so what matters is that every SM carries the same number of partitions: with the earlier 4-warp blocks handed out by
+// the block scheduler an SM ended up with 16 or 20 warps (2442 partitions of C3 over 148 SMs) and the kernel took as long as the 20.
+__global__ void __launch_bounds__(1024) bag_warp_kernel(int64_t seed, const int64_t* part_offsets, int P, int part0, int T, double rate,
+                                                        double expNegRate, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
   __shared__ uint32_t tabs[6 * 1024];              // M^(2^s), s = 0..5, as 4 x 256 byte tables
-  __shared__ BagWarpSmem sm_all[BAGW_WARPS];
+  extern __shared__ __align__(16) unsigned char bag_dyn_smem[];
+  BagWarpSmem* sm_all = reinterpret_cast<BagWarpSmem*>(bag_dyn_smem);
   // tables: entry (s, byte, val) = M^(2^s)(val << 8*byte)
   for (int e = threadIdx.x; e < 6 * 1024; e += blockDim.x) {
     const int st = e >> 10, byte = (e >> 8) & 3, val = e & 255;
@@ -237,10 +241,9 @@ __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed,
   }
   __syncthreads();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int p = blockIdx.x * BAGW_WARPS + warp;
-  if (p >= P) return;
   BagWarpSmem& sm = sm_all[warp];
   const unsigned FULL = 0xffffffffu;
+  for (int p = blockIdx.x + gridDim.x * warp; p < P; p += gridDim.x * (blockDim.x >> 5)) {
   // AbstractWell.setSeed: v[0..1] = (hi, lo); v[i] = 1812433253 * (l ^ (l >> 30)) + i with l = (long) v[i - 2]: two serial chains
   {
     const int64_t sd = seed + (int64_t)(part0 + p) + 1;
@@ -345,6 +348,8 @@ __global__ void __launch_bounds__(BAGW_WARPS * 32) bag_warp_kernel(int64_t seed,
     nc = (long)__shfl_sync(FULL, (long long)nc, 0);
     __syncwarp();
   }
+  __syncwarp();
+  }   // next partition of this warp
 }
 
 __global__ void bag_ones_kernel(int64_t n, int T, uint8_t* w, int64_t ldw, int32_t* node, int64_t ldn) {
@@ -392,9 +397,16 @@ int b2rf_bag(int64_t seed, const int64_t* h_part_offsets, int32_t P, int32_t par
   static const bool serialOnly = [] { const char* m = std::getenv("B2RF_BAG_SERIAL"); return m && *m == '1'; }();
   bool ok = true;
   if (bootstrap && 1000 * subsamplingRate >= 64 && !serialOnly) {   // warp per partition (window of 32 uniforms < iteration cap)
-    bag_warp_kernel<<<(P + BAGW_WARPS - 1) / BAGW_WARPS, BAGW_WARPS * 32, 0, s>>>(seed, d_po, P, part0, T, subsamplingRate, std::exp(-subsamplingRate),
-                                                                                d_w, ldw, d_node, ldn);
-    ok = cuda_ok(cudaGetLastError(), "b2rf_bag");
+    const int sms = device_sm_count();
+    int warps = (P + sms - 1) / sms;                       // partitions per SM, one warp each (more than 32: warps loop)
+    warps = warps < 1 ? 1 : (warps > 32 ? 32 : warps);
+    const int grid = std::min(sms, (P + warps - 1) / warps);
+    const size_t smem = (size_t)warps * sizeof(BagWarpSmem);
+    ok = cuda_ok(cudaFuncSetAttribute(bag_warp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bag attr");
+    if (ok) {
+      bag_warp_kernel<<<grid, warps * 32, smem, s>>>(seed, d_po, P, part0, T, subsamplingRate, std::exp(-subsamplingRate), d_w, ldw, d_node, ldn);
+      ok = cuda_ok(cudaGetLastError(), "b2rf_bag");
+    }
   } else {
     const size_t smem = (size_t)624 * BAG_THREADS * 4;
     ok = cuda_ok(cudaFuncSetAttribute(bag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem), "b2rf_bag attr");
