@@ -495,6 +495,9 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
   if (!t || !d_bins || !d_y || !d_w || !d_hist || n_rows_local < 0 || ((ldb * (t ? t->codeBytes : 1)) & 15) || ldb < n_rows_local || ldw < n_rows_local || (d_node && ldn < n_rows_local)) {
     set_error("b2rf_trainer_bind: bad argument (ldb must be a multiple of 16 and every leading dimension >= n_rows)"); return B2RF_ERR_ARG;
   }
+  if ((ldw & 7) != 0 || (reinterpret_cast<uintptr_t>(d_w) & 7) != 0) {
+    set_error("b2rf_trainer_bind: d_w must be 8-byte aligned with ldw a multiple of 8 (the row lists are built from 8-byte loads of bag weights)"); return B2RF_ERR_ARG;
+  }
   t->d_bins = d_bins; t->ldb = ldb; t->d_y = d_y; t->d_w = d_w; t->ldw = ldw; t->d_node = d_node; t->ldn = ldn; t->nLocal = n_rows_local;
   t->d_hist = d_hist; t->histCells = hist_cells;
   t->d_bins_rm = d_bins_rm; t->ldr = ldr;

@@ -14,11 +14,23 @@
 namespace b2rf {
 
 // ---- initial row lists: per tree, the in-bag rows in ascending order, packed row | weight << 27 ----
+// A block covers COMPACT_ROWS = 2048 consecutive rows of one tree, a thread 8 of them (one 8-byte load of bag weights; the weight rows
+// are padded to multiples of 128, so whole words can be read and rows past n_rows are masked).
+__device__ __forceinline__ uint64_t load_w8(const uint8_t* w, int64_t ldw, int t, int64_t r0, int64_t n_rows) {
+  if (r0 >= n_rows) return 0ull;
+  uint64_t v = *reinterpret_cast<const uint64_t*>(w + (size_t)t * ldw + r0);
+  const int64_t left = n_rows - r0;
+  if (left < 8) v &= (1ull << (8 * left)) - 1ull;
+  return v;
+}
+__device__ __forceinline__ uint32_t nonzero_bytes(uint64_t v) {   // bit k set <=> byte k != 0
+  uint64_t m = v | (v >> 4); m |= m >> 2; m |= m >> 1; m &= 0x0101010101010101ull;     // bit 0 of every byte = OR of its bits
+  return (uint32_t)((m * 0x0102040810204080ull) >> 56);                                  // gather the eight flag bits
+}
 __global__ void __launch_bounds__(256) compact_count_kernel(const uint8_t* w, int64_t ldw, int64_t n_rows, uint32_t* blockCnt, int nb) {
   const int t = blockIdx.y, b = blockIdx.x;
-  const int64_t r0 = (int64_t)b * COMPACT_ROWS;
-  uint32_t c = 0;
-  for (int i = threadIdx.x; i < COMPACT_ROWS; i += 256) { const int64_t r = r0 + i; c += (r < n_rows && w[(size_t)t * ldw + r] != 0); }
+  const int64_t r0 = (int64_t)b * COMPACT_ROWS + (int64_t)threadIdx.x * 8;
+  uint32_t c = __popc(nonzero_bytes(load_w8(w, ldw, t, r0, n_rows)));
   for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
   __shared__ uint32_t sw[8];
   if ((threadIdx.x & 31) == 0) sw[threadIdx.x >> 5] = c;
@@ -37,25 +49,27 @@ __global__ void __launch_bounds__(256) compact_write_kernel(const uint8_t* w, in
   const int t = blockIdx.y, b = blockIdx.x;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   __shared__ uint32_t sw[8];
-  uint32_t run = 0;
-  uint32_t* out = idx + treeBase[t] + blockOff[(size_t)t * nb + b];
-  double* yout = ylist ? ylist + treeBase[t] + blockOff[(size_t)t * nb + b] : nullptr;
-  for (int it = 0; it < COMPACT_ROWS / 256; it++) {
-    const int64_t r = (int64_t)b * COMPACT_ROWS + it * 256 + threadIdx.x;
-    uint32_t wv = (r < n_rows) ? w[(size_t)t * ldw + r] : 0u;
-    const unsigned bal = __ballot_sync(0xffffffffu, wv != 0);
-    if (lane == 0) sw[warp] = __popc(bal);
-    __syncthreads();
-    uint32_t before = 0, total = 0;
-    for (int i = 0; i < 8; i++) { if (i < warp) before += sw[i]; total += sw[i]; }
-    if (wv != 0) {
-      if (wv > 31u) wv = 31u;   // packed in 5 bits
-      const uint32_t at = run + before + __popc(bal & ((1u << lane) - 1u));
-      out[at] = (uint32_t)r | (wv << 27);
-      if (yout) yout[at] = y[r];
+  const int64_t r0 = (int64_t)b * COMPACT_ROWS + (int64_t)threadIdx.x * 8;
+  const uint64_t wv = load_w8(w, ldw, t, r0, n_rows);
+  const uint32_t flags = nonzero_bytes(wv);
+  const uint32_t mine = __popc(flags);
+  uint32_t incl = mine;                                      // exclusive rank of this thread's first kept row inside the block
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += u; }
+  if (lane == 31) sw[warp] = incl;
+  __syncthreads();
+  uint32_t before = incl - mine;
+  for (int i = 0; i < warp; i++) before += sw[i];
+  const size_t base = treeBase[t] + blockOff[(size_t)t * nb + b] + before;
+  uint32_t k = 0;
+#pragma unroll
+  for (int j = 0; j < 8; j++) {
+    if ((flags >> j) & 1u) {
+      uint32_t c = (uint32_t)(wv >> (8 * j)) & 0xffu;
+      if (c > 31u) c = 31u;   // packed in 5 bits
+      idx[base + k] = (uint32_t)(r0 + j) | (c << 27);
+      if (ylist) ylist[base + k] = y[r0 + j];
+      k++;
     }
-    run += total;
-    __syncthreads();
   }
 }
 cudaError_t launch_compact_count(const uint8_t* w, int64_t ldw, int T, int64_t n_rows, uint32_t* blockCnt, unsigned long long* totals, cudaStream_t s) {
