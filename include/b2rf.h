@@ -179,7 +179,8 @@ int b2rf_trainer_export_class_counts(b2rf_trainer* t, double* h_counts);
 int64_t b2rf_trainer_trace_size(const b2rf_trainer* t);
 /* Evidence / test hook: how many times this process launched each K4 implementation, h_counts[i] for i < n:
  * 0 limb kernel (native 32-bit shared-memory adds on fixed-point limbs; default of the segment mode), 1 fp64 kernel for
- * <= 32 features per node, 2 general fp64 kernel, 3 multiclass class-count kernel, 4 column-scan kernels. */
+ * <= 32 features per node, 2 general fp64 kernel, 3 multiclass class-count launches (either form), 4 column-scan kernels,
+ * 5 multiclass launches that took the staged form (code rows staged through shared memory, labels from the row lists). */
 int b2rf_k4_launch_counts(int64_t* h_counts, int32_t n);
 int b2rf_trainer_trace(const b2rf_trainer* t, int32_t* h_ints, double* h_dbls);
 

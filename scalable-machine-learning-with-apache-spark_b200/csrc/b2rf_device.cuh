@@ -35,4 +35,9 @@ __device__ __forceinline__ bool in_cat_mask(const uint32_t* masks, uint32_t aux,
   return (masks[(size_t)(aux & 0x7fffffffu) * maskWords + (bin >> 5)] >> (bin & 31)) & 1u;
 }
 
+// fp64 add to the GLOBAL histogram, no return value (SASS REDG.E.ADD.F64).  Written as PTX because the histogram pointer comes out of a
+// per-slot table: through atomicAdd() the compiler cannot prove the address space and emits a generic atomic — an address-space query
+// plus a shared-memory compare-and-swap path and a returning global ATOM per call site.
+__device__ __forceinline__ void red_add_f64(double* p, double v) { asm volatile("red.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory"); }
+
 }  // namespace b2rf

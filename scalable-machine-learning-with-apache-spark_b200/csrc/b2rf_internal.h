@@ -89,7 +89,7 @@ struct BucketLaunch {
 };
 
 // Which K4 implementation a launch used (b2rf_k4_launch_counts; tests assert on it).
-enum { B2RF_K4_LIMB = 0, B2RF_K4_FP64_32 = 1, B2RF_K4_FP64_GENERAL = 2, B2RF_K4_CLASS_COUNTS = 3, B2RF_K4_SCAN = 4, B2RF_K4_VARIANTS = 5 };
+enum { B2RF_K4_LIMB = 0, B2RF_K4_FP64_32 = 1, B2RF_K4_FP64_GENERAL = 2, B2RF_K4_CLASS_COUNTS = 3, B2RF_K4_SCAN = 4, B2RF_K4_CLASS_STAGED = 5, B2RF_K4_VARIANTS = 6 };
 void count_k4_variant(int v);
 long long k4_variant_count(int v);
 
@@ -160,6 +160,9 @@ struct ClsHistLaunch {                   // segment mode only
   unsigned long long* rows_acc;          // optional device counter: += rows visited by this launch
   double* hist;
   const DSeg* dseg; const int64_t* slot_pos; const uint32_t* idx0; const uint32_t* idx1;
+  const double* y0; const double* y1;    // labels carried with the row lists (nullptr: gather y[row]); the staged kernel needs them
+  const int32_t* slot_cells;             // [nSlots] histogram cells of the slot (over its Fsub features)
+  int32_t staged;                        // 0: always the gather kernel (B2RF_K4C=gather)
 };
 cudaError_t launch_cls_hist(const ClsHistLaunch& a, cudaStream_t s);
 

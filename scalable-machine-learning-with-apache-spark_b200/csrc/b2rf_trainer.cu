@@ -805,6 +805,8 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       c.nSlots = (int32_t)nSlots; c.CH = SEG_CH; c.slot_fo = t->dSlotFo.p; c.slot_base = t->dSlotBase.p; c.Fsub = t->Fsub;
       c.padB = maxBinsAll; c.C = t->C; c.M = t->M; c.direct = 0; c.hist = t->d_hist; c.rows_acc = t->dRowsAcc.p;
       c.dseg = t->dSeg.p; c.slot_pos = t->dSlotPos.p; c.idx0 = t->dIdx0.p; c.idx1 = t->dIdx1.p;
+      c.y0 = t->carryY ? t->dY0.p : nullptr; c.y1 = t->carryY ? t->dY1.p : nullptr; c.slot_cells = t->dSlotCells.p;
+      { static const bool gather = [] { const char* m = std::getenv("B2RF_K4C"); return m && !std::strcmp(m, "gather"); }(); c.staged = gather ? 0 : 1; }
       e = launch_cls_hist(c, s);
       t->nKernels += 2;
     } else if (t->segMode) {

@@ -37,10 +37,6 @@ constexpr uint32_t LIMB_MASK = (1u << 20) - 1u;
 constexpr int LIMB_EXP_MAX = 460;          // |exponent| of the task scale kept inside the range where every scale factor is a normal double
 constexpr int LIMB_WBITS = 5;              // bag weights are packed in 5 bits (<= 31)
 
-// fp64 add to the GLOBAL histogram, no return value (SASS REDG.E.ADD.F64).  Written as PTX because the histogram pointer comes out of a
-// per-slot table: through atomicAdd() the compiler cannot prove the address space and emits a generic atomic — an address-space query
-// plus a shared-memory compare-and-swap path and a returning global ATOM per call site.
-__device__ __forceinline__ void red_add_f64(double* p, double v) { asm volatile("red.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory"); }
 __device__ __forceinline__ double pow2d(int k) { return __hiloint2double((1023 + k) << 20, 0); }   // 2^k, k in the normal range
 __device__ __forceinline__ bool mbar_try(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
@@ -473,7 +469,7 @@ extern "C" {
 
 /* How many times each K4 implementation has been launched by this process (test / evidence hook):
  * 0 = limb kernel (k4_limb.cu), 1 = fp64 kernel for <= 32 features (bucket_hist32_kernel), 2 = general fp64 kernel,
- * 3 = multiclass class-count kernel, 4 = column-scan kernels (hist_kernel<0|1|2>). */
+ * 3 = multiclass class-count launches, 4 = column-scan kernels (hist_kernel<0|1|2>), 5 = multiclass launches in the staged form. */
 int b2rf_k4_launch_counts(int64_t* h_counts, int32_t n) {
   if (!h_counts || n <= 0) return B2RF_ERR_ARG;
   for (int i = 0; i < n; i++) h_counts[i] = (int64_t)b2rf::k4_variant_count(i);

@@ -89,10 +89,174 @@ __global__ void __launch_bounds__(CLS_THREADS) bucket_hist_cls_kernel(const ClsH
   }
 }
 
-cudaError_t launch_cls_hist(const ClsHistLaunch& a0, cudaStream_t s) {
-  cudaError_t e = launch_seg_tasks(a0.dseg, a0.slot_pos, a0.nSlots, a0.CH, const_cast<uint32_t*>(a0.chunk_prefix), s, false, a0.rows_acc);
+// ---- staged form (default when labels travel with the row lists and code rows are 64 or 128 bytes of uint8 codes) ----
+// The skeleton of the regression limb kernel (k4_limb.cu): dynamic ticket scheduling over (slot, chunk, feature group) tasks, 12
+// warps x 2 CTAs per SM, each warp register-stages the code rows of its next 32-row block (LDG.128 -> STS.128, in flight while the
+// current block is added) and writes one 8-byte (weight, class offset) pair per row next to them.  A lane then reads its feature's
+// code with one LDS.U8 and the row's pair with one broadcast LDS.64 and issues ONE native 32-bit add (ATOMS.ADD): three
+// shared-memory wavefronts per 32 updates against the gather kernel's dependent global loads.  Counter layout [bin][class][lane]
+// (bank == lane); bag counts are exact in u32 (<= 4096 rows x weight <= 31 per task).
+template <int G, int LDR>
+__global__ void __launch_bounds__(384, 2) staged_hist_cls_kernel(const ClsHistLaunch a, uint32_t* ticket) {
+  extern __shared__ __align__(16) unsigned char smraw[];
+  __shared__ uint32_t s_task;
+  constexpr int THREADS = 384, W = THREADS / 32, BR = 32;
+  constexpr int R = 32 / G, NU = BR / R;
+  constexpr int NPC = (BR * LDR) / 512, CPR = LDR / 16;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int C = a.C, padB = a.padB;
+  uint32_t* hist = reinterpret_cast<uint32_t*>(smraw);                 // [padB][C][G]
+  const int cellsPerBin = C * G;
+  const size_t histBytes = (size_t)padB * cellsPerBin * 4;
+  constexpr int tileBytes = BR * LDR, valBytes = BR * 8, warpBytes = tileBytes + 2 * valBytes;
+  unsigned char* ring = smraw + histBytes + (size_t)warp * warpBytes;
+  unsigned char* valsBase = ring + tileBytes;
+  const int fl = lane & (G - 1), r = lane / G;
+  const int nG = (a.Fsub + G - 1) / G;
+  const uint32_t total = a.chunk_prefix[a.nSlots] * (uint32_t)nG;
+  const uint8_t* bins_rm = reinterpret_cast<const uint8_t*>(a.bins_rm);
+  const size_t stride = (size_t)4 * a.M;
+  // rows past the end of a chunk carry weight 0; their staged code only has to be a valid bin index (see k4_limb.cu)
+  for (int c = lane; c < warpBytes >> 4; c += 32) reinterpret_cast<uint4*>(ring)[c] = make_uint4(0u, 0u, 0u, 0u);
+  __syncthreads();
+
+  for (;;) {
+    if (tid == 0) s_task = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t task = s_task;
+    if (task >= total) break;
+    const uint32_t bt = task / (uint32_t)nG;
+    const int g = (int)(task - bt * (uint32_t)nG);
+    int lo = 0, hi = a.nSlots;
+    while (hi - lo > 1) { const int mid = (lo + hi) >> 1; if (a.chunk_prefix[mid] <= bt) lo = mid; else hi = mid; }
+    const int slot = lo;
+    const uint32_t begin = (bt - a.chunk_prefix[slot]) * (uint32_t)a.CH;
+    const DSeg sg = a.dseg[a.slot_pos[slot]];
+    const uint32_t* rl = (sg.buf ? a.idx1 : a.idx0) + sg.start + begin;
+    const double* yl = (sg.buf ? a.y1 : a.y0) + sg.start + begin;
+    const uint2* fo = a.slot_fo + (size_t)slot * a.Fsub;
+    double* hb = a.hist + (size_t)a.slot_base[slot] * stride;
+    const int n = (int)min((uint32_t)a.CH, sg.count - begin);
+    const int j = g * G + fl;
+    const bool active = j < a.Fsub;
+    const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
+    const bool direct = (int64_t)n * a.Fsub < (int64_t)a.slot_cells[slot] * C;   // fewer updates than counters: straight to global memory
+    uint32_t ent = 0u; uint32_t cls = 0u;
+    auto load = [&](int blk, int nblk) {
+      const int i = blk * BR + lane;
+      const bool in = blk < nblk && i < n;
+      ent = in ? rl[i] : 0u;
+      cls = in ? min((uint32_t)(int)yl[i], (uint32_t)(C - 1)) : 0u;
+    };
+    if (direct) {
+      for (int base = warp * 32; base < n; base += W * 32) {
+        const bool in = base + lane < n;
+        const uint32_t en = in ? rl[base + lane] : 0u;
+        const uint32_t cl = in ? min((uint32_t)(int)yl[base + lane], (uint32_t)(C - 1)) : 0u;
+#pragma unroll 4
+        for (int u = 0; u < G; u++) {
+          const int src = u * R + r;
+          const uint32_t e2 = __shfl_sync(FULL, en, src), c2 = __shfl_sync(FULL, cl, src);
+          if (active && (e2 >> 27)) {
+            const uint32_t code = bins_rm[(size_t)(e2 & 0x7ffffffu) * LDR + e.x];
+            red_add_f64(hb + (size_t)(e.y + code) * stride + c2, (double)(e2 >> 27));
+          }
+        }
+      }
+      continue;   // the next iteration's __syncthreads (ticket) separates the tasks
+    }
+    {
+      uint4* h4 = reinterpret_cast<uint4*>(hist);
+      for (int c = tid; c < (int)(histBytes >> 4); c += THREADS) h4[c] = make_uint4(0u, 0u, 0u, 0u);
+    }
+    __syncthreads();
+    const int nblk = (n + BR - 1) / BR;
+    uint32_t* hcell = hist + fl;
+    auto put_vals = [&](int s) {
+      *reinterpret_cast<uint2*>(valsBase + s * valBytes + lane * 8) = make_uint2(ent >> 27, cls * (uint32_t)G);
+    };
+    uint4 creg[NPC];
+    auto fetch = [&](int blk) {                                    // (ent, cls) hold block blk
+      const int nvalid = min(BR, n - blk * BR);
+#pragma unroll
+      for (int q = 0; q < NPC; q++) {
+        const int c = lane + 32 * q, row = c / CPR, seg = c - row * CPR;
+        const uint32_t e2 = __shfl_sync(FULL, ent, row);
+        creg[q] = row < nvalid ? *reinterpret_cast<const uint4*>(bins_rm + (size_t)(e2 & 0x7ffffffu) * LDR + seg * 16) : make_uint4(0u, 0u, 0u, 0u);
+      }
+    };
+    int b = warp;
+    if (b < nblk) { load(b, nblk); fetch(b); put_vals(0); load(b + W, nblk); }
+    for (int k = 0; b < nblk; k++, b += W) {
+      const int s = k & 1;
+#pragma unroll
+      for (int q = 0; q < NPC; q++) reinterpret_cast<uint4*>(ring)[lane + 32 * q] = creg[q];
+      __syncwarp();
+      if (b + W < nblk) { fetch(b + W); put_vals(s ^ 1); load(b + 2 * W, nblk); }
+      if (active) {
+        const unsigned char* tl = ring + r * LDR + e.x;
+        const unsigned char* vv = valsBase + s * valBytes + r * 8;
+        uint32_t code = tl[0];
+        uint2 q = *reinterpret_cast<const uint2*>(vv);
+#pragma unroll
+        for (int u = 0; u < NU; u++) {
+          const uint32_t cc = code; const uint2 p = q;
+          if (u + 1 < NU) { code = tl[(u + 1) * R * LDR]; q = *reinterpret_cast<const uint2*>(vv + (u + 1) * R * 8); }
+          atomicAdd(hcell + cc * (uint32_t)cellsPerBin + p.y, p.x);       // padding rows add 0
+        }
+      }
+      __syncwarp();
+    }
+    __syncthreads();
+    for (int c = tid; c < padB * cellsPerBin; c += THREADS) {
+      const uint32_t k = hist[c];
+      if (!k) continue;                                                    // untouched counter (also every counter of an idle lane)
+      const int bin = c / cellsPerBin, rem = c - bin * cellsPerBin;
+      const int cl = rem / G, f2 = rem & (G - 1);
+      red_add_f64(hb + ((size_t)fo[g * G + f2].y + (size_t)bin) * stride + cl, (double)k);
+    }
+    // the ticket __syncthreads at the top of the next iteration orders this flush before the next task's zeroing
+  }
+}
+
+static size_t staged_cls_smem(int padB, int C, int G, int ldr) { return (size_t)padB * C * G * 4 + (size_t)12 * (32 * ldr + 2 * 32 * 8); }
+
+template <int G, int LDR>
+static cudaError_t launch_staged_cls(const ClsHistLaunch& a, uint32_t* ticket, size_t smem, cudaStream_t s) {
+  cudaError_t e = cudaFuncSetAttribute(staged_hist_cls_kernel<G, LDR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
+  staged_hist_cls_kernel<G, LDR><<<device_sm_count() * 2, 384, smem, s>>>(a, ticket);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_cls_hist(const ClsHistLaunch& a0, cudaStream_t s) {
   ClsHistLaunch a = a0;
+  // staged form: uint8 codes in 64- or 128-byte rows, labels in the row lists, and a task histogram that leaves two CTAs per SM
+  int G = 0;
+  if (a.staged && a.codeBytes == 1 && (a.ldr == 64 || a.ldr == 128) && a.y0 && a.y1 && a.slot_cells &&
+      (reinterpret_cast<uintptr_t>(a.bins_rm) & 15) == 0) {
+    G = 32;
+    while (G > 8 && G / 2 >= a.Fsub) G /= 2;
+    while (G >= 8 && staged_cls_smem(a.padB, a.C, G, (int)a.ldr) > (size_t)113 * 1024) G /= 2;
+    if (G < 8) G = 0;
+  }
+  cudaError_t e = launch_seg_tasks(a.dseg, a.slot_pos, a.nSlots, a.CH, const_cast<uint32_t*>(a.chunk_prefix), s, /*ticket=*/G != 0, a.rows_acc);
+  if (e != cudaSuccess) return e;
+  count_k4_variant(B2RF_K4_CLASS_COUNTS);
+  if (G) {
+    uint32_t* ticket = const_cast<uint32_t*>(a.chunk_prefix) + a.nSlots + 1;
+    const size_t smem = staged_cls_smem(a.padB, a.C, G, (int)a.ldr);
+    count_k4_variant(B2RF_K4_CLASS_STAGED);
+    if (a.ldr == 64) {
+      if (G == 32) return launch_staged_cls<32, 64>(a, ticket, smem, s);
+      if (G == 16) return launch_staged_cls<16, 64>(a, ticket, smem, s);
+      return launch_staged_cls<8, 64>(a, ticket, smem, s);
+    }
+    if (G == 32) return launch_staged_cls<32, 128>(a, ticket, smem, s);
+    if (G == 16) return launch_staged_cls<16, 128>(a, ticket, smem, s);
+    return launch_staged_cls<8, 128>(a, ticket, smem, s);
+  }
   size_t smem = (size_t)a.C * a.padB * 32 * 4;
   a.direct = smem > (size_t)200 * 1024;
   if (a.direct) smem = 16;
@@ -101,7 +265,6 @@ cudaError_t launch_cls_hist(const ClsHistLaunch& a0, cudaStream_t s) {
   if (perSM > 4) perSM = 4;
   e = cudaFuncSetAttribute(bucket_hist_cls_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  count_k4_variant(B2RF_K4_CLASS_COUNTS);
   bucket_hist_cls_kernel<<<device_sm_count() * perSM, CLS_THREADS, smem, s>>>(a);
   return cudaGetLastError();
 }

@@ -23,6 +23,18 @@ def _stream():
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
+# Row width of the row-major code matrix.  "auto": 64 codes for up to 64 features and 128 for up to 128 — the widths the histogram
+# kernels stage through registers with compile-time offsets (k4_limb.cu, k8_multiclass.cu), and rows that start on a 64- / 128-byte
+# boundary so a gather touches the fewest 32-byte sectors; wider matrices are padded to 16.  An integer pads to that multiple.
+CODE_ROW_ALIGN = "auto"
+
+
+def code_row_width(F: int) -> int:
+    if CODE_ROW_ALIGN == "auto":
+        return 64 if F <= 64 else 128 if F <= 128 else _pad(F, 16)
+    return _pad(F, int(CODE_ROW_ALIGN))
+
+
 def _pad(n: int, m: int = 128) -> int:
     return max(m, (n + m - 1) // m * m)
 
@@ -239,9 +251,9 @@ def _check_labels(y, params, dist=None, group=None, device=None):
 
 def k4_launch_counts() -> dict:
     """Launches of each K4 implementation by this process so far (b2rf_k4_launch_counts)."""
-    c = np.zeros(5, np.int64)
-    check(lib().b2rf_k4_launch_counts(c.ctypes.data_as(C.c_void_p), 5))
-    return dict(limb=int(c[0]), fp64_32=int(c[1]), fp64_general=int(c[2]), class_counts=int(c[3]), scan=int(c[4]))
+    c = np.zeros(6, np.int64)
+    check(lib().b2rf_k4_launch_counts(c.ctypes.data_as(C.c_void_p), 6))
+    return dict(limb=int(c[0]), fp64_32=int(c[1]), fp64_general=int(c[2]), class_counts=int(c[3]), scan=int(c[4]), class_staged=int(c[5]))
 
 
 def set_option(name: str, value: int):
@@ -353,7 +365,7 @@ def fit_tensors(X: torch.Tensor, y: torch.Tensor, arity, params: TreeParams, par
         else:
             code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
             bins = torch.empty((F, ld), dtype=code_dt, device=dev)
-            bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
+            bins_rm = torch.empty((max(n_local, 1), code_row_width(F)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
             if dbg:
                 torch.cuda.synchronize(dev); ta = time.perf_counter()
             bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm, check_errors=False)
@@ -409,7 +421,7 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
                 thr, ns = find_splits(samp, S["arity_d"], S["mpb"], fraction * float(S["N"]))
                 code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
                 bins = torch.empty((F, ld), dtype=code_dt, device=dev)
-                bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
+                bins_rm = torch.empty((max(n_local, 1), code_row_width(F)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
                 bin_features(X, thr, ns, S["arity_d"], bins=bins, row0=0, bins_rm=bins_rm, check_errors=False)
                 _raise_bin_errors(S["arity_d"], S["dist"], group)
                 shared[key] = (thr.cpu().numpy(), ns.cpu().numpy(), bins, bins_rm)
@@ -530,7 +542,7 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
         # K2 streamed over row chunks
         code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
         bins = torch.empty((F, ld), dtype=code_dt, device=dev)
-        bins_rm = torch.empty((max(n_local, 1), _pad(F, 16)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
+        bins_rm = torch.empty((max(n_local, 1), code_row_width(F)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
         chunk_rows = max(1, min(chunk_rows, n_local))
         stage = [torch.empty((chunk_rows, F), dtype=torch.float64, device=dev) for _ in range(2)]
         copied = [torch.cuda.Event() for _ in range(2)]

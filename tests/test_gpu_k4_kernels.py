@@ -253,3 +253,28 @@ def test_tma_staging_real_labels(b2rf, oracle, cuda):
     finally:
         trainer.set_option("k4_tma", 0)
     assert_parity_allowing_ties(g, o, max_ties=4)
+
+
+@pytest.mark.parametrize("F", [12, 40, 70])
+def test_odd_code_row_widths(b2rf, oracle, cuda, monkeypatch, F):
+    """Code rows that are neither 64 nor 128 bytes (matrices the caller pre-binned, or more than 128 features): the limb kernel
+    stages them with one bulk async copy per row at a run-time width.  Forced here by padding rows to 16 bytes."""
+    from b2rf import trainer
+    monkeypatch.setattr(trainer, "CODE_ROW_ALIGN", 16)
+    assert trainer.code_row_width(F) == (F + 15) // 16 * 16
+    X, y, arity = b2rf.synth.c3(20000, device="cpu", F=F)
+    before = trainer.k4_launch_counts()
+    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=8, maxBins=64, numTrees=3, bootstrap=True, seed=5)
+    assert trainer.k4_launch_counts()["limb"] > before["limb"]
+    assert_parity_allowing_ties(g, o, max_ties=4)
+
+
+def test_more_than_128_features(b2rf, oracle, cuda):
+    """150 features: 160-byte code rows (default padding), TMA staging at a run-time width."""
+    from b2rf import trainer
+    assert trainer.code_row_width(150) == 160 and trainer.code_row_width(64) == 64 and trainer.code_row_width(65) == 128
+    X, y, arity = b2rf.synth.c3(12000, device="cpu", F=150)
+    before = trainer.k4_launch_counts()
+    g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=6, maxBins=32, numTrees=2, bootstrap=True, seed=1)
+    assert trainer.k4_launch_counts()["limb"] > before["limb"]
+    assert_parity_allowing_ties(g, o, max_ties=4)

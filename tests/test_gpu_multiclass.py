@@ -60,6 +60,41 @@ def test_multiclass_parity(b2rf, cuda, C, impurity, kw):
     assert (g.ncat > 0).any()
 
 
+@pytest.mark.parametrize("F,C,kw,staged", [
+    (50, 4, dict(maxDepth=5, maxBins=40, numTrees=6, bootstrap=True, seed=11), True),                                      # 64-byte code rows
+    (50, 3, dict(maxDepth=4, maxBins=64, numTrees=3, bootstrap=True, seed=5, featureSubsetStrategy="all"), True),          # two feature groups
+    (100, 5, dict(maxDepth=4, maxBins=36, numTrees=4, bootstrap=True, seed=2, featureSubsetStrategy="onethird"), True),    # 128-byte code rows
+    (70, 3, dict(maxDepth=4, maxBins=48, numTrees=3, bootstrap=True, seed=9), False),                                      # 80-byte rows: gather kernel
+])
+def test_multiclass_staged_histograms(b2rf, cuda, monkeypatch, F, C, kw, staged):
+    """The class-count kernel that stages code rows through shared memory (64- / 128-byte rows, labels in the row lists) and the
+    gather kernel behind it produce the oracle's forest; `k4_launch_counts` proves which one ran."""
+    from oracle import multiclass as M
+    if not staged:
+        monkeypatch.setattr(b2rf.trainer, "CODE_ROW_ALIGN", 16)    # code rows padded to 16 instead of 64 / 128
+    n = 6000                                                       # the root of every tree spans two 4096-row chunks
+    X, y, arity = _data(b2rf, n, C)
+    rng = np.random.default_rng(F)
+    extra = rng.normal(size=(n, F - X.shape[1]))
+    extra[:, ::3] = np.round(extra[:, ::3] * 2)                    # some columns with few distinct values
+    X = np.concatenate([X, extra], axis=1); arity = arity + [0] * extra.shape[1]
+    y = np.where(extra[:, 1] + extra[:, 2] > 0.8, (y + 1) % C, y)  # the added columns carry signal
+    po = np.array([0, 1500, 3000, 4500, 6000])
+    m = M.fit(X, y, arity, C, part_offsets=po, impurity="gini", **kw)
+    before = b2rf.trainer.k4_launch_counts()
+    g = b2rf.trainer.fit_tensors(torch.as_tensor(X, device=cuda), torch.as_tensor(y, device=cuda), arity,
+                                 b2rf.TreeParams(impurity="gini", numClasses=C, **kw), part_offsets=po, keep_trace=True)
+    after = b2rf.trainer.k4_launch_counts()
+    assert after["class_counts"] > before["class_counts"]
+    assert (after["class_staged"] > before["class_staged"]) == staged
+    if staged:
+        assert after["class_staged"] - before["class_staged"] == after["class_counts"] - before["class_counts"]
+    _parity(g, m)
+    mi = m.impurity >= 0
+    assert np.array_equal(g.impurity[mi], m.impurity[mi]) and np.array_equal(g.gain, m.gain)
+    assert (g.feature >= 33).any()
+
+
 def test_multiclass_label_check(b2rf, cuda):
     X = np.random.default_rng(0).normal(size=(60, 3)); y = np.arange(60) % 4.0
     with pytest.raises(b2rf.IllegalArgumentException, match="numClasses == 3"):
