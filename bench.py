@@ -246,6 +246,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: b2rf has no CPU fallback (use --impl reference for the CPU oracle)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    numa_node = trainer.bind_host_thread_to_gpu_node(dev) if world > 1 else None   # pinned e2e buffers on the GPU's own NUMA node
     dist = None
     if world > 1:
         import torch.distributed as dist
@@ -397,7 +398,7 @@ def main():
                          "note": "K4 is bound by shared-memory atomic throughput, not HBM: 22 bin updates (9 native 32-bit adds each; 7 for integer labels) per 37 "
                                  "algorithmic bytes; see DESIGN.md section 2 and profiles/"},
             "e2e": e2e, "cpu_baseline": cpu, "cpu_baseline_sklearn": skl, "mgpu_parity": mgpu_parity, "c4": c4,
-            "gpu_launches": gpu_launches,
+            "gpu_launches": gpu_launches, "host_numa_node_rank0": numa_node,
             "clocks": sampler.summary(),
         }
         print(json.dumps(line), flush=True)

@@ -40,4 +40,19 @@ __device__ __forceinline__ bool in_cat_mask(const uint32_t* masks, uint32_t aux,
 // plus a shared-memory compare-and-swap path and a returning global ATOM per call site.
 __device__ __forceinline__ void red_add_f64(double* p, double v) { asm volatile("red.global.add.f64 [%0], %1;" ::"l"(p), "d"(v) : "memory"); }
 
+// Gathers from the code matrices.  A plain LDG that misses L2 makes B200 fetch the whole 128-byte line from DRAM (measured,
+// scratch/ubench_gather.cu / profiles/r02_ubench_gather.md: a scattered 64-byte row costs 127 B of DRAM traffic, a single byte ~100 B);
+// the L2::64B prefetch-size qualifier (SASS LDG.E.LTC64B) halves that: 68 B per 64-byte row.  Read-only data (ld.global.nc).
+__device__ __forceinline__ uint4 ldg128_sparse(const void* p) {
+  uint4 v;
+  asm("ld.global.nc.L2::64B.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint32_t load_code_sparse(const void* base, size_t idx, int codeBytes) {
+  uint32_t v;
+  if (codeBytes == 2) { uint16_t h; asm("ld.global.nc.L2::64B.u16 %0, [%1];" : "=h"(h) : "l"(reinterpret_cast<const uint16_t*>(base) + idx)); v = h; }
+  else asm("ld.global.nc.L2::64B.u8 %0, [%1];" : "=r"(v) : "l"(reinterpret_cast<const uint8_t*>(base) + idx));
+  return v;
+}
+
 }  // namespace b2rf

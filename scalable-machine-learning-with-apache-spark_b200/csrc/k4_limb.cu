@@ -315,7 +315,7 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
         for (int q = 0; q < NPC; q++) {
           const int c = lane + 32 * q, row = c / CPR, seg = c - row * CPR;
           const uint32_t e2 = __shfl_sync(FULL, ent, row);
-          creg[q] = row < nvalid ? *reinterpret_cast<const uint4*>(bins_rm + (size_t)(e2 & 0x7ffffffu) * ldr + seg * 16) : make_uint4(0u, 0u, 0u, 0u);
+          creg[q] = row < nvalid ? ldg128_sparse(bins_rm + (size_t)(e2 & 0x7ffffffu) * ldr + seg * 16) : make_uint4(0u, 0u, 0u, 0u);
         }
       };
       uint32_t slowM[2] = {0u, 0u};

@@ -122,7 +122,7 @@ __global__ void __launch_bounds__(256) part_count_kernel(const PartLaunch p) {
     for (int i = tid; i < SEG_CH; i += 256) {
       bool left = false;
       if (i < n) {
-        const uint32_t bin = load_code(col, src[i] & 0x7ffffffu, p.codeBytes);
+        const uint32_t bin = load_code_sparse(col, src[i] & 0x7ffffffu, p.codeBytes);
         left = cat ? ((mask[bin >> 5] >> (bin & 31)) & 1u) : (bin <= d.aux);
       }
       const unsigned bal = __ballot_sync(0xffffffffu, left);

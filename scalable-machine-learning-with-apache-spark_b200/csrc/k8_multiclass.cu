@@ -183,7 +183,7 @@ __global__ void __launch_bounds__(384, 2) staged_hist_cls_kernel(const ClsHistLa
       for (int q = 0; q < NPC; q++) {
         const int c = lane + 32 * q, row = c / CPR, seg = c - row * CPR;
         const uint32_t e2 = __shfl_sync(FULL, ent, row);
-        creg[q] = row < nvalid ? *reinterpret_cast<const uint4*>(bins_rm + (size_t)(e2 & 0x7ffffffu) * LDR + seg * 16) : make_uint4(0u, 0u, 0u, 0u);
+        creg[q] = row < nvalid ? ldg128_sparse(bins_rm + (size_t)(e2 & 0x7ffffffu) * LDR + seg * 16) : make_uint4(0u, 0u, 0u, 0u);
       }
     };
     int b = warp;

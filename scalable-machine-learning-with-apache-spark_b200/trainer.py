@@ -249,6 +249,34 @@ def _check_labels(y, params, dist=None, group=None, device=None):
                                            f"TreeParams(numClasses=...) for more than two classes). Found invalid labels.")
 
 
+def bind_host_thread_to_gpu_node(device) -> int | None:
+    """Deployment helper for `fit_host` with several GPUs per host: restrict the calling thread (and the threads it starts later) to
+    the CPUs of the NUMA node the GPU hangs off, so that pinned host buffers allocated afterwards are placed on that node and the
+    host-to-device copies of the ranks do not all cross the inter-socket link.  Returns the node, or None when sysfs does not say
+    (single-socket hosts, containers without /sys/bus/pci) — then nothing is changed."""
+    import os
+    try:
+        pr = torch.cuda.get_device_properties(device)
+        addr = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        with open(f"/sys/bus/pci/devices/{addr}/numa_node") as f:
+            node = int(f.read().strip())
+        if node < 0:
+            return None
+        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+            txt = f.read().strip()
+        cpus = set()
+        for part in txt.split(","):
+            lo, _, hi = part.partition("-")
+            cpus.update(range(int(lo), int(hi or lo) + 1))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except (OSError, ValueError, AttributeError):
+        return None
+
+
 def k4_launch_counts() -> dict:
     """Launches of each K4 implementation by this process so far (b2rf_k4_launch_counts)."""
     c = np.zeros(6, np.int64)
