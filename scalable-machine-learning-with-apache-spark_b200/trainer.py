@@ -423,8 +423,9 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
     What is shared: the findSplits sample, thresholds and both bin matrices (once per distinct (maxBins, seed): findSplits
     depends on nothing else), the label vector, the device copy of X — and the histogram passes: the candidates' node-group
     loops run in lockstep, and each round's K4 is ONE launch whose task table spans the node slots of every candidate still
-    growing (b2rf_trainers_begin_group_shared), so a shallow candidate's few nodes ride with the deep one's.  What is not
-    shared: bag weights and row lists (MLlib draws bag counts row-major over numTrees, so they differ between candidates).
+    growing (b2rf_trainers_begin_group_shared), so a shallow candidate's few nodes ride with the deep one's.  Bag weights are drawn
+    once per distinct (seed, numTrees, subsamplingRate, bootstrap) — MLlib draws them row-major over numTrees, so candidates with
+    different numTrees differ, candidates that differ only in depth / bins / feature subsets do not.  Not shared: the row lists.
     Each candidate's forest is identical to what fit_tensors returns for it."""
     _require_cuda(X, "X")
     _require_cuda(y, "y")
@@ -436,6 +437,7 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
         n_local, F = X.shape
         ld = _pad(n_local)
         shared = {}
+        bags = {}
         cands = []
         main = torch.cuda.current_stream()
         for params in params_list:
@@ -454,8 +456,17 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
                 _raise_bin_errors(S["arity_d"], S["dist"], group)
                 shared[key] = (thr.cpu().numpy(), ns.cpu().numpy(), bins, bins_rm)
             thr_h, ns_h, bins, bins_rm = shared[key]
-            w, node = bag(params.seed, S["po"], S["part0"], params.numTrees, params.subsamplingRate, params.bootstrap, dev, ld=ld,
-                          want_node=_want_node(hist_mode, bins_rm, n_local))
+            # bag counts depend on (seed, numTrees, rate, bootstrap) and the partition layout only: candidates that differ in depth,
+            # bins or feature subsets share one weight matrix (read-only after bind; the node cache of the scan modes is per candidate)
+            want_node = _want_node(hist_mode, bins_rm, n_local)
+            bkey = (params.seed, params.numTrees, float(params.subsamplingRate), bool(params.bootstrap))
+            if want_node or bkey not in bags:
+                w, node = bag(params.seed, S["po"], S["part0"], params.numTrees, params.subsamplingRate, params.bootstrap, dev, ld=ld,
+                              want_node=want_node)
+                if not want_node:
+                    bags[bkey] = w
+            else:
+                w, node = bags[bkey], None
             cands.append(dict(S=S, params=params, thr_h=thr_h, ns_h=ns_h, bins=bins, bins_rm=bins_rm, w=w, node=node, h=C.c_void_p()))
         torch.cuda.synchronize(dev)
         try:
