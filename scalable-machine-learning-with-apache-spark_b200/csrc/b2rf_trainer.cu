@@ -11,6 +11,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <atomic>
+#include <functional>
 #include <mutex>
 #include <thread>
 #include <string>
@@ -235,7 +236,6 @@ struct b2rf_trainer {
   std::vector<int32_t> cellBins, kind;
   std::vector<double> clsPool;
   std::vector<int64_t> drawCells;    // histogram cells of a draw's features
-  std::vector<double> x_cls;         // flat export: [node][C]
   std::vector<double> thresholds;  // [F][maxSplits]
   int64_t allBins = 0;
 
@@ -340,9 +340,9 @@ struct b2rf_trainer {
 
   // flat export cache
   bool exported = false;
-  std::vector<int64_t> x_tree_off;
-  std::vector<int32_t> x_feature, x_left, x_right, x_ncat, x_cat_off, x_cat_len;
-  std::vector<double> x_threshold, x_prediction, x_impurity, x_gain, x_stats, x_cats;
+  struct TreePlan { std::vector<uint8_t> leaf; std::vector<double> pred; std::vector<int32_t> sz, csz; };   // export pass 1 (see export_plan)
+  std::vector<TreePlan> x_plan;
+  std::vector<int64_t> x_tree_off, x_cat_base;
 
   ~b2rf_trainer() {
     dn.release(); dnUpd.release(); dCat.release(); dSlotFo.release(); dSlotBase.release(); dParent.release();
@@ -1108,30 +1108,36 @@ int b2rf_trainer_stats(const b2rf_trainer* t, double* h_seconds5, int64_t* h_cou
 
 // LearningNode.toNode(prune = true): pre-order flattening; an internal node whose children are leaves with equal predictions
 // collapses into a leaf.  Two passes per tree, trees in parallel on a few host threads:
-//   1. bottom-up over the node vector (children always sit behind their parent): does the node end up a leaf, its prediction, the
-//      size of its flattened subtree and of its category lists;
-//   2. pre-order walk with an explicit stack that writes every field straight into the forest-wide arrays (node i of a subtree at
-//      position p has its left child at p + 1 and its right child at p + 1 + size(left)).
-static void do_export(b2rf_trainer* t) {
-  if (t->exported) return;
+//   1. (export_plan, cached) bottom-up over the node vector (children always sit behind their parent): does the node end up a leaf,
+//      its prediction, the size of its flattened subtree and of its category lists; tree and category offsets of the forest;
+//   2. (export_write) pre-order walk with an explicit stack that writes every field straight into the CALLER's arrays (node i of a
+//      subtree at position p has its left child at p + 1 and its right child at p + 1 + size(left)); any array may be nullptr.
+struct ExportOut {
+  int32_t* feature; double* threshold; int32_t* left; int32_t* right; double* prediction; double* impurity; double* gain; double* stats4;
+  int32_t* ncat; int32_t* cat_off; int32_t* cat_len; double* cats; double* cls;   // cls: [node][C] class counts (multiclass) or [node][2] (binary)
+};
+
+static void export_parallel(const b2rf_trainer* t, const std::function<void(int)>& fn) {
   const int T = t->T;
-  struct TreePlan { std::vector<uint8_t> leaf; std::vector<double> pred; std::vector<int32_t> sz, csz; };
-  std::vector<TreePlan> plan(T);
   size_t total = 0;
   for (int tr = 0; tr < T; tr++) total += t->trees[tr].size();
   const int workers = (int)std::max<size_t>(1, std::min<size_t>({(size_t)T, (size_t)8, total / 4096 + 1}));
-  auto run_parallel = [&](auto&& fn) {
-    std::atomic<int> next{0};
-    auto work = [&]() { for (int tr = next.fetch_add(1); tr < T; tr = next.fetch_add(1)) fn(tr); };
-    std::vector<std::thread> pool;
-    for (int w = 1; w < workers; w++) pool.emplace_back(work);
-    work();
-    for (auto& th : pool) th.join();
-  };
-  run_parallel([&](int tr) {
+  std::atomic<int> next{0};
+  auto work = [&]() { for (int tr = next.fetch_add(1); tr < T; tr = next.fetch_add(1)) fn(tr); };
+  std::vector<std::thread> pool;
+  for (int w = 1; w < workers; w++) pool.emplace_back(work);
+  work();
+  for (auto& th : pool) th.join();
+}
+
+static void export_plan(b2rf_trainer* t) {
+  if (t->exported) return;
+  const int T = t->T;
+  t->x_plan.assign(T, {});
+  export_parallel(t, [&](int tr) {
     const std::vector<HNode>& nodes = t->trees[tr];
     const int n = (int)nodes.size();
-    TreePlan& p = plan[tr];
+    b2rf_trainer::TreePlan& p = t->x_plan[tr];
     p.leaf.resize(n); p.pred.resize(n); p.sz.resize(n); p.csz.resize(n);
     for (int i = n - 1; i >= 0; i--) {
       const HNode& nd = nodes[i];
@@ -1144,18 +1150,22 @@ static void do_export(b2rf_trainer* t) {
     }
   });
   t->x_tree_off.assign(T + 1, 0);
-  std::vector<int64_t> catBase(T + 1, 0);
-  for (int tr = 0; tr < T; tr++) { t->x_tree_off[tr + 1] = t->x_tree_off[tr] + plan[tr].sz[0]; catBase[tr + 1] = catBase[tr] + plan[tr].csz[0]; }
-  const size_t N = (size_t)t->x_tree_off[T];
-  t->x_feature.assign(N, -1); t->x_left.assign(N, -1); t->x_right.assign(N, -1); t->x_ncat.assign(N, 0); t->x_cat_off.assign(N, 0); t->x_cat_len.assign(N, 0);
-  t->x_threshold.assign(N, 0.0); t->x_prediction.assign(N, 0.0); t->x_impurity.assign(N, 0.0); t->x_gain.assign(N, 0.0);
-  t->x_stats.resize(N * 4); t->x_cats.resize((size_t)catBase[T]);
-  if (t->C) t->x_cls.resize(N * (size_t)t->C); else t->x_cls.clear();
-  run_parallel([&](int tr) {
+  t->x_cat_base.assign(T + 1, 0);
+  for (int tr = 0; tr < T; tr++) {
+    t->x_tree_off[tr + 1] = t->x_tree_off[tr] + t->x_plan[tr].sz[0];
+    t->x_cat_base[tr + 1] = t->x_cat_base[tr] + t->x_plan[tr].csz[0];
+  }
+  t->exported = true;
+}
+
+static void export_write(b2rf_trainer* t, const ExportOut& o) {
+  export_plan(t);
+  const int C = t->C;
+  export_parallel(t, [&](int tr) {
     const std::vector<HNode>& nodes = t->trees[tr];
-    const TreePlan& p = plan[tr];
+    const b2rf_trainer::TreePlan& p = t->x_plan[tr];
     const size_t base = (size_t)t->x_tree_off[tr];
-    int64_t catAt = catBase[tr];
+    int64_t catAt = t->x_cat_base[tr];
     std::vector<std::pair<int32_t, int32_t>> stack;   // (node index, tree-local flat position)
     stack.reserve(64);
     stack.push_back({0, 0});
@@ -1164,35 +1174,42 @@ static void do_export(b2rf_trainer* t) {
       stack.pop_back();
       const HNode& nd = nodes[ni];
       const size_t at = base + (size_t)pos;
-      for (int q = 0; q < 4; q++) t->x_stats[at * 4 + q] = nd.stats.calc[q];
-      if (t->C) for (int k = 0; k < t->C; k++) t->x_cls[at * (size_t)t->C + k] = nd.cls >= 0 ? t->clsPool[(size_t)nd.cls + k] : 0.0;
-      t->x_cat_off[at] = (int32_t)catAt;
-      t->x_prediction[at] = p.pred[ni];
-      if (nd.left < 0) { t->x_impurity[at] = nd.stats.valid ? nd.stats.impurity : -1.0; continue; }   // a leaf of the learned tree
-      t->x_impurity[at] = nd.stats.impurity;
-      if (p.leaf[ni]) continue;                                                                       // collapsed by the prune rule
-      const int l = nd.left, r = l + 1;
-      t->x_feature[at] = nd.feature; t->x_left[at] = pos + 1; t->x_right[at] = pos + 1 + p.sz[l];
-      t->x_threshold[at] = nd.threshold; t->x_gain[at] = nd.stats.gain;
-      if (nd.catMaskIdx >= 0) {
-        t->x_ncat[at] = t->arity[nd.feature];
-        const uint32_t* m = &t->catPool[(size_t)nd.catMaskIdx * t->maskWords];
-        int cnt = 0;
-        for (int c = 0; c < t->maskWords * 32; c++) if ((m[c >> 5] >> (c & 31)) & 1u) { t->x_cats[(size_t)catAt++] = (double)c; cnt++; }
-        t->x_cat_len[at] = cnt;
+      if (o.stats4) for (int q = 0; q < 4; q++) o.stats4[at * 4 + q] = nd.stats.calc[q];
+      if (o.cls) {
+        if (C) for (int k = 0; k < C; k++) o.cls[at * (size_t)C + k] = nd.cls >= 0 ? t->clsPool[(size_t)nd.cls + k] : 0.0;
+        else { o.cls[at * 2] = nd.stats.calc[0] - nd.stats.calc[1]; o.cls[at * 2 + 1] = nd.stats.calc[1]; }
       }
+      const bool learnedLeaf = nd.left < 0, internal = !learnedLeaf && !p.leaf[ni];
+      if (o.cat_off) o.cat_off[at] = (int32_t)catAt;
+      if (o.prediction) o.prediction[at] = p.pred[ni];
+      if (o.impurity) o.impurity[at] = learnedLeaf ? (nd.stats.valid ? nd.stats.impurity : -1.0) : nd.stats.impurity;
+      const int l = nd.left, r = l + 1;
+      if (o.feature) o.feature[at] = internal ? nd.feature : -1;
+      if (o.left) o.left[at] = internal ? pos + 1 : -1;
+      if (o.right) o.right[at] = internal ? pos + 1 + p.sz[l] : -1;
+      if (o.threshold) o.threshold[at] = internal ? nd.threshold : 0.0;
+      if (o.gain) o.gain[at] = internal ? nd.stats.gain : 0.0;
+      int cnt = 0, ncat = 0;
+      if (internal && nd.catMaskIdx >= 0) {
+        ncat = t->arity[nd.feature];
+        const uint32_t* m = &t->catPool[(size_t)nd.catMaskIdx * t->maskWords];
+        for (int q = 0; q < t->maskWords; q++)
+          for (uint32_t w = m[q]; w; w &= w - 1u) { if (o.cats) o.cats[(size_t)catAt] = (double)(q * 32 + __builtin_ctz(w)); catAt++; cnt++; }
+      }
+      if (o.ncat) o.ncat[at] = ncat;
+      if (o.cat_len) o.cat_len[at] = cnt;
+      if (!internal) continue;
       stack.push_back({r, pos + 1 + p.sz[l]});   // right first: the left subtree is popped (and its category lists placed) before it
       stack.push_back({l, pos + 1});
     }
   });
-  t->exported = true;
 }
 
 int b2rf_trainer_forest_sizes(b2rf_trainer* t, int64_t* n_nodes, int64_t* n_cats) {
   if (!t) return B2RF_ERR_ARG;
-  do_export(t);
-  if (n_nodes) *n_nodes = (int64_t)t->x_feature.size();
-  if (n_cats) *n_cats = (int64_t)t->x_cats.size();
+  export_plan(t);
+  if (n_nodes) *n_nodes = t->x_tree_off[t->T];
+  if (n_cats) *n_cats = t->x_cat_base[t->T];
   return B2RF_OK;
 }
 
@@ -1200,15 +1217,10 @@ int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature
                         double* h_prediction, double* h_impurity, double* h_gain, double* h_stats4, int32_t* h_ncat, int32_t* h_cat_off,
                         int32_t* h_cat_len, double* h_cats) {
   if (!t) return B2RF_ERR_ARG;
-  do_export(t);
-  const size_t n = t->x_feature.size();
-  memcpy(h_tree_off, t->x_tree_off.data(), t->x_tree_off.size() * 8);
-  memcpy(h_feature, t->x_feature.data(), n * 4); memcpy(h_threshold, t->x_threshold.data(), n * 8);
-  memcpy(h_left, t->x_left.data(), n * 4); memcpy(h_right, t->x_right.data(), n * 4);
-  memcpy(h_prediction, t->x_prediction.data(), n * 8); memcpy(h_impurity, t->x_impurity.data(), n * 8); memcpy(h_gain, t->x_gain.data(), n * 8);
-  memcpy(h_stats4, t->x_stats.data(), n * 32);
-  memcpy(h_ncat, t->x_ncat.data(), n * 4); memcpy(h_cat_off, t->x_cat_off.data(), n * 4); memcpy(h_cat_len, t->x_cat_len.data(), n * 4);
-  if (!t->x_cats.empty()) memcpy(h_cats, t->x_cats.data(), t->x_cats.size() * 8);
+  export_plan(t);
+  if (h_tree_off) memcpy(h_tree_off, t->x_tree_off.data(), t->x_tree_off.size() * 8);
+  ExportOut o{h_feature, h_threshold, h_left, h_right, h_prediction, h_impurity, h_gain, h_stats4, h_ncat, h_cat_off, h_cat_len, h_cats, nullptr};
+  export_write(t, o);
   return B2RF_OK;
 }
 
@@ -1217,10 +1229,9 @@ int b2rf_trainer_num_classes(const b2rf_trainer* t) { return t ? (t->C ? t->C : 
 int b2rf_trainer_export_class_counts(b2rf_trainer* t, double* h_counts) {
   if (!t || !h_counts) { set_error("b2rf_trainer_export_class_counts: bad argument"); return B2RF_ERR_ARG; }
   if (t->p.impurity == 0) { set_error("b2rf_trainer_export_class_counts: this trainer fits a regression forest"); return B2RF_ERR_STATE; }
-  do_export(t);
-  const size_t n = t->x_feature.size();
-  if (t->C) memcpy(h_counts, t->x_cls.data(), n * (size_t)t->C * 8);
-  else for (size_t i = 0; i < n; i++) { h_counts[i * 2] = t->x_stats[i * 4] - t->x_stats[i * 4 + 1]; h_counts[i * 2 + 1] = t->x_stats[i * 4 + 1]; }
+  ExportOut o{};
+  o.cls = h_counts;
+  export_write(t, o);
   return B2RF_OK;
 }
 

@@ -622,8 +622,8 @@ def _export(h, F: int, keep_trace: bool) -> Forest:
     L.b2rf_trainer_stats(h, sec.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p))
     T = None
     # number of trees = len(tree_off) - 1; query through a first export of tree_off sized generously
-    def Z(shape, dt):
-        return np.zeros(shape, dt)
+    def Z(shape, dt):      # every element is written by the export calls below
+        return np.empty(shape, dt)
     # the trainer knows T; tree_off has T+1 entries <= n+1
     tree_off = Z(n + 2, np.int64)
     feature, left, right = Z(n, np.int32), Z(n, np.int32), Z(n, np.int32)
