@@ -140,6 +140,20 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins, int64_t ldb, const vo
 int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream);
 /* K5 binsToBestSplit (row a8) on the (reduced) histogram, then the driver tail (row a9).  Synchronises the stream. */
 int b2rf_trainer_end_group(b2rf_trainer* t, void* stream);
+/* Rows sharded over `world` processes (reference: the reduceByKey + collectAsMap between the partition aggregates and
+ * the driver in RandomForest.findBestSplits — MLlib also reduces BY NODE and finds each node's best split on the executor that owns
+ * the node, sending only the split back): call b2rf_trainer_set_shard after create and before max_group_cells / bind.  A group's
+ * node slots are then cut into `world` ranges of equal slot count and the histogram buffer is laid out as `world` chunks of equal
+ * size (begin_group's *n_cells = world * chunk; padding cells stay zero), rank r's slots in chunk r.  Per group the caller does
+ *   begin_group; reduce-scatter d_hist (sum; chunk r -> rank r, in place: recv = d_hist + r * chunk * 4 doubles);
+ *   n = b2rf_trainer_shard_block_doubles(t); b2rf_trainer_end_group_shard_launch(t, d_block [n doubles], stream)   -- K5 on the own slots
+ *   all-gather d_block -> d_blocks (world * n doubles); b2rf_trainer_end_group_shard_finish(t, d_blocks, stream)     -- driver tail on every rank
+ * instead of all-reduce + b2rf_trainer_end_group (which still works on the padded layout: every rank then runs K5 on all slots).
+ * Segment mode only; in the other modes set_shard changes nothing and shard_block_doubles returns 0. */
+int b2rf_trainer_set_shard(b2rf_trainer* t, int32_t rank, int32_t world);
+int64_t b2rf_trainer_shard_block_doubles(const b2rf_trainer* t);
+int b2rf_trainer_end_group_shard_launch(b2rf_trainer* t, void* d_block, void* stream);
+int b2rf_trainer_end_group_shard_finish(b2rf_trainer* t, const void* d_blocks, void* stream);
 /* fitMultiple shared passes (reference: CrossValidator around the tree estimator, `ML 07 - Random Forests and
  * Hyperparameter Tuning.py:74-77,143-149`): the candidates of one fold are separate trainers bound to the SAME bin matrices.
  * b2rf_trainers_begin_group_shared = begin_group of every listed trainer (started[i] = 1 / 0, n_cells[i] as there) with ONE K4

@@ -58,6 +58,10 @@ _SIGS = {
     "b2rf_trainer_trace_size": (i64, [vp]),
     "b2rf_trainer_trace": (C.c_int, [vp, vp, vp]),
     "b2rf_k4_launch_counts": (C.c_int, [vp, i32]),
+    "b2rf_trainer_set_shard": (C.c_int, [vp, i32, i32]),
+    "b2rf_trainer_shard_block_doubles": (i64, [vp]),
+    "b2rf_trainer_end_group_shard_launch": (C.c_int, [vp, vp, vp]),
+    "b2rf_trainer_end_group_shard_finish": (C.c_int, [vp, vp, vp]),
     "b2rf_trainer_group_info": (C.c_int, [vp] * 6),
     "b2rf_trainers_begin_group_shared": (C.c_int, [vp, i32, vp, vp, vp]),
     "b2rf_trainers_end_group_shared": (C.c_int, [vp, i32, vp]),

@@ -249,6 +249,12 @@ struct b2rf_trainer {
   const uint8_t* d_bins_rm = nullptr; int64_t ldr = 0;   // optional row-major twin of the bin matrix => bucket mode
   bool bucketMode = false;
   bool segMode = false;   // bucket mode with per-tree row lists kept partitioned by node (default); else per-group counting sort
+  // rows sharded over `world` processes (b2rf_trainer_set_shard): a group's node slots are cut into `world` contiguous ranges of
+  // shardSpr slots, rank r's range starts at cell r * shardChunk of the histogram buffer (reduce-scatter by node), K5 runs on the
+  // own range only and the split records travel through an all-gather (b2rf_trainer_end_group_shard_launch / _finish)
+  int32_t shardRank = 0, shardWorld = 1;
+  int64_t shardSpr = 0, shardChunk = 0;        // block capacity in slots (largest range), cells per chunk
+  std::vector<int64_t> shardLo;                // [world + 1] first slot of every rank's range
   int32_t chunkRows = 4096;
 
   // host trees + scheduler
@@ -483,7 +489,9 @@ int64_t b2rf_trainer_max_group_cells(const b2rf_trainer* t) {
   // admitted MLlib bins <= maxMem / (statsSize * 8) + one node; an unordered feature can hold up to 2x more cells than bins (arity 2)
   const int64_t byMem = (maxMem / (statsSize * 8)) * (t->C ? 2 : 1) + worstNode;
   const int64_t maxNodesTotal = (int64_t)t->T << std::min(t->p.maxDepth, 24);
-  return t->M * std::max<int64_t>(worstNode, std::min<int64_t>(byMem, maxNodesTotal * worstNode));   // in units of 4 doubles
+  // sharded layout: every rank's range is padded to the largest one (< one node more per rank)
+  const int64_t pad = t->shardWorld > 1 ? (int64_t)t->shardWorld * worstNode : 0;
+  return t->M * (std::max<int64_t>(worstNode, std::min<int64_t>(byMem, maxNodesTotal * worstNode)) + pad);   // in units of 4 doubles
 }
 
 int b2rf_trainer_code_bytes(const b2rf_trainer* t) { return t ? t->codeBytes : 0; }
@@ -702,6 +710,34 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
     mem += nodeMem;
   }
   const size_t nSlots = t->group.size();
+  t->shardSpr = 0; t->shardChunk = 0;
+  if (t->shardWorld > 1 && t->segMode) {
+    // reduce-scatter by node: contiguous slot ranges of balanced CELL counts (a range ends with the first slot that carries its prefix
+    // past r/W of the group's cells, so no range exceeds cells / W by more than one node), every range padded to the largest one
+    const int64_t W = t->shardWorld;
+    t->shardLo.assign((size_t)W + 1, (int64_t)nSlots);
+    t->shardLo[0] = 0;
+    {
+      int64_t r = 1;
+      for (size_t sl = 0; sl < nSlots && r < W; sl++) {
+        const int64_t end = sl + 1 < nSlots ? slotBase[sl + 1] : cells;     // cells up to and including slot sl
+        while (r < W && end * W >= r * cells) t->shardLo[(size_t)r++] = (int64_t)sl + 1;
+      }
+    }
+    int64_t chunk = 0, spr = 0;
+    for (int64_t r = 0; r < W; r++) {
+      const int64_t lo = t->shardLo[(size_t)r], hi = t->shardLo[(size_t)r + 1];
+      if (hi > lo) chunk = std::max(chunk, (hi < (int64_t)nSlots ? slotBase[hi] : cells) - slotBase[lo]);
+      spr = std::max(spr, hi - lo);
+    }
+    for (int64_t r = W - 1; r >= 0; r--) {
+      const int64_t lo = t->shardLo[(size_t)r], hi = t->shardLo[(size_t)r + 1];
+      const int64_t first = hi > lo ? slotBase[lo] : 0;
+      for (int64_t sl = lo; sl < hi; sl++) slotBase[sl] = r * chunk + (slotBase[sl] - first);
+    }
+    cells = W * chunk;
+    t->shardSpr = spr; t->shardChunk = chunk;
+  }
   if (cells * t->M > t->histCells) { set_error("b2rf_trainer_begin_group: histogram buffer too small for this node group"); return B2RF_ERR_ARG; }
   t->groupCells = cells;
 
@@ -856,28 +892,35 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
 }  // extern "C"
 
 // end_group, first half: K5 + the copies of its results, all asynchronous on the stream.
-static int end_group_launch(b2rf_trainer* t, cudaStream_t s) {
-  const size_t nSlots = t->group.size();
-  // ---- K5 ----
+// K5 over the node slots [lo, lo + cnt) of the group in flight (the whole group unless the fit is sharded): every per-slot array is
+// passed from its lo-th entry, so the kernels see an ordinary group of cnt slots.
+static int end_group_k5(b2rf_trainer* t, cudaStream_t s, size_t lo, size_t cnt) {
+  if (cnt == 0) return B2RF_OK;
   SplitLaunch a;
-  a.hist = t->d_hist; a.slot_fo = t->dSlotFo.p; a.slot_base = t->dSlotBase.p; a.Fsub = t->Fsub; a.nSlots = (int32_t)nSlots;
-  a.parent4 = t->dParent.p; a.hasParent = t->dHasParent.p; a.numBins = t->dNumBins.p; a.isCat = t->dIsCat.p;
+  a.hist = t->d_hist; a.slot_fo = t->dSlotFo.p + lo * t->Fsub; a.slot_base = t->dSlotBase.p + lo; a.Fsub = t->Fsub; a.nSlots = (int32_t)cnt;
+  a.parent4 = t->dParent.p + lo * 4; a.hasParent = t->dHasParent.p + lo; a.numBins = t->dNumBins.p; a.isCat = t->dIsCat.p;
   a.minInstances = (double)t->p.minInstancesPerNode; a.minWeight = t->minWeightPerNode; a.minInfoGain = t->p.minInfoGain;
-  a.out = t->dRec.p; a.catmask_out = t->dRecMask.p; a.maskWords = t->maskWords; a.impurity = t->p.impurity;
+  a.out = t->dRec.p + lo; a.catmask_out = t->dRecMask.p + lo * t->maskWords; a.maskWords = t->maskWords; a.impurity = t->p.impurity;
   a.maxB = *std::max_element(t->cellBins.begin(), t->cellBins.end());
   a.allHaveParent = 1;
-  for (size_t sl = 0; sl < nSlots; sl++) if (!t->hHasParent.p[sl]) { a.allHaveParent = 0; break; }
+  for (size_t sl = lo; sl < lo + cnt; sl++) if (!t->hHasParent.p[sl]) { a.allHaveParent = 0; break; }
   if (t->C) {
     ClsSplitLaunch c;
-    c.hist = t->d_hist; c.slot_fo = t->dSlotFo.p; c.slot_base = t->dSlotBase.p; c.Fsub = t->Fsub; c.nSlots = (int32_t)nSlots;
-    c.parentCls = t->dParentCls.p; c.hasParent = t->dHasParent.p; c.cellBins = t->dCellBins.p; c.kind = t->dKind.p;
+    c.hist = t->d_hist; c.slot_fo = a.slot_fo; c.slot_base = a.slot_base; c.Fsub = t->Fsub; c.nSlots = (int32_t)cnt;
+    c.parentCls = t->dParentCls.p + lo * t->Cp; c.hasParent = a.hasParent; c.cellBins = t->dCellBins.p; c.kind = t->dKind.p;
     c.minInstances = a.minInstances; c.minWeight = a.minWeight; c.minInfoGain = a.minInfoGain;
-    c.out = t->dRec.p; c.clsOut = t->dClsOut.p; c.catmask_out = t->dRecMask.p;
+    c.out = a.out; c.clsOut = t->dClsOut.p + lo * 3 * t->Cp; c.catmask_out = a.catmask_out;
     c.maxB = a.maxB; c.maskWords = t->maskWords; c.impurity = t->p.impurity; c.C = t->C; c.Cp = t->Cp; c.M = t->M;
     if (!cuda_ok(launch_best_split_cls(c, s), "best_split_cls launch")) return B2RF_ERR_CUDA;
-    if (!cuda_ok(cudaMemcpyAsync(t->hClsOut.p, t->dClsOut.p, nSlots * 3 * t->Cp * 8, cudaMemcpyDeviceToHost, s), "download class counts")) return B2RF_ERR_CUDA;
   } else if (!cuda_ok(launch_best_split(a, s), "best_split launch")) return B2RF_ERR_CUDA;
   t->nKernels++;
+  return B2RF_OK;
+}
+
+// The copies of K5's results for all slots of the group (asynchronous on the stream), plus host work that overlaps them.
+static int end_group_download(b2rf_trainer* t, cudaStream_t s) {
+  const size_t nSlots = t->group.size();
+  if (t->C && !cuda_ok(cudaMemcpyAsync(t->hClsOut.p, t->dClsOut.p, nSlots * 3 * t->Cp * 8, cudaMemcpyDeviceToHost, s), "download class counts")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpyAsync(t->hRec.p, t->dRec.p, nSlots * sizeof(SplitRec), cudaMemcpyDeviceToHost, s), "download split records")) return B2RF_ERR_CUDA;
   if (!cuda_ok(cudaMemcpyAsync(t->hRecMask.p, t->dRecMask.p, nSlots * t->maskWords * 4, cudaMemcpyDeviceToHost, s), "download split masks")) return B2RF_ERR_CUDA;
   const double tw0 = now_s();
@@ -889,6 +932,37 @@ static int end_group_launch(b2rf_trainer* t, cudaStream_t s) {
   }
   t->tWait -= tw0;   // completed by end_group_tail
   return B2RF_OK;
+}
+
+// end_group, first half: K5 + the copies of its results, all asynchronous on the stream.
+static int end_group_launch(b2rf_trainer* t, cudaStream_t s) {
+  { const int rc = end_group_k5(t, s, 0, t->group.size()); if (rc) return rc; }
+  return end_group_download(t, s);
+}
+
+// ---- sharded K5: the records of the own slot range are packed into one block, all-gathered by the caller, and unpacked ----
+static size_t shard_block_bytes(const b2rf_trainer* t) {
+  const size_t perSlot = sizeof(SplitRec) + (size_t)t->maskWords * 4 + (t->C ? (size_t)3 * t->Cp * 8 : 0);
+  return ((size_t)t->shardSpr * perSlot + 7) / 8 * 8;
+}
+
+constexpr int SHARD_MAX_WORLD = 64;
+struct ShardRanges { int32_t world; int32_t lo[SHARD_MAX_WORLD + 1]; };
+
+__global__ void unpack_records_kernel(const uint32_t* x, int64_t blockWords, int64_t spr, int64_t nSlots, ShardRanges rg, int recW, int maskW, int clsW,
+                                      uint32_t* rec, uint32_t* mask, uint32_t* cls) {
+  const int perSlot = recW + maskW + clsW;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nSlots * perSlot; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t sl = i / perSlot;
+    const int w = (int)(i - sl * perSlot);
+    int r = 0;
+    while (r + 1 < rg.world && sl >= rg.lo[r + 1]) r++;
+    const int64_t k = sl - rg.lo[r];
+    const uint32_t* b = x + (int64_t)r * blockWords;           // [spr x rec][spr x mask][spr x cls]
+    if (w < recW) rec[sl * recW + w] = b[k * recW + w];
+    else if (w < recW + maskW) mask[sl * maskW + (w - recW)] = b[spr * recW + k * maskW + (w - recW)];
+    else cls[sl * clsW + (w - recW - maskW)] = b[spr * (recW + maskW) + k * clsW + (w - recW - maskW)];
+  }
 }
 
 // end_group, second half (after the stream has been synchronised): driver tail + K6 partitions.
@@ -999,6 +1073,56 @@ int b2rf_trainer_end_group(b2rf_trainer* t, void* stream) {
   if (!t || !t->inGroup) { set_error("b2rf_trainer_end_group: no group in flight"); return B2RF_ERR_STATE; }
   cudaStream_t s = (cudaStream_t)stream;
   { const int rc = end_group_launch(t, s); if (rc) return rc; }
+  if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
+  return end_group_tail(t, s);
+}
+
+// ---- rows sharded over several processes: reduce-scatter by node, K5 on the own slots, all-gather of the split records ----
+int b2rf_trainer_set_shard(b2rf_trainer* t, int32_t rank, int32_t world) {
+  if (!t || world < 1 || world > SHARD_MAX_WORLD || rank < 0 || rank >= world) { set_error("b2rf_trainer_set_shard: bad argument (1 <= world <= 64)"); return B2RF_ERR_ARG; }
+  if (t->d_bins) { set_error("b2rf_trainer_set_shard: call before b2rf_trainer_bind (the histogram buffer is sized for the padded layout)"); return B2RF_ERR_STATE; }
+  t->shardRank = rank; t->shardWorld = world;
+  return B2RF_OK;
+}
+
+int64_t b2rf_trainer_shard_block_doubles(const b2rf_trainer* t) {
+  if (!t || !t->inGroup || t->shardSpr <= 0) return 0;
+  return (int64_t)(shard_block_bytes(t) / 8);
+}
+
+int b2rf_trainer_end_group_shard_launch(b2rf_trainer* t, void* d_block, void* stream) {
+  if (!t || !t->inGroup) { set_error("b2rf_trainer_end_group_shard_launch: no group in flight"); return B2RF_ERR_STATE; }
+  if (t->shardSpr <= 0 || !d_block) { set_error("b2rf_trainer_end_group_shard_launch: the group was not laid out for sharding (b2rf_trainer_set_shard, segment mode)"); return B2RF_ERR_STATE; }
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t spr = (size_t)t->shardSpr;
+  const size_t lo = (size_t)t->shardLo[(size_t)t->shardRank], cnt = (size_t)t->shardLo[(size_t)t->shardRank + 1] - lo;
+  { const int rc = end_group_k5(t, s, lo, cnt); if (rc) return rc; }
+  unsigned char* b = static_cast<unsigned char*>(d_block);
+  const size_t recB = sizeof(SplitRec), maskB = (size_t)t->maskWords * 4, clsB = t->C ? (size_t)3 * t->Cp * 8 : 0;
+  bool ok = true;
+  if (cnt) {
+    ok &= cuda_ok(cudaMemcpyAsync(b, t->dRec.p + lo, cnt * recB, cudaMemcpyDeviceToDevice, s), "pack split records");
+    ok &= cuda_ok(cudaMemcpyAsync(b + spr * recB, t->dRecMask.p + lo * t->maskWords, cnt * maskB, cudaMemcpyDeviceToDevice, s), "pack split masks");
+    if (clsB) ok &= cuda_ok(cudaMemcpyAsync(b + spr * (recB + maskB), t->dClsOut.p + lo * 3 * t->Cp, cnt * clsB, cudaMemcpyDeviceToDevice, s), "pack class counts");
+  }
+  return ok ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+int b2rf_trainer_end_group_shard_finish(b2rf_trainer* t, const void* d_blocks, void* stream) {
+  if (!t || !t->inGroup || t->shardSpr <= 0 || !d_blocks) { set_error("b2rf_trainer_end_group_shard_finish: no sharded group in flight"); return B2RF_ERR_STATE; }
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t nSlots = t->group.size();
+  const int recW = (int)(sizeof(SplitRec) / 4), maskW = t->maskWords, clsW = t->C ? 3 * t->Cp * 2 : 0;
+  const int64_t total = (int64_t)nSlots * (recW + maskW + clsW);
+  const int grid = (int)std::min<int64_t>((total + 255) / 256, 4096);
+  ShardRanges rg;
+  rg.world = t->shardWorld;
+  for (int r = 0; r <= t->shardWorld; r++) rg.lo[r] = (int32_t)t->shardLo[(size_t)r];
+  unpack_records_kernel<<<grid, 256, 0, s>>>(static_cast<const uint32_t*>(d_blocks), (int64_t)(shard_block_bytes(t) / 4), t->shardSpr, (int64_t)nSlots, rg, recW, maskW,
+                                               clsW, reinterpret_cast<uint32_t*>(t->dRec.p), t->dRecMask.p, reinterpret_cast<uint32_t*>(t->dClsOut.p));
+  if (!cuda_ok(cudaGetLastError(), "unpack split records")) return B2RF_ERR_CUDA;
+  t->nKernels++;
+  { const int rc = end_group_download(t, s); if (rc) return rc; }
   if (!cuda_ok(cudaStreamSynchronize(s), "group synchronize")) return B2RF_ERR_CUDA;
   return end_group_tail(t, s);
 }

@@ -311,8 +311,15 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
     check(L.b2rf_trainer_create(C.byref(S["cp"]), F, S["arity_np"].ctypes.data_as(C.c_void_p), ns_h.ctypes.data_as(C.c_void_p),
                                 thr_h.ctypes.data_as(C.c_void_p), S["N"], C.byref(h)))
     try:
+        # rows sharded over ranks: reduce-scatter the group histogram by node, K5 on the own node slots, all-gather the split records
+        # (segment mode; B2RF_SHARD_K5=0 or a histogram hook keep the all-reduce + redundant K5 of every rank)
+        world, dist = S["world"], S["dist"]
+        shard = world > 1 and node is None and hist_hook is None and os.environ.get("B2RF_SHARD_K5", "1") != "0"
+        if shard:
+            check(L.b2rf_trainer_set_shard(h, dist.get_rank(group), world))
         cells = int(L.b2rf_trainer_max_group_cells(h))
         hist = torch.empty(cells * 4, dtype=torch.float64, device=dev)
+        xin = xall = None
         ld = w.stride(0)
         check(L.b2rf_trainer_bind(h, bins.data_ptr(), bins.stride(0), 0 if bins_rm is None else bins_rm.data_ptr(),
                                   0 if bins_rm is None else bins_rm.stride(0), y.data_ptr(), w.data_ptr(), w.stride(0),
@@ -324,6 +331,25 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
             torch.cuda.synchronize(dev); tb = time.perf_counter()
         ar_events = []
         while check(L.b2rf_trainer_begin_group(h, C.byref(ncell), st)) == 1:
+            blk = int(L.b2rf_trainer_shard_block_doubles(h)) if shard else 0
+            if blk > 0:
+                ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True),
+                      torch.cuda.Event(enable_timing=True))
+                chunk = ncell.value * 4 // world                             # doubles per rank: its node slots' cells (padded)
+                rank = dist.get_rank(group)
+                ev[0].record()
+                dist.reduce_scatter_tensor(hist[rank * chunk: (rank + 1) * chunk], hist[: world * chunk], group=group)   # merge by node, row a7
+                ev[1].record()
+                if xin is None or xin.numel() < blk:
+                    xin = torch.empty(blk + blk // 2, dtype=torch.float64, device=dev)
+                    xall = torch.empty(world * xin.numel(), dtype=torch.float64, device=dev)
+                check(L.b2rf_trainer_end_group_shard_launch(h, xin.data_ptr(), st))
+                ev[2].record()
+                dist.all_gather_into_tensor(xall[: world * blk], xin[:blk], group=group)                                   # the nodes' best splits
+                ev[3].record()
+                ar_events.append((ev[0], ev[1])); ar_events.append((ev[2], ev[3]))
+                check(L.b2rf_trainer_end_group_shard_finish(h, xall.data_ptr(), st))
+                continue
             if S["world"] > 1:
                 ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
                 ev[0].record()
