@@ -49,7 +49,7 @@ def make_config(wl_name, wl, n_local, world, extra=None):
     cfg = {"workload": f"{wl_name}: synthetic {n_local} rows/GPU x {wl['F']} features, RandomForestRegressor numTrees={wl['numTrees']} "
                        f"maxDepth={wl['maxDepth']} maxBins={wl['maxBins']} featureSubsetStrategy=auto seed=42",
            "rows_global": n_local * world, "rows_per_gpu": n_local, "rows_per_partition": ROWS_PER_PARTITION,
-           "parallelism": f"rows sharded over {world} GPU(s); per-group histogram all-reduce (NCCL)" if world > 1 else "1 GPU",
+           "parallelism": f"rows sharded over {world} GPU(s); per node group: histogram reduce-scatter by node, best splits on the owning rank, all-gather of the split records (NCCL)" if world > 1 else "1 GPU",
            "l2": "inputs (bin matrix 0.64 GB + per-tree arrays 5 GB) exceed the 126 MB L2; no explicit flush"}
     if extra:
         cfg.update(extra)
