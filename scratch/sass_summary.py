@@ -3,7 +3,7 @@ atomics of which kind, global reductions.  Usage: python scratch/sass_summary.py
 import collections, os, re, subprocess, sys
 so = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scalable-machine-learning-with-apache-spark_b200", "libb2rf.so")
 out = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
-pats = ["UBLKCP", "UTMALDG", "SYNCS", "LDGSTS", "ATOMS.ADD", "ATOMS.CAST.SPIN.64", "ATOMS.CAST.SPIN", "REDG.E.ADD.F64", "RED.E.ADD.F64", "ATOMG", "LDS", "STS", "SHFL", "MATCH", "REDUX", "HMMA", "UTC"]
+pats = ["UBLKCP", "UTMALDG", "SYNCS", "LDGSTS", "LDG.E.LTC64B", "ATOMS.ADD", "ATOMS.CAST.SPIN.64", "ATOMS.CAST.SPIN", "REDG.E.ADD.F64", "RED.E.ADD.F64", "ATOMG", "LDS", "STS", "SHFL", "MATCH", "REDUX", "HMMA", "UTC"]
 cur = None
 counts = collections.OrderedDict()
 for line in out.splitlines():
@@ -26,9 +26,9 @@ for line in out.splitlines():
             counts[cur][p] += 1
             break
 print("# SASS opcode summary per kernel (`cuobjdump -sass libb2rf.so`, sm_100a; scratch/sass_summary.py)\n")
-print("UBLKCP = `cp.async.bulk` (TMA engine, 1-D bulk copy), SYNCS = mbarrier operations, LDGSTS = `cp.async`, ATOMS.ADD = native 32-bit shared-memory add,")
+print("UBLKCP = `cp.async.bulk` (TMA engine, 1-D bulk copy), SYNCS = mbarrier operations, LDGSTS = `cp.async`, LDG.E.LTC64B = `ld.global.L2::64B` (64-byte DRAM fetch on an L2 miss), ATOMS.ADD = native 32-bit shared-memory add,")
 print("ATOMS.CAST.SPIN(.64) = compare-and-swap loop of a shared-memory fp32/fp64 (64) add, REDG/RED = global reduction (no return value).\n")
-cols = ["insts", "UBLKCP", "SYNCS", "LDGSTS", "ATOMS.ADD", "ATOMS.CAST.SPIN.64", "REDG.E.ADD.F64", "ATOMG", "SHFL", "MATCH", "HMMA", "UTC"]
+cols = ["insts", "UBLKCP", "SYNCS", "LDGSTS", "LDG.E.LTC64B", "ATOMS.ADD", "ATOMS.CAST.SPIN.64", "REDG.E.ADD.F64", "ATOMG", "SHFL", "MATCH", "HMMA", "UTC"]
 print("| kernel | " + " | ".join(cols) + " |")
 print("|---|" + "---|" * len(cols))
 for k, c in counts.items():
