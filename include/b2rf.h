@@ -170,7 +170,8 @@ int b2rf_trainer_group_info(const b2rf_trainer* t, int64_t* n_slots, int32_t* h_
                             int64_t* h_slot_base);
 /* Process-wide switches, for A/B runs and tests: "k4_fp64" (1: segment mode uses the fp64 compare-and-swap histogram kernels
  * instead of the limb kernel; env B2RF_K4=fp64), "k4_tma" (1: the limb kernel stages code rows with one bulk async copy per row on
- * the TMA engine instead of register-staged 128-bit loads; env B2RF_K4_STAGE=tma), "carry_labels" (0: row lists do not carry labels, K4 gathers them; env
+ * the TMA engine instead of register-staged 128-bit loads; env B2RF_K4_STAGE=tma), "k4_binary" (0: fits whose labels are all 0 / 1 use
+ * the general integer-label form instead of the two-plane form; env B2RF_K4_BINARY=0), "carry_labels" (0: row lists do not carry labels, K4 gathers them; env
  * B2RF_CARRY_Y=0).  Takes effect at the next b2rf_trainer_bind / begin_group. */
 int b2rf_set_option(const char* name, int64_t value);
 /* h_seconds5: init(0), findSplits(0), findBestSplits (K4 device time from CUDA events), chooseSplits (K5 + driver tail),

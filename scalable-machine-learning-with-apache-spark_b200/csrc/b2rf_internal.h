@@ -94,12 +94,13 @@ void count_k4_variant(int v);
 long long k4_variant_count(int v);
 
 // Limb kernel (k4_limb.cu): launch shape chosen by limb_plan from the histogram size and the code-row width.
-// NP = planes per cell: 9 (wide windows, exact for any realistic label range) or 7 (narrow: fits whose labels are all modest integers).
+// NP = planes per cell: 9 (wide windows, exact for any realistic label range), 7 (narrow: fits whose labels are all modest integers)
+// or 2 (labels all 0 / 1).
 struct LimbPlan { int G, BR, threads, padB, NP, tma; };
-bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, bool wantTma, LimbPlan* p);
+bool limb_plan(const BucketLaunch& b, int maxBinsAll, int form, bool wantTma, LimbPlan* p);   // form: 0 wide, 1 narrow, 2 binary
 cudaError_t launch_limb_hist(const BucketLaunch& b, const LimbPlan& p, cudaStream_t s);
 cudaError_t launch_seg_tasks_slots(const SlotSrc* slots, int n, int CH, uint32_t* chunkPrefix, cudaStream_t s);   // task table + ticket from SlotSrc segments
-cudaError_t launch_labels_integer(const double* y, int64_t n, int32_t* d_flag, cudaStream_t s);   // *d_flag (preset to 1) cleared unless every label is an integer, |y| <= 2^24
+cudaError_t launch_labels_integer(const double* y, int64_t n, int32_t* d_flag, cudaStream_t s);   // d_flag[0] / [1] (preset to 1) cleared unless every label is an integer, |y| <= 2^24 / is 0 or 1
 
 constexpr int SEG_CH = 4096;            // rows per (node, chunk) task
 constexpr int COMPACT_ROWS = 2048;      // rows per compaction block

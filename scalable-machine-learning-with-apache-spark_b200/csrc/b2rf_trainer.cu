@@ -215,6 +215,7 @@ double now_s() { return std::chrono::duration<double>(std::chrono::steady_clock:
 // Process-wide switches (b2rf_set_option; initial values from the environment: B2RF_K4=fp64, B2RF_CARRY_Y=0).
 std::atomic<int>& opt_k4_fp64() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_K4"); return (m && std::string(m) == "fp64") ? 1 : 0; }()}; return v; }
 std::atomic<int>& opt_k4_tma() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_K4_STAGE"); return (m && std::string(m) == "tma") ? 1 : 0; }()}; return v; }
+std::atomic<int>& opt_k4_bin() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_K4_BINARY"); return (m && *m == '0') ? 0 : 1; }()}; return v; }   // two-plane form for 0 / 1 labels
 std::atomic<int>& opt_carry_labels() { static std::atomic<int> v{[] { const char* m = std::getenv("B2RF_CARRY_Y"); return (m && *m == '0') ? 0 : 1; }()}; return v; }
 
 }  // namespace
@@ -311,6 +312,7 @@ struct b2rf_trainer {
   BucketLaunch deferB; LimbPlan deferPlan;
   DevBuf<SlotSrc> dShared; PinBuf<SlotSrc> hShared; DevBuf<uint32_t> dSharedPrefix;
   bool labelsInt = false;       // every local label is an integer of magnitude <= 2^24: the narrow (7-plane) limb kernel is exact
+  bool labels01 = false;        // every local label is 0 or 1: the two-plane form (count, sum of w*y)
   DevBuf<unsigned long long> dBindTmp;
   DevBuf<unsigned long long> dRowsAcc;   // rows visited by the K4 launches of this fit (segment mode)
   int64_t physRows = 0;
@@ -555,14 +557,15 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
           t->carryY = t->dY0.ensure(total) && t->dY1.ensure(total);
         if (!t->carryY) { t->dY0.release(); t->dY1.release(); }
       }
-      t->labelsInt = false;
+      t->labelsInt = false; t->labels01 = false;
       if (ok && t->carryY) {   // one pass over the labels decides which limb form is exact for this fit
-        int32_t one = 1, flag = 0;
+        int32_t ones[2] = {1, 1}, flag[2] = {0, 0};
         int32_t* d_flag = reinterpret_cast<int32_t*>(t->dBindTmp.p);    // the in-bag totals have been read back already
-        ok = ok && cuda_ok(cudaMemcpy(d_flag, &one, 4, cudaMemcpyHostToDevice), "bind copy");
+        ok = ok && cuda_ok(cudaMemcpy(d_flag, ones, 8, cudaMemcpyHostToDevice), "bind copy");
         ok = ok && cuda_ok(launch_labels_integer(d_y, n_rows_local, d_flag, 0), "label scan");
-        ok = ok && cuda_ok(cudaMemcpy(&flag, d_flag, 4, cudaMemcpyDeviceToHost), "bind copy");
-        t->labelsInt = ok && flag != 0;
+        ok = ok && cuda_ok(cudaMemcpy(flag, d_flag, 8, cudaMemcpyDeviceToHost), "bind copy");
+        t->labelsInt = ok && flag[0] != 0;
+        t->labels01 = ok && flag[1] != 0;
       }
       ok = ok && cuda_ok(cudaMemcpy(d_base, t->treeBase.data(), (size_t)(t->T + 1) * 8, cudaMemcpyHostToDevice), "bind copy");
       ok = ok && cuda_ok(launch_compact_write(d_w, ldw, t->T, n_rows_local, blockCnt.p, d_base, t->dIdx0.p, d_y, t->carryY ? t->dY0.p : nullptr, 0),
@@ -853,7 +856,7 @@ int b2rf_trainer_begin_group(b2rf_trainer* t, int64_t* n_cells, void* stream) {
       const bool fp64Only = opt_k4_fp64().load() != 0;
       LimbPlan plan;
       t->deferred = false;
-      if (!fp64Only && limb_plan(b, maxBinsAll, t->labelsInt, opt_k4_tma().load() != 0, &plan)) {
+      if (!fp64Only && limb_plan(b, maxBinsAll, t->labels01 && opt_k4_bin().load() ? 2 : (t->labelsInt ? 1 : 0), opt_k4_tma().load() != 0, &plan)) {
         if (t->deferK4) { t->deferB = b; t->deferPlan = plan; t->deferred = true; e = cudaSuccess; }   // launched by b2rf_trainers_begin_group_shared
         else e = launch_limb_hist(b, plan, s);
       } else e = launch_segment_hist(b, s);
@@ -1200,6 +1203,7 @@ int b2rf_set_option(const char* name, int64_t value) {
   if (n == "k4_fp64") { opt_k4_fp64().store(value ? 1 : 0); return B2RF_OK; }
   if (n == "carry_labels") { opt_carry_labels().store(value ? 1 : 0); return B2RF_OK; }
   if (n == "k4_tma") { opt_k4_tma().store(value ? 1 : 0); return B2RF_OK; }
+  if (n == "k4_binary") { opt_k4_bin().store(value ? 1 : 0); return B2RF_OK; }
   set_error("b2rf_set_option: unknown option \"" + n + "\" (k4_fp64, k4_tma, carry_labels)");
   return B2RF_ERR_ARG;
 }

@@ -85,7 +85,8 @@ __device__ __forceinline__ void limb_pack_wide(uint32_t w, double yv, LimbScale 
 // G    features per task group = lanes per row (32, 16 or 8); a warp instruction covers 32/G rows
 // LDR  bytes per row of the row-major code matrix (0: read a.ldr)
 // BR   rows per staged block (32 or 16)
-// NP   planes per cell: 7 = count + 3 + 3 limbs (narrow), 9 = count + 4 + 4 (wide)
+// NP   planes per cell: 7 = count + 3 + 3 limbs (narrow), 9 = count + 4 + 4 (wide), 2 = count + sum of w*y (labels all 0 or 1:
+//      binary classification; w*y*y == w*y, and both sums are small integers)
 // TMA  how a block's code rows reach shared memory.  true: one bulk async copy per row on the TMA engine (UBLKCP + mbarrier, two
 //      tile slots per warp); costs no LSU wavefronts, but UBLKCP is a uniform-datapath instruction — one copy per warp instruction —
 //      so a block is BR serialized R2UR / UBLKCP sequences, ~12 issue slots per row (ncu: profiles/r02_ncu_limb.md).  false (needs a
@@ -99,8 +100,8 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
   constexpr int W = THREADS / 32;
   constexpr int R = 32 / G;                  // rows per warp instruction
   constexpr int NU = BR / R;                 // warp instructions per staged block
-  constexpr bool WIDE = NP == 9;
-  constexpr int VB = WIDE ? 32 : 16;         // bytes of packed values per row (wide: 24 used)
+  constexpr bool WIDE = NP == 9, BIN = NP == 2;
+  constexpr int VB = WIDE ? 32 : (BIN ? 8 : 16);   // bytes of packed values per row (wide: 24 used)
   constexpr unsigned FULL = 0xffffffffu;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ldr = LDR ? LDR : (int)a.ldr;
@@ -164,7 +165,7 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
     const uint2 e = active ? fo[j] : make_uint2(0u, 0u);
     // ---- task scale: largest label magnitude of the task's rows (the high word is monotone in |y|) ----
     uint32_t ex = 0;
-    for (int i = tid; i < n; i += THREADS) ex = max(ex, (uint32_t)__double2hiint(yl[i]) & 0x7fffffffu);
+    if (!BIN) for (int i = tid; i < n; i += THREADS) ex = max(ex, (uint32_t)__double2hiint(yl[i]) & 0x7fffffffu);
     ex = __reduce_max_sync(FULL, ex);
     if (lane == 0) s_red[warp] = ex;
     bool direct = (int64_t)n * a.Fsub < (int64_t)slotCells;   // fewer updates than cells: skip the shared-memory round trip
@@ -220,7 +221,9 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
       const uint32_t w = ent >> 27;
       bool slow = false;
       if (lane < BR) {
-        if (WIDE) {
+        if (BIN) {
+          *reinterpret_cast<uint2*>(vals + lane * VB) = make_uint2(w, yv != 0.0 ? w : 0u);
+        } else if (WIDE) {
           uint4 p0; uint2 p1;
           limb_pack_wide(w, yv, sc, p0, p1, slow);
           *reinterpret_cast<uint4*>(vals + lane * VB) = p0;
@@ -236,7 +239,19 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
     auto consume = [&](const unsigned char* tile, const unsigned char* vals, uint32_t slowMask, int blk) {
       const unsigned char* tl = tile + r * ldr + e.x;
       const unsigned char* vv = vals + r * VB;
-      if (active) {
+      if (BIN) {
+        if (active) {
+          uint32_t code = tl[0];
+          uint2 q = *reinterpret_cast<const uint2*>(vv);
+#pragma unroll
+          for (int u = 0; u < NU; u++) {
+            const uint32_t cc = code; const uint2 p = q;
+            if (u + 1 < NU) { code = tl[(u + 1) * R * ldr]; q = *reinterpret_cast<const uint2*>(vv + (u + 1) * R * VB); }
+            uint32_t* c = hcell + cc * (NP * G);
+            atomicAdd(c, p.x); atomicAdd(c + G, p.y);      // rows past the end of the chunk add zeros
+          }
+        }
+      } else if (active) {
         // one row ahead: the next row's code and packed limbs are loaded before this row's adds are issued (the compiler keeps
         // shared loads behind earlier shared atomics, so the overlap has to be written out)
         uint32_t code = tl[0];
@@ -332,14 +347,16 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_ker
     }
     __syncthreads();
     // ---- flush: exact limb sums -> fp64 (one rounding), added to the global histogram ----
-    const double sA = pow2d(Ea - (WIDE ? 79 : 59)), sB = pow2d(Eb - (WIDE ? 80 : 60));
+    const double sA = BIN ? 1.0 : pow2d(Ea - (WIDE ? 79 : 59)), sB = BIN ? 1.0 : pow2d(Eb - (WIDE ? 80 : 60));
     for (int c = tid; c < padB * G; c += THREADS) {
       const int bin = c / G, f2 = c & (G - 1);
       const uint32_t* cell = hist + (size_t)bin * (NP * G) + f2;
       const uint32_t cnt = cell[0];
       if (!cnt) continue;                                                // untouched cell (also every cell of an idle lane)
       double A, B;
-      if (WIDE) {
+      if (BIN) {
+        A = B = (double)cell[G];
+      } else if (WIDE) {
         A = ((double)(int32_t)cell[4 * G] * 0x1p60 + (double)cell[3 * G] * 0x1p40) + ((double)cell[2 * G] * 0x1p20 + (double)cell[G]);
         B = ((double)cell[8 * G] * 0x1p60 + (double)cell[7 * G] * 0x1p40) + ((double)cell[6 * G] * 0x1p20 + (double)cell[5 * G]);
       } else {
@@ -360,7 +377,7 @@ long long k4_variant_count(int v) { return (v >= 0 && v < B2RF_K4_VARIANTS) ? g_
 // Shared memory of one CTA: the limb histogram, the warps' staging rings (code-row tile slots + two packed-value slots) and, for the
 // TMA form, two mbarriers per warp.
 static size_t limb_smem(int padB, int G, int ldr, int BR, int threads, int NP, bool tma) {
-  const size_t vb = NP == 9 ? 32 : 16;
+  const size_t vb = NP == 9 ? 32 : (NP == 2 ? 8 : 16);
   const size_t warp = (size_t)(tma ? 2 : 1) * BR * ldr + 2 * (size_t)BR * vb;
   return (size_t)padB * NP * G * 4 + (size_t)(threads / 32) * warp + (size_t)(threads / 32) * 16;
 }
@@ -368,11 +385,11 @@ static size_t limb_smem(int padB, int G, int ldr, int BR, int threads, int NP, b
 // Picks (G, block rows, threads, staging) for a launch, or returns false when the limb kernel does not apply (the caller then runs
 // the fp64 compare-and-swap kernel of k4_hist.cu): uint8 codes, labels carried in the row lists, 16-byte aligned code rows, and a
 // task histogram that leaves room for the staging ring.
-bool limb_plan(const BucketLaunch& b, int maxBinsAll, bool narrow, bool wantTma, LimbPlan* p) {
+bool limb_plan(const BucketLaunch& b, int maxBinsAll, int form, bool wantTma, LimbPlan* p) {
   if (b.codeBytes != 1 || ((b.dseg == nullptr || b.y0 == nullptr || b.y1 == nullptr) && b.slots == nullptr)) return false;
   if ((b.ldr & 15) != 0 || (reinterpret_cast<uintptr_t>(b.bins_rm) & 15) != 0 || b.ldr > 1024) return false;
   const size_t cap2 = (size_t)113 * 1024, cap1 = (size_t)226 * 1024;   // two CTAs per SM / one
-  const int NP = narrow ? 7 : 9;
+  const int NP = form == 2 ? 2 : (form == 1 ? 7 : 9);   // form: 0 wide, 1 narrow (integer labels), 2 binary (labels 0 / 1)
   const bool tma = wantTma || !(b.ldr == 64 || b.ldr == 128);          // register staging is compiled for the 64- and 128-byte rows
   const int ldr = (int)b.ldr;
   int G = 32;
@@ -435,6 +452,11 @@ cudaError_t launch_limb_hist(const BucketLaunch& b0, const LimbPlan& p, cudaStre
   const size_t smem = limb_smem(p.padB, p.G, (int)b.ldr, p.BR, p.threads, p.NP, p.tma != 0);
   const int grid = device_sm_count() * (p.threads <= 384 ? 2 : 1);
   count_k4_variant(B2RF_K4_LIMB);
+  if (p.NP == 2) {
+    if (p.G == 32) return launch_limb_br<32, 2>(b, p, ticket, grid, smem, s);
+    if (p.G == 16) return launch_limb_br<16, 2>(b, p, ticket, grid, smem, s);
+    return launch_limb_br<8, 2>(b, p, ticket, grid, smem, s);
+  }
   if (p.NP == 7) {
     if (p.G == 32) return launch_limb_br<32, 7>(b, p, ticket, grid, smem, s);
     if (p.G == 16) return launch_limb_br<16, 7>(b, p, ticket, grid, smem, s);
@@ -445,15 +467,18 @@ cudaError_t launch_limb_hist(const BucketLaunch& b0, const LimbPlan& p, cudaStre
   return launch_limb_br<8, 9>(b, p, ticket, grid, smem, s);
 }
 
-// 1 when every label is an integer of magnitude <= 2^24 (then w*y and w*y*y are integers below 2^53 and the narrow windows hold
-// every row exactly), else 0.  *flag must be 1 on entry.
+// flag[0]: 1 when every label is an integer of magnitude <= 2^24 (then w*y and w*y*y are integers below 2^53 and the narrow windows
+// hold every row exactly), else 0.  flag[1]: 1 when every label is 0 or 1 (binary classification: the two-plane form).  Both must be
+// 1 on entry.
 __global__ void labels_integer_kernel(const double* y, int64_t n, int32_t* flag) {
-  bool ok = true;
+  bool ok = true, ok01 = true;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const double v = y[i];
     ok = ok && (fabs(v) <= 16777216.0) && (v == rint(v));
+    ok01 = ok01 && (v == 0.0 || v == 1.0);
   }
-  if (!__all_sync(0xffffffffu, ok) && (threadIdx.x & 31) == 0) *flag = 0;
+  if (!__all_sync(0xffffffffu, ok) && (threadIdx.x & 31) == 0) flag[0] = 0;
+  if (!__all_sync(0xffffffffu, ok01) && (threadIdx.x & 31) == 0) flag[1] = 0;
 }
 cudaError_t launch_labels_integer(const double* y, int64_t n, int32_t* d_flag, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;

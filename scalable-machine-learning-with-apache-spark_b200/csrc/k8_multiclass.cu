@@ -91,13 +91,13 @@ __global__ void __launch_bounds__(CLS_THREADS) bucket_hist_cls_kernel(const ClsH
 
 // ---- staged form (default when labels travel with the row lists and code rows are 64 or 128 bytes of uint8 codes) ----
 // The skeleton of the regression limb kernel (k4_limb.cu): dynamic ticket scheduling over (slot, chunk, feature group) tasks, 12
-// warps x 2 CTAs per SM, each warp register-stages the code rows of its next 32-row block (LDG.128 -> STS.128, in flight while the
+// warps x 3 CTAs per SM (2 when the counters are large; 56 registers per thread), each warp register-stages the code rows of its next 32-row block (LDG.128 -> STS.128, in flight while the
 // current block is added) and writes one 8-byte (weight, class offset) pair per row next to them.  A lane then reads its feature's
 // code with one LDS.U8 and the row's pair with one broadcast LDS.64 and issues ONE native 32-bit add (ATOMS.ADD): three
 // shared-memory wavefronts per 32 updates against the gather kernel's dependent global loads.  Counter layout [bin][class][lane]
 // (bank == lane); bag counts are exact in u32 (<= 4096 rows x weight <= 31 per task).
 template <int G, int LDR>
-__global__ void __launch_bounds__(384, 2) staged_hist_cls_kernel(const ClsHistLaunch a, uint32_t* ticket) {
+__global__ void __launch_bounds__(384, 3) staged_hist_cls_kernel(const ClsHistLaunch a, uint32_t* ticket) {
   extern __shared__ __align__(16) unsigned char smraw[];
   __shared__ uint32_t s_task;
   constexpr int THREADS = 384, W = THREADS / 32, BR = 32;
@@ -226,7 +226,8 @@ template <int G, int LDR>
 static cudaError_t launch_staged_cls(const ClsHistLaunch& a, uint32_t* ticket, size_t smem, cudaStream_t s) {
   cudaError_t e = cudaFuncSetAttribute(staged_hist_cls_kernel<G, LDR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  staged_hist_cls_kernel<G, LDR><<<device_sm_count() * 2, 384, smem, s>>>(a, ticket);
+  const int perSM = (smem + 1024) * 3 <= (size_t)227 * 1024 ? 3 : 2;   // the kernel is bound by the latency of its gathers: as many warps as fit
+  staged_hist_cls_kernel<G, LDR><<<device_sm_count() * perSM, 384, smem, s>>>(a, ticket);
   return cudaGetLastError();
 }
 

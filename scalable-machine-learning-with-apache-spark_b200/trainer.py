@@ -285,7 +285,7 @@ def k4_launch_counts() -> dict:
 
 
 def set_option(name: str, value: int):
-    """Process-wide switch of the library (b2rf_set_option): "k4_fp64", "carry_labels"."""
+    """Process-wide switch of the library (b2rf_set_option): "k4_fp64", "k4_tma", "k4_binary", "carry_labels"."""
     check(lib().b2rf_set_option(name.encode(), int(value)))
 
 

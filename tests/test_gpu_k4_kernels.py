@@ -278,3 +278,44 @@ def test_more_than_128_features(b2rf, oracle, cuda):
     g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), y.numpy(), arity, maxDepth=6, maxBins=32, numTrees=2, bootstrap=True, seed=1)
     assert trainer.k4_launch_counts()["limb"] > before["limb"]
     assert_parity_allowing_ties(g, o, max_ties=4)
+
+
+@pytest.mark.parametrize("impurity,tma,F", [("gini", 0, 64), ("variance", 0, 64), ("gini", 1, 64), ("entropy", 0, 100), ("gini", 0, 12)])
+def test_binary_labels_two_plane_form(b2rf, oracle, cuda, impurity, tma, F):
+    """Labels that are all 0 or 1 (binary classification, or a 0 / 1 regression target): the limb kernel keeps two planes per cell
+    (count and sum of w*y; w*y*y == w*y) instead of seven.  All sums are small integers, so counts and sums must be bit-identical to
+    the oracle's, and the forest must be the one the general integer-label form builds."""
+    from b2rf import trainer
+    from helpers import first_tie_in_order
+    X, y, arity = b2rf.synth.c3(30000, device="cpu", F=F)
+    yb = (y > y.median()).to(torch.float64)
+    kw = dict(maxDepth=8, maxBins=64, numTrees=3, bootstrap=True, seed=6, impurity=impurity, featureSubsetStrategy="all")
+    trainer.set_option("k4_tma", tma)
+    try:
+        before = trainer.k4_launch_counts()
+        g, o = _fit_both(b2rf, oracle, cuda, X.numpy(), yb.numpy(), arity, **kw)
+        assert trainer.k4_launch_counts()["limb"] > before["limb"]
+        trainer.set_option("k4_binary", 0)
+        g7 = b2rf.trainer.fit_tensors(X.to(cuda), yb.to(cuda), arity, b2rf.TreeParams(**kw), part_offsets=trainer.default_partitions(30000, 1024), keep_trace=True)
+    finally:
+        trainer.set_option("k4_tma", 0)
+        trainer.set_option("k4_binary", 1)
+    if impurity == "variance":
+        k = first_tie_in_order(g, o)
+        upto = len(o.trace_i) if k is None else k
+        assert upto > 0.5 * len(o.trace_i)
+        assert np.array_equal(g.trace_d[:upto, 2:5], o.trace_d[:upto, 2:5])      # counts AND both sums bit-identical
+        if k is None:
+            assert_forest_parity(g, o)
+    else:   # class counts are exact integers on both sides and Gini / entropy ties resolve identically: full parity (the oracle's trace
+            # holds (count of class 0, count of class 1), the device's (count, sum of w*y, sum of w*y*y))
+        from helpers import assert_classifier_parity
+        assert_classifier_parity(g, o, exact=(impurity == "gini"))
+        assert np.array_equal(g.trace_d[:, 2] - g.trace_d[:, 3], o.trace_d[:, 2]) and np.array_equal(g.trace_d[:, 3], o.trace_d[:, 3])
+        assert np.array_equal(g.trace_d[:, 3], g.trace_d[:, 4])
+    # exact integer sums in both forms: identical node statistics as long as the two device fits take the same path
+    m = min(len(g.trace_i), len(g7.trace_i))
+    same = np.all(g.trace_i[:m] == g7.trace_i[:m], axis=1)
+    first_diff = m if same.all() else int(np.argmin(same))
+    assert first_diff > 0.5 * m
+    assert np.array_equal(g.trace_d[:first_diff, 2:5], g7.trace_d[:first_diff, 2:5])

@@ -42,7 +42,7 @@ def _fit_both(b2rf, oracle, cuda, X, y, arity, part_offsets=None, hist_mode="seg
     o = oracle.fit(X, y, arity, maxDepth=p.maxDepth, maxBins=p.maxBins, minInstancesPerNode=p.minInstancesPerNode, numTrees=p.numTrees,
                    featureSubsetStrategy=p.featureSubsetStrategy, maxMemoryInMB=p.maxMemoryInMB, bootstrap=p.bootstrap,
                    minInfoGain=p.minInfoGain, minWeightFractionPerNode=p.minWeightFractionPerNode, subsamplingRate=p.subsamplingRate,
-                   seed=p.seed, part_offsets=part_offsets, sample_idx=sample_idx, fraction=fraction)
+                   seed=p.seed, part_offsets=part_offsets, sample_idx=sample_idx, fraction=fraction, impurity=p.impurity)
     return g, o
 
 
