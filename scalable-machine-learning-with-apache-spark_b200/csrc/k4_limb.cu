@@ -93,7 +93,7 @@ __device__ __forceinline__ void limb_pack_wide(uint32_t w, double yv, LimbScale 
 //      compile-time LDR): every lane fetches 16-byte pieces with LDG.128 one block ahead, holds them in registers while the warp adds
 //      the current block, and stores them with STS.128 (0.5 wavefronts and ~1 issue slot per row; one tile slot per warp).
 template <int G, int LDR, int BR, int THREADS, int NP, bool TMA>
-__global__ void __launch_bounds__(THREADS, THREADS <= 384 ? 2 : 1) limb_hist_kernel(const BucketLaunch a, uint32_t* ticket) {
+__global__ void __launch_bounds__(THREADS, THREADS <= 384 ? (NP == 2 ? 3 : 2) : 1) limb_hist_kernel(const BucketLaunch a, uint32_t* ticket) {
   extern __shared__ __align__(16) unsigned char smraw[];
   __shared__ uint32_t s_red[THREADS / 32];
   __shared__ uint32_t s_task;
@@ -450,7 +450,10 @@ cudaError_t launch_limb_hist(const BucketLaunch& b0, const LimbPlan& p, cudaStre
   if (e != cudaSuccess) return e;
   uint32_t* ticket = const_cast<uint32_t*>(b.chunk_prefix) + b.nSlots + 1;
   const size_t smem = limb_smem(p.padB, p.G, (int)b.ldr, p.BR, p.threads, p.NP, p.tma != 0);
-  const int grid = device_sm_count() * (p.threads <= 384 ? 2 : 1);
+  // the two-plane form is bound by its gathers (two adds per update): a third CTA per SM when the shared memory allows (its launch
+  // bounds keep it at 56 registers)
+  const int perSM = p.threads > 384 ? 1 : (p.NP == 2 && (smem + 1024) * 3 <= (size_t)227 * 1024 ? 3 : 2);
+  const int grid = device_sm_count() * perSM;
   count_k4_variant(B2RF_K4_LIMB);
   if (p.NP == 2) {
     if (p.G == 32) return launch_limb_br<32, 2>(b, p, ticket, grid, smem, s);
