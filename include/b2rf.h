@@ -83,6 +83,10 @@ int b2rf_sample_rows(const double* d_X, int64_t ldx, int64_t n_rows, int64_t row
 /* Host twin of b2rf_sample_rows: the local indices (ascending) of the rows it keeps, so a host-side caller can gather the
  * sample before any feature data reaches the device.  Returns the number kept (may exceed cap: then only cap are written). */
 int64_t b2rf_sample_indices(int64_t seed, int64_t row0_global, int64_t n_rows, double fraction, int64_t* h_idx_out, int64_t cap);
+/* Device form of the same decision without touching X (the rows may still be on the host): the local ids of the kept rows, in any
+ * order, appended to d_ids_out [cap]; *d_count (device int64, caller-zeroed) counts them. */
+int b2rf_sample_row_ids(int64_t n_rows, int64_t row0_global, int64_t seed, double fraction, int64_t* d_ids_out, int64_t cap, int64_t* d_count,
+                        void* stream);
 size_t b2rf_find_splits_workspace_bytes(int64_t n_sample, int32_t F);
 /* d_sample [n_sample][F]; d_arity[F] (0 = continuous); out: d_thresholds [F][maxPossibleBins-1], d_nsplits[F]. */
 int b2rf_find_splits(const double* d_sample, int64_t n_sample, int32_t F, const int32_t* d_arity, int32_t maxPossibleBins,

@@ -39,6 +39,7 @@ _SIGS = {
     "b2rf_samples_fraction": (f64, [i64, i32]),
     "b2rf_sample_rows": (C.c_int, [vp, i64, i64, i64, i32, i64, f64, vp, i64, vp, vp]),
     "b2rf_sample_indices": (i64, [i64, i64, i64, f64, vp, i64]),
+    "b2rf_sample_row_ids": (C.c_int, [i64, i64, i64, f64, vp, i64, vp, vp]),
     "b2rf_find_splits_workspace_bytes": (sz, [i64, i32]),
     "b2rf_find_splits": (C.c_int, [vp, i64, i32, vp, i32, f64, vp, vp, vp, sz, vp]),
     "b2rf_find_splits_noalloc_max_bytes": (sz, []),

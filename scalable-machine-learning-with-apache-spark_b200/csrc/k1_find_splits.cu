@@ -41,6 +41,26 @@ __global__ void sample_rows_kernel(const double* X, int64_t ldx, int64_t n_rows,
   for (int f = lane; f < F; f += 32) out[(size_t)pos * F + f] = X[(size_t)row * ldx + f];
 }
 
+// The same decision for callers whose rows are still on the host: only the local ids of the kept rows (any order), warp-aggregated append.
+__global__ void sample_row_ids_kernel(int64_t n_rows, int64_t row0, uint64_t seedWord, double fraction, int64_t* out, int64_t cap,
+                                      unsigned long long* count) {
+  const int lane = threadIdx.x & 31;
+  for (int64_t base = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) - lane; base < n_rows; base += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = base + lane;
+    bool keep = false;
+    if (row < n_rows) {
+      const uint64_t h = mix64(seedWord + (uint64_t)(row0 + row) * 0x9E3779B97F4A7C15ULL);
+      keep = ((double)(h >> 11) * 0x1.0p-53) < fraction;
+    }
+    const unsigned m = __ballot_sync(0xffffffffu, keep);
+    if (!m) continue;
+    unsigned long long pos = 0;
+    if (lane == 0) pos = atomicAdd(count, (unsigned long long)__popc(m));
+    pos = __shfl_sync(0xffffffffu, pos, 0) + __popc(m & ((1u << lane) - 1u));
+    if (keep && (int64_t)pos < cap) out[pos] = row;
+  }
+}
+
 // One CTA per feature.  Workspace: F * n_pad doubles (sorted non-zero sample values, +inf padded).
 __global__ void __launch_bounds__(1024) find_splits_kernel(const double* sample, int64_t n_s, int F, const int32_t* arity, int maxSplits,
                                                             double wns, double* thresholds, int32_t* nsplits, double* ws, int64_t n_pad) {
@@ -162,6 +182,17 @@ int b2rf_sample_rows(const double* d_X, int64_t ldx, int64_t n_rows, int64_t row
   sample_rows_kernel<<<(unsigned)((threads + 255) / 256), 256, 0, (cudaStream_t)stream>>>(d_X, ldx, n_rows, row0_global, F, seedWord, fraction,
                                                                                         d_sample_out, cap, (unsigned long long*)d_count);
   return cuda_ok(cudaGetLastError(), "b2rf_sample_rows") ? B2RF_OK : B2RF_ERR_CUDA;
+}
+
+int b2rf_sample_row_ids(int64_t n_rows, int64_t row0_global, int64_t seed, double fraction, int64_t* d_ids_out, int64_t cap, int64_t* d_count,
+                        void* stream) {
+  if (n_rows < 0 || !d_ids_out || !d_count || cap < 0) { set_error("b2rf_sample_row_ids: bad argument"); return B2RF_ERR_ARG; }
+  if (n_rows == 0) return B2RF_OK;
+  const uint64_t seedWord = ((uint64_t)(uint32_t)xorshift_first_int(seed) << 32) | 0x9E3779B9u;
+  const int64_t blocks = std::min<int64_t>((n_rows + 255) / 256, (int64_t)device_sm_count() * 16);
+  sample_row_ids_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(n_rows, row0_global, seedWord, fraction, d_ids_out, cap,
+                                                                               reinterpret_cast<unsigned long long*>(d_count));
+  return cuda_ok(cudaGetLastError(), "b2rf_sample_row_ids") ? B2RF_OK : B2RF_ERR_CUDA;
 }
 
 int64_t b2rf_sample_indices(int64_t seed, int64_t row0_global, int64_t n_rows, double fraction, int64_t* h_idx_out, int64_t cap) {

@@ -550,6 +550,22 @@ def fit_many_tensors(X: torch.Tensor, y: torch.Tensor, arity, params_list, part_
         return forests
 
 
+def sample_row_ids(seed: int, row0_global: int, n_rows: int, fraction: float, device) -> torch.Tensor:
+    """Local ids (ascending, int64, on the host) of the rows the findSplits sampler keeps, decided on the device without touching X:
+    what fit_host uses to gather the sample from host memory (10M hashes: microseconds on the GPU, tens of milliseconds on the host)."""
+    if fraction >= 1.0:
+        return torch.arange(n_rows, dtype=torch.int64)
+    cap = int(n_rows * fraction + 6.0 * (n_rows * fraction * (1 - fraction)) ** 0.5 + 64)
+    ids = torch.empty(cap, dtype=torch.int64, device=device)
+    cnt = torch.zeros(1, dtype=torch.int64, device=device)
+    with torch.cuda.device(device):
+        check(lib().b2rf_sample_row_ids(int(n_rows), int(row0_global), int(seed), float(fraction), ids.data_ptr(), cap, cnt.data_ptr(), _stream()))
+    k = int(cnt.item())
+    if k > cap:
+        raise RuntimeError("b2rf_sample_row_ids: capacity exceeded")
+    return torch.sort(ids[:k]).values.cpu()
+
+
 def sample_indices(seed: int, row0_global: int, n_rows: int, fraction: float) -> np.ndarray:
     """Local indices of the rows the findSplits sampler keeps (host twin of sample_rows: same hash of the global row index)."""
     if fraction >= 1.0:
@@ -568,8 +584,9 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
     (numpy or CPU torch tensors; pinned memory makes the copies asynchronous).
 
     The raw feature matrix never has to be resident on the GPU: the findSplits row sample is gathered on the host (5 MB),
-    then X streams through two staging buffers in `chunk_rows` pieces — copy on one stream, K2 binning of the previous
-    piece on another — while K3 bagging, which does not depend on X, runs concurrently on a third stream."""
+    then X streams through up to four staging buffers in `chunk_rows` pieces — copies on one stream (the first ones start before
+    the thresholds exist), K2 binning of the arrived pieces on another — while K3 bagging, which does not depend on X, runs
+    concurrently on a third stream."""
     dev = torch.device(device)
     Xh = torch.as_tensor(X_host, dtype=torch.float64)
     yh = torch.as_tensor(y_host, dtype=torch.float64)
@@ -595,10 +612,31 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
             w, node = bag(params.seed, S["po"], S["part0"], T, params.subsamplingRate, params.bootstrap, dev, ld=ld,
                           want_node=_want_node(hist_mode, True, n_local))
         t0 = time.perf_counter()
-        # K1 on the host-gathered sample
+        # the first pieces of X start moving before the thresholds exist: `n_stage` staging buffers are filled while K1 runs and its
+        # results travel back (K2 of a piece waits for K1 on the main stream anyway)
+        chunk_rows = max(1, min(chunk_rows, n_local))
+        n_chunks = (n_local + chunk_rows - 1) // chunk_rows
+        n_stage = max(2, min(4, n_chunks))
+        stage = [torch.empty((chunk_rows, F), dtype=torch.float64, device=dev) for _ in range(n_stage)]
+        copied = [torch.cuda.Event() for _ in range(n_stage)]
+        binned = [torch.cuda.Event() for _ in range(n_stage)]
+        copy_s.wait_stream(main)
+
+        def issue_copy(k):
+            b = k % n_stage
+            r0 = k * chunk_rows
+            r1 = min(n_local, r0 + chunk_rows)
+            with torch.cuda.stream(copy_s):
+                if k >= n_stage:
+                    copy_s.wait_event(binned[b])
+                stage[b][: r1 - r0].copy_(Xh[r0:r1], non_blocking=True)
+                copied[b].record(copy_s)
+
+        # K1 on the host-gathered sample; its (small) copy is queued ahead of the big pieces, which then stream while K1 runs
         fraction = S["fraction"]
-        idx = sample_indices(params.seed, S["row0"], n_local, fraction)
-        samp = Xh[torch.as_tensor(idx)].to(dev) if fraction < 1.0 else Xh.to(dev)
+        samp = Xh[sample_row_ids(params.seed, S["row0"], n_local, fraction, dev)].to(dev) if fraction < 1.0 else Xh.to(dev)
+        for k in range(min(n_stage, n_chunks)):
+            issue_copy(k)
         samp = gather_samples(samp, S["dist"], group)
         thr, ns = find_splits(samp, S["arity_d"], S["mpb"], fraction * float(S["N"]))
         thr_h = thr.cpu().numpy()
@@ -608,22 +646,15 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
         code_dt = torch.uint8 if S["mpb"] <= 256 else torch.int16
         bins = torch.empty((F, ld), dtype=code_dt, device=dev)
         bins_rm = torch.empty((max(n_local, 1), code_row_width(F)), dtype=code_dt, device=dev) if hist_mode != "scan" else None
-        chunk_rows = max(1, min(chunk_rows, n_local))
-        stage = [torch.empty((chunk_rows, F), dtype=torch.float64, device=dev) for _ in range(2)]
-        copied = [torch.cuda.Event() for _ in range(2)]
-        binned = [torch.cuda.Event() for _ in range(2)]
-        copy_s.wait_stream(main)
-        for k, r0 in enumerate(range(0, n_local, chunk_rows)):
-            b = k & 1
+        for k in range(n_chunks):
+            b = k % n_stage
+            r0 = k * chunk_rows
             r1 = min(n_local, r0 + chunk_rows)
-            with torch.cuda.stream(copy_s):
-                if k >= 2:
-                    copy_s.wait_event(binned[b])
-                stage[b][: r1 - r0].copy_(Xh[r0:r1], non_blocking=True)
-                copied[b].record(copy_s)
             main.wait_event(copied[b])
             bin_features(stage[b][: r1 - r0], thr, ns, S["arity_d"], bins=bins, row0=r0, bins_rm=bins_rm, check_errors=False)
             binned[b].record(main)
+            if k + n_stage < n_chunks:
+                issue_copy(k + n_stage)
         main.wait_stream(bag_s)
         _raise_bin_errors(S["arity_d"], S["dist"], group)
         torch.cuda.synchronize(dev)
@@ -634,7 +665,7 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
         forest = _train_loop(S, params, F, n_local, yd, bins, bins_rm, w, node, thr_h, ns_h, group, keep_trace)
         t3 = time.perf_counter()
         forest.timers.update(init=(t0 - t_start) + (t2 - t1), findSplits=t1 - t0, total=t3 - t_start, loop=t3 - t2)
-        forest.counters["kernel_launches"] += 2 + (n_local + chunk_rows - 1) // chunk_rows
+        forest.counters["kernel_launches"] += 2 + n_chunks
         return forest
 
 

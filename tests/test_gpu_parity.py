@@ -371,6 +371,9 @@ def test_fit_host_streams_and_matches_fit_tensors(b2rf, oracle, cuda):
     assert np.array_equal(a.thresholds, b.thresholds) and np.array_equal(a.feature, b.feature) and np.array_equal(a.threshold, b.threshold)
     idx = trainer.sample_indices(42, 0, 40000, a.counters["fraction"])
     assert np.array_equal(idx, np.nonzero(oracle.sample_keep(42, np.arange(40000), a.counters["fraction"]))[0])
+    ids = trainer.sample_row_ids(42, 0, 40000, a.counters["fraction"], cuda)          # the device form fit_host uses
+    assert ids.device.type == "cpu" and np.array_equal(ids.numpy(), idx)
+    assert np.array_equal(trainer.sample_row_ids(42, 1000, 5000, 0.3, cuda).numpy(), trainer.sample_indices(42, 1000, 5000, 0.3))
     bad = X.numpy().copy(); bad[4321, 5] = 99.0
     with pytest.raises(b2rf.IllegalArgumentException, match="Feature 5 is categorical"):
         trainer.fit_host(bad, y.numpy(), arity, b2rf.TreeParams(maxBins=40), device=cuda, chunk_rows=1000)
