@@ -82,7 +82,42 @@ __device__ __forceinline__ void limb_pack_wide(uint32_t w, double yv, LimbScale 
   p1 = make_uint2((uint32_t)x2, (uint32_t)(x2 >> 32));
 }
 
-// G    features per task group = lanes per row (32, 16 or 8); a warp instruction covers 32/G rows
+// The per-plane add values of one row in plane order (what the packed forms above encode), for the plane-split lane mapping:
+//   wide  : L[0] = w, L[1..4] = the four 20-bit limbs of w*y (top one signed), L[5..8] = those of w*y*y
+//   narrow: L[0] = w, L[1..3] / L[4..6] likewise with three limbs
+template <int NP>
+__device__ __forceinline__ void limb_values(uint32_t w, double yv, LimbScale sc, uint32_t (&L)[NP], bool& slow) {
+#pragma unroll
+  for (int i = 0; i < NP; i++) L[i] = 0u;
+  if constexpr (NP == 2) { slow = false; L[0] = w; L[1] = yv != 0.0 ? w : 0u; return; }
+  const double wy = (double)w * yv, wyy = wy * yv;
+  const double ta = wy * sc.sa, tb = wyy * sc.sb;
+  if constexpr (NP == 9) {
+    const double ta40 = ta * 0x1p40, tb40 = tb * 0x1p40;
+    slow = !(ta40 == rint(ta40) && tb40 == rint(tb40));
+    if (slow) return;
+    const double fa = floor(ta), fb = floor(tb);
+    const long long hiA = __double2ll_rz(fa);
+    const unsigned long long loA = __double2ull_rz((ta - fa) * 0x1p40), hiB = __double2ull_rz(fb), loB = __double2ull_rz((tb - fb) * 0x1p40);
+    L[0] = w;
+    L[1] = (uint32_t)loA & LIMB_MASK; L[2] = (uint32_t)(loA >> 20); L[3] = (uint32_t)hiA & LIMB_MASK; L[4] = (uint32_t)(hiA >> 20);
+    L[5] = (uint32_t)loB & LIMB_MASK; L[6] = (uint32_t)(loB >> 20); L[7] = (uint32_t)hiB & LIMB_MASK; L[8] = (uint32_t)(hiB >> 20);
+  } else if constexpr (NP == 7) {
+    const long long v = __double2ll_rn(ta);
+    const unsigned long long u = __double2ull_rn(tb);
+    slow = !((double)v == ta && (double)u == tb);
+    if (slow) return;
+    L[0] = w;
+    L[1] = (uint32_t)v & LIMB_MASK; L[2] = (uint32_t)(v >> 20) & LIMB_MASK; L[3] = (uint32_t)(v >> 40);
+    L[4] = (uint32_t)u & LIMB_MASK; L[5] = (uint32_t)(u >> 20) & LIMB_MASK; L[6] = (uint32_t)(u >> 40);
+  }
+}
+
+// G    features per task group = lanes per row (32, 16 or 8).  G = 32: a warp instruction is one row, lane = feature.  G < 32
+//      ("plane split"): a warp instruction is still ONE row; the H = 32 / G lane groups take the planes p == q (mod H) of the row's
+//      cells.  Cells are [bin][plane][G], so the lanes of one feature (same code) land in different bank groups whatever the code is:
+//      always one wavefront.  (Two or four ROWS per instruction collide whenever any feature's codes agree mod H: measured 2.00
+//      wavefronts per add for G = 16 on C4.)  Packed values: H records per row, record q = the add values of planes q, q + H, ...
 // LDR  bytes per row of the row-major code matrix (0: read a.ldr)
 // BR   rows per staged block (32 or 16)
 // NP   planes per cell: 7 = count + 3 + 3 limbs (narrow), 9 = count + 4 + 4 (wide), 2 = count + sum of w*y (labels all 0 or 1:
@@ -101,7 +136,12 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? (NP == 2 ? 3 : 2) : 
   constexpr int R = 32 / G;                  // rows per warp instruction
   constexpr int NU = BR / R;                 // warp instructions per staged block
   constexpr bool WIDE = NP == 9, BIN = NP == 2;
-  constexpr int VB = WIDE ? 32 : (BIN ? 8 : 16);   // bytes of packed values per row (wide: 24 used)
+  constexpr int H = 32 / G;                    // lane groups
+  constexpr bool PS = G < 32;                  // plane-split mapping
+  constexpr bool SQ = NP == 9 && H == 2;       // five planes for lane group 0: the count rides in bits 20.. of plane 2's word
+  constexpr int KW = SQ ? 4 : (NP + H - 1) / H;                     // words per record
+  constexpr int RB = KW <= 1 ? 4 : (KW == 2 ? 8 : 16);              // bytes per record
+  constexpr int VB = PS ? H * RB : (WIDE ? 32 : (BIN ? 8 : 16));    // bytes of packed values per row (wide, G = 32: 24 used)
   constexpr unsigned FULL = 0xffffffffu;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int ldr = LDR ? LDR : (int)a.ldr;
@@ -220,7 +260,27 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? (NP == 2 ? 3 : 2) : 
       unsigned char* vals = valsBase + s * valBytes;
       const uint32_t w = ent >> 27;
       bool slow = false;
-      if (lane < BR) {
+      if (PS) {
+        if (lane < BR) {
+          uint32_t L[NP];
+          limb_values<NP>(w, yv, sc, L, slow);
+#pragma unroll
+          for (int q = 0; q < H; q++) {
+            uint32_t rec[4] = {0u, 0u, 0u, 0u};
+            if constexpr (SQ) {
+              if (q == 0) { rec[0] = L[2] | (L[0] << 20); rec[1] = L[4]; rec[2] = L[6]; rec[3] = L[8]; }
+              else { rec[0] = L[1]; rec[1] = L[3]; rec[2] = L[5]; rec[3] = L[7]; }
+            } else {
+#pragma unroll
+              for (int k = 0; k < KW; k++) if (q + k * H < NP) rec[k] = L[q + k * H];
+            }
+            unsigned char* d = vals + lane * VB + q * RB;
+            if (RB == 16) *reinterpret_cast<uint4*>(d) = make_uint4(rec[0], rec[1], rec[2], rec[3]);
+            else if (RB == 8) *reinterpret_cast<uint2*>(d) = make_uint2(rec[0], rec[1]);
+            else *reinterpret_cast<uint32_t*>(d) = rec[0];
+          }
+        }
+      } else if (lane < BR) {
         if (BIN) {
           *reinterpret_cast<uint2*>(vals + lane * VB) = make_uint2(w, yv != 0.0 ? w : 0u);
         } else if (WIDE) {
@@ -239,7 +299,37 @@ __global__ void __launch_bounds__(THREADS, THREADS <= 384 ? (NP == 2 ? 3 : 2) : 
     auto consume = [&](const unsigned char* tile, const unsigned char* vals, uint32_t slowMask, int blk) {
       const unsigned char* tl = tile + r * ldr + e.x;
       const unsigned char* vv = vals + r * VB;
-      if (BIN) {
+      if (PS) {
+        if (active) {
+          // one row per instruction; lane group r adds the planes r, r + H, ... of its feature's cell
+          const unsigned char* tp = tile + e.x;
+          const unsigned char* vp = vals + r * RB;
+          uint32_t* cb = hcell + r * G;
+          uint32_t code = tp[0];
+          uint4 rc = make_uint4(0u, 0u, 0u, 0u);
+          auto ldrec = [&](const unsigned char* a) {
+            if (RB == 16) rc = *reinterpret_cast<const uint4*>(a);
+            else if (RB == 8) { const uint2 t2 = *reinterpret_cast<const uint2*>(a); rc.x = t2.x; rc.y = t2.y; }
+            else rc.x = *reinterpret_cast<const uint32_t*>(a);
+          };
+          ldrec(vp);
+#pragma unroll
+          for (int u = 0; u < BR; u++) {
+            const uint32_t cc = code; const uint4 cur = rc;
+            if (u + 1 < BR) { code = tp[(u + 1) * ldr]; ldrec(vp + (u + 1) * VB); }
+            uint32_t* c = cb + cc * (NP * G);
+            if (SQ) {
+              const uint32_t v0 = r ? cur.x : cur.x >> 20, v1 = r ? cur.y : cur.x & LIMB_MASK, v2 = r ? cur.z : cur.y, v3 = r ? cur.w : cur.z;
+              atomicAdd(c, v0); atomicAdd(c + 2 * G, v1); atomicAdd(c + 4 * G, v2); atomicAdd(c + 6 * G, v3);
+              if (r == 0) atomicAdd(c + 8 * G, cur.w);
+            } else {
+              const uint32_t v[4] = {cur.x, cur.y, cur.z, cur.w};
+#pragma unroll
+              for (int k = 0; k < KW; k++) if (r + k * H < NP) atomicAdd(c + k * H * G, v[k]);
+            }
+          }
+        }
+      } else if (BIN) {
         if (active) {
           uint32_t code = tl[0];
           uint2 q = *reinterpret_cast<const uint2*>(vv);
@@ -377,7 +467,11 @@ long long k4_variant_count(int v) { return (v >= 0 && v < B2RF_K4_VARIANTS) ? g_
 // Shared memory of one CTA: the limb histogram, the warps' staging rings (code-row tile slots + two packed-value slots) and, for the
 // TMA form, two mbarriers per warp.
 static size_t limb_smem(int padB, int G, int ldr, int BR, int threads, int NP, bool tma) {
-  const size_t vb = NP == 9 ? 32 : (NP == 2 ? 8 : 16);
+  size_t vb = NP == 9 ? 32 : (NP == 2 ? 8 : 16);
+  if (G < 32) {   // plane split: H records per row (see the kernel's VB)
+    const int H = 32 / G, KW = (NP == 9 && H == 2) ? 4 : (NP + H - 1) / H, RB = KW <= 1 ? 4 : (KW == 2 ? 8 : 16);
+    vb = (size_t)H * RB;
+  }
   const size_t warp = (size_t)(tma ? 2 : 1) * BR * ldr + 2 * (size_t)BR * vb;
   return (size_t)padB * NP * G * 4 + (size_t)(threads / 32) * warp + (size_t)(threads / 32) * 16;
 }
@@ -400,6 +494,8 @@ bool limb_plan(const BucketLaunch& b, int maxBinsAll, int form, bool wantTma, Li
     if (!tma && limb_smem(maxBinsAll, G, ldr, 16, 384, NP, false) <= cap2) { *p = {G, 16, 384, maxBinsAll, NP, 0}; return true; }
     if (limb_smem(maxBinsAll, G, ldr, 32, 256, NP, tma) <= cap2) { *p = {G, 32, 256, maxBinsAll, NP, tma}; return true; }
     if (limb_smem(maxBinsAll, G, ldr, 16, 256, NP, tma) <= cap2) { *p = {G, 16, 256, maxBinsAll, NP, tma}; return true; }
+    // one CTA per SM (large histograms): 24 warps when the rings fit beside the planes (register staging, 16-row blocks), else 16
+    if (!tma && limb_smem(maxBinsAll, G, ldr, 16, 768, NP, false) <= cap1) { *p = {G, 16, 768, maxBinsAll, NP, 0}; return true; }
     if (limb_smem(maxBinsAll, G, ldr, 32, 512, NP, tma) <= cap1) { *p = {G, 32, 512, maxBinsAll, NP, tma}; return true; }
     if (limb_smem(maxBinsAll, G, ldr, 16, 512, NP, tma) <= cap1) { *p = {G, 16, 512, maxBinsAll, NP, tma}; return true; }
   }
@@ -417,6 +513,12 @@ static cudaError_t launch_limb_inst(const BucketLaunch& b, uint32_t* ticket, int
 template <int G, int NP, int BR>
 static cudaError_t launch_limb_g(const BucketLaunch& b, const LimbPlan& p, uint32_t* ticket, int grid, size_t smem, cudaStream_t s) {
   if (!p.tma) {   // register staging: 64- or 128-byte rows
+    if constexpr (BR == 16) {
+      if (p.threads == 768) {
+        if (b.ldr == 64) return launch_limb_inst<G, 64, 16, 768, NP, false>(b, ticket, grid, smem, s);
+        return launch_limb_inst<G, 128, 16, 768, NP, false>(b, ticket, grid, smem, s);
+      }
+    }
     if (b.ldr == 64) {
       if (p.threads == 384) return launch_limb_inst<G, 64, BR, 384, NP, false>(b, ticket, grid, smem, s);
       if (p.threads == 256) return launch_limb_inst<G, 64, BR, 256, NP, false>(b, ticket, grid, smem, s);

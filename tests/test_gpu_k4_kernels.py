@@ -75,7 +75,8 @@ def test_feature_width_edges(b2rf, oracle, cuda, kernel, fsub):
 
 def test_c4_config_depth(b2rf, oracle, cuda, kernel):
     """C4's shape and depth: 96 continuous + 32 categorical features (arity up to 256), maxBins 256, 43 features per node, depth 12:
-    feature groups of 16 (two rows per warp instruction), 512-thread CTAs."""
+    feature groups of 16 (plane-split lane mapping: one row per warp instruction, even / odd planes on the two half-warps), one 768-thread
+    CTA per SM."""
     from b2rf import trainer
     X, y, arity = b2rf.synth.c4(60000, device="cpu")
     before = trainer.k4_launch_counts()
