@@ -249,32 +249,44 @@ def _check_labels(y, params, dist=None, group=None, device=None):
                                            f"TreeParams(numClasses=...) for more than two classes). Found invalid labels.")
 
 
-def bind_host_thread_to_gpu_node(device) -> int | None:
+def bind_host_thread_to_gpu_node(device):
     """Deployment helper for `fit_host` with several GPUs per host: restrict the calling thread (and the threads it starts later) to
-    the CPUs of the NUMA node the GPU hangs off, so that pinned host buffers allocated afterwards are placed on that node and the
-    host-to-device copies of the ranks do not all cross the inter-socket link.  Returns the node, or None when sysfs does not say
-    (single-socket hosts, containers without /sys/bus/pci) — then nothing is changed."""
+    the CPUs next to the GPU, so that pinned host buffers allocated afterwards are placed on that NUMA node and the host-to-device
+    copies of the ranks do not all cross the inter-socket link.  The CPU set comes from sysfs (the PCI device's numa_node) or, where a
+    container hides that, from NVML's CPU affinity of the device.  Returns a short description of what was applied, or None when
+    neither source says anything (single-socket hosts) — then nothing is changed."""
     import os
+    pr = torch.cuda.get_device_properties(device)
+    allowed = os.sched_getaffinity(0)
+    cpus, how = set(), None
     try:
-        pr = torch.cuda.get_device_properties(device)
         addr = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
         with open(f"/sys/bus/pci/devices/{addr}/numa_node") as f:
             node = int(f.read().strip())
-        if node < 0:
-            return None
-        with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
-            txt = f.read().strip()
-        cpus = set()
-        for part in txt.split(","):
-            lo, _, hi = part.partition("-")
-            cpus.update(range(int(lo), int(hi or lo) + 1))
-        cpus &= os.sched_getaffinity(0)
-        if not cpus:
-            return None
-        os.sched_setaffinity(0, cpus)
-        return node
+        if node >= 0:
+            with open(f"/sys/devices/system/node/node{node}/cpulist") as f:
+                for part in f.read().strip().split(","):
+                    lo, _, hi = part.partition("-")
+                    cpus.update(range(int(lo), int(hi or lo) + 1))
+            how = f"sysfs numa node {node}"
     except (OSError, ValueError, AttributeError):
-        return None
+        pass
+    if not cpus:
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = pynvml.nvmlDeviceGetHandleByPciBusId(f"{pr.pci_domain_id:08x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0".encode())
+            ncpu = max(os.cpu_count() or 1, max(allowed) + 1)
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, (ncpu + 63) // 64)
+            cpus = {i for i in range(ncpu) if (int(words[i // 64]) >> (i % 64)) & 1}
+            how = "nvml cpu affinity"
+        except Exception:   # noqa: BLE001 — NVML absent or too old: leave the placement to the default policy
+            return None
+    cpus &= allowed
+    if not cpus or cpus == allowed:
+        return None          # nothing to narrow
+    os.sched_setaffinity(0, cpus)
+    return f"{how}: {len(cpus)} of {len(allowed)} cpus"
 
 
 def k4_launch_counts() -> dict:
