@@ -2,7 +2,7 @@
 code-row width, register vs TMA staging), bins, label kinds (real / integer / 0-1), depth, memory budget (group cuts), partition layout
 and featureSubsetStrategy drawn from a seeded generator.  Every case must equal the oracle's forest up to documented gain ties; cases
 without ties must match bit for bit in structure and to 1e-9 in sums (helpers.assert_parity_allowing_ties).
-B2RF_SWEEP_CASES sets the number of cases (default 14; scratch runs use a few hundred)."""
+B2RF_SWEEP_CASES sets the number of cases (default 24; profiles/r02_parity_sweep.md records a 600-case run)."""
 import os
 
 import numpy as np
@@ -13,7 +13,7 @@ from helpers import assert_parity_allowing_ties, assert_classifier_parity
 from test_gpu_parity import _fit_both
 
 pytestmark = pytest.mark.gpu
-N_CASES = int(os.environ.get("B2RF_SWEEP_CASES", "14"))
+N_CASES = int(os.environ.get("B2RF_SWEEP_CASES", "24"))
 
 
 def _case(i):
