@@ -66,3 +66,44 @@ def test_sweep_case(b2rf, oracle, cuda, i):
         assert_parity_allowing_ties(g, o, max_ties=6 + c["F"] // 4, subsampling=sub, min_fraction=0.0)
     else:
         assert_classifier_parity(g, o, exact=(c["impurity"] == "gini"))
+
+
+N_MC = int(os.environ.get("B2RF_SWEEP_MC_CASES", "6"))
+
+
+@pytest.mark.parametrize("i", range(N_MC))
+def test_sweep_multiclass_case(b2rf, cuda, i):
+    """The same for multiclass classification (class-count histograms: staged kernel for 64- / 128-byte code rows, gather kernel
+    otherwise; unordered and impurity-ordered categorical splits) against oracle/multiclass.py."""
+    from oracle import multiclass as M
+    from test_gpu_multiclass import _parity
+    rng = np.random.default_rng(5000 + i)
+    F = int(rng.choice([5, 9, 16, 17, 33, 50, 64, 70, 100, 130]))
+    n = int(rng.choice([800, 3000, 6000]))
+    C = int(rng.choice([3, 4, 5, 7]))
+    bins = int(rng.choice([16, 32, 64]))
+    T = int(rng.choice([1, 3, 4]))
+    kw = dict(maxDepth=int(rng.integers(2, 6)), maxBins=bins, numTrees=T, bootstrap=T > 1, seed=int(rng.integers(1, 999)),
+              featureSubsetStrategy=str(rng.choice(["all", "auto", "onethird"])) if T > 1 else "all", maxMemoryInMB=int(rng.choice([256, 1])))
+    impurity = str(rng.choice(["gini", "gini", "entropy"]))
+    X, y, arity = b2rf.synth.c3(n, device="cpu", F=F, seed=int(rng.integers(1, 9999)))
+    Xn = X.numpy().copy()
+    arity = list(arity)
+    for f in rng.choice(F, size=min(3, F // 3), replace=False):
+        k = int(rng.integers(2, min(bins, 9) + 1))          # small arities: unordered splits for some, ordered for others
+        Xn[:, f] = rng.integers(0, k, size=n).astype(np.float64)
+        arity[int(f)] = k
+    yn = y.numpy()
+    lab = np.digitize(yn, np.quantile(yn, np.linspace(0, 1, C + 1)[1:-1])).astype(np.float64)
+    po = np.array([0, n // 3, n // 2, n], np.int64)
+    m = M.fit(Xn, lab, arity, C, part_offsets=po, impurity=impurity, **kw)
+    g = b2rf.trainer.fit_tensors(torch.as_tensor(Xn, device=cuda), torch.as_tensor(lab, device=cuda), arity,
+                                 b2rf.TreeParams(impurity=impurity, numClasses=C, **kw), part_offsets=po, keep_trace=True)
+    print("multiclass case", i, dict(F=F, n=n, C=C, bins=bins, impurity=impurity, **kw), "nodes", int(g.num_nodes()))
+    _parity(g, m)
+    mi = m.impurity >= 0
+    if impurity == "gini":
+        assert np.array_equal(g.impurity[mi], m.impurity[mi]) and np.array_equal(g.gain, m.gain)
+    else:
+        np.testing.assert_allclose(g.impurity[mi], m.impurity[mi], rtol=1e-12, atol=1e-15)
+        np.testing.assert_allclose(g.gain, m.gain, rtol=1e-9, atol=1e-13)
