@@ -21,3 +21,23 @@ for mode in ("segment", "scan"):
 f = trainer.fit_host(X.numpy(), y.numpy(), arity, b2rf.TreeParams(maxDepth=4, maxBins=40, numTrees=2, bootstrap=False, subsamplingRate=0.7, seed=3), device=dev, chunk_rows=700)
 m = trainer.fit_many_tensors(Xd, yd, arity, [b2rf.TreeParams(maxDepth=3, maxBins=40, numTrees=2, bootstrap=True, seed=4), b2rf.TreeParams(maxDepth=2, maxBins=40)])
 print("ok", f.num_nodes(), [q.num_nodes() for q in m])
+# round 2 kernels: limb forms (wide / narrow / two-plane) at feature groups of 32 / 16 / 8 with register and TMA staging, the staged and the
+# gather class-count kernels, the device sampler ids, the sharded-K5 pack / unpack path emulated on one GPU
+import ctypes as C
+for F, strat in [(64, "all"), (64, "onethird"), (40, "onethird"), (12, "all"), (12, "sqrt"), (140, "onethird"), (100, "all")]:
+    Xs, ys, ars = b2rf.synth.c3(6000, device="cpu", F=F)
+    for lab, imp in [(ys, "variance"), (torch.round(ys * 3), "variance"), ((ys > ys.median()).double(), "gini")]:
+        for tma in (0, 1):
+            trainer.set_option("k4_tma", tma)
+            f = trainer.fit_tensors(Xs.to(dev), lab.to(dev), ars, b2rf.TreeParams(maxDepth=5, maxBins=64, numTrees=2, bootstrap=True, seed=5, impurity=imp,
+                                                                                   featureSubsetStrategy=strat), part_offsets=trainer.default_partitions(6000, 2048))
+    print("limb", F, strat, f.num_nodes(), flush=True)
+trainer.set_option("k4_tma", 0)
+for F in (50, 100, 70 + 66):
+    Xs, ys, ars = b2rf.synth.c3(6000, device="cpu", F=F)
+    lab = torch.bucketize(ys, torch.quantile(ys, torch.tensor([0.25, 0.5, 0.75], dtype=torch.float64))).double()
+    f = trainer.fit_tensors(Xs.to(dev), lab.to(dev), ars, b2rf.TreeParams(maxDepth=5, maxBins=32, numTrees=3, bootstrap=True, seed=6, impurity="gini", numClasses=4))
+    print("multiclass", F, f.num_nodes(), flush=True)
+ids = trainer.sample_row_ids(42, 0, 50000, 0.2, dev)
+print("sampler ids", len(ids), flush=True)
+print("round 2 kernels ok")
