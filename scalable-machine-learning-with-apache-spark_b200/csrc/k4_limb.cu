@@ -18,10 +18,13 @@
 //   * Tasks whose labels are not finite or lie outside 2^+-460 take the plain fp64 path (global atomics: MLlib's own overflow /
 //     underflow behaviour), as do tasks with fewer updates than histogram cells.
 // Data path.  Labels travel WITH the per-tree row lists (a y list parallel to the packed row | weight list, moved by the K6
-// partitions): a row visit costs one code-row gather instead of that plus a 32 B label sector.  The code rows of the next block
-// are fetched by the TMA engine — one bulk async copy per row (cp.async.bulk, SASS UBLKCP) completing on an mbarrier, two
-// stages per warp — while the warp adds the current block; a lane reads its feature's code with one LDS.U8 and the row's packed
-// limbs with one or two broadcast loads at immediate offsets: no 64-bit address arithmetic and no load-to-use stall in the loop.
+// partitions): a row visit costs one code-row gather instead of that plus a 32 B label sector.  The code rows of a warp's next block
+// are fetched one block ahead — by default with 16-byte loads held in registers (ld.global.nc.L2::64B: a 64-byte DRAM fetch per
+// miss instead of the 128-byte line) and stored to the warp's shared-memory tile just before use; for row widths other than 64 /
+// 128 bytes, or on request, by the TMA engine (one cp.async.bulk per row completing on an mbarrier, two stages per warp).  A lane
+// reads its feature's code with one LDS.U8 and the row's packed limbs with one or two broadcast loads at immediate offsets: no
+// 64-bit address arithmetic and no load-to-use stall in the loop.  Feature groups narrower than 32 split the limb PLANES, not the
+// rows, over the lane groups, so every add is conflict-free (see the kernel's parameter list).
 // Compiled with -fmad=false like the rest of the library.
 #include "b2rf_internal.h"
 #include "b2rf_device.cuh"
