@@ -592,18 +592,21 @@ def sample_indices(seed: int, row0_global: int, n_rows: int, fraction: float) ->
 
 def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_offsets=None, part0: int = None, group=None,
              keep_trace: bool = False, hist_mode: str = "segment", chunk_rows: int = 1 << 20) -> Forest:
-    """Public host-buffer entry point (what the Spark adapter's single-estimator fit calls): X_host f64 [n, F] / y_host f64 [n] are HOST arrays
-    (numpy or CPU torch tensors; pinned memory makes the copies asynchronous).
+    """Public host-buffer entry point (what the Spark adapter's single-estimator fit calls): X_host f64 or f32 [n, F] / y_host f64 [n] are
+    HOST arrays (numpy or CPU torch tensors; pinned memory makes the copies asynchronous).  float32 features are copied as float32 and
+    widened on the device, which trains exactly the forest of the widened matrix.
 
     The raw feature matrix never has to be resident on the GPU: the findSplits row sample is gathered on the host (5 MB),
     then X streams through up to four staging buffers in `chunk_rows` pieces — copies on one stream (the first ones start before
     the thresholds exist), K2 binning of the arrived pieces on another — while K3 bagging, which does not depend on X, runs
     concurrently on a third stream."""
     dev = torch.device(device)
-    Xh = torch.as_tensor(X_host, dtype=torch.float64)
+    Xh = torch.as_tensor(X_host)
+    if Xh.dtype != torch.float32:          # float32 features travel as they are (half the PCIe bytes) and are widened on the device: exact
+        Xh = Xh.to(torch.float64)
     yh = torch.as_tensor(y_host, dtype=torch.float64)
     if Xh.is_cuda:
-        return fit_tensors(Xh, yh.to(Xh.device), arity, params, part_offsets=part_offsets, part0=part0, group=group,
+        return fit_tensors(Xh.to(torch.float64), yh.to(Xh.device), arity, params, part_offsets=part_offsets, part0=part0, group=group,
                            keep_trace=keep_trace, hist_mode=hist_mode)
     if not Xh.is_contiguous():
         Xh = Xh.contiguous()
@@ -629,7 +632,8 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
         chunk_rows = max(1, min(chunk_rows, n_local))
         n_chunks = (n_local + chunk_rows - 1) // chunk_rows
         n_stage = max(2, min(4, n_chunks))
-        stage = [torch.empty((chunk_rows, F), dtype=torch.float64, device=dev) for _ in range(n_stage)]
+        stage = [torch.empty((chunk_rows, F), dtype=Xh.dtype, device=dev) for _ in range(n_stage)]
+        wide = torch.empty((chunk_rows, F), dtype=torch.float64, device=dev) if Xh.dtype != torch.float64 else None
         copied = [torch.cuda.Event() for _ in range(n_stage)]
         binned = [torch.cuda.Event() for _ in range(n_stage)]
         copy_s.wait_stream(main)
@@ -646,7 +650,7 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
 
         # K1 on the host-gathered sample; its (small) copy is queued ahead of the big pieces, which then stream while K1 runs
         fraction = S["fraction"]
-        samp = Xh[sample_row_ids(params.seed, S["row0"], n_local, fraction, dev)].to(dev) if fraction < 1.0 else Xh.to(dev)
+        samp = (Xh[sample_row_ids(params.seed, S["row0"], n_local, fraction, dev)].to(dev) if fraction < 1.0 else Xh.to(dev)).to(torch.float64)
         for k in range(min(n_stage, n_chunks)):
             issue_copy(k)
         samp = gather_samples(samp, S["dist"], group)
@@ -663,7 +667,11 @@ def fit_host(X_host, y_host, arity, params: TreeParams, device="cuda:0", part_of
             r0 = k * chunk_rows
             r1 = min(n_local, r0 + chunk_rows)
             main.wait_event(copied[b])
-            bin_features(stage[b][: r1 - r0], thr, ns, S["arity_d"], bins=bins, row0=r0, bins_rm=bins_rm, check_errors=False)
+            piece = stage[b][: r1 - r0]
+            if wide is not None:
+                wide[: r1 - r0].copy_(piece)
+                piece = wide[: r1 - r0]
+            bin_features(piece, thr, ns, S["arity_d"], bins=bins, row0=r0, bins_rm=bins_rm, check_errors=False)
             binned[b].record(main)
             if k + n_stage < n_chunks:
                 issue_copy(k + n_stage)

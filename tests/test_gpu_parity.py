@@ -374,6 +374,12 @@ def test_fit_host_streams_and_matches_fit_tensors(b2rf, oracle, cuda):
     ids = trainer.sample_row_ids(42, 0, 40000, a.counters["fraction"], cuda)          # the device form fit_host uses
     assert ids.device.type == "cpu" and np.array_equal(ids.numpy(), idx)
     assert np.array_equal(trainer.sample_row_ids(42, 1000, 5000, 0.3, cuda).numpy(), trainer.sample_indices(42, 1000, 5000, 0.3))
+    X32 = Xc.to(torch.float32)                                                     # float32 host features: copied as they are, widened on the device
+    c32 = trainer.fit_host(X32.numpy(), yc, ar, p, device=cuda, chunk_rows=9000)
+    r32 = trainer.fit_tensors(X32.to(torch.float64).to(cuda), yc.to(cuda), ar, p)
+    assert np.array_equal(c32.thresholds, r32.thresholds) and np.array_equal(c32.feature, r32.feature) and np.array_equal(c32.threshold, r32.threshold)
+    assert np.array_equal(c32.stats[:, 0], r32.stats[:, 0])
+    np.testing.assert_allclose(c32.stats, r32.stats, rtol=1e-12)      # real-valued sums: the order of the tasks' global adds differs run to run
     bad = X.numpy().copy(); bad[4321, 5] = 99.0
     with pytest.raises(b2rf.IllegalArgumentException, match="Feature 5 is categorical"):
         trainer.fit_host(bad, y.numpy(), arity, b2rf.TreeParams(maxBins=40), device=cuda, chunk_rows=1000)
