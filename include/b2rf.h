@@ -195,6 +195,9 @@ int b2rf_trainer_export(b2rf_trainer* t, int64_t* h_tree_off, int32_t* h_feature
  * h_counts[n_nodes][numClasses] (the model's impurityStats).  0 / B2RF_ERR_STATE for a regression trainer. */
 int b2rf_trainer_num_classes(const b2rf_trainer* t);
 int b2rf_trainer_export_class_counts(b2rf_trainer* t, double* h_counts);
+/* The trace is recorded only after b2rf_trainer_set_trace(t, 1) (call before the first begin_group); off by default: one 72-byte row per
+ * evaluated node is measurable host work on the critical path of large forests. */
+int b2rf_trainer_set_trace(b2rf_trainer* t, int32_t on);
 int64_t b2rf_trainer_trace_size(const b2rf_trainer* t);
 /* Evidence / test hook: how many times this process launched each K4 implementation, h_counts[i] for i < n:
  * 0 limb kernel (native 32-bit shared-memory adds on fixed-point limbs; default of the segment mode), 1 fp64 kernel for

@@ -56,6 +56,7 @@ _SIGS = {
     "b2rf_trainer_stats": (C.c_int, [vp, vp, vp]),
     "b2rf_trainer_forest_sizes": (C.c_int, [vp, vp, vp]),
     "b2rf_trainer_export": (C.c_int, [vp] * 14),
+    "b2rf_trainer_set_trace": (C.c_int, [vp, i32]),
     "b2rf_trainer_trace_size": (i64, [vp]),
     "b2rf_trainer_trace": (C.c_int, [vp, vp, vp]),
     "b2rf_k4_launch_counts": (C.c_int, [vp, i32]),

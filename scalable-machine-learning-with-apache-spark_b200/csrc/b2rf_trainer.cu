@@ -338,6 +338,7 @@ struct b2rf_trainer {
   // trace + stats
   struct Trace { int32_t g, t, id, f, s; double gain, imp, cnt, sum, sq; };
   std::vector<Trace> trace;
+  bool keepTrace = false;   // b2rf_trainer_set_trace: record one Trace row per evaluated node (tests / parity tooling)
   double tHist = 0, tChoose = 0, tStart = 0, tTotal = 0;
   double tSelect = 0, tTail = 0, tWait = 0;   // host shares of tChoose (begin_group / end_group) and the end_group wait; printed with B2RF_TIMING=1
   int64_t nHistLaunches = 0, nScanned = 0, nKernels = 0;
@@ -1003,7 +1004,7 @@ static int end_group_tail(b2rf_trainer* t, cudaStream_t s) {
       for (int q = 0; q < 4; q++) n.stats.calc[q] = r.parent[q];
       const double* cls3 = t->C ? t->hClsOut.p + (size_t)sl * 3 * t->Cp : nullptr;
       if (t->C) { n.cls = (int64_t)t->clsPool.size(); t->clsPool.insert(t->clsPool.end(), cls3, cls3 + t->C); }
-      t->trace.push_back({t->groupNo, tr, id, r.feature, r.splitIdx, r.gain, r.impurity, r.parent[0], r.parent[1], r.parent[2]});
+      if (t->keepTrace) t->trace.push_back({t->groupNo, tr, id, r.feature, r.splitIdx, r.gain, r.impurity, r.parent[0], r.parent[1], r.parent[2]});
       t->weightedRows += r.parent[0];
       if (!isLeaf) {
         n.hasSplit = true; n.feature = r.feature;
@@ -1360,6 +1361,12 @@ int b2rf_trainer_export_class_counts(b2rf_trainer* t, double* h_counts) {
   ExportOut o{};
   o.cls = h_counts;
   export_write(t, o);
+  return B2RF_OK;
+}
+
+int b2rf_trainer_set_trace(b2rf_trainer* t, int32_t on) {
+  if (!t) return B2RF_ERR_ARG;
+  t->keepTrace = on != 0;
   return B2RF_OK;
 }
 

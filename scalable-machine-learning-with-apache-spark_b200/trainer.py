@@ -325,6 +325,8 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
     try:
         # rows sharded over ranks: reduce-scatter the group histogram by node, K5 on the own node slots, all-gather the split records
         # (segment mode; B2RF_SHARD_K5=0 or a histogram hook keep the all-reduce + redundant K5 of every rank)
+        if keep_trace:
+            check(L.b2rf_trainer_set_trace(h, 1))
         world, dist = S["world"], S["dist"]
         shard = world > 1 and node is None and hist_hook is None and os.environ.get("B2RF_SHARD_K5", "1") != "0"
         if shard:
