@@ -165,10 +165,36 @@ struct BlockPool {
       if (best >= 0) { Block b = free_[best]; free_.erase(free_.begin() + best); *got = b.bytes; return b.p; }
     }
     void* p = nullptr;
-    const cudaError_t e = pinned ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
+    cudaError_t e = pinned ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
+    if (e == cudaErrorMemoryAllocation && trim() > 0) {   // the cached blocks of earlier fits are in the way: give them back and try again
+      cudaGetLastError();
+      e = pinned ? cudaMallocHost(&p, bytes) : cudaMalloc(&p, bytes);
+    }
     if (!cuda_ok(e, pinned ? "trainer pinned alloc" : "trainer device alloc")) return nullptr;
     *got = bytes;
     return p;
+  }
+  // bytes of cached (unused) blocks of the current device / of pinned memory
+  size_t cached() {
+    std::lock_guard<std::mutex> lk(mu);
+    const int dev = pinned ? -1 : current_device();
+    size_t n = 0;
+    for (const Block& b : free_) if (b.dev == dev) n += b.bytes;
+    return n;
+  }
+  // frees every cached block of the current device; returns the bytes released
+  size_t trim() {
+    std::vector<Block> drop;
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      const int dev = pinned ? -1 : current_device();
+      for (size_t i = 0; i < free_.size();) {
+        if (free_[i].dev == dev) { drop.push_back(free_[i]); free_[i] = free_.back(); free_.pop_back(); } else i++;
+      }
+    }
+    size_t n = 0;
+    for (const Block& b : drop) { if (pinned) cudaFreeHost(b.p); else cudaFree(b.p); n += b.bytes; }
+    return n;
   }
   void give(void* p, size_t bytes) {
     if (!p) return;
@@ -554,8 +580,13 @@ int b2rf_trainer_bind(b2rf_trainer* t, const void* d_bins_v, int64_t ldb, const 
         const bool want = opt_carry_labels().load() != 0;
         size_t freeB = 0, totB = 0;
         const size_t have = t->dY0.bytes + t->dY1.bytes;
-        if (want && cudaMemGetInfo(&freeB, &totB) == cudaSuccess && (have >= 2 * total * 8 || freeB + have > 2 * total * 8 + ((size_t)4 << 30)))
-          t->carryY = t->dY0.ensure(total) && t->dY1.ensure(total);
+        const size_t needY = 2 * total * 8 + ((size_t)4 << 30);
+        bool fits = want && cudaMemGetInfo(&freeB, &totB) == cudaSuccess && (have >= 2 * total * 8 || freeB + have > needY);
+        if (want && !fits && freeB + have + device_pool().cached() > needY) {   // blocks cached from earlier (smaller) fits would make the difference
+          device_pool().trim();
+          fits = cudaMemGetInfo(&freeB, &totB) == cudaSuccess && freeB + have > needY;
+        }
+        if (fits) t->carryY = t->dY0.ensure(total) && t->dY1.ensure(total);
         if (!t->carryY) { t->dY0.release(); t->dY1.release(); }
       }
       t->labelsInt = false; t->labels01 = false;

@@ -333,6 +333,9 @@ def _train_loop(S, params, F, n_local, y, bins, bins_rm, w, node, thr_h, ns_h, g
             check(L.b2rf_trainer_set_shard(h, dist.get_rank(group), world))
         cells = int(L.b2rf_trainer_max_group_cells(h))
         hist = torch.empty(cells * 4, dtype=torch.float64, device=dev)
+        free_b, total_b = torch.cuda.mem_get_info(dev)
+        if free_b < 0.5 * total_b:          # a large fit: hand torch's cached blocks back so that the trainer's row and label lists fit
+            torch.cuda.empty_cache()
         xin = xall = None
         ld = w.stride(0)
         check(L.b2rf_trainer_bind(h, bins.data_ptr(), bins.stride(0), 0 if bins_rm is None else bins_rm.data_ptr(),
