@@ -35,9 +35,10 @@ for k, c in counts.items():
     if not c["insts"]:
         continue
     if "limb_hist_kernel" in k and k not in ("limb_hist_kernel<32, 64, 16, 384, 9, false>", "limb_hist_kernel<32, 64, 16, 256, 9, true>", "limb_hist_kernel<32, 64, 32, 384, 7, false>",
-                                             "limb_hist_kernel<16, 128, 16, 512, 9, false>", "limb_hist_kernel<16, 0, 32, 256, 7, true>"):
+                                             "limb_hist_kernel<16, 128, 16, 768, 9, false>", "limb_hist_kernel<16, 0, 32, 256, 7, true>", "limb_hist_kernel<8, 64, 32, 384, 2, false>",
+                                             "limb_hist_kernel<16, 64, 32, 384, 9, false>"):
         continue   # one line per representative instantiation keeps the table readable
     print(f"| `{k}` | " + " | ".join(str(c[x]) if c[x] else "" for x in cols) + " |")
 n_limb = sum(1 for k in counts if "limb_hist_kernel" in k)
-print(f"\n{n_limb} instantiations of limb_hist_kernel<G, LDR, BR, THREADS, NP, TMA> are compiled; the table lists the ones the named configurations run: C3 <32, 64, 16, 384, 9, false> (and its TMA-staged twin), integer labels <32, 64, 32, 384, 7, false>, C4 <16, 128, 16, 512, 9, false>, the Airbnb-shaped tables <16, 0, 32, 256, 7, true> (48-byte rows: TMA staging).")
+print(f"\n{n_limb} instantiations of limb_hist_kernel<G, LDR, BR, THREADS, NP, TMA> are compiled; the table lists the ones the named configurations run: C3 <32, 64, 16, 384, 9, false> (and its TMA-staged twin), integer labels <32, 64, 32, 384, 7, false>, C4 <16, 128, 16, 768, 9, false> (plane-split lane mapping, one CTA of 24 warps per SM), 11 - 16 features per node on 64-byte rows <16, 64, 32, 384, 9, false>, 0 / 1 labels with 8 features per node <8, 64, 32, 384, 2, false> (two planes), rows padded to 16 bytes <16, 0, 32, 256, 7, true> (TMA staging at a run-time width).")
 print("No kernel contains tensor-core instructions (HMMA / UTC*MMA): nothing on this path is a dense contraction.")
